@@ -1,0 +1,164 @@
+"""Decoder shapes for the scoring path.
+
+The reference never names shapes itself: it calls ``AutoModelForCausalLM.from_pretrained``
+(reference ``analysis/run_base_vs_instruct_100q.py:426-450``).  The shapes below are the
+ones SURVEY.md Appendix C records (Falcon-7B = ``transformers`` ``FalconConfig()`` defaults;
+the GPT-NeoX ones recalled from the public ``config.json`` files) plus tiny variants of each
+family that the parity tests run against the HF CPU path.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, asdict, replace
+
+# arch codes (must match include/b200score.h)
+ARCH_FALCON = 0
+ARCH_GPT_NEOX = 1
+
+# qkv column layouts (must match include/b200score.h)
+QKV_FALCON_MQA = 0       # [q_0 .. q_{nh-1}, k, v] each head_dim wide   (HF falcon _split_heads, multi_query)
+QKV_NEOX_INTERLEAVED = 1  # per head [q, k, v]                            (HF gpt_neox qkv.chunk(3))
+
+# compute modes (must match include/b200score.h)
+MODE_BF16_FAST = 0    # bf16 MMA operands, fp32 accumulate in TMEM, fp32 residual stream
+MODE_FP32_CHECK = 3   # fp32 weights + activations on CUDA cores; parity gate 1e-5
+
+
+@dataclass(frozen=True)
+class DecoderShape:
+    name: str
+    arch: int
+    n_layer: int
+    d_model: int
+    n_head: int
+    n_kv_head: int
+    head_dim: int
+    d_ff: int
+    vocab: int
+    rotary_dim: int
+    rope_theta: float = 10000.0
+    norm_eps: float = 1e-5
+    parallel_residual: bool = True
+    n_ln_per_layer: int = 1
+    has_bias: bool = False
+    tied_head: bool = True
+    qkv_layout: int = QKV_FALCON_MQA
+    eos_id: int = 11
+    max_pos: int = 2048
+
+    @property
+    def qkv_dim(self) -> int:
+        return (self.n_head + 2 * self.n_kv_head) * self.head_dim
+
+    @property
+    def layer_params(self) -> int:
+        d, ff = self.d_model, self.d_ff
+        return d * self.qkv_dim + d * self.n_head * self.head_dim + 2 * d * ff
+
+    def flops_per_token(self) -> float:
+        """Algorithmic GEMM FLOPs per prompt token."""
+        return 2.0 * self.n_layer * self.layer_params
+
+    def flops_per_position(self) -> float:
+        """LM-head FLOPs per scored position."""
+        return 2.0 * self.vocab * self.d_model
+
+    def attn_flops(self, L: int) -> float:
+        """Causal attention FLOPs for one prompt of L tokens (QK^T and PV, half masked)."""
+        return 4.0 * L * L * self.n_head * self.head_dim * self.n_layer / 2.0
+
+    def to_dict(self):
+        return asdict(self)
+
+    def with_layers(self, n):
+        return replace(self, n_layer=n, name=f"{self.name}-L{n}")
+
+
+def falcon_7b() -> DecoderShape:
+    # HF:models/falcon/configuration_falcon.py:53-76
+    return DecoderShape("falcon-7b", ARCH_FALCON, 32, 4544, 71, 1, 64, 18176, 65024, 64,
+                        parallel_residual=True, n_ln_per_layer=1, has_bias=False, tied_head=True,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=11)
+
+
+def stablelm_alpha_7b() -> DecoderShape:
+    return DecoderShape("stablelm-base-alpha-7b", ARCH_GPT_NEOX, 16, 6144, 48, 48, 128, 24576, 50432, 32,
+                        parallel_residual=True, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0, max_pos=4096)
+
+
+def redpajama_7b() -> DecoderShape:
+    return DecoderShape("redpajama-incite-7b", ARCH_GPT_NEOX, 32, 4096, 32, 32, 128, 16384, 50432, 128,
+                        parallel_residual=False, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
+
+
+def redpajama_3b() -> DecoderShape:
+    return DecoderShape("redpajama-incite-base-3b", ARCH_GPT_NEOX, 32, 2560, 32, 32, 80, 10240, 50432, 80,
+                        parallel_residual=False, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
+
+
+def h2ogpt_12b() -> DecoderShape:
+    return DecoderShape("h2ogpt-oasst1-512-12b", ARCH_GPT_NEOX, 36, 5120, 40, 40, 128, 20480, 50688, 32,
+                        parallel_residual=True, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
+
+
+def dolly_v2_7b() -> DecoderShape:
+    # pythia-6.9b shape
+    return DecoderShape("dolly-v2-7b", ARCH_GPT_NEOX, 32, 4096, 32, 32, 128, 16384, 50280, 32,
+                        parallel_residual=True, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
+
+
+# tiny variants (CPU-oracle sized) --------------------------------------------------------
+def tiny_falcon(vocab=256, n_layer=2, n_head=3) -> DecoderShape:
+    hd = 64
+    d = n_head * hd
+    return DecoderShape("tiny-falcon", ARCH_FALCON, n_layer, d, n_head, 1, hd, 4 * d, vocab, hd,
+                        parallel_residual=True, n_ln_per_layer=1, has_bias=False, tied_head=True,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=11)
+
+
+def tiny_neox_parallel(vocab=320, n_layer=2, n_head=2) -> DecoderShape:
+    # StableLM-alpha-like: hd 128, rotary_pct 0.25, parallel residual, biases
+    hd = 128
+    d = n_head * hd
+    return DecoderShape("tiny-neox-par", ARCH_GPT_NEOX, n_layer, d, n_head, n_head, hd, 4 * d, vocab, 32,
+                        parallel_residual=True, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
+
+
+def tiny_neox_sequential(vocab=200, n_layer=2, n_head=2) -> DecoderShape:
+    # RedPajama-3B-like: hd 80, full rotary, sequential residual, biases
+    hd = 80
+    d = n_head * hd
+    return DecoderShape("tiny-neox-seq", ARCH_GPT_NEOX, n_layer, d, n_head, n_head, hd, 4 * d, vocab, hd,
+                        parallel_residual=False, n_ln_per_layer=2, has_bias=True, tied_head=False,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
+
+
+REGISTRY = {
+    "falcon-7b": falcon_7b,
+    "stablelm-base-alpha-7b": stablelm_alpha_7b,
+    "redpajama-incite-7b": redpajama_7b,
+    "redpajama-incite-base-3b": redpajama_3b,
+    "h2ogpt-oasst1-512-12b": h2ogpt_12b,
+    "dolly-v2-7b": dolly_v2_7b,
+    "tiny-falcon": tiny_falcon,
+    "tiny-neox-par": tiny_neox_parallel,
+    "tiny-neox-seq": tiny_neox_sequential,
+}
+
+# HF hub name -> shape, for the kept entry points (random-init; no weights offline)
+HUB_TO_SHAPE = {
+    "tiiuae/falcon-7b": falcon_7b, "tiiuae/falcon-7b-instruct": falcon_7b,
+    "stabilityai/stablelm-base-alpha-7b": stablelm_alpha_7b,
+    "stabilityai/stablelm-tuned-alpha-7b": stablelm_alpha_7b,
+    "togethercomputer/RedPajama-INCITE-7B-Base": redpajama_7b,
+    "togethercomputer/RedPajama-INCITE-7B-Instruct": redpajama_7b,
+    "togethercomputer/RedPajama-INCITE-Base-3B-v1": redpajama_3b,
+    "togethercomputer/RedPajama-INCITE-Instruct-3B-v1": redpajama_3b,
+    "h2oai/h2ogpt-oasst1-512-12b": h2ogpt_12b,
+    "EleutherAI/pythia-6.9b": dolly_v2_7b, "databricks/dolly-v2-7b": dolly_v2_7b,
+}

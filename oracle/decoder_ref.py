@@ -1,0 +1,149 @@
+"""Plain torch-fp32 restatement of the decoder forward the reference runs through HF
+``transformers`` (test infrastructure only; never imported by the product package).
+
+Follows, for the two families on the hot path:
+  Falcon   HF:models/falcon/modeling_falcon.py:60-99 (linear, rotate_half RoPE), :154-165 (cos/sin),
+           :285-288 (MQA qkv split), :316-378 (attention), :531-544 (MLP, exact GELU),
+           :580-636 (parallel-attn layer, single input_layernorm), :700-834 (model), :905-906 (head)
+  GPT-NeoX HF:models/gpt_neox/modeling_gpt_neox.py:38-49 (MLP), :126-159 (partial rotary),
+           :203-244 (attention, per-head [q,k,v] interleave), :258-289 (layer, parallel/sequential),
+           :331-381 (model), :463-464 (embed_out)
+It is validated against the HF modules themselves in tests/test_oracle_decoder.py, and is what the
+GPU parity tests call (it is faster than ``generate`` and can emulate bf16 operand rounding).
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict, List, Optional
+
+import torch
+import torch.nn.functional as F
+
+from llm_interpretation_replication_b200.shapes import DecoderShape, QKV_FALCON_MQA
+
+
+def _rope_cos_sin(shape: DecoderShape, L: int):
+    rd = shape.rotary_dim
+    inv_freq = 1.0 / (shape.rope_theta ** (torch.arange(0, rd, 2, dtype=torch.int64).float() / rd))
+    pos = torch.arange(L, dtype=torch.float32)
+    freqs = pos[:, None] * inv_freq[None, :]
+    emb = torch.cat((freqs, freqs), dim=-1)
+    return emb.cos(), emb.sin()          # [L, rd]
+
+
+def _rotate_half(x):
+    h = x.shape[-1] // 2
+    return torch.cat((-x[..., h:], x[..., :h]), dim=-1)
+
+
+def _apply_rope(x, cos, sin, rd):
+    # x [L, H, hd]; rotate the first rd dims
+    xr, xp = x[..., :rd], x[..., rd:]
+    xr = xr * cos[:, None, :] + _rotate_half(xr) * sin[:, None, :]
+    return torch.cat((xr, xp), dim=-1)
+
+
+def _split_qkv(shape: DecoderShape, qkv):
+    L = qkv.shape[0]
+    nh, nkv, hd = shape.n_head, shape.n_kv_head, shape.head_dim
+    if shape.qkv_layout == QKV_FALCON_MQA:
+        x = qkv.view(L, nh + 2, hd)
+        return x[:, :nh], x[:, nh:nh + 1], x[:, nh + 1:nh + 2]
+    x = qkv.view(L, nh, 3, hd)
+    return x[:, :, 0], x[:, :, 1], x[:, :, 2]
+
+
+def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.Tensor,
+                   round_act: Optional[Callable] = None, dtype=torch.float32) -> torch.Tensor:
+    """ids [L] -> hidden after the final LayerNorm, [L, d].  ``round_act`` (e.g. bf16 round trip) is
+    applied to every GEMM input and to q/k/v, emulating bf16 MMA operands with fp32 accumulate."""
+    r = round_act if round_act is not None else (lambda t: t)
+    d, nh, nkv, hd = shape.d_model, shape.n_head, shape.n_kv_head, shape.head_dim
+    L = ids.shape[0]
+    cos, sin = _rope_cos_sin(shape, L)
+    cos, sin = cos.to(dtype), sin.to(dtype)
+    x = W["wte"].to(dtype)[ids]
+    causal = torch.tril(torch.ones(L, L, dtype=torch.bool))
+    for l in range(shape.n_layer):
+        p = f"l{l}."
+        bias = (lambda n: W[p + n].to(dtype)) if shape.has_bias else (lambda n: None)
+        ln1 = F.layer_norm(x, (d,), W[p + "ln1_g"].to(dtype), W[p + "ln1_b"].to(dtype), shape.norm_eps)
+        qkv = F.linear(r(ln1), W[p + "w_qkv"].to(dtype), bias("b_qkv"))
+        q, k, v = _split_qkv(shape, qkv)
+        q = r(_apply_rope(q, cos, sin, shape.rotary_dim))
+        k = r(_apply_rope(k, cos, sin, shape.rotary_dim))
+        v = r(v)
+        rep = nh // k.shape[1]
+        kk = k.repeat_interleave(rep, dim=1)
+        vv = v.repeat_interleave(rep, dim=1)
+        s = torch.einsum("qhd,khd->hqk", q, kk) / math.sqrt(hd)
+        s = s.masked_fill(~causal[None], float("-inf"))
+        a = torch.softmax(s, dim=-1)
+        o = torch.einsum("hqk,khd->qhd", a, vv).reshape(L, nh * hd)
+        attn = F.linear(r(o), W[p + "w_dense"].to(dtype), bias("b_dense"))
+        if shape.parallel_residual:
+            ln2 = ln1 if shape.n_ln_per_layer == 1 else F.layer_norm(
+                x, (d,), W[p + "ln2_g"].to(dtype), W[p + "ln2_b"].to(dtype), shape.norm_eps)
+            h = F.gelu(F.linear(r(ln2), W[p + "w_up"].to(dtype), bias("b_up")))
+            mlp = F.linear(r(h), W[p + "w_down"].to(dtype), bias("b_down"))
+            x = mlp + attn + x
+        else:
+            x1 = attn + x
+            ln2 = F.layer_norm(x1, (d,), W[p + "ln2_g"].to(dtype), W[p + "ln2_b"].to(dtype), shape.norm_eps)
+            h = F.gelu(F.linear(r(ln2), W[p + "w_up"].to(dtype), bias("b_up")))
+            mlp = F.linear(r(h), W[p + "w_down"].to(dtype), bias("b_down"))
+            x = mlp + x1
+    return F.layer_norm(x, (d,), W["lnf_g"].to(dtype), W["lnf_b"].to(dtype), shape.norm_eps)
+
+
+def last_logits(shape, W, ids, round_act=None, dtype=torch.float32) -> torch.Tensor:
+    r = round_act if round_act is not None else (lambda t: t)
+    h = forward_hidden(shape, W, ids, round_act, dtype)[-1]
+    return F.linear(r(h), W["lm_head"].to(dtype)).float()
+
+
+def bf16_round(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.bfloat16).to(t.dtype)
+
+
+def scan_positions(score_rows: List[torch.Tensor], id_a: int, id_b: int, topk: int):
+    """The reference's look-ahead rule (analysis/run_base_vs_instruct_100q.py:348-363;
+    compare_instruct_models.py:249-272): first of the (<=10) positions where either candidate id is
+    among the top-k probabilities; both probabilities are read there; otherwise position 0."""
+    for pos, row in enumerate(score_rows):
+        probs = torch.softmax(row, dim=-1)
+        _, top = torch.topk(probs, k=topk)
+        if id_a in top or id_b in top:
+            return probs[id_a].item(), probs[id_b].item(), pos, True
+    probs = torch.softmax(score_rows[0], dim=-1)
+    return probs[id_a].item(), probs[id_b].item(), 0, False
+
+
+def greedy_scores(shape, W, ids: List[int], n_positions: int, eos_id: int, round_act=None,
+                  dtype=torch.float32):
+    """Greedy decode restated without a KV cache: scores[t] = logits after prompt + t generated
+    tokens (HF:generation/utils.py:2743-2805; SURVEY.md Appendix A, last row).  Stops after the
+    position whose argmax is EOS, as ``generate`` does."""
+    seq = list(ids)
+    rows, gen = [], []
+    for _ in range(n_positions):
+        row = last_logits(shape, W, torch.tensor(seq, dtype=torch.long), round_act, dtype)
+        rows.append(row)
+        nxt = int(torch.argmax(row))
+        gen.append(nxt)
+        seq.append(nxt)
+        if nxt == eos_id:
+            break
+    return rows, gen
+
+
+def score_ids(shape, W, ids: List[int], id_a: int, id_b: int, topk: int = 5, max_lookahead: int = 10,
+              eos_id: Optional[int] = None, round_act=None, dtype=torch.float32):
+    eos = shape.eos_id if eos_id is None else eos_id
+    rows, gen = greedy_scores(shape, W, ids, max_lookahead, eos, round_act, dtype)
+    pa, pb, pos, found = scan_positions(rows, id_a, id_b, topk)
+    row = rows[pos]
+    lse = torch.logsumexp(row, dim=-1).item()
+    return dict(p_a=pa, p_b=pb, rel=(pa / (pa + pb) if pa + pb > 0 else float("nan")), lse=lse,
+                logit_a=row[id_a].item(), logit_b=row[id_b].item(), pos_found=pos, found=found,
+                gen_ids=gen, n_scores=len(rows))
