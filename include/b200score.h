@@ -1,0 +1,143 @@
+/* b200score.h -- C ABI of libb200score.so: B200 (sm_100a) relative-probability scorer + bootstrap.
+ *
+ * The reference (jonathanhchoi/llm-interpretation-replication) is pure Python and has no FFI of
+ * its own; its de-facto boundary for this path is two Python callables.  Each entry
+ * point below names the reference code it replaces.  All pointers are borrowed: the caller (torch
+ * in our host layer) owns every allocation; the library allocates nothing on the device unless
+ * stated, never frees caller memory, and keeps only the weight pointers registered at
+ * b2s_model_create (they must outlive the handle).  Every function returns 0 on success or a
+ * negative B2S_E* code and records a thread-local message for b2s_last_error(); nothing throws
+ * across the boundary.  All device work is enqueued on the caller's stream (a cudaStream_t passed
+ * as void*); functions return after enqueueing unless they say they synchronise.
+ */
+#ifndef B200SCORE_H
+#define B200SCORE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2S_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define B2S_API __attribute__((visibility("default")))
+#else
+#define B2S_API
+#endif
+
+enum { B2S_OK = 0, B2S_EINVAL = -1, B2S_ECUDA = -2, B2S_ENOMEM = -3, B2S_EUNSUPPORTED = -4 };
+
+enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1 };
+enum { B2S_QKV_FALCON_MQA = 0, B2S_QKV_NEOX_INTERLEAVED = 1 };
+/* compute modes: BF16_FAST = bf16 tcgen05 MMA operands, fp32 accumulation in TMEM, fp32 residual
+ * stream; FP32_CHECK = fp32 weights and activations on CUDA cores (parity gate 1e-5). */
+enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP32_CHECK = 3 };
+
+/* weight_ptrs slots: 6 global + 16 per layer (see llm_interpretation_replication_b200/weights.py) */
+enum { B2S_W_WTE = 0, B2S_W_LNF_G = 1, B2S_W_LNF_B = 2, B2S_W_LM_HEAD = 3, B2S_W_ROPE_COS = 4,
+       B2S_W_ROPE_SIN = 5, B2S_W_NGLOBAL = 6, B2S_W_PER_LAYER = 16 };
+enum { B2S_WL_LN1_G = 0, B2S_WL_LN1_B, B2S_WL_LN2_G, B2S_WL_LN2_B, B2S_WL_W_QKV, B2S_WL_B_QKV,
+       B2S_WL_W_DENSE, B2S_WL_B_DENSE, B2S_WL_W_UP, B2S_WL_B_UP, B2S_WL_W_DOWN, B2S_WL_B_DOWN };
+
+typedef struct {
+  int32_t abi_version;      /* B2S_ABI_VERSION */
+  int32_t arch;             /* B2S_ARCH_* */
+  int32_t n_layer, d_model, n_head, n_kv_head, head_dim, d_ff, vocab, rotary_dim;
+  float   norm_eps;
+  int32_t parallel_residual;   /* HF gpt_neox use_parallel_residual / falcon parallel_attn */
+  int32_t n_ln_per_layer;      /* 1 (falcon-7b) or 2 */
+  int32_t has_bias;
+  int32_t qkv_layout;          /* B2S_QKV_* */
+  int32_t max_pos;             /* rows of the rope cos/sin tables */
+  int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST expects bf16 matrices, FP32_CHECK fp32 */
+} b2s_model_desc;
+
+typedef struct b2s_model b2s_model;
+
+B2S_API const char* b2s_last_error(void);
+B2S_API int         b2s_abi_version(void);
+
+/* ---- scorer ------------------------------------------------------------------------------
+ * Replaces, for a whole batch of prompts at once, the per-prompt body of the reference's
+ * get_yes_no_logprobs (analysis/run_base_vs_instruct_100q.py:329-363; compare_instruct_models.py:
+ * 228-272; compare_base_vs_instruct.py:242-286): HF model.generate(...) prefill + greedy look-ahead
+ * (HF generation/utils.py:2736-2805), softmax, top-k membership test of the two candidate ids over
+ * the first max_lookahead positions, fallback to position 0. */
+B2S_API int    b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs, int32_t n_ptrs,
+                        int32_t device, b2s_model** out);
+B2S_API void   b2s_model_destroy(b2s_model* m);
+B2S_API size_t b2s_workspace_bytes(const b2s_model* m, int64_t max_tokens, int32_t max_seqs, int32_t max_lookahead);
+
+/* out rows: [p_a, p_b, rel, lse, logit_a, logit_b, pos_found, found]; gen_ids[N,max_lookahead]
+ * holds the greedy tokens (-1 after EOS).  topk is 5 (100q script) or 2 (compare_* scripts).
+ * tokens/cu_seqlens/cand_ids/out/gen_ids are DEVICE pointers; the call only enqueues work, except
+ * for one 4-byte readback per look-ahead step that lets it stop once every prompt is resolved. */
+B2S_API int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs,
+              int32_t total_tokens, int32_t max_seqlen, const int32_t* cand_ids /*[N,2]*/,
+              int32_t topk, int32_t max_lookahead, int32_t eos_id,
+              float* out /*[N,8]*/, int32_t* gen_ids /*[N,max_lookahead] or NULL*/,
+              void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same call with HOST buffers (pinned or pageable): copies inputs host->device into the workspace,
+ * runs b2s_score, copies the result rows back and synchronises the stream.  This is the call the
+ * reference-side binding makes and the one bench.py times as "e2e". */
+B2S_API int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_seqlens_h, int32_t n_seqs,
+                   const int32_t* cand_ids_h, int32_t topk, int32_t max_lookahead, int32_t eos_id,
+                   float* out_h, int32_t* gen_ids_h /*or NULL*/,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Number of kernels this library launched since the last call with reset != 0 (bench "gpu_launches"). */
+B2S_API int64_t b2s_launch_count(int32_t reset);
+
+/* ---- building blocks (exported so the parity tests can exercise each kernel through the ABI) ----
+ * C[M,N] = A[M,K] . W[N,K]^T (+bias[N]) with the epilogues the decoder layers need; replaces the
+ * FalconLinear / nn.Linear calls (HF falcon:60-65, gpt_neox:41-42,200-201).
+ *  epilogue: 0 store bf16, 1 GELU(erf) then store bf16, 2 out_f32 += acc (residual), 4 store fp32 */
+B2S_API int b2s_gemm_bf16(const void* A /*bf16 [M,K]*/, const void* W /*bf16 [N,K]*/, const float* bias,
+                  void* out, int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
+B2S_API int b2s_gemm_f32(const float* A, const float* W, const float* bias, float* out,
+                 int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
+
+/* Last-position LM head fused with online log-sum-exp, running top-5, argmax and candidate gather
+ * (replaces lm_head + .float() + softmax + topk + 2x .item(): HF falcon:905-906, generation/utils.py:
+ * 2762; run_base_vs_instruct_100q.py:351-356).  hidden bf16 [M,d], W bf16 [V,d].
+ * stats rows: [lse, top1..top5, argmax(as float), logit_a, logit_b, 0...] (16 floats per row).
+ * scratch: b2s_lm_head_scratch_bytes(M, V) bytes of device memory (per-tile partials). */
+B2S_API size_t b2s_lm_head_scratch_bytes(int32_t M, int32_t V);
+B2S_API int b2s_lm_head_bf16(const void* hidden, const void* W, const int32_t* cand_ids /*[M,2]*/,
+                     int32_t M, int32_t V, int32_t d, float* stats /*[M,16]*/,
+                     void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- bootstrap ---------------------------------------------------------------------------
+ * NumPy legacy RNG (MT19937 + masked rejection), bit-exact: np.random.seed(s) followed by repeated
+ * np.random.choice(n, size=..., replace=True), as used at run_base_vs_instruct_100q.py:616,657;
+ * analyze_base_vs_instruct_mae_100q.py:296,312,357,382; analyze_results_base_versus_instruct.py:304,
+ * 312,349.  state = 624 words + position (625 uint32, device). */
+B2S_API int b2s_mt19937_seed(uint32_t seed, uint32_t* state /*dev [625]*/, void* stream);
+B2S_API int b2s_mt19937_choice(uint32_t* state /*dev [625], in/out*/, int32_t n, int64_t count,
+                       int32_t* idx_out /*dev [count]*/, void* stream);
+
+/* Resample statistics: vals [F,n] fp64 (rows < split are "base", rows >= split "instruct"; all F rows
+ * share the resampled column indices, as analyze_base_vs_instruct_mae_100q.py:380-388 does).
+ * idx [B,n] from b2s_mt19937_choice, or NULL for the counter-based Philox4x32-10 stream keyed by
+ * (philox_seed, b, j) (not NumPy-compatible; for unseeded reference loops).
+ * boot[B,3] = {mean over rows<split, mean over rows>=split (NaN if none), mean |v| over all rows}. */
+B2S_API int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t n, int64_t B,
+                           const int32_t* idx, uint64_t philox_seed, double* boot /*dev [B,3]*/, void* stream);
+
+/* Percentile CI + tail fractions of one statistic of boot (np.percentile linear interpolation):
+ * stat 0 = boot[:,0], 1 = boot[:,1]-boot[:,0], 2 = boot[:,2].
+ * summary[8] = {pct(q_lo), pct(q_hi), frac(x<=0), frac(x>=0), mean(x), frac(x>=observed), min, max}.
+ * scratch: B rounded up to a power of two doubles (device). */
+B2S_API size_t b2s_bootstrap_scratch_bytes(int64_t B);
+B2S_API int b2s_bootstrap_summary(const double* boot, int64_t B, int32_t stat, double q_lo, double q_hi,
+                          double observed, double* summary /*dev [8]*/, double* stat_out /*dev [B] or NULL*/,
+                          void* scratch, size_t scratch_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SCORE_H */

@@ -1,0 +1,177 @@
+"""Host-side mirror of the reference's bootstrap functions on top of libb200score.
+
+Kept names, arguments and return dicts:
+  * bootstrap_mae_difference, bootstrap_overall_mae_difference
+      -- reference survey_analysis/analyze_base_vs_instruct_mae_100q.py:289-345, 348-414
+  * analyze_results_bootstrap (the resampling core of analyze_results)
+      -- reference analysis/run_base_vs_instruct_100q.py:614-705
+  * prompt_bootstrap_and_signflip
+      -- reference analysis/analyze_results_base_versus_instruct.py:300-365
+The `for _ in range(n_bootstrap)` loops become: one MT19937 kernel that reproduces NumPy's legacy index
+stream bit for bit, one gather/mean kernel, one sort + percentile kernel.  Only scalars come back.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+class NumpyLegacyStream:
+    """Device-resident equivalent of ``np.random.seed(seed)`` + repeated ``np.random.choice``."""
+
+    def __init__(self, seed: int, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.B2SError("no CUDA device: the bootstrap kernels have no CPU fallback")
+        self.lib = _lib.load()
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.state = torch.empty(625, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2s_mt19937_seed(int(seed) & 0xFFFFFFFF, _lib.ptr(self.state), _lib.current_stream()),
+                       "b2s_mt19937_seed")
+
+    def choice(self, n: int, count: int) -> torch.Tensor:
+        """``count`` draws of ``np.random.choice(n, ...)`` in stream order (int32, device)."""
+        out = torch.empty(int(count), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2s_mt19937_choice(_lib.ptr(self.state), int(n), int(count), _lib.ptr(out),
+                                                   _lib.current_stream()), "b2s_mt19937_choice")
+        return out
+
+
+def resample(vals: np.ndarray, split: int, B: int, idx: Optional[torch.Tensor] = None, philox_seed: int = 0,
+             device=None) -> torch.Tensor:
+    """boot[B,3] = (mean rows<split, mean rows>=split, mean|.| all rows) for B resamples of the columns."""
+    lib = _lib.load()
+    device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+    v = torch.as_tensor(np.ascontiguousarray(vals, dtype=np.float64)).to(device)
+    F, n = v.shape
+    boot = torch.empty((B, 3), dtype=torch.float64, device=device)
+    if idx is not None:
+        assert idx.dtype == torch.int32 and idx.numel() == B * n and idx.is_cuda
+    with torch.cuda.device(device):
+        _lib.check(lib.b2s_bootstrap_resample(_lib.ptr(v), F, split, n, B, _lib.ptr(idx), int(philox_seed),
+                                              _lib.ptr(boot), _lib.current_stream()), "b2s_bootstrap_resample")
+    return boot
+
+
+def summary(boot: torch.Tensor, stat: int, q_lo: float, q_hi: float, observed: float, want_stat: bool = False):
+    """(dict, stat vector or None).  dict keys: pct_lo, pct_hi, frac_le0, frac_ge0, mean, frac_ge_obs, min, max."""
+    lib = _lib.load()
+    B = boot.shape[0]
+    dev = boot.device
+    nbytes = lib.b2s_bootstrap_scratch_bytes(B)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    out = torch.empty(8, dtype=torch.float64, device=dev)
+    stat_out = torch.empty(B, dtype=torch.float64, device=dev) if want_stat else None
+    with torch.cuda.device(dev):
+        _lib.check(lib.b2s_bootstrap_summary(_lib.ptr(boot), B, stat, float(q_lo), float(q_hi), float(observed),
+                                             _lib.ptr(out), _lib.ptr(stat_out), _lib.ptr(scratch), nbytes,
+                                             _lib.current_stream()), "b2s_bootstrap_summary")
+    o = out.cpu().numpy()
+    keys = ("pct_lo", "pct_hi", "frac_le0", "frac_ge0", "mean", "frac_ge_obs", "min", "max")
+    return dict(zip(keys, map(float, o))), stat_out
+
+
+def _two_sided_p(observed: float, s: dict, cap: bool = True) -> float:
+    p = 2 * s["frac_le0"] if observed > 0 else 2 * s["frac_ge0"]
+    return min(p, 1.0) if cap else p
+
+
+N_BOOTSTRAP = 10000
+RANDOM_SEED = 42
+CONFIDENCE_LEVEL = 0.95
+
+
+def bootstrap_mae_difference(base_errors, instruct_errors, n_bootstrap=N_BOOTSTRAP, seed=RANDOM_SEED,
+                             stream: Optional[NumpyLegacyStream] = None, device=None):
+    """Same contract as the reference function (dict incl. ``bootstrap_diffs``)."""
+    base_mae = np.mean(base_errors)
+    instruct_mae = np.mean(instruct_errors)
+    observed_diff = instruct_mae - base_mae
+    n = min(len(base_errors), len(instruct_errors))
+    vals = np.stack([np.asarray(base_errors[:n], dtype=np.float64), np.asarray(instruct_errors[:n], dtype=np.float64)])
+    rs = stream if stream is not None else NumpyLegacyStream(seed, device)
+    idx = rs.choice(n, n_bootstrap * n)
+    boot = resample(vals, 1, n_bootstrap, idx, device=rs.device)
+    alpha = 1 - CONFIDENCE_LEVEL
+    s, diffs = summary(boot, 1, (alpha / 2) * 100, (1 - alpha / 2) * 100, observed_diff, want_stat=True)
+    return dict(base_mae=base_mae, instruct_mae=instruct_mae, observed_diff=observed_diff, ci_lower=s["pct_lo"],
+                ci_upper=s["pct_hi"], p_value=_two_sided_p(observed_diff, s), n_questions=n,
+                bootstrap_diffs=diffs.cpu().numpy())
+
+
+def bootstrap_overall_mae_difference(all_family_errors: Dict[str, dict], n_bootstrap=N_BOOTSTRAP, seed=RANDOM_SEED,
+                                     device=None):
+    n = None
+    for fam, e in all_family_errors.items():
+        m = min(len(e["base"]), len(e["instruct"]))
+        n = m if n is None else min(n, m)
+    fams = list(all_family_errors.keys())
+    Bm = np.array([all_family_errors[f]["base"][:n] for f in fams], dtype=np.float64)
+    Im = np.array([all_family_errors[f]["instruct"][:n] for f in fams], dtype=np.float64)
+    obs_b, obs_i = np.mean(Bm), np.mean(Im)
+    observed_diff = obs_i - obs_b
+    rs = NumpyLegacyStream(seed, device)
+    idx = rs.choice(n, n_bootstrap * n)
+    boot = resample(np.concatenate([Bm, Im], axis=0), len(fams), n_bootstrap, idx, device=rs.device)
+    alpha = 1 - CONFIDENCE_LEVEL
+    s, diffs = summary(boot, 1, (alpha / 2) * 100, (1 - alpha / 2) * 100, observed_diff, want_stat=True)
+    return dict(base_mae=obs_b, instruct_mae=obs_i, observed_diff=observed_diff, ci_lower=s["pct_lo"],
+                ci_upper=s["pct_hi"], p_value=_two_sided_p(observed_diff, s), n_questions=n, n_models=len(fams),
+                bootstrap_diffs=diffs.cpu().numpy())
+
+
+def analyze_results_bootstrap(family_diffs: Dict[str, np.ndarray], n_bootstrap=N_BOOTSTRAP, seed=RANDOM_SEED, device=None):
+    """Resampling core of the reference's analyze_results(): ONE seed, then the families in order, then the
+    concatenation, all on the same stream (run_base_vs_instruct_100q.py:616,655-658,692-695)."""
+    rs = NumpyLegacyStream(seed, device)
+    out, kept = {}, {}
+    for fam, diffs in family_diffs.items():
+        diffs = np.asarray(diffs, dtype=np.float64)
+        if len(diffs) < 10:
+            continue
+        kept[fam] = diffs
+        n = len(diffs)
+        obs = float(np.mean(diffs))
+        boot = resample(diffs[None, :], 1, n_bootstrap, rs.choice(n, n_bootstrap * n), device=rs.device)
+        s, _ = summary(boot, 0, 2.5, 97.5, obs)
+        out[fam] = dict(n_prompts=n, mean_diff=obs, mae=float(np.mean(np.abs(diffs))), ci_lower=s["pct_lo"],
+                        ci_upper=s["pct_hi"], p_value=_two_sided_p(obs, s))
+    overall = None
+    if len(kept) >= 2:
+        alld = np.concatenate(list(kept.values()))
+        n = len(alld)
+        obs = float(np.mean(alld))
+        boot = resample(alld[None, :], 1, n_bootstrap, rs.choice(n, n_bootstrap * n), device=rs.device)
+        s, _ = summary(boot, 0, 2.5, 97.5, obs)
+        overall = dict(mean_diff=obs, mae=float(np.mean(np.abs(alld))), ci_lower=s["pct_lo"], ci_upper=s["pct_hi"],
+                       p_value=_two_sided_p(obs, s))
+    return out, overall
+
+
+def prompt_bootstrap_and_signflip(pivot: np.ndarray, n_bootstrap=N_BOOTSTRAP, seed=RANDOM_SEED, device=None):
+    """reference analyze_results_base_versus_instruct.py:300-365.  pivot [n_prompts, F]; rows are resampled,
+    statistics are taken over the flattened resample.  The sign-flip "permutation" MAE equals the observed MAE
+    for every draw (|x*s| == |x|), so its p-value is 1.0 by construction; the draws are still taken from the
+    stream (n_bootstrap * n*F words) to keep the stream position identical to the reference's."""
+    pivot = np.asarray(pivot, dtype=np.float64)
+    n, F = pivot.shape
+    observed_mae = float(np.mean(np.abs(pivot.flatten())))
+    observed_mean = float(np.mean(pivot.flatten()))
+    rs = NumpyLegacyStream(seed, device)
+    idx = rs.choice(n, n_bootstrap * n)
+    boot = resample(np.ascontiguousarray(pivot.T), F, n_bootstrap, idx, device=rs.device)
+    s_mae, _ = summary(boot, 2, 2.5, 97.5, observed_mae)
+    s_mean, _ = summary(boot, 0, 2.5, 97.5, observed_mean)
+    signs = rs.choice(2, n_bootstrap * n * F)          # choice([-1, 1]) consumes one masked word per draw
+    # perm_mae[b] = mean(|x * s|) = mean(|x|) exactly -> fraction >= observed is 1.0
+    del signs
+    p_mean = 2 * s_mean["frac_le0"] if observed_mean > 0 else 2 * s_mean["frac_ge0"]
+    return dict(mae=observed_mae, mae_ci_lower=s_mae["pct_lo"], mae_ci_upper=s_mae["pct_hi"], mae_p_value=1.0,
+                mean_diff=observed_mean, mean_ci_lower=s_mean["pct_lo"], mean_ci_upper=s_mean["pct_hi"],
+                mean_p_value=p_mean, n_prompts=n, n_models=F)

@@ -1,0 +1,108 @@
+// Shared host/device helpers for libb200score (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/b200score.h"
+
+namespace b2s {
+
+// ---- error plumbing --------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern thread_local std::string g_last_error;
+extern int64_t g_launch_count;
+
+#define B2S_CHECK_CUDA(expr)                                                                  \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      b2s::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return B2S_ECUDA;                                                                       \
+    }                                                                                         \
+  } while (0)
+
+#define B2S_CHECK_LAUNCH()                                                                    \
+  do {                                                                                        \
+    b2s::g_launch_count++;                                                                    \
+    cudaError_t _e = cudaGetLastError();                                                      \
+    if (_e != cudaSuccess) {                                                                  \
+      b2s::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return B2S_ECUDA;                                                                       \
+    }                                                                                         \
+  } while (0)
+
+#define B2S_REQUIRE(cond, ...)                                                                \
+  do {                                                                                        \
+    if (!(cond)) { b2s::set_error(__VA_ARGS__); return B2S_EINVAL; }                          \
+  } while (0)
+
+#define B2S_TRY(expr)                                                                         \
+  do { int _r = (expr); if (_r != B2S_OK) return _r; } while (0)
+
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
+
+// ---- epilogue codes (b200score.h) ---------------------------------------------------------------
+enum { EPI_STORE_BF16 = 0, EPI_GELU_BF16 = 1, EPI_RESID_F32 = 2, EPI_LMHEAD = 3, EPI_STORE_F32 = 4 };
+
+// LM-head partial record per (row, vocab tile): 8 floats
+//   [0] max  [1] sum exp(x-max)  [2..6] top-5 (desc)  [7] argmax column (int bits)
+constexpr int LMH_PART = 8;
+constexpr int LMH_TILE_N = 256;
+constexpr int LMH_STATS = 16;   // floats per row in the public stats layout
+
+// ---- internal launchers (defined across the .cu files) -----------------------------------------
+struct LmHeadArgs {
+  const int32_t* cand_ids;  // [M,2]
+  float* partials;          // [M, tiles_n, LMH_PART]
+  float* cand_logits;       // [M,2]
+};
+
+int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K,
+                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st);
+int gemm_f32_launch(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
+                    int epilogue, cudaStream_t st);
+
+#ifdef __CUDACC__
+// ---- device math -------------------------------------------------------------------------------
+__device__ __forceinline__ float gelu_erf(float x) {
+  // HF "gelu" = x * 0.5 * (1 + erf(x / sqrt(2)))   (HF falcon:537, gpt_neox:43)
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float to_f32(float v) { return v; }
+__device__ __forceinline__ float to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// insert v into a descending top-5 list
+__device__ __forceinline__ void top5_insert(float (&t)[5], float v) {
+  if (v > t[4]) {
+    if (v > t[0]) { t[4] = t[3]; t[3] = t[2]; t[2] = t[1]; t[1] = t[0]; t[0] = v; }
+    else if (v > t[1]) { t[4] = t[3]; t[3] = t[2]; t[2] = t[1]; t[1] = v; }
+    else if (v > t[2]) { t[4] = t[3]; t[3] = t[2]; t[2] = v; }
+    else if (v > t[3]) { t[4] = t[3]; t[3] = v; }
+    else t[4] = v;
+  }
+}
+#endif
+
+}  // namespace b2s

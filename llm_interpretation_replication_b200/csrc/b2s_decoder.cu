@@ -1,0 +1,437 @@
+// Non-GEMM kernels of the decoder forward: batch bookkeeping, embedding gather + LayerNorm,
+// RoPE + KV-cache append, varlen causal attention, LM-head reduction/merge and the look-ahead
+// scan state machine.  All HBM-bound; templated on the activation type
+// (bf16 in BF16_FAST mode, float in FP32_CHECK mode).
+#include "b2s_decoder.cuh"
+
+namespace b2s {
+
+// =================================================================================================
+// batch bookkeeping: positions, cache slots, last rows  (replaces HF position_ids / cache_position,
+// HF falcon:760-775)
+// =================================================================================================
+__global__ void prep_prefill_kernel(const int32_t* __restrict__ cu, int n_seqs, int lookahead, BatchMeta m) {
+  const int i = blockIdx.x;
+  if (i >= n_seqs) return;
+  const int s = cu[i], e = cu[i + 1];
+  const int kv0 = s + i * lookahead;
+  if (threadIdx.x == 0) {
+    m.q_start[i] = s; m.q_len[i] = e - s; m.kv_start[i] = kv0; m.kv_len[i] = e - s; m.last_row[i] = e - 1;
+  }
+  for (int t = s + threadIdx.x; t < e; t += blockDim.x) { m.pos[t] = t - s; m.slot[t] = kv0 + (t - s); }
+}
+
+// decode step `step` (>= 1): row i holds the token generated at position step-1 of prompt i
+__global__ void prep_decode_kernel(const int32_t* __restrict__ cu, int n_seqs, int lookahead, int step, BatchMeta m) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_seqs) return;
+  const int L = cu[i + 1] - cu[i];
+  const int kv0 = cu[i] + i * lookahead;
+  const int p = L + step - 1;
+  m.q_start[i] = i; m.q_len[i] = 1; m.kv_start[i] = kv0; m.kv_len[i] = p + 1; m.last_row[i] = i;
+  m.pos[i] = p; m.slot[i] = kv0 + p;
+}
+
+int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const BatchMeta& m, cudaStream_t st) {
+  if (step == 0) prep_prefill_kernel<<<n_seqs, 128, 0, st>>>(cu, n_seqs, lookahead, m);
+  else prep_decode_kernel<<<static_cast<unsigned>(ceil_div(n_seqs, 128)), 128, 0, st>>>(cu, n_seqs, lookahead, step, m);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+// =================================================================================================
+// LayerNorm (+ embedding gather, + second affine output, + row gather)
+//   HF falcon:578,598,686,744,819; gpt_neox:251-252,321,345,376.  torch.nn.functional.layer_norm:
+//   mean, biased variance, (x-mean)*rsqrt(var+eps)*g+b, all in fp32.
+// One CTA per row; the row lives in shared memory between the two passes.
+// =================================================================================================
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float t = (l < nw) ? red[l] : 0.f;
+  t = warp_sum(t);
+  return t;
+}
+
+template <typename AT, typename WT>
+__global__ void __launch_bounds__(256)
+ln_kernel(LnArgs a) {
+  extern __shared__ float srow[];
+  __shared__ float red[8];
+  const int orow = blockIdx.x;
+  const int irow = a.rows ? a.rows[orow] : orow;
+  const int d = a.d;
+  float sum = 0.f;
+  if (a.tokens != nullptr) {
+    const WT* e = reinterpret_cast<const WT*>(a.wte) + static_cast<size_t>(a.tokens[irow]) * d;
+    float* xr = a.x + static_cast<size_t>(irow) * d;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+      const float v = to_f32(e[i]);
+      srow[i] = v; xr[i] = v; sum += v;
+    }
+  } else {
+    const float4* xr = reinterpret_cast<const float4*>(a.x + static_cast<size_t>(irow) * d);
+    for (int i = threadIdx.x; i < d / 4; i += blockDim.x) {
+      const float4 v = xr[i];
+      reinterpret_cast<float4*>(srow)[i] = v;
+      sum += (v.x + v.y) + (v.z + v.w);
+    }
+  }
+  const float mean = block_sum(sum, red) / d;
+  float sq = 0.f;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) { const float c = srow[i] - mean; sq += c * c; }
+  const float rstd = rsqrtf(block_sum(sq, red) / d + a.eps);
+  AT* y1 = reinterpret_cast<AT*>(a.y1) + static_cast<size_t>(orow) * d;
+  AT* y2 = a.y2 ? reinterpret_cast<AT*>(a.y2) + static_cast<size_t>(orow) * d : nullptr;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) {
+    const float n = (srow[i] - mean) * rstd;
+    y1[i] = from_f32<AT>(n * a.g1[i] + a.b1[i]);
+    if (y2) y2[i] = from_f32<AT>(n * a.g2[i] + a.b2[i]);
+  }
+}
+
+template <typename AT, typename WT>
+int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st) {
+  B2S_REQUIRE(a.d % 4 == 0, "layernorm: d=%d must be a multiple of 4", a.d);
+  const size_t smem = static_cast<size_t>(a.d) * sizeof(float);
+  if (smem > 48 * 1024) {
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(ln_kernel<AT, WT>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  }
+  ln_kernel<AT, WT><<<n_rows, 256, smem, st>>>(a);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+template int launch_ln<float, float>(const LnArgs&, int, cudaStream_t);
+template int launch_ln<__nv_bfloat16, __nv_bfloat16>(const LnArgs&, int, cudaStream_t);
+
+// =================================================================================================
+// RoPE (rotate_half form on the first rotary_dim dims) + KV-cache append.
+//   HF falcon:69-99,154-165 / gpt_neox:126-159: q' = q*cos + rotate_half(q)*sin with cos/sin of shape
+//   [pos, rd] = cat(freqs, freqs); here cos/sin tables hold the first rd/2 columns.
+// One CTA per token row; q rotated in place, k rotated into the cache, v copied into the cache.
+// =================================================================================================
+template <typename AT>
+__global__ void __launch_bounds__(256)
+rope_cache_kernel(RopeArgs a) {
+  const int t = blockIdx.x;
+  const int pos = a.pos[t];
+  const size_t slot = static_cast<size_t>(a.slot[t]);
+  AT* row = reinterpret_cast<AT*>(a.qkv) + static_cast<size_t>(t) * a.qkv_dim;
+  const int hd = a.hd, half = a.rd / 2;
+  const float* cs = a.cos + static_cast<size_t>(pos) * half;
+  const float* sn = a.sin + static_cast<size_t>(pos) * half;
+  // q heads: pairs (i, i+half)
+  const int nq = a.nh * half;
+  for (int w = threadIdx.x; w < nq; w += blockDim.x) {
+    const int h = w / half, i = w - h * half;
+    AT* q = row + a.q_base + h * a.q_hstride;
+    const float x1 = to_f32(q[i]), x2 = to_f32(q[i + half]);
+    const float c = cs[i], s = sn[i];
+    q[i] = from_f32<AT>(x1 * c - x2 * s);
+    q[i + half] = from_f32<AT>(x2 * c + x1 * s);
+  }
+  AT* kc = reinterpret_cast<AT*>(a.kcache) + slot * (a.nkv * hd);
+  AT* vc = reinterpret_cast<AT*>(a.vcache) + slot * (a.nkv * hd);
+  const int nk = a.nkv * hd;
+  for (int w = threadIdx.x; w < nk; w += blockDim.x) {
+    const int g = w / hd, i = w - g * hd;
+    const AT* k = row + a.k_base + g * a.kv_hstride;
+    const AT* v = row + a.v_base + g * a.kv_hstride;
+    float kv;
+    if (i < half) kv = to_f32(k[i]) * cs[i] - to_f32(k[i + half]) * sn[i];
+    else if (i < a.rd) kv = to_f32(k[i]) * cs[i - half] + to_f32(k[i - half]) * sn[i - half];
+    else kv = to_f32(k[i]);
+    kc[w] = from_f32<AT>(kv);
+    vc[w] = v[i];
+  }
+}
+
+template <typename AT>
+int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st) {
+  rope_cache_kernel<AT><<<n_rows, 256, 0, st>>>(a);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+template int launch_rope_cache<float>(const RopeArgs&, int, cudaStream_t);
+template int launch_rope_cache<__nv_bfloat16>(const RopeArgs&, int, cudaStream_t);
+
+// =================================================================================================
+// Varlen causal attention over the KV cache (prefill: q_len = L; decode: q_len = 1).
+//   HF falcon:349-362 (SDPA, is_causal, scale 1/sqrt(hd)); gpt_neox:162-185,224-238.  fp32 softmax.
+// One CTA per (sequence, group of <= ATT_HG query heads sharing one KV head).  K and V of the whole
+// sequence for that KV head are staged in shared memory once (rows padded to dodge bank conflicts);
+// each warp then owns (query, head) items: lanes split keys for Q.K^T, exchange the softmax statistics
+// with shuffles, and split head dims for P.V.
+// =================================================================================================
+template <typename AT, int HD>
+__global__ void __launch_bounds__(ATT_THREADS)
+attn_kernel(AttnArgs a) {
+  constexpr int HDP = HD + 4;              // padded row (floats)
+  constexpr int DPL = (HD + 31) / 32;      // output dims per lane
+  extern __shared__ float smem[];
+  const int seq = blockIdx.x;
+  const int groups_per_kv = (a.rep + ATT_HG - 1) / ATT_HG;
+  const int g = blockIdx.y / groups_per_kv;           // kv head
+  const int hg = blockIdx.y - g * groups_per_kv;      // head group inside this kv head
+  const int h0 = g * a.rep + hg * ATT_HG;
+  const int nh_here = min(ATT_HG, a.rep - hg * ATT_HG);
+  const int q0 = a.meta.q_start[seq], ql = a.meta.q_len[seq];
+  const int kv0 = a.meta.kv_start[seq], kl = a.meta.kv_len[seq];
+  float* sK = smem;
+  float* sV = sK + static_cast<size_t>(a.max_kv) * HDP;
+  float* sQ = sV + static_cast<size_t>(a.max_kv) * HDP;     // [warps][HD]
+  float* sP = sQ + (ATT_THREADS / 32) * HD;                 // [warps][32]
+  const AT* kc = reinterpret_cast<const AT*>(a.kcache) + (static_cast<size_t>(kv0) * a.nkv + g) * HD;
+  const AT* vc = reinterpret_cast<const AT*>(a.vcache) + (static_cast<size_t>(kv0) * a.nkv + g) * HD;
+  const size_t kv_stride = static_cast<size_t>(a.nkv) * HD;
+  for (int idx = threadIdx.x; idx < kl * HD; idx += blockDim.x) {
+    const int j = idx / HD, dd = idx - j * HD;
+    sK[j * HDP + dd] = to_f32(kc[j * kv_stride + dd]);
+    sV[j * HDP + dd] = to_f32(vc[j * kv_stride + dd]);
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  float* q = sQ + warp * HD;
+  float* pbuf = sP + warp * 32;
+  const int n_items = ql * nh_here;
+  const AT* qkv = reinterpret_cast<const AT*>(a.qkv);
+  AT* out = reinterpret_cast<AT*>(a.out);
+  for (int item = warp; item < n_items; item += nw) {
+    const int qi = item / nh_here, h = h0 + (item - qi * nh_here);
+    const size_t row = static_cast<size_t>(q0 + qi);
+    const AT* qp = qkv + row * a.qkv_dim + a.q_base + h * a.q_hstride;
+    for (int dd = lane; dd < HD; dd += 32) q[dd] = to_f32(qp[dd]) * a.scale;
+    __syncwarp();
+    const int nkeys = kl - ql + qi + 1;     // causal: query qi sees keys [0, nkeys)
+    float m = -INFINITY, l = 0.f;
+    float acc[DPL];
+#pragma unroll
+    for (int r = 0; r < DPL; ++r) acc[r] = 0.f;
+    for (int j0 = 0; j0 < nkeys; j0 += 32) {
+      const int j = j0 + lane;
+      float s = -INFINITY;
+      if (j < nkeys) {
+        const float4* kr = reinterpret_cast<const float4*>(sK + j * HDP);
+        const float4* qr = reinterpret_cast<const float4*>(q);
+        float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < HD / 4; ++c) {
+          const float4 kk = kr[c], qq = qr[c];
+          d0 = fmaf(kk.x, qq.x, d0); d1 = fmaf(kk.y, qq.y, d1);
+          d0 = fmaf(kk.z, qq.z, d0); d1 = fmaf(kk.w, qq.w, d1);
+        }
+        s = d0 + d1;
+      }
+      const float mn = fmaxf(m, warp_max(s));
+      const float p = (j < nkeys) ? __expf(s - mn) : 0.f;
+      const float corr = __expf(m - mn);
+      l = l * corr + warp_sum(p);
+      m = mn;
+      pbuf[lane] = p;
+      __syncwarp();
+      const int cnt = min(32, nkeys - j0);
+#pragma unroll
+      for (int r = 0; r < DPL; ++r) {
+        const int dd = lane + 32 * r;
+        float o = acc[r] * corr;
+        if (dd < HD) {
+          for (int jj = 0; jj < cnt; ++jj) o = fmaf(pbuf[jj], sV[(j0 + jj) * HDP + dd], o);
+        }
+        acc[r] = o;
+      }
+      __syncwarp();
+    }
+    const float inv = 1.f / l;
+    AT* op = out + row * (static_cast<size_t>(a.nh) * HD) + h * HD;
+#pragma unroll
+    for (int r = 0; r < DPL; ++r) {
+      const int dd = lane + 32 * r;
+      if (dd < HD) op[dd] = from_f32<AT>(acc[r] * inv);
+    }
+    __syncwarp();
+  }
+}
+
+template <typename AT>
+int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st) {
+  const int hd = a.hd;
+  const size_t smem = (2 * static_cast<size_t>(a.max_kv) * (hd + 4) + (ATT_THREADS / 32) * (hd + 32)) * sizeof(float);
+  B2S_REQUIRE(smem <= 227 * 1024,
+              "attention: a sequence of %d keys (head_dim %d) needs %zu bytes of shared memory; the limit is %d keys",
+              a.max_kv, hd, smem, static_cast<int>((227 * 1024 / sizeof(float) - (ATT_THREADS / 32) * (hd + 32)) / (2 * (hd + 4))));
+  const int groups_per_kv = (a.rep + ATT_HG - 1) / ATT_HG;
+  dim3 grid(n_seqs, a.nkv * groups_per_kv);
+#define B2S_ATT_CASE(HDV)                                                                                         \
+  case HDV:                                                                                                      \
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_kernel<AT, HDV>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
+                                        static_cast<int>(smem)));                                                 \
+    attn_kernel<AT, HDV><<<grid, ATT_THREADS, smem, st>>>(a);                                                     \
+    break;
+  switch (hd) {
+    B2S_ATT_CASE(64)
+    B2S_ATT_CASE(80)
+    B2S_ATT_CASE(128)
+    default: set_error("attention: unsupported head_dim %d (64, 80, 128)", hd); return B2S_EUNSUPPORTED;
+  }
+#undef B2S_ATT_CASE
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+template int launch_attn<float>(const AttnArgs&, int, cudaStream_t);
+template int launch_attn<__nv_bfloat16>(const AttnArgs&, int, cudaStream_t);
+
+// =================================================================================================
+// LM head: reduce full fp32 logits to per-tile partials (FP32_CHECK mode; the bf16 path produces the
+// same partial records inside the GEMM epilogue), merge partials per row, then advance the look-ahead
+// scan state.
+// =================================================================================================
+// grid (tiles_n, M); one warp per (row, 256-column tile)
+__global__ void __launch_bounds__(32)
+lmhead_partials_from_logits_kernel(const float* __restrict__ logits, int M, int V, int tiles_n,
+                                   const int32_t* __restrict__ cand, float* __restrict__ partials,
+                                   float* __restrict__ cand_logits) {
+  const int nb = blockIdx.x, row = blockIdx.y, lane = threadIdx.x;
+  const float* lr = logits + static_cast<size_t>(row) * V;
+  float m = -INFINITY, best = -INFINITY;
+  int arg = 0;
+  float top[5] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  const int c0 = nb * LMH_TILE_N;
+  const int ca = cand[2 * row], cb = cand[2 * row + 1];
+  for (int c = c0 + lane; c < min(c0 + LMH_TILE_N, V); c += 32) {
+    const float x = lr[c];
+    if (x > best) { best = x; arg = c; }
+    m = fmaxf(m, x);
+    top5_insert(top, x);
+    if (c == ca) cand_logits[2 * row] = x;
+    if (c == cb) cand_logits[2 * row + 1] = x;
+  }
+  const float wm = warp_max(m);
+  float s = 0.f;
+  for (int c = c0 + lane; c < min(c0 + LMH_TILE_N, V); c += 32) s += expf(lr[c] - wm);
+  s = warp_sum(s);
+  // merge top-5 and argmax across lanes through shared memory
+  __shared__ float st[32 * 5];
+  __shared__ float sb[32];
+  __shared__ int sa[32];
+#pragma unroll
+  for (int j = 0; j < 5; ++j) st[lane * 5 + j] = top[j];
+  sb[lane] = best; sa[lane] = arg;
+  __syncwarp();
+  if (lane == 0) {
+    float t5[5] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < 160; ++i) top5_insert(t5, st[i]);
+    float bb = -INFINITY; int ba = 0;
+    for (int i = 0; i < 32; ++i) if (sb[i] > bb || (sb[i] == bb && sa[i] < ba)) { bb = sb[i]; ba = sa[i]; }
+    float* o = partials + (static_cast<size_t>(row) * tiles_n + nb) * LMH_PART;
+    o[0] = wm; o[1] = s;
+    for (int j = 0; j < 5; ++j) o[2 + j] = t5[j];
+    o[7] = __int_as_float(ba);
+  }
+}
+
+int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const int32_t* cand, float* partials,
+                                       float* cand_logits, cudaStream_t st) {
+  const int tiles_n = static_cast<int>(ceil_div(V, LMH_TILE_N));
+  dim3 grid(tiles_n, M);
+  lmhead_partials_from_logits_kernel<<<grid, 32, 0, st>>>(logits, M, V, tiles_n, cand, partials, cand_logits);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+// One warp per row: merge the per-tile partial records into the public 16-float stats row
+//   [lse, top1..top5, argmax, logit_a, logit_b, 0..]
+__global__ void __launch_bounds__(128)
+lmhead_merge_kernel(const float* __restrict__ partials, const float* __restrict__ cand_logits, int M, int tiles_n,
+                    float* __restrict__ stats) {
+  __shared__ float st[4][32 * 5];
+  __shared__ float sb[4][32];
+  __shared__ int sa[4][32];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 4 + w;
+  if (row >= M) return;
+  float m = -INFINITY, best = -INFINITY;
+  int arg = 0x7fffffff;
+  float top[5] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  const float* pr = partials + static_cast<size_t>(row) * tiles_n * LMH_PART;
+  for (int t = lane; t < tiles_n; t += 32) m = fmaxf(m, pr[t * LMH_PART]);
+  m = warp_max(m);
+  float s = 0.f;
+  for (int t = lane; t < tiles_n; t += 32) {
+    const float* p = pr + t * LMH_PART;
+    s += p[1] * expf(p[0] - m);
+    const int a = __float_as_int(p[7]);
+    if (p[2] > best || (p[2] == best && a < arg)) { best = p[2]; arg = a; }   // p[2] is the tile max
+#pragma unroll
+    for (int j = 0; j < 5; ++j) top5_insert(top, p[2 + j]);
+  }
+  s = warp_sum(s);
+#pragma unroll
+  for (int j = 0; j < 5; ++j) st[w][lane * 5 + j] = top[j];
+  sb[w][lane] = best; sa[w][lane] = arg;
+  __syncwarp();
+  if (lane == 0) {
+    float t5[5] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < 160; ++i) top5_insert(t5, st[w][i]);
+    float bb = -INFINITY; int ba = 0x7fffffff;
+    for (int i = 0; i < 32; ++i) if (sb[w][i] > bb || (sb[w][i] == bb && sa[w][i] < ba)) { bb = sb[w][i]; ba = sa[w][i]; }
+    float* o = stats + static_cast<size_t>(row) * LMH_STATS;
+    o[0] = m + logf(s);
+    for (int j = 0; j < 5; ++j) o[1 + j] = t5[j];
+    o[6] = static_cast<float>(ba);
+    o[7] = cand_logits[2 * row];
+    o[8] = cand_logits[2 * row + 1];
+    for (int j = 9; j < LMH_STATS; ++j) o[j] = 0.f;
+    reinterpret_cast<int*>(o)[15] = ba;   // exact integer copy of the argmax
+  }
+}
+
+int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, int tiles_n, float* stats,
+                        cudaStream_t st) {
+  lmhead_merge_kernel<<<static_cast<unsigned>(ceil_div(M, 4)), 128, 0, st>>>(partials, cand_logits, M, tiles_n, stats);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+// Look-ahead scan (reference analysis/run_base_vs_instruct_100q.py:348-363; compare_instruct_models.py:
+// 249-272) as a per-prompt state machine advanced once per scored position:
+//   - a prompt is "alive" at position s if no EOS was generated before s (HF generate stops there, so
+//     outputs.scores has no entry for later positions);
+//   - first alive position where either candidate logit is >= the k-th largest logit wins;
+//   - otherwise the position-0 probabilities stand.
+__global__ void scan_update_kernel(const float* __restrict__ stats, int n, int pos, int topk, int eos_id,
+                                   int lookahead, ScanState s) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* r = stats + static_cast<size_t>(i) * LMH_STATS;
+  const int arg = reinterpret_cast<const int*>(r)[15];
+  int alive = (pos == 0) ? 1 : s.alive[i];
+  int resolved = (pos == 0) ? 0 : s.resolved[i];
+  if (alive && !resolved) {
+    const float lse = r[0], la = r[7], lb = r[8], kth = r[topk];   // r[1..5] = top1..top5
+    const float pa = expf(la - lse), pb = expf(lb - lse);
+    const bool hit = (la >= kth) || (lb >= kth);
+    if (pos == 0 || hit) {
+      float* o = s.out + static_cast<size_t>(i) * 8;
+      o[0] = pa; o[1] = pb; o[2] = pa / (pa + pb); o[3] = lse; o[4] = la; o[5] = lb;
+      o[6] = static_cast<float>(pos); o[7] = hit ? 1.f : 0.f;
+    }
+    if (hit) resolved = 1;
+  }
+  if (s.gen_ids) s.gen_ids[static_cast<size_t>(i) * lookahead + pos] = alive ? arg : -1;
+  s.next_tok[i] = arg;
+  if (alive && arg == eos_id) alive = 0;
+  s.alive[i] = alive; s.resolved[i] = resolved;
+  if (alive && !resolved) atomicAdd(s.n_active, 1);
+}
+
+int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int lookahead, const ScanState& s,
+                       cudaStream_t st) {
+  scan_update_kernel<<<static_cast<unsigned>(ceil_div(n, 128)), 128, 0, st>>>(stats, n, pos, topk, eos_id, lookahead, s);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+}  // namespace b2s

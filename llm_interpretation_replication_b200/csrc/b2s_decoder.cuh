@@ -1,0 +1,71 @@
+// Argument blocks and launchers for the non-GEMM decoder kernels (b2s_decoder.cu).
+#pragma once
+#include "b2s_common.cuh"
+
+namespace b2s {
+
+constexpr int ATT_THREADS = 256;
+constexpr int ATT_HG = 8;   // query heads per CTA (sharing one KV head)
+
+struct BatchMeta {           // all device pointers, sized for max_seqs / max_tokens
+  int32_t* q_start;   // [N] first row of the sequence in the current activation buffers
+  int32_t* q_len;     // [N]
+  int32_t* kv_start;  // [N] first cache slot of the sequence
+  int32_t* kv_len;    // [N] keys visible to the last query row
+  int32_t* last_row;  // [N] row whose hidden state feeds the LM head
+  int32_t* pos;       // [T] rotary position of each row
+  int32_t* slot;      // [T] cache slot each row's K/V is appended to
+};
+
+struct LnArgs {
+  float* x;                 // [rows_in, d] residual stream (written when tokens != null)
+  const int32_t* tokens;    // gather rows of wte instead of reading x (layer-0 fusion), or null
+  const void* wte;          // embedding table (bf16 or f32)
+  const int32_t* rows;      // optional row gather: output row i <- input row rows[i]
+  const float *g1, *b1, *g2, *b2;
+  void *y1, *y2;            // outputs (AT); y2 optional (second LayerNorm of a parallel-residual layer)
+  int d;
+  float eps;
+};
+
+struct RopeArgs {
+  void* qkv;                // [T, qkv_dim] (AT), q rotated in place
+  void *kcache, *vcache;    // this layer's cache: [slots, nkv*hd] (AT)
+  const int32_t *pos, *slot;
+  const float *cos, *sin;   // [max_pos, rd/2]
+  int qkv_dim, nh, nkv, hd, rd;
+  int q_base, q_hstride, k_base, v_base, kv_hstride;
+};
+
+struct AttnArgs {
+  const void* qkv;          // rotated queries live here
+  const void *kcache, *vcache;
+  void* out;                // [T, nh*hd] (AT)
+  BatchMeta meta;
+  int qkv_dim, nh, nkv, hd, rep /* nh / nkv */;
+  int q_base, q_hstride;
+  int max_kv;
+  float scale;
+};
+
+struct ScanState {
+  int32_t* alive;      // [N]
+  int32_t* resolved;   // [N]
+  int32_t* next_tok;   // [N] greedy token = input of the next decode step
+  int32_t* gen_ids;    // [N, lookahead] or null
+  int32_t* n_active;   // [1] prompts still needing another position
+  float* out;          // [N, 8]
+};
+
+int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const BatchMeta& m, cudaStream_t st);
+template <typename AT, typename WT> int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st);
+template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st);
+template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
+int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const int32_t* cand, float* partials,
+                                       float* cand_logits, cudaStream_t st);
+int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, int tiles_n, float* stats,
+                        cudaStream_t st);
+int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int lookahead, const ScanState& s,
+                       cudaStream_t st);
+
+}  // namespace b2s

@@ -1,0 +1,458 @@
+// tcgen05 + TMA bf16 GEMM for sm_100a:  C[M,N] = A[M,K] . W[N,K]^T  (both operands K-major).
+//
+// Replaces the FalconLinear / nn.Linear calls of the reference's decoder forward
+// (HF:models/falcon/modeling_falcon.py:60-65, HF:models/gpt_neox/modeling_gpt_neox.py:41-42,200-201)
+// and, with the LM-head epilogue, lm_head + float() + softmax + topk of the scoring step
+// (HF falcon:905-906; reference analysis/run_base_vs_instruct_100q.py:351-356).
+//
+// Structure: persistent CTAs (one per SM), 6 warps:
+//   warp 0      TMA producer   cp.async.bulk.tensor 2D, 128B-swizzled boxes -> smem ring (STAGES deep)
+//   warp 1      MMA issuer     one lane issues tcgen05.mma 128x256x16 (kind::f16, bf16 in / fp32 acc in TMEM)
+//   warps 2..5  epilogue       tcgen05.ld 32x32b.x32 (thread == output row), fused epilogue, global stores
+// TMEM holds two 128x256 fp32 accumulators (all 512 columns) so the epilogue of tile i overlaps the
+// MMAs of tile i+1.  Tiles are rasterised in groups of GROUP_M row-blocks so that the CTAs running at
+// the same time share A/W boxes in L2.
+#include "b2s_common.cuh"
+#include <mutex>
+#include <stdarg.h>
+
+namespace b2s {
+
+static constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
+static constexpr int STAGES = 4;
+static constexpr int GROUP_M = 16;
+static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
+static constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KB
+static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+static constexpr int NUM_THREADS = 192;
+static constexpr uint32_t TMEM_COLS = 512;
+
+struct GemmParams {
+  int M, N, K;
+  int tiles_m, tiles_n, num_kb;
+  void* out;             // bf16 or f32 [M,N]
+  const float* bias;     // [N] or null
+  LmHeadArgs lmh;
+};
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Spin with a watchdog: a protocol bug becomes a trapped kernel (reported as a CUDA error) instead of a
+// hung GPU box.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("b2s gemm_tc: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n",
+             blockIdx.x, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar,
+                                            int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tcgen05_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128B-swizzled operand tile whose rows are 128 bytes (BK = 64 bf16): 8-row groups are 1024 B
+// apart (SBO), LBO is unused for swizzled K-major layouts (canonical value 1), descriptor version 1
+// (Blackwell), layout type 2 = SWIZZLE_128B.  Fields as in cute/arch/mma_sm100_desc.hpp (SmemDescriptor).
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);   // start address, bits [0,14)
+  d |= static_cast<uint64_t>(1) << 16;                      // leading byte offset (>>4), bits [16,30)
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;              // stride byte offset (>>4), bits [32,46)
+  d |= static_cast<uint64_t>(1) << 46;                      // version = 1
+  d |= static_cast<uint64_t>(2) << 61;                      // SWIZZLE_128B
+  return d;
+}
+// Instruction descriptor (cute UMMA::InstrDescriptor): fp32 accumulate, bf16 A/B, both K-major.
+__device__ __host__ constexpr uint32_t make_idesc_bf16(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(n >> 3) << 17) |
+         (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& mb, int& nb) {
+  const int per_group = GROUP_M * tiles_n;
+  const int g = tile / per_group;
+  const int first_m = g * GROUP_M;
+  const int gm = min(GROUP_M, tiles_m - first_m);
+  const int within = tile - g * per_group;
+  mb = first_m + within % gm;
+  nb = within / gm;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Epilogues.  One thread owns one output row (TMEM lane) and sees 32 consecutive columns at a time.
+// ---------------------------------------------------------------------------------------------
+template <int EPI>
+struct RowState {};
+template <>
+struct RowState<EPI_LMHEAD> {
+  float m, s, top[5], best;
+  int arg;
+  float la, lb;
+  bool has_a, has_b;
+};
+
+template <int EPI>
+__device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0, float (&v)[32],
+                                          RowState<EPI>& st, int ca, int cb) {
+  const int N = p.N;
+  if (col0 >= N) return;
+  if (p.bias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      if (col0 + j < N) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+      }
+    }
+  }
+  if constexpr (EPI == EPI_STORE_BF16 || EPI == EPI_GELU_BF16) {
+    if constexpr (EPI == EPI_GELU_BF16) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+    }
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(row) * N + col0;
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      if (col0 + j < N) {   // N % 8 == 0 is required by the launcher
+        uint4 w;
+        w.x = pack_bf16x2(v[j], v[j + 1]);
+        w.y = pack_bf16x2(v[j + 2], v[j + 3]);
+        w.z = pack_bf16x2(v[j + 4], v[j + 5]);
+        w.w = pack_bf16x2(v[j + 6], v[j + 7]);
+        *reinterpret_cast<uint4*>(o + j) = w;
+      }
+    }
+  } else if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE_F32) {
+    float* o = reinterpret_cast<float*>(p.out) + static_cast<size_t>(row) * N + col0;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      if (col0 + j < N) {
+        float4 w = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        if constexpr (EPI == EPI_RESID_F32) {
+          const float4 r = *reinterpret_cast<const float4*>(o + j);
+          w.x += r.x; w.y += r.y; w.z += r.z; w.w += r.w;
+        }
+        *reinterpret_cast<float4*>(o + j) = w;
+      }
+    }
+  } else if constexpr (EPI == EPI_LMHEAD) {
+    float cm = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (col0 + j >= N) v[j] = -INFINITY;
+      cm = fmaxf(cm, v[j]);
+    }
+    if (cm > st.m) {
+      st.s *= __expf(st.m - cm);   // exp(-inf) = 0 on the first chunk
+      st.m = cm;
+    }
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float x = v[j];
+      acc += __expf(x - st.m);
+      if (x > st.best) { st.best = x; st.arg = col0 + j; }
+      top5_insert(st.top, x);
+      if (col0 + j == ca) { st.la = x; st.has_a = true; }
+      if (col0 + j == cb) { st.lb = x; st.has_b = true; }
+    }
+    st.s += acc;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Kernel
+// ---------------------------------------------------------------------------------------------
+template <int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = smem_base + STAGES * STAGE_BYTES;
+  // barrier layout (8 B each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then tmem ptr (4 B)
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {   // whole warp: allocate all 512 TMEM columns (1 CTA/SM, so no contention)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int mb, nb;
+        tile_coords(tile, p.tiles_m, p.tiles_n, mb, nb);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t sb = sa + A_STAGE_BYTES;
+          mbar_arrive_expect_tx(full_bar(stage), STAGE_BYTES);
+          tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, mb * BM);
+          tma_load_2d(sb, &tmB, full_bar(stage), kb * BK, nb * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1u;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);   // epilogue has drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          const uint32_t sb = sa + A_STAGE_BYTES;
+          const uint64_t adesc = make_kmajor_sw128_desc(sa);
+          const uint64_t bdesc = make_kmajor_sw128_desc(sb);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advance 16 elements (32 B) along K inside the 128B swizzle atom: +2 in the (>>4) address field
+            tcgen05_mma_bf16(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          tcgen05_commit(empty_bar(stage));   // frees the smem slot when these MMAs have read it
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        tcgen05_commit(tfull_bar(acc));       // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5) =====================
+    const int quad = warp & 3;                      // TMEM lane quadrant this warp may read
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      int mb, nb;
+      tile_coords(tile, p.tiles_m, p.tiles_n, mb, nb);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tcgen05_fence_after();
+      const int row = mb * BM + quad * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      RowState<EPI> st;
+      int ca = -1, cb = -1;
+      if constexpr (EPI == EPI_LMHEAD) {
+        st.m = -INFINITY; st.s = 0.f; st.best = -INFINITY; st.arg = 0;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) st.top[j] = -INFINITY;
+        st.la = 0.f; st.lb = 0.f; st.has_a = false; st.has_b = false;
+        if (row < p.M) { ca = p.lmh.cand_ids[2 * row]; cb = p.lmh.cand_ids[2 * row + 1]; }
+      }
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);   // warp-collective: all lanes participate
+        if (row < p.M) epi_chunk<EPI>(p, row, nb * BN + c * 32, v, st, ca, cb);
+      }
+      // all TMEM reads of this accumulator are done: hand it back to the MMA warp
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if constexpr (EPI == EPI_LMHEAD) {
+        if (row < p.M) {
+          float* o = p.lmh.partials + (static_cast<size_t>(row) * p.tiles_n + nb) * LMH_PART;
+          o[0] = st.m; o[1] = st.s;
+#pragma unroll
+          for (int j = 0; j < 5; ++j) o[2 + j] = st.top[j];
+          o[7] = __int_as_float(st.arg);
+          if (st.has_a) p.lmh.cand_logits[2 * row] = st.la;
+          if (st.has_b) p.lmh.cand_logits[2 * row + 1] = st.lb;
+        }
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static int get_encode_fn() {
+  std::call_once(g_encode_once, [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess) {
+      g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    }
+  });
+  if (g_encode == nullptr) {
+    set_error("cuTensorMapEncodeTiled not available from the CUDA driver");
+    return B2S_ECUDA;
+  }
+  return B2S_OK;
+}
+
+// row-major [rows, cols] bf16 matrix, box = [box_rows, 64 cols], 128B swizzle, OOB -> zeros
+static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  B2S_TRY(get_encode_fn());
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu base=%p)", static_cast<int>(r),
+              static_cast<unsigned long long>(rows), static_cast<unsigned long long>(cols), base);
+    return B2S_ECUDA;
+  }
+  return B2S_OK;
+}
+
+static int g_num_sms = 0;
+
+template <int EPI>
+static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr_set = true;
+  }
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+  gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, p);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
+                   const LmHeadArgs* lmh, cudaStream_t st) {
+  B2S_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
+  B2S_REQUIRE(K % 8 == 0, "gemm_bf16: K=%d must be a multiple of 8 (16-byte TMA row pitch)", K);
+  B2S_REQUIRE(epilogue == EPI_LMHEAD || N % 8 == 0, "gemm_bf16: N=%d must be a multiple of 8", N);
+  B2S_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+              "gemm_bf16: operands must be 16-byte aligned");
+  if (g_num_sms == 0) {
+    int dev = 0;
+    B2S_CHECK_CUDA(cudaGetDevice(&dev));
+    B2S_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  CUtensorMap ta, tb;
+  B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM));
+  B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN));
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.tiles_m = static_cast<int>(ceil_div(M, BM));
+  p.tiles_n = static_cast<int>(ceil_div(N, BN));
+  p.num_kb = static_cast<int>(ceil_div(K, BK));
+  p.out = out; p.bias = bias;
+  p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
+  switch (epilogue) {
+    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, p, st);
+    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, p, st);
+    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, p, st);
+    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, p, st);
+    case EPI_LMHEAD:
+      B2S_REQUIRE(lmh && lmh->partials && lmh->cand_ids && lmh->cand_logits, "gemm_bf16: LM-head epilogue needs its buffers");
+      return launch_epi<EPI_LMHEAD>(ta, tb, p, st);
+    default:
+      set_error("gemm_bf16: unknown epilogue %d", epilogue);
+      return B2S_EINVAL;
+  }
+}
+
+}  // namespace b2s

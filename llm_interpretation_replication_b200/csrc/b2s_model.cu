@@ -1,0 +1,402 @@
+// Model handle, workspace carving, the decoder forward and the scorer entry points.
+//
+// b2s_score() is the batched replacement of the reference's per-prompt get_yes_no_logprobs body
+// (analysis/run_base_vs_instruct_100q.py:329-363): prefill over varlen-packed prompts, LM head on the last
+// row of each prompt, then up to max_lookahead-1 batched single-token greedy steps over a KV cache while
+// the look-ahead scan (:348-363) is unresolved.
+#include "b2s_decoder.cuh"
+#include <stdarg.h>
+#include <vector>
+
+namespace b2s {
+
+thread_local std::string g_last_error;
+int64_t g_launch_count = 0;
+
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+}
+
+}  // namespace b2s
+
+using namespace b2s;
+
+struct b2s_model {
+  b2s_model_desc d;
+  std::vector<const void*> w;
+  int device;
+  int qkv_dim;
+  int q_base, q_hstride, k_base, v_base, kv_hstride;
+  bool bf16;
+  size_t at_size;
+  const void* gw(int slot) const { return w[slot]; }
+  const void* lw(int layer, int slot) const { return w[B2S_W_NGLOBAL + layer * B2S_W_PER_LAYER + slot]; }
+  const float* lwf(int layer, int slot) const { return reinterpret_cast<const float*>(lw(layer, slot)); }
+};
+
+namespace {
+
+struct Workspace {
+  BatchMeta meta;
+  int32_t *tokens, *cu, *cand, *gen;
+  float* out;
+  ScanState scan;
+  float* resid;
+  void *ln1, *ln2, *qkv, *attn, *act, *hfin;
+  void *kcache, *vcache;
+  size_t cache_layer_bytes;
+  float *partials, *cand_logits, *stats, *logits;
+  size_t total;
+};
+
+// Carve `base` (may be null: size query) into the buffers above.
+Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* base) {
+  Workspace w{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) -> uint8_t* {
+    uint8_t* p = base ? base + off : nullptr;
+    off += align_up(bytes, 256);
+    return p;
+  };
+  const b2s_model_desc& d = m->d;
+  const size_t at = m->at_size;
+  const int64_t rows = T > N ? T : N;   // decode steps run N rows through the same buffers
+  w.meta.q_start = reinterpret_cast<int32_t*>(take(4 * N));
+  w.meta.q_len = reinterpret_cast<int32_t*>(take(4 * N));
+  w.meta.kv_start = reinterpret_cast<int32_t*>(take(4 * N));
+  w.meta.kv_len = reinterpret_cast<int32_t*>(take(4 * N));
+  w.meta.last_row = reinterpret_cast<int32_t*>(take(4 * N));
+  w.meta.pos = reinterpret_cast<int32_t*>(take(4 * rows));
+  w.meta.slot = reinterpret_cast<int32_t*>(take(4 * rows));
+  w.tokens = reinterpret_cast<int32_t*>(take(4 * rows));
+  w.cu = reinterpret_cast<int32_t*>(take(4 * (N + 1)));
+  w.cand = reinterpret_cast<int32_t*>(take(8 * N));
+  w.gen = reinterpret_cast<int32_t*>(take(4 * static_cast<size_t>(N) * LA));
+  w.out = reinterpret_cast<float*>(take(32 * N));
+  w.scan.alive = reinterpret_cast<int32_t*>(take(4 * N));
+  w.scan.resolved = reinterpret_cast<int32_t*>(take(4 * N));
+  w.scan.next_tok = reinterpret_cast<int32_t*>(take(4 * N));
+  w.scan.n_active = reinterpret_cast<int32_t*>(take(256));
+  w.scan.gen_ids = nullptr;
+  w.scan.out = nullptr;
+  w.resid = reinterpret_cast<float*>(take(4 * rows * d.d_model));
+  w.ln1 = take(at * rows * d.d_model);
+  w.ln2 = d.n_ln_per_layer == 2 ? take(at * rows * d.d_model) : nullptr;
+  w.qkv = take(at * rows * m->qkv_dim);
+  w.attn = take(at * rows * d.n_head * d.head_dim);
+  w.act = take(at * rows * d.d_ff);
+  w.hfin = take(at * static_cast<size_t>(N) * d.d_model);
+  const size_t slots = static_cast<size_t>(T) + static_cast<size_t>(N) * LA;
+  w.cache_layer_bytes = align_up(at * slots * d.n_kv_head * d.head_dim, 256);
+  w.kcache = take(w.cache_layer_bytes * d.n_layer);
+  w.vcache = take(w.cache_layer_bytes * d.n_layer);
+  const size_t tiles_n = static_cast<size_t>(ceil_div(d.vocab, LMH_TILE_N));
+  w.partials = reinterpret_cast<float*>(take(4 * static_cast<size_t>(N) * tiles_n * LMH_PART));
+  w.cand_logits = reinterpret_cast<float*>(take(8 * N));
+  w.stats = reinterpret_cast<float*>(take(4 * static_cast<size_t>(N) * LMH_STATS));
+  w.logits = m->bf16 ? nullptr : reinterpret_cast<float*>(take(4 * static_cast<size_t>(N) * d.vocab));
+  w.total = off;
+  return w;
+}
+
+// C = A . W^T with the mode's GEMM.  `out` is AT except for EPI_RESID_F32 (always the fp32 residual).
+int linear(const b2s_model* m, const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epi,
+           cudaStream_t st) {
+  if (m->bf16) return gemm_tc_launch(A, W, bias, out, M, N, K, epi, nullptr, st);
+  return gemm_f32_launch(reinterpret_cast<const float*>(A), reinterpret_cast<const float*>(W), bias,
+                         reinterpret_cast<float*>(out), M, N, K, epi, st);
+}
+
+template <typename AT>
+int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
+              cudaStream_t st) {
+  const b2s_model_desc& d = m->d;
+  const int dm = d.d_model;
+  const bool two_ln = d.n_ln_per_layer == 2;
+  for (int l = 0; l < d.n_layer; ++l) {
+    LnArgs ln{};
+    ln.x = w.resid; ln.d = dm; ln.eps = d.norm_eps;
+    ln.tokens = (l == 0) ? tokens : nullptr;
+    ln.wte = m->gw(B2S_W_WTE);
+    ln.g1 = m->lwf(l, B2S_WL_LN1_G); ln.b1 = m->lwf(l, B2S_WL_LN1_B);
+    ln.y1 = w.ln1;
+    if (two_ln && d.parallel_residual) {   // both LayerNorms read the same residual: one pass, two affines
+      ln.g2 = m->lwf(l, B2S_WL_LN2_G); ln.b2 = m->lwf(l, B2S_WL_LN2_B); ln.y2 = w.ln2;
+    }
+    B2S_TRY((launch_ln<AT, AT>(ln, rows, st)));
+
+    B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
+                   EPI_STORE_BF16, st));
+    uint8_t* kc = reinterpret_cast<uint8_t*>(w.kcache) + w.cache_layer_bytes * l;
+    uint8_t* vc = reinterpret_cast<uint8_t*>(w.vcache) + w.cache_layer_bytes * l;
+    RopeArgs ro{};
+    ro.qkv = w.qkv; ro.kcache = kc; ro.vcache = vc; ro.pos = w.meta.pos; ro.slot = w.meta.slot;
+    ro.cos = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_COS));
+    ro.sin = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_SIN));
+    ro.qkv_dim = m->qkv_dim; ro.nh = d.n_head; ro.nkv = d.n_kv_head; ro.hd = d.head_dim; ro.rd = d.rotary_dim;
+    ro.q_base = m->q_base; ro.q_hstride = m->q_hstride; ro.k_base = m->k_base; ro.v_base = m->v_base;
+    ro.kv_hstride = m->kv_hstride;
+    B2S_TRY(launch_rope_cache<AT>(ro, rows, st));
+
+    AttnArgs at{};
+    at.qkv = w.qkv; at.kcache = kc; at.vcache = vc; at.out = w.attn; at.meta = w.meta;
+    at.qkv_dim = m->qkv_dim; at.nh = d.n_head; at.nkv = d.n_kv_head; at.hd = d.head_dim; at.rep = d.n_head / d.n_kv_head;
+    at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
+    at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
+    B2S_TRY(launch_attn<AT>(at, n_seqs, st));
+
+    B2S_TRY(linear(m, w.attn, m->lw(l, B2S_WL_W_DENSE), m->lwf(l, B2S_WL_B_DENSE), w.resid, rows, dm,
+                   d.n_head * d.head_dim, EPI_RESID_F32, st));
+    const void* mlp_in = w.ln1;
+    if (two_ln) {
+      mlp_in = w.ln2;
+      if (!d.parallel_residual) {   // sequential residual: second LayerNorm reads x + attn
+        LnArgs l2{};
+        l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps;
+        l2.g1 = m->lwf(l, B2S_WL_LN2_G); l2.b1 = m->lwf(l, B2S_WL_LN2_B); l2.y1 = w.ln2;
+        B2S_TRY((launch_ln<AT, AT>(l2, rows, st)));
+      }
+    }
+    B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st));
+    B2S_TRY(linear(m, w.act, m->lw(l, B2S_WL_W_DOWN), m->lwf(l, B2S_WL_B_DOWN), w.resid, rows, dm, d.d_ff,
+                   EPI_RESID_F32, st));
+  }
+  // final LayerNorm on the last row of every prompt only (HF generate sets logits_to_keep=1)
+  LnArgs lf{};
+  lf.x = w.resid; lf.d = dm; lf.eps = d.norm_eps; lf.rows = w.meta.last_row;
+  lf.g1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_G)); lf.b1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_B));
+  lf.y1 = w.hfin;
+  B2S_TRY((launch_ln<AT, AT>(lf, n_seqs, st)));
+  return B2S_OK;
+}
+
+int forward(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
+            cudaStream_t st) {
+  if (m->bf16) return forward_t<__nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, st);
+  return forward_t<float>(m, w, tokens, rows, n_seqs, max_kv, st);
+}
+
+int lm_head(const b2s_model* m, const Workspace& w, const int32_t* cand, int n_seqs, cudaStream_t st) {
+  const b2s_model_desc& d = m->d;
+  const int tiles_n = static_cast<int>(ceil_div(d.vocab, LMH_TILE_N));
+  B2S_CHECK_CUDA(cudaMemsetAsync(w.cand_logits, 0, 8 * static_cast<size_t>(n_seqs), st));
+  if (m->bf16) {
+    LmHeadArgs a{cand, w.partials, w.cand_logits};
+    B2S_TRY(gemm_tc_launch(w.hfin, m->gw(B2S_W_LM_HEAD), nullptr, nullptr, n_seqs, d.vocab, d.d_model, EPI_LMHEAD, &a, st));
+  } else {
+    B2S_TRY(gemm_f32_launch(reinterpret_cast<const float*>(w.hfin), reinterpret_cast<const float*>(m->gw(B2S_W_LM_HEAD)),
+                            nullptr, w.logits, n_seqs, d.vocab, d.d_model, EPI_STORE_F32, st));
+    B2S_TRY(launch_lmhead_partials_from_logits(w.logits, n_seqs, d.vocab, cand, w.partials, w.cand_logits, st));
+  }
+  return launch_lmhead_merge(w.partials, w.cand_logits, n_seqs, tiles_n, w.stats, st);
+}
+
+}  // namespace
+
+// =================================================================================================
+// extern "C"
+// =================================================================================================
+extern "C" {
+
+const char* b2s_last_error(void) { return g_last_error.c_str(); }
+int b2s_abi_version(void) { return B2S_ABI_VERSION; }
+
+int64_t b2s_launch_count(int32_t reset) {
+  const int64_t v = g_launch_count;
+  if (reset) g_launch_count = 0;
+  return v;
+}
+
+int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs, int32_t n_ptrs, int32_t device,
+                     b2s_model** out) {
+  B2S_REQUIRE(desc && weight_ptrs && out, "model_create: null argument");
+  B2S_REQUIRE(desc->abi_version == B2S_ABI_VERSION, "model_create: ABI version %d, library is %d", desc->abi_version,
+              B2S_ABI_VERSION);
+  const b2s_model_desc& d = *desc;
+  B2S_REQUIRE(d.n_layer > 0 && d.d_model > 0 && d.n_head > 0 && d.n_kv_head > 0 && d.vocab > 0 && d.d_ff > 0,
+              "model_create: non-positive dimension");
+  B2S_REQUIRE(d.n_head % d.n_kv_head == 0, "model_create: n_head %d not a multiple of n_kv_head %d", d.n_head, d.n_kv_head);
+  B2S_REQUIRE(d.head_dim == 64 || d.head_dim == 80 || d.head_dim == 128, "model_create: head_dim %d unsupported (64, 80, 128)",
+              d.head_dim);
+  B2S_REQUIRE(d.rotary_dim > 0 && d.rotary_dim <= d.head_dim && d.rotary_dim % 2 == 0, "model_create: bad rotary_dim %d",
+              d.rotary_dim);
+  B2S_REQUIRE(d.n_ln_per_layer == 1 || d.n_ln_per_layer == 2, "model_create: n_ln_per_layer must be 1 or 2");
+  B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
+  B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP32_CHECK,
+              "model_create: unknown compute mode %d", d.compute_mode);
+  B2S_REQUIRE(d.d_model % 8 == 0 && d.d_ff % 8 == 0, "model_create: d_model and d_ff must be multiples of 8");
+  const int need = B2S_W_NGLOBAL + B2S_W_PER_LAYER * d.n_layer;
+  B2S_REQUIRE(n_ptrs >= need, "model_create: %d weight pointers given, %d needed", n_ptrs, need);
+  int ndev = 0;
+  B2S_CHECK_CUDA(cudaGetDeviceCount(&ndev));
+  B2S_REQUIRE(device >= 0 && device < ndev, "model_create: device %d out of range (%d visible)", device, ndev);
+  cudaDeviceProp prop;
+  B2S_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error("model_create: device %d is sm_%d%d; this library only contains sm_100a code", device, prop.major, prop.minor);
+    return B2S_EUNSUPPORTED;
+  }
+  b2s_model* m = new b2s_model();
+  m->d = d;
+  m->w.assign(weight_ptrs, weight_ptrs + need);
+  m->device = device;
+  m->bf16 = d.compute_mode == B2S_MODE_BF16_FAST;
+  m->at_size = m->bf16 ? 2 : 4;
+  m->qkv_dim = (d.n_head + 2 * d.n_kv_head) * d.head_dim;
+  if (d.qkv_layout == B2S_QKV_FALCON_MQA) {
+    m->q_base = 0; m->q_hstride = d.head_dim;
+    m->k_base = d.n_head * d.head_dim; m->v_base = (d.n_head + d.n_kv_head) * d.head_dim; m->kv_hstride = d.head_dim;
+  } else if (d.qkv_layout == B2S_QKV_NEOX_INTERLEAVED) {
+    if (d.n_head != d.n_kv_head) { delete m; set_error("model_create: NeoX qkv layout needs n_kv_head == n_head"); return B2S_EINVAL; }
+    m->q_base = 0; m->q_hstride = 3 * d.head_dim; m->k_base = d.head_dim; m->v_base = 2 * d.head_dim;
+    m->kv_hstride = 3 * d.head_dim;
+  } else {
+    delete m;
+    set_error("model_create: unknown qkv layout %d", d.qkv_layout);
+    return B2S_EINVAL;
+  }
+  const int required[] = {B2S_W_WTE, B2S_W_LNF_G, B2S_W_LNF_B, B2S_W_LM_HEAD, B2S_W_ROPE_COS, B2S_W_ROPE_SIN};
+  for (int s : required) {
+    if (m->w[s] == nullptr) { delete m; set_error("model_create: global weight slot %d is null", s); return B2S_EINVAL; }
+  }
+  for (int l = 0; l < d.n_layer; ++l) {
+    const int mats[] = {B2S_WL_LN1_G, B2S_WL_LN1_B, B2S_WL_W_QKV, B2S_WL_W_DENSE, B2S_WL_W_UP, B2S_WL_W_DOWN};
+    for (int s : mats) {
+      if (m->lw(l, s) == nullptr) { delete m; set_error("model_create: layer %d slot %d is null", l, s); return B2S_EINVAL; }
+    }
+    if (d.n_ln_per_layer == 2 && (m->lw(l, B2S_WL_LN2_G) == nullptr || m->lw(l, B2S_WL_LN2_B) == nullptr)) {
+      delete m; set_error("model_create: layer %d second LayerNorm is null", l); return B2S_EINVAL;
+    }
+  }
+  *out = m;
+  return B2S_OK;
+}
+
+void b2s_model_destroy(b2s_model* m) { delete m; }
+
+size_t b2s_workspace_bytes(const b2s_model* m, int64_t max_tokens, int32_t max_seqs, int32_t max_lookahead) {
+  if (!m || max_tokens <= 0 || max_seqs <= 0 || max_lookahead <= 0) return 0;
+  return carve(m, max_tokens, max_seqs, max_lookahead, nullptr).total + 256;
+}
+
+int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs, int32_t total_tokens,
+              int32_t max_seqlen, const int32_t* cand_ids, int32_t topk, int32_t max_lookahead, int32_t eos_id, float* out,
+              int32_t* gen_ids, void* workspace, size_t workspace_bytes, void* stream) {
+  B2S_REQUIRE(m && tokens && cu_seqlens && cand_ids && out && workspace, "score: null argument");
+  B2S_REQUIRE(n_seqs > 0 && total_tokens >= n_seqs && max_seqlen > 0, "score: empty batch (n_seqs=%d total_tokens=%d)", n_seqs,
+              total_tokens);
+  B2S_REQUIRE(topk >= 1 && topk <= 5, "score: topk=%d outside [1,5]", topk);
+  B2S_REQUIRE(max_lookahead >= 1 && max_lookahead <= 64, "score: max_lookahead=%d outside [1,64]", max_lookahead);
+  B2S_REQUIRE(max_seqlen + max_lookahead <= m->d.max_pos, "score: prompt of %d tokens + %d look-ahead exceeds max_pos %d",
+              max_seqlen, max_lookahead, m->d.max_pos);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  uint8_t* base = reinterpret_cast<uint8_t*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
+  Workspace w = carve(m, total_tokens, n_seqs, max_lookahead, base);
+  B2S_REQUIRE(w.total + (base - reinterpret_cast<uint8_t*>(workspace)) <= workspace_bytes,
+              "score: workspace of %zu bytes is too small, %zu needed", workspace_bytes, w.total + 256);
+  B2S_CHECK_CUDA(cudaSetDevice(m->device));
+  w.scan.out = out;
+  w.scan.gen_ids = gen_ids;
+  if (gen_ids) B2S_CHECK_CUDA(cudaMemsetAsync(gen_ids, 0xFF, 4 * static_cast<size_t>(n_seqs) * max_lookahead, st));
+
+  B2S_TRY(launch_prep(cu_seqlens, n_seqs, max_lookahead, 0, w.meta, st));
+  B2S_TRY(forward(m, w, tokens, total_tokens, n_seqs, max_seqlen, st));
+  B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
+  B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
+  B2S_TRY(launch_scan_update(w.stats, n_seqs, 0, topk, eos_id, max_lookahead, w.scan, st));
+  for (int step = 1; step < max_lookahead; ++step) {
+    int32_t active = 0;
+    B2S_CHECK_CUDA(cudaMemcpyAsync(&active, w.scan.n_active, 4, cudaMemcpyDeviceToHost, st));
+    B2S_CHECK_CUDA(cudaStreamSynchronize(st));
+    if (active == 0) break;
+    B2S_TRY(launch_prep(cu_seqlens, n_seqs, max_lookahead, step, w.meta, st));
+    B2S_TRY(forward(m, w, w.scan.next_tok, n_seqs, n_seqs, max_seqlen + step, st));
+    B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
+    B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
+    B2S_TRY(launch_scan_update(w.stats, n_seqs, step, topk, eos_id, max_lookahead, w.scan, st));
+  }
+  return B2S_OK;
+}
+
+int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_h, int32_t n_seqs, const int32_t* cand_h,
+                   int32_t topk, int32_t max_lookahead, int32_t eos_id, float* out_h, int32_t* gen_h, void* workspace,
+                   size_t workspace_bytes, void* stream) {
+  B2S_REQUIRE(m && tokens_h && cu_h && cand_h && out_h && workspace, "score_host: null argument");
+  B2S_REQUIRE(n_seqs > 0, "score_host: empty batch");
+  B2S_REQUIRE(max_lookahead >= 1 && max_lookahead <= 64, "score_host: max_lookahead=%d outside [1,64]", max_lookahead);
+  int64_t total = cu_h[n_seqs];
+  int max_len = 0;
+  B2S_REQUIRE(cu_h[0] == 0, "score_host: cu_seqlens[0] must be 0");
+  for (int i = 0; i < n_seqs; ++i) {
+    const int L = cu_h[i + 1] - cu_h[i];
+    B2S_REQUIRE(L > 0, "score_host: prompt %d is empty", i);
+    if (L > max_len) max_len = L;
+  }
+  for (int64_t t = 0; t < total; ++t)
+    B2S_REQUIRE(tokens_h[t] >= 0 && tokens_h[t] < m->d.vocab, "score_host: token %d at %lld outside the vocabulary", tokens_h[t],
+                static_cast<long long>(t));
+  for (int i = 0; i < 2 * n_seqs; ++i)
+    B2S_REQUIRE(cand_h[i] >= 0 && cand_h[i] < m->d.vocab, "score_host: candidate id %d outside the vocabulary", cand_h[i]);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  uint8_t* base = reinterpret_cast<uint8_t*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
+  Workspace w = carve(m, total, n_seqs, max_lookahead, base);
+  B2S_REQUIRE(w.total + 256 <= workspace_bytes, "score_host: workspace of %zu bytes is too small, %zu needed", workspace_bytes,
+              w.total + 256);
+  B2S_CHECK_CUDA(cudaSetDevice(m->device));
+  B2S_CHECK_CUDA(cudaMemcpyAsync(w.tokens, tokens_h, 4 * total, cudaMemcpyHostToDevice, st));
+  B2S_CHECK_CUDA(cudaMemcpyAsync(w.cu, cu_h, 4 * (n_seqs + 1), cudaMemcpyHostToDevice, st));
+  B2S_CHECK_CUDA(cudaMemcpyAsync(w.cand, cand_h, 8 * n_seqs, cudaMemcpyHostToDevice, st));
+  // During the prefill the token buffer is only read by layer 0; decode steps read scan.next_tok.
+  B2S_TRY(b2s_score(m, w.tokens, w.cu, n_seqs, static_cast<int32_t>(total), max_len, w.cand, topk, max_lookahead, eos_id, w.out,
+                    gen_h ? w.gen : nullptr, workspace, workspace_bytes, stream));
+  B2S_CHECK_CUDA(cudaMemcpyAsync(out_h, w.out, 32 * static_cast<size_t>(n_seqs), cudaMemcpyDeviceToHost, st));
+  if (gen_h)
+    B2S_CHECK_CUDA(cudaMemcpyAsync(gen_h, w.gen, 4 * static_cast<size_t>(n_seqs) * max_lookahead, cudaMemcpyDeviceToHost, st));
+  B2S_CHECK_CUDA(cudaStreamSynchronize(st));
+  return B2S_OK;
+}
+
+// ---- building blocks ------------------------------------------------------------------------------
+int b2s_gemm_bf16(const void* A, const void* W, const float* bias, void* out, int32_t M, int32_t N, int32_t K, int32_t epilogue,
+                  void* stream) {
+  B2S_REQUIRE(A && W && out, "gemm_bf16: null argument");
+  B2S_REQUIRE(epilogue != EPI_LMHEAD, "gemm_bf16: use b2s_lm_head_bf16 for the LM-head epilogue");
+  return gemm_tc_launch(A, W, bias, out, M, N, K, epilogue, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b2s_gemm_f32(const float* A, const float* W, const float* bias, float* out, int32_t M, int32_t N, int32_t K, int32_t epilogue,
+                 void* stream) {
+  B2S_REQUIRE(A && W && out, "gemm_f32: null argument");
+  return gemm_f32_launch(A, W, bias, out, M, N, K, epilogue, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t b2s_lm_head_scratch_bytes(int32_t M, int32_t V) {
+  if (M <= 0 || V <= 0) return 0;
+  const size_t tiles_n = static_cast<size_t>(ceil_div(V, LMH_TILE_N));
+  return align_up(4 * static_cast<size_t>(M) * tiles_n * LMH_PART, 256) + align_up(8 * static_cast<size_t>(M), 256);
+}
+
+int b2s_lm_head_bf16(const void* hidden, const void* W, const int32_t* cand_ids, int32_t M, int32_t V, int32_t d, float* stats,
+                     void* scratch, size_t scratch_bytes, void* stream) {
+  B2S_REQUIRE(hidden && W && cand_ids && stats && scratch, "lm_head: null argument");
+  B2S_REQUIRE(M > 0 && V > 0 && d > 0, "lm_head: empty problem");
+  B2S_REQUIRE(scratch_bytes >= b2s_lm_head_scratch_bytes(M, V), "lm_head: scratch of %zu bytes is too small, %zu needed",
+              scratch_bytes, b2s_lm_head_scratch_bytes(M, V));
+  B2S_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 255) == 0, "lm_head: scratch must be 256-byte aligned");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int tiles_n = static_cast<int>(ceil_div(V, LMH_TILE_N));
+  float* partials = reinterpret_cast<float*>(scratch);
+  float* cand_logits = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) +
+                                                align_up(4 * static_cast<size_t>(M) * tiles_n * LMH_PART, 256));
+  B2S_CHECK_CUDA(cudaMemsetAsync(cand_logits, 0, 8 * static_cast<size_t>(M), st));
+  LmHeadArgs a{cand_ids, partials, cand_logits};
+  B2S_TRY(gemm_tc_launch(hidden, W, nullptr, nullptr, M, V, d, EPI_LMHEAD, &a, st));
+  return launch_lmhead_merge(partials, cand_logits, M, tiles_n, stats, st);
+}
+
+}  // extern "C"

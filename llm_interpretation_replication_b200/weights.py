@@ -7,8 +7,8 @@ paths carry signal.  The same tensors are loaded into the HF model that serves a
 (``to_hf_state_dict``), so both sides see identical (bf16-representable when asked) numbers.
 
 Slot order (``B2S_W_*`` in the header):
-  global:    0 wte[V,d]  1 lnf_g[d]  2 lnf_b[d]  3 lm_head[V,d]
-  per layer: base = 4 + 16*l
+  global:    0 wte[V,d]  1 lnf_g[d]  2 lnf_b[d]  3 lm_head[V,d]  4 rope_cos[max_pos,rd/2]  5 rope_sin
+  per layer: base = 6 + 16*l
              +0 ln1_g +1 ln1_b +2 ln2_g +3 ln2_b +4 w_qkv[qkv,d] +5 b_qkv +6 w_dense[d,nh*hd] +7 b_dense
              +8 w_up[ff,d] +9 b_up +10 w_down[d,ff] +11 b_down   (+12..15 reserved)
 Matrices are stored in the model's weight dtype (bf16 or fp32); vectors are always fp32.
@@ -21,13 +21,22 @@ import torch
 
 from .shapes import DecoderShape, ARCH_FALCON, ARCH_GPT_NEOX
 
-N_GLOBAL = 4
+N_GLOBAL = 6
 N_PER_LAYER = 16
-MATRIX_SLOTS = (4, 6, 8, 10)
+
+
+def rope_tables(shape: DecoderShape, device="cpu"):
+    """cos/sin of HF's rotary embedding (HF falcon:154-165): fp32 inv_freq x fp32 position, first
+    rotary_dim/2 columns (the table HF builds is cat(freqs, freqs))."""
+    rd = shape.rotary_dim
+    inv_freq = 1.0 / (shape.rope_theta ** (torch.arange(0, rd, 2, dtype=torch.int64).float() / rd))
+    pos = torch.arange(shape.max_pos, dtype=torch.float32)
+    freqs = pos[:, None] * inv_freq[None, :]
+    return freqs.cos().contiguous().to(device), freqs.sin().contiguous().to(device)
 
 
 def slot_names(shape: DecoderShape) -> List[Optional[str]]:
-    names: List[Optional[str]] = ["wte", "lnf_g", "lnf_b", "lm_head"]
+    names: List[Optional[str]] = ["wte", "lnf_g", "lnf_b", "lm_head", "rope_cos", "rope_sin"]
     per = ["ln1_g", "ln1_b", "ln2_g", "ln2_b", "w_qkv", "b_qkv", "w_dense", "b_dense",
            "w_up", "b_up", "w_down", "b_down", None, None, None, None]
     for l in range(shape.n_layer):
@@ -136,6 +145,17 @@ def to_device(W: Dict[str, torch.Tensor], device, weight_dtype) -> Dict[str, tor
     if "lm_head" not in out:
         out["lm_head"] = out["wte"]
     return out
+
+
+def pointer_table(shape: DecoderShape, Wdev: Dict[str, torch.Tensor]):
+    """ctypes array of device pointers in slot order (null where the model has no such tensor)."""
+    import ctypes as C
+    names = slot_names(shape)
+    arr = (C.c_void_p * len(names))()
+    for i, n in enumerate(names):
+        t = Wdev.get(n) if n is not None else None
+        arr[i] = None if t is None else t.data_ptr()
+    return arr
 
 
 # ---- HF oracle side ---------------------------------------------------------------------

@@ -1,0 +1,95 @@
+"""GPU parity of the building-block kernels, called through the C-ABI."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, scale=1.0, seed=0, dtype=torch.bfloat16):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(shape, generator=g, device="cuda") * scale).to(dtype)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (128, 256, 512), (256, 512, 4544), (300, 520, 192),
+                                   (77, 4672, 4544), (1, 264, 72), (1000, 4544, 1024), (513, 18176, 4544)])
+def test_gemm_tc_store_f32(M, N, K):
+    import gpu_util as U
+    A, W = _rand((M, K), 1.0, 1), _rand((N, K), 0.05, 2)
+    ref = A.float() @ W.float().T
+    out = U.gemm_bf16(A, W, None, 4)
+    torch.cuda.synchronize()
+    err = (out - ref).abs().max().item()
+    assert err <= 2e-3 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("epi", [0, 1, 2])
+@pytest.mark.parametrize("use_bias", [False, True])
+def test_gemm_tc_epilogues(epi, use_bias):
+    import gpu_util as U
+    M, N, K = 391, 1160, 832
+    A, W = _rand((M, K), 1.0, 3), _rand((N, K), 0.05, 4)
+    bias = _rand((N,), 0.5, 5, torch.float32) if use_bias else None
+    ref = A.float() @ W.float().T
+    if use_bias:
+        ref = ref + bias
+    if epi == 1:
+        ref = torch.nn.functional.gelu(ref)
+    if epi == 2:
+        resid = _rand((M, N), 1.0, 6, torch.float32)
+        out = U.gemm_bf16(A, W, bias, 2, out=resid.clone())
+        ref = ref + resid
+        tol = 2e-3
+    else:
+        out = U.gemm_bf16(A, W, bias, epi).float()
+        tol = 2.0 ** -7   # one bf16 ulp relative
+    torch.cuda.synchronize()
+    err = ((out - ref).abs() / (ref.abs() + 1.0)).max().item()
+    assert err <= tol, err
+
+
+def test_gemm_tc_rejects_bad_shapes():
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import _lib
+    A, W = _rand((8, 20), 1, 1), _rand((16, 20), 1, 2)   # K not a multiple of 8
+    with pytest.raises(_lib.B2SError):
+        U.gemm_bf16(A, W, None, 4)
+
+
+@pytest.mark.parametrize("M,N,K", [(64, 64, 16), (100, 70, 33), (257, 513, 129)])
+@pytest.mark.parametrize("epi", [4, 1, 2])
+def test_gemm_f32(M, N, K, epi):
+    import gpu_util as U
+    A, W = _rand((M, K), 1.0, 1, torch.float32), _rand((N, K), 0.1, 2, torch.float32)
+    bias = _rand((N,), 0.5, 3, torch.float32)
+    ref = (A.double() @ W.double().T + bias.double())
+    if epi == 1:
+        ref = torch.nn.functional.gelu(ref)
+    out0 = _rand((M, N), 1.0, 4, torch.float32)
+    if epi == 2:
+        ref = ref + out0.double()
+    out = U.gemm_f32(A, W, bias, epi, out=out0.clone())
+    torch.cuda.synchronize()
+    assert (out.double() - ref).abs().max().item() <= 1e-4
+
+
+@pytest.mark.parametrize("M,V,d", [(5, 1000, 192), (128, 65024, 256), (200, 50432, 512), (1, 320, 64)])
+def test_lm_head_fused(M, V, d):
+    import gpu_util as U
+    h, W = _rand((M, d), 1.0, 7), _rand((V, d), 0.05, 8)
+    g = torch.Generator(device="cuda").manual_seed(9)
+    cand = torch.randint(0, V, (M, 2), generator=g, device="cuda", dtype=torch.int32)
+    logits = h.float() @ W.float().T
+    cand[0, 0] = int(logits[0].argmax())       # a candidate that is the arg max
+    cand[-1, 1] = V - 1                        # last column of the (ragged) last tile
+    stats = U.lm_head(h, W, cand)
+    torch.cuda.synchronize()
+    lse = torch.logsumexp(logits, dim=-1)
+    top5 = torch.topk(logits, 5, dim=-1).values
+    assert (stats[:, 0] - lse).abs().max().item() <= 2e-3
+    assert (stats[:, 1:6] - top5).abs().max().item() <= 2e-3
+    arg = stats.view(torch.int32)[:, 15].long()
+    picked = logits.gather(1, arg[:, None])[:, 0]
+    assert (picked - logits.max(dim=-1).values).abs().max().item() <= 2e-3   # arg max up to fp32 summation order
+    ca = logits.gather(1, cand.long())
+    assert (stats[:, 7:9] - ca).abs().max().item() <= 2e-3

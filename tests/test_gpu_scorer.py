@@ -1,0 +1,117 @@
+"""GPU parity of the scorer against the oracle and the reference-generated golden vectors.
+
+Tolerances (BASELINE.json north_star): |delta relative_prob| <= 1e-5 per prompt in the fp32 check mode,
+<= 2e-3 in bf16; identical candidate ids; identical look-ahead position."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-5
+TOL_BF16 = 2e-3
+
+
+def _run_case(case, mode, tol):
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights
+    from llm_interpretation_replication_b200 import scorer as S
+    from oracle import decoder_ref
+    shp = shapes.REGISTRY[case["shape"]]()
+    W = weights.init_weights(shp, seed=case["seed"])
+    sc = U.make_scorer(shp, W, mode, max_tokens=4096, max_seqs=64)
+    worst = 0.0
+    for variant, key, topk in (("100q", "ref_100q", 5), ("instruct", "ref_instruct", 2)):
+        ids, cands = [], []
+        for row in case["rows"]:
+            tok = U.tok_for(shp, row)
+            ids.append(tok(row["prompt"]).input_ids)
+            cands.append(S.candidate_ids(tok, variant))
+        rows, gens = sc.score_ids(ids, np.array(cands), topk=topk, eos_id=shp.eos_id)
+        for i, row in enumerate(case["rows"]):
+            g = row[key]
+            d = S._row_to_dict(rows[i], gens[i], variant, row["prompt"], U.tok_for(shp, row))
+            # golden = the reference's own function; oracle = its restatement (tested equal on CPU)
+            o = decoder_ref.score_ids(shp, W, ids[i], cands[i][0], cands[i][1], topk=topk, eos_id=shp.eos_id)
+            if mode == shapes.MODE_FP32_CHECK or o["pos_found"] == int(rows[i][6]):
+                assert int(rows[i][6]) == o["pos_found"], (variant, i)
+                assert bool(rows[i][7]) == o["found"]
+                err = abs(d["relative_prob"] - g["relative_prob"])
+                worst = max(worst, err)
+                assert err <= tol, (variant, i, err)
+                assert abs(d["yes_prob"] - g["yes_prob"]) <= tol and abs(d["no_prob"] - g["no_prob"]) <= tol
+                n = min(len(o["gen_ids"]), 10)
+                if mode == shapes.MODE_FP32_CHECK:
+                    assert [int(t) for t in gens[i][:n]] == o["gen_ids"][:n]
+                    assert g["completion"].startswith(d["completion"][:100]) or d["completion"].startswith(g["completion"])
+            if variant == "instruct" and mode == shapes.MODE_FP32_CHECK:
+                assert d["position_found"] == g["position_found"] and d["yes_no_found"] == g["yes_no_found"]
+    sc.close()
+    return worst
+
+
+@pytest.mark.parametrize("case_idx", [0, 1, 2])
+def test_scorer_fp32_check_vs_reference_golden(case_idx):
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes
+    _run_case(U.golden_cases()[case_idx], shapes.MODE_FP32_CHECK, TOL_FP32)
+
+
+@pytest.mark.parametrize("case_idx", [0, 1, 2])
+def test_scorer_bf16_vs_reference_golden(case_idx):
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes
+    _run_case(U.golden_cases()[case_idx], shapes.MODE_BF16_FAST, TOL_BF16)
+
+
+def test_scorer_edge_cases():
+    """Empty input, ragged lengths down to one token, EOS stopping the look-ahead, size limits."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights, _lib
+    from oracle import decoder_ref
+    shp = shapes.tiny_falcon()
+    W = weights.init_weights(shp, seed=7)
+    sc = U.make_scorer(shp, W, shapes.MODE_FP32_CHECK, max_tokens=512, max_seqs=8)
+    rows, gens = sc.score_ids([], np.zeros((0, 2)))
+    assert rows.shape == (0, 8)
+    g = np.random.RandomState(0)
+    ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (1, 2, 17, 64, 5, 130, 33, 1, 96, 3)]
+    # use the token greedy decoding emits at position 2 of prompt 2 as "EOS": the look-ahead must stop there
+    o = decoder_ref.score_ids(shp, W, ids[2], 40, 41, topk=5, eos_id=-1)
+    eos = o["gen_ids"][2]
+    rows, gens = sc.score_ids(ids, np.array([[40, 41]]), topk=5, eos_id=eos)     # > max_seqs -> several batches
+    for i, x in enumerate(ids):
+        o = decoder_ref.score_ids(shp, W, x, 40, 41, topk=5, eos_id=eos)
+        assert abs(rows[i][2] - o["rel"]) <= 1e-5, i
+        assert int(rows[i][6]) == o["pos_found"]
+        k = o["n_scores"]
+        assert [int(t) for t in gens[i][:k]] == o["gen_ids"]
+        assert all(int(t) == -1 for t in gens[i][k:])
+    assert any(len(decoder_ref.score_ids(shp, W, x, 40, 41, eos_id=eos)["gen_ids"]) < 10 for x in ids)
+    with pytest.raises(ValueError):
+        sc.score_ids([list(range(32, 32 + 600))], np.array([[40, 41]]))          # longer than max_tokens
+    with pytest.raises(ValueError):
+        sc.score_ids([[40, 41]], np.array([[40, shp.vocab]]))                     # candidate outside vocab
+    with pytest.raises(ValueError):
+        sc.score_ids([[]], np.array([[40, 41]]))                                  # empty prompt
+    sc.close()
+
+
+def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle():
+    """Falcon-7B widths (d=4544, 71 heads MQA, ffn 18176, V=65024; ragged GEMM tails) at 2 layers."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights
+    from oracle import decoder_ref
+    shp = shapes.falcon_7b().with_layers(2)
+    W = weights.init_weights(shp, seed=3)
+    sc = U.make_scorer(shp, W, shapes.MODE_BF16_FAST, max_tokens=2048, max_seqs=16, max_lookahead=2)
+    g = np.random.RandomState(1)
+    ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (66, 111, 190, 128, 97)]
+    rows, gens = sc.score_ids(ids, np.array([[1000, 2000]]), topk=5, max_lookahead=2)
+    for i, x in enumerate(ids):
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=decoder_ref.bf16_round)
+        p = torch.softmax(lo, -1)
+        rel = (p[1000] / (p[1000] + p[2000])).item()
+        assert abs(rows[i][2] - rel) <= TOL_BF16, (i, rows[i][2], rel)
+        assert abs(rows[i][3] - torch.logsumexp(lo, -1).item()) <= 5e-3
+    sc.close()
