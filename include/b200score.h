@@ -92,6 +92,12 @@ B2S_API int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t*
 /* Number of kernels this library launched since the last call with reset != 0 (bench "gpu_launches"). */
 B2S_API int64_t b2s_launch_count(int32_t reset);
 
+/* Measurement hook (no counterpart in the reference): when enabled, every tensor-core GEMM launch is
+ * bracketed by CUDA events on its stream; _read() waits for them and returns the summed device time, the
+ * number of launches and their algorithmic FLOPs (2*M*N*K) since the previous read. */
+B2S_API int b2s_profile_gemm(int32_t enable);
+B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* flops);
+
 /* ---- building blocks (exported so the parity tests can exercise each kernel through the ABI) ----
  * C[M,N] = A[M,K] . W[N,K]^T (+bias[N]) with the epilogues the decoder layers need; replaces the
  * FalconLinear / nn.Linear calls (HF falcon:60-65, gpt_neox:41-42,200-201).

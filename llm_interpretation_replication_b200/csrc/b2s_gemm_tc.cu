@@ -14,6 +14,7 @@
 // the same time share A/W boxes in L2.
 #include "b2s_common.cuh"
 #include <mutex>
+#include <vector>
 #include <stdarg.h>
 
 namespace b2s {
@@ -404,6 +405,24 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
 
 static int g_num_sms = 0;
 
+// ---- optional per-launch timing (bench.py roofline): CUDA events on the launching stream ----------
+struct GemmProfile {
+  bool on = false;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;       // events handed out since the last read (pairs: start, stop)
+  double flops = 0.0;
+};
+static GemmProfile g_prof;
+
+static cudaEvent_t prof_event() {
+  if (g_prof.used == g_prof.pool.size()) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    g_prof.pool.push_back(e);
+  }
+  return g_prof.pool[g_prof.used++];
+}
+
 template <int EPI>
 static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
   static bool attr_set = false;
@@ -413,7 +432,12 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
   }
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+  if (g_prof.on) cudaEventRecord(prof_event(), st);
   gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, p);
+  if (g_prof.on) {
+    cudaEventRecord(prof_event(), st);
+    g_prof.flops += 2.0 * p.M * p.N * p.K;
+  }
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
@@ -456,3 +480,31 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
 }
 
 }  // namespace b2s
+
+extern "C" {
+
+int b2s_profile_gemm(int32_t enable) {
+  b2s::g_prof.on = enable != 0;
+  return B2S_OK;
+}
+
+// Synchronises on the recorded events; returns the sums since the last read and clears them.
+int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* flops) {
+  using namespace b2s;
+  double ms = 0.0;
+  for (size_t i = 0; i + 1 < g_prof.used; i += 2) {
+    B2S_CHECK_CUDA(cudaEventSynchronize(g_prof.pool[i + 1]));
+    float t = 0.f;
+    B2S_CHECK_CUDA(cudaEventElapsedTime(&t, g_prof.pool[i], g_prof.pool[i + 1]));
+    ms += t;
+  }
+  if (total_ms) *total_ms = ms;
+  if (launches) *launches = static_cast<int64_t>(g_prof.used / 2);
+  if (flops) *flops = g_prof.flops;
+  g_prof.used = 0;
+  g_prof.flops = 0.0;
+  return B2S_OK;
+}
+
+}  // extern "C"
+

@@ -1,0 +1,47 @@
+"""world_size-2 gloo test of the sharding + gather host logic (the N>1 path of bench.py)."""
+import os
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from llm_interpretation_replication_b200.dist import gather_rows, shard_prompts
+from llm_interpretation_replication_b200.scorer import plan_batches
+
+
+def test_shard_prompts_balanced():
+    rs = np.random.RandomState(0)
+    lens = rs.randint(66, 191, size=10000).tolist()
+    for ws in (1, 2, 4, 8):
+        sh = shard_prompts(lens, ws)
+        assert sorted(i for s in sh for i in s) == list(range(10000))
+        toks = [sum(lens[i] for i in s) for s in sh]
+        assert max(len(s) for s in sh) - min(len(s) for s in sh) <= 1
+        assert (max(toks) - min(toks)) / np.mean(toks) < 0.002
+
+
+def test_plan_batches_limits():
+    lens = [5, 100, 7, 64, 64, 1, 99]
+    b = plan_batches(lens, max_tokens=128, max_seqs=3)
+    assert sorted(i for x in b for i in x) == list(range(7))
+    for x in b:
+        assert sum(lens[i] for i in x) <= 128 and len(x) <= 3
+    assert plan_batches([], 10, 10) == []
+
+
+def _worker(rank, ws, port, n_total):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    lens = np.random.RandomState(1).randint(3, 50, size=n_total).tolist()
+    mine = shard_prompts(lens, ws)[rank]
+    rows = torch.tensor([[i * 1.5, lens[i], rank] for i in mine], dtype=torch.float32).reshape(-1, 3)
+    full = gather_rows(rows, mine, n_total, ws)
+    exp = torch.tensor([[i * 1.5, lens[i]] for i in range(n_total)], dtype=torch.float32)
+    assert torch.equal(full[:, :2], exp)
+    dist.destroy_process_group()
+
+
+def test_gather_rows_gloo_world2():
+    mp.spawn(_worker, args=(2, 29611, 101), nprocs=2, join=True)

@@ -82,7 +82,7 @@ def test_bootstrap_properties_large_and_philox():
     vals = np.random.RandomState(0).normal(size=(1, n))
     b1 = B.resample(vals, 1, Bn, None, philox_seed=5)
     b2 = B.resample(vals, 1, Bn, None, philox_seed=5)
-    assert torch.equal(b1, b2)
+    assert torch.equal(b1[:, [0, 2]], b2[:, [0, 2]]) and bool(torch.isnan(b1[:, 1]).all())   # no rows >= split
     s, srt = B.summary(b1, 0, 2.5, 97.5, 0.0, want_stat=True)
     x = b1[:, 0].cpu().numpy()
     assert abs(s["pct_lo"] - np.percentile(x, 2.5)) <= 1e-12 and abs(s["pct_hi"] - np.percentile(x, 97.5)) <= 1e-12
