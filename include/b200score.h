@@ -107,6 +107,18 @@ B2S_API int b2s_gemm_bf16(const void* A /*bf16 [M,K]*/, const void* W /*bf16 [N,
 B2S_API int b2s_gemm_f32(const float* A, const float* W, const float* bias, float* out,
                  int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
 
+/* Varlen causal attention over a KV cache (replaces F.scaled_dot_product_attention(..., is_causal=True),
+ * HF falcon:349-362 / gpt_neox:162-185).  qkv bf16 [total_rows, qkv_dim] holds the (already rotated) queries of
+ * head h at columns q_base + h*q_hstride; kcache/vcache bf16 [cache_slots, n_kv_head*head_dim]; sequence i has
+ * q_len[i] query rows starting at q_start[i] and kv_len[i] keys starting at slot kv_start[i]; query j sees keys
+ * [0, kv_len - q_len + j].  out bf16 [total_rows, n_head*head_dim].  use_tensor_cores != 0 selects the tcgen05
+ * kernel (head_dim 64, <= 256 keys; cache slots past a sequence must hold finite values), 0 the CUDA-core one. */
+B2S_API int b2s_attention_bf16(const void* qkv, const void* kcache, const void* vcache, void* out,
+                       const int32_t* q_start, const int32_t* q_len, const int32_t* kv_start, const int32_t* kv_len,
+                       int32_t n_seqs, int32_t total_rows, int32_t cache_slots, int32_t max_qlen, int32_t max_kv,
+                       int32_t n_head, int32_t n_kv_head, int32_t head_dim, int32_t qkv_dim, int32_t q_base,
+                       int32_t q_hstride, int32_t use_tensor_cores, void* stream);
+
 /* Last-position LM head fused with online log-sum-exp, running top-5, argmax and candidate gather
  * (replaces lm_head + .float() + softmax + topk + 2x .item(): HF falcon:905-906, generation/utils.py:
  * 2762; run_base_vs_instruct_100q.py:351-356).  hidden bf16 [M,d], W bf16 [V,d].

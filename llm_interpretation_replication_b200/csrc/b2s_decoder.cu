@@ -173,11 +173,12 @@ attn_kernel(AttnArgs a) {
   constexpr int DPL = (HD + 31) / 32;      // output dims per lane
   extern __shared__ float smem[];
   const int seq = blockIdx.x;
-  const int groups_per_kv = (a.rep + ATT_HG - 1) / ATT_HG;
+  const int HG = a.heads_per_cta;
+  const int groups_per_kv = (a.rep + HG - 1) / HG;
   const int g = blockIdx.y / groups_per_kv;           // kv head
   const int hg = blockIdx.y - g * groups_per_kv;      // head group inside this kv head
-  const int h0 = g * a.rep + hg * ATT_HG;
-  const int nh_here = min(ATT_HG, a.rep - hg * ATT_HG);
+  const int h0 = g * a.rep + hg * HG;
+  const int nh_here = min(HG, a.rep - hg * HG);
   const int q0 = a.meta.q_start[seq], ql = a.meta.q_len[seq];
   const int kv0 = a.meta.kv_start[seq], kl = a.meta.kv_len[seq];
   float* sK = smem;
@@ -256,13 +257,17 @@ attn_kernel(AttnArgs a) {
 }
 
 template <typename AT>
-int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st) {
+int launch_attn(const AttnArgs& a_in, int n_seqs, cudaStream_t st) {
+  AttnArgs a = a_in;
+  // single-token steps: one CTA per (sequence, KV head) stages K/V once for every query head that shares it
+  if (a.heads_per_cta <= 0) a.heads_per_cta = ATT_HG;
+  if (a.heads_per_cta > a.rep) a.heads_per_cta = a.rep;
   const int hd = a.hd;
   const size_t smem = (2 * static_cast<size_t>(a.max_kv) * (hd + 4) + (ATT_THREADS / 32) * (hd + 32)) * sizeof(float);
   B2S_REQUIRE(smem <= 227 * 1024,
               "attention: a sequence of %d keys (head_dim %d) needs %zu bytes of shared memory; the limit is %d keys",
               a.max_kv, hd, smem, static_cast<int>((227 * 1024 / sizeof(float) - (ATT_THREADS / 32) * (hd + 32)) / (2 * (hd + 4))));
-  const int groups_per_kv = (a.rep + ATT_HG - 1) / ATT_HG;
+  const int groups_per_kv = (a.rep + a.heads_per_cta - 1) / a.heads_per_cta;
   dim3 grid(n_seqs, a.nkv * groups_per_kv);
 #define B2S_ATT_CASE(HDV)                                                                                         \
   case HDV:                                                                                                      \

@@ -5,7 +5,7 @@
 namespace b2s {
 
 constexpr int ATT_THREADS = 256;
-constexpr int ATT_HG = 8;   // query heads per CTA (sharing one KV head)
+constexpr int ATT_HG = 8;   // query heads per CTA (sharing one KV head) for multi-row sequences
 
 struct BatchMeta {           // all device pointers, sized for max_seqs / max_tokens
   int32_t* q_start;   // [N] first row of the sequence in the current activation buffers
@@ -45,6 +45,7 @@ struct AttnArgs {
   int qkv_dim, nh, nkv, hd, rep /* nh / nkv */;
   int q_base, q_hstride;
   int max_kv;
+  int heads_per_cta;   // set by the launcher: ATT_HG for prefill, all heads of the KV head for single-token steps
   float scale;
 };
 
@@ -61,6 +62,9 @@ int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const Ba
 template <typename AT, typename WT> int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
+// tcgen05 prefill attention (b2s_attn_tc.cu): head_dim 64, <= 256 keys per sequence
+bool attn_tc_supported(int hd, int max_kv);
+int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st);
 int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const int32_t* cand, float* partials,
                                        float* cand_logits, cudaStream_t st);
 int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, int tiles_n, float* stats,

@@ -50,6 +50,7 @@ struct Workspace {
   void *ln1, *ln2, *qkv, *attn, *act, *hfin;
   void *kcache, *vcache;
   size_t cache_layer_bytes;
+  size_t cache_slots;
   float *partials, *cand_logits, *stats, *logits;
   size_t total;
 };
@@ -92,6 +93,7 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.act = take(at * rows * d.d_ff);
   w.hfin = take(at * static_cast<size_t>(N) * d.d_model);
   const size_t slots = static_cast<size_t>(T) + static_cast<size_t>(N) * LA;
+  w.cache_slots = slots;
   w.cache_layer_bytes = align_up(at * slots * d.n_kv_head * d.head_dim, 256);
   w.kcache = take(w.cache_layer_bytes * d.n_layer);
   w.vcache = take(w.cache_layer_bytes * d.n_layer);
@@ -114,7 +116,7 @@ int linear(const b2s_model* m, const void* A, const void* W, const float* bias, 
 
 template <typename AT>
 int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
-              cudaStream_t st) {
+              int max_qlen, cudaStream_t st) {
   const b2s_model_desc& d = m->d;
   const int dm = d.d_model;
   const bool two_ln = d.n_ln_per_layer == 2;
@@ -147,8 +149,14 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.qkv = w.qkv; at.kcache = kc; at.vcache = vc; at.out = w.attn; at.meta = w.meta;
     at.qkv_dim = m->qkv_dim; at.nh = d.n_head; at.nkv = d.n_kv_head; at.hd = d.head_dim; at.rep = d.n_head / d.n_kv_head;
     at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
+    at.heads_per_cta = (max_qlen == 1) ? at.rep : ATT_HG;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
-    B2S_TRY(launch_attn<AT>(at, n_seqs, st));
+    // prefill on the tensor cores when the shape allows it; single-token steps use the CUDA-core kernel
+    if (m->bf16 && max_qlen > 1 && attn_tc_supported(d.head_dim, max_kv)) {
+      B2S_TRY(launch_attn_tc(at, n_seqs, rows, static_cast<int>(w.cache_slots), max_qlen, st));
+    } else {
+      B2S_TRY(launch_attn<AT>(at, n_seqs, st));
+    }
 
     B2S_TRY(linear(m, w.attn, m->lw(l, B2S_WL_W_DENSE), m->lwf(l, B2S_WL_B_DENSE), w.resid, rows, dm,
                    d.n_head * d.head_dim, EPI_RESID_F32, st));
@@ -176,9 +184,9 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
 }
 
 int forward(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
-            cudaStream_t st) {
-  if (m->bf16) return forward_t<__nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, st);
-  return forward_t<float>(m, w, tokens, rows, n_seqs, max_kv, st);
+            int max_qlen, cudaStream_t st) {
+  if (m->bf16) return forward_t<__nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
+  return forward_t<float>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
 }
 
 int lm_head(const b2s_model* m, const Workspace& w, const int32_t* cand, int n_seqs, cudaStream_t st) {
@@ -304,8 +312,12 @@ int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, in
   w.scan.gen_ids = gen_ids;
   if (gen_ids) B2S_CHECK_CUDA(cudaMemsetAsync(gen_ids, 0xFF, 4 * static_cast<size_t>(n_seqs) * max_lookahead, st));
 
+  // The tensor-core attention kernel loads whole 256-slot K/V boxes; slots it masks out must hold finite
+  // numbers (0 * NaN would poison P.V), so the cache starts from zeros on every call.
+  B2S_CHECK_CUDA(cudaMemsetAsync(w.kcache, 0, w.cache_layer_bytes * m->d.n_layer, st));
+  B2S_CHECK_CUDA(cudaMemsetAsync(w.vcache, 0, w.cache_layer_bytes * m->d.n_layer, st));
   B2S_TRY(launch_prep(cu_seqlens, n_seqs, max_lookahead, 0, w.meta, st));
-  B2S_TRY(forward(m, w, tokens, total_tokens, n_seqs, max_seqlen, st));
+  B2S_TRY(forward(m, w, tokens, total_tokens, n_seqs, max_seqlen, max_seqlen, st));
   B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
   B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
   B2S_TRY(launch_scan_update(w.stats, n_seqs, 0, topk, eos_id, max_lookahead, w.scan, st));
@@ -315,7 +327,7 @@ int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, in
     B2S_CHECK_CUDA(cudaStreamSynchronize(st));
     if (active == 0) break;
     B2S_TRY(launch_prep(cu_seqlens, n_seqs, max_lookahead, step, w.meta, st));
-    B2S_TRY(forward(m, w, w.scan.next_tok, n_seqs, n_seqs, max_seqlen + step, st));
+    B2S_TRY(forward(m, w, w.scan.next_tok, n_seqs, n_seqs, max_seqlen + step, 1, st));
     B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
     B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
     B2S_TRY(launch_scan_update(w.stats, n_seqs, step, topk, eos_id, max_lookahead, w.scan, st));
@@ -373,6 +385,24 @@ int b2s_gemm_f32(const float* A, const float* W, const float* bias, float* out, 
                  void* stream) {
   B2S_REQUIRE(A && W && out, "gemm_f32: null argument");
   return gemm_f32_launch(A, W, bias, out, M, N, K, epilogue, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b2s_attention_bf16(const void* qkv, const void* kcache, const void* vcache, void* out, const int32_t* q_start,
+                       const int32_t* q_len, const int32_t* kv_start, const int32_t* kv_len, int32_t n_seqs, int32_t total_rows,
+                       int32_t cache_slots, int32_t max_qlen, int32_t max_kv, int32_t n_head, int32_t n_kv_head, int32_t head_dim,
+                       int32_t qkv_dim, int32_t q_base, int32_t q_hstride, int32_t use_tensor_cores, void* stream) {
+  B2S_REQUIRE(qkv && kcache && vcache && out && q_start && q_len && kv_start && kv_len, "attention: null argument");
+  B2S_REQUIRE(n_seqs > 0 && n_head > 0 && n_kv_head > 0 && n_head % n_kv_head == 0, "attention: bad head counts");
+  AttnArgs a{};
+  a.qkv = qkv; a.kcache = kcache; a.vcache = vcache; a.out = out;
+  a.meta.q_start = const_cast<int32_t*>(q_start); a.meta.q_len = const_cast<int32_t*>(q_len);
+  a.meta.kv_start = const_cast<int32_t*>(kv_start); a.meta.kv_len = const_cast<int32_t*>(kv_len);
+  a.qkv_dim = qkv_dim; a.nh = n_head; a.nkv = n_kv_head; a.hd = head_dim; a.rep = n_head / n_kv_head;
+  a.q_base = q_base; a.q_hstride = q_hstride; a.max_kv = max_kv;
+  a.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (use_tensor_cores) return launch_attn_tc(a, n_seqs, total_rows, cache_slots, max_qlen, st);
+  return launch_attn<__nv_bfloat16>(a, n_seqs, st);
 }
 
 size_t b2s_lm_head_scratch_bytes(int32_t M, int32_t V) {

@@ -93,3 +93,52 @@ def test_lm_head_fused(M, V, d):
     assert (picked - logits.max(dim=-1).values).abs().max().item() <= 2e-3   # arg max up to fp32 summation order
     ca = logits.gather(1, cand.long())
     assert (stats[:, 7:9] - ca).abs().max().item() <= 2e-3
+
+
+def _attn_ref(q, k, v, lens, kv_extra):
+    """fp32 torch reference: per sequence causal softmax(q k^T / sqrt(d)) v with kv_extra earlier keys."""
+    outs = []
+    for (qs, ql, ks, kl) in lens:
+        Q = q[qs:qs + ql].float()                # [ql, nh, hd]
+        K = k[ks:ks + kl].float()                # [kl, nkv, hd]
+        V = v[ks:ks + kl].float()
+        rep = Q.shape[1] // K.shape[1]
+        K = K.repeat_interleave(rep, dim=1); V = V.repeat_interleave(rep, dim=1)
+        s = torch.einsum("qhd,khd->hqk", Q, K) / (Q.shape[-1] ** 0.5)
+        qi = torch.arange(ql, device=q.device)[:, None]; kj = torch.arange(kl, device=q.device)[None, :]
+        s = s.masked_fill((kj > (kl - ql) + qi)[None], float("-inf"))
+        outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(s, -1), V))
+    return outs
+
+
+@pytest.mark.parametrize("use_tc", [0, 1])
+@pytest.mark.parametrize("nh,nkv", [(71, 1), (4, 2), (3, 3)])
+def test_attention_bf16(use_tc, nh, nkv):
+    """Ragged prefill batch (lengths 1..256, incl. exactly 128/129/256) + extra cached keys for some sequences."""
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    hd = 64
+    qlens = [1, 2, 17, 64, 127, 128, 129, 190, 256, 33, 100]
+    extra = [0, 0, 3, 0, 0, 0, 0, 10, 0, 64, 28]      # keys already in the cache before the first query
+    slack = 10
+    q_start, kv_start, t, c = [], [], 0, 0
+    for ql, ex in zip(qlens, extra):
+        q_start.append(t); kv_start.append(c); t += ql; c += ql + ex + slack
+    T, slots = t, c + 300
+    qkv_dim = (nh + 2 * nkv) * hd
+    qkv = _rand((T, qkv_dim), 1.0, 11)
+    kc, vc = _rand((slots, nkv * hd), 1.0, 12), _rand((slots, nkv * hd), 1.0, 13)
+    out = torch.zeros((T, nh * hd), dtype=torch.bfloat16, device="cuda")
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device="cuda")
+    kvl = [a + b for a, b in zip(qlens, extra)]
+    a_qs, a_ql, a_ks, a_kl = i32(q_start), i32(qlens), i32(kv_start), i32(kvl)
+    _lib.check(lib.b2s_attention_bf16(_lib.ptr(qkv), _lib.ptr(kc), _lib.ptr(vc), _lib.ptr(out), _lib.ptr(a_qs), _lib.ptr(a_ql),
+                                      _lib.ptr(a_ks), _lib.ptr(a_kl), len(qlens), T, slots, max(qlens), max(kvl), nh, nkv, hd,
+                                      qkv_dim, 0, hd, use_tc, _lib.current_stream()), "attention")
+    torch.cuda.synchronize()
+    q = qkv[:, :nh * hd].view(T, nh, hd)
+    ref = _attn_ref(q, kc.view(slots, nkv, hd), vc.view(slots, nkv, hd), list(zip(q_start, qlens, kv_start, kvl)), extra)
+    for (qs, ql), r in zip(zip(q_start, qlens), ref):
+        got = out[qs:qs + ql].view(ql, nh, hd).float()
+        err = (got - r).abs().max().item()
+        assert err <= (3e-2 if use_tc else 1.5e-2), (use_tc, ql, err)     # bf16 output (+ bf16 P on the tensor-core path)

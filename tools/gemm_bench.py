@@ -44,6 +44,16 @@ def bench(M, N, K, epi, iters=5):
 if __name__ == "__main__":
     M = int(sys.argv[1]) if len(sys.argv) > 1 else 32768
     res = []
+    if len(sys.argv) > 2 and sys.argv[2] == "ncu":     # one launch per shape, for an ncu --set full capture
+        lib = _lib.load()
+        for (N, K, epi) in ((18176, 4544, 1), (4544, 18176, 2), (4672, 4544, 0)):
+            A = (torch.randn(M, K, device="cuda")).to(torch.bfloat16)
+            W = (torch.randn(N, K, device="cuda") * 0.02).to(torch.bfloat16)
+            out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi in (2, 4) else torch.bfloat16)
+            for _ in range(2):
+                _lib.check(lib.b2s_gemm_bf16(_lib.ptr(A), _lib.ptr(W), None, _lib.ptr(out), M, N, K, epi, _lib.current_stream()), "gemm")
+            torch.cuda.synchronize()
+        sys.exit(0)
     for (N, K, epi) in ((4672, 4544, 0), (4544, 4544, 2), (18176, 4544, 1), (4544, 18176, 2), (8192, 8192, 0)):
         r = bench(M, N, K, epi)
         print(json.dumps(r), flush=True)
