@@ -129,6 +129,24 @@ B2S_API int b2s_lm_head_bf16(const void* hidden, const void* W, const int32_t* c
                      int32_t M, int32_t V, int32_t d, float* stats /*[M,16]*/,
                      void* scratch, size_t scratch_bytes, void* stream);
 
+/* No counterpart in the reference.  Same computation and same stats layout as b2s_lm_head_bf16, for callers
+ * that cannot allocate device memory: plug-ins living inside an application whose memory pool owns the whole
+ * GPU, latency-sensitive loops that must avoid the device-wide synchronisation of cudaMalloc/cudaFree, and
+ * code that is handed only input/output pointers by a foreign runtime.  The per-tile partial records go into
+ * a fixed array compiled into the library (b2s_lm_head_static_capacity() bytes = 4 MiB + 4 KiB, reserved on
+ * every GPU that loads the library until the process exits); the call performs no cudaMalloc/cudaFree and calls
+ * no allocating library routine.  Limits and rules:
+ *   - b2s_lm_head_scratch_bytes(M, V) must not exceed the capacity (e.g. M <= 512 at V = 65024); larger
+ *     problems are rejected with B2S_EINVAL and a message, nothing is launched;
+ *   - the first call on each device looks the array's device address up (the device must be current); make
+ *     that first call before starting any stream capture on that device;
+ *   - every call on a device shares the one array and finds the previous call's contents in it (the call
+ *     clears the part that must start at zero itself): two calls whose GPU work can overlap -- different
+ *     streams, or different host threads -- race on it and must be serialised by the caller. */
+B2S_API size_t b2s_lm_head_static_capacity(void);
+B2S_API int b2s_lm_head_bf16_static(const void* hidden, const void* W, const int32_t* cand_ids /*[M,2]*/,
+                            int32_t M, int32_t V, int32_t d, float* stats /*[M,16]*/, void* stream);
+
 /* ---- bootstrap ---------------------------------------------------------------------------
  * NumPy legacy RNG (MT19937 + masked rejection), bit-exact: np.random.seed(s) followed by repeated
  * np.random.choice(n, size=..., replace=True), as used at run_base_vs_instruct_100q.py:616,657;

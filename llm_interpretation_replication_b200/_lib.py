@@ -44,6 +44,8 @@ SIGNATURES = {
     "b2s_attention_bf16": (C.c_int, [_vp] * 8 + [_i32] * 12 + [_vp]),
     "b2s_lm_head_scratch_bytes": (_sz, [_i32, _i32]),
     "b2s_lm_head_bf16": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),
+    "b2s_lm_head_static_capacity": (_sz, []),
+    "b2s_lm_head_bf16_static": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
     "b2s_mt19937_seed": (C.c_int, [_u32, _vp, _vp]),
     "b2s_mt19937_choice": (C.c_int, [_vp, _i32, _i64, _vp, _vp]),
     "b2s_bootstrap_resample": (C.c_int, [_vp, _i32, _i32, _i32, _i64, _vp, _u64, _vp, _vp]),
