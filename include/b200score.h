@@ -98,6 +98,10 @@ B2S_API int64_t b2s_launch_count(int32_t reset);
 B2S_API int b2s_profile_gemm(int32_t enable);
 B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* flops);
 
+/* Tuning knobs (no counterpart in the reference).  "gemm_cta_group": 1 = one CTA per 128x256 tile,
+ * 2 = CTA pairs (tcgen05 cta_group::2) on 256x256 tiles. */
+B2S_API int b2s_set_option(const char* name, int32_t value);
+
 /* ---- building blocks (exported so the parity tests can exercise each kernel through the ABI) ----
  * C[M,N] = A[M,K] . W[N,K]^T (+bias[N]) with the epilogues the decoder layers need; replaces the
  * FalconLinear / nn.Linear calls (HF falcon:60-65, gpt_neox:41-42,200-201).

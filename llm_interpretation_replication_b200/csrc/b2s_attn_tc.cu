@@ -1,39 +1,46 @@
-// tcgen05 varlen causal prefill attention, head_dim 64, bf16 (Falcon MQA; also GQA/MHA with head_dim 64).
+// tcgen05 varlen causal attention, head_dim 64, bf16 (Falcon MQA; also GQA/MHA with head_dim 64).
 //
 // Replaces F.scaled_dot_product_attention(q, k, v, is_causal=True) of the reference's decoder forward
-// (HF:models/falcon/modeling_falcon.py:349-362) for a whole varlen-packed batch.
-//
-// One CTA per (sequence, 128-query tile, KV head).  K and V of the sequence (<= 256 keys; the reference's
-// prompts have <= 190 tokens) are TMA-staged ONCE into 128B-swizzled shared memory and reused
-// by every query head that shares the KV head (71 heads for Falcon's multi-query attention); Q tiles are
-// streamed with double-buffered TMA loads.  Per head:
-//     S = Q.K^T      tcgen05.mma 128 x kvp x 64   (A, B K-major)          -> TMEM columns [0, kvp)
-//     softmax        thread == query row: tcgen05.ld, causal mask, exp2, bf16 P -> swizzled smem (A operand)
-//     O = P.V        tcgen05.mma 128 x 64 x kvp   (A K-major, B = V MN-major) -> TMEM columns [256, 320)
+// (HF:models/falcon/modeling_falcon.py:349-362) for a whole varlen-packed batch, in both phases of the scorer:
+//   prefill    one CTA per (prompt, 128-query tile, KV head); rows of the MMA tile are query positions and the
+//              CTA loops over the query heads that share the KV head (71 for Falcon's multi-query attention);
+//   one-token  (look-ahead steps) one CTA per (prompt, KV head); rows of the tile are the query HEADS of the
+//              single new token (the qkv row is read as a [heads, 64] matrix), one iteration, no causal mask.
+// K and V of the prompt (<= 256 keys; the reference's prompts have <= 190 tokens) are TMA-staged
+// ONCE into 128B-swizzled shared memory; Q tiles stream through a 3-deep TMA ring.  Per item:
+//     S = Q.K^T      tcgen05.mma 128 x kvp x 64   (A, B K-major)            -> TMEM
+//     softmax        thread == tile row: tcgen05.ld, mask, ex2, bf16 P      -> swizzled smem (A operand of P.V)
+//     O = P.V        tcgen05.mma 128 x 64 x kvp   (A K-major, B = V MN-major) -> TMEM
 //     epilogue       tcgen05.ld, 1/rowsum, bf16, 128 B per thread to global
-// Warps 0-3 are the softmax/epilogue threads (TMEM lane quadrant == warp), warp 4 lane 0 issues TMA and MMA.
+// With <= 192 keys two items are in flight at once: warps 0-3 ("lane" 0) and 4-7 (lane 1) each own one S/O
+// accumulator pair and one P buffer, and the single issuing thread (warp 8) interleaves S(i), P.V(i-1), so the
+// tensor core works on one lane while the other lane's threads are in softmax.  Longer prompts use lane 0 only.
 #include "b2s_tc.cuh"
 #include "b2s_decoder.cuh"
 
 namespace b2s {
 
 static constexpr int AT_HD = 64;
-static constexpr int AT_BM = 128;          // queries per tile
-static constexpr int AT_MAXKV = 256;       // keys per sequence supported by this kernel
+static constexpr int AT_BM = 128;          // tile rows
+static constexpr int AT_MAXKV = 256;       // keys per prompt supported by this kernel
+static constexpr int AT_KV2 = 192;         // keys up to which both lanes are used
 static constexpr int AT_KV_BYTES = AT_MAXKV * AT_HD * 2;    // 32 KB per K or V
 static constexpr int AT_Q_BYTES = AT_BM * AT_HD * 2;        // 16 KB per Q tile
+static constexpr int AT_NQ = 3;                             // Q ring depth
 static constexpr int AT_P_ATOM = AT_BM * 128;               // one 64-key swizzle atom of P: 16 KB
-static constexpr int AT_P_BYTES = (AT_MAXKV / 64) * AT_P_ATOM;
-static constexpr int AT_SMEM = 2 * AT_KV_BYTES + 2 * AT_Q_BYTES + AT_P_BYTES + 1024 + 128;
-static constexpr int AT_THREADS = 160;
+static constexpr int AT_P_LANE = (AT_KV2 / 64) * AT_P_ATOM; // 48 KB per lane (lane 0 may use 64 KB when alone)
+static constexpr int AT_SMEM = 2 * AT_KV_BYTES + AT_NQ * AT_Q_BYTES + 2 * AT_P_LANE + 1024 + 128;
+static constexpr int AT_THREADS = 288;     // 8 softmax warps + 1 issuer warp
 static constexpr uint32_t AT_TMEM_COLS = 512;
-static constexpr uint32_t AT_O_COL = 256;
+static constexpr uint32_t AT_O_COL = 384;  // O accumulators: lane l at columns [384 + 64 l, +64)
 
 struct AttnTcParams {
   BatchMeta meta;
   __nv_bfloat16* out;     // [T, nh*64]
   int nh, nkv, rep;
   int q_base, q_hstride;  // column of head h in the qkv row = q_base + h*q_hstride
+  int decode;             // 0: rows are query positions (prefill); 1: rows are heads of one token
+  int qrows_per_token;    // decode: qkv_dim / 64 (rows of the [*, 64] view per token)
   float scale_log2e;      // (1/sqrt(hd)) * log2(e)
 };
 
@@ -53,34 +60,55 @@ __device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr) 
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const AttnTcParams p) {
   const int seq = blockIdx.x, mt = blockIdx.y, g = blockIdx.z;
   const int ql = p.meta.q_len[seq];
-  if (mt * AT_BM >= ql) return;                       // uniform per CTA: nothing allocated yet
-  const int q0 = p.meta.q_start[seq] + mt * AT_BM;
+  if (!p.decode && mt * AT_BM >= ql) return;          // uniform per CTA: nothing allocated yet
+  const int q0 = p.meta.q_start[seq] + (p.decode ? 0 : mt * AT_BM);
   const int kv0 = p.meta.kv_start[seq];
   const int kl = p.meta.kv_len[seq];
-  const int rows_here = min(AT_BM, ql - mt * AT_BM);
-  // keys visible to the last query row of this tile; padded to the MMA granularity (N % 16, K % 16)
-  const int kv_tile = min(kl, kl - ql + mt * AT_BM + rows_here);
-  const int kvp = (kv_tile + 15) & ~15;
+  // rows of the tile that carry data, keys visible to the last of them, number of items
+  int rows_here, kv_tile, n_items;
+  if (p.decode) {
+    n_items = (p.rep + AT_BM - 1) / AT_BM;
+    rows_here = 0;                                     // per item, see below
+    kv_tile = kl;
+  } else {
+    n_items = p.rep;
+    rows_here = min(AT_BM, ql - mt * AT_BM);
+    kv_tile = min(kl, kl - ql + mt * AT_BM + rows_here);
+  }
+  const int kvp = (kv_tile + 15) & ~15;               // MMA granularity (N % 16, K % 16)
+  const bool two = (kvp <= AT_KV2) && (n_items > 1);
+  const int nl = two ? 2 : 1;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sK = base, sV = base + AT_KV_BYTES, sQ = base + 2 * AT_KV_BYTES;
-  const uint32_t sP = sQ + 2 * AT_Q_BYTES;
-  const uint32_t bars = sP + AT_P_BYTES;
-  const uint32_t bar_kv = bars, bar_q0 = bars + 8, bar_q1 = bars + 16, bar_s = bars + 24, bar_p = bars + 32,
-                 bar_o = bars + 40, tmem_slot = bars + 48;
+  const uint32_t sP = sQ + AT_NQ * AT_Q_BYTES;
+  const uint32_t bars = sP + 2 * AT_P_LANE;
+  // barriers (8 B each): kv, q[3], s[2], p[2], o[2]; then the TMEM slot
+  const uint32_t bar_kv = bars;
+  auto bar_q = [&](int b) { return bars + 8u * (1 + b); };
+  auto bar_s = [&](int l) { return bars + 8u * (4 + l); };
+  auto bar_p = [&](int l) { return bars + 8u * (6 + l); };
+  auto bar_o = [&](int l) { return bars + 8u * (8 + l); };
+  const uint32_t tmem_slot = bars + 8u * 10;
   uint8_t* sP_gen = smem_raw + (sP - smem_u32(smem_raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 128) {
-    mbar_init(bar_kv, 1); mbar_init(bar_q0, 1); mbar_init(bar_q1, 1);
-    mbar_init(bar_s, 1); mbar_init(bar_p, 128); mbar_init(bar_o, 1);
+  if (threadIdx.x == 256) {
+    mbar_init(bar_kv, 1);
+    for (int b = 0; b < AT_NQ; ++b) mbar_init(bar_q(b), 1);
+    for (int l = 0; l < 2; ++l) { mbar_init(bar_s(l), 1); mbar_init(bar_p(l), 128); mbar_init(bar_o(l), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -94,59 +122,87 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
   const int h_first = g * p.rep;
-  const int H = p.rep;
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
-      // ---- TMA + MMA issuer ----
+      // ---------------- TMA + MMA issuer ----------------
+      auto load_q = [&](int i) {
+        const uint32_t bq = bar_q(i % AT_NQ);
+        mbar_arrive_expect_tx(bq, AT_Q_BYTES);
+        if (p.decode)
+          tma_load_2d(sQ + (i % AT_NQ) * AT_Q_BYTES, &tmQ, bq, 0,
+                      q0 * p.qrows_per_token + p.q_base / AT_HD + h_first + i * AT_BM);
+        else
+          tma_load_2d(sQ + (i % AT_NQ) * AT_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i) * p.q_hstride, q0);
+      };
       mbar_arrive_expect_tx(bar_kv, 2 * AT_KV_BYTES);
       tma_load_2d(sK, &tmK, bar_kv, g * AT_HD, kv0);
       tma_load_2d(sV, &tmV, bar_kv, g * AT_HD, kv0);
-      mbar_arrive_expect_tx(bar_q0, AT_Q_BYTES);
-      tma_load_2d(sQ, &tmQ, bar_q0, p.q_base + h_first * p.q_hstride, q0);
+      for (int i = 0; i < AT_NQ && i < n_items; ++i) load_q(i);
       mbar_wait(bar_kv, 0);
       const uint32_t idesc_s = idesc_bf16(AT_BM, kvp, 0);
       const uint32_t idesc_o = idesc_bf16(AT_BM, AT_HD, 1);
       const uint64_t kdesc = make_kmajor_sw128_desc(sK);
       const uint64_t vdesc = make_mnmajor_sw128_desc(sV);
-      for (int i = 0; i < H; ++i) {
-        const int b = i & 1;
-        if (i + 1 < H) {   // prefetch the next head's Q tile into the other buffer (its S MMA is long finished)
-          const uint32_t bq = b ? bar_q0 : bar_q1;
-          mbar_arrive_expect_tx(bq, AT_Q_BYTES);
-          tma_load_2d(sQ + (b ^ 1) * AT_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i + 1) * p.q_hstride, q0);
-        }
-        mbar_wait(b ? bar_q1 : bar_q0, (i >> 1) & 1);
-        tcgen05_fence_after();
-        const uint64_t qdesc = make_kmajor_sw128_desc(sQ + b * AT_Q_BYTES);
+      const int skew = two ? 1 : 0;
+      for (int i = 0; i < n_items + skew; ++i) {
+        if (i < n_items) {
+          // S(i): its lane's S accumulator was last read by item i - nl, whose P arrival was waited below
+          const int l = two ? (i & 1) : 0;
+          mbar_wait(bar_q(i % AT_NQ), (i / AT_NQ) & 1);
+          tcgen05_fence_after();
+          const uint64_t qdesc = make_kmajor_sw128_desc(sQ + (i % AT_NQ) * AT_Q_BYTES);
+          const uint32_t t_s = tmem_base + static_cast<uint32_t>(l * AT_KV2);
 #pragma unroll
-        for (int k = 0; k < AT_HD / 16; ++k)
-          tcgen05_mma_bf16(tmem_base, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
-        tcgen05_commit(bar_s);
-        // P written by the 128 softmax threads (they have also finished reading O of the previous head)
-        mbar_wait(bar_p, i & 1);
-        tcgen05_fence_after();
-        for (int ks = 0; ks < kvp / 16; ++ks) {
-          const uint64_t pdesc = make_kmajor_sw128_desc(sP + (ks >> 2) * AT_P_ATOM) + 2u * (ks & 3);
-          tcgen05_mma_bf16(tmem_base + AT_O_COL, pdesc, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o,
-                           ks != 0 ? 1u : 0u);
+          for (int k = 0; k < AT_HD / 16; ++k)
+            tcgen05_mma_bf16(t_s, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
+          tcgen05_commit(bar_s(l));
         }
-        tcgen05_commit(bar_o);
+        const int j = i - skew;
+        if (j >= 0) {
+          const int l = two ? (j & 1) : 0;
+          mbar_wait(bar_p(l), (j / nl) & 1);     // P(j) written; S(j) and O(j - nl) fully read
+          tcgen05_fence_after();
+          const uint32_t pbase = sP + l * AT_P_LANE;
+          const uint32_t t_o = tmem_base + AT_O_COL + static_cast<uint32_t>(l * AT_HD);
+          for (int ks = 0; ks < kvp / 16; ++ks) {
+            const uint64_t pdesc = make_kmajor_sw128_desc(pbase + (ks >> 2) * AT_P_ATOM) + 2u * (ks & 3);
+            tcgen05_mma_bf16(t_o, pdesc, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o, ks != 0 ? 1u : 0u);
+          }
+          tcgen05_commit(bar_o(l));
+          if (j + AT_NQ < n_items) load_q(j + AT_NQ);   // S(j) is complete, so its Q buffer is free
+        }
       }
     }
-  } else {
-    // ---- softmax + epilogue: thread == query row ----
-    const int row = warp * 32 + lane;
-    const bool valid = row < rows_here;
-    const int limit = kl - ql + mt * AT_BM + row;       // last visible key index (causal)
-    const uint32_t t_s = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
-    const uint32_t t_o = t_s + AT_O_COL;
-    // keys the whole warp can skip: chunks starting beyond the warp's largest limit are fully masked
-    const int warp_limit = kl - ql + mt * AT_BM + min(warp * 32 + 31, rows_here - 1);
-    const int nchunks = kvp / 32 + ((kvp & 31) ? 1 : 0);
-    __nv_bfloat16* orow = p.out + static_cast<size_t>(q0 + row) * (static_cast<size_t>(p.nh) * AT_HD);
-    for (int i = 0; i < H; ++i) {
-      mbar_wait(bar_s, i & 1);
+  } else if (warp < 4 * nl) {
+    // ---------------- softmax + epilogue: thread == tile row ----------------
+    const int l = warp >> 2;                   // lane
+    const int quad = warp & 3;                 // TMEM lane quadrant
+    const int row = quad * 32 + lane;
+    const uint32_t t_s = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(l * AT_KV2);
+    const uint32_t t_o = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + AT_O_COL + static_cast<uint32_t>(l * AT_HD);
+    uint8_t* pl = sP_gen + l * AT_P_LANE;
+    const int nchunks = (kvp + 31) / 32;
+    for (int i = l; i < n_items; i += nl) {
+      int limit, warp_limit;
+      bool valid;
+      __nv_bfloat16* optr;
+      if (p.decode) {
+        const int rows_i = min(AT_BM, p.rep - i * AT_BM);
+        valid = row < rows_i;
+        limit = kl - 1;
+        warp_limit = kl - 1;
+        optr = p.out + static_cast<size_t>(q0) * (static_cast<size_t>(p.nh) * AT_HD) +
+               static_cast<size_t>(h_first + i * AT_BM + row) * AT_HD;
+      } else {
+        valid = row < rows_here;
+        limit = kl - ql + mt * AT_BM + row;   // last visible key (causal)
+        warp_limit = kl - ql + mt * AT_BM + min(quad * 32 + 31, rows_here - 1);
+        optr = p.out + static_cast<size_t>(q0 + row) * (static_cast<size_t>(p.nh) * AT_HD) +
+               static_cast<size_t>(h_first + i) * AT_HD;
+      }
+      const uint32_t ph = static_cast<uint32_t>((i / nl) & 1);
+      mbar_wait(bar_s(l), ph);
       tcgen05_fence_after();
       // pass 1: row maximum over the visible keys
       float m = -INFINITY;
@@ -159,8 +215,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
       }
       const float ms = m * p.scale_log2e;
-      // pass 2: p = exp2(s*scale*log2e - max), rounded to bf16, written to the swizzled A-operand tile
-      float l = 0.f;
+      // pass 2: p = 2^(s*scale*log2e - max), rounded to bf16, written to the swizzled A-operand tile
+      float lsum = 0.f;
       for (int c = 0; c < nchunks; ++c) {
         const bool live = c * 32 <= warp_limit;         // warp-uniform
         float v[32];
@@ -170,15 +226,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int j = 0; j < 32; j += 2) {
           float p0 = 0.f, p1 = 0.f;
           if (live && valid) {
-            if (c * 32 + j <= limit) p0 = exp2f(fmaf(v[j], p.scale_log2e, -ms));
-            if (c * 32 + j + 1 <= limit) p1 = exp2f(fmaf(v[j + 1], p.scale_log2e, -ms));
+            if (c * 32 + j <= limit) p0 = ex2_approx(fmaf(v[j], p.scale_log2e, -ms));
+            if (c * 32 + j + 1 <= limit) p1 = ex2_approx(fmaf(v[j + 1], p.scale_log2e, -ms));
           }
           const __nv_bfloat162 b2 = __floats2bfloat162_rn(p0, p1);
-          l += __low2float(b2) + __high2float(b2);      // normalise by what the MMA actually multiplies
+          lsum += __low2float(b2) + __high2float(b2);   // normalise by what the MMA actually multiplies
           pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&b2);
         }
         // 32 keys = 64 B = four 16-byte chunks of this row inside atom (c/2); swizzle: chunk ^= row % 8
-        uint8_t* prow = sP_gen + (c >> 1) * AT_P_ATOM + row * 128;
+        uint8_t* prow = pl + (c >> 1) * AT_P_ATOM + row * 128;
         const int cbase = (c & 1) * 4;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -189,16 +245,16 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       // make the generic-proxy smem writes visible to the tensor core (async proxy), then signal
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       tcgen05_fence_before();
-      mbar_arrive(bar_p);
-      // epilogue of this head
-      mbar_wait(bar_o, i & 1);
+      mbar_arrive(bar_p(l));
+      // epilogue of this item
+      mbar_wait(bar_o(l), ph);
       tcgen05_fence_after();
       float o0[32], o1[32];
       tmem_ld32(t_o, o0);
       tmem_ld32(t_o + 32, o1);
       if (valid) {
-        const float inv = 1.f / l;
-        uint4* dst = reinterpret_cast<uint4*>(orow + static_cast<size_t>(h_first + i) * AT_HD);
+        const float inv = 1.f / lsum;
+        uint4* dst = reinterpret_cast<uint4*>(optr);
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           dst[q] = make_uint4(pack_bf16x2(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack_bf16x2(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
@@ -208,7 +264,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           dst[4 + q] = make_uint4(pack_bf16x2(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack_bf16x2(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
                                   pack_bf16x2(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack_bf16x2(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
       }
-      tcgen05_fence_before();   // O and S reads done before the next head's MMAs are released by bar_p
+      tcgen05_fence_before();   // O and S reads are ordered before this thread's next bar_p arrival
     }
   }
 
@@ -220,20 +276,31 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
-// Host launcher.  Falls back (returns B2S_EUNSUPPORTED without setting an error the caller must report) is NOT
-// done here: the caller decides which kernel to use from attn_tc_supported().
+// The caller decides which kernel to use from attn_tc_supported(); there is no silent fallback here.
 bool attn_tc_supported(int hd, int max_kv) { return hd == AT_HD && max_kv <= AT_MAXKV; }
+// one-token steps additionally need contiguous 64-wide query heads (the qkv row is read as a [heads, 64] matrix)
+bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride) {
+  return attn_tc_supported(hd, max_kv) && q_hstride == AT_HD && qkv_dim % AT_HD == 0 && q_base % AT_HD == 0;
+}
 
 int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
   B2S_REQUIRE(attn_tc_supported(a.hd, a.max_kv), "attn_tc: head_dim %d / %d keys not supported", a.hd, a.max_kv);
+  const bool decode = max_qlen == 1;
+  B2S_REQUIRE(!decode || attn_tc_decode_supported(a.hd, a.max_kv, a.qkv_dim, a.q_base, a.q_hstride),
+              "attn_tc: one-token mode needs contiguous 64-wide query heads");
   static bool attr_set = false;
   if (!attr_set) {
     B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     attr_set = true;
   }
   CUtensorMap tq, tk, tv;
-  B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
-                            static_cast<uint64_t>(a.qkv_dim) * 2, AT_BM, AT_HD));
+  if (decode) {   // qkv viewed as [total_rows * qkv_dim/64, 64]
+    const uint64_t rpt = static_cast<uint64_t>(a.qkv_dim / AT_HD);
+    B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows) * rpt, AT_HD, AT_HD * 2, AT_BM, AT_HD));
+  } else {
+    B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
+                              static_cast<uint64_t>(a.qkv_dim) * 2, AT_BM, AT_HD));
+  }
   const uint64_t kvw = static_cast<uint64_t>(a.nkv) * AT_HD;
   B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, AT_MAXKV, AT_HD));
   B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, AT_MAXKV, AT_HD));
@@ -242,8 +309,10 @@ int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slot
   p.out = reinterpret_cast<__nv_bfloat16*>(a.out);
   p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
   p.q_base = a.q_base; p.q_hstride = a.q_hstride;
+  p.decode = decode ? 1 : 0;
+  p.qrows_per_token = a.qkv_dim / AT_HD;
   p.scale_log2e = a.scale * 1.4426950408889634f;
-  dim3 grid(n_seqs, static_cast<unsigned>(ceil_div(max_qlen, AT_BM)), a.nkv);
+  dim3 grid(n_seqs, decode ? 1u : static_cast<unsigned>(ceil_div(max_qlen, AT_BM)), a.nkv);
   attn_tc_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(tq, tk, tv, p);
   B2S_CHECK_LAUNCH();
   return B2S_OK;

@@ -64,6 +64,7 @@ template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cuda
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
 // tcgen05 prefill attention (b2s_attn_tc.cu): head_dim 64, <= 256 keys per sequence
 bool attn_tc_supported(int hd, int max_kv);
+bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride);
 int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st);
 int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const int32_t* cand, float* partials,
                                        float* cand_logits, cudaStream_t st);

@@ -129,6 +129,43 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
   }
 }
 
+// One epilogue warp drains its 32 rows x 256 columns of an accumulator, then releases it (one arrival per warp on
+// `release_bar`, which may live in the peer CTA of a pair: shared::cluster address).
+template <int EPI>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int nb, uint32_t taddr, int lane,
+                                              uint32_t release_bar) {
+  RowState<EPI> st;
+  int ca = -1, cb = -1;
+  if constexpr (EPI == EPI_LMHEAD) {
+    st.m = -INFINITY; st.s = 0.f; st.best = -INFINITY; st.arg = 0;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) st.top[j] = -INFINITY;
+    st.la = 0.f; st.lb = 0.f; st.has_a = false; st.has_b = false;
+    if (row < p.M) { ca = p.lmh.cand_ids[2 * row]; cb = p.lmh.cand_ids[2 * row + 1]; }
+  }
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; ++c) {
+    float v[32];
+    tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);   // warp-collective: all lanes participate
+    if (row < p.M) epi_chunk<EPI>(p, row, nb * BN + c * 32, v, st, ca, cb);
+  }
+  // all TMEM reads of this accumulator are done: hand it back to the MMA warp
+  tcgen05_fence_before();
+  __syncwarp();
+  if (lane == 0) asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(release_bar) : "memory");
+  if constexpr (EPI == EPI_LMHEAD) {
+    if (row < p.M) {
+      float* o = p.lmh.partials + (static_cast<size_t>(row) * p.tiles_n + nb) * LMH_PART;
+      o[0] = st.m; o[1] = st.s;
+#pragma unroll
+      for (int j = 0; j < 5; ++j) o[2 + j] = st.top[j];
+      o[7] = __int_as_float(st.arg);
+      if (st.has_a) p.lmh.cand_logits[2 * row] = st.la;
+      if (st.has_b) p.lmh.cand_logits[2 * row + 1] = st.lb;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Kernel
 // ---------------------------------------------------------------------------------------------
@@ -227,36 +264,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tcgen05_fence_after();
       const int row = mb * BM + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
-      RowState<EPI> st;
-      int ca = -1, cb = -1;
-      if constexpr (EPI == EPI_LMHEAD) {
-        st.m = -INFINITY; st.s = 0.f; st.best = -INFINITY; st.arg = 0;
-#pragma unroll
-        for (int j = 0; j < 5; ++j) st.top[j] = -INFINITY;
-        st.la = 0.f; st.lb = 0.f; st.has_a = false; st.has_b = false;
-        if (row < p.M) { ca = p.lmh.cand_ids[2 * row]; cb = p.lmh.cand_ids[2 * row + 1]; }
-      }
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        float v[32];
-        tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);   // warp-collective: all lanes participate
-        if (row < p.M) epi_chunk<EPI>(p, row, nb * BN + c * 32, v, st, ca, cb);
-      }
-      // all TMEM reads of this accumulator are done: hand it back to the MMA warp
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
-      if constexpr (EPI == EPI_LMHEAD) {
-        if (row < p.M) {
-          float* o = p.lmh.partials + (static_cast<size_t>(row) * p.tiles_n + nb) * LMH_PART;
-          o[0] = st.m; o[1] = st.s;
-#pragma unroll
-          for (int j = 0; j < 5; ++j) o[2 + j] = st.top[j];
-          o[7] = __int_as_float(st.arg);
-          if (st.has_a) p.lmh.cand_logits[2 * row] = st.la;
-          if (st.has_b) p.lmh.cand_logits[2 * row + 1] = st.lb;
-        }
-      }
+      epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc));
     }
   }
 
@@ -265,6 +273,166 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 1) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// CTA-pair kernel (cta_group::2): the two CTAs of a cluster compute one 256 x 256 tile.  Each CTA stages its own
+// 128 rows of A and its own 128 rows (N) of W per k-block (32 KB per stage instead of 48 KB, so the ring is
+// 6 deep and every W box is fetched once per pair); the leader CTA issues tcgen05.mma.cta_group::2 (M = 256)
+// for both, and each CTA's TMEM receives its own 128 accumulator rows.  Barrier protocol:
+//   full[s]    in the LEADER's smem; both CTAs' TMA loads complete_tx on it (64 KB per stage)
+//   empty[s]   in each CTA's smem; released by the leader's multicast tcgen05.commit
+//   tfull[a]   in each CTA's smem; multicast commit when an accumulator is complete
+//   tempty[a]  in the LEADER's smem; the 4 epilogue warps of BOTH CTAs arrive (count 8)
+// ---------------------------------------------------------------------------------------------
+static constexpr int STAGES2 = 6;
+static constexpr int STAGE2_BYTES = 2 * A_STAGE_BYTES;   // 16 KB A + 16 KB W
+static constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 256;
+static constexpr int BM2 = 256;
+
+__device__ __forceinline__ void tma_load_2d_cg2(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_commit_cg2_mc(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"(static_cast<uint16_t>(3)) : "memory");
+}
+__device__ __forceinline__ void tcgen05_mma_bf16_cg2(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                     uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n, int& mb, int& nb) {
+  constexpr int GM = 8;    // 8 x 256 rows per group
+  const int per_group = GM * tiles_n;
+  const int g = tile / per_group;
+  const int first_m = g * GM;
+  const int gm = min(GM, tiles_m - first_m);
+  const int within = tile - g * per_group;
+  mb = first_m + within % gm;
+  nb = within / gm;
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = smem_base + STAGES2 * STAGE2_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES2 + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * STAGES2 + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * STAGES2 + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * STAGES2 + 4);
+  constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;   // shared::cluster address of the same offset in the pair's leader CTA
+
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const bool leader = rank == 0;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_m2 = (p.M + BM2 - 1) / BM2;
+  const int num_tiles = tiles_m2 * p.tiles_n;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    for (int s = 0; s < STAGES2; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();          // barrier inits and TMEM allocation of both CTAs are visible to both
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int mb, nb;
+        tile_coords2(tile, tiles_m2, p.tiles_n, mb, nb);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * STAGE2_BYTES;
+          const uint32_t sb = sa + A_STAGE_BYTES;
+          const uint32_t fb = full_bar(stage) & PEER_MASK;
+          if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
+          tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM2 + static_cast<int>(rank) * BM);
+          tma_load_2d_cg2(sb, &tmB, fb, kb * BK, nb * BN + static_cast<int>(rank) * (BN / 2));
+          if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM2, BN);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1u;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE2_BYTES;
+          const uint32_t sb = sa + A_STAGE_BYTES;
+          const uint64_t adesc = make_kmajor_sw128_desc(sa);
+          const uint64_t bdesc = make_kmajor_sw128_desc(sb);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            tcgen05_mma_bf16_cg2(tmem_d, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          tcgen05_commit_cg2_mc(empty_bar(stage));
+          if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
+        }
+        tcgen05_commit_cg2_mc(tfull_bar(acc));
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5), both CTAs =====================
+    const int quad = warp & 3;
+    int it = 0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
+      int mb, nb;
+      tile_coords2(tile, tiles_m2, p.tiles_n, mb, nb);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tcgen05_fence_after();
+      const int row = mb * BM2 + static_cast<int>(rank) * BM + quad * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc) & PEER_MASK);
+    }
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();          // neither CTA may exit (or free TMEM) while its peer can still signal it
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
   }
 }
 
@@ -318,6 +486,7 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
 }
 
 static int g_num_sms = 0;
+int g_opt_cta_group = 1;   // 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256 tiles (b2s_set_option "gemm_cta_group")
 
 // ---- optional per-launch timing (bench.py roofline): CUDA events on the launching stream ----------
 struct GemmProfile {
@@ -338,7 +507,7 @@ static cudaEvent_t prof_event() {
 }
 
 template <int EPI>
-static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb2, const GemmParams& p, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
@@ -347,7 +516,19 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
   if (g_prof.on) cudaEventRecord(prof_event(), st);
-  gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, p);
+  if (g_opt_cta_group == 2) {
+    static bool attr2_set = false;
+    if (!attr2_set) {
+      B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
+      attr2_set = true;
+    }
+    const int tiles2 = static_cast<int>(ceil_div(p.M, BM2)) * p.tiles_n;
+    int pairs = g_num_sms / 2;
+    if (tiles2 < pairs) pairs = tiles2;
+    gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, p);
+  } else {
+    gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, p);
+  }
   if (g_prof.on) {
     cudaEventRecord(prof_event(), st);
     g_prof.flops += 2.0 * p.M * p.N * p.K;
@@ -369,9 +550,10 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     B2S_CHECK_CUDA(cudaGetDevice(&dev));
     B2S_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tb2;
   B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM));
   B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN));
+  B2S_TRY(make_tmap_bf16(&tb2, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN / 2));   // per-CTA half of a W box
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = static_cast<int>(ceil_div(M, BM));
@@ -380,13 +562,13 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   p.out = out; p.bias = bias;
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
   switch (epilogue) {
-    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, p, st);
-    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, p, st);
-    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, p, st);
-    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, p, st);
+    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, p, st);
+    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, p, st);
+    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, p, st);
+    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, p, st);
     case EPI_LMHEAD:
       B2S_REQUIRE(lmh && lmh->partials && lmh->cand_ids && lmh->cand_logits, "gemm_bf16: LM-head epilogue needs its buffers");
-      return launch_epi<EPI_LMHEAD>(ta, tb, p, st);
+      return launch_epi<EPI_LMHEAD>(ta, tb, tb2, p, st);
     default:
       set_error("gemm_bf16: unknown epilogue %d", epilogue);
       return B2S_EINVAL;
@@ -396,6 +578,17 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
 }  // namespace b2s
 
 extern "C" {
+
+int b2s_set_option(const char* name, int32_t value) {
+  B2S_REQUIRE(name != nullptr, "set_option: null name");
+  if (std::string(name) == "gemm_cta_group") {
+    B2S_REQUIRE(value == 1 || value == 2, "set_option: gemm_cta_group must be 1 or 2");
+    b2s::g_opt_cta_group = value;
+    return B2S_OK;
+  }
+  b2s::set_error("set_option: unknown option '%s'", name);
+  return B2S_EINVAL;
+}
 
 int b2s_profile_gemm(int32_t enable) {
   b2s::g_prof.on = enable != 0;

@@ -151,8 +151,10 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
     at.heads_per_cta = (max_qlen == 1) ? at.rep : ATT_HG;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
-    // prefill on the tensor cores when the shape allows it; single-token steps use the CUDA-core kernel
-    if (m->bf16 && max_qlen > 1 && attn_tc_supported(d.head_dim, max_kv)) {
+    // tensor-core kernel when the shape allows it (head_dim 64, <= 256 keys), CUDA-core kernel otherwise
+    const bool tc_ok = m->bf16 && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
+                                                : attn_tc_decode_supported(d.head_dim, max_kv, m->qkv_dim, m->q_base, m->q_hstride));
+    if (tc_ok) {
       B2S_TRY(launch_attn_tc(at, n_seqs, rows, static_cast<int>(w.cache_slots), max_qlen, st));
     } else {
       B2S_TRY(launch_attn<AT>(at, n_seqs, st));
