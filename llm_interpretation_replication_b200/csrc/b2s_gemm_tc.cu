@@ -32,16 +32,17 @@ static constexpr uint32_t TMEM_COLS = 512;
 struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
+  int group_m;           // row-blocks (of 128 rows) per rasterisation group
   void* out;             // bf16 or f32 [M,N]
   const float* bias;     // [N] or null
   LmHeadArgs lmh;
 };
 
-__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& mb, int& nb) {
-  const int per_group = GROUP_M * tiles_n;
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
+  const int per_group = group_m * tiles_n;
   const int g = tile / per_group;
-  const int first_m = g * GROUP_M;
-  const int gm = min(GROUP_M, tiles_m - first_m);
+  const int first_m = g * group_m;
+  const int gm = min(group_m, tiles_m - first_m);
   const int within = tile - g * per_group;
   mb = first_m + within % gm;
   nb = within / gm;
@@ -62,7 +63,7 @@ struct RowState<EPI_LMHEAD> {
 
 template <int EPI>
 __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0, float (&v)[32],
-                                          RowState<EPI>& st, int ca, int cb) {
+                                          RowState<EPI>& st, int ca, int cb, const float* resid) {
   const int N = p.N;
   if (col0 >= N) return;
   if (p.bias != nullptr) {
@@ -98,8 +99,7 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
       if (col0 + j < N) {
         float4 w = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
         if constexpr (EPI == EPI_RESID_F32) {
-          const float4 r = *reinterpret_cast<const float4*>(o + j);
-          w.x += r.x; w.y += r.y; w.z += r.z; w.w += r.w;
+          w.x += resid[j]; w.y += resid[j + 1]; w.z += resid[j + 2]; w.w += resid[j + 3];
         }
         *reinterpret_cast<float4*>(o + j) = w;
       }
@@ -129,6 +129,28 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
   }
 }
 
+__device__ __forceinline__ void load_resid_chunk(const GemmParams& p, int row, int col0, float (&r)[32]) {
+  if (row < p.M) {
+    const float* o = reinterpret_cast<const float*>(p.out) + static_cast<size_t>(row) * p.N + col0;
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      if (col0 + j < p.N) {
+        const float4 t = *reinterpret_cast<const float4*>(o + j);
+        r[j] = t.x; r[j + 1] = t.y; r[j + 2] = t.z; r[j + 3] = t.w;
+      }
+    }
+  }
+}
+// Pull this thread's 1 KB slice of the residual tile into L2 while the MMAs of the tile are still running.
+__device__ __forceinline__ void prefetch_resid_tile(const GemmParams& p, int row, int nb) {
+  if (row < p.M) {
+    const float* o = reinterpret_cast<const float*>(p.out) + static_cast<size_t>(row) * p.N + nb * BN;
+#pragma unroll
+    for (int j = 0; j < BN; j += 32)
+      if (nb * BN + j < p.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(o + j));
+  }
+}
+
 // One epilogue warp drains its 32 rows x 256 columns of an accumulator, then releases it (one arrival per warp on
 // `release_bar`, which may live in the peer CTA of a pair: shared::cluster address).
 template <int EPI>
@@ -143,11 +165,24 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
     st.la = 0.f; st.lb = 0.f; st.has_a = false; st.has_b = false;
     if (row < p.M) { ca = p.lmh.cand_ids[2 * row]; cb = p.lmh.cand_ids[2 * row + 1]; }
   }
+  if constexpr (EPI == EPI_RESID_F32) {
+    // read-modify-write of the fp32 residual: the loads of chunk c+1 are in flight while chunk c is processed
+    float rbuf[2][32];
+    load_resid_chunk(p, row, nb * BN, rbuf[0]);
+#pragma unroll
+    for (int c = 0; c < BN / 32; ++c) {
+      if (c + 1 < BN / 32) load_resid_chunk(p, row, nb * BN + (c + 1) * 32, rbuf[(c + 1) & 1]);
+      float v[32];
+      tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);
+      if (row < p.M) epi_chunk<EPI>(p, row, nb * BN + c * 32, v, st, ca, cb, rbuf[c & 1]);
+    }
+  } else {
 #pragma unroll 1
-  for (int c = 0; c < BN / 32; ++c) {
-    float v[32];
-    tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);   // warp-collective: all lanes participate
-    if (row < p.M) epi_chunk<EPI>(p, row, nb * BN + c * 32, v, st, ca, cb);
+    for (int c = 0; c < BN / 32; ++c) {
+      float v[32];
+      tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);   // warp-collective: all lanes participate
+      if (row < p.M) epi_chunk<EPI>(p, row, nb * BN + c * 32, v, st, ca, cb, nullptr);
+    }
   }
   // all TMEM reads of this accumulator are done: hand it back to the MMA warp
   tcgen05_fence_before();
@@ -209,7 +244,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mb, nb;
-        tile_coords(tile, p.tiles_m, p.tiles_n, mb, nb);
+        tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, mb, nb);
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -257,12 +292,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       int mb, nb;
-      tile_coords(tile, p.tiles_m, p.tiles_n, mb, nb);
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, mb, nb);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
+      const int row = mb * BM + quad * 32 + lane;
+      if constexpr (EPI == EPI_RESID_F32) prefetch_resid_tile(p, row, nb);
       mbar_wait(tfull_bar(acc), acc_phase);
       tcgen05_fence_after();
-      const int row = mb * BM + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc));
     }
@@ -314,8 +350,8 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n, int& mb, int& nb) {
-  constexpr int GM = 8;    // 8 x 256 rows per group
+__device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
+  const int GM = max(1, group_m / 2);    // groups of group_m x 128 rows = GM x 256 rows
   const int per_group = GM * tiles_n;
   const int g = tile / per_group;
   const int first_m = g * GM;
@@ -370,7 +406,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int stage = 0; uint32_t phase = 0;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
-        tile_coords2(tile, tiles_m2, p.tiles_n, mb, nb);
+        tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, mb, nb);
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE2_BYTES;
@@ -417,12 +453,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int it = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
       int mb, nb;
-      tile_coords2(tile, tiles_m2, p.tiles_n, mb, nb);
+      tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, mb, nb);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
+      const int row = mb * BM2 + static_cast<int>(rank) * BM + quad * 32 + lane;
+      if constexpr (EPI == EPI_RESID_F32) prefetch_resid_tile(p, row, nb);
       mbar_wait(tfull_bar(acc), acc_phase);
       tcgen05_fence_after();
-      const int row = mb * BM2 + static_cast<int>(rank) * BM + quad * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc) & PEER_MASK);
     }
@@ -486,7 +523,8 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
 }
 
 static int g_num_sms = 0;
-int g_opt_cta_group = 1;   // 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256 tiles (b2s_set_option "gemm_cta_group")
+int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
+int g_opt_cta_group = 2;   // 2: CTA pairs on 256x256 tiles (default, ~5-15% faster); 1: one CTA per 128x256 tile (b2s_set_option "gemm_cta_group")
 
 // ---- optional per-launch timing (bench.py roofline): CUDA events on the launching stream ----------
 struct GemmProfile {
@@ -559,6 +597,15 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   p.tiles_m = static_cast<int>(ceil_div(M, BM));
   p.tiles_n = static_cast<int>(ceil_div(N, BN));
   p.num_kb = static_cast<int>(ceil_div(K, BK));
+  // Rasterisation: the A panel of a group (group_m x 128 rows x K) is re-read by every wave of the group, so it
+  // should stay L2-resident (<= ~40 MB); when K is so long that even 16 row-blocks exceed that, no cross-wave
+  // reuse is possible and the near-square wave footprint (16 x 9 tiles) minimises the bytes each wave streams.
+  {
+    const double mb_bytes = 2.0 * BM * K;
+    int gm = 64;
+    while (gm > 16 && gm * mb_bytes > 40e6) gm >>= 1;
+    p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
+  }
   p.out = out; p.bias = bias;
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
   switch (epilogue) {
@@ -584,6 +631,11 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_cta_group") {
     B2S_REQUIRE(value == 1 || value == 2, "set_option: gemm_cta_group must be 1 or 2");
     b2s::g_opt_cta_group = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_group_m") {
+    B2S_REQUIRE(value >= 0 && value <= 1024, "set_option: gemm_group_m must be in [0, 1024]");
+    b2s::g_opt_group_m = value;
     return B2S_OK;
   }
   b2s::set_error("set_option: unknown option '%s'", name);

@@ -1,0 +1,86 @@
+"""Shared pieces of the kept entry points: model construction (random-init, no hub access offline),
+prompt formats, logging."""
+from __future__ import annotations
+
+import json
+import os
+import sys
+
+import torch
+
+from .. import shapes, weights
+from ..scorer import Scorer
+from ..tokenizer import HashTokenizer
+
+DATA_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data")
+
+# reference analysis/run_base_vs_instruct_100q.py:455-461
+FEW_SHOT = '''Question: Is "soup" a "beverage"? Answer either 'Yes' or 'No', without any other text.
+Answer: No.
+
+Question: Is a "tweet" a "publication"? Answer either 'Yes' or 'No', without any other text.
+Answer: Yes.
+
+'''
+
+
+def log_print(*args, **kwargs):
+    print(*args, **kwargs)
+    sys.stdout.flush()
+
+
+def survey_questions():
+    """The 100 ordinary-meaning questions (hard-coded list of the reference script, :122-230)."""
+    d = json.load(open(os.path.join(DATA_DIR, "survey_questions.json")))
+    return d["survey1"], d["survey2"]
+
+
+def format_base(prompt: str) -> str:      # run_base_vs_instruct_100q.py:466-467
+    return f"{FEW_SHOT}Question: {prompt} Answer either 'Yes' or 'No', without any other text.\nAnswer:"
+
+
+def format_instruct(prompt: str) -> str:  # run_base_vs_instruct_100q.py:468-469; compare_instruct_models.py:488
+    return f"{prompt} Answer either 'Yes' or 'No', without any other text."
+
+
+def format_baichuan(prompt: str) -> str:  # compare_instruct_models.py:491-492
+    return f"<human>: {prompt} Answer either 'Yes' or 'No', without any other text.\n<bot>:"
+
+
+def format_perturbation(rephrased_main: str, response_format: str) -> str:   # perturb_prompts.py:215
+    return f"{rephrased_main} {response_format}"
+
+
+def model_seed(model_name: str) -> int:
+    import zlib
+    return zlib.crc32(model_name.encode()) & 0x7FFFFFFF
+
+
+def load_model(model_name: str, device=None, mode=shapes.MODE_BF16_FAST, n_layer: int = 0, max_tokens: int = 65536,
+               max_seqs: int = 1024):
+    """Stand-in for AutoTokenizer/AutoModelForCausalLM.from_pretrained (reference :416-450): the shape of the
+    named hub model with random-init weights (seeded by the name) and the offline tokenizer.  Raises KeyError for
+    architectures outside the supported families, which the callers turn into NaN rows as the reference does for
+    models that fail to load."""
+    if model_name in shapes.HUB_TO_SHAPE:
+        shp = shapes.HUB_TO_SHAPE[model_name]()
+    elif model_name in shapes.REGISTRY:
+        shp = shapes.REGISTRY[model_name]()
+    else:
+        raise KeyError(f"architecture of {model_name} is not supported by the B200 scorer")
+    if n_layer:
+        shp = shp.with_layers(n_layer)
+    device = torch.device(device if device is not None else "cuda:0")
+    dt = torch.bfloat16 if mode == shapes.MODE_BF16_FAST else torch.float32
+    W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
+    scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs)
+    tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
+    return scorer, tok
+
+
+def unload(scorer):
+    scorer.close()
+    del scorer
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()

@@ -1,0 +1,96 @@
+#!/usr/bin/env python
+"""Entry point 2 -- mirrors reference analysis/compare_instruct_models.py and ..._survey2.py (byte-identical in
+the reference except for the prompt list and the CSV name).
+
+Keeps the model list (:145-166), the bare / Baichuan prompt formats (:488-492), the k=2 scorer variant with
+candidate ids resolved WITH special tokens (:229-233), the NaN rows for models that cannot be run (:502-522), and
+`prepare_data_for_csv` (:103-121) with columns prompt, model, model_family, model_output, yes_prob, no_prob,
+relative_prob.  Encoder-decoder models (T5/T0/tk-instruct, :178-226) and architectures outside Falcon / GPT-NeoX
+get NaN rows ("next" row N4).  The reference's cache purge (:81-101) is deliberately not reproduced.
+
+    python -m llm_interpretation_replication_b200.entrypoints.compare_instruct_models [--survey 1|2] [--out DIR]
+"""
+from __future__ import annotations
+
+import argparse
+import os
+
+import pandas as pd
+
+from .. import scorer as S
+from .common import format_baichuan, format_instruct, load_model, log_print, survey_questions, unload
+
+models = [
+    "allenai/tk-instruct-3b-def",
+    "baichuan-inc/Baichuan2-7B-Chat",
+    "bigscience/bloomz-7b1",
+    "bigscience/T0_3B",
+    "facebook/opt-iml-1.3b",
+    "h2oai/h2ogpt-oasst1-512-12b",
+    "mistralai/Mistral-7B-Instruct-v0.3",
+    "Qwen/Qwen-7B-Chat",
+    "tiiuae/falcon-7b-instruct",
+    "togethercomputer/RedPajama-INCITE-7B-Instruct",
+]
+
+
+def prepare_data_for_csv(outputs, model_names):
+    data = []
+    for model_name in model_names:
+        model_family = model_name.split("/")[1].split("-")[0].lower()
+        for prompt in outputs.get(model_name, {}):
+            result = outputs[model_name][prompt]
+            data.append({"prompt": prompt, "model": model_name, "model_family": model_family,
+                         "model_output": result.get("completion", "N/A"),
+                         "yes_prob": result.get("yes_prob", float("nan")),
+                         "no_prob": result.get("no_prob", float("nan")),
+                         "relative_prob": result.get("relative_prob", float("nan"))})
+    return pd.DataFrame(data)
+
+
+def run(prompts, model_names=None, n_layer=0, device=None):
+    outputs = {}
+    for model_name in (model_names or models):
+        outputs[model_name] = {}
+        scorer = None
+        try:
+            scorer, tok = load_model(model_name, device=device, n_layer=n_layer)
+            fmt = format_baichuan if "baichuan" in model_name.lower() else format_instruct
+            formatted = [fmt(p) for p in prompts]
+            rows = S.score_prompts(scorer, tok, formatted, variant="instruct")
+            for p, r in zip(prompts, rows):
+                outputs[model_name][p] = r
+        except Exception as e:
+            log_print(f"Error running {model_name}: {e}")
+            for p in prompts:
+                outputs[model_name][p] = {"yes_prob": float("nan"), "no_prob": float("nan"), "relative_prob": float("nan"),
+                                          "prompt": p, "completion": "N/A"}
+        finally:
+            if scorer is not None:
+                unload(scorer)
+    return outputs
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--survey", type=int, default=1, choices=[1, 2])
+    ap.add_argument("--out", default=os.environ.get("B2S_OUTPUT_DIR", "llm_interpretation_out"))
+    ap.add_argument("--layers", type=int, default=0)
+    ap.add_argument("--questions", type=int, default=0)
+    args = ap.parse_args(argv)
+    os.makedirs(args.out, exist_ok=True)
+    s1, s2 = survey_questions()
+    prompts = s1 if args.survey == 1 else s2
+    if args.questions:
+        prompts = prompts[:args.questions]
+    outputs = run(prompts, n_layer=args.layers)
+    df = prepare_data_for_csv(outputs, models)
+    name = "instruct_model_comparison_results.csv" if args.survey == 1 else "instruct_model_comparison_results_survey2.csv"
+    path = os.path.join(args.out, name)
+    df.to_csv(path, index=False)
+    log_print(f"Results saved to {path}")
+    return df
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,71 @@
+"""Kept entry points end to end on the GPU (truncated random-init models), output schemas of SURVEY Appendix E."""
+import json
+import os
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+def test_entry_point_1_run_and_resume(tmp_path):
+    from llm_interpretation_replication_b200.entrypoints import run_base_vs_instruct_100q as E1
+    args = ["--out", str(tmp_path), "--layers", "1", "--questions", "12", "--pairs", "1"]
+    df = E1.main(args)
+    assert list(df.columns) == ["yes_prob", "no_prob", "relative_prob", "completion", "success", "prompt", "model",
+                                "formatted_prompt", "model_family", "base_or_instruct"]
+    assert len(df) == 24 and df["success"].all() and df["relative_prob"].between(0, 1).all()
+    ck = json.load(open(os.path.join(tmp_path, E1.CHECKPOINT_NAME)))
+    assert ck["completed_models"] == ["tiiuae/falcon-7b", "tiiuae/falcon-7b-instruct"] and len(ck["results"]) == 24
+    df2 = E1.main(args)                       # everything is in the checkpoint: nothing is re-run
+    assert len(df2) == 24 and np.allclose(df2["relative_prob"], df["relative_prob"])
+    on_disk = pd.read_csv(os.path.join(tmp_path, E1.RESULTS_NAME))
+    assert len(on_disk) == 24
+
+
+def test_entry_point_2_nan_rows_for_unsupported_models(tmp_path):
+    from llm_interpretation_replication_b200.entrypoints import compare_instruct_models as E2
+    out = E2.run(['Is a "tent" a "dwelling"?', 'Is "water" a "food"?'],
+                 model_names=["bigscience/T0_3B", "tiiuae/falcon-7b-instruct"], n_layer=1)
+    df = E2.prepare_data_for_csv(out, ["bigscience/T0_3B", "tiiuae/falcon-7b-instruct"])
+    assert df[df.model == "bigscience/T0_3B"]["relative_prob"].isna().all()
+    ok = df[df.model == "tiiuae/falcon-7b-instruct"]
+    assert ok["relative_prob"].between(0, 1).all() and len(ok) == 2
+
+
+def test_entry_point_3_matches_reference_output(tmp_path):
+    from llm_interpretation_replication_b200.entrypoints import analyze_results_base_versus_instruct as E3
+    g = json.load(open(os.path.join(GOLDEN, "bootstrap_golden.json")))["a9_shipped"]["expect"]
+    out = E3.main([os.path.join(GOLDEN, "model_comparison_results.csv"), "--out", str(tmp_path)])
+    v = dict(zip(out["Metric"], out["Value"]))
+    for k_csv, k_g in (("MAE", "mae"), ("MAE_CI_Lower", "mae_ci_lower"), ("MAE_CI_Upper", "mae_ci_upper"),
+                       ("MAE_P_Value", "mae_p_value"), ("Mean_Diff", "mean_diff"), ("Mean_Diff_CI_Lower", "mean_ci_lower"),
+                       ("Mean_Diff_CI_Upper", "mean_ci_upper"), ("Mean_Diff_P_Value", "mean_p_value")):
+        assert abs(v[k_csv] - g[k_g]) <= 1e-6, k_csv
+    assert v["N_Prompts"] == 49 and v["N_Models"] == 3 and v["N_Bootstrap"] == 10000
+
+
+def test_entry_point_5_matches_survey_appendix_d1(tmp_path):
+    """base_vs_instruct_mae_results.csv on the shipped data = SURVEY.md Appendix D.1 (reference run), to 1e-6."""
+    from llm_interpretation_replication_b200.entrypoints import analyze_base_vs_instruct_mae_100q as E5
+    df = E5.main(["--survey", os.path.join(GOLDEN, "word_meaning_survey_results.csv"),
+                  os.path.join(GOLDEN, "word_meaning_survey_results_part_2.csv"),
+                  "--models", os.path.join(GOLDEN, "model_comparison_results.csv"), "--out", str(tmp_path)])
+    assert list(df.columns) == ["Model_Family", "Base_MAE", "Instruct_MAE", "Difference", "CI_Lower", "CI_Upper",
+                                "P_Value", "N_Questions"]
+    want = {
+        "Falcon": (0.21272931615254154, 0.2860028824961106, 0.07327356634356907, 0.03890079381792252, 0.10571830556034265, 0.0),
+        "StableLM": (0.2463026667542609, 0.21132069200343345, -0.034981974750827455, -0.06531580056361877, -0.004964252070598784, 0.022),
+        "RedPajama": (0.13668646460875206, 0.13478036259181617, -0.00190610201693589, -0.0330549058077339, 0.03000247566316429, 0.9),
+        "BLOOM": (0.15951182759937632, 0.1941379214681884, 0.034626093868812075, -0.0031113518582683228, 0.07109445910330933, 0.0694),
+        "Pythia-Dolly": (0.18341891794251156, 0.3791966521247064, 0.19577773418219482, 0.13710473748786867, 0.25161111176486795, 0.0),
+        "OVERALL": (0.18772983861148848, 0.241087702136851, 0.05335786352536251, 0.035142340773154666, 0.07126612798098764, 0.0),
+    }
+    assert df["Model_Family"].tolist() == list(want)
+    for _, r in df.iterrows():
+        got = (r.Base_MAE, r.Instruct_MAE, r.Difference, r.CI_Lower, r.CI_Upper, r.P_Value)
+        assert np.allclose(got, want[r.Model_Family], atol=1e-6), r.Model_Family
+        assert r.N_Questions == 49

@@ -6,6 +6,16 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=[1, 2], ids=["cta1", "cta_pair"])
+def cta_group(request):
+    """Run the tensor-core GEMM tests on both tilings: one CTA per 128x256 tile and CTA pairs (cta_group::2)."""
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    _lib.check(lib.b2s_set_option(b"gemm_cta_group", request.param), "set_option")
+    yield request.param
+    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 2), "set_option")   # library default
+
+
 def _rand(shape, scale=1.0, seed=0, dtype=torch.bfloat16):
     g = torch.Generator(device="cuda").manual_seed(seed)
     return (torch.randn(shape, generator=g, device="cuda") * scale).to(dtype)
@@ -13,7 +23,7 @@ def _rand(shape, scale=1.0, seed=0, dtype=torch.bfloat16):
 
 @pytest.mark.parametrize("M,N,K", [(128, 256, 64), (128, 256, 512), (256, 512, 4544), (300, 520, 192),
                                    (77, 4672, 4544), (1, 264, 72), (1000, 4544, 1024), (513, 18176, 4544)])
-def test_gemm_tc_store_f32(M, N, K):
+def test_gemm_tc_store_f32(M, N, K, cta_group):
     import gpu_util as U
     A, W = _rand((M, K), 1.0, 1), _rand((N, K), 0.05, 2)
     ref = A.float() @ W.float().T
@@ -25,7 +35,7 @@ def test_gemm_tc_store_f32(M, N, K):
 
 @pytest.mark.parametrize("epi", [0, 1, 2])
 @pytest.mark.parametrize("use_bias", [False, True])
-def test_gemm_tc_epilogues(epi, use_bias):
+def test_gemm_tc_epilogues(epi, use_bias, cta_group):
     import gpu_util as U
     M, N, K = 391, 1160, 832
     A, W = _rand((M, K), 1.0, 3), _rand((N, K), 0.05, 4)
@@ -74,7 +84,7 @@ def test_gemm_f32(M, N, K, epi):
 
 
 @pytest.mark.parametrize("M,V,d", [(5, 1000, 192), (128, 65024, 256), (200, 50432, 512), (1, 320, 64)])
-def test_lm_head_fused(M, V, d):
+def test_lm_head_fused(M, V, d, cta_group):
     import gpu_util as U
     h, W = _rand((M, d), 1.0, 7), _rand((V, d), 0.05, 8)
     g = torch.Generator(device="cuda").manual_seed(9)
