@@ -32,9 +32,13 @@ enum { B2S_OK = 0, B2S_EINVAL = -1, B2S_ECUDA = -2, B2S_ENOMEM = -3, B2S_EUNSUPP
 
 enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1 };
 enum { B2S_QKV_FALCON_MQA = 0, B2S_QKV_NEOX_INTERLEAVED = 1 };
-/* compute modes: BF16_FAST = bf16 tcgen05 MMA operands, fp32 accumulation in TMEM, fp32 residual
- * stream; FP32_CHECK = fp32 weights and activations on CUDA cores (parity gate 1e-5). */
-enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP32_CHECK = 3 };
+/* compute modes (tensor-core modes: fp32 accumulation in TMEM, fp32 residual stream, LayerNorm and softmax):
+ *   BF16_FAST   bf16 weight matrices; activations (every GEMM A operand, Q/K/V/P) rounded to bf16;
+ *   FP16        fp16 weight matrices (bf16 checkpoints convert exactly for |w| >= 2^-17) and activations rounded
+ *               to fp16: 3 more mantissa bits at the same MMA rate (tcgen05 kind::f16 needs A and B alike, a
+ *               mixed fp16 x bf16 MMA is an illegal instruction); the mode that holds the 2e-3 gate at 32 layers;
+ *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5). */
+enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_FP32_CHECK = 3 };
 
 /* weight_ptrs slots: 6 global + 16 per layer (see llm_interpretation_replication_b200/weights.py) */
 enum { B2S_W_WTE = 0, B2S_W_LNF_G = 1, B2S_W_LNF_B = 2, B2S_W_LM_HEAD = 3, B2S_W_ROPE_COS = 4,
@@ -52,7 +56,7 @@ typedef struct {
   int32_t has_bias;
   int32_t qkv_layout;          /* B2S_QKV_* */
   int32_t max_pos;             /* rows of the rope cos/sin tables */
-  int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST expects bf16 matrices, FP32_CHECK fp32 */
+  int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST expects bf16 matrices, FP16 fp16, FP32_CHECK fp32 */
 } b2s_model_desc;
 
 typedef struct b2s_model b2s_model;
@@ -107,6 +111,9 @@ B2S_API int b2s_set_option(const char* name, int32_t value);
  * FalconLinear / nn.Linear calls (HF falcon:60-65, gpt_neox:41-42,200-201).
  *  epilogue: 0 store bf16, 1 GELU(erf) then store bf16, 2 out_f32 += acc (residual), 4 store fp32 */
 B2S_API int b2s_gemm_bf16(const void* A /*bf16 [M,K]*/, const void* W /*bf16 [N,K]*/, const float* bias,
+                  void* out, int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
+/* same as b2s_gemm_bf16 with fp16 operands (and fp16 16-bit outputs) */
+B2S_API int b2s_gemm_f16(const void* A /*fp16 [M,K]*/, const void* W /*fp16 [N,K]*/, const float* bias,
                   void* out, int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
 B2S_API int b2s_gemm_f32(const float* A, const float* W, const float* bias, float* out,
                  int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
@@ -176,6 +183,19 @@ B2S_API size_t b2s_bootstrap_scratch_bytes(int64_t B);
 B2S_API int b2s_bootstrap_summary(const double* boot, int64_t B, int32_t stat, double q_lo, double q_hi,
                           double observed, double* summary /*dev [8]*/, double* stat_out /*dev [B] or NULL*/,
                           void* scratch, size_t scratch_bytes, void* stream);
+
+/* Simulated-individual correlation bootstrap: the body of the 10,000-iteration loop of
+ * survey_analysis/bootstrap_confidence_intervals.py:54-99,126-148.  Seed s = seed0 + i runs
+ * calculate_individual_correlations(model_responses, n_samples, seed=s) on a NumPy-legacy MT19937 of its own
+ * (randint(1,6), normal(mean,std) with the cached polar-method Gaussian, scipy pearsonr) and yields the mean
+ * correlation of base and of instruct models.  avail/rel [n_models,5,10] (groups x questions 1..11 without 8),
+ * mean/std [5,10] on the 0-1 scale, model_type 0 = base / 1 = instruct, models in CSV order.
+ * corrs_out (optional) receives the per-sample correlations of the first seed; final_state (optional) the MT19937
+ * state after the last seed, so that the script's later np.random.choice calls continue the same stream. */
+B2S_API int b2s_ci_simulate(const uint8_t* avail, const double* rel, const double* mean, const double* stdv,
+                    const int32_t* model_type, int32_t n_models, int32_t n_samples, uint32_t seed0, int32_t n_seeds,
+                    double* means_out /*dev [n_seeds,2]*/, double* corrs_out /*dev [n_models,n_samples] or NULL*/,
+                    uint32_t* final_state /*dev [625] or NULL*/, void* stream);
 
 #ifdef __cplusplus
 }

@@ -41,6 +41,7 @@ SIGNATURES = {
     "b2s_profile_gemm": (C.c_int, [_i32]),
     "b2s_profile_gemm_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(_i64), C.POINTER(C.c_double)]),
     "b2s_gemm_bf16": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "b2s_gemm_f16": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "b2s_gemm_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "b2s_attention_bf16": (C.c_int, [_vp] * 8 + [_i32] * 12 + [_vp]),
     "b2s_lm_head_scratch_bytes": (_sz, [_i32, _i32]),
@@ -50,6 +51,7 @@ SIGNATURES = {
     "b2s_mt19937_seed": (C.c_int, [_u32, _vp, _vp]),
     "b2s_mt19937_choice": (C.c_int, [_vp, _i32, _i64, _vp, _vp]),
     "b2s_bootstrap_resample": (C.c_int, [_vp, _i32, _i32, _i32, _i64, _vp, _u64, _vp, _vp]),
+    "b2s_ci_simulate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _u32, _i32, _vp, _vp, _vp, _vp]),
     "b2s_bootstrap_scratch_bytes": (_sz, [_i64]),
     "b2s_bootstrap_summary": (C.c_int, [_vp, _i64, _i32, _dbl, _dbl, _dbl, _vp, _vp, _vp, _sz, _vp]),
 }

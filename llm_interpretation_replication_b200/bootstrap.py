@@ -175,3 +175,69 @@ def prompt_bootstrap_and_signflip(pivot: np.ndarray, n_bootstrap=N_BOOTSTRAP, se
     return dict(mae=observed_mae, mae_ci_lower=s_mae["pct_lo"], mae_ci_upper=s_mae["pct_hi"], mae_p_value=1.0,
                 mean_diff=observed_mean, mean_ci_lower=s_mean["pct_lo"], mean_ci_upper=s_mean["pct_hi"],
                 mean_p_value=p_mean, n_prompts=n, n_models=F)
+
+
+# ---- simulated-individual correlation bootstrap (bootstrap_confidence_intervals.py) ----------------------------
+CI_GROUPS = {g: [f"Q{g}_{i}" for i in range(1, 12) if i != 8] for g in range(1, 6)}   # reference :45-51
+
+
+def build_ci_tables(model_responses: Dict[str, dict], question_mapping: Dict[str, str], by_question: Dict[str, dict]):
+    """Flatten the script's dict lookups (:67-90) into dense tables for the kernel: for group g and its k-th
+    question, the FIRST prompt of question_mapping that maps to the id (the script's linear search), whether that
+    prompt is in the model's responses and the id has human statistics, the model's rel_prob, mean/std on 0-1."""
+    models = list(model_responses.keys())
+    M = len(models)
+    avail = np.zeros((M, 5, 10), np.uint8)
+    rel = np.full((M, 5, 10), np.nan, np.float64)
+    mean = np.zeros((5, 10), np.float64)
+    std = np.zeros((5, 10), np.float64)
+    first_prompt = {}
+    for p, q in question_mapping.items():
+        first_prompt.setdefault(q, p)
+    for g in range(1, 6):
+        for k, qid in enumerate(CI_GROUPS[g]):
+            p = first_prompt.get(qid)
+            if qid in by_question:
+                mean[g - 1, k] = by_question[qid]["mean_response"] / 100.0
+                std[g - 1, k] = by_question[qid]["std_response"] / 100.0
+            for m, name in enumerate(models):
+                r = model_responses[name]
+                if p and p in r and qid in by_question:
+                    avail[m, g - 1, k] = 1
+                    rel[m, g - 1, k] = r[p]["rel_prob"]
+    types = np.array([0 if model_responses[n][next(iter(model_responses[n]))]["type"] == "base" else 1 for n in models],
+                     dtype=np.int32)
+    return models, avail, rel, mean, std, types
+
+
+def simulate_individual_correlations(tables, n_samples: int, seed0: int, n_seeds: int, want_corrs: bool = False,
+                                     want_state: bool = False, device=None):
+    """means [n_seeds, 2] (base, instruct); optionally the first seed's per-sample correlations [M, n_samples]
+    and the MT19937 state after the last seed (a NumpyLegacyStream that continues it)."""
+    lib = _lib.load()
+    if not torch.cuda.is_available():
+        raise _lib.B2SError("no CUDA device: the bootstrap kernels have no CPU fallback")
+    device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+    models, avail, rel, mean, std, types = tables
+    d = lambda a: torch.as_tensor(np.ascontiguousarray(a)).to(device)
+    t_av, t_rel, t_mean, t_std, t_ty = d(avail), d(rel), d(mean), d(std), d(types)
+    means = torch.empty((n_seeds, 2), dtype=torch.float64, device=device)
+    corrs = torch.empty((len(models), n_samples), dtype=torch.float64, device=device) if want_corrs else None
+    stream_obj = None
+    state = None
+    if want_state:
+        stream_obj = NumpyLegacyStream(0, device)
+        state = stream_obj.state
+    with torch.cuda.device(device):
+        _lib.check(lib.b2s_ci_simulate(_lib.ptr(t_av), _lib.ptr(t_rel), _lib.ptr(t_mean), _lib.ptr(t_std), _lib.ptr(t_ty),
+                                       len(models), n_samples, int(seed0) & 0xFFFFFFFF, n_seeds, _lib.ptr(means),
+                                       _lib.ptr(corrs), _lib.ptr(state), _lib.current_stream()), "b2s_ci_simulate")
+    return means, corrs, stream_obj
+
+
+def percentile_ci(x: torch.Tensor, q_lo=2.5, q_hi=97.5):
+    """np.percentile CI of a device vector (NaNs must have been removed) through the sort/percentile kernel."""
+    boot = torch.zeros((x.numel(), 3), dtype=torch.float64, device=x.device)
+    boot[:, 0] = x
+    s, _ = summary(boot, 0, q_lo, q_hi, 0.0)
+    return s["pct_lo"], s["pct_hi"]

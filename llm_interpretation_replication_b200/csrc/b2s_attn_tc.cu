@@ -36,7 +36,8 @@ static constexpr uint32_t AT_O_COL = 384;  // O accumulators: lane l at columns 
 
 struct AttnTcParams {
   BatchMeta meta;
-  __nv_bfloat16* out;     // [T, nh*64]
+  uint16_t* out;          // [T, nh*64] bf16 or fp16 bits
+  int f16;                // Q/K/V/P/out are fp16 instead of bf16
   int nh, nkv, rep;
   int q_base, q_hstride;  // column of head h in the qkv row = q_base + h*q_hstride
   int decode;             // 0: rows are query positions (prefill); 1: rows are heads of one token
@@ -45,8 +46,9 @@ struct AttnTcParams {
 };
 
 // instruction descriptor: fp32 accumulate, bf16 A/B, A K-major, B K-major (b_mn = 0) or MN-major (b_mn = 1)
-__device__ __forceinline__ uint32_t idesc_bf16(int m, int n, int b_mn) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(b_mn) << 16) |
+__device__ __forceinline__ uint32_t idesc_16(int m, int n, int b_mn, int f16) {
+  const uint32_t fmt = f16 ? 0u : 1u;    // F16 = 0, BF16 = 1 for both operands
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | (static_cast<uint32_t>(b_mn) << 16) |
          (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 // V tile [keys, 64 dims] with 128-byte rows, 128B swizzle, used as the MN-major B operand (N = dims, K = keys):
@@ -140,8 +142,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       tma_load_2d(sV, &tmV, bar_kv, g * AT_HD, kv0);
       for (int i = 0; i < AT_NQ && i < n_items; ++i) load_q(i);
       mbar_wait(bar_kv, 0);
-      const uint32_t idesc_s = idesc_bf16(AT_BM, kvp, 0);
-      const uint32_t idesc_o = idesc_bf16(AT_BM, AT_HD, 1);
+      const uint32_t idesc_s = idesc_16(AT_BM, kvp, 0, p.f16);
+      const uint32_t idesc_o = idesc_16(AT_BM, AT_HD, 1, p.f16);
       const uint64_t kdesc = make_kmajor_sw128_desc(sK);
       const uint64_t vdesc = make_mnmajor_sw128_desc(sV);
       const int skew = two ? 1 : 0;
@@ -186,7 +188,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int i = l; i < n_items; i += nl) {
       int limit, warp_limit;
       bool valid;
-      __nv_bfloat16* optr;
+      uint16_t* optr;
       if (p.decode) {
         const int rows_i = min(AT_BM, p.rep - i * AT_BM);
         valid = row < rows_i;
@@ -229,9 +231,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             if (c * 32 + j <= limit) p0 = ex2_approx(fmaf(v[j], p.scale_log2e, -ms));
             if (c * 32 + j + 1 <= limit) p1 = ex2_approx(fmaf(v[j + 1], p.scale_log2e, -ms));
           }
-          const __nv_bfloat162 b2 = __floats2bfloat162_rn(p0, p1);
-          lsum += __low2float(b2) + __high2float(b2);   // normalise by what the MMA actually multiplies
-          pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&b2);
+          if (p.f16) {
+            const __half2 h2 = __floats2half2_rn(p0, p1);
+            lsum += __low2float(h2) + __high2float(h2);   // normalise by what the MMA actually multiplies
+            pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&h2);
+          } else {
+            const __nv_bfloat162 b2 = __floats2bfloat162_rn(p0, p1);
+            lsum += __low2float(b2) + __high2float(b2);
+            pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&b2);
+          }
         }
         // 32 keys = 64 B = four 16-byte chunks of this row inside atom (c/2); swizzle: chunk ^= row % 8
         uint8_t* prow = pl + (c >> 1) * AT_P_ATOM + row * 128;
@@ -257,12 +265,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         uint4* dst = reinterpret_cast<uint4*>(optr);
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-          dst[q] = make_uint4(pack_bf16x2(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack_bf16x2(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
-                              pack_bf16x2(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack_bf16x2(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
+          dst[q] = make_uint4(pack_act16x2(o0[8 * q] * inv, o0[8 * q + 1] * inv, p.f16), pack_act16x2(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv, p.f16),
+                              pack_act16x2(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv, p.f16), pack_act16x2(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv, p.f16));
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-          dst[4 + q] = make_uint4(pack_bf16x2(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack_bf16x2(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
-                                  pack_bf16x2(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack_bf16x2(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
+          dst[4 + q] = make_uint4(pack_act16x2(o1[8 * q] * inv, o1[8 * q + 1] * inv, p.f16), pack_act16x2(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv, p.f16),
+                                  pack_act16x2(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv, p.f16), pack_act16x2(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv, p.f16));
       }
       tcgen05_fence_before();   // O and S reads are ordered before this thread's next bar_p arrival
     }
@@ -296,17 +304,18 @@ int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slot
   CUtensorMap tq, tk, tv;
   if (decode) {   // qkv viewed as [total_rows * qkv_dim/64, 64]
     const uint64_t rpt = static_cast<uint64_t>(a.qkv_dim / AT_HD);
-    B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows) * rpt, AT_HD, AT_HD * 2, AT_BM, AT_HD));
+    B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows) * rpt, AT_HD, AT_HD * 2, AT_BM, AT_HD, a.f16));
   } else {
     B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
-                              static_cast<uint64_t>(a.qkv_dim) * 2, AT_BM, AT_HD));
+                              static_cast<uint64_t>(a.qkv_dim) * 2, AT_BM, AT_HD, a.f16));
   }
   const uint64_t kvw = static_cast<uint64_t>(a.nkv) * AT_HD;
-  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, AT_MAXKV, AT_HD));
-  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, AT_MAXKV, AT_HD));
+  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, AT_MAXKV, AT_HD, a.f16));
+  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, AT_MAXKV, AT_HD, a.f16));
   AttnTcParams p;
   p.meta = a.meta;
-  p.out = reinterpret_cast<__nv_bfloat16*>(a.out);
+  p.out = reinterpret_cast<uint16_t*>(a.out);
+  p.f16 = a.f16;
   p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
   p.q_base = a.q_base; p.q_hstride = a.q_hstride;
   p.decode = decode ? 1 : 0;

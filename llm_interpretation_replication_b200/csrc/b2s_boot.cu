@@ -126,61 +126,62 @@ __device__ __forceinline__ void philox4x32_10(uint32_t (&c)[4], uint32_t k0, uin
   }
 }
 
-// One warp per resample b.  vals sit in shared memory (<= 5 KB at the BASELINE sizes); the index row is read
-// with coalesced 16-byte loads (or generated from the Philox counter (b, j/4)); fp64 accumulation.
+// One THREAD per resample b: its n indices are one contiguous row of the table, read with 16-byte loads, eight
+// indices (two loads) in flight per step so that every 32-byte sector is consumed as soon as it arrives; vals sit in
+// shared memory (<= 5 KB at the BASELINE sizes); fp64 accumulation in index order.  Without a table the indices come
+// from the Philox4x32-10 counter (b, j/4).
+__device__ __forceinline__ void boot_accum(const double* sv, int F, int split, int n, int id, double& lo, double& hi, double& ab) {
+  for (int f = 0; f < F; ++f) {
+    const double v = sv[f * n + id];
+    if (f < split) lo += v; else hi += v;
+    ab += fabs(v);
+  }
+}
+
 __global__ void __launch_bounds__(256)
 boot_resample_kernel(const double* __restrict__ vals, int F, int split, int n, long long B,
                      const int32_t* __restrict__ idx, unsigned long long seed, double* __restrict__ boot) {
   extern __shared__ double sv[];
   for (int i = threadIdx.x; i < F * n; i += blockDim.x) sv[i] = vals[i];
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const long long warps_total = static_cast<long long>(gridDim.x) * (blockDim.x >> 5);
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   const uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
-  for (long long b = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); b < B; b += warps_total) {
+  const bool vec = idx && (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(idx) & 15) == 0);
+  for (long long b = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; b < B; b += stride) {
     double lo = 0.0, hi = 0.0, ab = 0.0;
-    const int32_t* row = idx ? idx + b * n : nullptr;
-    const bool vec = row && ((reinterpret_cast<uintptr_t>(row) & 15) == 0);
-    for (int j0 = lane * 4; j0 < n; j0 += 128) {
-      int id[4];
-      if (row) {
-        if (vec && j0 + 3 < n) {
-          const int4 q = __ldg(reinterpret_cast<const int4*>(row + j0));
-          id[0] = q.x; id[1] = q.y; id[2] = q.z; id[3] = q.w;
-        } else {
-#pragma unroll
-          for (int u = 0; u < 4; ++u) id[u] = (j0 + u < n) ? __ldg(row + j0 + u) : 0;
-        }
-      } else {
+    if (vec) {
+      const int4* row = reinterpret_cast<const int4*>(idx + b * n);
+      const int nv = n / 4;
+      int j = 0;
+      for (; j + 1 < nv; j += 2) {
+        const int4 q0 = __ldg(row + j), q1 = __ldg(row + j + 1);
+        boot_accum(sv, F, split, n, q0.x, lo, hi, ab); boot_accum(sv, F, split, n, q0.y, lo, hi, ab);
+        boot_accum(sv, F, split, n, q0.z, lo, hi, ab); boot_accum(sv, F, split, n, q0.w, lo, hi, ab);
+        boot_accum(sv, F, split, n, q1.x, lo, hi, ab); boot_accum(sv, F, split, n, q1.y, lo, hi, ab);
+        boot_accum(sv, F, split, n, q1.z, lo, hi, ab); boot_accum(sv, F, split, n, q1.w, lo, hi, ab);
+      }
+      if (j < nv) {
+        const int4 q0 = __ldg(row + j);
+        boot_accum(sv, F, split, n, q0.x, lo, hi, ab); boot_accum(sv, F, split, n, q0.y, lo, hi, ab);
+        boot_accum(sv, F, split, n, q0.z, lo, hi, ab); boot_accum(sv, F, split, n, q0.w, lo, hi, ab);
+      }
+    } else if (idx) {
+      const int32_t* row = idx + b * n;
+      for (int j = 0; j < n; ++j) boot_accum(sv, F, split, n, __ldg(row + j), lo, hi, ab);
+    } else {
+      for (int j0 = 0; j0 < n; j0 += 4) {
         uint32_t c[4] = {static_cast<uint32_t>(b), static_cast<uint32_t>(static_cast<unsigned long long>(b) >> 32),
                          static_cast<uint32_t>(j0 >> 2), 0u};
         philox4x32_10(c, k0, k1);
 #pragma unroll
-        for (int u = 0; u < 4; ++u) id[u] = static_cast<int>(__umulhi(c[u], static_cast<uint32_t>(n)));
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (j0 + u < n) {
-          for (int f = 0; f < F; ++f) {
-            const double v = sv[f * n + id[u]];
-            if (f < split) lo += v; else hi += v;
-            ab += fabs(v);
-          }
-        }
+        for (int u = 0; u < 4; ++u)
+          if (j0 + u < n) boot_accum(sv, F, split, n, static_cast<int>(__umulhi(c[u], static_cast<uint32_t>(n))), lo, hi, ab);
       }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      lo += __shfl_xor_sync(0xffffffffu, lo, o);
-      hi += __shfl_xor_sync(0xffffffffu, hi, o);
-      ab += __shfl_xor_sync(0xffffffffu, ab, o);
-    }
-    if (lane == 0) {
-      const double nlo = static_cast<double>(split) * n, nhi = static_cast<double>(F - split) * n;
-      boot[b * 3 + 0] = split > 0 ? lo / nlo : nan("");
-      boot[b * 3 + 1] = F > split ? hi / nhi : nan("");
-      boot[b * 3 + 2] = ab / (static_cast<double>(F) * n);
-    }
+    const double nlo = static_cast<double>(split) * n, nhi = static_cast<double>(F - split) * n;
+    boot[b * 3 + 0] = split > 0 ? lo / nlo : nan("");
+    boot[b * 3 + 1] = F > split ? hi / nhi : nan("");
+    boot[b * 3 + 2] = ab / (static_cast<double>(F) * n);
   }
 }
 
@@ -336,7 +337,7 @@ int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t
   int dev = 0, sms = 0;
   B2S_CHECK_CUDA(cudaGetDevice(&dev));
   B2S_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  long long blocks = ceil_div(B, 8);
+  long long blocks = ceil_div(B, 256);
   const long long cap = static_cast<long long>(sms) * 8;   // 8 resident CTAs of 256 threads per SM
   if (blocks > cap) blocks = cap;
   boot_resample_kernel<<<static_cast<unsigned>(blocks), 256, smem, st>>>(vals, F, split, n, B, idx, philox_seed, boot);

@@ -3,6 +3,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
@@ -62,8 +63,9 @@ struct LmHeadArgs {
   float* cand_logits;       // [M,2]
 };
 
+// act_f16: A, W and the 16-bit outputs are fp16 instead of bf16 (tcgen05 kind::f16 needs both operands alike)
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K,
-                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st);
+                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0);
 int gemm_f32_launch(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
                     int epilogue, cudaStream_t st);
 
@@ -77,6 +79,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+// two fp32 -> packed 16-bit pair in the activation format of the run (bf16 or fp16)
+__device__ __forceinline__ uint32_t pack_act16x2(float lo, float hi, int f16) { return f16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi); }
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -89,9 +97,11 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 __device__ __forceinline__ float to_f32(float v) { return v; }
 __device__ __forceinline__ float to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f32(__half v) { return __half2float(v); }
 template <typename T> __device__ __forceinline__ T from_f32(float v);
 template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
 
 // insert v into a descending top-5 list
 __device__ __forceinline__ void top5_insert(float (&t)[5], float v) {

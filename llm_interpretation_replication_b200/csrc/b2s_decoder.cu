@@ -106,6 +106,7 @@ int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st) {
 }
 template int launch_ln<float, float>(const LnArgs&, int, cudaStream_t);
 template int launch_ln<__nv_bfloat16, __nv_bfloat16>(const LnArgs&, int, cudaStream_t);
+template int launch_ln<__half, __half>(const LnArgs&, int, cudaStream_t);
 
 // =================================================================================================
 // RoPE (rotate_half form on the first rotary_dim dims) + KV-cache append.
@@ -157,6 +158,7 @@ int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st) {
 }
 template int launch_rope_cache<float>(const RopeArgs&, int, cudaStream_t);
 template int launch_rope_cache<__nv_bfloat16>(const RopeArgs&, int, cudaStream_t);
+template int launch_rope_cache<__half>(const RopeArgs&, int, cudaStream_t);
 
 // =================================================================================================
 // Varlen causal attention over the KV cache (prefill: q_len = L; decode: q_len = 1).
@@ -287,6 +289,7 @@ int launch_attn(const AttnArgs& a_in, int n_seqs, cudaStream_t st) {
 }
 template int launch_attn<float>(const AttnArgs&, int, cudaStream_t);
 template int launch_attn<__nv_bfloat16>(const AttnArgs&, int, cudaStream_t);
+template int launch_attn<__half>(const AttnArgs&, int, cudaStream_t);
 
 // =================================================================================================
 // LM head: reduce full fp32 logits to per-tile partials (FP32_CHECK mode; the bf16 path produces the

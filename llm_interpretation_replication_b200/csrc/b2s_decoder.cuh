@@ -45,6 +45,7 @@ struct AttnArgs {
   int qkv_dim, nh, nkv, hd, rep /* nh / nkv */;
   int q_base, q_hstride;
   int max_kv;
+  int f16;             // 16-bit buffers hold fp16 instead of bf16 (tensor-core kernel)
   int heads_per_cta;   // set by the launcher: ATT_HG for prefill, all heads of the KV head for single-token steps
   float scale;
 };

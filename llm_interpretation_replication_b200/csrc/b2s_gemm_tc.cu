@@ -33,6 +33,7 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
+  int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
   void* out;             // bf16 or f32 [M,N]
   const float* bias;     // [N] or null
   LmHeadArgs lmh;
@@ -85,10 +86,10 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
     for (int j = 0; j < 32; j += 8) {
       if (col0 + j < N) {   // N % 8 == 0 is required by the launcher
         uint4 w;
-        w.x = pack_bf16x2(v[j], v[j + 1]);
-        w.y = pack_bf16x2(v[j + 2], v[j + 3]);
-        w.z = pack_bf16x2(v[j + 4], v[j + 5]);
-        w.w = pack_bf16x2(v[j + 6], v[j + 7]);
+        w.x = pack_act16x2(v[j], v[j + 1], p.act_f16);
+        w.y = pack_act16x2(v[j + 2], v[j + 3], p.act_f16);
+        w.z = pack_act16x2(v[j + 4], v[j + 5], p.act_f16);
+        w.w = pack_act16x2(v[j + 6], v[j + 7], p.act_f16);
         *reinterpret_cast<uint4*>(o + j) = w;
       }
     }
@@ -259,7 +260,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+      // a_format (bits 7..9) and b_format (bits 10..12): BF16 = 1, F16 = 0 -- the hardware wants both alike
+      const uint32_t idesc = make_idesc_bf16(BM, BN) & ~(p.act_f16 ? ((7u << 7) | (7u << 10)) : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
@@ -422,7 +424,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM2, BN);
+      const uint32_t idesc = make_idesc_bf16(BM2, BN) & ~(p.act_f16 ? ((7u << 7) | (7u << 10)) : 0u);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
@@ -499,13 +501,13 @@ static int get_encode_fn() {
 }
 
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
-                      uint32_t box_rows, uint32_t box_cols) {
+                      uint32_t box_rows, uint32_t box_cols, int f16) {
   B2S_TRY(get_encode_fn());
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {pitch_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = g_encode(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -518,8 +520,8 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_
 }
 
 // row-major [rows, cols] bf16 matrix, box = [box_rows, 64 cols]
-static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
-  return make_tmap_bf16_2d(map, base, rows, cols, cols * 2, box_rows, BK);
+static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, int f16 = 0) {
+  return make_tmap_bf16_2d(map, base, rows, cols, cols * 2, box_rows, BK, f16);
 }
 
 static int g_num_sms = 0;
@@ -576,7 +578,7 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
 }
 
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
-                   const LmHeadArgs* lmh, cudaStream_t st) {
+                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16) {
   B2S_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
   B2S_REQUIRE(K % 8 == 0, "gemm_bf16: K=%d must be a multiple of 8 (16-byte TMA row pitch)", K);
   B2S_REQUIRE(epilogue == EPI_LMHEAD || N % 8 == 0, "gemm_bf16: N=%d must be a multiple of 8", N);
@@ -589,9 +591,9 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     B2S_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
   CUtensorMap ta, tb, tb2;
-  B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM));
-  B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN));
-  B2S_TRY(make_tmap_bf16(&tb2, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN / 2));   // per-CTA half of a W box
+  B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM, act_f16));
+  B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN, act_f16));
+  B2S_TRY(make_tmap_bf16(&tb2, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN / 2, act_f16));   // per-CTA half of a W box
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = static_cast<int>(ceil_div(M, BM));
@@ -607,6 +609,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
   }
   p.out = out; p.bias = bias;
+  p.act_f16 = act_f16 ? 1 : 0;
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
   switch (epilogue) {
     case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, p, st);

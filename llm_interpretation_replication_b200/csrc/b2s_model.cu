@@ -32,7 +32,8 @@ struct b2s_model {
   int device;
   int qkv_dim;
   int q_base, q_hstride, k_base, v_base, kv_hstride;
-  bool bf16;
+  bool bf16;      // tensor-core mode (bf16 weights); false = fp32 check mode
+  int act_f16;    // tensor-core mode with fp16 operands (weights handed over as fp16)
   size_t at_size;
   const void* gw(int slot) const { return w[slot]; }
   const void* lw(int layer, int slot) const { return w[B2S_W_NGLOBAL + layer * B2S_W_PER_LAYER + slot]; }
@@ -109,12 +110,12 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
 // C = A . W^T with the mode's GEMM.  `out` is AT except for EPI_RESID_F32 (always the fp32 residual).
 int linear(const b2s_model* m, const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epi,
            cudaStream_t st) {
-  if (m->bf16) return gemm_tc_launch(A, W, bias, out, M, N, K, epi, nullptr, st);
+  if (m->bf16) return gemm_tc_launch(A, W, bias, out, M, N, K, epi, nullptr, st, m->act_f16);
   return gemm_f32_launch(reinterpret_cast<const float*>(A), reinterpret_cast<const float*>(W), bias,
                          reinterpret_cast<float*>(out), M, N, K, epi, st);
 }
 
-template <typename AT>
+template <typename AT, typename WT>
 int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
               int max_qlen, cudaStream_t st) {
   const b2s_model_desc& d = m->d;
@@ -130,7 +131,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     if (two_ln && d.parallel_residual) {   // both LayerNorms read the same residual: one pass, two affines
       ln.g2 = m->lwf(l, B2S_WL_LN2_G); ln.b2 = m->lwf(l, B2S_WL_LN2_B); ln.y2 = w.ln2;
     }
-    B2S_TRY((launch_ln<AT, AT>(ln, rows, st)));
+    B2S_TRY((launch_ln<AT, WT>(ln, rows, st)));
 
     B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
                    EPI_STORE_BF16, st));
@@ -150,6 +151,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.qkv_dim = m->qkv_dim; at.nh = d.n_head; at.nkv = d.n_kv_head; at.hd = d.head_dim; at.rep = d.n_head / d.n_kv_head;
     at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
     at.heads_per_cta = (max_qlen == 1) ? at.rep : ATT_HG;
+    at.f16 = m->act_f16;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
     // tensor-core kernel when the shape allows it (head_dim 64, <= 256 keys), CUDA-core kernel otherwise
     const bool tc_ok = m->bf16 && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
@@ -169,7 +171,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
         LnArgs l2{};
         l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps;
         l2.g1 = m->lwf(l, B2S_WL_LN2_G); l2.b1 = m->lwf(l, B2S_WL_LN2_B); l2.y1 = w.ln2;
-        B2S_TRY((launch_ln<AT, AT>(l2, rows, st)));
+        B2S_TRY((launch_ln<AT, WT>(l2, rows, st)));
       }
     }
     B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st));
@@ -181,14 +183,15 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
   lf.x = w.resid; lf.d = dm; lf.eps = d.norm_eps; lf.rows = w.meta.last_row;
   lf.g1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_G)); lf.b1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_B));
   lf.y1 = w.hfin;
-  B2S_TRY((launch_ln<AT, AT>(lf, n_seqs, st)));
+  B2S_TRY((launch_ln<AT, WT>(lf, n_seqs, st)));
   return B2S_OK;
 }
 
 int forward(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
             int max_qlen, cudaStream_t st) {
-  if (m->bf16) return forward_t<__nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
-  return forward_t<float>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
+  if (m->bf16 && m->act_f16) return forward_t<__half, __half>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
+  if (m->bf16) return forward_t<__nv_bfloat16, __nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
+  return forward_t<float, float>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
 }
 
 int lm_head(const b2s_model* m, const Workspace& w, const int32_t* cand, int n_seqs, cudaStream_t st) {
@@ -197,7 +200,8 @@ int lm_head(const b2s_model* m, const Workspace& w, const int32_t* cand, int n_s
   B2S_CHECK_CUDA(cudaMemsetAsync(w.cand_logits, 0, 8 * static_cast<size_t>(n_seqs), st));
   if (m->bf16) {
     LmHeadArgs a{cand, w.partials, w.cand_logits};
-    B2S_TRY(gemm_tc_launch(w.hfin, m->gw(B2S_W_LM_HEAD), nullptr, nullptr, n_seqs, d.vocab, d.d_model, EPI_LMHEAD, &a, st));
+    B2S_TRY(gemm_tc_launch(w.hfin, m->gw(B2S_W_LM_HEAD), nullptr, nullptr, n_seqs, d.vocab, d.d_model, EPI_LMHEAD, &a, st,
+                           m->act_f16));
   } else {
     B2S_TRY(gemm_f32_launch(reinterpret_cast<const float*>(w.hfin), reinterpret_cast<const float*>(m->gw(B2S_W_LM_HEAD)),
                             nullptr, w.logits, n_seqs, d.vocab, d.d_model, EPI_STORE_F32, st));
@@ -237,7 +241,7 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
               d.rotary_dim);
   B2S_REQUIRE(d.n_ln_per_layer == 1 || d.n_ln_per_layer == 2, "model_create: n_ln_per_layer must be 1 or 2");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
-  B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP32_CHECK,
+  B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_FP32_CHECK,
               "model_create: unknown compute mode %d", d.compute_mode);
   B2S_REQUIRE(d.d_model % 8 == 0 && d.d_ff % 8 == 0, "model_create: d_model and d_ff must be multiples of 8");
   const int need = B2S_W_NGLOBAL + B2S_W_PER_LAYER * d.n_layer;
@@ -255,7 +259,8 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   m->d = d;
   m->w.assign(weight_ptrs, weight_ptrs + need);
   m->device = device;
-  m->bf16 = d.compute_mode == B2S_MODE_BF16_FAST;
+  m->bf16 = d.compute_mode != B2S_MODE_FP32_CHECK;
+  m->act_f16 = d.compute_mode == B2S_MODE_FP16 ? 1 : 0;
   m->at_size = m->bf16 ? 2 : 4;
   m->qkv_dim = (d.n_head + 2 * d.n_kv_head) * d.head_dim;
   if (d.qkv_layout == B2S_QKV_FALCON_MQA) {
@@ -381,6 +386,13 @@ int b2s_gemm_bf16(const void* A, const void* W, const float* bias, void* out, in
   B2S_REQUIRE(A && W && out, "gemm_bf16: null argument");
   B2S_REQUIRE(epilogue != EPI_LMHEAD, "gemm_bf16: use b2s_lm_head_bf16 for the LM-head epilogue");
   return gemm_tc_launch(A, W, bias, out, M, N, K, epilogue, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b2s_gemm_f16(const void* A, const void* W, const float* bias, void* out, int32_t M, int32_t N, int32_t K, int32_t epilogue,
+                  void* stream) {
+  B2S_REQUIRE(A && W && out, "gemm_f16: null argument");
+  B2S_REQUIRE(epilogue != EPI_LMHEAD, "gemm_f16: LM-head epilogue not available here");
+  return gemm_tc_launch(A, W, bias, out, M, N, K, epilogue, nullptr, reinterpret_cast<cudaStream_t>(stream), 1);
 }
 
 int b2s_gemm_f32(const float* A, const float* W, const float* bias, float* out, int32_t M, int32_t N, int32_t K, int32_t epilogue,

@@ -98,9 +98,9 @@ __device__ __host__ constexpr uint32_t make_idesc_bf16(int m, int n) {
 
 
 // ---- host: TMA tensor maps --------------------------------------------------------------------------
-// 2D bf16 tensor [rows, cols] with a row pitch of pitch_bytes; box = [box_rows, box_cols]; 128B swizzle;
+// 2D bf16 (or fp16 when f16 != 0) tensor [rows, cols] with a row pitch of pitch_bytes; box = [box_rows, box_cols]; 128B swizzle;
 // out-of-bounds elements read as zero.
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
-                      uint32_t box_rows, uint32_t box_cols);
+                      uint32_t box_rows, uint32_t box_cols, int f16 = 0);
 
 }  // namespace b2s

@@ -43,3 +43,20 @@ def gather_rows(local_rows: torch.Tensor, local_index: Sequence[int], n_total: i
     result = torch.empty((n_total, C), dtype=torch.float32, device=dev)
     result[idx[keep]] = out[keep, :C]
     return result
+
+
+def score_ids_sharded(scorer, id_lists, cand, topk, max_lookahead, eos_id, group=None):
+    """Each rank scores its shard of already-tokenised prompts on its own GPU; one all-gather returns every
+    prompt's row (and greedy tokens) to every rank, in the callers' order."""
+    import torch.distributed as dist
+    g = None if group is True else group
+    world = dist.get_world_size(g)
+    rank = dist.get_rank(g)
+    lens = [len(x) for x in id_lists]
+    mine = shard_prompts(lens, world)[rank]
+    rows, gens = scorer.score_ids([id_lists[i] for i in mine], cand[mine], topk=topk, max_lookahead=max_lookahead,
+                                  eos_id=eos_id)
+    dev = scorer.device
+    local = torch.cat([torch.from_numpy(rows), torch.from_numpy(gens.astype(np.float32))], dim=1).to(dev)
+    full = gather_rows(local, mine, len(id_lists), world, group=g).cpu().numpy()
+    return full[:, :8].astype(np.float32), full[:, 8:].astype(np.int32)

@@ -84,3 +84,18 @@ def unload(scorer):
     import gc
     gc.collect()
     torch.cuda.empty_cache()
+
+
+def maybe_init_dist():
+    """Under torchrun (WORLD_SIZE > 1): one process per GPU, NCCL process group; returns (rank, world, shard_group)
+    where shard_group is what score_prompts(..., shard_group=) takes (None when single-process)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1:
+        return 0, 1, None
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    return dist.get_rank(), world, True

@@ -18,7 +18,9 @@ import os
 import pandas as pd
 
 from .. import scorer as S
-from .common import format_baichuan, format_instruct, load_model, log_print, survey_questions, unload
+import torch
+
+from .common import format_baichuan, format_instruct, load_model, log_print, maybe_init_dist, survey_questions, unload
 
 models = [
     "allenai/tk-instruct-3b-def",
@@ -48,7 +50,9 @@ def prepare_data_for_csv(outputs, model_names):
     return pd.DataFrame(data)
 
 
-def run(prompts, model_names=None, n_layer=0, device=None):
+def run(prompts, model_names=None, n_layer=0, device=None, shard_group=None):
+    """With shard_group (torchrun, one rank per GPU) the prompts of every model are sharded across the ranks and
+    the rows all-gathered (BASELINE config 4); every rank returns the full table."""
     outputs = {}
     for model_name in (model_names or models):
         outputs[model_name] = {}
@@ -57,7 +61,7 @@ def run(prompts, model_names=None, n_layer=0, device=None):
             scorer, tok = load_model(model_name, device=device, n_layer=n_layer)
             fmt = format_baichuan if "baichuan" in model_name.lower() else format_instruct
             formatted = [fmt(p) for p in prompts]
-            rows = S.score_prompts(scorer, tok, formatted, variant="instruct")
+            rows = S.score_prompts(scorer, tok, formatted, variant="instruct", shard_group=shard_group)
             for p, r in zip(prompts, rows):
                 outputs[model_name][p] = r
         except Exception as e:
@@ -77,14 +81,20 @@ def main(argv=None):
     ap.add_argument("--out", default=os.environ.get("B2S_OUTPUT_DIR", "llm_interpretation_out"))
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--questions", type=int, default=0)
+    ap.add_argument("--models", nargs="*", default=None, help="subset of the model list")
     args = ap.parse_args(argv)
+    rank, world, group = maybe_init_dist()
     os.makedirs(args.out, exist_ok=True)
     s1, s2 = survey_questions()
     prompts = s1 if args.survey == 1 else s2
     if args.questions:
         prompts = prompts[:args.questions]
-    outputs = run(prompts, n_layer=args.layers)
-    df = prepare_data_for_csv(outputs, models)
+    names = args.models or models
+    dev = f"cuda:{torch.cuda.current_device()}" if torch.cuda.is_available() else None
+    outputs = run(prompts, model_names=names, n_layer=args.layers, device=dev, shard_group=group)
+    df = prepare_data_for_csv(outputs, names)
+    if rank != 0:
+        return df
     name = "instruct_model_comparison_results.csv" if args.survey == 1 else "instruct_model_comparison_results_survey2.csv"
     path = os.path.join(args.out, name)
     df.to_csv(path, index=False)

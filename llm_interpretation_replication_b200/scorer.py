@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .shapes import DecoderShape, MODE_BF16_FAST, MODE_FP32_CHECK
+from .shapes import DecoderShape, MODE_BF16_FAST, MODE_FP16, MODE_FP32_CHECK
 from . import weights as _weights
 
 MAX_LOOK_AHEAD = 10   # reference run_base_vs_instruct_100q.py:285
@@ -81,8 +81,12 @@ class Scorer:
         self.mode = mode
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.max_tokens, self.max_seqs, self.max_lookahead = int(max_tokens), int(max_seqs), int(max_lookahead)
-        want = torch.bfloat16 if mode == MODE_BF16_FAST else torch.float32
+        want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
         W = dict(weights_dev)
+        if mode == MODE_FP16:   # bf16 (or fp32) checkpoints are handed to the library as fp16 copies
+            W = {k: (v.to(torch.float16) if _weights.is_matrix(k) and v.dtype != torch.float16 else v) for k, v in W.items()}
+            if weights_dev.get("lm_head") is weights_dev.get("wte"):
+                W["lm_head"] = W["wte"]
         if "rope_cos" not in W:
             W["rope_cos"], W["rope_sin"] = _weights.rope_tables(shape, self.device)
         for k, v in W.items():
@@ -215,26 +219,38 @@ def _nan_dict(variant: str, prompt: str, err: Exception) -> dict:
     return d
 
 
+def tokenize_prompts(tokenizer, prompts, variant, cand_strings=None):
+    """Token ids per prompt and the [N,2] candidate-id table, resolved as the chosen entry point does."""
+    ids = [list(tokenizer(p).input_ids) for p in prompts]
+    if cand_strings is None:
+        cand = np.array([candidate_ids(tokenizer, variant)] * len(prompts), dtype=np.int32).reshape(-1, 2)
+    else:
+        cache = {}
+        cand = np.zeros((len(prompts), 2), np.int32)
+        for i, (a, b) in enumerate(cand_strings):
+            if (a, b) not in cache:
+                cache[(a, b)] = candidate_ids(tokenizer, variant, a, b)
+            cand[i] = cache[(a, b)]
+    return ids, cand
+
+
 def score_prompts(scorer: Scorer, tokenizer, prompts: Sequence[str], variant: str = "100q",
                   cand_strings: Optional[Sequence[Tuple[str, str]]] = None,
-                  max_lookahead: int = MAX_LOOK_AHEAD) -> List[dict]:
+                  max_lookahead: int = MAX_LOOK_AHEAD, shard_group=None) -> List[dict]:
     """Batched replacement of the reference's per-prompt loop.  ``cand_strings`` optionally gives a
     (token_1, token_2) pair per prompt (the perturbation scenarios' ``target_tokens``); default is
-    (" Yes", " No")."""
+    (" Yes", " No").  With ``shard_group`` (a torch.distributed group, or True for the default group) every rank
+    scores its shard of the prompts and all ranks receive all rows (BASELINE config 4: sharded by prompt)."""
     V = VARIANTS[variant]
     try:
-        ids = [list(tokenizer(p).input_ids) for p in prompts]
-        if cand_strings is None:
-            cand = np.array([candidate_ids(tokenizer, variant)] * len(prompts), dtype=np.int32).reshape(-1, 2)
+        ids, cand = tokenize_prompts(tokenizer, prompts, variant, cand_strings)
+        if shard_group is not None:
+            from .dist import score_ids_sharded
+            rows, gens = score_ids_sharded(scorer, ids, cand, topk=V["topk"], max_lookahead=max_lookahead,
+                                           eos_id=tokenizer.eos_token_id, group=shard_group)
         else:
-            cache = {}
-            cand = np.zeros((len(prompts), 2), np.int32)
-            for i, (a, b) in enumerate(cand_strings):
-                if (a, b) not in cache:
-                    cache[(a, b)] = candidate_ids(tokenizer, variant, a, b)
-                cand[i] = cache[(a, b)]
-        rows, gens = scorer.score_ids(ids, cand, topk=V["topk"], max_lookahead=max_lookahead,
-                                      eos_id=tokenizer.eos_token_id)
+            rows, gens = scorer.score_ids(ids, cand, topk=V["topk"], max_lookahead=max_lookahead,
+                                          eos_id=tokenizer.eos_token_id)
     except Exception as e:   # reference error policy: NaN rows, sweep continues
         if variant != "100q":
             raise

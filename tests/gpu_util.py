@@ -28,6 +28,17 @@ def gemm_bf16(A, W, bias, epi, out=None):
     return out
 
 
+def gemm_f16(A, W, bias, epi, out=None):
+    """fp16 A x fp16 W (the FP16 mode's GEMM)."""
+    lib = _lib.load()
+    M, K = A.shape
+    N = W.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32 if epi in (2, 4) else torch.float16, device=A.device)
+    _lib.check(lib.b2s_gemm_f16(_lib.ptr(A), _lib.ptr(W), _lib.ptr(bias), _lib.ptr(out), M, N, K, epi, stream()), "gemm_f16")
+    return out
+
+
 def gemm_f32(A, W, bias, epi, out=None):
     lib = _lib.load()
     M, K = A.shape
@@ -51,7 +62,7 @@ def lm_head(hidden, W, cand):
 
 
 def make_scorer(shp, W, mode, **kw):
-    dt = torch.bfloat16 if mode == shapes.MODE_BF16_FAST else torch.float32
+    dt = torch.float32 if mode == shapes.MODE_FP32_CHECK else torch.bfloat16
     return Scorer(shp, weights.to_device(W, DEV, dt), mode=mode, device=DEV, **kw)
 
 

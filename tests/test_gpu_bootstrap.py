@@ -88,3 +88,62 @@ def test_bootstrap_properties_large_and_philox():
     assert abs(s["pct_lo"] - np.percentile(x, 2.5)) <= 1e-12 and abs(s["pct_hi"] - np.percentile(x, 97.5)) <= 1e-12
     assert abs(s["mean"] - x.mean()) <= 1e-12 and s["min"] == x.min() and s["max"] == x.max()
     assert abs(s["mean"] - vals.mean()) < 5 * vals.std() / np.sqrt(n) / np.sqrt(Bn) * 10
+
+
+def _ci_inputs():
+    import pandas as pd
+    from llm_interpretation_replication_b200.entrypoints import bootstrap_confidence_intervals as E4
+    fx = json.load(open(os.path.join(GOLDEN, "ci_fixture.json")))
+    mr = E4.build_model_responses(pd.read_csv(os.path.join(GOLDEN, "model_comparison_results.csv")))
+    return mr, fx["consolidated"]["matching_stats"]["matches"], fx["detailed"]["results"]["by_question"]
+
+
+def test_ci_simulation_matches_numpy_restatement():
+    """Row A11: per-seed means and the seed-42 per-sample correlations equal the NumPy/scipy restatement of
+    bootstrap_confidence_intervals.py (the reference script itself cannot run as shipped: parity unpinned)."""
+    from llm_interpretation_replication_b200 import bootstrap as B
+    from oracle import ci_oracle as O
+    mr, qm, bq = _ci_inputs()
+    tables = B.build_ci_tables(mr, qm, bq)
+    models = tables[0]
+    means, _, _ = B.simulate_individual_correlations(tables, 100, 0, 6)
+    ob, oi = O.bootstrap_means(mr, qm, bq, 6, 100)
+    assert np.allclose(means[:, 0].cpu().numpy(), ob, atol=1e-12, rtol=0)
+    assert np.allclose(means[:, 1].cpu().numpy(), oi, atol=1e-12, rtol=0)
+    _, corrs, _ = B.simulate_individual_correlations(tables, 40, 42, 1, want_corrs=True)
+    oc = O.calculate_individual_correlations(mr, qm, bq, 40, seed=42)
+    corrs = corrs.cpu().numpy()
+    for m, name in enumerate(models):
+        got = corrs[m][~np.isnan(corrs[m])]
+        want = np.array(oc.get(name, []))
+        assert len(got) == len(want), name
+        assert np.allclose(got, want, atol=1e-12, rtol=0), name
+
+
+def test_ci_stream_continues_into_per_model_bootstrap():
+    """np.random.choice after the loop continues the stream of the last seed (:211-230)."""
+    from llm_interpretation_replication_b200 import bootstrap as B
+    from oracle import ci_oracle as O
+    mr, qm, bq = _ci_inputs()
+    tables = B.build_ci_tables(mr, qm, bq)
+    _, _, stream = B.simulate_individual_correlations(tables, 100, 0, 3, want_state=True)
+    got = stream.choice(37, 500).cpu().numpy()
+    O.bootstrap_means(mr, qm, bq, 3, 100)               # leaves numpy's global stream after seed 2's run
+    want = np.random.choice(37, size=500, replace=True)
+    assert np.array_equal(got, want)
+
+
+def test_entry_point_4_schema(tmp_path):
+    import shutil
+    from llm_interpretation_replication_b200.entrypoints import bootstrap_confidence_intervals as E4
+    fx = json.load(open(os.path.join(GOLDEN, "ci_fixture.json")))
+    json.dump(fx["consolidated"], open(os.path.join(tmp_path, "consolidated_analysis_results.json"), "w"))
+    json.dump(fx["detailed"], open(os.path.join(tmp_path, "survey_analysis_detailed.json"), "w"))
+    shutil.copy(os.path.join(GOLDEN, "model_comparison_results.csv"), tmp_path)
+    res = E4.main(["--dir", str(tmp_path), "--n-bootstrap", "256"])
+    assert set(res) == {"methodology", "n_bootstrap", "overall_results", "per_model_results"}
+    o = res["overall_results"]
+    for k in ("base", "instruct", "difference"):
+        assert o[k]["ci_lower"] <= o[k]["mean"] + 0.05 and o[k]["ci_upper"] >= o[k]["mean"] - 0.05
+    assert len(res["per_model_results"]) >= 10          # models whose rel_probs are all finite
+    assert os.path.exists(os.path.join(tmp_path, "bootstrap_confidence_intervals.json"))

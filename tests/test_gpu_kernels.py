@@ -58,6 +58,26 @@ def test_gemm_tc_epilogues(epi, use_bias, cta_group):
     assert err <= tol, err
 
 
+@pytest.mark.parametrize("M,N,K,epi", [(300, 520, 192, 4), (513, 4672, 4544, 0), (391, 1160, 832, 1), (200, 264, 4544, 2)])
+def test_gemm_tc_fp16_operands(M, N, K, epi, cta_group):
+    """FP16 mode: both operands fp16 (tcgen05 kind::f16 with a_format = b_format = F16)."""
+    import gpu_util as U
+    A, W = _rand((M, K), 1.0, 21, torch.float16), _rand((N, K), 0.05, 22, torch.float16)
+    ref = A.float() @ W.float().T
+    if epi == 1:
+        ref = torch.nn.functional.gelu(ref)
+    if epi == 2:
+        resid = _rand((M, N), 1.0, 23, torch.float32)
+        out = U.gemm_f16(A, W, None, 2, out=resid.clone())
+        ref = ref + resid
+    else:
+        out = U.gemm_f16(A, W, None, epi).float()
+    torch.cuda.synchronize()
+    tol = 2e-3 if epi in (2, 4) else 2.0 ** -10      # fp16 output: one ulp relative
+    err = ((out - ref).abs() / (ref.abs() + 1.0)).max().item()
+    assert err <= tol, err
+
+
 def test_gemm_tc_rejects_bad_shapes():
     import gpu_util as U
     from llm_interpretation_replication_b200 import _lib

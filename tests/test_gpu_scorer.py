@@ -58,10 +58,11 @@ def test_scorer_fp32_check_vs_reference_golden(case_idx):
 
 
 @pytest.mark.parametrize("case_idx", [0, 1, 2])
-def test_scorer_bf16_vs_reference_golden(case_idx):
+@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+def test_scorer_bf16_vs_reference_golden(case_idx, mode_name):
     import gpu_util as U
     from llm_interpretation_replication_b200 import shapes
-    _run_case(U.golden_cases()[case_idx], shapes.MODE_BF16_FAST, TOL_BF16)
+    _run_case(U.golden_cases()[case_idx], getattr(shapes, mode_name), TOL_BF16)
 
 
 def test_scorer_edge_cases():
@@ -100,21 +101,45 @@ def test_scorer_edge_cases():
     sc.close()
 
 
-def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle():
+@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle(mode_name):
     """Falcon-7B widths (d=4544, 71 heads MQA, ffn 18176, V=65024; ragged GEMM tails) at 2 layers."""
     import gpu_util as U
     from llm_interpretation_replication_b200 import shapes, weights
     from oracle import decoder_ref
     shp = shapes.falcon_7b().with_layers(2)
     W = weights.init_weights(shp, seed=3)
-    sc = U.make_scorer(shp, W, shapes.MODE_BF16_FAST, max_tokens=2048, max_seqs=16, max_lookahead=2)
+    sc = U.make_scorer(shp, W, getattr(shapes, mode_name), max_tokens=2048, max_seqs=16, max_lookahead=2)
     g = np.random.RandomState(1)
     ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (66, 111, 190, 128, 97)]
     rows, gens = sc.score_ids(ids, np.array([[1000, 2000]]), topk=5, max_lookahead=2)
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=decoder_ref.bf16_round)
+        rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
         p = torch.softmax(lo, -1)
         rel = (p[1000] / (p[1000] + p[2000])).item()
         assert abs(rows[i][2] - rel) <= TOL_BF16, (i, rows[i][2], rel)
         assert abs(rows[i][3] - torch.logsumexp(lo, -1).item()) <= 5e-3
+    sc.close()
+
+
+@pytest.mark.parametrize("maker,lens", [("stablelm_alpha_7b", (18, 84, 40)), ("redpajama_3b", (74, 28, 111))])
+@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+def test_scorer_real_dims_neox_bf16(maker, lens, mode_name):
+    """GPT-NeoX shapes of BASELINE configs 1-2 at real widths (StableLM-alpha-7B: d 6144, 48 heads x 128, rotary 32,
+    parallel residual; RedPajama-3B: d 2560, 32 heads x 80, sequential residual; biases, untied head) at 2 layers."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights
+    from oracle import decoder_ref
+    shp = getattr(shapes, maker)().with_layers(2)
+    W = weights.init_weights(shp, seed=5)
+    sc = U.make_scorer(shp, W, getattr(shapes, mode_name), max_tokens=1024, max_seqs=8, max_lookahead=2)
+    g = np.random.RandomState(2)
+    ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in lens]
+    rows, gens = sc.score_ids(ids, np.array([[500, 600]]), topk=5, max_lookahead=2)
+    for i, x in enumerate(ids):
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=decoder_ref.bf16_round)
+        p = torch.softmax(lo, -1)
+        rel = (p[500] / (p[500] + p[600])).item()
+        assert abs(rows[i][2] - rel) <= TOL_BF16, (i, rows[i][2], rel)
     sc.close()
