@@ -324,9 +324,9 @@ def main():
                 "config": {"workload": "Falcon-7B (random-init) x 10,000 perturbation-shaped prompts, top-5 / 10-position look-ahead (BASELINE configs[2])",
                            "n_prompts": n_total, "total_prompt_tokens": int(L.sum()), "n_layer": shp.n_layer, "max_lookahead": LOOKAHEAD,
                            "topk": TOPK, "batch_tokens": args.batch_tokens, "gemm_cta_group": args.gemm_cta_group or 2, "batches_per_rank": len(batches), "parallelism": f"prompt-sharded x{world}, replicated weights",
-                           "l2": "inputs larger than L2: 13.8 GB of bf16 weights are re-read for every batch", "all_rel_prob_finite": finite},
+                           "l2": "inputs larger than L2: 13.8 GB of 16-bit weights are re-read for every batch", "all_rel_prob_finite": finite},
                 "clocks": clk, "gpu_launches": launches,
-                "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "roofline": {"bound": "tensor", "kernel": "gemm_tc2_kernel (tcgen05 cta_group::2)" if (args.gemm_cta_group or 2) == 2 else "gemm_tc_kernel (tcgen05)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                              "frac": achieved / peak if peak else None, "traffic": traffic, "peak_source": peak_src,
                              "launches": int(g_n.value), "gemm_ms_per_step": g_ms.value / args.steps,
                              "gemm_share_of_step": (g_ms.value / ms) if ms else None,

@@ -48,7 +48,7 @@ static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 
 // ---- epilogue codes (b200score.h) ---------------------------------------------------------------
-enum { EPI_STORE_BF16 = 0, EPI_GELU_BF16 = 1, EPI_RESID_F32 = 2, EPI_LMHEAD = 3, EPI_STORE_F32 = 4 };
+enum { EPI_STORE_BF16 = 0, EPI_GELU_BF16 = 1, EPI_RESID_F32 = 2, EPI_LMHEAD = 3, EPI_STORE_F32 = 4, EPI_QKV_ROPE = 5 };
 
 // LM-head partial record per (row, vocab tile): 8 floats
 //   [0] max  [1] sum exp(x-max)  [2..6] top-5 (desc)  [7] argmax column (int bits)
@@ -63,9 +63,19 @@ struct LmHeadArgs {
   float* cand_logits;       // [M,2]
 };
 
+// QKV projection fused with RoPE and the KV-cache append (EPI_QKV_ROPE): head_dim 64 = rotary_dim, query heads
+// first then key heads then value heads (Falcon layout).  Query heads are rotated and stored to `out`; key heads are
+// rotated and stored to the cache slot of their row; value heads are copied to the cache.
+struct RopeEpiArgs {
+  const int32_t *pos, *slot;     // [M]
+  const float *cos, *sin;        // [max_pos, 32]
+  void *kcache, *vcache;         // this layer: [slots, nkv*64] 16-bit
+  int nh, nkv;
+};
+
 // act_f16: A, W and the 16-bit outputs are fp16 instead of bf16 (tcgen05 kind::f16 needs both operands alike)
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K,
-                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0);
+                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0, const RopeEpiArgs* rope = nullptr);
 int gemm_f32_launch(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
                     int epilogue, cudaStream_t st);
 

@@ -37,6 +37,7 @@ struct GemmParams {
   void* out;             // bf16 or f32 [M,N]
   const float* bias;     // [N] or null
   LmHeadArgs lmh;
+  RopeEpiArgs rope;
 };
 
 __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
@@ -166,7 +167,59 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
     st.la = 0.f; st.lb = 0.f; st.has_a = false; st.has_b = false;
     if (row < p.M) { ca = p.lmh.cand_ids[2 * row]; cb = p.lmh.cand_ids[2 * row + 1]; }
   }
-  if constexpr (EPI == EPI_RESID_F32) {
+  if constexpr (EPI == EPI_QKV_ROPE) {
+    // one 64-wide head = two 32-column chunks (x1 | x2 of rotate_half); cos/sin of this row's position once per tile
+    float cs[32], sn[32];
+    int slot = 0;
+    if (row < p.M) {
+      const int pos = p.rope.pos[row];
+      slot = p.rope.slot[row];
+      const float4* c4 = reinterpret_cast<const float4*>(p.rope.cos + static_cast<size_t>(pos) * 32);
+      const float4* s4 = reinterpret_cast<const float4*>(p.rope.sin + static_cast<size_t>(pos) * 32);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 a = __ldg(c4 + j), b = __ldg(s4 + j);
+        cs[4 * j] = a.x; cs[4 * j + 1] = a.y; cs[4 * j + 2] = a.z; cs[4 * j + 3] = a.w;
+        sn[4 * j] = b.x; sn[4 * j + 1] = b.y; sn[4 * j + 2] = b.z; sn[4 * j + 3] = b.w;
+      }
+    }
+#pragma unroll 1
+    for (int hh = 0; hh < BN / 64; ++hh) {
+      const int col = nb * BN + hh * 64;
+      float x1[32], x2[32];
+      tmem_ld32(taddr + static_cast<uint32_t>(hh * 64), x1);
+      tmem_ld32(taddr + static_cast<uint32_t>(hh * 64 + 32), x2);
+      if (row >= p.M || col >= p.N) continue;          // whole heads only: N is a multiple of 64
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { x1[j] += __ldg(p.bias + col + j); x2[j] += __ldg(p.bias + col + 32 + j); }
+      }
+      const int head = col >> 6;
+      uint16_t* dst;
+      if (head < p.rope.nh) dst = reinterpret_cast<uint16_t*>(p.out) + static_cast<size_t>(row) * p.N + col;
+      else if (head < p.rope.nh + p.rope.nkv)
+        dst = reinterpret_cast<uint16_t*>(p.rope.kcache) + (static_cast<size_t>(slot) * p.rope.nkv + (head - p.rope.nh)) * 64;
+      else
+        dst = reinterpret_cast<uint16_t*>(p.rope.vcache) + (static_cast<size_t>(slot) * p.rope.nkv + (head - p.rope.nh - p.rope.nkv)) * 64;
+      if (head < p.rope.nh + p.rope.nkv) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float a = x1[j], b = x2[j];
+          x1[j] = a * cs[j] - b * sn[j];
+          x2[j] = b * cs[j] + a * sn[j];
+        }
+      }
+      uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        d4[q] = make_uint4(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.act_f16), pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.act_f16),
+                           pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.act_f16), pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.act_f16));
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        d4[4 + q] = make_uint4(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.act_f16), pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.act_f16),
+                               pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.act_f16), pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.act_f16));
+    }
+  } else if constexpr (EPI == EPI_RESID_F32) {
     // read-modify-write of the fp32 residual: the loads of chunk c+1 are in flight while chunk c is processed
     float rbuf[2][32];
     load_resid_chunk(p, row, nb * BN, rbuf[0]);
@@ -578,7 +631,7 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
 }
 
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
-                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16) {
+                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope) {
   B2S_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
   B2S_REQUIRE(K % 8 == 0, "gemm_bf16: K=%d must be a multiple of 8 (16-byte TMA row pitch)", K);
   B2S_REQUIRE(epilogue == EPI_LMHEAD || N % 8 == 0, "gemm_bf16: N=%d must be a multiple of 8", N);
@@ -611,11 +664,17 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
+  p.rope = rope ? *rope : RopeEpiArgs{};
   switch (epilogue) {
     case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, p, st);
     case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, p, st);
     case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, p, st);
     case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, p, st);
+    case EPI_QKV_ROPE:
+      B2S_REQUIRE(rope && rope->pos && rope->slot && rope->cos && rope->sin && rope->kcache && rope->vcache,
+                  "gemm_bf16: the QKV+RoPE epilogue needs its buffers");
+      B2S_REQUIRE(N == (rope->nh + 2 * rope->nkv) * 64, "gemm_bf16: QKV+RoPE epilogue expects N = (nh + 2 nkv) * 64");
+      return launch_epi<EPI_QKV_ROPE>(ta, tb, tb2, p, st);
     case EPI_LMHEAD:
       B2S_REQUIRE(lmh && lmh->partials && lmh->cand_ids && lmh->cand_logits, "gemm_bf16: LM-head epilogue needs its buffers");
       return launch_epi<EPI_LMHEAD>(ta, tb, tb2, p, st);

@@ -133,18 +133,30 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     }
     B2S_TRY((launch_ln<AT, WT>(ln, rows, st)));
 
-    B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
-                   EPI_STORE_BF16, st));
     uint8_t* kc = reinterpret_cast<uint8_t*>(w.kcache) + w.cache_layer_bytes * l;
     uint8_t* vc = reinterpret_cast<uint8_t*>(w.vcache) + w.cache_layer_bytes * l;
-    RopeArgs ro{};
-    ro.qkv = w.qkv; ro.kcache = kc; ro.vcache = vc; ro.pos = w.meta.pos; ro.slot = w.meta.slot;
-    ro.cos = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_COS));
-    ro.sin = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_SIN));
-    ro.qkv_dim = m->qkv_dim; ro.nh = d.n_head; ro.nkv = d.n_kv_head; ro.hd = d.head_dim; ro.rd = d.rotary_dim;
-    ro.q_base = m->q_base; ro.q_hstride = m->q_hstride; ro.k_base = m->k_base; ro.v_base = m->v_base;
-    ro.kv_hstride = m->kv_hstride;
-    B2S_TRY(launch_rope_cache<AT>(ro, rows, st));
+    // Falcon layout with 64-wide fully rotated heads: RoPE and the cache append ride in the QKV GEMM epilogue
+    const bool fused_rope = m->bf16 && d.qkv_layout == B2S_QKV_FALCON_MQA && d.head_dim == 64 && d.rotary_dim == 64;
+    if (fused_rope) {
+      RopeEpiArgs re{};
+      re.pos = w.meta.pos; re.slot = w.meta.slot;
+      re.cos = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_COS));
+      re.sin = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_SIN));
+      re.kcache = kc; re.vcache = vc; re.nh = d.n_head; re.nkv = d.n_kv_head;
+      B2S_TRY(gemm_tc_launch(w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
+                             EPI_QKV_ROPE, nullptr, st, m->act_f16, &re));
+    } else {
+      B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
+                     EPI_STORE_BF16, st));
+      RopeArgs ro{};
+      ro.qkv = w.qkv; ro.kcache = kc; ro.vcache = vc; ro.pos = w.meta.pos; ro.slot = w.meta.slot;
+      ro.cos = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_COS));
+      ro.sin = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_SIN));
+      ro.qkv_dim = m->qkv_dim; ro.nh = d.n_head; ro.nkv = d.n_kv_head; ro.hd = d.head_dim; ro.rd = d.rotary_dim;
+      ro.q_base = m->q_base; ro.q_hstride = m->q_hstride; ro.k_base = m->k_base; ro.v_base = m->v_base;
+      ro.kv_hstride = m->kv_hstride;
+      B2S_TRY(launch_rope_cache<AT>(ro, rows, st));
+    }
 
     AttnArgs at{};
     at.qkv = w.qkv; at.kcache = kc; at.vcache = vc; at.out = w.attn; at.meta = w.meta;

@@ -56,7 +56,7 @@ def model_seed(model_name: str) -> int:
     return zlib.crc32(model_name.encode()) & 0x7FFFFFFF
 
 
-def load_model(model_name: str, device=None, mode=shapes.MODE_BF16_FAST, n_layer: int = 0, max_tokens: int = 65536,
+def load_model(model_name: str, device=None, mode=shapes.MODE_FP16, n_layer: int = 0, max_tokens: int = 65536,
                max_seqs: int = 1024):
     """Stand-in for AutoTokenizer/AutoModelForCausalLM.from_pretrained (reference :416-450): the shape of the
     named hub model with random-init weights (seeded by the name) and the offline tokenizer.  Raises KeyError for
@@ -71,7 +71,7 @@ def load_model(model_name: str, device=None, mode=shapes.MODE_BF16_FAST, n_layer
     if n_layer:
         shp = shp.with_layers(n_layer)
     device = torch.device(device if device is not None else "cuda:0")
-    dt = torch.bfloat16 if mode == shapes.MODE_BF16_FAST else torch.float32
+    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
     W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
     scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs)
     tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
