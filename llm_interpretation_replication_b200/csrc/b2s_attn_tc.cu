@@ -206,23 +206,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       const uint32_t ph = static_cast<uint32_t>((i / nl) & 1);
       mbar_wait(bar_s(l), ph);
       tcgen05_fence_after();
-      // pass 1: row maximum over the visible keys
-      float m = -INFINITY;
-      for (int c = 0; c < nchunks; ++c) {
-        if (c * 32 > warp_limit) break;                 // warp-uniform
-        float v[32];
-        tmem_ld32(t_s + static_cast<uint32_t>(c * 32), v);
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
-      }
-      const float ms = m * p.scale_log2e;
-      // pass 2: p = 2^(s*scale*log2e - max), rounded to bf16, written to the swizzled A-operand tile
       float lsum = 0.f;
-      for (int c = 0; c < nchunks; ++c) {
-        const bool live = c * 32 <= warp_limit;         // warp-uniform
-        float v[32];
-        if (live) tmem_ld32(t_s + static_cast<uint32_t>(c * 32), v);
+      // p = 2^(s*scale*log2e - max) for 32 keys, rounded to the 16-bit format and written to the swizzled A tile
+      auto emit_chunk = [&](int c, const float (&v)[32], bool live, float ms) {
         uint32_t pk[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
@@ -248,6 +234,56 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int q = 0; q < 4; ++q) {
           const int chunk = (cbase + q) ^ (row & 7);
           *reinterpret_cast<uint4*>(prow + chunk * 16) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        }
+      };
+      if (nchunks <= 4) {
+        // <= 128 keys (most tiles): S is read from TMEM ONCE and kept in registers between the max and the exp pass
+        // (TMEM reads, not the math, bound this kernel)
+        float v0[32], v1[32], v2[32], v3[32];
+        const bool l0 = true, l1 = nchunks > 1 && 32 <= warp_limit, l2 = nchunks > 2 && 64 <= warp_limit,
+                   l3 = nchunks > 3 && 96 <= warp_limit;        // warp-uniform
+        float m = -INFINITY;
+        tmem_ld32(t_s, v0);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j <= limit) m = fmaxf(m, v0[j]);
+        if (l1) {
+          tmem_ld32(t_s + 32u, v1);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (32 + j <= limit) m = fmaxf(m, v1[j]);
+        }
+        if (l2) {
+          tmem_ld32(t_s + 64u, v2);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (64 + j <= limit) m = fmaxf(m, v2[j]);
+        }
+        if (l3) {
+          tmem_ld32(t_s + 96u, v3);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (96 + j <= limit) m = fmaxf(m, v3[j]);
+        }
+        const float ms = m * p.scale_log2e;
+        emit_chunk(0, v0, l0, ms);
+        if (nchunks > 1) emit_chunk(1, v1, l1, ms);
+        if (nchunks > 2) emit_chunk(2, v2, l2, ms);
+        if (nchunks > 3) emit_chunk(3, v3, l3, ms);
+      } else {
+        // pass 1: row maximum over the visible keys
+        float m = -INFINITY;
+        for (int c = 0; c < nchunks; ++c) {
+          if (c * 32 > warp_limit) break;                 // warp-uniform
+          float v[32];
+          tmem_ld32(t_s + static_cast<uint32_t>(c * 32), v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
+        }
+        const float ms = m * p.scale_log2e;
+        // pass 2: re-read S chunk by chunk
+        for (int c = 0; c < nchunks; ++c) {
+          const bool live = c * 32 <= warp_limit;         // warp-uniform
+          float v[32];
+          if (live) tmem_ld32(t_s + static_cast<uint32_t>(c * 32), v);
+          emit_chunk(c, v, live, ms);
         }
       }
       // make the generic-proxy smem writes visible to the tensor core (async proxy), then signal

@@ -20,6 +20,7 @@
 namespace b2s {
 
 static constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
+static constexpr unsigned long long HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull;
 static constexpr int STAGES = 4;
 static constexpr int GROUP_M = 16;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
@@ -33,12 +34,22 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
+  unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
   void* out;             // bf16 or f32 [M,N]
   const float* bias;     // [N] or null
   LmHeadArgs lmh;
   RopeEpiArgs rope;
 };
+
+__device__ __forceinline__ void tma_load_2d_h(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1,
+                                              unsigned long long hint) {
+  if (hint == 0) { tma_load_2d(smem_dst, map, bar, c0, c1); return; }
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(hint)
+      : "memory");
+}
 
 __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
   const int per_group = group_m * tiles_n;
@@ -169,19 +180,13 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
   }
   if constexpr (EPI == EPI_QKV_ROPE) {
     // one 64-wide head = two 32-column chunks (x1 | x2 of rotate_half); cos/sin of this row's position once per tile
-    float cs[32], sn[32];
     int slot = 0;
+    const float4 *c4 = nullptr, *s4 = nullptr;       // cos/sin rows of this token's position (L1/L2 resident tables)
     if (row < p.M) {
       const int pos = p.rope.pos[row];
       slot = p.rope.slot[row];
-      const float4* c4 = reinterpret_cast<const float4*>(p.rope.cos + static_cast<size_t>(pos) * 32);
-      const float4* s4 = reinterpret_cast<const float4*>(p.rope.sin + static_cast<size_t>(pos) * 32);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float4 a = __ldg(c4 + j), b = __ldg(s4 + j);
-        cs[4 * j] = a.x; cs[4 * j + 1] = a.y; cs[4 * j + 2] = a.z; cs[4 * j + 3] = a.w;
-        sn[4 * j] = b.x; sn[4 * j + 1] = b.y; sn[4 * j + 2] = b.z; sn[4 * j + 3] = b.w;
-      }
+      c4 = reinterpret_cast<const float4*>(p.rope.cos + static_cast<size_t>(pos) * 32);
+      s4 = reinterpret_cast<const float4*>(p.rope.sin + static_cast<size_t>(pos) * 32);
     }
 #pragma unroll 1
     for (int hh = 0; hh < BN / 64; ++hh) {
@@ -203,10 +208,15 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
         dst = reinterpret_cast<uint16_t*>(p.rope.vcache) + (static_cast<size_t>(slot) * p.rope.nkv + (head - p.rope.nh - p.rope.nkv)) * 64;
       if (head < p.rope.nh + p.rope.nkv) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float a = x1[j], b = x2[j];
-          x1[j] = a * cs[j] - b * sn[j];
-          x2[j] = b * cs[j] + a * sn[j];
+        for (int j = 0; j < 8; ++j) {
+          const float4 c = __ldg(c4 + j), sn = __ldg(s4 + j);
+          const float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float a = x1[4 * j + u], b = x2[4 * j + u];
+            x1[4 * j + u] = a * cc[u] - b * ss[u];
+            x2[4 * j + u] = b * cc[u] + a * ss[u];
+          }
         }
       }
       uint4* d4 = reinterpret_cast<uint4*>(dst);
@@ -304,8 +314,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           const uint32_t sb = sa + A_STAGE_BYTES;
           mbar_arrive_expect_tx(full_bar(stage), STAGE_BYTES);
-          tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, mb * BM);
-          tma_load_2d(sb, &tmB, full_bar(stage), kb * BK, nb * BN);
+          tma_load_2d_h(sa, &tmA, full_bar(stage), kb * BK, mb * BM, p.hint_a);
+          tma_load_2d_h(sb, &tmB, full_bar(stage), kb * BK, nb * BN, p.hint_b);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -352,7 +362,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t acc_phase = (it >> 1) & 1u;
       const int row = mb * BM + quad * 32 + lane;
       if constexpr (EPI == EPI_RESID_F32) prefetch_resid_tile(p, row, nb);
-      mbar_wait(tfull_bar(acc), acc_phase);
+      mbar_wait_warp(tfull_bar(acc), acc_phase, lane);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc));
@@ -382,7 +392,15 @@ static constexpr int STAGE2_BYTES = 2 * A_STAGE_BYTES;   // 16 KB A + 16 KB W
 static constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 256;
 static constexpr int BM2 = 256;
 
-__device__ __forceinline__ void tma_load_2d_cg2(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1) {
+__device__ __forceinline__ void tma_load_2d_cg2(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1,
+                                                unsigned long long hint) {
+  if (hint != 0) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(hint)
+        : "memory");
+    return;
+  }
   asm volatile(
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
@@ -468,8 +486,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t sb = sa + A_STAGE_BYTES;
           const uint32_t fb = full_bar(stage) & PEER_MASK;
           if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
-          tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM2 + static_cast<int>(rank) * BM);
-          tma_load_2d_cg2(sb, &tmB, fb, kb * BK, nb * BN + static_cast<int>(rank) * (BN / 2));
+          tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM2 + static_cast<int>(rank) * BM, p.hint_a);
+          tma_load_2d_cg2(sb, &tmB, fb, kb * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
           if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
         }
       }
@@ -513,7 +531,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint32_t acc_phase = (it >> 1) & 1u;
       const int row = mb * BM2 + static_cast<int>(rank) * BM + quad * 32 + lane;
       if constexpr (EPI == EPI_RESID_F32) prefetch_resid_tile(p, row, nb);
-      mbar_wait(tfull_bar(acc), acc_phase);
+      mbar_wait_warp(tfull_bar(acc), acc_phase, lane);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc) & PEER_MASK);
@@ -522,6 +540,145 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
   tcgen05_fence_before();
   cluster_sync_all();          // neither CTA may exit (or free TMEM) while its peer can still signal it
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Big-tile CTA-pair kernel: the pair computes a 512 x 256 tile, each CTA 256 rows as two 128-row accumulators that
+// fill all 512 TMEM columns.  Per k-block a CTA stages 256 rows of A (32 KB) and its 128 rows of W (16 KB) and the
+// leader issues two M=256 MMAs (upper and lower row halves) against the same W stage, so 25 % fewer bytes cross
+// L2 -> SM per FLOP than with 256 x 256 tiles and the W boxes are read half as often.  There is no second
+// accumulator set: the epilogue (8 warps, 4 per accumulator) is exposed between tiles, which costs a few percent of
+// tensor time but draws less power -- under the 1 kW cap that is the better trade (profiles/r1_gemm_power.md).
+// ---------------------------------------------------------------------------------------------
+static constexpr int STAGES3 = 4;
+static constexpr int A3_STAGE_BYTES = 2 * A_STAGE_BYTES;            // 256 x 64 bf16
+static constexpr int STAGE3_BYTES = A3_STAGE_BYTES + A_STAGE_BYTES; // + 128 x 64 of W
+static constexpr int SMEM3_BYTES = STAGES3 * STAGE3_BYTES + 1024 + 256;
+static constexpr int BM3 = 512;
+static constexpr int NUM_THREADS3 = 320;   // producer, MMA, 8 epilogue warps
+
+__device__ __forceinline__ void tile_coords3(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
+  const int GM = max(1, group_m / 4);    // groups of group_m x 128 rows = GM x 512 rows
+  const int per_group = GM * tiles_n;
+  const int g = tile / per_group;
+  const int first_m = g * GM;
+  const int gm = min(GM, tiles_m - first_m);
+  const int within = tile - g * per_group;
+  mb = first_m + within % gm;
+  nb = within / gm;
+}
+
+template <int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS3, 1)
+gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = smem_base + STAGES3 * STAGE3_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES3 + s); };
+  const uint32_t tfull_bar = bars + 8u * (2 * STAGES3);
+  const uint32_t tempty_bar = bars + 8u * (2 * STAGES3 + 1);
+  const uint32_t tmem_slot = bars + 8u * (2 * STAGES3 + 2);
+  constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;
+
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const bool leader = rank == 0;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_m3 = (p.M + BM3 - 1) / BM3;
+  const int num_tiles = tiles_m3 * p.tiles_n;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    for (int s = 0; s < STAGES3; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tfull_bar, 1);
+    mbar_init(tempty_bar, 16);     // 8 epilogue warps in each CTA of the pair
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int mb, nb;
+        tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, mb, nb);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * STAGE3_BYTES;
+          const uint32_t sb = sa + A3_STAGE_BYTES;
+          const uint32_t fb = full_bar(stage) & PEER_MASK;
+          if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE3_BYTES);
+          tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM3 + static_cast<int>(rank) * 256, p.hint_a);
+          tma_load_2d_cg2(sb, &tmB, fb, kb * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
+          if (++stage == STAGES3) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(256, BN) & ~(p.act_f16 ? ((7u << 7) | (7u << 10)) : 0u);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
+        mbar_wait(tempty_bar, (static_cast<uint32_t>(it) & 1u) ^ 1u);   // both accumulators drained by all 16 warps
+        tcgen05_fence_after();
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + stage * STAGE3_BYTES;
+          const uint64_t adesc0 = make_kmajor_sw128_desc(sa);
+          const uint64_t adesc1 = make_kmajor_sw128_desc(sa + A_STAGE_BYTES);      // rows 128..255 of this CTA's A box
+          const uint64_t bdesc = make_kmajor_sw128_desc(sa + A3_STAGE_BYTES);
+          const uint32_t accf = kb != 0 ? 1u : 0u;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            tcgen05_mma_bf16_cg2(tmem_base, adesc0 + 2u * k, bdesc + 2u * k, idesc, (accf | k) != 0 ? 1u : 0u);
+            tcgen05_mma_bf16_cg2(tmem_base + static_cast<uint32_t>(BN), adesc1 + 2u * k, bdesc + 2u * k, idesc,
+                                 (accf | k) != 0 ? 1u : 0u);
+          }
+          tcgen05_commit_cg2_mc(empty_bar(stage));
+          if (++stage == STAGES3) { stage = 0; phase ^= 1u; }
+        }
+        tcgen05_commit_cg2_mc(tfull_bar);
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..9: warps 2-5 drain accumulator 0, warps 6-9 accumulator 1 =====================
+    const int quad = warp & 3;
+    const int acc = (warp - 2) >> 2;
+    int it = 0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
+      int mb, nb;
+      tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, mb, nb);
+      const int row = mb * BM3 + static_cast<int>(rank) * 256 + acc * BM + quad * 32 + lane;
+      if constexpr (EPI == EPI_RESID_F32) prefetch_resid_tile(p, row, nb);
+      mbar_wait_warp(tfull_bar, static_cast<uint32_t>(it) & 1u, lane);
+      tcgen05_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar & PEER_MASK);
+    }
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();
   if (warp == 1) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
@@ -578,6 +735,7 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
 }
 
 static int g_num_sms = 0;
+int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
 int g_opt_cta_group = 2;   // 2: CTA pairs on 256x256 tiles (default, ~5-15% faster); 1: one CTA per 128x256 tile (b2s_set_option "gemm_cta_group")
 
@@ -600,7 +758,8 @@ static cudaEvent_t prof_event() {
 }
 
 template <int EPI>
-static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb2, const GemmParams& p, cudaStream_t st) {
+static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb2, const CUtensorMap& ta3,
+                      const GemmParams& p, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
@@ -609,7 +768,19 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
   if (g_prof.on) cudaEventRecord(prof_event(), st);
-  if (g_opt_cta_group == 2) {
+  // big tiles pay when there are enough 512-row blocks; short batches (one-token steps, LM head) keep 256-row tiles
+  const bool big = (g_opt_cta_group == 3 && p.M >= 4096) || g_opt_cta_group == 4;   // 4 = always (tests)
+  if (big) {
+    static bool attr3_set = false;
+    if (!attr3_set) {
+      B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc3_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3_BYTES));
+      attr3_set = true;
+    }
+    const int tiles3 = static_cast<int>(ceil_div(p.M, BM3)) * p.tiles_n;
+    int pairs = g_num_sms / 2;
+    if (tiles3 < pairs) pairs = tiles3;
+    gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, p);
+  } else if (g_opt_cta_group >= 2) {
     static bool attr2_set = false;
     if (!attr2_set) {
       B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
@@ -643,9 +814,10 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     B2S_CHECK_CUDA(cudaGetDevice(&dev));
     B2S_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
-  CUtensorMap ta, tb, tb2;
+  CUtensorMap ta, tb, tb2, ta3;
   B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM, act_f16));
   B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN, act_f16));
+  B2S_TRY(make_tmap_bf16(&ta3, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), 256, act_f16));   // big-tile kernel: 256-row A boxes
   B2S_TRY(make_tmap_bf16(&tb2, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN / 2, act_f16));   // per-CTA half of a W box
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
@@ -663,21 +835,23 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   }
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
+  p.hint_a = g_opt_hint == 1 ? HINT_EVICT_FIRST : (g_opt_hint >= 2 ? HINT_EVICT_LAST : 0ull);
+  p.hint_b = g_opt_hint == 2 ? HINT_EVICT_FIRST : (g_opt_hint == 1 || g_opt_hint == 3 ? HINT_EVICT_LAST : 0ull);
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
   p.rope = rope ? *rope : RopeEpiArgs{};
   switch (epilogue) {
-    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, p, st);
-    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, p, st);
-    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, p, st);
-    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, p, st);
+    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, ta3, p, st);
+    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, ta3, p, st);
+    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, ta3, p, st);
+    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, ta3, p, st);
     case EPI_QKV_ROPE:
       B2S_REQUIRE(rope && rope->pos && rope->slot && rope->cos && rope->sin && rope->kcache && rope->vcache,
                   "gemm_bf16: the QKV+RoPE epilogue needs its buffers");
       B2S_REQUIRE(N == (rope->nh + 2 * rope->nkv) * 64, "gemm_bf16: QKV+RoPE epilogue expects N = (nh + 2 nkv) * 64");
-      return launch_epi<EPI_QKV_ROPE>(ta, tb, tb2, p, st);
+      return launch_epi<EPI_QKV_ROPE>(ta, tb, tb2, ta3, p, st);
     case EPI_LMHEAD:
       B2S_REQUIRE(lmh && lmh->partials && lmh->cand_ids && lmh->cand_logits, "gemm_bf16: LM-head epilogue needs its buffers");
-      return launch_epi<EPI_LMHEAD>(ta, tb, tb2, p, st);
+      return launch_epi<EPI_LMHEAD>(ta, tb, tb2, ta3, p, st);
     default:
       set_error("gemm_bf16: unknown epilogue %d", epilogue);
       return B2S_EINVAL;
@@ -691,8 +865,13 @@ extern "C" {
 int b2s_set_option(const char* name, int32_t value) {
   B2S_REQUIRE(name != nullptr, "set_option: null name");
   if (std::string(name) == "gemm_cta_group") {
-    B2S_REQUIRE(value == 1 || value == 2, "set_option: gemm_cta_group must be 1 or 2");
+    B2S_REQUIRE(value >= 1 && value <= 4, "set_option: gemm_cta_group must be 1..4");
     b2s::g_opt_cta_group = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_l2_hint") {
+    B2S_REQUIRE(value >= 0 && value <= 3, "set_option: gemm_l2_hint must be in [0, 3]");
+    b2s::g_opt_hint = value;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_group_m") {

@@ -6,9 +6,10 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=[1, 2], ids=["cta1", "cta_pair"])
+@pytest.fixture(params=[1, 2, 4], ids=["cta1", "cta_pair", "cta_pair_big"])
 def cta_group(request):
-    """Run the tensor-core GEMM tests on both tilings: one CTA per 128x256 tile and CTA pairs (cta_group::2)."""
+    """Run the tensor-core GEMM tests on every tiling: one CTA per 128x256 tile, CTA pairs (cta_group::2) on 256x256
+    tiles, and CTA pairs on 512x256 tiles (4 = forced also for small M)."""
     from llm_interpretation_replication_b200 import _lib
     lib = _lib.load()
     _lib.check(lib.b2s_set_option(b"gemm_cta_group", request.param), "set_option")
