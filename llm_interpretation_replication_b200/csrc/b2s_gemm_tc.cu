@@ -26,7 +26,8 @@ static constexpr int GROUP_M = 16;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
 static constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KB
 static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+static constexpr int EPI_STAGE_BYTES = 4096;   // per epilogue warp: 32 rows x 128 B, 128B-swizzled
+static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 1024 /*barriers*/ + 4 * EPI_STAGE_BYTES;
 static constexpr int NUM_THREADS = 192;
 static constexpr uint32_t TMEM_COLS = 512;
 
@@ -35,6 +36,7 @@ struct GemmParams {
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
+  int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
   void* out;             // bf16 or f32 [M,N]
   const float* bias;     // [N] or null
@@ -266,11 +268,136 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
 }
 
 // ---------------------------------------------------------------------------------------------
+// Epilogue through shared memory + TMA (default): the warp's 32 x 64 (16-bit) or 32 x 32 (fp32) sub-tile is written
+// to a 4 KB 128B-swizzled staging buffer and leaves as ONE bulk tensor store -- or, for the fp32 residual, one bulk
+// tensor reduce-add, so the residual is never read back by the SM.  Stores are fully coalesced, need no bounds
+// checks (the TMA unit clips at the tensor edge) and cost the LSU nothing.
+//   row0  first row of this warp's 32-row slab;  stage  shared address of the warp's staging buffer
+// ---------------------------------------------------------------------------------------------
+template <int EPI>
+__device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUtensorMap* tmC, int row0, int nb,
+                                                  uint32_t taddr, int lane, uint32_t release_bar, uint32_t stage) {
+  const int row = row0 + lane;
+  const uint32_t my_line = stage + static_cast<uint32_t>(lane) * 128u;
+  const uint32_t sw = static_cast<uint32_t>(lane & 7);
+  if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE_F32) {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int col0 = nb * BN + c * 32;
+      if (col0 >= p.N) break;
+      float v[32];
+      tmem_ld32(taddr + static_cast<uint32_t>(c * 32), v);
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
+      }
+      if (lane == 0) tma_store_wait_read();        // the previous bulk store has finished reading the buffer
+      __syncwarp();
+#pragma unroll
+      for (uint32_t q = 0; q < 8; ++q)
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + ((q ^ sw) << 4)), "f"(v[4 * q]), "f"(v[4 * q + 1]),
+                     "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (EPI == EPI_RESID_F32) tma_reduce_add_2d(tmC, stage, col0, row0);
+        else tma_store_2d(tmC, stage, col0, row0);
+        tma_store_commit();
+      }
+    }
+  } else {
+    // 16-bit outputs: 64 columns (two TMEM chunks) per bulk store
+    int slot = 0;
+    const float4 *c4 = nullptr, *s4 = nullptr;
+    if constexpr (EPI == EPI_QKV_ROPE) {
+      if (row < p.M) {
+        const int pos = p.rope.pos[row];
+        slot = p.rope.slot[row];
+        c4 = reinterpret_cast<const float4*>(p.rope.cos + static_cast<size_t>(pos) * 32);
+        s4 = reinterpret_cast<const float4*>(p.rope.sin + static_cast<size_t>(pos) * 32);
+      }
+    }
+#pragma unroll 1
+    for (int g = 0; g < BN / 64; ++g) {
+      const int col0 = nb * BN + g * 64;
+      if (col0 >= p.N) break;
+      float x1[32], x2[32];
+      tmem_ld32(taddr + static_cast<uint32_t>(g * 64), x1);
+      tmem_ld32(taddr + static_cast<uint32_t>(g * 64 + 32), x2);
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (col0 + j < p.N) x1[j] += __ldg(p.bias + col0 + j);
+          if (col0 + 32 + j < p.N) x2[j] += __ldg(p.bias + col0 + 32 + j);
+        }
+      }
+      if constexpr (EPI == EPI_GELU_BF16) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { x1[j] = gelu_erf(x1[j]); x2[j] = gelu_erf(x2[j]); }
+      }
+      bool to_cache = false;
+      if constexpr (EPI == EPI_QKV_ROPE) {
+        const int head = col0 >> 6;
+        if (head < p.rope.nh + p.rope.nkv && row < p.M) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 c = __ldg(c4 + j), sn = __ldg(s4 + j);
+            const float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {sn.x, sn.y, sn.z, sn.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const float a = x1[4 * j + u], b = x2[4 * j + u];
+              x1[4 * j + u] = a * cc[u] - b * ss[u];
+              x2[4 * j + u] = b * cc[u] + a * ss[u];
+            }
+          }
+        }
+        if (head >= p.rope.nh) {   // key / value head: straight into this row's cache slot (rows map to arbitrary slots)
+          to_cache = true;
+          if (row < p.M) {
+            uint16_t* dst = head < p.rope.nh + p.rope.nkv
+                ? reinterpret_cast<uint16_t*>(p.rope.kcache) + (static_cast<size_t>(slot) * p.rope.nkv + (head - p.rope.nh)) * 64
+                : reinterpret_cast<uint16_t*>(p.rope.vcache) + (static_cast<size_t>(slot) * p.rope.nkv + (head - p.rope.nh - p.rope.nkv)) * 64;
+            uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              d4[q] = make_uint4(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.act_f16), pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.act_f16),
+                                 pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.act_f16), pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.act_f16));
+              d4[4 + q] = make_uint4(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.act_f16), pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.act_f16),
+                                     pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.act_f16), pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.act_f16));
+            }
+          }
+        }
+      }
+      if (to_cache) continue;
+      if (lane == 0) tma_store_wait_read();
+      __syncwarp();
+#pragma unroll
+      for (uint32_t q = 0; q < 4; ++q) {
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + ((q ^ sw) << 4)),
+                     "r"(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.act_f16)), "r"(pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.act_f16)),
+                     "r"(pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.act_f16)), "r"(pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.act_f16)) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + (((q + 4) ^ sw) << 4)),
+                     "r"(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.act_f16)), "r"(pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.act_f16)),
+                     "r"(pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.act_f16)), "r"(pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.act_f16)) : "memory");
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) { tma_store_2d(tmC, stage, col0, row0); tma_store_commit(); }
+    }
+  }
+  // all TMEM reads of this accumulator are done: hand it back to the MMA warp
+  tcgen05_fence_before();
+  __syncwarp();
+  if (lane == 0) asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(release_bar) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
 // Kernel
 // ---------------------------------------------------------------------------------------------
 template <int EPI>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = smem_base + STAGES * STAGE_BYTES;
@@ -365,8 +492,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait_warp(tfull_bar(acc), acc_phase, lane);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      if constexpr (EPI != EPI_LMHEAD) {
+        if (p.tma_store) {
+          epilogue_tile_tma<EPI>(p, &tmC, mb * BM + quad * 32, nb, taddr, lane, tempty_bar(acc),
+                                 bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES));
+          continue;
+        }
+      }
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc));
     }
+    if (p.tma_store && lane == 0) tma_store_wait_all();   // bulk stores must have left shared memory before the CTA exits
   }
 
   tcgen05_fence_before();
@@ -389,7 +524,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // ---------------------------------------------------------------------------------------------
 static constexpr int STAGES2 = 6;
 static constexpr int STAGE2_BYTES = 2 * A_STAGE_BYTES;   // 16 KB A + 16 KB W
-static constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 256;
+static constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 1024 + 4 * EPI_STAGE_BYTES;
 static constexpr int BM2 = 256;
 
 __device__ __forceinline__ void tma_load_2d_cg2(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1,
@@ -436,7 +571,8 @@ __device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n,
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = smem_base + STAGES2 * STAGE2_BYTES;
@@ -534,8 +670,16 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_wait_warp(tfull_bar(acc), acc_phase, lane);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      if constexpr (EPI != EPI_LMHEAD) {
+        if (p.tma_store) {
+          epilogue_tile_tma<EPI>(p, &tmC, mb * BM2 + static_cast<int>(rank) * BM + quad * 32, nb, taddr, lane,
+                                 tempty_bar(acc) & PEER_MASK, bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES));
+          continue;
+        }
+      }
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar(acc) & PEER_MASK);
     }
+    if (p.tma_store && lane == 0) tma_store_wait_all();   // bulk stores must have left shared memory before the CTA exits
   }
 
   tcgen05_fence_before();
@@ -557,7 +701,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 static constexpr int STAGES3 = 4;
 static constexpr int A3_STAGE_BYTES = 2 * A_STAGE_BYTES;            // 256 x 64 bf16
 static constexpr int STAGE3_BYTES = A3_STAGE_BYTES + A_STAGE_BYTES; // + 128 x 64 of W
-static constexpr int SMEM3_BYTES = STAGES3 * STAGE3_BYTES + 1024 + 256;
+static constexpr int SMEM3_BYTES = STAGES3 * STAGE3_BYTES + 1024 + 1024 + 8 * EPI_STAGE_BYTES;
 static constexpr int BM3 = 512;
 static constexpr int NUM_THREADS3 = 320;   // producer, MMA, 8 epilogue warps
 
@@ -574,7 +718,8 @@ __device__ __forceinline__ void tile_coords3(int tile, int tiles_m, int tiles_n,
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS3, 1)
-gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = smem_base + STAGES3 * STAGE3_BYTES;
@@ -673,8 +818,16 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_wait_warp(tfull_bar, static_cast<uint32_t>(it) & 1u, lane);
       tcgen05_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      if constexpr (EPI != EPI_LMHEAD) {
+        if (p.tma_store) {
+          epilogue_tile_tma<EPI>(p, &tmC, mb * BM3 + static_cast<int>(rank) * 256 + acc * BM + quad * 32, nb, taddr, lane,
+                                 tempty_bar & PEER_MASK, bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES));
+          continue;
+        }
+      }
       epilogue_tile<EPI>(p, row, nb, taddr, lane, tempty_bar & PEER_MASK);
     }
+    if (p.tma_store && lane == 0) tma_store_wait_all();   // bulk stores must have left shared memory before the CTA exits
   }
 
   tcgen05_fence_before();
@@ -710,16 +863,17 @@ static int get_encode_fn() {
   return B2S_OK;
 }
 
-int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
-                      uint32_t box_rows, uint32_t box_cols, int f16) {
+int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
+                 uint32_t box_rows, uint32_t box_cols, int esize, int f16) {
   B2S_TRY(get_encode_fn());
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {pitch_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = g_encode(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  const CUtensorMapDataType dt = esize == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                            : (f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+  CUresult r = g_encode(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu pitch=%llu base=%p)", static_cast<int>(r),
               static_cast<unsigned long long>(rows), static_cast<unsigned long long>(cols),
@@ -729,15 +883,21 @@ int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_
   return B2S_OK;
 }
 
+int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
+                      uint32_t box_rows, uint32_t box_cols, int f16) {
+  return make_tmap_2d(map, base, rows, cols, pitch_bytes, box_rows, box_cols, 2, f16);
+}
+
 // row-major [rows, cols] bf16 matrix, box = [box_rows, 64 cols]
 static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows, int f16 = 0) {
   return make_tmap_bf16_2d(map, base, rows, cols, cols * 2, box_rows, BK, f16);
 }
 
 static int g_num_sms = 0;
+int g_opt_tma_store = 1;   // 1: epilogue via shared memory + TMA bulk store / reduce-add; 0: per-thread global stores
 int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
-int g_opt_cta_group = 2;   // 2: CTA pairs on 256x256 tiles (default, ~5-15% faster); 1: one CTA per 128x256 tile (b2s_set_option "gemm_cta_group")
+int g_opt_cta_group = 0;   // 0: per-launch policy (default); 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256; 3: CTA pairs on 512x256 (b2s_set_option "gemm_cta_group")
 
 // ---- optional per-launch timing (bench.py roofline): CUDA events on the launching stream ----------
 struct GemmProfile {
@@ -759,7 +919,7 @@ static cudaEvent_t prof_event() {
 
 template <int EPI>
 static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb2, const CUtensorMap& ta3,
-                      const GemmParams& p, cudaStream_t st) {
+                      const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
@@ -769,7 +929,13 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
   if (g_prof.on) cudaEventRecord(prof_event(), st);
   // big tiles pay when there are enough 512-row blocks; short batches (one-token steps, LM head) keep 256-row tiles
-  const bool big = (g_opt_cta_group == 3 && p.M >= 4096) || g_opt_cta_group == 4;   // 4 = always (tests)
+  // Tiling policy.  Under the 1 kW power cap the variants trade clock for tensor-pipe utilisation and land within
+  // ~10 % of each other (profiles/r1_gemm_sustained_sweep.jsonl); option 0 picks per launch what sustained best:
+  // long-K and GELU launches (down / up projections) on single-CTA tiles, the short-K store/residual launches
+  // (QKV, dense, LM head, one-token steps) on CTA pairs.
+  int cg = g_opt_cta_group;
+  if (cg == 0) cg = (p.M >= 4096 && (p.K >= 8192 || EPI == EPI_GELU_BF16)) ? 1 : 2;
+  const bool big = (cg == 3 && p.M >= 4096) || cg == 4;   // 4 = always (tests)
   if (big) {
     static bool attr3_set = false;
     if (!attr3_set) {
@@ -779,8 +945,8 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
     const int tiles3 = static_cast<int>(ceil_div(p.M, BM3)) * p.tiles_n;
     int pairs = g_num_sms / 2;
     if (tiles3 < pairs) pairs = tiles3;
-    gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, p);
-  } else if (g_opt_cta_group >= 2) {
+    gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, tc, p);
+  } else if (cg >= 2) {
     static bool attr2_set = false;
     if (!attr2_set) {
       B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
@@ -789,9 +955,9 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
     const int tiles2 = static_cast<int>(ceil_div(p.M, BM2)) * p.tiles_n;
     int pairs = g_num_sms / 2;
     if (tiles2 < pairs) pairs = tiles2;
-    gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, p);
+    gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, tc, p);
   } else {
-    gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, p);
+    gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, tc, p);
   }
   if (g_prof.on) {
     cudaEventRecord(prof_event(), st);
@@ -839,19 +1005,26 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   p.hint_b = g_opt_hint == 2 ? HINT_EVICT_FIRST : (g_opt_hint == 1 || g_opt_hint == 3 ? HINT_EVICT_LAST : 0ull);
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
   p.rope = rope ? *rope : RopeEpiArgs{};
+  p.tma_store = (g_opt_tma_store && epilogue != EPI_LMHEAD) ? 1 : 0;
+  CUtensorMap tc = ta;   // placeholder when the epilogue writes no [M,N] matrix
+  if (p.tma_store) {
+    const bool f32 = epilogue == EPI_RESID_F32 || epilogue == EPI_STORE_F32;
+    B2S_TRY(make_tmap_2d(&tc, out, static_cast<uint64_t>(M), static_cast<uint64_t>(N), static_cast<uint64_t>(N) * (f32 ? 4 : 2),
+                         32, f32 ? 32 : 64, f32 ? 4 : 2, act_f16));
+  }
   switch (epilogue) {
-    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, ta3, p, st);
-    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, ta3, p, st);
-    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, ta3, p, st);
-    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, ta3, p, st);
+    case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, ta3, tc, p, st);
+    case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, ta3, tc, p, st);
+    case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, ta3, tc, p, st);
+    case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, ta3, tc, p, st);
     case EPI_QKV_ROPE:
       B2S_REQUIRE(rope && rope->pos && rope->slot && rope->cos && rope->sin && rope->kcache && rope->vcache,
                   "gemm_bf16: the QKV+RoPE epilogue needs its buffers");
       B2S_REQUIRE(N == (rope->nh + 2 * rope->nkv) * 64, "gemm_bf16: QKV+RoPE epilogue expects N = (nh + 2 nkv) * 64");
-      return launch_epi<EPI_QKV_ROPE>(ta, tb, tb2, ta3, p, st);
+      return launch_epi<EPI_QKV_ROPE>(ta, tb, tb2, ta3, tc, p, st);
     case EPI_LMHEAD:
       B2S_REQUIRE(lmh && lmh->partials && lmh->cand_ids && lmh->cand_logits, "gemm_bf16: LM-head epilogue needs its buffers");
-      return launch_epi<EPI_LMHEAD>(ta, tb, tb2, ta3, p, st);
+      return launch_epi<EPI_LMHEAD>(ta, tb, tb2, ta3, tc, p, st);
     default:
       set_error("gemm_bf16: unknown epilogue %d", epilogue);
       return B2S_EINVAL;
@@ -865,8 +1038,12 @@ extern "C" {
 int b2s_set_option(const char* name, int32_t value) {
   B2S_REQUIRE(name != nullptr, "set_option: null name");
   if (std::string(name) == "gemm_cta_group") {
-    B2S_REQUIRE(value >= 1 && value <= 4, "set_option: gemm_cta_group must be 1..4");
+    B2S_REQUIRE(value >= 0 && value <= 4, "set_option: gemm_cta_group must be 0..4");
     b2s::g_opt_cta_group = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_tma_store") {
+    b2s::g_opt_tma_store = value ? 1 : 0;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_l2_hint") {

@@ -14,7 +14,7 @@ def cta_group(request):
     lib = _lib.load()
     _lib.check(lib.b2s_set_option(b"gemm_cta_group", request.param), "set_option")
     yield request.param
-    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 2), "set_option")   # library default
+    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 0), "set_option")   # library default
 
 
 def _rand(shape, scale=1.0, seed=0, dtype=torch.bfloat16):

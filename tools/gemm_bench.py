@@ -50,7 +50,7 @@ def main():
         med = {k: sorted(v)[len(v) // 2] for k, v in t.items()}
         print(json.dumps({"M": M, "N": N, "K": K, "epi": epi, **{k + "_ms": round(v, 4) for k, v in med.items()},
                           **{k + "_tflops": round(fl / v / 1e9, 1) for k, v in med.items()}}), flush=True)
-    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 2), "opt")
+    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 0), "opt")
 
 
 if __name__ == "__main__":

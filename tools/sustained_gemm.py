@@ -82,7 +82,7 @@ def main():
         run("ours_cta1_bf16", ours(torch.bfloat16, 1))
         run("ours_pair_fp16", ours(torch.float16, 2))
         run("cublas_fp16", cublas(torch.float16))
-    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 2), "opt")
+    _lib.check(lib.b2s_set_option(b"gemm_cta_group", 0), "opt")
 
 
 if __name__ == "__main__":

@@ -29,7 +29,7 @@ for name in which:
         print(json.dumps({"shape": name, "cfg": tag, "tflops": round(n * 2.0 * M * N * K / ms / 1e9, 1), "sm_mhz": clk, "power_w": pw}), flush=True)
     run("cublas", lambda: A @ W.T)
     for cg in (1, 2, 3):
-        for gm in ((0, 16, 32) if cg == 3 else (0,)):
+        for gm in (0,):
             for hint in (0,):
                 def f(cg=cg, gm=gm, hint=hint):
                     lib.b2s_set_option(b"gemm_cta_group", cg); lib.b2s_set_option(b"gemm_group_m", gm); lib.b2s_set_option(b"gemm_l2_hint", hint)
