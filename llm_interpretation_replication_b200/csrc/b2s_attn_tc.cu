@@ -68,6 +68,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+template <bool HOLD_S>   // keep S in registers between the max and the exp pass when it fits (<= 128 keys)
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const AttnTcParams p) {
@@ -236,7 +237,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
           *reinterpret_cast<uint4*>(prow + chunk * 16) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
         }
       };
-      if (nchunks <= 4) {
+      if (HOLD_S && nchunks <= 4) {
         // <= 128 keys (most tiles): S is read from TMEM ONCE and kept in registers between the max and the exp pass
         // (TMEM reads, not the math, bound this kernel)
         float v0[32], v1[32], v2[32], v3[32];
@@ -320,6 +321,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
+int g_opt_attn_hold_s = 0;   // b2s_set_option("attn_hold_s")
+
 // The caller decides which kernel to use from attn_tc_supported(); there is no silent fallback here.
 bool attn_tc_supported(int hd, int max_kv) { return hd == AT_HD && max_kv <= AT_MAXKV; }
 // one-token steps additionally need contiguous 64-wide query heads (the qkv row is read as a [heads, 64] matrix)
@@ -334,7 +337,8 @@ int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slot
               "attn_tc: one-token mode needs contiguous 64-wide query heads");
   static bool attr_set = false;
   if (!attr_set) {
-    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     attr_set = true;
   }
   CUtensorMap tq, tk, tv;
@@ -358,7 +362,8 @@ int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slot
   p.qrows_per_token = a.qkv_dim / AT_HD;
   p.scale_log2e = a.scale * 1.4426950408889634f;
   dim3 grid(n_seqs, decode ? 1u : static_cast<unsigned>(ceil_div(max_qlen, AT_BM)), a.nkv);
-  attn_tc_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(tq, tk, tv, p);
+  if (g_opt_attn_hold_s) attn_tc_kernel<true><<<grid, AT_THREADS, AT_SMEM, st>>>(tq, tk, tv, p);
+  else attn_tc_kernel<false><<<grid, AT_THREADS, AT_SMEM, st>>>(tq, tk, tv, p);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }

@@ -85,6 +85,20 @@ __device__ __forceinline__ float gelu_erf(float x) {
   // HF "gelu" = x * 0.5 * (1 + erf(x / sqrt(2)))   (HF falcon:537, gpt_neox:43)
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }
+// GELU for the tensor-core epilogues: x * Phi(x) with Phi(-|x|) = 0.5 erfc(|x|/sqrt 2) from Abramowitz-Stegun 7.1.26
+// (|error| < 5e-7 absolute, three orders below the 16-bit rounding that follows; 16 FP instructions instead of 25 for
+// erff -- epilogue instructions cost clock under the power cap, profiles/r1_gemm_power.md).  The fp32 check mode
+// keeps erff.
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float ax = fabsf(x) * 0.70710678118654752f;
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
+  float q = fmaf(1.061405429f, t, -1.453152027f);
+  q = fmaf(q, t, 1.421413741f); q = fmaf(q, t, -0.284496736f); q = fmaf(q, t, 0.254829592f); q *= t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-ax * ax * 1.4426950408889634f));
+  const float h = 0.5f * q * e;
+  return x * (x >= 0.f ? 1.0f - h : h);
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -95,6 +109,9 @@ __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
 }
 // two fp32 -> packed 16-bit pair in the activation format of the run (bf16 or fp16)
 __device__ __forceinline__ uint32_t pack_act16x2(float lo, float hi, int f16) { return f16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi); }
+template <bool F16> __device__ __forceinline__ uint32_t pack16x2(float lo, float hi) {
+  if constexpr (F16) return pack_f16x2(lo, hi); else return pack_bf16x2(lo, hi);
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

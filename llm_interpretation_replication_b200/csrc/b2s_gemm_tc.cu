@@ -27,7 +27,7 @@ static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
 static constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KB
 static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 static constexpr int EPI_STAGE_BYTES = 4096;   // per epilogue warp: 32 rows x 128 B, 128B-swizzled
-static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 1024 /*barriers*/ + 4 * EPI_STAGE_BYTES;
+static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 1024 /*barriers*/ + 8 * EPI_STAGE_BYTES;
 static constexpr int NUM_THREADS = 192;
 static constexpr uint32_t TMEM_COLS = 512;
 
@@ -93,7 +93,7 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
   if constexpr (EPI == EPI_STORE_BF16 || EPI == EPI_GELU_BF16) {
     if constexpr (EPI == EPI_GELU_BF16) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+      for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
     }
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(row) * N + col0;
 #pragma unroll
@@ -267,6 +267,20 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
   }
 }
 
+// one thread's 64 values (two 32-column chunks) -> its 128-byte line of the swizzled staging buffer
+template <bool F16>
+__device__ __forceinline__ void stage_store16(uint32_t my_line, uint32_t sw, const float (&x1)[32], const float (&x2)[32]) {
+#pragma unroll
+  for (uint32_t q = 0; q < 4; ++q) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + ((q ^ sw) << 4)),
+                 "r"(pack16x2<F16>(x1[8 * q], x1[8 * q + 1])), "r"(pack16x2<F16>(x1[8 * q + 2], x1[8 * q + 3])),
+                 "r"(pack16x2<F16>(x1[8 * q + 4], x1[8 * q + 5])), "r"(pack16x2<F16>(x1[8 * q + 6], x1[8 * q + 7])) : "memory");
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + (((q + 4) ^ sw) << 4)),
+                 "r"(pack16x2<F16>(x2[8 * q], x2[8 * q + 1])), "r"(pack16x2<F16>(x2[8 * q + 2], x2[8 * q + 3])),
+                 "r"(pack16x2<F16>(x2[8 * q + 4], x2[8 * q + 5])), "r"(pack16x2<F16>(x2[8 * q + 6], x2[8 * q + 7])) : "memory");
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Epilogue through shared memory + TMA (default): the warp's 32 x 64 (16-bit) or 32 x 32 (fp32) sub-tile is written
 // to a 4 KB 128B-swizzled staging buffer and leaves as ONE bulk tensor store -- or, for the fp32 residual, one bulk
@@ -274,12 +288,20 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
 // checks (the TMA unit clips at the tensor edge) and cost the LSU nothing.
 //   row0  first row of this warp's 32-row slab;  stage  shared address of the warp's staging buffer
 // ---------------------------------------------------------------------------------------------
-template <int EPI>
+template <int EPI, int NBUF>   // NBUF staging buffers of 4 KB per warp (2: a store may still be draining while the next is staged)
 __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUtensorMap* tmC, int row0, int nb,
-                                                  uint32_t taddr, int lane, uint32_t release_bar, uint32_t stage) {
+                                                  uint32_t taddr, int lane, uint32_t release_bar, uint32_t stage0,
+                                                  uint32_t& flip /* which buffer comes next; lives across tiles */) {
   const int row = row0 + lane;
-  const uint32_t my_line = stage + static_cast<uint32_t>(lane) * 128u;
   const uint32_t sw = static_cast<uint32_t>(lane & 7);
+  auto next_buffer = [&](uint32_t& stage, uint32_t& my_line) {
+    stage = stage0 + (NBUF == 2 ? flip * EPI_STAGE_BYTES : 0u);
+    my_line = stage + static_cast<uint32_t>(lane) * 128u;
+    flip ^= 1u;
+    if (lane == 0) { if constexpr (NBUF == 2) tma_store_wait_read1(); else tma_store_wait_read(); }
+    __syncwarp();
+  };
+  uint32_t stage = stage0, my_line = stage0 + static_cast<uint32_t>(lane) * 128u;
   if constexpr (EPI == EPI_RESID_F32 || EPI == EPI_STORE_F32) {
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
@@ -291,8 +313,7 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
 #pragma unroll
         for (int j = 0; j < 32; ++j) if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
       }
-      if (lane == 0) tma_store_wait_read();        // the previous bulk store has finished reading the buffer
-      __syncwarp();
+      next_buffer(stage, my_line);                 // the store that used this buffer has finished reading it
 #pragma unroll
       for (uint32_t q = 0; q < 8; ++q)
         asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + ((q ^ sw) << 4)), "f"(v[4 * q]), "f"(v[4 * q + 1]),
@@ -333,7 +354,7 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
       }
       if constexpr (EPI == EPI_GELU_BF16) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) { x1[j] = gelu_erf(x1[j]); x2[j] = gelu_erf(x2[j]); }
+        for (int j = 0; j < 32; ++j) { x1[j] = gelu_fast(x1[j]); x2[j] = gelu_fast(x2[j]); }
       }
       bool to_cache = false;
       if constexpr (EPI == EPI_QKV_ROPE) {
@@ -369,17 +390,8 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
         }
       }
       if (to_cache) continue;
-      if (lane == 0) tma_store_wait_read();
-      __syncwarp();
-#pragma unroll
-      for (uint32_t q = 0; q < 4; ++q) {
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + ((q ^ sw) << 4)),
-                     "r"(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.act_f16)), "r"(pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.act_f16)),
-                     "r"(pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.act_f16)), "r"(pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.act_f16)) : "memory");
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_line + (((q + 4) ^ sw) << 4)),
-                     "r"(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.act_f16)), "r"(pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.act_f16)),
-                     "r"(pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.act_f16)), "r"(pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.act_f16)) : "memory");
-      }
+      next_buffer(stage, my_line);
+      if (p.act_f16) stage_store16<true>(my_line, sw, x1, x2); else stage_store16<false>(my_line, sw, x1, x2);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) { tma_store_2d(tmC, stage, col0, row0); tma_store_commit(); }
@@ -481,6 +493,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else {
     // ===================== epilogue warps (2..5) =====================
     const int quad = warp & 3;                      // TMEM lane quadrant this warp may read
+    uint32_t epi_flip = 0;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       int mb, nb;
@@ -494,8 +507,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       if constexpr (EPI != EPI_LMHEAD) {
         if (p.tma_store) {
-          epilogue_tile_tma<EPI>(p, &tmC, mb * BM + quad * 32, nb, taddr, lane, tempty_bar(acc),
-                                 bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES));
+          epilogue_tile_tma<EPI, 2>(p, &tmC, mb * BM + quad * 32, nb, taddr, lane, tempty_bar(acc),
+                                    bars + 1024u + static_cast<uint32_t>((warp - 2) * 2 * EPI_STAGE_BYTES), epi_flip);
           continue;
         }
       }
@@ -524,7 +537,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // ---------------------------------------------------------------------------------------------
 static constexpr int STAGES2 = 6;
 static constexpr int STAGE2_BYTES = 2 * A_STAGE_BYTES;   // 16 KB A + 16 KB W
-static constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 1024 + 4 * EPI_STAGE_BYTES;
+static constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 1024 + 8 * EPI_STAGE_BYTES;
 static constexpr int BM2 = 256;
 
 __device__ __forceinline__ void tma_load_2d_cg2(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int32_t c0, int32_t c1,
@@ -659,6 +672,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else {
     // ===================== epilogue warps (2..5), both CTAs =====================
     const int quad = warp & 3;
+    uint32_t epi_flip = 0;
     int it = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
       int mb, nb;
@@ -672,8 +686,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       if constexpr (EPI != EPI_LMHEAD) {
         if (p.tma_store) {
-          epilogue_tile_tma<EPI>(p, &tmC, mb * BM2 + static_cast<int>(rank) * BM + quad * 32, nb, taddr, lane,
-                                 tempty_bar(acc) & PEER_MASK, bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES));
+          epilogue_tile_tma<EPI, 2>(p, &tmC, mb * BM2 + static_cast<int>(rank) * BM + quad * 32, nb, taddr, lane,
+                                    tempty_bar(acc) & PEER_MASK, bars + 1024u + static_cast<uint32_t>((warp - 2) * 2 * EPI_STAGE_BYTES), epi_flip);
           continue;
         }
       }
@@ -809,6 +823,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===================== epilogue warps 2..9: warps 2-5 drain accumulator 0, warps 6-9 accumulator 1 =====================
     const int quad = warp & 3;
     const int acc = (warp - 2) >> 2;
+    uint32_t epi_flip = 0;
     int it = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
       int mb, nb;
@@ -820,8 +835,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * BN);
       if constexpr (EPI != EPI_LMHEAD) {
         if (p.tma_store) {
-          epilogue_tile_tma<EPI>(p, &tmC, mb * BM3 + static_cast<int>(rank) * 256 + acc * BM + quad * 32, nb, taddr, lane,
-                                 tempty_bar & PEER_MASK, bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES));
+          epilogue_tile_tma<EPI, 1>(p, &tmC, mb * BM3 + static_cast<int>(rank) * 256 + acc * BM + quad * 32, nb, taddr, lane,
+                                 tempty_bar & PEER_MASK, bars + 1024u + static_cast<uint32_t>((warp - 2) * EPI_STAGE_BYTES), epi_flip);
           continue;
         }
       }
@@ -894,6 +909,7 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
 }
 
 static int g_num_sms = 0;
+extern int g_opt_attn_hold_s;
 int g_opt_tma_store = 1;   // 1: epilogue via shared memory + TMA bulk store / reduce-add; 0: per-thread global stores
 int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
@@ -1040,6 +1056,10 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_cta_group") {
     B2S_REQUIRE(value >= 0 && value <= 4, "set_option: gemm_cta_group must be 0..4");
     b2s::g_opt_cta_group = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "attn_hold_s") {
+    b2s::g_opt_attn_hold_s = value ? 1 : 0;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_tma_store") {

@@ -13,7 +13,7 @@ for (N, K, epi) in ((4544, 18176, 0), (18176, 4544, 0)):     # plain bf16 store 
     out = torch.zeros(M, N, device="cuda", dtype=torch.bfloat16)
     for rep in range(2):
         ref = A @ W.T
-        for cg in (1, 2):
+        for cg in (1, 2, 4):
             lib.b2s_set_option(b"gemm_cta_group", cg)
             _lib.check(lib.b2s_gemm_bf16(_lib.ptr(A), _lib.ptr(W), None, _lib.ptr(out), M, N, K, epi, st), "gemm")
         torch.cuda.synchronize()

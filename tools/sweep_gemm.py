@@ -10,9 +10,11 @@ M = int(sys.argv[1]) if len(sys.argv) > 1 else 111104
 secs = float(sys.argv[2]) if len(sys.argv) > 2 else 1.5
 lib = _lib.load(); st = _lib.current_stream()
 shapes = {"up": (18176, 4544, 1), "down": (4544, 18176, 2), "dense": (4544, 4544, 2), "qkv": (4672, 4544, 0)}
+epi_override = int(sys.argv[4]) if len(sys.argv) > 4 else -1
 which = sys.argv[3].split(",") if len(sys.argv) > 3 else ["down", "up", "dense", "qkv"]
 for name in which:
     N, K, epi = shapes[name]
+    if epi_override >= 0: epi = epi_override
     A = torch.randn(M, K, device="cuda").to(torch.bfloat16)
     W = (torch.randn(N, K, device="cuda") * 0.02).to(torch.bfloat16)
     out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi == 2 else torch.bfloat16)
