@@ -145,8 +145,9 @@ def test_scorer_real_dims_neox_bf16(maker, lens, mode_name):
     g = np.random.RandomState(2)
     ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in lens]
     rows, gens = sc.score_ids(ids, np.array([[500, 600]]), topk=5, max_lookahead=2)
+    rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=decoder_ref.bf16_round)
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
         p = torch.softmax(lo, -1)
         rel = (p[500] / (p[500] + p[600])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
