@@ -1,0 +1,344 @@
+// tcgen05 varlen causal attention for the prompt pass, second generation: P stays in tensor memory.
+//
+// Same contract as attn_tc_kernel's prefill mode (b2s_attn_tc.cu; HF:models/falcon/modeling_falcon.py:349-362):
+// head_dim 64, <= 256 keys per prompt, one CTA per (prompt, 128-query tile, KV head) looping over the query heads
+// that share the KV head.  What changed, and why (profiles/r1_attn_ncu.md): the first kernel spent its time in the
+// 256 softmax threads (two per scheduler, latency-bound) and in moving P through shared memory.  Here
+//   * P is written back over S in tensor memory (tcgen05.st, two 16-bit probabilities per column) and P.V reads its
+//     A operand from tensor memory (tcgen05.mma [d], [a_tmem], b_desc): no shared-memory P tile, no proxy fence;
+//   * O overlays the dead upper half of S, so an item needs max(keys, 128) columns and FOUR items are in flight
+//     for <= 128 keys (two for <= 256): 16 softmax warps, four per scheduler;
+//   * a chunk of 32 keys that every row of the warp may see skips the causal compare; chunks no row may see are
+//     not computed (their P columns are zero-filled);
+//   * the row sum is taken in fp32 before rounding; the 16-bit format is a template parameter, not a branch.
+// The issuing thread polls: S of the next item when its lane is free and its Q tile has landed, P.V of the oldest
+// item whose P is written.
+#include "b2s_tc.cuh"
+#include "b2s_decoder.cuh"
+
+namespace b2s {
+
+static constexpr int A2_HD = 64;
+static constexpr int A2_BM = 128;
+static constexpr int A2_MAXKV = 256;
+static constexpr int A2_KV_BYTES = A2_MAXKV * A2_HD * 2;     // 32 KB per K or V
+static constexpr int A2_Q_BYTES = A2_BM * A2_HD * 2;         // 16 KB per Q tile
+static constexpr int A2_NQ = 6;                              // Q ring depth
+static constexpr int A2_LANES = 4;
+static constexpr int A2_SMEM = 2 * A2_KV_BYTES + A2_NQ * A2_Q_BYTES + 1024 + 256;
+static constexpr int A2_THREADS = A2_LANES * 128 + 32;       // 16 softmax warps + the issuer warp
+static constexpr uint32_t A2_TMEM_COLS = 512;
+
+struct Attn2Params {
+  BatchMeta meta;
+  uint16_t* out;          // [T, nh*64] 16-bit
+  int nh, nkv, rep;
+  int q_base, q_hstride;
+  float scale_log2e;
+};
+
+__device__ __forceinline__ uint32_t a2_idesc(int m, int n, int b_mn, bool f16) {
+  const uint32_t fmt = f16 ? 0u : 1u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | (static_cast<uint32_t>(b_mn) << 16) |
+         (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+__device__ __forceinline__ uint64_t a2_vdesc(uint32_t smem_addr) {   // V [keys, 64] as the MN-major B operand
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(1024 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+__device__ __forceinline__ float a2_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// D[tmem] (+)= A[tmem] . B[smem]
+__device__ __forceinline__ void a2_mma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 16 (or 8) consecutive 32-bit columns of this thread's TMEM lane
+__device__ __forceinline__ void a2_tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+        "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void a2_tmem_st8(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+      : "memory");
+}
+__device__ __forceinline__ void a2_tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// wait without reading the clock every spin (try_wait itself suspends the thread for a while)
+__device__ __forceinline__ void a2_wait(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 27)) {
+      printf("b2s attn_tc2: mbarrier wait timed out (block %d,%d thread %d bar %u parity %u)\n", blockIdx.x, blockIdx.y,
+             threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ bool a2_test(uint32_t bar, uint32_t parity) {   // non-blocking probe
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
+template <bool F16>
+__global__ void __launch_bounds__(A2_THREADS, 1)
+attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const Attn2Params p) {
+  const int seq = blockIdx.x, mt = blockIdx.y, g = blockIdx.z;
+  const int ql = p.meta.q_len[seq];
+  if (mt * A2_BM >= ql) return;                        // uniform per CTA: nothing allocated yet
+  const int q0 = p.meta.q_start[seq] + mt * A2_BM;
+  const int kv0 = p.meta.kv_start[seq];
+  const int kl = p.meta.kv_len[seq];
+  const int n_items = p.rep;
+  const int rows_here = min(A2_BM, ql - mt * A2_BM);
+  const int base_lim = kl - ql + mt * A2_BM;           // last key visible to row 0 of the tile (causal)
+  const int kv_tile = min(kl, base_lim + rows_here);   // keys visible to the last data row
+  const int kvp = (kv_tile + 15) & ~15;                // MMA granularity (N % 16, K % 16)
+  const int nl = kvp <= 128 ? 4 : 2;                   // items in flight
+  const uint32_t lane_cols = 512u / static_cast<uint32_t>(nl);
+  const uint32_t o_off = nl == 4 ? 64u : 128u;         // O overlays S columns that P does not cover
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sK = base, sV = base + A2_KV_BYTES, sQ = base + 2 * A2_KV_BYTES;
+  const uint32_t bars = sQ + A2_NQ * A2_Q_BYTES;
+  // barriers (8 B each): kv, q[6], s[4], p[4], o[4], e[4]; then the TMEM slot
+  const uint32_t bar_kv = bars;
+  auto bar_q = [&](int b) { return bars + 8u * (1 + b); };
+  auto bar_s = [&](int l) { return bars + 8u * (7 + l); };    // S(i) accumulated            (tensor core -> softmax)
+  auto bar_p = [&](int l) { return bars + 8u * (11 + l); };   // P(i) written, S(i) consumed (softmax -> issuer)
+  auto bar_o = [&](int l) { return bars + 8u * (15 + l); };   // O(i) accumulated            (tensor core -> softmax)
+  auto bar_e = [&](int l) { return bars + 8u * (19 + l); };   // O(i) read: lane free        (softmax -> issuer)
+  const uint32_t tmem_slot = bars + 8u * 23;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == A2_LANES * 128) {
+    mbar_init(bar_kv, 1);
+    for (int b = 0; b < A2_NQ; ++b) mbar_init(bar_q(b), 1);
+    for (int l = 0; l < A2_LANES; ++l) {
+      mbar_init(bar_s(l), 1); mbar_init(bar_p(l), 128); mbar_init(bar_o(l), 1); mbar_init(bar_e(l), 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(A2_TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  const int h_first = g * p.rep;
+
+  if (warp == A2_LANES * 4) {
+    if (lane == 0) {
+      // ---------------- TMA + MMA issuer ----------------
+      auto load_q = [&](int i) {
+        const uint32_t bq = bar_q(i % A2_NQ);
+        mbar_arrive_expect_tx(bq, A2_Q_BYTES);
+        tma_load_2d(sQ + (i % A2_NQ) * A2_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i) * p.q_hstride, q0);
+      };
+      mbar_arrive_expect_tx(bar_kv, 2 * A2_KV_BYTES);
+      tma_load_2d(sK, &tmK, bar_kv, g * A2_HD, kv0);
+      tma_load_2d(sV, &tmV, bar_kv, g * A2_HD, kv0);
+      for (int i = 0; i < A2_NQ && i < n_items; ++i) load_q(i);
+      a2_wait(bar_kv, 0);
+      const uint32_t idesc_s = a2_idesc(A2_BM, kvp, 0, F16);
+      const uint32_t idesc_o = a2_idesc(A2_BM, A2_HD, 1, F16);
+      const uint64_t kdesc = make_kmajor_sw128_desc(sK);
+      const uint64_t vdesc = a2_vdesc(sV);
+      int is = 0, ipv = 0;
+      uint32_t idle = 0;
+      while (ipv < n_items) {
+        bool did = false;
+        if (is < n_items) {
+          // S(is): its lane is free once the previous item of the lane has had its O read
+          const int l = is & (nl - 1);
+          const int qb = is % A2_NQ;
+          const bool free_lane = is < nl || a2_test(bar_e(l), static_cast<uint32_t>((is / nl) - 1) & 1u);
+          if (free_lane && a2_test(bar_q(qb), static_cast<uint32_t>(is / A2_NQ) & 1u)) {
+            tcgen05_fence_after();
+            const uint64_t qdesc = make_kmajor_sw128_desc(sQ + qb * A2_Q_BYTES);
+            const uint32_t t_s = tmem_base + static_cast<uint32_t>(l) * lane_cols;
+#pragma unroll
+            for (int k = 0; k < A2_HD / 16; ++k)
+              tcgen05_mma_bf16(t_s, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
+            tcgen05_commit(bar_s(l));
+            ++is; did = true;
+          }
+        }
+        if (ipv < is) {
+          const int l = ipv & (nl - 1);
+          if (a2_test(bar_p(l), static_cast<uint32_t>(ipv / nl) & 1u)) {   // P(ipv) in tensor memory, S(ipv) consumed
+            tcgen05_fence_after();
+            const uint32_t t_p = tmem_base + static_cast<uint32_t>(l) * lane_cols;
+            const uint32_t t_o = t_p + o_off;
+            for (int ks = 0; ks < kvp / 16; ++ks)   // 16 keys = 8 columns of packed P, 16 rows (2048 B) of V
+              a2_mma_ts(t_o, t_p + 8u * ks, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o, ks != 0 ? 1u : 0u);
+            tcgen05_commit(bar_o(l));
+            if (ipv + A2_NQ < n_items) load_q(ipv + A2_NQ);   // S(ipv) is complete, so its Q buffer is free
+            ++ipv; did = true;
+          }
+        }
+        if (did) idle = 0;
+        else if (++idle > (1u << 28)) {
+          printf("b2s attn_tc2: issuer stalled (block %d,%d S %d PV %d of %d)\n", blockIdx.x, blockIdx.y, is, ipv, n_items);
+          __trap();
+        }
+      }
+    }
+  } else if (warp < 4 * nl) {
+    // ---------------- softmax + epilogue: thread == tile row ----------------
+    const int l = warp >> 2;                   // lane (item slot)
+    const int quad = warp & 3;                 // TMEM lane quadrant of this warp
+    const int row = quad * 32 + lane;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(l) * lane_cols;
+    const uint32_t t_o = t_lane + o_off;
+    const bool valid = row < rows_here;
+    const int limit = min(kl - 1, base_lim + row);              // last key this row may see
+    const int lim_lo = min(kl - 1, base_lim + quad * 32);       // ... the first row of the warp
+    const int lim_hi = min(kl - 1, base_lim + quad * 32 + 31);  // ... the last row of the warp
+    const int n_live = lim_hi / 32 + 1;        // 32-key chunks some row of the warp sees
+    const int n_full = (lim_lo + 1) / 32;      // chunks every row of the warp sees entirely (no compare needed)
+    const int n_p = (kvp + 31) / 32;           // chunks of P the tensor core will read
+    const float sc = p.scale_log2e;
+    for (int i = l; i < n_items; i += nl) {
+      const uint32_t ph = static_cast<uint32_t>(i / nl) & 1u;
+      a2_wait(bar_s(l), ph);
+      tcgen05_fence_after();
+      // pass 1: row maximum over the visible keys
+      float m = -INFINITY;
+      for (int c = 0; c < n_live; ++c) {
+        float v[32];
+        tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
+        if (c < n_full) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m = fmaxf(m, v[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
+        }
+      }
+      const float ms = m * sc;
+      // pass 2: p = 2^(s*scale*log2e - max), rounded to 16 bits, two per column over the first half of S
+      float lsum = 0.f;
+      for (int c = 0; c < n_p; ++c) {
+        uint32_t pk[16];
+        if (c < n_live) {
+          float v[32];
+          tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
+          if (c < n_full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float p0 = a2_ex2(fmaf(v[j], sc, -ms)), p1 = a2_ex2(fmaf(v[j + 1], sc, -ms));
+              lsum += p0 + p1;
+              pk[j >> 1] = pack16x2<F16>(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float p0 = (c * 32 + j <= limit) ? a2_ex2(fmaf(v[j], sc, -ms)) : 0.f;
+              const float p1 = (c * 32 + j + 1 <= limit) ? a2_ex2(fmaf(v[j + 1], sc, -ms)) : 0.f;
+              lsum += p0 + p1;
+              pk[j >> 1] = pack16x2<F16>(p0, p1);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) pk[j] = 0u;
+        }
+        if (c * 32 + 32 <= kvp) a2_tmem_st16(t_lane + static_cast<uint32_t>(c * 16), pk);
+        else a2_tmem_st8(t_lane + static_cast<uint32_t>(c * 16), pk);
+      }
+      a2_tmem_st_wait();
+      tcgen05_fence_before();
+      mbar_arrive(bar_p(l));
+      // epilogue of this item: O / rowsum
+      a2_wait(bar_o(l), ph);
+      tcgen05_fence_after();
+      float o0[32], o1[32];
+      tmem_ld32(t_o, o0);
+      tmem_ld32(t_o + 32, o1);
+      tcgen05_fence_before();
+      mbar_arrive(bar_e(l));                   // the lane's columns may be overwritten by the next S
+      if (valid) {
+        const float inv = 1.f / lsum;
+        uint4* dst = reinterpret_cast<uint4*>(p.out + static_cast<size_t>(q0 + row) * (static_cast<size_t>(p.nh) * A2_HD) +
+                                              static_cast<size_t>(h_first + i) * A2_HD);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
+                              pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
+                                  pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(A2_TMEM_COLS) : "memory");
+  }
+}
+
+int g_opt_attn_ts = 1;   // b2s_set_option("attn_ts"): 1 = this kernel for the prompt pass, 0 = attn_tc_kernel
+
+int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
+  B2S_REQUIRE(attn_tc_supported(a.hd, a.max_kv), "attn_tc2: head_dim %d / %d keys not supported", a.hd, a.max_kv);
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
+    attr_set = true;
+  }
+  CUtensorMap tq, tk, tv;
+  B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
+                            static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, A2_HD, a.f16));
+  const uint64_t kvw = static_cast<uint64_t>(a.nkv) * A2_HD;
+  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, A2_HD, a.f16));
+  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, A2_HD, a.f16));
+  Attn2Params p;
+  p.meta = a.meta;
+  p.out = reinterpret_cast<uint16_t*>(a.out);
+  p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
+  p.q_base = a.q_base; p.q_hstride = a.q_hstride;
+  p.scale_log2e = a.scale * 1.4426950408889634f;
+  dim3 grid(n_seqs, static_cast<unsigned>(ceil_div(max_qlen, A2_BM)), a.nkv);
+  if (a.f16) attn_tc2_kernel<true><<<grid, A2_THREADS, A2_SMEM, st>>>(tq, tk, tv, p);
+  else attn_tc2_kernel<false><<<grid, A2_THREADS, A2_SMEM, st>>>(tq, tk, tv, p);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+}  // namespace b2s

@@ -35,6 +35,7 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
+  int serp;              // serpentine order: odd groups walk the column tiles backwards, odd waves walk K backwards
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
@@ -53,7 +54,7 @@ __device__ __forceinline__ void tma_load_2d_h(uint32_t smem_dst, const CUtensorM
       : "memory");
 }
 
-__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int serp, int& mb, int& nb) {
   const int per_group = group_m * tiles_n;
   const int g = tile / per_group;
   const int first_m = g * group_m;
@@ -61,6 +62,7 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
   const int within = tile - g * per_group;
   mb = first_m + within % gm;
   nb = within / gm;
+  if (serp && (g & 1)) nb = tiles_n - 1 - nb;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -447,8 +449,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mb, nb;
-        tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, mb, nb);
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, p.serp, mb, nb);
+        const bool rev = p.serp && (((tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x)) & 1);
+        for (int kq = 0; kq < p.num_kb; ++kq) {
+          const int kb = rev ? p.num_kb - 1 - kq : kq;   // the MMA side only counts k-blocks, so the order is free
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           const uint32_t sb = sa + A_STAGE_BYTES;
@@ -497,7 +501,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       int mb, nb;
-      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, mb, nb);
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, p.serp, mb, nb);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
       const int row = mb * BM + quad * 32 + lane;
@@ -571,7 +575,7 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
+__device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n, int group_m, int serp, int& mb, int& nb) {
   const int GM = max(1, group_m / 2);    // groups of group_m x 128 rows = GM x 256 rows
   const int per_group = GM * tiles_n;
   const int g = tile / per_group;
@@ -580,6 +584,7 @@ __device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n,
   const int within = tile - g * per_group;
   mb = first_m + within % gm;
   nb = within / gm;
+  if (serp && (g & 1)) nb = tiles_n - 1 - nb;
 }
 
 template <int EPI>
@@ -628,8 +633,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int stage = 0; uint32_t phase = 0;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
-        tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, mb, nb);
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
+        const bool rev = p.serp && (((tile - pair) / num_pairs) & 1);
+        for (int kq = 0; kq < p.num_kb; ++kq) {
+          const int kb = rev ? p.num_kb - 1 - kq : kq;
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE2_BYTES;
           const uint32_t sb = sa + A_STAGE_BYTES;
@@ -676,7 +683,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int it = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
       int mb, nb;
-      tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, mb, nb);
+      tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
       const int row = mb * BM2 + static_cast<int>(rank) * BM + quad * 32 + lane;
@@ -719,7 +726,7 @@ static constexpr int SMEM3_BYTES = STAGES3 * STAGE3_BYTES + 1024 + 1024 + 8 * EP
 static constexpr int BM3 = 512;
 static constexpr int NUM_THREADS3 = 320;   // producer, MMA, 8 epilogue warps
 
-__device__ __forceinline__ void tile_coords3(int tile, int tiles_m, int tiles_n, int group_m, int& mb, int& nb) {
+__device__ __forceinline__ void tile_coords3(int tile, int tiles_m, int tiles_n, int group_m, int serp, int& mb, int& nb) {
   const int GM = max(1, group_m / 4);    // groups of group_m x 128 rows = GM x 512 rows
   const int per_group = GM * tiles_n;
   const int g = tile / per_group;
@@ -728,6 +735,7 @@ __device__ __forceinline__ void tile_coords3(int tile, int tiles_m, int tiles_n,
   const int within = tile - g * per_group;
   mb = first_m + within % gm;
   nb = within / gm;
+  if (serp && (g & 1)) nb = tiles_n - 1 - nb;
 }
 
 template <int EPI>
@@ -777,8 +785,10 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       int stage = 0; uint32_t phase = 0;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
-        tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, mb, nb);
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, p.serp, mb, nb);
+        const bool rev = p.serp && (((tile - pair) / num_pairs) & 1);
+        for (int kq = 0; kq < p.num_kb; ++kq) {
+          const int kb = rev ? p.num_kb - 1 - kq : kq;
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE3_BYTES;
           const uint32_t sb = sa + A3_STAGE_BYTES;
@@ -827,7 +837,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int it = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
       int mb, nb;
-      tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, mb, nb);
+      tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, p.serp, mb, nb);
       const int row = mb * BM3 + static_cast<int>(rank) * 256 + acc * BM + quad * 32 + lane;
       if constexpr (EPI == EPI_RESID_F32) prefetch_resid_tile(p, row, nb);
       mbar_wait_warp(tfull_bar, static_cast<uint32_t>(it) & 1u, lane);
@@ -910,8 +920,10 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
 
 static int g_num_sms = 0;
 extern int g_opt_attn_hold_s;
+extern int g_opt_attn_ts;
 int g_opt_tma_store = 1;   // 1: epilogue via shared memory + TMA bulk store / reduce-add; 0: per-thread global stores
 int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
+int g_opt_serp = 1;        // b2s_set_option "gemm_serpentine"
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
 int g_opt_cta_group = 0;   // 0: per-launch policy (default); 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256; 3: CTA pairs on 512x256 (b2s_set_option "gemm_cta_group")
 
@@ -1014,6 +1026,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     int gm = 64;
     while (gm > 16 && gm * mb_bytes > 40e6) gm >>= 1;
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
+    p.serp = g_opt_serp;
   }
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
@@ -1058,6 +1071,10 @@ int b2s_set_option(const char* name, int32_t value) {
     b2s::g_opt_cta_group = value;
     return B2S_OK;
   }
+  if (std::string(name) == "attn_ts") {
+    b2s::g_opt_attn_ts = value ? 1 : 0;
+    return B2S_OK;
+  }
   if (std::string(name) == "attn_hold_s") {
     b2s::g_opt_attn_hold_s = value ? 1 : 0;
     return B2S_OK;
@@ -1069,6 +1086,11 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_l2_hint") {
     B2S_REQUIRE(value >= 0 && value <= 3, "set_option: gemm_l2_hint must be in [0, 3]");
     b2s::g_opt_hint = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_serpentine") {
+    B2S_REQUIRE(value == 0 || value == 1, "set_option: gemm_serpentine must be 0 or 1");
+    b2s::g_opt_serp = value;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_group_m") {

@@ -34,6 +34,31 @@ def test_gemm_tc_store_f32(M, N, K, cta_group):
     assert err <= 2e-3 * max(1.0, ref.abs().max().item()), err
 
 
+@pytest.mark.parametrize("epi", [4, 2])
+def test_gemm_tc_serpentine_rasterisation(epi, cta_group):
+    """Serpentine order (odd groups walk column tiles backwards, odd waves walk K backwards; K tail of 8): several
+    groups and several waves per CTA, same result as the plain order."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    M, N, K = 4200, 2600, 520
+    A, W = _rand((M, K), 1.0, 11), _rand((N, K), 0.05, 12)
+    ref = A.float() @ W.float().T
+    resid = _rand((M, N), 1.0, 13, torch.float32)
+    try:
+        _lib.check(lib.b2s_set_option(b"gemm_serpentine", 1), "set_option")
+        _lib.check(lib.b2s_set_option(b"gemm_group_m", 4), "set_option")
+        out = U.gemm_bf16(A, W, None, epi, out=resid.clone() if epi == 2 else None)
+        torch.cuda.synchronize()
+    finally:
+        _lib.check(lib.b2s_set_option(b"gemm_serpentine", 0), "set_option")
+        _lib.check(lib.b2s_set_option(b"gemm_group_m", 0), "set_option")
+    if epi == 2:
+        ref = ref + resid
+    err = (out - ref).abs().max().item()
+    assert err <= 2e-3 * max(1.0, ref.abs().max().item()), err
+
+
 @pytest.mark.parametrize("epi", [0, 1, 2])
 @pytest.mark.parametrize("use_bias", [False, True])
 def test_gemm_tc_epilogues(epi, use_bias, cta_group):
@@ -142,7 +167,7 @@ def _attn_ref(q, k, v, lens, kv_extra):
     return outs
 
 
-@pytest.mark.parametrize("use_tc", [0, 1])
+@pytest.mark.parametrize("use_tc", [0, 1, 2], ids=["simt", "tc_p_in_tmem", "tc_p_in_smem"])
 @pytest.mark.parametrize("nh,nkv", [(71, 1), (4, 2), (3, 3)])
 @pytest.mark.parametrize("phase", ["prefill", "one_token"])
 def test_attention_bf16(use_tc, nh, nkv, phase):
@@ -169,10 +194,15 @@ def test_attention_bf16(use_tc, nh, nkv, phase):
     i32 = lambda x: torch.tensor(x, dtype=torch.int32, device="cuda")
     kvl = [a + b for a, b in zip(qlens, extra)]
     a_qs, a_ql, a_ks, a_kl = i32(q_start), i32(qlens), i32(kv_start), i32(kvl)
-    _lib.check(lib.b2s_attention_bf16(_lib.ptr(qkv), _lib.ptr(kc), _lib.ptr(vc), _lib.ptr(out), _lib.ptr(a_qs), _lib.ptr(a_ql),
-                                      _lib.ptr(a_ks), _lib.ptr(a_kl), len(qlens), T, slots, max(qlens), max(kvl), nh, nkv, hd,
-                                      qkv_dim, 0, hd, use_tc, _lib.current_stream()), "attention")
-    torch.cuda.synchronize()
+    # prompt pass on the tensor cores: 1 = P kept in tensor memory (default), 2 = first kernel (P through shared memory)
+    _lib.check(lib.b2s_set_option(b"attn_ts", 0 if use_tc == 2 else 1), "set_option")
+    try:
+        _lib.check(lib.b2s_attention_bf16(_lib.ptr(qkv), _lib.ptr(kc), _lib.ptr(vc), _lib.ptr(out), _lib.ptr(a_qs), _lib.ptr(a_ql),
+                                          _lib.ptr(a_ks), _lib.ptr(a_kl), len(qlens), T, slots, max(qlens), max(kvl), nh, nkv, hd,
+                                          qkv_dim, 0, hd, min(use_tc, 1), _lib.current_stream()), "attention")
+        torch.cuda.synchronize()
+    finally:
+        _lib.check(lib.b2s_set_option(b"attn_ts", 1), "set_option")
     q = qkv[:, :nh * hd].view(T, nh, hd)
     ref = _attn_ref(q, kc.view(slots, nkv, hd), vc.view(slots, nkv, hd), list(zip(q_start, qlens, kv_start, kvl)), extra)
     for (qs, ql), r in zip(zip(q_start, qlens), ref):

@@ -5,8 +5,9 @@ sys.path.insert(0, ".")
 from llm_interpretation_replication_b200 import _lib
 import bench
 lib = _lib.load()
-L = bench.synthetic_lengths(10000)
-L = np.sort(L)[::-1][:1180].copy()
+Lall = bench.synthetic_lengths(10000)
+which = sys.argv[1] if len(sys.argv) > 1 else "longest"
+L = np.sort(Lall)[::-1][:1180].copy() if which == "longest" else Lall[:1175].copy()
 nh, nkv, hd = 71, 1, 64
 T = int(L.sum()); LA = 10
 qs = np.concatenate([[0], np.cumsum(L)[:-1]]).astype(np.int32)
@@ -20,7 +21,7 @@ for dt in (torch.bfloat16,):
     kc = torch.randn(slots, nkv * hd, device="cuda").to(dt); vc = torch.randn(slots, nkv * hd, device="cuda").to(dt)
     out = torch.zeros(T, nh * hd, device="cuda", dtype=dt)
     for hold in (0, 1, 0, 1):
-        lib.b2s_set_option(b"attn_hold_s", hold)
+        lib.b2s_set_option(b"attn_ts", hold)
         ts = []
         for it in range(6):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -30,4 +31,4 @@ for dt in (torch.bfloat16,):
                                               qkv_dim, 0, hd, 1, _lib.current_stream()), "attn")
             e1.record(); torch.cuda.synchronize()
             ts.append(e0.elapsed_time(e1))
-        print(json.dumps({"hold_s": hold, "tokens": T, "ms": round(sorted(ts)[2], 3)}), flush=True)
+        print(json.dumps({"batch": which, "attn_ts": hold, "tokens": T, "ms": round(sorted(ts)[2], 3)}), flush=True)
