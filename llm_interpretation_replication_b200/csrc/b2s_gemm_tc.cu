@@ -20,7 +20,8 @@
 namespace b2s {
 
 static constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
-static constexpr unsigned long long HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull;
+static constexpr unsigned long long HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull,
+                                    HINT_EVICT_NORMAL = 0x1000000000000000ull;
 static constexpr int STAGES = 4;
 static constexpr int GROUP_M = 16;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
@@ -1025,13 +1026,21 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     const double mb_bytes = 2.0 * BM * K;
     int gm = 64;
     while (gm > 16 && gm * mb_bytes > 40e6) gm >>= 1;
+    // a W that can stay L2-resident by itself (qkv, dense: 42 MB) is better served by one-wave groups: the A panel
+    // is then 9 MB and W is the only thing re-read (measured: profiles/r1_gemm_l2_hints.txt, DRAM 5.4 -> 4.1 GB on qkv)
+    if (2.0 * N * K <= 48e6) gm = 8;
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
     p.serp = g_opt_serp;
   }
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
-  p.hint_a = g_opt_hint == 1 ? HINT_EVICT_FIRST : (g_opt_hint >= 2 ? HINT_EVICT_LAST : 0ull);
-  p.hint_b = g_opt_hint == 2 ? HINT_EVICT_FIRST : (g_opt_hint == 1 || g_opt_hint == 3 ? HINT_EVICT_LAST : 0ull);
+  {
+    // 0 none | 1 A first, W last | 2 A last, W first | 3 both last | 4 both normal | 5 W last | 6 A first | 7 A normal, W last
+    static const unsigned long long HA[8] = {0ull, HINT_EVICT_FIRST, HINT_EVICT_LAST, HINT_EVICT_LAST, HINT_EVICT_NORMAL, 0ull, HINT_EVICT_FIRST, HINT_EVICT_NORMAL};
+    static const unsigned long long HB[8] = {0ull, HINT_EVICT_LAST, HINT_EVICT_FIRST, HINT_EVICT_LAST, HINT_EVICT_NORMAL, HINT_EVICT_LAST, 0ull, HINT_EVICT_LAST};
+    p.hint_a = HA[g_opt_hint & 7];
+    p.hint_b = HB[g_opt_hint & 7];
+  }
   p.lmh = lmh ? *lmh : LmHeadArgs{nullptr, nullptr, nullptr};
   p.rope = rope ? *rope : RopeEpiArgs{};
   p.tma_store = (g_opt_tma_store && epilogue != EPI_LMHEAD) ? 1 : 0;
@@ -1084,7 +1093,7 @@ int b2s_set_option(const char* name, int32_t value) {
     return B2S_OK;
   }
   if (std::string(name) == "gemm_l2_hint") {
-    B2S_REQUIRE(value >= 0 && value <= 3, "set_option: gemm_l2_hint must be in [0, 3]");
+    B2S_REQUIRE(value >= 0 && value <= 7, "set_option: gemm_l2_hint must be in [0, 7]");
     b2s::g_opt_hint = value;
     return B2S_OK;
   }

@@ -11,18 +11,21 @@ timed = "--time" in sys.argv
 secs = 1.0
 lib = _lib.load(); st = _lib.current_stream()
 shapes = {"up": (18176, 4544, 1), "down": (4544, 18176, 2), "dense": (4544, 4544, 2), "qkv": (4672, 4544, 0)}
-grid = [(cg, gm, serp) for cg in (0,) for gm in (0, 8, 16, 32, 64, 128) for serp in (0, 1)]
-grid += [(3, 0, 0), (3, 0, 1), (3, 64, 1), (2, 0, 1)]
+if "--hints" in sys.argv:
+    grid = [(0, gm, 1, h) for gm in (0, 8) for h in (0, 4, 5, 6, 7, 1)]
+else:
+    grid = [(cg, gm, serp, 0) for cg in (0,) for gm in (0, 8, 16, 32, 64, 128) for serp in (0, 1)]
+    grid += [(3, 0, 0, 0), (3, 0, 1, 0), (3, 64, 1, 0), (2, 0, 1, 0)]
 for name, (N, K, epi) in shapes.items():
     A = torch.randn(M, K, device="cuda").to(torch.float16)
     W = (torch.randn(N, K, device="cuda") * 0.02).to(torch.float16)
     out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi == 2 else torch.float16)
     alg = 2 * (M * K + N * K) + (8 if epi == 2 else 2) * M * N
-    for cg, gm, serp in grid:
+    for cg, gm, serp, hint in grid:
         def f():
-            lib.b2s_set_option(b"gemm_cta_group", cg); lib.b2s_set_option(b"gemm_group_m", gm); lib.b2s_set_option(b"gemm_serpentine", serp)
+            lib.b2s_set_option(b"gemm_cta_group", cg); lib.b2s_set_option(b"gemm_group_m", gm); lib.b2s_set_option(b"gemm_serpentine", serp); lib.b2s_set_option(b"gemm_l2_hint", hint)
             _lib.check(lib.b2s_gemm_f16(_lib.ptr(A), _lib.ptr(W), None, _lib.ptr(out), M, N, K, epi, st), "gemm")
-        rec = {"shape": name, "cg": cg, "group_m": gm, "serp": serp, "algorithmic_bytes": alg}
+        rec = {"shape": name, "cg": cg, "group_m": gm, "serp": serp, "hint": hint, "algorithmic_bytes": alg}
         if timed:
             f(); torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
