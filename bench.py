@@ -192,6 +192,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--mode", default="fp16", choices=["bf16", "fp16"],
                     help="operand format of the tensor-core path: bf16, or fp16 (weights converted from bf16)")
+    ap.add_argument("--option", action="append", default=[], metavar="NAME=VALUE",
+                    help="A/B only: b2s_set_option(NAME, VALUE) before the run (recorded in config.options)")
     ap.add_argument("--gemm-cta-group", type=int, default=-1,
                     help="tuning: 0 = per-launch policy (library default), 1 = one CTA per tile, 2 = CTA pairs, 3 = CTA pairs on 512x256 tiles")
     args = ap.parse_args()
@@ -233,6 +235,9 @@ def main():
     lib = sc.lib
     if args.gemm_cta_group >= 0:
         _lib.check(lib.b2s_set_option(b"gemm_cta_group", args.gemm_cta_group), "set_option")
+    for kv in args.option:
+        name, val = kv.split("=")
+        _lib.check(lib.b2s_set_option(name.encode(), int(val)), "set_option")
     batches = plan_batches(my_len, args.batch_tokens, max_seqs)
 
     # host (pinned) and device-resident copies of every batch
@@ -324,7 +329,7 @@ def main():
                 "dtype": "bf16" if args.mode == "bf16" else "fp16", "data": "synthetic",
                 "config": {"workload": "Falcon-7B (random-init) x 10,000 perturbation-shaped prompts, top-5 / 10-position look-ahead (BASELINE configs[2])",
                            "n_prompts": n_total, "total_prompt_tokens": int(L.sum()), "n_layer": shp.n_layer, "max_lookahead": LOOKAHEAD,
-                           "topk": TOPK, "batch_tokens": args.batch_tokens, "gemm_cta_group": max(args.gemm_cta_group, 0), "batches_per_rank": len(batches), "parallelism": f"prompt-sharded x{world}, replicated weights",
+                           "topk": TOPK, "batch_tokens": args.batch_tokens, "gemm_cta_group": max(args.gemm_cta_group, 0), "options": args.option, "batches_per_rank": len(batches), "parallelism": f"prompt-sharded x{world}, replicated weights",
                            "l2": "inputs larger than L2: 13.8 GB of 16-bit weights are re-read for every batch", "all_rel_prob_finite": finite},
                 "clocks": clk, "gpu_launches": launches,
                 "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel / gemm_tc2_kernel (tcgen05, cta_group::1 / ::2)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",

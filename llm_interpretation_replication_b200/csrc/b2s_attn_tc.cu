@@ -332,11 +332,14 @@ bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q
 
 extern int g_opt_attn_ts;
 int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st);
+int launch_attn_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, cudaStream_t st);
 
 int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
   B2S_REQUIRE(attn_tc_supported(a.hd, a.max_kv), "attn_tc: head_dim %d / %d keys not supported", a.hd, a.max_kv);
   const bool decode = max_qlen == 1;
   if (!decode && g_opt_attn_ts) return launch_attn_tc2(a, n_seqs, total_rows, cache_slots, max_qlen, st);   // prompt pass: P-in-TMEM kernel
+  if (decode && g_opt_attn_ts && attn_tc_decode_supported(a.hd, a.max_kv, a.qkv_dim, a.q_base, a.q_hstride))
+    return launch_attn_dec2(a, n_seqs, total_rows, cache_slots, st);                                          // one-token steps: small CTAs
   B2S_REQUIRE(!decode || attn_tc_decode_supported(a.hd, a.max_kv, a.qkv_dim, a.q_base, a.q_hstride),
               "attn_tc: one-token mode needs contiguous 64-wide query heads");
   static bool attr_set = false;

@@ -103,6 +103,85 @@ __device__ __forceinline__ bool a2_test(uint32_t bar, uint32_t parity) {   // no
   return ok != 0;
 }
 
+// One item for one thread (== tile row): wait for S, two passes over this row's S in tensor memory (max, then
+// exp / pack / store P over S), hand P to the issuer, wait for O, normalise and write 64 outputs.
+template <bool F16>
+__device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_live, int n_full, int n_p, int kvp, int limit, float sc,
+                                        uint32_t bar_s, uint32_t bar_p, uint32_t bar_o, uint32_t bar_e, uint32_t ph, bool valid,
+                                        uint16_t* out_row) {
+  const uint32_t t_o = t_lane + o_off;
+  a2_wait(bar_s, ph);
+  tcgen05_fence_after();
+  // pass 1: row maximum over the visible keys
+  float m = -INFINITY;
+  for (int c = 0; c < n_live; ++c) {
+    float v[32];
+    tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
+    if (c < n_full) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) m = fmaxf(m, v[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
+    }
+  }
+  const float ms = m * sc;
+  // pass 2: p = 2^(s*scale*log2e - max), rounded to 16 bits, two per column over the first half of S
+  float lsum = 0.f;
+  for (int c = 0; c < n_p; ++c) {
+    uint32_t pk[16];
+    if (c < n_live) {
+      float v[32];
+      tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
+      if (c < n_full) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float p0 = a2_ex2(fmaf(v[j], sc, -ms)), p1 = a2_ex2(fmaf(v[j + 1], sc, -ms));
+          lsum += p0 + p1;
+          pk[j >> 1] = pack16x2<F16>(p0, p1);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float p0 = (c * 32 + j <= limit) ? a2_ex2(fmaf(v[j], sc, -ms)) : 0.f;
+          const float p1 = (c * 32 + j + 1 <= limit) ? a2_ex2(fmaf(v[j + 1], sc, -ms)) : 0.f;
+          lsum += p0 + p1;
+          pk[j >> 1] = pack16x2<F16>(p0, p1);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) pk[j] = 0u;
+    }
+    if (c * 32 + 32 <= kvp) a2_tmem_st16(t_lane + static_cast<uint32_t>(c * 16), pk);
+    else a2_tmem_st8(t_lane + static_cast<uint32_t>(c * 16), pk);
+  }
+  a2_tmem_st_wait();
+  tcgen05_fence_before();
+  mbar_arrive(bar_p);
+  // epilogue of this item: O / rowsum
+  a2_wait(bar_o, ph);
+  tcgen05_fence_after();
+  float o0[32], o1[32];
+  tmem_ld32(t_o, o0);
+  tmem_ld32(t_o + 32, o1);
+  tcgen05_fence_before();
+  mbar_arrive(bar_e);                   // the lane's columns may be overwritten by the next S
+  if (valid) {
+    const float inv = 1.f / lsum;
+    uint4* dst = reinterpret_cast<uint4*>(out_row);
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
+                          pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
+                              pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
+  }
+}
+
 template <bool F16>
 __global__ void __launch_bounds__(A2_THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -219,7 +298,6 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int quad = warp & 3;                 // TMEM lane quadrant of this warp
     const int row = quad * 32 + lane;
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(l) * lane_cols;
-    const uint32_t t_o = t_lane + o_off;
     const bool valid = row < rows_here;
     const int limit = min(kl - 1, base_lim + row);              // last key this row may see
     const int lim_lo = min(kl - 1, base_lim + quad * 32);       // ... the first row of the warp
@@ -230,77 +308,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const float sc = p.scale_log2e;
     for (int i = l; i < n_items; i += nl) {
       const uint32_t ph = static_cast<uint32_t>(i / nl) & 1u;
-      a2_wait(bar_s(l), ph);
-      tcgen05_fence_after();
-      // pass 1: row maximum over the visible keys
-      float m = -INFINITY;
-      for (int c = 0; c < n_live; ++c) {
-        float v[32];
-        tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
-        if (c < n_full) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) m = fmaxf(m, v[j]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
-        }
-      }
-      const float ms = m * sc;
-      // pass 2: p = 2^(s*scale*log2e - max), rounded to 16 bits, two per column over the first half of S
-      float lsum = 0.f;
-      for (int c = 0; c < n_p; ++c) {
-        uint32_t pk[16];
-        if (c < n_live) {
-          float v[32];
-          tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
-          if (c < n_full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              const float p0 = a2_ex2(fmaf(v[j], sc, -ms)), p1 = a2_ex2(fmaf(v[j + 1], sc, -ms));
-              lsum += p0 + p1;
-              pk[j >> 1] = pack16x2<F16>(p0, p1);
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              const float p0 = (c * 32 + j <= limit) ? a2_ex2(fmaf(v[j], sc, -ms)) : 0.f;
-              const float p1 = (c * 32 + j + 1 <= limit) ? a2_ex2(fmaf(v[j + 1], sc, -ms)) : 0.f;
-              lsum += p0 + p1;
-              pk[j >> 1] = pack16x2<F16>(p0, p1);
-            }
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) pk[j] = 0u;
-        }
-        if (c * 32 + 32 <= kvp) a2_tmem_st16(t_lane + static_cast<uint32_t>(c * 16), pk);
-        else a2_tmem_st8(t_lane + static_cast<uint32_t>(c * 16), pk);
-      }
-      a2_tmem_st_wait();
-      tcgen05_fence_before();
-      mbar_arrive(bar_p(l));
-      // epilogue of this item: O / rowsum
-      a2_wait(bar_o(l), ph);
-      tcgen05_fence_after();
-      float o0[32], o1[32];
-      tmem_ld32(t_o, o0);
-      tmem_ld32(t_o + 32, o1);
-      tcgen05_fence_before();
-      mbar_arrive(bar_e(l));                   // the lane's columns may be overwritten by the next S
-      if (valid) {
-        const float inv = 1.f / lsum;
-        uint4* dst = reinterpret_cast<uint4*>(p.out + static_cast<size_t>(q0 + row) * (static_cast<size_t>(p.nh) * A2_HD) +
-                                              static_cast<size_t>(h_first + i) * A2_HD);
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
-                              pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
-                                  pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
-      }
+      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (static_cast<size_t>(p.nh) * A2_HD) + static_cast<size_t>(h_first + i) * A2_HD;
+      a2_item<F16>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst);
     }
   }
 
@@ -310,6 +319,153 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(A2_TMEM_COLS) : "memory");
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// One-token (look-ahead) steps: one CTA per (prompt, KV head); the rows of the tile are the query HEADS of the single
+// new token (the qkv row is read as a [heads, 64] matrix), no causal mask.  One item per CTA for <= 128 heads per KV
+// head, so the only parallelism is between CTAs: the CTA is made small (160 threads, K/V boxes of KVBOX keys, KVBOX
+// tensor-memory columns) so that 2 (KVBOX 256) or 4 (KVBOX 128) CTAs share an SM and hide each other's TMA / MMA /
+// barrier latencies.  The first-generation kernel ran this with one 209 KB CTA per SM.
+// ---------------------------------------------------------------------------------------------
+struct AttnDec2Params {
+  BatchMeta meta;
+  uint16_t* out;
+  int nh, nkv, rep;
+  int q_base;             // column of head 0 in the qkv row (multiple of 64)
+  int qrows_per_token;    // qkv_dim / 64
+  float scale_log2e;
+};
+
+template <int KVBOX> constexpr int dec2_smem() { return 2 * KVBOX * A2_HD * 2 + A2_Q_BYTES + 1024 + 128; }
+
+template <bool F16, int KVBOX>
+__global__ void __launch_bounds__(160, KVBOX == 128 ? 4 : 2)
+attn_dec2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, const AttnDec2Params p) {
+  constexpr uint32_t KV_BYTES = KVBOX * A2_HD * 2;
+  constexpr uint32_t O_OFF = KVBOX / 2;                 // P covers [0, KVBOX/2), O the 64 columns after it
+  const int seq = blockIdx.x, g = blockIdx.z;
+  const int q0 = p.meta.q_start[seq];
+  const int kv0 = p.meta.kv_start[seq];
+  const int kl = p.meta.kv_len[seq];
+  const int n_items = (p.rep + A2_BM - 1) / A2_BM;
+  const int kvp = (kl + 15) & ~15;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sK = base, sV = base + KV_BYTES, sQ = base + 2 * KV_BYTES;
+  const uint32_t bars = sQ + A2_Q_BYTES;
+  const uint32_t bar_kv = bars, bar_q = bars + 8, bar_s = bars + 16, bar_p = bars + 24, bar_o = bars + 32, bar_e = bars + 40;
+  const uint32_t tmem_slot = bars + 48;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 128) {
+    mbar_init(bar_kv, 1); mbar_init(bar_q, 1); mbar_init(bar_s, 1); mbar_init(bar_p, 128); mbar_init(bar_o, 1); mbar_init(bar_e, 128);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(static_cast<uint32_t>(KVBOX)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  const int h_first = g * p.rep;
+  if (warp == 4) {
+    if (lane == 0) {
+      auto load_q = [&](int i) {
+        mbar_arrive_expect_tx(bar_q, A2_Q_BYTES);
+        tma_load_2d(sQ, &tmQ, bar_q, 0, q0 * p.qrows_per_token + p.q_base / A2_HD + h_first + i * A2_BM);
+      };
+      mbar_arrive_expect_tx(bar_kv, 2 * KV_BYTES);
+      tma_load_2d(sK, &tmK, bar_kv, g * A2_HD, kv0);
+      tma_load_2d(sV, &tmV, bar_kv, g * A2_HD, kv0);
+      load_q(0);
+      a2_wait(bar_kv, 0);
+      const uint32_t idesc_s = a2_idesc(A2_BM, kvp, 0, F16);
+      const uint32_t idesc_o = a2_idesc(A2_BM, A2_HD, 1, F16);
+      const uint64_t kdesc = make_kmajor_sw128_desc(sK);
+      const uint64_t qdesc = make_kmajor_sw128_desc(sQ);
+      const uint64_t vdesc = a2_vdesc(sV);
+      for (int i = 0; i < n_items; ++i) {
+        const uint32_t ph = static_cast<uint32_t>(i) & 1u;
+        if (i > 0) a2_wait(bar_e, ph ^ 1u);             // O(i-1) read: the columns are free
+        a2_wait(bar_q, ph);
+        tcgen05_fence_after();
+#pragma unroll
+        for (int k = 0; k < A2_HD / 16; ++k)
+          tcgen05_mma_bf16(tmem_base, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
+        tcgen05_commit(bar_s);
+        a2_wait(bar_p, ph);                             // P(i) in tensor memory, S(i) (and so Q(i)) consumed
+        tcgen05_fence_after();
+        if (i + 1 < n_items) load_q(i + 1);
+        for (int ks = 0; ks < kvp / 16; ++ks)
+          a2_mma_ts(tmem_base + O_OFF, tmem_base + 8u * ks, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o, ks != 0 ? 1u : 0u);
+        tcgen05_commit(bar_o);
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    const int limit = kl - 1;                  // the new token sees every cached key, its own included
+    const int n_live = limit / 32 + 1;
+    const int n_full = kl / 32;
+    const int n_p = (kvp + 31) / 32;
+    for (int i = 0; i < n_items; ++i) {
+      const bool valid = row < min(A2_BM, p.rep - i * A2_BM);
+      uint16_t* dst = p.out + static_cast<size_t>(q0) * (static_cast<size_t>(p.nh) * A2_HD) +
+                      static_cast<size_t>(h_first + i * A2_BM + row) * A2_HD;
+      a2_item<F16>(t_lane, O_OFF, n_live, n_full, n_p, kvp, limit, p.scale_log2e, bar_s, bar_p, bar_o, bar_e,
+                   static_cast<uint32_t>(i) & 1u, valid, dst);
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(static_cast<uint32_t>(KVBOX)) : "memory");
+  }
+}
+
+template <bool F16, int KVBOX>
+static int launch_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_dec2_kernel<F16, KVBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, dec2_smem<KVBOX>()));
+    attr_set = true;
+  }
+  CUtensorMap tq, tk, tv;
+  const uint64_t rpt = static_cast<uint64_t>(a.qkv_dim / A2_HD);   // qkv viewed as [total_rows * qkv_dim/64, 64]
+  B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows) * rpt, A2_HD, A2_HD * 2, A2_BM, A2_HD, a.f16));
+  const uint64_t kvw = static_cast<uint64_t>(a.nkv) * A2_HD;
+  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, KVBOX, A2_HD, a.f16));
+  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, KVBOX, A2_HD, a.f16));
+  AttnDec2Params p;
+  p.meta = a.meta;
+  p.out = reinterpret_cast<uint16_t*>(a.out);
+  p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
+  p.q_base = a.q_base;
+  p.qrows_per_token = a.qkv_dim / A2_HD;
+  p.scale_log2e = a.scale * 1.4426950408889634f;
+  dim3 grid(n_seqs, 1, a.nkv);
+  attn_dec2_kernel<F16, KVBOX><<<grid, 160, dec2_smem<KVBOX>(), st>>>(tq, tk, tv, p);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+int launch_attn_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, cudaStream_t st) {
+  B2S_REQUIRE(attn_tc_decode_supported(a.hd, a.max_kv, a.qkv_dim, a.q_base, a.q_hstride),
+              "attn_dec2: needs head_dim 64, <= 256 keys and contiguous 64-wide query heads");
+  if (a.max_kv <= 128) return a.f16 ? launch_dec2<true, 128>(a, n_seqs, total_rows, cache_slots, st)
+                                    : launch_dec2<false, 128>(a, n_seqs, total_rows, cache_slots, st);
+  return a.f16 ? launch_dec2<true, 256>(a, n_seqs, total_rows, cache_slots, st)
+               : launch_dec2<false, 256>(a, n_seqs, total_rows, cache_slots, st);
 }
 
 int g_opt_attn_ts = 1;   // b2s_set_option("attn_ts"): 1 = this kernel for the prompt pass, 0 = attn_tc_kernel

@@ -924,6 +924,7 @@ extern int g_opt_attn_hold_s;
 extern int g_opt_attn_ts;
 int g_opt_tma_store = 1;   // 1: epilogue via shared memory + TMA bulk store / reduce-add; 0: per-thread global stores
 int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
+int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = rule off; b2s_set_option "gemm_small_w_group")
 int g_opt_serp = 1;        // b2s_set_option "gemm_serpentine"
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
 int g_opt_cta_group = 0;   // 0: per-launch policy (default); 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256; 3: CTA pairs on 512x256 (b2s_set_option "gemm_cta_group")
@@ -1028,7 +1029,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     while (gm > 16 && gm * mb_bytes > 40e6) gm >>= 1;
     // a W that can stay L2-resident by itself (qkv, dense: 42 MB) is better served by one-wave groups: the A panel
     // is then 9 MB and W is the only thing re-read (measured: profiles/r1_gemm_l2_hints.txt, DRAM 5.4 -> 4.1 GB on qkv)
-    if (2.0 * N * K <= 48e6) gm = 8;
+    if (g_opt_small_w_group > 0 && 2.0 * N * K <= 48e6) gm = g_opt_small_w_group;
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
     p.serp = g_opt_serp;
   }
@@ -1095,6 +1096,11 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_l2_hint") {
     B2S_REQUIRE(value >= 0 && value <= 7, "set_option: gemm_l2_hint must be in [0, 7]");
     b2s::g_opt_hint = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_small_w_group") {
+    B2S_REQUIRE(value >= 0 && value <= 1024, "set_option: gemm_small_w_group must be in [0, 1024]");
+    b2s::g_opt_small_w_group = value;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_serpentine") {

@@ -169,7 +169,7 @@ def _attn_ref(q, k, v, lens, kv_extra):
 
 @pytest.mark.parametrize("use_tc", [0, 1, 2], ids=["simt", "tc_p_in_tmem", "tc_p_in_smem"])
 @pytest.mark.parametrize("nh,nkv", [(71, 1), (4, 2), (3, 3)])
-@pytest.mark.parametrize("phase", ["prefill", "one_token"])
+@pytest.mark.parametrize("phase", ["prefill", "one_token", "one_token_short"])
 def test_attention_bf16(use_tc, nh, nkv, phase):
     """Ragged prefill batch (lengths 1..256, incl. exactly 128/129/192/193/256) + extra cached keys for some
     sequences; and the one-token (look-ahead) phase: every sequence has one query row and 1..256 cached keys."""
@@ -179,9 +179,12 @@ def test_attention_bf16(use_tc, nh, nkv, phase):
     if phase == "prefill":
         qlens = [1, 2, 17, 64, 127, 128, 129, 190, 256, 33, 100, 192, 193]
         extra = [0, 0, 3, 0, 0, 0, 0, 10, 0, 64, 28, 0, 0]      # keys already in the cache before the first query
-    else:
+    elif phase == "one_token":
         qlens = [1] * 12
         extra = [0, 1, 15, 16, 66, 110, 127, 128, 190, 191, 192, 255]
+    else:                                                       # every prompt <= 128 keys: the 4-CTAs-per-SM variant
+        qlens = [1] * 10
+        extra = [0, 1, 15, 16, 31, 32, 66, 110, 126, 127]
     slack = 10
     q_start, kv_start, t, c = [], [], 0, 0
     for ql, ex in zip(qlens, extra):
