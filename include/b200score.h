@@ -40,7 +40,8 @@ enum { B2S_QKV_FALCON_MQA = 0, B2S_QKV_NEOX_INTERLEAVED = 1 };
  *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5). */
 enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_FP32_CHECK = 3 };
 
-/* weight_ptrs slots: 6 global + 16 per layer (see llm_interpretation_replication_b200/weights.py) */
+/* weight_ptrs slots: 6 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
+ * pointer must be 16-byte aligned (B2S_EINVAL otherwise) */
 enum { B2S_W_WTE = 0, B2S_W_LNF_G = 1, B2S_W_LNF_B = 2, B2S_W_LM_HEAD = 3, B2S_W_ROPE_COS = 4,
        B2S_W_ROPE_SIN = 5, B2S_W_NGLOBAL = 6, B2S_W_PER_LAYER = 16 };
 enum { B2S_WL_LN1_G = 0, B2S_WL_LN1_B, B2S_WL_LN2_G, B2S_WL_LN2_B, B2S_WL_W_QKV, B2S_WL_B_QKV,
@@ -90,6 +91,23 @@ B2S_API int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seq
  * reference-side binding makes and the one bench.py times as "e2e". */
 B2S_API int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_seqlens_h, int32_t n_seqs,
                    const int32_t* cand_ids_h, int32_t topk, int32_t max_lookahead, int32_t eos_id,
+                   float* out_h, int32_t* gen_ids_h /*or NULL*/,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* Score + complete ("next" row N1 of SURVEY.md 8f): the reference always generates max_new_tokens=50 and scans only
+ * the first 10 positions (run_base_vs_instruct_100q.py:338-346,348-363,365-368; compare_instruct_models.py:274,290).
+ * Same as b2s_score / b2s_score_host, except that greedy decoding continues to gen_tokens (>= scan_positions, <= 64)
+ * for every prompt that has not produced eos_id, whether or not it is already resolved; the top-k membership scan
+ * still covers positions < scan_positions only.  gen_ids is [N, gen_tokens] (-1 after EOS); the workspace must be
+ * sized with b2s_workspace_bytes(..., max_lookahead = gen_tokens).  b2s_score(max_lookahead) ==
+ * b2s_score_complete(scan_positions = gen_tokens = max_lookahead). */
+B2S_API int b2s_score_complete(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs,
+              int32_t total_tokens, int32_t max_seqlen, const int32_t* cand_ids /*[N,2]*/,
+              int32_t topk, int32_t scan_positions, int32_t gen_tokens, int32_t eos_id,
+              float* out /*[N,8]*/, int32_t* gen_ids /*[N,gen_tokens] or NULL*/,
+              void* workspace, size_t workspace_bytes, void* stream);
+B2S_API int b2s_score_complete_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_seqlens_h, int32_t n_seqs,
+                   const int32_t* cand_ids_h, int32_t topk, int32_t scan_positions, int32_t gen_tokens, int32_t eos_id,
                    float* out_h, int32_t* gen_ids_h /*or NULL*/,
                    void* workspace, size_t workspace_bytes, void* stream);
 

@@ -45,6 +45,15 @@ int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const Ba
 //   mean, biased variance, (x-mean)*rsqrt(var+eps)*g+b, all in fp32.
 // One CTA per row; the row lives in shared memory between the two passes.
 // =================================================================================================
+__device__ __forceinline__ void store4(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float a, float b, float c, float d) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(a, b), pack_bf16x2(c, d));
+}
+__device__ __forceinline__ void store4(__half* p, float a, float b, float c, float d) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(pack_f16x2(a, b), pack_f16x2(c, d));
+}
 __device__ __forceinline__ float block_sum(float v, float* red) {
   v = warp_sum(v);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -81,15 +90,32 @@ ln_kernel(LnArgs a) {
     }
   }
   const float mean = block_sum(sum, red) / d;
+  // passes 2 and 3 walk the row four elements at a time (d % 4 == 0): 16-byte smem / gain / bias loads, 8-byte
+  // (16-bit outputs) or 16-byte (fp32) stores
+  const float4* s4 = reinterpret_cast<const float4*>(srow);
+  const int d4 = d >> 2;
   float sq = 0.f;
-  for (int i = threadIdx.x; i < d; i += blockDim.x) { const float c = srow[i] - mean; sq += c * c; }
+  for (int i = threadIdx.x; i < d4; i += blockDim.x) {
+    const float4 v = s4[i];
+    const float c0 = v.x - mean, c1 = v.y - mean, c2 = v.z - mean, c3 = v.w - mean;
+    sq += (c0 * c0 + c1 * c1) + (c2 * c2 + c3 * c3);
+  }
   const float rstd = rsqrtf(block_sum(sq, red) / d + a.eps);
   AT* y1 = reinterpret_cast<AT*>(a.y1) + static_cast<size_t>(orow) * d;
   AT* y2 = a.y2 ? reinterpret_cast<AT*>(a.y2) + static_cast<size_t>(orow) * d : nullptr;
-  for (int i = threadIdx.x; i < d; i += blockDim.x) {
-    const float n = (srow[i] - mean) * rstd;
-    y1[i] = from_f32<AT>(n * a.g1[i] + a.b1[i]);
-    if (y2) y2[i] = from_f32<AT>(n * a.g2[i] + a.b2[i]);
+  const float4* g1 = reinterpret_cast<const float4*>(a.g1);
+  const float4* b1 = reinterpret_cast<const float4*>(a.b1);
+  const float4* g2 = reinterpret_cast<const float4*>(a.g2);
+  const float4* b2 = reinterpret_cast<const float4*>(a.b2);
+  for (int i = threadIdx.x; i < d4; i += blockDim.x) {
+    const float4 v = s4[i];
+    const float n0 = (v.x - mean) * rstd, n1 = (v.y - mean) * rstd, n2 = (v.z - mean) * rstd, n3 = (v.w - mean) * rstd;
+    const float4 g = g1[i], b = b1[i];
+    store4(y1 + 4 * i, n0 * g.x + b.x, n1 * g.y + b.y, n2 * g.z + b.z, n3 * g.w + b.w);
+    if (y2) {
+      const float4 h = g2[i], c = b2[i];
+      store4(y2 + 4 * i, n0 * h.x + c.x, n1 * h.y + c.y, n2 * h.z + c.z, n3 * h.w + c.w);
+    }
   }
 }
 
@@ -168,7 +194,9 @@ template int launch_rope_cache<__half>(const RopeArgs&, int, cudaStream_t);
 // each warp then owns (query, head) items: lanes split keys for Q.K^T, exchange the softmax statistics
 // with shuffles, and split head dims for P.V.
 // =================================================================================================
-template <typename AT, int HD>
+// KV_GLOBAL: the prompt's K/V do not fit in shared memory as fp32 (e.g. head_dim 128 with more than 215 keys: a
+// 190-token prompt plus a 50-token completion); keys and values are then read from global memory (L2) instead.
+template <typename AT, int HD, bool KV_GLOBAL>
 __global__ void __launch_bounds__(ATT_THREADS)
 attn_kernel(AttnArgs a) {
   constexpr int HDP = HD + 4;              // padded row (floats)
@@ -183,19 +211,22 @@ attn_kernel(AttnArgs a) {
   const int nh_here = min(HG, a.rep - hg * HG);
   const int q0 = a.meta.q_start[seq], ql = a.meta.q_len[seq];
   const int kv0 = a.meta.kv_start[seq], kl = a.meta.kv_len[seq];
+  const size_t kv_rows = KV_GLOBAL ? 0 : static_cast<size_t>(a.max_kv);
   float* sK = smem;
-  float* sV = sK + static_cast<size_t>(a.max_kv) * HDP;
-  float* sQ = sV + static_cast<size_t>(a.max_kv) * HDP;     // [warps][HD]
+  float* sV = sK + kv_rows * HDP;
+  float* sQ = sV + kv_rows * HDP;                           // [warps][HD]
   float* sP = sQ + (ATT_THREADS / 32) * HD;                 // [warps][32]
   const AT* kc = reinterpret_cast<const AT*>(a.kcache) + (static_cast<size_t>(kv0) * a.nkv + g) * HD;
   const AT* vc = reinterpret_cast<const AT*>(a.vcache) + (static_cast<size_t>(kv0) * a.nkv + g) * HD;
   const size_t kv_stride = static_cast<size_t>(a.nkv) * HD;
-  for (int idx = threadIdx.x; idx < kl * HD; idx += blockDim.x) {
-    const int j = idx / HD, dd = idx - j * HD;
-    sK[j * HDP + dd] = to_f32(kc[j * kv_stride + dd]);
-    sV[j * HDP + dd] = to_f32(vc[j * kv_stride + dd]);
+  if (!KV_GLOBAL) {
+    for (int idx = threadIdx.x; idx < kl * HD; idx += blockDim.x) {
+      const int j = idx / HD, dd = idx - j * HD;
+      sK[j * HDP + dd] = to_f32(kc[j * kv_stride + dd]);
+      sV[j * HDP + dd] = to_f32(vc[j * kv_stride + dd]);
+    }
+    __syncthreads();
   }
-  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
   float* q = sQ + warp * HD;
   float* pbuf = sP + warp * 32;
@@ -217,14 +248,24 @@ attn_kernel(AttnArgs a) {
       const int j = j0 + lane;
       float s = -INFINITY;
       if (j < nkeys) {
-        const float4* kr = reinterpret_cast<const float4*>(sK + j * HDP);
         const float4* qr = reinterpret_cast<const float4*>(q);
         float d0 = 0.f, d1 = 0.f;
+        if (KV_GLOBAL) {
+          const AT* kg = kc + static_cast<size_t>(j) * kv_stride;
 #pragma unroll
-        for (int c = 0; c < HD / 4; ++c) {
-          const float4 kk = kr[c], qq = qr[c];
-          d0 = fmaf(kk.x, qq.x, d0); d1 = fmaf(kk.y, qq.y, d1);
-          d0 = fmaf(kk.z, qq.z, d0); d1 = fmaf(kk.w, qq.w, d1);
+          for (int c = 0; c < HD / 4; ++c) {      // same summation order as the shared-memory path
+            const float4 qq = qr[c];
+            d0 = fmaf(to_f32(kg[4 * c]), qq.x, d0); d1 = fmaf(to_f32(kg[4 * c + 1]), qq.y, d1);
+            d0 = fmaf(to_f32(kg[4 * c + 2]), qq.z, d0); d1 = fmaf(to_f32(kg[4 * c + 3]), qq.w, d1);
+          }
+        } else {
+          const float4* kr = reinterpret_cast<const float4*>(sK + j * HDP);
+#pragma unroll
+          for (int c = 0; c < HD / 4; ++c) {
+            const float4 kk = kr[c], qq = qr[c];
+            d0 = fmaf(kk.x, qq.x, d0); d1 = fmaf(kk.y, qq.y, d1);
+            d0 = fmaf(kk.z, qq.z, d0); d1 = fmaf(kk.w, qq.w, d1);
+          }
         }
         s = d0 + d1;
       }
@@ -241,7 +282,11 @@ attn_kernel(AttnArgs a) {
         const int dd = lane + 32 * r;
         float o = acc[r] * corr;
         if (dd < HD) {
-          for (int jj = 0; jj < cnt; ++jj) o = fmaf(pbuf[jj], sV[(j0 + jj) * HDP + dd], o);
+          if (KV_GLOBAL) {
+            for (int jj = 0; jj < cnt; ++jj) o = fmaf(pbuf[jj], to_f32(vc[static_cast<size_t>(j0 + jj) * kv_stride + dd]), o);
+          } else {
+            for (int jj = 0; jj < cnt; ++jj) o = fmaf(pbuf[jj], sV[(j0 + jj) * HDP + dd], o);
+          }
         }
         acc[r] = o;
       }
@@ -265,17 +310,20 @@ int launch_attn(const AttnArgs& a_in, int n_seqs, cudaStream_t st) {
   if (a.heads_per_cta <= 0) a.heads_per_cta = ATT_HG;
   if (a.heads_per_cta > a.rep) a.heads_per_cta = a.rep;
   const int hd = a.hd;
-  const size_t smem = (2 * static_cast<size_t>(a.max_kv) * (hd + 4) + (ATT_THREADS / 32) * (hd + 32)) * sizeof(float);
-  B2S_REQUIRE(smem <= 227 * 1024,
-              "attention: a sequence of %d keys (head_dim %d) needs %zu bytes of shared memory; the limit is %d keys",
-              a.max_kv, hd, smem, static_cast<int>((227 * 1024 / sizeof(float) - (ATT_THREADS / 32) * (hd + 32)) / (2 * (hd + 4))));
+  size_t smem = (2 * static_cast<size_t>(a.max_kv) * (hd + 4) + (ATT_THREADS / 32) * (hd + 32)) * sizeof(float);
+  const bool kv_global = smem > 227 * 1024;     // K/V too long to stage: read them through L2
+  if (kv_global) smem = static_cast<size_t>(ATT_THREADS / 32) * (hd + 32) * sizeof(float);
   const int groups_per_kv = (a.rep + a.heads_per_cta - 1) / a.heads_per_cta;
   dim3 grid(n_seqs, a.nkv * groups_per_kv);
 #define B2S_ATT_CASE(HDV)                                                                                         \
   case HDV:                                                                                                      \
-    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_kernel<AT, HDV>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
-                                        static_cast<int>(smem)));                                                 \
-    attn_kernel<AT, HDV><<<grid, ATT_THREADS, smem, st>>>(a);                                                     \
+    if (kv_global) {                                                                                             \
+      attn_kernel<AT, HDV, true><<<grid, ATT_THREADS, smem, st>>>(a);                                            \
+    } else {                                                                                                     \
+      B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_kernel<AT, HDV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                          static_cast<int>(smem)));                                               \
+      attn_kernel<AT, HDV, false><<<grid, ATT_THREADS, smem, st>>>(a);                                           \
+    }                                                                                                            \
     break;
   switch (hd) {
     B2S_ATT_CASE(64)
@@ -410,14 +458,14 @@ int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, 
 //   - first alive position where either candidate logit is >= the k-th largest logit wins;
 //   - otherwise the position-0 probabilities stand.
 __global__ void scan_update_kernel(const float* __restrict__ stats, int n, int pos, int topk, int eos_id,
-                                   int lookahead, ScanState s) {
+                                   int scan_positions, int gen_tokens, ScanState s) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float* r = stats + static_cast<size_t>(i) * LMH_STATS;
   const int arg = reinterpret_cast<const int*>(r)[15];
   int alive = (pos == 0) ? 1 : s.alive[i];
   int resolved = (pos == 0) ? 0 : s.resolved[i];
-  if (alive && !resolved) {
+  if (alive && !resolved && pos < scan_positions) {
     const float lse = r[0], la = r[7], lb = r[8], kth = r[topk];   // r[1..5] = top1..top5
     const float pa = expf(la - lse), pb = expf(lb - lse);
     const bool hit = (la >= kth) || (lb >= kth);
@@ -428,16 +476,18 @@ __global__ void scan_update_kernel(const float* __restrict__ stats, int n, int p
     }
     if (hit) resolved = 1;
   }
-  if (s.gen_ids) s.gen_ids[static_cast<size_t>(i) * lookahead + pos] = alive ? arg : -1;
+  if (s.gen_ids) s.gen_ids[static_cast<size_t>(i) * gen_tokens + pos] = alive ? arg : -1;
   s.next_tok[i] = arg;
   if (alive && arg == eos_id) alive = 0;
   s.alive[i] = alive; s.resolved[i] = resolved;
-  if (alive && !resolved) atomicAdd(s.n_active, 1);
+  // another step is needed while a prompt is unresolved (scoring only), or, in completion mode (gen_tokens >
+  // scan_positions: the reference's max_new_tokens=50), while it has not produced EOS
+  if (alive && (gen_tokens > scan_positions ? pos + 1 < gen_tokens : !resolved)) atomicAdd(s.n_active, 1);
 }
 
-int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int lookahead, const ScanState& s,
-                       cudaStream_t st) {
-  scan_update_kernel<<<static_cast<unsigned>(ceil_div(n, 128)), 128, 0, st>>>(stats, n, pos, topk, eos_id, lookahead, s);
+int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int scan_positions, int gen_tokens,
+                       const ScanState& s, cudaStream_t st) {
+  scan_update_kernel<<<static_cast<unsigned>(ceil_div(n, 128)), 128, 0, st>>>(stats, n, pos, topk, eos_id, scan_positions, gen_tokens, s);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }

@@ -71,7 +71,7 @@ int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const 
                                        float* cand_logits, cudaStream_t st);
 int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, int tiles_n, float* stats,
                         cudaStream_t st);
-int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int lookahead, const ScanState& s,
-                       cudaStream_t st);
+int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int scan_positions, int gen_tokens,
+                       const ScanState& s, cudaStream_t st);
 
 }  // namespace b2s

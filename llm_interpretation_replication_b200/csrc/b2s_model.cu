@@ -258,6 +258,8 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   B2S_REQUIRE(d.d_model % 8 == 0 && d.d_ff % 8 == 0, "model_create: d_model and d_ff must be multiples of 8");
   const int need = B2S_W_NGLOBAL + B2S_W_PER_LAYER * d.n_layer;
   B2S_REQUIRE(n_ptrs >= need, "model_create: %d weight pointers given, %d needed", n_ptrs, need);
+  for (int i = 0; i < need; ++i)   // TMA descriptors and the vectorised LayerNorm need 16-byte aligned tensors (null = absent)
+    B2S_REQUIRE((reinterpret_cast<uintptr_t>(weight_ptrs[i]) & 15u) == 0, "model_create: weight pointer %d is not 16-byte aligned", i);
   int ndev = 0;
   B2S_CHECK_CUDA(cudaGetDeviceCount(&ndev));
   B2S_REQUIRE(device >= 0 && device < ndev, "model_create: device %d out of range (%d visible)", device, ndev);
@@ -311,55 +313,66 @@ size_t b2s_workspace_bytes(const b2s_model* m, int64_t max_tokens, int32_t max_s
   return carve(m, max_tokens, max_seqs, max_lookahead, nullptr).total + 256;
 }
 
-int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs, int32_t total_tokens,
-              int32_t max_seqlen, const int32_t* cand_ids, int32_t topk, int32_t max_lookahead, int32_t eos_id, float* out,
-              int32_t* gen_ids, void* workspace, size_t workspace_bytes, void* stream) {
+int b2s_score_complete(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs, int32_t total_tokens,
+                       int32_t max_seqlen, const int32_t* cand_ids, int32_t topk, int32_t scan_positions, int32_t gen_tokens,
+                       int32_t eos_id, float* out, int32_t* gen_ids, void* workspace, size_t workspace_bytes, void* stream) {
   B2S_REQUIRE(m && tokens && cu_seqlens && cand_ids && out && workspace, "score: null argument");
   B2S_REQUIRE(n_seqs > 0 && total_tokens >= n_seqs && max_seqlen > 0, "score: empty batch (n_seqs=%d total_tokens=%d)", n_seqs,
               total_tokens);
   B2S_REQUIRE(topk >= 1 && topk <= 5, "score: topk=%d outside [1,5]", topk);
-  B2S_REQUIRE(max_lookahead >= 1 && max_lookahead <= 64, "score: max_lookahead=%d outside [1,64]", max_lookahead);
-  B2S_REQUIRE(max_seqlen + max_lookahead <= m->d.max_pos, "score: prompt of %d tokens + %d look-ahead exceeds max_pos %d",
-              max_seqlen, max_lookahead, m->d.max_pos);
+  B2S_REQUIRE(scan_positions >= 1 && scan_positions <= 64, "score: max_lookahead=%d outside [1,64]", scan_positions);
+  B2S_REQUIRE(gen_tokens >= scan_positions && gen_tokens <= 64, "score: gen_tokens=%d outside [max_lookahead=%d, 64]", gen_tokens,
+              scan_positions);
+  B2S_REQUIRE(max_seqlen + gen_tokens <= m->d.max_pos, "score: prompt of %d tokens + %d generated exceeds max_pos %d",
+              max_seqlen, gen_tokens, m->d.max_pos);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   uint8_t* base = reinterpret_cast<uint8_t*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
-  Workspace w = carve(m, total_tokens, n_seqs, max_lookahead, base);
+  Workspace w = carve(m, total_tokens, n_seqs, gen_tokens, base);
   B2S_REQUIRE(w.total + (base - reinterpret_cast<uint8_t*>(workspace)) <= workspace_bytes,
               "score: workspace of %zu bytes is too small, %zu needed", workspace_bytes, w.total + 256);
   B2S_CHECK_CUDA(cudaSetDevice(m->device));
   w.scan.out = out;
   w.scan.gen_ids = gen_ids;
-  if (gen_ids) B2S_CHECK_CUDA(cudaMemsetAsync(gen_ids, 0xFF, 4 * static_cast<size_t>(n_seqs) * max_lookahead, st));
+  if (gen_ids) B2S_CHECK_CUDA(cudaMemsetAsync(gen_ids, 0xFF, 4 * static_cast<size_t>(n_seqs) * gen_tokens, st));
 
   // The tensor-core attention kernel loads whole 256-slot K/V boxes; slots it masks out must hold finite
   // numbers (0 * NaN would poison P.V), so the cache starts from zeros on every call.
   B2S_CHECK_CUDA(cudaMemsetAsync(w.kcache, 0, w.cache_layer_bytes * m->d.n_layer, st));
   B2S_CHECK_CUDA(cudaMemsetAsync(w.vcache, 0, w.cache_layer_bytes * m->d.n_layer, st));
-  B2S_TRY(launch_prep(cu_seqlens, n_seqs, max_lookahead, 0, w.meta, st));
+  B2S_TRY(launch_prep(cu_seqlens, n_seqs, gen_tokens, 0, w.meta, st));
   B2S_TRY(forward(m, w, tokens, total_tokens, n_seqs, max_seqlen, max_seqlen, st));
   B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
   B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
-  B2S_TRY(launch_scan_update(w.stats, n_seqs, 0, topk, eos_id, max_lookahead, w.scan, st));
-  for (int step = 1; step < max_lookahead; ++step) {
+  B2S_TRY(launch_scan_update(w.stats, n_seqs, 0, topk, eos_id, scan_positions, gen_tokens, w.scan, st));
+  for (int step = 1; step < gen_tokens; ++step) {
     int32_t active = 0;
     B2S_CHECK_CUDA(cudaMemcpyAsync(&active, w.scan.n_active, 4, cudaMemcpyDeviceToHost, st));
     B2S_CHECK_CUDA(cudaStreamSynchronize(st));
     if (active == 0) break;
-    B2S_TRY(launch_prep(cu_seqlens, n_seqs, max_lookahead, step, w.meta, st));
+    B2S_TRY(launch_prep(cu_seqlens, n_seqs, gen_tokens, step, w.meta, st));
     B2S_TRY(forward(m, w, w.scan.next_tok, n_seqs, n_seqs, max_seqlen + step, 1, st));
     B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
     B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
-    B2S_TRY(launch_scan_update(w.stats, n_seqs, step, topk, eos_id, max_lookahead, w.scan, st));
+    B2S_TRY(launch_scan_update(w.stats, n_seqs, step, topk, eos_id, scan_positions, gen_tokens, w.scan, st));
   }
   return B2S_OK;
 }
 
-int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_h, int32_t n_seqs, const int32_t* cand_h,
-                   int32_t topk, int32_t max_lookahead, int32_t eos_id, float* out_h, int32_t* gen_h, void* workspace,
-                   size_t workspace_bytes, void* stream) {
+int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs, int32_t total_tokens,
+              int32_t max_seqlen, const int32_t* cand_ids, int32_t topk, int32_t max_lookahead, int32_t eos_id, float* out,
+              int32_t* gen_ids, void* workspace, size_t workspace_bytes, void* stream) {
+  return b2s_score_complete(m, tokens, cu_seqlens, n_seqs, total_tokens, max_seqlen, cand_ids, topk, max_lookahead, max_lookahead,
+                            eos_id, out, gen_ids, workspace, workspace_bytes, stream);
+}
+
+int b2s_score_complete_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_h, int32_t n_seqs, const int32_t* cand_h,
+                            int32_t topk, int32_t scan_positions, int32_t gen_tokens, int32_t eos_id, float* out_h,
+                            int32_t* gen_h, void* workspace, size_t workspace_bytes, void* stream) {
   B2S_REQUIRE(m && tokens_h && cu_h && cand_h && out_h && workspace, "score_host: null argument");
   B2S_REQUIRE(n_seqs > 0, "score_host: empty batch");
-  B2S_REQUIRE(max_lookahead >= 1 && max_lookahead <= 64, "score_host: max_lookahead=%d outside [1,64]", max_lookahead);
+  B2S_REQUIRE(scan_positions >= 1 && scan_positions <= 64, "score_host: max_lookahead=%d outside [1,64]", scan_positions);
+  B2S_REQUIRE(gen_tokens >= scan_positions && gen_tokens <= 64, "score_host: gen_tokens=%d outside [max_lookahead=%d, 64]",
+              gen_tokens, scan_positions);
   int64_t total = cu_h[n_seqs];
   int max_len = 0;
   B2S_REQUIRE(cu_h[0] == 0, "score_host: cu_seqlens[0] must be 0");
@@ -375,7 +388,7 @@ int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_h, i
     B2S_REQUIRE(cand_h[i] >= 0 && cand_h[i] < m->d.vocab, "score_host: candidate id %d outside the vocabulary", cand_h[i]);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   uint8_t* base = reinterpret_cast<uint8_t*>(align_up(reinterpret_cast<uintptr_t>(workspace), 256));
-  Workspace w = carve(m, total, n_seqs, max_lookahead, base);
+  Workspace w = carve(m, total, n_seqs, gen_tokens, base);
   B2S_REQUIRE(w.total + 256 <= workspace_bytes, "score_host: workspace of %zu bytes is too small, %zu needed", workspace_bytes,
               w.total + 256);
   B2S_CHECK_CUDA(cudaSetDevice(m->device));
@@ -383,13 +396,20 @@ int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_h, i
   B2S_CHECK_CUDA(cudaMemcpyAsync(w.cu, cu_h, 4 * (n_seqs + 1), cudaMemcpyHostToDevice, st));
   B2S_CHECK_CUDA(cudaMemcpyAsync(w.cand, cand_h, 8 * n_seqs, cudaMemcpyHostToDevice, st));
   // During the prefill the token buffer is only read by layer 0; decode steps read scan.next_tok.
-  B2S_TRY(b2s_score(m, w.tokens, w.cu, n_seqs, static_cast<int32_t>(total), max_len, w.cand, topk, max_lookahead, eos_id, w.out,
-                    gen_h ? w.gen : nullptr, workspace, workspace_bytes, stream));
+  B2S_TRY(b2s_score_complete(m, w.tokens, w.cu, n_seqs, static_cast<int32_t>(total), max_len, w.cand, topk, scan_positions,
+                             gen_tokens, eos_id, w.out, gen_h ? w.gen : nullptr, workspace, workspace_bytes, stream));
   B2S_CHECK_CUDA(cudaMemcpyAsync(out_h, w.out, 32 * static_cast<size_t>(n_seqs), cudaMemcpyDeviceToHost, st));
   if (gen_h)
-    B2S_CHECK_CUDA(cudaMemcpyAsync(gen_h, w.gen, 4 * static_cast<size_t>(n_seqs) * max_lookahead, cudaMemcpyDeviceToHost, st));
+    B2S_CHECK_CUDA(cudaMemcpyAsync(gen_h, w.gen, 4 * static_cast<size_t>(n_seqs) * gen_tokens, cudaMemcpyDeviceToHost, st));
   B2S_CHECK_CUDA(cudaStreamSynchronize(st));
   return B2S_OK;
+}
+
+int b2s_score_host(b2s_model* m, const int32_t* tokens_h, const int32_t* cu_h, int32_t n_seqs, const int32_t* cand_h,
+                   int32_t topk, int32_t max_lookahead, int32_t eos_id, float* out_h, int32_t* gen_h, void* workspace,
+                   size_t workspace_bytes, void* stream) {
+  return b2s_score_complete_host(m, tokens_h, cu_h, n_seqs, cand_h, topk, max_lookahead, max_lookahead, eos_id, out_h, gen_h,
+                                 workspace, workspace_bytes, stream);
 }
 
 // ---- building blocks ------------------------------------------------------------------------------

@@ -12,6 +12,10 @@ from .. import shapes, weights
 from ..scorer import Scorer
 from ..tokenizer import HashTokenizer
 
+# The reference always generates max_new_tokens=50 (run_base_vs_instruct_100q.py:338-346, compare_instruct_models.py:
+# 274) and decodes them into the `completion` / `model_output` columns; only the first 10 positions are scanned.
+COMPLETION_TOKENS = int(os.environ.get("B2S_COMPLETION_TOKENS", "50"))
+
 DATA_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data")
 
 # reference analysis/run_base_vs_instruct_100q.py:455-461
@@ -73,7 +77,9 @@ def load_model(model_name: str, device=None, mode=shapes.MODE_FP16, n_layer: int
     device = torch.device(device if device is not None else "cuda:0")
     dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
     W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
-    scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs)
+    from ..scorer import MAX_LOOK_AHEAD
+    scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs,
+                    max_lookahead=max(MAX_LOOK_AHEAD, COMPLETION_TOKENS))
     tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
     return scorer, tok
 

@@ -20,7 +20,7 @@ import pandas as pd
 from .. import scorer as S
 import torch
 
-from .common import format_baichuan, format_instruct, load_model, log_print, maybe_init_dist, survey_questions, unload
+from .common import COMPLETION_TOKENS, format_baichuan, format_instruct, load_model, log_print, maybe_init_dist, survey_questions, unload
 
 models = [
     "allenai/tk-instruct-3b-def",
@@ -61,7 +61,8 @@ def run(prompts, model_names=None, n_layer=0, device=None, shard_group=None):
             scorer, tok = load_model(model_name, device=device, n_layer=n_layer)
             fmt = format_baichuan if "baichuan" in model_name.lower() else format_instruct
             formatted = [fmt(p) for p in prompts]
-            rows = S.score_prompts(scorer, tok, formatted, variant="instruct", shard_group=shard_group)
+            rows = S.score_prompts(scorer, tok, formatted, variant="instruct", shard_group=shard_group,
+                                   gen_tokens=COMPLETION_TOKENS)
             for p, r in zip(prompts, rows):
                 outputs[model_name][p] = r
         except Exception as e:

@@ -19,7 +19,7 @@ import numpy as np
 import pandas as pd
 
 from .. import bootstrap, scorer as S
-from .common import format_base, format_instruct, load_model, log_print, survey_questions, unload
+from .common import COMPLETION_TOKENS, format_base, format_instruct, load_model, log_print, survey_questions, unload
 
 OUTPUT_DIR = os.environ.get("B2S_OUTPUT_DIR", "llm_interpretation_out")
 CHECKPOINT_NAME = "base_vs_instruct_100q_checkpoint.json"
@@ -53,7 +53,7 @@ def run_model_on_prompts(model_name, prompts, is_base_model=True, n_layer=0, dev
     try:
         scorer, tok = load_model(model_name, device=device, n_layer=n_layer)
         formatted = [format_base(p) if is_base_model else format_instruct(p) for p in prompts]
-        rows = S.score_prompts(scorer, tok, formatted, variant="100q")
+        rows = S.score_prompts(scorer, tok, formatted, variant="100q", gen_tokens=COMPLETION_TOKENS)
         for p, f, r in zip(prompts, formatted, rows):
             r["prompt"] = p
             r["model"] = model_name

@@ -138,14 +138,21 @@ class Scorer:
 
     # ---- scoring ----------------------------------------------------------------------------
     def score_batch_host(self, t_tok, t_cu, t_cand, topk: int, max_lookahead: int, eos_id: int,
-                         out: torch.Tensor, gen: Optional[torch.Tensor]):
-        """One C-ABI call with host buffers (H2D + compute + D2H + sync inside)."""
+                         out: torch.Tensor, gen: Optional[torch.Tensor], gen_tokens: Optional[int] = None):
+        """One C-ABI call with host buffers (H2D + compute + D2H + sync inside).  With ``gen_tokens`` greedy decoding
+        continues past the scan window (b2s_score_complete_host) and ``gen`` is [n, gen_tokens]."""
         n = t_cu.numel() - 1
         with torch.cuda.device(self.device):
-            _lib.check(self.lib.b2s_score_host(self._handle, _lib.ptr(t_tok), _lib.ptr(t_cu), n, _lib.ptr(t_cand),
-                                               topk, max_lookahead, eos_id, _lib.ptr(out), _lib.ptr(gen),
-                                               _lib.ptr(self.workspace), self.workspace_bytes, _lib.current_stream()),
-                       "b2s_score_host")
+            if gen_tokens is None or gen_tokens == max_lookahead:
+                _lib.check(self.lib.b2s_score_host(self._handle, _lib.ptr(t_tok), _lib.ptr(t_cu), n, _lib.ptr(t_cand),
+                                                   topk, max_lookahead, eos_id, _lib.ptr(out), _lib.ptr(gen),
+                                                   _lib.ptr(self.workspace), self.workspace_bytes, _lib.current_stream()),
+                           "b2s_score_host")
+            else:
+                _lib.check(self.lib.b2s_score_complete_host(self._handle, _lib.ptr(t_tok), _lib.ptr(t_cu), n, _lib.ptr(t_cand),
+                                                            topk, max_lookahead, gen_tokens, eos_id, _lib.ptr(out), _lib.ptr(gen),
+                                                            _lib.ptr(self.workspace), self.workspace_bytes,
+                                                            _lib.current_stream()), "b2s_score_complete_host")
 
     def score_batch_device(self, d_tok, d_cu, d_cand, n: int, total: int, max_len: int, topk: int, max_lookahead: int,
                            eos_id: int, d_out: torch.Tensor, d_gen: Optional[torch.Tensor]):
@@ -157,12 +164,17 @@ class Scorer:
                        "b2s_score")
 
     def score_ids(self, id_lists: Sequence[Sequence[int]], cand_pairs, topk: int = 5,
-                  max_lookahead: int = MAX_LOOK_AHEAD, eos_id: Optional[int] = None):
-        """Score already-tokenised prompts.  Returns (rows [N,8] float32, gen_ids [N,max_lookahead] int32) in the
-        callers' order.  rows: p_a, p_b, rel, lse, logit_a, logit_b, pos_found, found."""
+                  max_lookahead: int = MAX_LOOK_AHEAD, eos_id: Optional[int] = None, gen_tokens: Optional[int] = None):
+        """Score already-tokenised prompts.  Returns (rows [N,8] float32, gen_ids [N,G] int32) in the callers' order.
+        rows: p_a, p_b, rel, lse, logit_a, logit_b, pos_found, found.  G = ``max_lookahead``, or ``gen_tokens`` when
+        given: the reference's max_new_tokens (50), generated for every prompt up to EOS while only the first
+        ``max_lookahead`` positions are scanned (run_base_vs_instruct_100q.py:338-363)."""
         N = len(id_lists)
+        G = max_lookahead if gen_tokens is None else int(gen_tokens)
+        if G < max_lookahead:
+            raise ValueError(f"gen_tokens {G} < max_lookahead {max_lookahead}")
         if N == 0:   # empty input: nothing to do (the reference loop would simply not execute)
-            return np.zeros((0, 8), np.float32), np.zeros((0, max_lookahead), np.int32)
+            return np.zeros((0, 8), np.float32), np.zeros((0, G), np.int32)
         eos = self.shape.eos_id if eos_id is None else int(eos_id)
         cand = np.asarray(cand_pairs, dtype=np.int32).reshape(-1, 2)
         if cand.shape[0] == 1 and N > 1:
@@ -174,15 +186,15 @@ class Scorer:
         lens = [len(x) for x in id_lists]
         if min(lens) <= 0:
             raise ValueError("empty prompt")
-        if max_lookahead > self.max_lookahead:
-            raise ValueError(f"max_lookahead {max_lookahead} > workspace limit {self.max_lookahead}")
+        if G > self.max_lookahead:
+            raise ValueError(f"max_lookahead / gen_tokens {G} > workspace limit {self.max_lookahead}")
         rows = np.zeros((N, 8), np.float32)
-        gens = np.full((N, max_lookahead), -1, np.int32)
+        gens = np.full((N, G), -1, np.int32)
         for batch in plan_batches(lens, self.max_tokens, self.max_seqs):
             t_tok, t_cu, t_cand, _ = self.pack([id_lists[i] for i in batch], cand[batch])
             out = torch.empty((len(batch), 8), dtype=torch.float32).pin_memory()
-            gen = torch.empty((len(batch), max_lookahead), dtype=torch.int32).pin_memory()
-            self.score_batch_host(t_tok, t_cu, t_cand, topk, max_lookahead, eos, out, gen)
+            gen = torch.empty((len(batch), G), dtype=torch.int32).pin_memory()
+            self.score_batch_host(t_tok, t_cu, t_cand, topk, max_lookahead, eos, out, gen, gen_tokens=G)
             rows[batch] = out.numpy()
             gens[batch] = gen.numpy()
         return rows, gens
@@ -236,8 +248,9 @@ def tokenize_prompts(tokenizer, prompts, variant, cand_strings=None):
 
 def score_prompts(scorer: Scorer, tokenizer, prompts: Sequence[str], variant: str = "100q",
                   cand_strings: Optional[Sequence[Tuple[str, str]]] = None,
-                  max_lookahead: int = MAX_LOOK_AHEAD, shard_group=None) -> List[dict]:
-    """Batched replacement of the reference's per-prompt loop.  ``cand_strings`` optionally gives a
+                  max_lookahead: int = MAX_LOOK_AHEAD, shard_group=None, gen_tokens: Optional[int] = None) -> List[dict]:
+    """Batched replacement of the reference's per-prompt loop.  ``gen_tokens`` (e.g. 50 = the reference's
+    max_new_tokens) makes ``completion`` the full greedy continuation instead of the look-ahead window.  ``cand_strings`` optionally gives a
     (token_1, token_2) pair per prompt (the perturbation scenarios' ``target_tokens``); default is
     (" Yes", " No").  With ``shard_group`` (a torch.distributed group, or True for the default group) every rank
     scores its shard of the prompts and all ranks receive all rows (BASELINE config 4: sharded by prompt)."""
@@ -247,10 +260,10 @@ def score_prompts(scorer: Scorer, tokenizer, prompts: Sequence[str], variant: st
         if shard_group is not None:
             from .dist import score_ids_sharded
             rows, gens = score_ids_sharded(scorer, ids, cand, topk=V["topk"], max_lookahead=max_lookahead,
-                                           eos_id=tokenizer.eos_token_id, group=shard_group)
+                                           eos_id=tokenizer.eos_token_id, group=shard_group, gen_tokens=gen_tokens)
         else:
             rows, gens = scorer.score_ids(ids, cand, topk=V["topk"], max_lookahead=max_lookahead,
-                                          eos_id=tokenizer.eos_token_id)
+                                          eos_id=tokenizer.eos_token_id, gen_tokens=gen_tokens)
     except Exception as e:   # reference error policy: NaN rows, sweep continues
         if variant != "100q":
             raise

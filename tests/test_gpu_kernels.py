@@ -167,6 +167,35 @@ def _attn_ref(q, k, v, lens, kv_extra):
     return outs
 
 
+def test_attention_simt_kv_longer_than_shared_memory():
+    """head_dim 128 with 240 keys (a 190-token prompt + a 50-token completion): K/V no longer fit in shared memory
+    as fp32, the CUDA-core kernel reads them through L2 instead (prefill rows and a one-token row)."""
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    nh, nkv, hd = 4, 2, 128
+    qlens, extra = [200, 1, 37], [40, 239, 0]
+    q_start, kv_start, t, c = [], [], 0, 0
+    for ql, ex in zip(qlens, extra):
+        q_start.append(t); kv_start.append(c); t += ql; c += ql + ex + 7
+    T, slots = t, c + 16
+    qkv_dim = (nh + 2 * nkv) * hd
+    qkv = _rand((T, qkv_dim), 1.0, 21)
+    kc, vc = _rand((slots, nkv * hd), 1.0, 22), _rand((slots, nkv * hd), 1.0, 23)
+    out = torch.zeros((T, nh * hd), dtype=torch.bfloat16, device="cuda")
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device="cuda")
+    kvl = [a + b for a, b in zip(qlens, extra)]
+    a_qs, a_ql, a_ks, a_kl = i32(q_start), i32(qlens), i32(kv_start), i32(kvl)     # keep alive across the launch
+    _lib.check(lib.b2s_attention_bf16(_lib.ptr(qkv), _lib.ptr(kc), _lib.ptr(vc), _lib.ptr(out), _lib.ptr(a_qs),
+                                      _lib.ptr(a_ql), _lib.ptr(a_ks), _lib.ptr(a_kl), len(qlens), T, slots,
+                                      max(qlens), max(kvl), nh, nkv, hd, qkv_dim, 0, hd, 0, _lib.current_stream()), "attention")
+    torch.cuda.synchronize()
+    q = qkv[:, :nh * hd].view(T, nh, hd)
+    ref = _attn_ref(q, kc.view(slots, nkv, hd), vc.view(slots, nkv, hd), list(zip(q_start, qlens, kv_start, kvl)), extra)
+    for (qs, ql), r in zip(zip(q_start, qlens), ref):
+        err = (out[qs:qs + ql].view(ql, nh, hd).float() - r).abs().max().item()
+        assert err <= 1.5e-2, (ql, err)
+
+
 @pytest.mark.parametrize("use_tc", [0, 1, 2], ids=["simt", "tc_p_in_tmem", "tc_p_in_smem"])
 @pytest.mark.parametrize("nh,nkv", [(71, 1), (4, 2), (3, 3)])
 @pytest.mark.parametrize("phase", ["prefill", "one_token", "one_token_short"])

@@ -66,6 +66,42 @@ def test_scorer_fp32_check_vs_reference_golden(case_idx):
 
 
 @pytest.mark.parametrize("case_idx", [0, 1, 2])
+def test_completion_50_tokens_vs_reference_golden(case_idx):
+    """greedy decoding continues to the reference's max_new_tokens=50 for every prompt (up to EOS)
+    while only the first 10 positions are scanned.  The decoded `completion` must equal the string the reference's
+    own function produced (golden), and the scored row must equal the look-ahead-only run bit for bit."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights
+    from llm_interpretation_replication_b200 import scorer as S
+    case = U.golden_cases()[case_idx]
+    shp = shapes.REGISTRY[case["shape"]]()
+    W = weights.init_weights(shp, seed=case["seed"])
+    sc = U.make_scorer(shp, W, shapes.MODE_FP32_CHECK, max_tokens=4096, max_seqs=64, max_lookahead=50)
+    for variant, key, topk in (("100q", "ref_100q", 5), ("instruct", "ref_instruct", 2)):
+        ids, cands = [], []
+        for row in case["rows"]:
+            tok = U.tok_for(shp, row)
+            ids.append(tok(row["prompt"]).input_ids)
+            cands.append(S.candidate_ids(tok, variant))
+        rows10, gens10 = sc.score_ids(ids, np.array(cands), topk=topk, eos_id=shp.eos_id)
+        rows50, gens50 = sc.score_ids(ids, np.array(cands), topk=topk, eos_id=shp.eos_id, gen_tokens=50)
+        assert gens50.shape == (len(ids), 50)
+        assert np.array_equal(rows10, rows50, equal_nan=True)
+        for i, row in enumerate(case["rows"]):
+            n10 = int((gens10[i] >= 0).sum())
+            assert np.array_equal(gens10[i][:n10], gens50[i][:n10])        # same greedy prefix
+            d = S._row_to_dict(rows50[i], gens50[i], variant, row["prompt"], U.tok_for(shp, row))
+            assert d["completion"] == row[key]["completion"], (variant, i)
+            live = gens50[i][gens50[i] >= 0]
+            assert len(live) == 50 or live[-1] == shp.eos_id                # stops only at EOS
+    with pytest.raises(ValueError):
+        sc.score_ids(ids, np.array(cands), gen_tokens=5)                    # fewer than the scan window
+    with pytest.raises(ValueError):
+        sc.score_ids(ids, np.array(cands), gen_tokens=60)                   # beyond the workspace
+    sc.close()
+
+
+@pytest.mark.parametrize("case_idx", [0, 1, 2])
 @pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
 def test_scorer_bf16_vs_reference_golden(case_idx, mode_name):
     import gpu_util as U
