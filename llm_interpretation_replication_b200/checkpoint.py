@@ -1,0 +1,220 @@
+"""Local Hugging Face checkpoints and tokenizers -> the scorer.
+
+Replaces ``AutoTokenizer.from_pretrained`` / ``AutoModelForCausalLM.from_pretrained`` of the reference
+(``analysis/run_base_vs_instruct_100q.py:416-450``, ``compare_instruct_models.py:178-226``) for checkpoints that are
+already on disk (there is no hub access here): a directory with ``config.json`` plus ``*.safetensors`` (single file or
+sharded with ``model.safetensors.index.json``) or ``pytorch_model*.bin``.
+
+* ``shape_from_hf_config``  Falcon (``model_type`` "falcon" or the original "RefinedWebModel" key names; multi-query,
+  parallel attention, rotary: HF:models/falcon/configuration_falcon.py:53-76) and GPT-NeoX (StableLM-alpha, RedPajama,
+  Pythia/Dolly, h2oGPT: HF:models/gpt_neox/configuration_gpt_neox.py) configs to a ``DecoderShape``; anything else
+  raises ``KeyError``, which the entry points turn into the reference's NaN rows for a model that fails to load.
+* ``flat_from_hf``          inverse of ``weights.to_hf_state_dict``.  The fused QKV matrices keep HF's own row order
+  (Falcon ``[q heads..., k, v]`` HF falcon:285-288; NeoX per-head ``[q, k, v]`` HF gpt_neox:212-215): the kernels
+  index them through ``qkv_layout``, nothing is permuted at load time.
+* ``load_checkpoint``       streams tensor by tensor to the device in the compute dtype (a 7B model never holds a
+  second host copy) and returns ``(shape, weights)`` ready for ``Scorer``.
+* ``load_tokenizer``        ``AutoTokenizer.from_pretrained(dir, local_files_only=True)`` passed through unchanged, so
+  the F4 quirk (`` Yes`` looked up through ``tokenizer(...).input_ids[0]`` with or without special tokens) behaves
+  exactly as in the reference; ``pad_token = eos_token`` when the tokenizer has none (reference :420-421).
+"""
+from __future__ import annotations
+
+import glob
+import json
+import os
+import re
+from typing import Dict, Iterator, Optional, Tuple
+
+import torch
+
+from .shapes import ARCH_FALCON, ARCH_GPT_NEOX, QKV_FALCON_MQA, QKV_NEOX_INTERLEAVED, DecoderShape
+from . import weights as _weights
+
+
+def _rope(cfg: dict, theta_keys, pct_default):
+    """(rope_theta, partial rotary factor) from either generation of config keys: the hub checkpoints of the sweep carry
+    ``rotary_emb_base`` / ``rotary_pct`` (GPT-NeoX) or ``rope_theta`` (Falcon); transformers >= 5 re-serialises them as
+    ``rope_parameters = {rope_theta, partial_rotary_factor, rope_type}``."""
+    rp = cfg.get("rope_parameters") or {}
+    if rp.get("rope_type", "default") not in ("default", None):
+        raise KeyError(f"rope_type {rp.get('rope_type')!r} is not supported")
+    if cfg.get("rope_scaling") and (cfg["rope_scaling"].get("rope_type") or cfg["rope_scaling"].get("type")) not in (None, "default"):
+        raise KeyError("rope_scaling is not supported")
+    theta = rp.get("rope_theta")
+    for k in theta_keys:
+        if theta is None:
+            theta = cfg.get(k)
+    pct = rp.get("partial_rotary_factor", cfg.get("rotary_pct", cfg.get("partial_rotary_factor", pct_default)))
+    return float(10000.0 if theta is None else theta), float(pct)
+
+
+def shape_from_hf_config(cfg: dict, name: str = "checkpoint") -> DecoderShape:
+    mt = cfg.get("model_type", "")
+    if mt in ("falcon", "RefinedWebModel", "RefinedWeb"):
+        n_layer = cfg.get("num_hidden_layers", cfg.get("n_layer"))
+        n_head = cfg.get("num_attention_heads", cfg.get("n_head"))
+        d = cfg["hidden_size"]
+        if cfg.get("new_decoder_architecture", False) or mt == "RefinedWeb":
+            raise KeyError(f"{name}: Falcon new_decoder_architecture (40B/180B layout) is not supported")
+        if not cfg.get("multi_query", True) or not cfg.get("parallel_attn", True):
+            raise KeyError(f"{name}: only multi-query, parallel-attention Falcon is supported")
+        if cfg.get("alibi", False) or cfg.get("bias", False):
+            raise KeyError(f"{name}: Falcon with alibi or biases is not supported")
+        hd = d // n_head
+        theta, _ = _rope(cfg, ("rope_theta",), 1.0)
+        return DecoderShape(name, ARCH_FALCON, int(n_layer), int(d), int(n_head), 1, hd, int(cfg.get("ffn_hidden_size") or 4 * d),
+                            int(cfg["vocab_size"]), hd, rope_theta=theta,
+                            norm_eps=float(cfg.get("layer_norm_epsilon", 1e-5)), parallel_residual=True, n_ln_per_layer=1,
+                            has_bias=False, tied_head=True, qkv_layout=QKV_FALCON_MQA,
+                            eos_id=int(cfg.get("eos_token_id", 11)), max_pos=int(cfg.get("max_position_embeddings", 2048)))
+    if mt == "gpt_neox":
+        if cfg.get("hidden_act", "gelu") != "gelu":
+            raise KeyError(f"{name}: GPT-NeoX hidden_act {cfg.get('hidden_act')!r} is not supported (erf GELU only)")
+        if not cfg.get("attention_bias", True):
+            raise KeyError(f"{name}: GPT-NeoX without attention biases is not supported")
+        d, n_head = int(cfg["hidden_size"]), int(cfg["num_attention_heads"])
+        hd = d // n_head
+        theta, pct = _rope(cfg, ("rotary_emb_base", "rope_theta"), 0.25)
+        rd = int(hd * pct)
+        eos = cfg.get("eos_token_id", 0)
+        eos = eos[0] if isinstance(eos, (list, tuple)) else eos
+        return DecoderShape(name, ARCH_GPT_NEOX, int(cfg["num_hidden_layers"]), d, n_head, n_head, hd,
+                            int(cfg["intermediate_size"]), int(cfg["vocab_size"]), rd,
+                            rope_theta=theta,
+                            norm_eps=float(cfg.get("layer_norm_eps", 1e-5)),
+                            parallel_residual=bool(cfg.get("use_parallel_residual", True)), n_ln_per_layer=2, has_bias=True,
+                            tied_head=bool(cfg.get("tie_word_embeddings", False)), qkv_layout=QKV_NEOX_INTERLEAVED,
+                            eos_id=int(eos), max_pos=int(cfg.get("max_position_embeddings", 2048)))
+    raise KeyError(f"{name}: architecture {mt!r} is not supported by the B200 scorer")
+
+
+_FALCON_GLOBAL = {"transformer.word_embeddings.weight": "wte", "transformer.ln_f.weight": "lnf_g",
+                  "transformer.ln_f.bias": "lnf_b", "lm_head.weight": "lm_head"}
+_FALCON_LAYER = {"input_layernorm.weight": "ln1_g", "input_layernorm.bias": "ln1_b",
+                 "self_attention.query_key_value.weight": "w_qkv", "self_attention.dense.weight": "w_dense",
+                 "mlp.dense_h_to_4h.weight": "w_up", "mlp.dense_4h_to_h.weight": "w_down"}
+_NEOX_GLOBAL = {"gpt_neox.embed_in.weight": "wte", "gpt_neox.final_layer_norm.weight": "lnf_g",
+                "gpt_neox.final_layer_norm.bias": "lnf_b", "embed_out.weight": "lm_head"}
+_NEOX_LAYER = {"input_layernorm.weight": "ln1_g", "input_layernorm.bias": "ln1_b",
+               "post_attention_layernorm.weight": "ln2_g", "post_attention_layernorm.bias": "ln2_b",
+               "attention.query_key_value.weight": "w_qkv", "attention.query_key_value.bias": "b_qkv",
+               "attention.dense.weight": "w_dense", "attention.dense.bias": "b_dense",
+               "mlp.dense_h_to_4h.weight": "w_up", "mlp.dense_h_to_4h.bias": "b_up",
+               "mlp.dense_4h_to_h.weight": "w_down", "mlp.dense_4h_to_h.bias": "b_down"}
+_LAYER_RE = re.compile(r"^(?:transformer\.h|gpt_neox\.layers)\.(\d+)\.(.+)$")
+
+
+def flat_name(shape: DecoderShape, hf_name: str) -> Optional[str]:
+    """Name of an HF state-dict entry in the flat layout, or None for entries the scorer does not use (rotary
+    ``inv_freq`` buffers, causal-mask buffers)."""
+    glob_map, layer_map = (_FALCON_GLOBAL, _FALCON_LAYER) if shape.arch == ARCH_FALCON else (_NEOX_GLOBAL, _NEOX_LAYER)
+    if hf_name in glob_map:
+        return glob_map[hf_name]
+    m = _LAYER_RE.match(hf_name)
+    if m and m.group(2) in layer_map:
+        return f"l{int(m.group(1))}.{layer_map[m.group(2)]}"
+    return None
+
+
+def expected_names(shape: DecoderShape):
+    names = [n for n in _weights.slot_names(shape) if n is not None and not n.startswith("rope_")]
+    out = []
+    for n in names:
+        leaf = n.split(".")[-1]
+        if leaf in ("ln2_g", "ln2_b") and shape.n_ln_per_layer != 2:
+            continue
+        if leaf.startswith("b_") and not shape.has_bias:
+            continue
+        out.append(n)
+    return out
+
+
+def _check_shape(shape: DecoderShape, name: str, t: torch.Tensor):
+    d, ff, V = shape.d_model, shape.d_ff, shape.vocab
+    leaf = name.split(".")[-1]
+    want = {"wte": (V, d), "lm_head": (V, d), "lnf_g": (d,), "lnf_b": (d,), "ln1_g": (d,), "ln1_b": (d,), "ln2_g": (d,),
+            "ln2_b": (d,), "w_qkv": (shape.qkv_dim, d), "b_qkv": (shape.qkv_dim,), "w_dense": (d, shape.n_head * shape.head_dim),
+            "b_dense": (d,), "w_up": (ff, d), "b_up": (ff,), "w_down": (d, ff), "b_down": (d,)}[leaf]
+    if tuple(t.shape) != want:
+        raise ValueError(f"checkpoint tensor {name} has shape {tuple(t.shape)}, the config implies {want}")
+
+
+def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.float32) -> Dict[str, torch.Tensor]:
+    """``tensors``: a state dict or an iterator of (hf_name, tensor).  Matrices are converted to ``weight_dtype``,
+    vectors to fp32, each moved to ``device`` as it arrives."""
+    items = tensors.items() if hasattr(tensors, "items") else tensors
+    W: Dict[str, torch.Tensor] = {}
+    for hf_name, t in items:
+        n = flat_name(shape, hf_name)
+        if n is None:
+            continue
+        _check_shape(shape, n, t)
+        W[n] = t.to(device=device, dtype=weight_dtype if _weights.is_matrix(n) else torch.float32).contiguous()
+    if "lm_head" not in W:
+        if not shape.tied_head:
+            raise ValueError("checkpoint has no output embedding and the config does not tie it to the input embedding")
+        W["lm_head"] = W["wte"]
+    missing = [n for n in expected_names(shape) if n not in W]
+    if missing:
+        raise ValueError(f"checkpoint is missing {len(missing)} tensors, e.g. {missing[:4]}")
+    return W
+
+
+def iter_checkpoint_tensors(path: str) -> Iterator[Tuple[str, torch.Tensor]]:
+    st = sorted(glob.glob(os.path.join(path, "*.safetensors")))
+    if st:
+        from safetensors import safe_open
+        for f in st:
+            with safe_open(f, framework="pt", device="cpu") as fh:
+                for k in fh.keys():
+                    yield k, fh.get_tensor(k)
+        return
+    bins = sorted(glob.glob(os.path.join(path, "pytorch_model*.bin")))
+    if not bins:
+        raise FileNotFoundError(f"no *.safetensors or pytorch_model*.bin under {path}")
+    for f in bins:
+        sd = torch.load(f, map_location="cpu", weights_only=True)
+        for k, v in sd.items():
+            yield k, v
+        del sd
+
+
+def resolve_local(model_name: str) -> Optional[str]:
+    """Directory of a checkpoint for ``model_name``: the name itself if it is a directory, else
+    ``$B2S_CHECKPOINT_ROOT/<name>`` (with or without the organisation prefix).  None when there is no local copy."""
+    cands = [model_name]
+    root = os.environ.get("B2S_CHECKPOINT_ROOT")
+    if root:
+        cands += [os.path.join(root, model_name), os.path.join(root, model_name.split("/")[-1]),
+                  os.path.join(root, model_name.replace("/", "--"))]
+    for c in cands:
+        if os.path.isfile(os.path.join(c, "config.json")):
+            return c
+    return None
+
+
+def load_checkpoint(path: str, device="cuda:0", weight_dtype=torch.float16, n_layer: int = 0):
+    """(shape, weights on ``device``) from a local HF checkpoint directory.  ``n_layer`` > 0 keeps only the first
+    layers (smoke runs)."""
+    with open(os.path.join(path, "config.json")) as f:
+        cfg = json.load(f)
+    shape = shape_from_hf_config(cfg, name=os.path.basename(os.path.normpath(path)))
+    if n_layer:
+        shape = shape.with_layers(min(n_layer, shape.n_layer))
+
+    def wanted():
+        for k, v in iter_checkpoint_tensors(path):
+            m = _LAYER_RE.match(k)
+            if m and int(m.group(1)) >= shape.n_layer:
+                continue
+            yield k, v
+    return shape, flat_from_hf(shape, wanted(), device=device, weight_dtype=weight_dtype)
+
+
+def load_tokenizer(path: str):
+    from transformers import AutoTokenizer
+    tok = AutoTokenizer.from_pretrained(path, local_files_only=True)
+    if tok.pad_token is None:                       # reference run_base_vs_instruct_100q.py:420-421
+        tok.pad_token = tok.eos_token
+    return tok

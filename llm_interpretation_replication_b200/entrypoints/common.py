@@ -62,25 +62,36 @@ def model_seed(model_name: str) -> int:
 
 def load_model(model_name: str, device=None, mode=shapes.MODE_FP16, n_layer: int = 0, max_tokens: int = 65536,
                max_seqs: int = 1024):
-    """Stand-in for AutoTokenizer/AutoModelForCausalLM.from_pretrained (reference :416-450): the shape of the
-    named hub model with random-init weights (seeded by the name) and the offline tokenizer.  Raises KeyError for
-    architectures outside the supported families, which the callers turn into NaN rows as the reference does for
-    models that fail to load."""
-    if model_name in shapes.HUB_TO_SHAPE:
-        shp = shapes.HUB_TO_SHAPE[model_name]()
-    elif model_name in shapes.REGISTRY:
-        shp = shapes.REGISTRY[model_name]()
-    else:
-        raise KeyError(f"architecture of {model_name} is not supported by the B200 scorer")
-    if n_layer:
-        shp = shp.with_layers(n_layer)
+    """AutoTokenizer/AutoModelForCausalLM.from_pretrained of the reference (:416-450).  A checkpoint that is on disk
+    (``model_name`` is a directory, or ``$B2S_CHECKPOINT_ROOT/<model_name>`` exists; see ``checkpoint.py``) is loaded
+    with its own tokenizer.  Otherwise (no hub access here) the stand-in is the shape of the named hub model with
+    random-init weights seeded by the name and the offline tokenizer.  Raises KeyError for architectures outside the
+    supported families, which the callers turn into NaN rows as the reference does for models that fail to load."""
+    from .. import checkpoint
+    from ..scorer import MAX_LOOK_AHEAD
     device = torch.device(device if device is not None else "cuda:0")
     dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
-    W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
-    from ..scorer import MAX_LOOK_AHEAD
+    local = checkpoint.resolve_local(model_name)
+    if local is not None:
+        shp, W = checkpoint.load_checkpoint(local, device=device, weight_dtype=dt, n_layer=n_layer)
+        try:
+            tok = checkpoint.load_tokenizer(local)
+        except Exception as e:   # weights without tokenizer files: offline tokenizer, said out loud
+            log_print(f"  no usable tokenizer under {local} ({type(e).__name__}); using the offline HashTokenizer")
+            tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
+    else:
+        if model_name in shapes.HUB_TO_SHAPE:
+            shp = shapes.HUB_TO_SHAPE[model_name]()
+        elif model_name in shapes.REGISTRY:
+            shp = shapes.REGISTRY[model_name]()
+        else:
+            raise KeyError(f"architecture of {model_name} is not supported by the B200 scorer")
+        if n_layer:
+            shp = shp.with_layers(n_layer)
+        W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
+        tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
     scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs,
                     max_lookahead=max(MAX_LOOK_AHEAD, COMPLETION_TOKENS))
-    tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
     return scorer, tok
 
 

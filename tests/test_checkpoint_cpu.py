@@ -1,0 +1,119 @@
+"""SURVEY 8f row N2 on the CPU: local HF checkpoints (safetensors / .bin) and tokenizers -> the flat weight layout."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from llm_interpretation_replication_b200 import checkpoint, shapes, weights
+
+
+def _save_hf(shape, W, path, safe=True):
+    model = weights.build_hf_model(shape, W)
+    model.save_pretrained(path, safe_serialization=safe)
+    return model
+
+
+@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_neox_sequential"])
+@pytest.mark.parametrize("safe", [True, False], ids=["safetensors", "bin"])
+def test_checkpoint_round_trip(tmp_path, maker, safe):
+    """A checkpoint written by transformers itself comes back as the same shape and bit-identical tensors."""
+    shp = getattr(shapes, maker)()
+    W = weights.init_weights(shp, seed=7)
+    _save_hf(shp, W, str(tmp_path), safe=safe)
+    shp2, W2 = checkpoint.load_checkpoint(str(tmp_path), device="cpu", weight_dtype=torch.float32)
+    for f in ("arch", "n_layer", "d_model", "n_head", "n_kv_head", "head_dim", "d_ff", "vocab", "rotary_dim", "rope_theta",
+              "norm_eps", "parallel_residual", "n_ln_per_layer", "has_bias", "tied_head", "qkv_layout", "eos_id", "max_pos"):
+        assert getattr(shp2, f) == getattr(shp, f), f
+    names = checkpoint.expected_names(shp)
+    assert set(names) <= set(W2)
+    for n in names:
+        assert torch.equal(W2[n], W[n]), n
+    if shp.tied_head:
+        assert W2["lm_head"] is W2["wte"]
+    # truncated load keeps the first layer only
+    shp1, W1 = checkpoint.load_checkpoint(str(tmp_path), device="cpu", weight_dtype=torch.bfloat16, n_layer=1)
+    assert shp1.n_layer == 1 and "l1.w_qkv" not in W1 and W1["l0.w_qkv"].dtype == torch.bfloat16
+    assert W1["l0.ln1_g"].dtype == torch.float32
+
+
+def test_config_mapping_matches_registry():
+    """The public config.json key sets of the sweep's models map onto the registry shapes."""
+    old_falcon = dict(model_type="RefinedWebModel", n_layer=32, n_head=71, hidden_size=4544, vocab_size=65024, multi_query=True,
+                      parallel_attn=True, bias=False, alibi=False, layer_norm_epsilon=1e-5, eos_token_id=11, bos_token_id=11)
+    new_falcon = dict(model_type="falcon", num_hidden_layers=32, num_attention_heads=71, hidden_size=4544, vocab_size=65024,
+                      multi_query=True, parallel_attn=True, bias=False, alibi=False, new_decoder_architecture=False,
+                      layer_norm_epsilon=1e-5, eos_token_id=11, max_position_embeddings=2048, rope_theta=10000.0)
+    stablelm = dict(model_type="gpt_neox", hidden_size=6144, num_hidden_layers=16, num_attention_heads=48, intermediate_size=24576,
+                    rotary_pct=0.25, rotary_emb_base=10000, layer_norm_eps=1e-5, use_parallel_residual=True, vocab_size=50432,
+                    max_position_embeddings=4096, eos_token_id=0, hidden_act="gelu", tie_word_embeddings=False)
+    redpajama = dict(model_type="gpt_neox", hidden_size=2560, num_hidden_layers=32, num_attention_heads=32, intermediate_size=10240,
+                     rotary_pct=1.0, rotary_emb_base=10000, layer_norm_eps=1e-5, use_parallel_residual=False, vocab_size=50432,
+                     max_position_embeddings=2048, eos_token_id=0, hidden_act="gelu", tie_word_embeddings=False)
+    for cfg, ref in ((old_falcon, shapes.falcon_7b()), (new_falcon, shapes.falcon_7b()), (stablelm, shapes.stablelm_alpha_7b()),
+                     (redpajama, shapes.redpajama_3b())):
+        got = checkpoint.shape_from_hf_config(cfg, ref.name)
+        assert got == ref, (got, ref)
+    for bad in (dict(model_type="llama"), dict(model_type="falcon", hidden_size=8192, num_attention_heads=128, num_hidden_layers=60,
+                                                  vocab_size=65024, new_decoder_architecture=True),
+                dict(model_type="gpt_neox", hidden_size=64, num_attention_heads=1, num_hidden_layers=1, intermediate_size=256,
+                     vocab_size=10, hidden_act="gelu_new")):
+        with pytest.raises(KeyError):
+            checkpoint.shape_from_hf_config(bad, "x")
+
+
+def test_wrong_or_missing_tensors_are_rejected(tmp_path):
+    shp = shapes.tiny_falcon()
+    W = weights.init_weights(shp, seed=1)
+    sd = weights.to_hf_state_dict(shp, W)
+    bad = dict(sd); bad["transformer.h.0.mlp.dense_h_to_4h.weight"] = torch.zeros(3, 3)
+    with pytest.raises(ValueError, match="shape"):
+        checkpoint.flat_from_hf(shp, bad)
+    short = {k: v for k, v in sd.items() if "h.1.self_attention.dense" not in k}
+    with pytest.raises(ValueError, match="missing"):
+        checkpoint.flat_from_hf(shp, short)
+    # buffers HF checkpoints carry but the scorer does not use are ignored
+    extra = dict(sd); extra["transformer.h.0.self_attention.rotary_emb.inv_freq"] = torch.zeros(32)
+    assert set(checkpoint.flat_from_hf(shp, extra)) == set(checkpoint.flat_from_hf(shp, sd))
+    with pytest.raises(FileNotFoundError):
+        (tmp_path / "config.json").write_text(json.dumps(weights.hf_config(shp).to_dict()))
+        checkpoint.load_checkpoint(str(tmp_path), device="cpu")
+
+
+def _write_tokenizer(path, vocab_size=256):
+    """A real (fast) HF tokenizer on disk: word-level over a closed vocabulary, ' Yes' / ' No' as single tokens."""
+    from tokenizers import Tokenizer, models, pre_tokenizers
+    from transformers import PreTrainedTokenizerFast
+    words = ["<eos>", "<unk>", "Yes", "No", "Is", "a", "the", "Question", "Answer", ":", "?", ".", ",", "'", '"', "soup",
+             "beverage", "tweet", "publication", "either", "or", "without", "any", "other", "text", "screenshot", "photograph"]
+    vocab = {w: i for i, w in enumerate(words)}
+    tk = Tokenizer(models.WordLevel(vocab, unk_token="<unk>"))
+    tk.pre_tokenizer = pre_tokenizers.Sequence([pre_tokenizers.Whitespace()])
+    fast = PreTrainedTokenizerFast(tokenizer_object=tk, eos_token="<eos>", unk_token="<unk>")
+    fast.save_pretrained(path)
+    return vocab
+
+
+def test_tokenizer_pass_through_and_candidate_ids(tmp_path):
+    from llm_interpretation_replication_b200 import scorer as S
+    vocab = _write_tokenizer(str(tmp_path))
+    tok = checkpoint.load_tokenizer(str(tmp_path))
+    assert tok.pad_token == tok.eos_token                      # reference :420-421
+    ids = tok('Is a "tweet" a "publication"?').input_ids
+    assert ids[0] == vocab["Is"] and vocab["tweet"] in ids
+    for variant in ("100q", "instruct"):
+        a, b = S.candidate_ids(tok, variant)
+        assert (a, b) == (vocab["Yes"], vocab["No"])
+    assert tok.decode([vocab["Yes"], vocab["<eos>"]], skip_special_tokens=True).strip() == "Yes"
+
+
+def test_resolve_local(tmp_path, monkeypatch):
+    d = tmp_path / "tiiuae" / "falcon-7b"
+    d.mkdir(parents=True)
+    (d / "config.json").write_text("{}")
+    assert checkpoint.resolve_local("tiiuae/falcon-7b") is None
+    monkeypatch.setenv("B2S_CHECKPOINT_ROOT", str(tmp_path))
+    assert checkpoint.resolve_local("tiiuae/falcon-7b") == str(d)
+    assert checkpoint.resolve_local(str(d)) == str(d)
+    assert checkpoint.resolve_local("tiiuae/falcon-40b") is None
