@@ -202,6 +202,18 @@ B2S_API int b2s_bootstrap_summary(const double* boot, int64_t B, int32_t stat, d
                           double observed, double* summary /*dev [8]*/, double* stat_out /*dev [B] or NULL*/,
                           void* scratch, size_t scratch_bytes, void* stream);
 
+/* Prompt-resampled inter-model correlation bootstrap: the body of the loop of
+ * analysis/model_comparison_graph.py:261-291 -- per resample b, DataFrame.corr(method) of the rows idx[b, :] of the
+ * [P prompts, M models] table X (fp64, NaN = missing; pairwise-complete observations, min_periods 1 as pandas) for
+ * the listed model pairs, then np.mean / np.median / np.std of the non-NaN pair values.
+ * method 0 = pearson, 1 = spearman (average-tie ranks of the rows both models answered; P <= 2048).
+ * idx [B, P] int32 row numbers (b2s_mt19937_choice reproduces np.random.choice(P, P) of a seeded stream),
+ * pairs [n_pairs, 2] int32 column numbers.  corr [B, n_pairs] receives every pair correlation (NaN where pandas
+ * yields NaN); stats (optional, n_pairs <= 2048) [B, 4] = mean, median, std (ddof 0), number of non-NaN pairs. */
+B2S_API int b2s_corr_bootstrap(const double* X, int32_t P, int32_t M, const int32_t* idx, int32_t B,
+                       const int32_t* pairs, int32_t n_pairs, int32_t method, double* corr, double* stats /*or NULL*/,
+                       void* stream);
+
 /* Simulated-individual correlation bootstrap: the body of the 10,000-iteration loop of
  * survey_analysis/bootstrap_confidence_intervals.py:54-99,126-148.  Seed s = seed0 + i runs
  * calculate_individual_correlations(model_responses, n_samples, seed=s) on a NumPy-legacy MT19937 of its own

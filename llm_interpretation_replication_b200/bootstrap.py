@@ -42,6 +42,13 @@ class NumpyLegacyStream:
                                                    _lib.current_stream()), "b2s_mt19937_choice")
         return out
 
+    def choice_into(self, n: int, out: torch.Tensor) -> None:
+        """``np.random.choice(n, out.numel())`` written into a contiguous int32 device view (no allocation)."""
+        assert out.dtype == torch.int32 and out.is_contiguous() and out.device == self.device
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.b2s_mt19937_choice(_lib.ptr(self.state), int(n), int(out.numel()), _lib.ptr(out),
+                                                   _lib.current_stream()), "b2s_mt19937_choice")
+
 
 def resample(vals: np.ndarray, split: int, B: int, idx: Optional[torch.Tensor] = None, philox_seed: int = 0,
              device=None) -> torch.Tensor:
