@@ -36,7 +36,7 @@ def corr_bootstrap(X: np.ndarray, idx: torch.Tensor, pairs: np.ndarray, method: 
     device = torch.device(device if device is not None else idx.device)
     P, M = X.shape
     B = idx.numel() // P
-    x = torch.as_tensor(np.ascontiguousarray(X, dtype=np.float64)).to(device)
+    x = torch.as_tensor(np.array(X, dtype=np.float64, order="C", copy=True)).to(device)
     pr = torch.as_tensor(np.ascontiguousarray(pairs, dtype=np.int32)).to(device)
     corr = torch.empty((B, pr.shape[0]), dtype=torch.float64, device=device)
     stats = torch.empty((B, 4), dtype=torch.float64, device=device)
