@@ -36,7 +36,7 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
-  int serp;              // serpentine order: odd groups walk the column tiles backwards, odd waves walk K backwards
+  int serp;              // serpentine order: odd groups walk the column tiles backwards; K walked backwards by odd column tiles (1) or odd waves (2)
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
@@ -451,7 +451,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mb, nb;
         tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, p.serp, mb, nb);
-        const bool rev = p.serp && (((tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x)) & 1);
+        const bool rev = p.serp == 2 ? ((((tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x)) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
           const int kb = rev ? p.num_kb - 1 - kq : kq;   // the MMA side only counts k-blocks, so the order is free
           mbar_wait(empty_bar(stage), phase ^ 1u);
@@ -635,7 +635,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
         tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
-        const bool rev = p.serp && (((tile - pair) / num_pairs) & 1);
+        const bool rev = p.serp == 2 ? ((((tile - pair) / num_pairs) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
           const int kb = rev ? p.num_kb - 1 - kq : kq;
           mbar_wait(empty_bar(stage), phase ^ 1u);
@@ -787,7 +787,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
         tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, p.serp, mb, nb);
-        const bool rev = p.serp && (((tile - pair) / num_pairs) & 1);
+        const bool rev = p.serp == 2 ? ((((tile - pair) / num_pairs) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
           const int kb = rev ? p.num_kb - 1 - kq : kq;
           mbar_wait(empty_bar(stage), phase ^ 1u);
@@ -925,7 +925,11 @@ extern int g_opt_attn_ts;
 int g_opt_tma_store = 1;   // 1: epilogue via shared memory + TMA bulk store / reduce-add; 0: per-thread global stores
 int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
 int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = rule off; b2s_set_option "gemm_small_w_group")
-int g_opt_serp = 1;        // b2s_set_option "gemm_serpentine"
+// b2s_set_option "gemm_serpentine": 0 (default) plain order.  2 = odd waves walk K backwards: +1 % end to end (each wave
+// starts on the panel bytes the previous one touched last) but a row's fp32 summation order then depends on which wave
+// its tile falls in, i.e. on the batch around it -- sharded and unsharded runs stop being bit-identical.  1 = direction by
+// column tile: batch-invariant, but CTAs that share an A row-block no longer walk K together: -1 %.
+int g_opt_serp = 0;
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
 int g_opt_cta_group = 0;   // 0: per-launch policy (default); 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256; 3: CTA pairs on 512x256 (b2s_set_option "gemm_cta_group")
 
@@ -1104,7 +1108,7 @@ int b2s_set_option(const char* name, int32_t value) {
     return B2S_OK;
   }
   if (std::string(name) == "gemm_serpentine") {
-    B2S_REQUIRE(value == 0 || value == 1, "set_option: gemm_serpentine must be 0 or 1");
+    B2S_REQUIRE(value >= 0 && value <= 2, "set_option: gemm_serpentine must be 0, 1 or 2");
     b2s::g_opt_serp = value;
     return B2S_OK;
   }

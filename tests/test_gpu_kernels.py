@@ -34,10 +34,11 @@ def test_gemm_tc_store_f32(M, N, K, cta_group):
     assert err <= 2e-3 * max(1.0, ref.abs().max().item()), err
 
 
+@pytest.mark.parametrize("serp", [1, 2], ids=["by_column", "by_wave"])
 @pytest.mark.parametrize("epi", [4, 2])
-def test_gemm_tc_serpentine_rasterisation(epi, cta_group):
-    """Serpentine order (odd groups walk column tiles backwards, odd waves walk K backwards; K tail of 8): several
-    groups and several waves per CTA, same result as the plain order."""
+def test_gemm_tc_serpentine_rasterisation(epi, serp, cta_group):
+    """Serpentine order (odd groups walk column tiles backwards; K walked backwards by odd column tiles or odd waves;
+    K tail of 8): several groups and several waves per CTA, same result as the plain order."""
     import gpu_util as U
     from llm_interpretation_replication_b200 import _lib
     lib = _lib.load()
@@ -46,7 +47,7 @@ def test_gemm_tc_serpentine_rasterisation(epi, cta_group):
     ref = A.float() @ W.float().T
     resid = _rand((M, N), 1.0, 13, torch.float32)
     try:
-        _lib.check(lib.b2s_set_option(b"gemm_serpentine", 1), "set_option")
+        _lib.check(lib.b2s_set_option(b"gemm_serpentine", serp), "set_option")
         _lib.check(lib.b2s_set_option(b"gemm_group_m", 4), "set_option")
         out = U.gemm_bf16(A, W, None, epi, out=resid.clone() if epi == 2 else None)
         torch.cuda.synchronize()
