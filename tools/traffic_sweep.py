@@ -11,7 +11,10 @@ timed = "--time" in sys.argv
 secs = 1.0
 lib = _lib.load(); st = _lib.current_stream()
 shapes = {"up": (18176, 4544, 1), "down": (4544, 18176, 2), "dense": (4544, 4544, 2), "qkv": (4672, 4544, 0)}
-if "--hints" in sys.argv:
+if "--cg3" in sys.argv:
+    grid = [(3, gm, 0, 0) for gm in (4, 8, 12, 16, 24, 32, 48, 64, 128)] + [(1, 0, 0, 0), (2, 0, 0, 0)]
+    shapes = {k: shapes[k] for k in ("down", "up")}
+elif "--hints" in sys.argv:
     grid = [(0, gm, 1, h) for gm in (0, 8) for h in (0, 4, 5, 6, 7, 1)]
 else:
     grid = [(cg, gm, serp, 0) for cg in (0,) for gm in (0, 8, 16, 32, 64, 128) for serp in (0, 1)]
