@@ -187,7 +187,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--prompts", type=int, default=N_PROMPTS, help="prompts per step (default: the full 10,000)")
     ap.add_argument("--layers", type=int, default=0, help="debug only: truncate the model (result is then not a bench value)")
-    ap.add_argument("--batch-tokens", type=int, default=131072)
+    ap.add_argument("--batch-tokens", type=int, default=262144,
+                    help="packed prompt tokens per C-ABI call; 262144 = 2350 prompts per batch, which fills the waves of the one-token GEMMs (profiles/r1_bench_batch_tokens.jsonl)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--mode", default="fp16", choices=["bf16", "fp16"],
@@ -228,7 +229,7 @@ def main():
     my_len = [int(L[i]) for i in mine]
 
     W = weights.init_weights_device(shp, seed=0, device=dev, weight_dtype=torch.bfloat16)
-    max_seqs = 2048
+    max_seqs = max(2048, args.batch_tokens // 64)   # prompts per batch are bounded by tokens, not by this
     mode = shapes.MODE_FP16 if args.mode == "fp16" else shapes.MODE_BF16_FAST
     sc = Scorer(shp, W, mode=mode, device=dev, max_tokens=args.batch_tokens, max_seqs=max_seqs,
                 max_lookahead=LOOKAHEAD)
