@@ -36,6 +36,7 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
+  int pair_stride;       // experiment: CTA pair p works on the tile sequence of pair (p * pair_stride) % num_pairs
   int serp;              // serpentine order: odd groups walk the column tiles backwards; K walked backwards by odd column tiles (1) or odd waves (2)
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
@@ -609,7 +610,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int lane = threadIdx.x & 31;
   const int tiles_m2 = (p.M + BM2 - 1) / BM2;
   const int num_tiles = tiles_m2 * p.tiles_n;
-  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int pair = static_cast<int>((static_cast<long long>(blockIdx.x >> 1) * p.pair_stride) % num_pairs);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -760,7 +762,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int lane = threadIdx.x & 31;
   const int tiles_m3 = (p.M + BM3 - 1) / BM3;
   const int num_tiles = tiles_m3 * p.tiles_n;
-  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int pair = static_cast<int>((static_cast<long long>(blockIdx.x >> 1) * p.pair_stride) % num_pairs);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -929,6 +932,7 @@ int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = ru
 // starts on the panel bytes the previous one touched last) but a row's fp32 summation order then depends on which wave
 // its tile falls in, i.e. on the batch around it -- sharded and unsharded runs stop being bit-identical.  1 = direction by
 // column tile: batch-invariant, but CTAs that share an A row-block no longer walk K together: -1 %.
+int g_opt_pair_stride = 1;   // b2s_set_option "gemm_pair_stride" (experiment; must be coprime to the number of CTA pairs)
 int g_opt_serp = 0;
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
 int g_opt_cta_group = 0;   // 0: per-launch policy (default); 1: one CTA per 128x256 tile; 2: CTA pairs on 256x256; 3: CTA pairs on 512x256 (b2s_set_option "gemm_cta_group")
@@ -979,7 +983,9 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
     const int tiles3 = static_cast<int>(ceil_div(p.M, BM3)) * p.tiles_n;
     int pairs = g_num_sms / 2;
     if (tiles3 < pairs) pairs = tiles3;
-    gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, tc, p);
+    GemmParams q = p;
+    if (pairs != g_num_sms / 2) q.pair_stride = 1;   // the permutation is only a bijection on the full grid
+    gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, tc, q);
   } else if (cg >= 2) {
     static bool attr2_set = false;
     if (!attr2_set) {
@@ -989,7 +995,9 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
     const int tiles2 = static_cast<int>(ceil_div(p.M, BM2)) * p.tiles_n;
     int pairs = g_num_sms / 2;
     if (tiles2 < pairs) pairs = tiles2;
-    gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, tc, p);
+    GemmParams q = p;
+    if (pairs != g_num_sms / 2) q.pair_stride = 1;
+    gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, tc, q);
   } else {
     gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, tc, p);
   }
@@ -1036,6 +1044,13 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     if (g_opt_small_w_group > 0 && 2.0 * N * K <= 48e6) gm = g_opt_small_w_group;
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
     p.serp = g_opt_serp;
+    p.pair_stride = 1;
+    {
+      const int np = g_num_sms / 2;
+      int a = g_opt_pair_stride, b = np;
+      while (b) { const int t = a % b; a = b; b = t; }
+      if (g_opt_pair_stride > 1 && a == 1) p.pair_stride = g_opt_pair_stride;
+    }
   }
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
@@ -1100,6 +1115,11 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_l2_hint") {
     B2S_REQUIRE(value >= 0 && value <= 7, "set_option: gemm_l2_hint must be in [0, 7]");
     b2s::g_opt_hint = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_pair_stride") {
+    B2S_REQUIRE(value >= 1 && value <= 1024, "set_option: gemm_pair_stride must be in [1, 1024]");
+    b2s::g_opt_pair_stride = value;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_small_w_group") {
