@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define B2S_ABI_VERSION 1
+#define B2S_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define B2S_API __attribute__((visibility("default")))
@@ -30,8 +30,11 @@ extern "C" {
 
 enum { B2S_OK = 0, B2S_EINVAL = -1, B2S_ECUDA = -2, B2S_ENOMEM = -3, B2S_EUNSUPPORTED = -4 };
 
-enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1 };
-enum { B2S_QKV_FALCON_MQA = 0, B2S_QKV_NEOX_INTERLEAVED = 1 };
+enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1, B2S_ARCH_LLAMA = 2 };
+enum { B2S_NORM_LAYERNORM = 0, B2S_NORM_RMS = 1 };   /* RMSNorm: x * rsqrt(mean(x^2) + eps) * g, *_B slots null (HF llama LlamaRMSNorm) */
+enum { B2S_MLP_GELU = 0, B2S_MLP_SWIGLU = 1 };      /* SwiGLU: down(silu(gate(x)) * up(x)); W_UP slot = [2*d_ff, d_model], gate rows first */
+enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQA, cat(q,k,v)_proj of the Llama family */,
+       B2S_QKV_NEOX_INTERLEAVED = 1 /* per head [q, k, v] */ };
 /* compute modes (tensor-core modes: fp32 accumulation in TMEM, fp32 residual stream, LayerNorm and softmax):
  *   BF16_FAST   bf16 weight matrices; activations (every GEMM A operand, Q/K/V/P) rounded to bf16;
  *   FP16        fp16 weight matrices (bf16 checkpoints convert exactly for |w| >= 2^-17) and activations rounded
@@ -58,6 +61,8 @@ typedef struct {
   int32_t qkv_layout;          /* B2S_QKV_* */
   int32_t max_pos;             /* rows of the rope cos/sin tables */
   int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST expects bf16 matrices, FP16 fp16, FP32_CHECK fp32 */
+  int32_t norm_type;           /* B2S_NORM_*  (ABI 2) */
+  int32_t mlp_type;            /* B2S_MLP_*   (ABI 2) */
 } b2s_model_desc;
 
 typedef struct b2s_model b2s_model;

@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200score.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class B2SError(RuntimeError):
@@ -23,6 +23,7 @@ class ModelDesc(C.Structure):
         ("norm_eps", C.c_float),
         ("parallel_residual", C.c_int32), ("n_ln_per_layer", C.c_int32), ("has_bias", C.c_int32),
         ("qkv_layout", C.c_int32), ("max_pos", C.c_int32), ("compute_mode", C.c_int32),
+        ("norm_type", C.c_int32), ("mlp_type", C.c_int32),
     ]
 
 

@@ -28,7 +28,8 @@ from typing import Dict, Iterator, Optional, Tuple
 
 import torch
 
-from .shapes import ARCH_FALCON, ARCH_GPT_NEOX, QKV_FALCON_MQA, QKV_NEOX_INTERLEAVED, DecoderShape
+from .shapes import (ARCH_FALCON, ARCH_GPT_NEOX, ARCH_LLAMA, MLP_SWIGLU, NORM_RMS, QKV_FALCON_MQA, QKV_NEOX_INTERLEAVED,
+                     DecoderShape)
 from . import weights as _weights
 
 
@@ -86,6 +87,31 @@ def shape_from_hf_config(cfg: dict, name: str = "checkpoint") -> DecoderShape:
                             parallel_residual=bool(cfg.get("use_parallel_residual", True)), n_ln_per_layer=2, has_bias=True,
                             tied_head=bool(cfg.get("tie_word_embeddings", False)), qkv_layout=QKV_NEOX_INTERLEAVED,
                             eos_id=int(eos), max_pos=int(cfg.get("max_position_embeddings", 2048)))
+    if mt in ("llama", "mistral"):
+        # HF:models/llama/configuration_llama.py, models/mistral/configuration_mistral.py (Mistral-7B-Instruct-v0.3 of the
+        # instruct sweep, compare_instruct_models.py:157).  A sliding window shorter than the prompts would change the
+        # attention mask and is refused; v0.3 has none.
+        if cfg.get("hidden_act", "silu") != "silu":
+            raise KeyError(f"{name}: hidden_act {cfg.get('hidden_act')!r} is not supported (SiLU-gated MLP only)")
+        if cfg.get("attention_bias", False) or cfg.get("mlp_bias", False):
+            raise KeyError(f"{name}: Llama-family checkpoints with projection biases are not supported")
+        max_pos = int(cfg.get("max_position_embeddings", 4096))
+        sw = cfg.get("sliding_window")
+        if sw is not None and int(sw) < 4096:
+            raise KeyError(f"{name}: sliding_window {sw} is not supported")
+        d, n_head = int(cfg["hidden_size"]), int(cfg["num_attention_heads"])
+        hd = int(cfg.get("head_dim") or d // n_head)
+        theta, pct = _rope(cfg, ("rope_theta",), 1.0)
+        if pct != 1.0:
+            raise KeyError(f"{name}: partial rotary in a Llama-family model is not supported")
+        eos = cfg.get("eos_token_id", 2)
+        eos = eos[0] if isinstance(eos, (list, tuple)) else eos
+        return DecoderShape(name, ARCH_LLAMA, int(cfg["num_hidden_layers"]), d, n_head,
+                            int(cfg.get("num_key_value_heads") or n_head), hd, int(cfg["intermediate_size"]),
+                            int(cfg["vocab_size"]), hd, rope_theta=theta, norm_eps=float(cfg.get("rms_norm_eps", 1e-6)),
+                            parallel_residual=False, n_ln_per_layer=2, has_bias=False,
+                            tied_head=bool(cfg.get("tie_word_embeddings", False)), qkv_layout=QKV_FALCON_MQA, eos_id=int(eos),
+                            max_pos=min(max_pos, 32768), norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
     raise KeyError(f"{name}: architecture {mt!r} is not supported by the B200 scorer")
 
 
@@ -102,13 +128,20 @@ _NEOX_LAYER = {"input_layernorm.weight": "ln1_g", "input_layernorm.bias": "ln1_b
                "attention.dense.weight": "w_dense", "attention.dense.bias": "b_dense",
                "mlp.dense_h_to_4h.weight": "w_up", "mlp.dense_h_to_4h.bias": "b_up",
                "mlp.dense_4h_to_h.weight": "w_down", "mlp.dense_4h_to_h.bias": "b_down"}
-_LAYER_RE = re.compile(r"^(?:transformer\.h|gpt_neox\.layers)\.(\d+)\.(.+)$")
+_LLAMA_GLOBAL = {"model.embed_tokens.weight": "wte", "model.norm.weight": "lnf_g", "lm_head.weight": "lm_head"}
+# q/k/v and gate/up arrive as separate tensors and are fused by rows (":0" = first block of the fused matrix, ...)
+_LLAMA_LAYER = {"input_layernorm.weight": "ln1_g", "post_attention_layernorm.weight": "ln2_g",
+                "self_attn.q_proj.weight": "w_qkv:0", "self_attn.k_proj.weight": "w_qkv:1", "self_attn.v_proj.weight": "w_qkv:2",
+                "self_attn.o_proj.weight": "w_dense", "mlp.gate_proj.weight": "w_up:0", "mlp.up_proj.weight": "w_up:1",
+                "mlp.down_proj.weight": "w_down"}
+_LAYER_RE = re.compile(r"^(?:transformer\.h|gpt_neox\.layers|model\.layers)\.(\d+)\.(.+)$")
 
 
 def flat_name(shape: DecoderShape, hf_name: str) -> Optional[str]:
     """Name of an HF state-dict entry in the flat layout, or None for entries the scorer does not use (rotary
     ``inv_freq`` buffers, causal-mask buffers)."""
-    glob_map, layer_map = (_FALCON_GLOBAL, _FALCON_LAYER) if shape.arch == ARCH_FALCON else (_NEOX_GLOBAL, _NEOX_LAYER)
+    glob_map, layer_map = {ARCH_FALCON: (_FALCON_GLOBAL, _FALCON_LAYER), ARCH_GPT_NEOX: (_NEOX_GLOBAL, _NEOX_LAYER),
+                           ARCH_LLAMA: (_LLAMA_GLOBAL, _LLAMA_LAYER)}[shape.arch]
     if hf_name in glob_map:
         return glob_map[hf_name]
     m = _LAYER_RE.match(hf_name)
@@ -126,6 +159,8 @@ def expected_names(shape: DecoderShape):
             continue
         if leaf.startswith("b_") and not shape.has_bias:
             continue
+        if leaf in ("lnf_b", "ln1_b", "ln2_b") and shape.norm_type == NORM_RMS:
+            continue
         out.append(n)
     return out
 
@@ -133,9 +168,15 @@ def expected_names(shape: DecoderShape):
 def _check_shape(shape: DecoderShape, name: str, t: torch.Tensor):
     d, ff, V = shape.d_model, shape.d_ff, shape.vocab
     leaf = name.split(".")[-1]
+    nq, nk = shape.n_head * shape.head_dim, shape.n_kv_head * shape.head_dim
+    part = {"w_qkv:0": (nq, d), "w_qkv:1": (nk, d), "w_qkv:2": (nk, d), "w_up:0": (ff, d), "w_up:1": (ff, d)}
+    if leaf in part:
+        if tuple(t.shape) != part[leaf]:
+            raise ValueError(f"checkpoint tensor {name} has shape {tuple(t.shape)}, the config implies {part[leaf]}")
+        return
     want = {"wte": (V, d), "lm_head": (V, d), "lnf_g": (d,), "lnf_b": (d,), "ln1_g": (d,), "ln1_b": (d,), "ln2_g": (d,),
             "ln2_b": (d,), "w_qkv": (shape.qkv_dim, d), "b_qkv": (shape.qkv_dim,), "w_dense": (d, shape.n_head * shape.head_dim),
-            "b_dense": (d,), "w_up": (ff, d), "b_up": (ff,), "w_down": (d, ff), "b_down": (d,)}[leaf]
+            "b_dense": (d,), "w_up": (shape.up_dim, d), "b_up": (ff,), "w_down": (d, ff), "b_down": (d,)}[leaf]
     if tuple(t.shape) != want:
         raise ValueError(f"checkpoint tensor {name} has shape {tuple(t.shape)}, the config implies {want}")
 
@@ -150,7 +191,12 @@ def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.
         if n is None:
             continue
         _check_shape(shape, n, t)
-        W[n] = t.to(device=device, dtype=weight_dtype if _weights.is_matrix(n) else torch.float32).contiguous()
+        W[n] = t.to(device=device, dtype=weight_dtype if _weights.is_matrix(n.split(":")[0]) else torch.float32).contiguous()
+        base = n.split(":")[0]
+        if base != n:                                  # a block of a fused matrix: fuse once every block is here
+            blocks = [f"{base}:{i}" for i in range(3 if base.endswith("w_qkv") else 2)]
+            if all(b in W for b in blocks):
+                W[base] = torch.cat([W.pop(b) for b in blocks], dim=0).contiguous()
     if "lm_head" not in W:
         if not shape.tied_head:
             raise ValueError("checkpoint has no output embedding and the config does not tie it to the input embedding")

@@ -89,7 +89,8 @@ ln_kernel(LnArgs a) {
       sum += (v.x + v.y) + (v.z + v.w);
     }
   }
-  const float mean = block_sum(sum, red) / d;
+  const float row_sum = block_sum(sum, red);                  // (also the barrier that publishes srow)
+  const float mean = a.rms ? 0.f : row_sum / d;               // RMSNorm: second moment about zero
   // passes 2 and 3 walk the row four elements at a time (d % 4 == 0): 16-byte smem / gain / bias loads, 8-byte
   // (16-bit outputs) or 16-byte (fp32) stores
   const float4* s4 = reinterpret_cast<const float4*>(srow);
@@ -107,13 +108,14 @@ ln_kernel(LnArgs a) {
   const float4* b1 = reinterpret_cast<const float4*>(a.b1);
   const float4* g2 = reinterpret_cast<const float4*>(a.g2);
   const float4* b2 = reinterpret_cast<const float4*>(a.b2);
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int i = threadIdx.x; i < d4; i += blockDim.x) {
     const float4 v = s4[i];
     const float n0 = (v.x - mean) * rstd, n1 = (v.y - mean) * rstd, n2 = (v.z - mean) * rstd, n3 = (v.w - mean) * rstd;
-    const float4 g = g1[i], b = b1[i];
+    const float4 g = g1[i], b = b1 ? b1[i] : zero;
     store4(y1 + 4 * i, n0 * g.x + b.x, n1 * g.y + b.y, n2 * g.z + b.z, n3 * g.w + b.w);
     if (y2) {
-      const float4 h = g2[i], c = b2[i];
+      const float4 h = g2[i], c = b2 ? b2[i] : zero;
       store4(y2 + 4 * i, n0 * h.x + c.x, n1 * h.y + c.y, n2 * h.z + c.z, n3 * h.w + c.w);
     }
   }
@@ -133,6 +135,46 @@ int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st) {
 template int launch_ln<float, float>(const LnArgs&, int, cudaStream_t);
 template int launch_ln<__nv_bfloat16, __nv_bfloat16>(const LnArgs&, int, cudaStream_t);
 template int launch_ln<__half, __half>(const LnArgs&, int, cudaStream_t);
+
+// =================================================================================================
+// SwiGLU gate (Llama family): act = silu(gate) * up on the [rows, 2*ff] output of the fused gate/up projection
+//   HF:models/llama/modeling_llama.py LlamaMLP.forward: down_proj(act_fn(gate_proj(x)) * up_proj(x)), act_fn = SiLU.
+// HBM-bound: rows * ff * 3 elements; four elements per thread, fp32 math.
+// =================================================================================================
+template <typename AT>
+__global__ void __launch_bounds__(256)
+swiglu_kernel(const AT* __restrict__ gu, AT* __restrict__ act, int64_t rows, int ff) {
+  const int ff4 = ff >> 2;
+  const int64_t n = rows * ff4;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / ff4;
+    const int c = static_cast<int>(i - r * ff4) * 4;
+    const AT* g = gu + r * (2 * static_cast<int64_t>(ff)) + c;
+    const AT* u = g + ff;
+    float o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float x = to_f32(g[k]);
+      o[k] = x / (1.f + expf(-x)) * to_f32(u[k]);
+    }
+    store4(act + r * ff + c, o[0], o[1], o[2], o[3]);
+  }
+}
+
+template <typename AT>
+int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st) {
+  B2S_REQUIRE(ff % 4 == 0, "swiglu: d_ff=%d must be a multiple of 4", ff);
+  const int64_t n = rows * (ff >> 2);
+  const int64_t blocks = ceil_div(n, 256);
+  const unsigned grid = static_cast<unsigned>(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
+  swiglu_kernel<AT><<<grid, 256, 0, st>>>(reinterpret_cast<const AT*>(gu), reinterpret_cast<AT*>(act), rows, ff);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+template int launch_swiglu<float>(const void*, void*, int64_t, int, cudaStream_t);
+template int launch_swiglu<__nv_bfloat16>(const void*, void*, int64_t, int, cudaStream_t);
+template int launch_swiglu<__half>(const void*, void*, int64_t, int, cudaStream_t);
 
 // =================================================================================================
 // RoPE (rotate_half form on the first rotary_dim dims) + KV-cache append.

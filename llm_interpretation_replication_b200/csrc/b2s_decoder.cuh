@@ -26,6 +26,7 @@ struct LnArgs {
   void *y1, *y2;            // outputs (AT); y2 optional (second LayerNorm of a parallel-residual layer)
   int d;
   float eps;
+  int rms;                  // RMSNorm: no mean subtraction, no bias (b1/b2 null)
 };
 
 struct RopeArgs {
@@ -63,6 +64,8 @@ int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const Ba
 template <typename AT, typename WT> int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
+// act[r, j] = silu(gu[r, j]) * gu[r, ff + j]   (HF llama LlamaMLP: act_fn(gate_proj(x)) * up_proj(x))
+template <typename AT> int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st);
 // tcgen05 prefill attention (b2s_attn_tc.cu): head_dim 64, <= 256 keys per sequence
 bool attn_tc_supported(int hd, int max_kv);
 bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride);

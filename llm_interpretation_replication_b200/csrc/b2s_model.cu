@@ -48,7 +48,7 @@ struct Workspace {
   float* out;
   ScanState scan;
   float* resid;
-  void *ln1, *ln2, *qkv, *attn, *act, *hfin;
+  void *ln1, *ln2, *qkv, *attn, *act, *gu, *hfin;
   void *kcache, *vcache;
   size_t cache_layer_bytes;
   size_t cache_slots;
@@ -92,6 +92,7 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.qkv = take(at * rows * m->qkv_dim);
   w.attn = take(at * rows * d.n_head * d.head_dim);
   w.act = take(at * rows * d.d_ff);
+  w.gu = d.mlp_type == B2S_MLP_SWIGLU ? take(at * rows * 2 * d.d_ff) : nullptr;   // gate | up before the SwiGLU kernel
   w.hfin = take(at * static_cast<size_t>(N) * d.d_model);
   const size_t slots = static_cast<size_t>(T) + static_cast<size_t>(N) * LA;
   w.cache_slots = slots;
@@ -123,7 +124,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
   const bool two_ln = d.n_ln_per_layer == 2;
   for (int l = 0; l < d.n_layer; ++l) {
     LnArgs ln{};
-    ln.x = w.resid; ln.d = dm; ln.eps = d.norm_eps;
+    ln.x = w.resid; ln.d = dm; ln.eps = d.norm_eps; ln.rms = d.norm_type == B2S_NORM_RMS;
     ln.tokens = (l == 0) ? tokens : nullptr;
     ln.wte = m->gw(B2S_W_WTE);
     ln.g1 = m->lwf(l, B2S_WL_LN1_G); ln.b1 = m->lwf(l, B2S_WL_LN1_B);
@@ -181,18 +182,23 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       mlp_in = w.ln2;
       if (!d.parallel_residual) {   // sequential residual: second LayerNorm reads x + attn
         LnArgs l2{};
-        l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps;
+        l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps; l2.rms = d.norm_type == B2S_NORM_RMS;
         l2.g1 = m->lwf(l, B2S_WL_LN2_G); l2.b1 = m->lwf(l, B2S_WL_LN2_B); l2.y1 = w.ln2;
         B2S_TRY((launch_ln<AT, WT>(l2, rows, st)));
       }
     }
-    B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st));
+    if (d.mlp_type == B2S_MLP_SWIGLU) {   // fused gate|up projection, then act = silu(gate) * up
+      B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), nullptr, w.gu, rows, 2 * d.d_ff, dm, EPI_STORE_BF16, st));
+      B2S_TRY(launch_swiglu<AT>(w.gu, w.act, rows, d.d_ff, st));
+    } else {
+      B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st));
+    }
     B2S_TRY(linear(m, w.act, m->lw(l, B2S_WL_W_DOWN), m->lwf(l, B2S_WL_B_DOWN), w.resid, rows, dm, d.d_ff,
                    EPI_RESID_F32, st));
   }
   // final LayerNorm on the last row of every prompt only (HF generate sets logits_to_keep=1)
   LnArgs lf{};
-  lf.x = w.resid; lf.d = dm; lf.eps = d.norm_eps; lf.rows = w.meta.last_row;
+  lf.x = w.resid; lf.d = dm; lf.eps = d.norm_eps; lf.rows = w.meta.last_row; lf.rms = d.norm_type == B2S_NORM_RMS;
   lf.g1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_G)); lf.b1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_B));
   lf.y1 = w.hfin;
   B2S_TRY((launch_ln<AT, WT>(lf, n_seqs, st)));
@@ -252,6 +258,9 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   B2S_REQUIRE(d.rotary_dim > 0 && d.rotary_dim <= d.head_dim && d.rotary_dim % 2 == 0, "model_create: bad rotary_dim %d",
               d.rotary_dim);
   B2S_REQUIRE(d.n_ln_per_layer == 1 || d.n_ln_per_layer == 2, "model_create: n_ln_per_layer must be 1 or 2");
+  B2S_REQUIRE(d.norm_type == B2S_NORM_LAYERNORM || d.norm_type == B2S_NORM_RMS, "model_create: unknown norm_type %d", d.norm_type);
+  B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || d.mlp_type == B2S_MLP_SWIGLU, "model_create: unknown mlp_type %d", d.mlp_type);
+  B2S_REQUIRE(d.mlp_type != B2S_MLP_SWIGLU || !d.has_bias, "model_create: SwiGLU with biases is not supported");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
   B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_FP32_CHECK,
               "model_create: unknown compute mode %d", d.compute_mode);
@@ -289,16 +298,17 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
     set_error("model_create: unknown qkv layout %d", d.qkv_layout);
     return B2S_EINVAL;
   }
+  const bool rms = d.norm_type == B2S_NORM_RMS;   // RMSNorm has gains only
   const int required[] = {B2S_W_WTE, B2S_W_LNF_G, B2S_W_LNF_B, B2S_W_LM_HEAD, B2S_W_ROPE_COS, B2S_W_ROPE_SIN};
   for (int s : required) {
-    if (m->w[s] == nullptr) { delete m; set_error("model_create: global weight slot %d is null", s); return B2S_EINVAL; }
+    if (m->w[s] == nullptr && !(rms && s == B2S_W_LNF_B)) { delete m; set_error("model_create: global weight slot %d is null", s); return B2S_EINVAL; }
   }
   for (int l = 0; l < d.n_layer; ++l) {
     const int mats[] = {B2S_WL_LN1_G, B2S_WL_LN1_B, B2S_WL_W_QKV, B2S_WL_W_DENSE, B2S_WL_W_UP, B2S_WL_W_DOWN};
     for (int s : mats) {
-      if (m->lw(l, s) == nullptr) { delete m; set_error("model_create: layer %d slot %d is null", l, s); return B2S_EINVAL; }
+      if (m->lw(l, s) == nullptr && !(rms && s == B2S_WL_LN1_B)) { delete m; set_error("model_create: layer %d slot %d is null", l, s); return B2S_EINVAL; }
     }
-    if (d.n_ln_per_layer == 2 && (m->lw(l, B2S_WL_LN2_G) == nullptr || m->lw(l, B2S_WL_LN2_B) == nullptr)) {
+    if (d.n_ln_per_layer == 2 && (m->lw(l, B2S_WL_LN2_G) == nullptr || (!rms && m->lw(l, B2S_WL_LN2_B) == nullptr))) {
       delete m; set_error("model_create: layer %d second LayerNorm is null", l); return B2S_EINVAL;
     }
   }

@@ -102,7 +102,7 @@ class Scorer:
                            vocab=shape.vocab, rotary_dim=shape.rotary_dim, norm_eps=shape.norm_eps,
                            parallel_residual=int(shape.parallel_residual), n_ln_per_layer=shape.n_ln_per_layer,
                            has_bias=int(shape.has_bias), qkv_layout=shape.qkv_layout, max_pos=shape.max_pos,
-                           compute_mode=mode)
+                           compute_mode=mode, norm_type=shape.norm_type, mlp_type=shape.mlp_type)
         self._handle = C.c_void_p()
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2s_model_create(C.byref(d), self._ptrs, len(self._ptrs), self.device.index or 0,

@@ -13,9 +13,17 @@ from dataclasses import dataclass, asdict, replace
 # arch codes (must match include/b200score.h)
 ARCH_FALCON = 0
 ARCH_GPT_NEOX = 1
+ARCH_LLAMA = 2            # Llama / Mistral family: RMSNorm, SwiGLU, grouped-query attention, no biases
+
+# normalisation and MLP kinds (must match include/b200score.h)
+NORM_LAYERNORM = 0
+NORM_RMS = 1              # x * rsqrt(mean(x^2) + eps) * g, no bias   (HF llama LlamaRMSNorm)
+MLP_GELU = 0              # down(gelu(up(x)))
+MLP_SWIGLU = 1            # down(silu(gate(x)) * up(x)); the W_UP slot holds [gate rows; up rows]  (HF llama LlamaMLP)
 
 # qkv column layouts (must match include/b200score.h)
-QKV_FALCON_MQA = 0       # [q_0 .. q_{nh-1}, k, v] each head_dim wide   (HF falcon _split_heads, multi_query)
+QKV_FALCON_MQA = 0       # [q_0 .. q_{nh-1}, k_0 .. k_{nkv-1}, v_0 .. v_{nkv-1}] each head_dim wide (HF falcon _split_heads with
+                         # multi_query: nkv = 1; also cat(q_proj, k_proj, v_proj) of the Llama family)
 QKV_NEOX_INTERLEAVED = 1  # per head [q, k, v]                            (HF gpt_neox qkv.chunk(3))
 
 # compute modes (must match include/b200score.h)
@@ -45,6 +53,13 @@ class DecoderShape:
     qkv_layout: int = QKV_FALCON_MQA
     eos_id: int = 11
     max_pos: int = 2048
+    norm_type: int = NORM_LAYERNORM
+    mlp_type: int = MLP_GELU
+
+    @property
+    def up_dim(self) -> int:
+        """Rows of the W_UP slot: d_ff, or 2 * d_ff (gate rows, then up rows) for SwiGLU."""
+        return self.d_ff * (2 if self.mlp_type == MLP_SWIGLU else 1)
 
     @property
     def qkv_dim(self) -> int:
@@ -53,7 +68,7 @@ class DecoderShape:
     @property
     def layer_params(self) -> int:
         d, ff = self.d_model, self.d_ff
-        return d * self.qkv_dim + d * self.n_head * self.head_dim + 2 * d * ff
+        return d * self.qkv_dim + d * self.n_head * self.head_dim + d * self.up_dim + d * ff
 
     def flops_per_token(self) -> float:
         """Algorithmic GEMM FLOPs per prompt token."""
@@ -112,7 +127,41 @@ def dolly_v2_7b() -> DecoderShape:
                         qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=0)
 
 
+def mistral_7b() -> DecoderShape:
+    # mistralai/Mistral-7B-Instruct-v0.3 (compare_instruct_models.py:157): GQA 32/8, head_dim 128, SwiGLU 14336,
+    # vocab 32768, rope_theta 1e6, no sliding window
+    return DecoderShape("mistral-7b", ARCH_LLAMA, 32, 4096, 32, 8, 128, 14336, 32768, 128, rope_theta=1000000.0,
+                        norm_eps=1e-5, parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=2, max_pos=32768, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+
+
+def llama2_7b() -> DecoderShape:
+    # meta-llama/Llama-2-7b-chat-hf (commented out in the reference's list, compare_instruct_models.py:155)
+    return DecoderShape("llama-2-7b", ARCH_LLAMA, 32, 4096, 32, 32, 128, 11008, 32000, 128, rope_theta=10000.0,
+                        norm_eps=1e-5, parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=2, max_pos=4096, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+
+
 # tiny variants (CPU-oracle sized) --------------------------------------------------------
+def tiny_llama(vocab=288, n_layer=2, n_head=4, n_kv_head=2) -> DecoderShape:
+    # head_dim 64: the tensor-core attention and the fused QKV+RoPE epilogue with grouped-query heads
+    hd = 64
+    d = n_head * hd
+    return DecoderShape("tiny-llama", ARCH_LLAMA, n_layer, d, n_head, n_kv_head, hd, 3 * d - 64, vocab, hd, rope_theta=10000.0,
+                        norm_eps=1e-5, parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=2, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+
+
+def tiny_mistral(vocab=264, n_layer=2, n_head=4, n_kv_head=1) -> DecoderShape:
+    # Mistral-like: head_dim 128 (CUDA-core attention, separate RoPE kernel), rope_theta 1e6
+    hd = 128
+    d = n_head * hd
+    return DecoderShape("tiny-mistral", ARCH_LLAMA, n_layer, d, n_head, n_kv_head, hd, 2 * d + 128, vocab, hd,
+                        rope_theta=1000000.0, norm_eps=1e-5, parallel_residual=False, n_ln_per_layer=2, has_bias=False,
+                        tied_head=False, qkv_layout=QKV_FALCON_MQA, eos_id=2, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+
+
+
 def tiny_falcon(vocab=256, n_layer=2, n_head=3) -> DecoderShape:
     hd = 64
     d = n_head * hd
@@ -146,6 +195,10 @@ REGISTRY = {
     "redpajama-incite-base-3b": redpajama_3b,
     "h2ogpt-oasst1-512-12b": h2ogpt_12b,
     "dolly-v2-7b": dolly_v2_7b,
+    "mistral-7b": mistral_7b,
+    "llama-2-7b": llama2_7b,
+    "tiny-llama": tiny_llama,
+    "tiny-mistral": tiny_mistral,
     "tiny-falcon": tiny_falcon,
     "tiny-neox-par": tiny_neox_parallel,
     "tiny-neox-seq": tiny_neox_sequential,
@@ -162,4 +215,6 @@ HUB_TO_SHAPE = {
     "togethercomputer/RedPajama-INCITE-Instruct-3B-v1": redpajama_3b,
     "h2oai/h2ogpt-oasst1-512-12b": h2ogpt_12b,
     "EleutherAI/pythia-6.9b": dolly_v2_7b, "databricks/dolly-v2-7b": dolly_v2_7b,
+    "mistralai/Mistral-7B-Instruct-v0.3": mistral_7b, "mistralai/Mistral-7B-v0.3": mistral_7b,
+    "meta-llama/Llama-2-7b-chat-hf": llama2_7b, "meta-llama/Llama-2-7b-hf": llama2_7b,
 }

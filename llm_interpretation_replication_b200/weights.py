@@ -10,7 +10,8 @@ Slot order (``B2S_W_*`` in the header):
   global:    0 wte[V,d]  1 lnf_g[d]  2 lnf_b[d]  3 lm_head[V,d]  4 rope_cos[max_pos,rd/2]  5 rope_sin
   per layer: base = 6 + 16*l
              +0 ln1_g +1 ln1_b +2 ln2_g +3 ln2_b +4 w_qkv[qkv,d] +5 b_qkv +6 w_dense[d,nh*hd] +7 b_dense
-             +8 w_up[ff,d] +9 b_up +10 w_down[d,ff] +11 b_down   (+12..15 reserved)
+             +8 w_up[ff,d] ([2ff,d] = gate rows then up rows for SwiGLU) +9 b_up +10 w_down[d,ff] +11 b_down   (+12..15 reserved)
+RMSNorm models have no *_b vectors (null slots).
 Matrices are stored in the model's weight dtype (bf16 or fp32); vectors are always fp32.
 """
 from __future__ import annotations
@@ -19,7 +20,7 @@ from typing import Dict, List, Optional
 
 import torch
 
-from .shapes import DecoderShape, ARCH_FALCON, ARCH_GPT_NEOX
+from .shapes import DecoderShape, ARCH_FALCON, ARCH_GPT_NEOX, ARCH_LLAMA, NORM_RMS
 
 N_GLOBAL = 6
 N_PER_LAYER = 16
@@ -72,19 +73,23 @@ def init_weights(shape: DecoderShape, seed: int = 0, device: str = "cpu",
 
     W: Dict[str, torch.Tensor] = {}
     W["wte"] = mat(V, d)
+    rms = shape.norm_type == NORM_RMS
     W["lnf_g"] = vec(d, 1.0, 0.1)
-    W["lnf_b"] = vec(d, 0.0, 0.05)
+    if not rms:
+        W["lnf_b"] = vec(d, 0.0, 0.05)
     W["lm_head"] = W["wte"] if shape.tied_head else mat(V, d)
     for l in range(shape.n_layer):
         p = f"l{l}."
         W[p + "ln1_g"] = vec(d, 1.0, 0.1)
-        W[p + "ln1_b"] = vec(d, 0.0, 0.05)
+        if not rms:
+            W[p + "ln1_b"] = vec(d, 0.0, 0.05)
         if shape.n_ln_per_layer == 2:
             W[p + "ln2_g"] = vec(d, 1.0, 0.1)
-            W[p + "ln2_b"] = vec(d, 0.0, 0.05)
+            if not rms:
+                W[p + "ln2_b"] = vec(d, 0.0, 0.05)
         W[p + "w_qkv"] = mat(shape.qkv_dim, d)
         W[p + "w_dense"] = mat(d, shape.n_head * shape.head_dim)
-        W[p + "w_up"] = mat(ff, d)
+        W[p + "w_up"] = mat(shape.up_dim, d)
         W[p + "w_down"] = mat(d, ff)
         if shape.has_bias:
             W[p + "b_qkv"] = vec(shape.qkv_dim, 0.0, 0.02)
@@ -114,19 +119,23 @@ def init_weights_device(shape: DecoderShape, seed: int, device, weight_dtype=tor
 
     W: Dict[str, torch.Tensor] = {}
     W["wte"] = mat(V, d)
+    rms = shape.norm_type == NORM_RMS
     W["lnf_g"] = vec(d, 1.0, 0.1)
-    W["lnf_b"] = vec(d, 0.0, 0.05)
+    if not rms:
+        W["lnf_b"] = vec(d, 0.0, 0.05)
     W["lm_head"] = W["wte"] if shape.tied_head else mat(V, d)
     for l in range(shape.n_layer):
         p = f"l{l}."
         W[p + "ln1_g"] = vec(d, 1.0, 0.1)
-        W[p + "ln1_b"] = vec(d, 0.0, 0.05)
+        if not rms:
+            W[p + "ln1_b"] = vec(d, 0.0, 0.05)
         if shape.n_ln_per_layer == 2:
             W[p + "ln2_g"] = vec(d, 1.0, 0.1)
-            W[p + "ln2_b"] = vec(d, 0.0, 0.05)
+            if not rms:
+                W[p + "ln2_b"] = vec(d, 0.0, 0.05)
         W[p + "w_qkv"] = mat(shape.qkv_dim, d)
         W[p + "w_dense"] = mat(d, shape.n_head * shape.head_dim)
-        W[p + "w_up"] = mat(ff, d)
+        W[p + "w_up"] = mat(shape.up_dim, d)
         W[p + "w_down"] = mat(d, ff)
         if shape.has_bias:
             W[p + "b_qkv"] = vec(shape.qkv_dim, 0.0, 0.02)
@@ -180,6 +189,14 @@ def hf_config(shape: DecoderShape):
                              bos_token_id=shape.eos_id, eos_token_id=shape.eos_id,
                              max_position_embeddings=shape.max_pos, tie_word_embeddings=False,
                              attention_bias=True, hidden_dropout=0.0, attention_dropout=0.0)
+    if shape.arch == ARCH_LLAMA:
+        from transformers import LlamaConfig
+        return LlamaConfig(vocab_size=shape.vocab, hidden_size=shape.d_model, intermediate_size=shape.d_ff,
+                           num_hidden_layers=shape.n_layer, num_attention_heads=shape.n_head,
+                           num_key_value_heads=shape.n_kv_head, head_dim=shape.head_dim, hidden_act="silu",
+                           max_position_embeddings=shape.max_pos, rms_norm_eps=shape.norm_eps, rope_theta=shape.rope_theta,
+                           attention_bias=False, mlp_bias=False, tie_word_embeddings=shape.tied_head,
+                           bos_token_id=1, eos_token_id=shape.eos_id, attention_dropout=0.0)
     raise ValueError(shape.arch)
 
 
@@ -198,6 +215,23 @@ def to_hf_state_dict(shape: DecoderShape, W: Dict[str, torch.Tensor]) -> Dict[st
             sd[h + "self_attention.dense.weight"] = W[p + "w_dense"]
             sd[h + "mlp.dense_h_to_4h.weight"] = W[p + "w_up"]
             sd[h + "mlp.dense_4h_to_h.weight"] = W[p + "w_down"]
+    elif shape.arch == ARCH_LLAMA:
+        # HF:models/llama/modeling_llama.py: separate q/k/v and gate/up projections; the flat layout fuses them by rows
+        nq, nk, ff = shape.n_head * shape.head_dim, shape.n_kv_head * shape.head_dim, shape.d_ff
+        sd["model.embed_tokens.weight"] = W["wte"]
+        sd["model.norm.weight"] = W["lnf_g"]
+        sd["lm_head.weight"] = W["lm_head"]
+        for l in range(shape.n_layer):
+            p, h = f"l{l}.", f"model.layers.{l}."
+            sd[h + "input_layernorm.weight"] = W[p + "ln1_g"]
+            sd[h + "post_attention_layernorm.weight"] = W[p + "ln2_g"]
+            sd[h + "self_attn.q_proj.weight"] = W[p + "w_qkv"][:nq]
+            sd[h + "self_attn.k_proj.weight"] = W[p + "w_qkv"][nq:nq + nk]
+            sd[h + "self_attn.v_proj.weight"] = W[p + "w_qkv"][nq + nk:]
+            sd[h + "self_attn.o_proj.weight"] = W[p + "w_dense"]
+            sd[h + "mlp.gate_proj.weight"] = W[p + "w_up"][:ff]
+            sd[h + "mlp.up_proj.weight"] = W[p + "w_up"][ff:]
+            sd[h + "mlp.down_proj.weight"] = W[p + "w_down"]
     else:
         sd["gpt_neox.embed_in.weight"] = W["wte"]
         sd["gpt_neox.final_layer_norm.weight"] = W["lnf_g"]
@@ -224,12 +258,12 @@ def build_hf_model(shape: DecoderShape, W: Dict[str, torch.Tensor]):
     """Instantiate the HF model on the meta device and bind ``W`` (fp32, CPU) to it; avoids the
     minutes-long HF random init for 7B shapes."""
     import torch.nn as nn
-    from transformers import FalconForCausalLM, GPTNeoXForCausalLM
+    from transformers import FalconForCausalLM, GPTNeoXForCausalLM, LlamaForCausalLM
     cfg = hf_config(shape)
-    cls = FalconForCausalLM if shape.arch == ARCH_FALCON else GPTNeoXForCausalLM
+    cls = {ARCH_FALCON: FalconForCausalLM, ARCH_GPT_NEOX: GPTNeoXForCausalLM, ARCH_LLAMA: LlamaForCausalLM}[shape.arch]
     with torch.device("meta"):
         model = cls(cfg)
-    sd = {k: v.to(torch.float32) for k, v in to_hf_state_dict(shape, W).items()}
+    sd = {k: v.to(torch.float32).contiguous() for k, v in to_hf_state_dict(shape, W).items()}
     missing, unexpected = model.load_state_dict(sd, strict=False, assign=True)
     # rotary inv_freq buffers are non-persistent and were created on meta: rebuild them
     for mod in model.modules():

@@ -8,6 +8,9 @@ Follows, for the two families on the hot path:
   GPT-NeoX HF:models/gpt_neox/modeling_gpt_neox.py:38-49 (MLP), :126-159 (partial rotary),
            :203-244 (attention, per-head [q,k,v] interleave), :258-289 (layer, parallel/sequential),
            :331-381 (model), :463-464 (embed_out)
+  Llama    HF:models/llama/modeling_llama.py LlamaRMSNorm (x * rsqrt(mean(x^2) + eps) * w), LlamaMLP
+           (down(silu(gate(x)) * up(x))), LlamaAttention (grouped-query heads, rotate_half RoPE on the whole head),
+           LlamaDecoderLayer (sequential residual, two norms) -- also Mistral without a sliding window
 It is validated against the HF modules themselves in tests/test_oracle_decoder.py, and is what the
 GPU parity tests call (it is faster than ``generate`` and can emulate bf16 operand rounding).
 """
@@ -19,7 +22,7 @@ from typing import Callable, Dict, List, Optional
 import torch
 import torch.nn.functional as F
 
-from llm_interpretation_replication_b200.shapes import DecoderShape, QKV_FALCON_MQA
+from llm_interpretation_replication_b200.shapes import DecoderShape, QKV_FALCON_MQA, NORM_RMS, MLP_SWIGLU
 
 
 def _rope_cos_sin(shape: DecoderShape, L: int):
@@ -47,8 +50,8 @@ def _split_qkv(shape: DecoderShape, qkv):
     L = qkv.shape[0]
     nh, nkv, hd = shape.n_head, shape.n_kv_head, shape.head_dim
     if shape.qkv_layout == QKV_FALCON_MQA:
-        x = qkv.view(L, nh + 2, hd)
-        return x[:, :nh], x[:, nh:nh + 1], x[:, nh + 1:nh + 2]
+        x = qkv.view(L, nh + 2 * nkv, hd)
+        return x[:, :nh], x[:, nh:nh + nkv], x[:, nh + nkv:nh + 2 * nkv]
     x = qkv.view(L, nh, 3, hd)
     return x[:, :, 0], x[:, :, 1], x[:, :, 2]
 
@@ -64,10 +67,23 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
     cos, sin = cos.to(dtype), sin.to(dtype)
     x = W["wte"].to(dtype)[ids]
     causal = torch.tril(torch.ones(L, L, dtype=torch.bool))
+
+    def norm(t, g, b):
+        if shape.norm_type == NORM_RMS:
+            return t * torch.rsqrt(t.pow(2).mean(-1, keepdim=True) + shape.norm_eps) * W[g].to(dtype)
+        return F.layer_norm(t, (d,), W[g].to(dtype), W[b].to(dtype), shape.norm_eps)
+
+    def mlp_act(t, p, bias):
+        up = F.linear(r(t), W[p + "w_up"].to(dtype), bias("b_up"))
+        if shape.mlp_type == MLP_SWIGLU:        # rows [0, ff) = gate_proj, [ff, 2ff) = up_proj
+            up = r(up)                          # the 16-bit modes store gate/up before the elementwise kernel
+            return F.silu(up[..., :shape.d_ff]) * up[..., shape.d_ff:]
+        return F.gelu(up)
+
     for l in range(shape.n_layer):
         p = f"l{l}."
         bias = (lambda n: W[p + n].to(dtype)) if shape.has_bias else (lambda n: None)
-        ln1 = F.layer_norm(x, (d,), W[p + "ln1_g"].to(dtype), W[p + "ln1_b"].to(dtype), shape.norm_eps)
+        ln1 = norm(x, p + "ln1_g", p + "ln1_b")
         qkv = F.linear(r(ln1), W[p + "w_qkv"].to(dtype), bias("b_qkv"))
         q, k, v = _split_qkv(shape, qkv)
         q = r(_apply_rope(q, cos, sin, shape.rotary_dim))
@@ -82,18 +98,17 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         o = torch.einsum("hqk,khd->qhd", a, vv).reshape(L, nh * hd)
         attn = F.linear(r(o), W[p + "w_dense"].to(dtype), bias("b_dense"))
         if shape.parallel_residual:
-            ln2 = ln1 if shape.n_ln_per_layer == 1 else F.layer_norm(
-                x, (d,), W[p + "ln2_g"].to(dtype), W[p + "ln2_b"].to(dtype), shape.norm_eps)
-            h = F.gelu(F.linear(r(ln2), W[p + "w_up"].to(dtype), bias("b_up")))
+            ln2 = ln1 if shape.n_ln_per_layer == 1 else norm(x, p + "ln2_g", p + "ln2_b")
+            h = mlp_act(ln2, p, bias)
             mlp = F.linear(r(h), W[p + "w_down"].to(dtype), bias("b_down"))
             x = mlp + attn + x
         else:
             x1 = attn + x
-            ln2 = F.layer_norm(x1, (d,), W[p + "ln2_g"].to(dtype), W[p + "ln2_b"].to(dtype), shape.norm_eps)
-            h = F.gelu(F.linear(r(ln2), W[p + "w_up"].to(dtype), bias("b_up")))
+            ln2 = norm(x1, p + "ln2_g", p + "ln2_b")
+            h = mlp_act(ln2, p, bias)
             mlp = F.linear(r(h), W[p + "w_down"].to(dtype), bias("b_down"))
             x = mlp + x1
-    return F.layer_norm(x, (d,), W["lnf_g"].to(dtype), W["lnf_b"].to(dtype), shape.norm_eps)
+    return norm(x, "lnf_g", "lnf_b")
 
 
 def last_logits(shape, W, ids, round_act=None, dtype=torch.float32) -> torch.Tensor:

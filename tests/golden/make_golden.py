@@ -71,14 +71,20 @@ def extract_k2_scorer():
     return ns["get_yes_no_logprobs"]
 
 
-def scorer_goldens(R, k2_fn):
+SPECS = [
+    ("tiny-falcon", shapes.tiny_falcon(), 101),
+    ("tiny-neox-par", shapes.tiny_neox_parallel(), 102),
+    ("tiny-neox-seq", shapes.tiny_neox_sequential(), 103),
+    # Llama family (Mistral-7B-Instruct of the instruct sweep, compare_instruct_models.py:157): added later with
+    # `make_golden.py --append 3`, which leaves the first three cases and the bootstrap goldens untouched
+    ("tiny-llama", shapes.tiny_llama(), 104),
+    ("tiny-mistral", shapes.tiny_mistral(), 105),
+]
+
+
+def scorer_goldens(R, k2_fn, specs=SPECS):
     pert = json.load(open(os.path.join(REF, "data", "perturbations.json")))
     cases = []
-    specs = [
-        ("tiny-falcon", shapes.tiny_falcon(), 101),
-        ("tiny-neox-par", shapes.tiny_neox_parallel(), 102),
-        ("tiny-neox-seq", shapes.tiny_neox_sequential(), 103),
-    ]
     for name, shp, seed in specs:
         W = weights.init_weights(shp, seed=seed)
         model = weights.build_hf_model(shp, W)
@@ -224,6 +230,15 @@ def main():
     scratch = tempfile.mkdtemp(prefix="golden_")
     R = import_reference_100q(scratch)
     k2 = extract_k2_scorer()
+    if len(sys.argv) > 2 and sys.argv[1] == "--append":      # only the cases from SPECS[n:], appended to the file
+        n = int(sys.argv[2])
+        path = os.path.join(HERE, "scorer_golden.json")
+        old = json.load(open(path))
+        assert len(old["cases"]) == n, (len(old["cases"]), n)
+        old["cases"] += scorer_goldens(R, k2, SPECS[n:])["cases"]
+        json.dump(old, open(path, "w"), indent=1)
+        print("appended", len(SPECS) - n, "cases")
+        return
     sg = scorer_goldens(R, k2)
     json.dump(sg, open(os.path.join(HERE, "scorer_golden.json"), "w"), indent=1)
     bg = bootstrap_goldens(R, scratch)

@@ -15,7 +15,7 @@ def _save_hf(shape, W, path, safe=True):
     return model
 
 
-@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_neox_sequential"])
+@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_neox_sequential", "tiny_llama", "tiny_mistral"])
 @pytest.mark.parametrize("safe", [True, False], ids=["safetensors", "bin"])
 def test_checkpoint_round_trip(tmp_path, maker, safe):
     """A checkpoint written by transformers itself comes back as the same shape and bit-identical tensors."""
@@ -24,7 +24,8 @@ def test_checkpoint_round_trip(tmp_path, maker, safe):
     _save_hf(shp, W, str(tmp_path), safe=safe)
     shp2, W2 = checkpoint.load_checkpoint(str(tmp_path), device="cpu", weight_dtype=torch.float32)
     for f in ("arch", "n_layer", "d_model", "n_head", "n_kv_head", "head_dim", "d_ff", "vocab", "rotary_dim", "rope_theta",
-              "norm_eps", "parallel_residual", "n_ln_per_layer", "has_bias", "tied_head", "qkv_layout", "eos_id", "max_pos"):
+              "norm_eps", "parallel_residual", "n_ln_per_layer", "has_bias", "tied_head", "qkv_layout", "eos_id", "max_pos",
+              "norm_type", "mlp_type"):
         assert getattr(shp2, f) == getattr(shp, f), f
     names = checkpoint.expected_names(shp)
     assert set(names) <= set(W2)
@@ -51,11 +52,19 @@ def test_config_mapping_matches_registry():
     redpajama = dict(model_type="gpt_neox", hidden_size=2560, num_hidden_layers=32, num_attention_heads=32, intermediate_size=10240,
                      rotary_pct=1.0, rotary_emb_base=10000, layer_norm_eps=1e-5, use_parallel_residual=False, vocab_size=50432,
                      max_position_embeddings=2048, eos_token_id=0, hidden_act="gelu", tie_word_embeddings=False)
+    mistral = dict(model_type="mistral", hidden_size=4096, num_hidden_layers=32, num_attention_heads=32, num_key_value_heads=8,
+                   intermediate_size=14336, vocab_size=32768, rms_norm_eps=1e-5, rope_theta=1000000.0, sliding_window=None,
+                   max_position_embeddings=32768, hidden_act="silu", tie_word_embeddings=False, eos_token_id=2, bos_token_id=1)
+    llama2 = dict(model_type="llama", hidden_size=4096, num_hidden_layers=32, num_attention_heads=32, num_key_value_heads=32,
+                  intermediate_size=11008, vocab_size=32000, rms_norm_eps=1e-5, max_position_embeddings=4096, hidden_act="silu",
+                  tie_word_embeddings=False, eos_token_id=2, bos_token_id=1)
     for cfg, ref in ((old_falcon, shapes.falcon_7b()), (new_falcon, shapes.falcon_7b()), (stablelm, shapes.stablelm_alpha_7b()),
-                     (redpajama, shapes.redpajama_3b())):
+                     (redpajama, shapes.redpajama_3b()), (mistral, shapes.mistral_7b()), (llama2, shapes.llama2_7b())):
         got = checkpoint.shape_from_hf_config(cfg, ref.name)
         assert got == ref, (got, ref)
-    for bad in (dict(model_type="llama"), dict(model_type="falcon", hidden_size=8192, num_attention_heads=128, num_hidden_layers=60,
+    for bad in (dict(model_type="bloom"), dict(model_type="mistral", hidden_size=64, num_attention_heads=2, num_hidden_layers=1,
+                                                  intermediate_size=128, vocab_size=32, sliding_window=1024),
+                dict(model_type="falcon", hidden_size=8192, num_attention_heads=128, num_hidden_layers=60,
                                                   vocab_size=65024, new_decoder_architecture=True),
                 dict(model_type="gpt_neox", hidden_size=64, num_attention_heads=1, num_hidden_layers=1, intermediate_size=256,
                      vocab_size=10, hidden_act="gelu_new")):
