@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define B2S_ABI_VERSION 2
+#define B2S_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define B2S_API __attribute__((visibility("default")))
@@ -30,7 +30,11 @@ extern "C" {
 
 enum { B2S_OK = 0, B2S_EINVAL = -1, B2S_ECUDA = -2, B2S_ENOMEM = -3, B2S_EUNSUPPORTED = -4 };
 
-enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1, B2S_ARCH_LLAMA = 2 };
+enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1, B2S_ARCH_LLAMA = 2, B2S_ARCH_OPT = 3, B2S_ARCH_BLOOM = 4 };
+/* position encoding: rotary; learned table added to the token embedding (HF opt, rows pos + pos_offset); ALiBi
+ * (HF bloom: slope[head] * key position added to the scaled scores) */
+enum { B2S_POS_ROPE = 0, B2S_POS_LEARNED = 1, B2S_POS_ALIBI = 2 };
+enum { B2S_ACT_GELU = 0, B2S_ACT_RELU = 1, B2S_ACT_GELU_TANH = 2 };   /* MLP activation when mlp_type == B2S_MLP_GELU */
 enum { B2S_NORM_LAYERNORM = 0, B2S_NORM_RMS = 1 };   /* RMSNorm: x * rsqrt(mean(x^2) + eps) * g, *_B slots null (HF llama LlamaRMSNorm) */
 enum { B2S_MLP_GELU = 0, B2S_MLP_SWIGLU = 1 };      /* SwiGLU: down(silu(gate(x)) * up(x)); W_UP slot = [2*d_ff, d_model], gate rows first */
 enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQA, cat(q,k,v)_proj of the Llama family */,
@@ -43,10 +47,11 @@ enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQ
  *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5). */
 enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_FP32_CHECK = 3 };
 
-/* weight_ptrs slots: 6 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
+/* weight_ptrs slots: 10 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
  * pointer must be 16-byte aligned (B2S_EINVAL otherwise) */
 enum { B2S_W_WTE = 0, B2S_W_LNF_G = 1, B2S_W_LNF_B = 2, B2S_W_LM_HEAD = 3, B2S_W_ROPE_COS = 4,
-       B2S_W_ROPE_SIN = 5, B2S_W_NGLOBAL = 6, B2S_W_PER_LAYER = 16 };
+       B2S_W_ROPE_SIN = 5, B2S_W_WPE = 6 /* [max_pos + pos_offset, d] */, B2S_W_EMB_LN_G = 7, B2S_W_EMB_LN_B = 8,
+       B2S_W_ALIBI = 9 /* fp32 [n_head] */, B2S_W_NGLOBAL = 10, B2S_W_PER_LAYER = 16 };
 enum { B2S_WL_LN1_G = 0, B2S_WL_LN1_B, B2S_WL_LN2_G, B2S_WL_LN2_B, B2S_WL_W_QKV, B2S_WL_B_QKV,
        B2S_WL_W_DENSE, B2S_WL_B_DENSE, B2S_WL_W_UP, B2S_WL_B_UP, B2S_WL_W_DOWN, B2S_WL_B_DOWN };
 
@@ -63,6 +68,10 @@ typedef struct {
   int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST expects bf16 matrices, FP16 fp16, FP32_CHECK fp32 */
   int32_t norm_type;           /* B2S_NORM_*  (ABI 2) */
   int32_t mlp_type;            /* B2S_MLP_*   (ABI 2) */
+  int32_t pos_type;            /* B2S_POS_*   (ABI 3) */
+  int32_t pos_offset;          /* learned positions: table row of position 0 (OPT: 2) */
+  int32_t act_type;            /* B2S_ACT_*   (ABI 3) */
+  int32_t emb_norm;            /* LayerNorm on the token embeddings with B2S_W_EMB_LN_* (BLOOM) */
 } b2s_model_desc;
 
 typedef struct b2s_model b2s_model;

@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200score.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class B2SError(RuntimeError):
@@ -24,6 +24,7 @@ class ModelDesc(C.Structure):
         ("parallel_residual", C.c_int32), ("n_ln_per_layer", C.c_int32), ("has_bias", C.c_int32),
         ("qkv_layout", C.c_int32), ("max_pos", C.c_int32), ("compute_mode", C.c_int32),
         ("norm_type", C.c_int32), ("mlp_type", C.c_int32),
+        ("pos_type", C.c_int32), ("pos_offset", C.c_int32), ("act_type", C.c_int32), ("emb_norm", C.c_int32),
     ]
 
 

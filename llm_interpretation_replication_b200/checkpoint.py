@@ -28,8 +28,8 @@ from typing import Dict, Iterator, Optional, Tuple
 
 import torch
 
-from .shapes import (ARCH_FALCON, ARCH_GPT_NEOX, ARCH_LLAMA, MLP_SWIGLU, NORM_RMS, QKV_FALCON_MQA, QKV_NEOX_INTERLEAVED,
-                     DecoderShape)
+from .shapes import (ACT_GELU_TANH, ACT_RELU, ARCH_BLOOM, ARCH_FALCON, ARCH_GPT_NEOX, ARCH_LLAMA, ARCH_OPT, MLP_SWIGLU, NORM_RMS,
+                     POS_ALIBI, POS_LEARNED, QKV_FALCON_MQA, QKV_NEOX_INTERLEAVED, DecoderShape)
 from . import weights as _weights
 
 
@@ -112,6 +112,30 @@ def shape_from_hf_config(cfg: dict, name: str = "checkpoint") -> DecoderShape:
                             parallel_residual=False, n_ln_per_layer=2, has_bias=False,
                             tied_head=bool(cfg.get("tie_word_embeddings", False)), qkv_layout=QKV_FALCON_MQA, eos_id=int(eos),
                             max_pos=min(max_pos, 32768), norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+    if mt == "opt":
+        # HF:models/opt/configuration_opt.py (facebook/opt-iml-1.3b of the instruct sweep, compare_instruct_models.py:151)
+        d = int(cfg["hidden_size"])
+        if int(cfg.get("word_embed_proj_dim", d)) != d or not cfg.get("do_layer_norm_before", True):
+            raise KeyError(f"{name}: OPT with projected embeddings or post-LayerNorm (opt-350m) is not supported")
+        if cfg.get("activation_function", "relu") != "relu" or not cfg.get("enable_bias", True):
+            raise KeyError(f"{name}: OPT variant (activation / no biases) is not supported")
+        n_head = int(cfg["num_attention_heads"])
+        return DecoderShape(name, ARCH_OPT, int(cfg["num_hidden_layers"]), d, n_head, n_head, d // n_head, int(cfg["ffn_dim"]),
+                            int(cfg["vocab_size"]), 0, norm_eps=1e-5, parallel_residual=False, n_ln_per_layer=2, has_bias=True,
+                            tied_head=bool(cfg.get("tie_word_embeddings", True)), qkv_layout=QKV_FALCON_MQA,
+                            eos_id=int(cfg.get("eos_token_id", 2)), max_pos=int(cfg.get("max_position_embeddings", 2048)),
+                            pos_type=POS_LEARNED, pos_offset=2, act_type=ACT_RELU)
+    if mt == "bloom":
+        # HF:models/bloom/configuration_bloom.py (bigscience/bloomz-7b1, compare_instruct_models.py:148)
+        if cfg.get("apply_residual_connection_post_layernorm", False):
+            raise KeyError(f"{name}: BLOOM with apply_residual_connection_post_layernorm is not supported")
+        d = int(cfg.get("hidden_size", cfg.get("n_embed")))
+        n_head = int(cfg.get("n_head", cfg.get("num_attention_heads")))
+        return DecoderShape(name, ARCH_BLOOM, int(cfg.get("n_layer", cfg.get("num_hidden_layers"))), d, n_head, n_head,
+                            d // n_head, 4 * d, int(cfg["vocab_size"]), 0, norm_eps=float(cfg.get("layer_norm_epsilon", 1e-5)),
+                            parallel_residual=False, n_ln_per_layer=2, has_bias=True, tied_head=True,
+                            qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=int(cfg.get("eos_token_id", 2)),
+                            max_pos=int(cfg.get("seq_length", 2048)), pos_type=POS_ALIBI, act_type=ACT_GELU_TANH, emb_norm=True)
     raise KeyError(f"{name}: architecture {mt!r} is not supported by the B200 scorer")
 
 
@@ -134,14 +158,31 @@ _LLAMA_LAYER = {"input_layernorm.weight": "ln1_g", "post_attention_layernorm.wei
                 "self_attn.q_proj.weight": "w_qkv:0", "self_attn.k_proj.weight": "w_qkv:1", "self_attn.v_proj.weight": "w_qkv:2",
                 "self_attn.o_proj.weight": "w_dense", "mlp.gate_proj.weight": "w_up:0", "mlp.up_proj.weight": "w_up:1",
                 "mlp.down_proj.weight": "w_down"}
-_LAYER_RE = re.compile(r"^(?:transformer\.h|gpt_neox\.layers|model\.layers)\.(\d+)\.(.+)$")
+_OPT_GLOBAL = {"model.decoder.embed_tokens.weight": "wte", "model.decoder.embed_positions.weight": "wpe",
+               "model.decoder.final_layer_norm.weight": "lnf_g", "model.decoder.final_layer_norm.bias": "lnf_b",
+               "lm_head.weight": "lm_head"}
+_OPT_LAYER = {"self_attn_layer_norm.weight": "ln1_g", "self_attn_layer_norm.bias": "ln1_b", "final_layer_norm.weight": "ln2_g",
+              "final_layer_norm.bias": "ln2_b", "self_attn.q_proj.weight": "w_qkv:0", "self_attn.k_proj.weight": "w_qkv:1",
+              "self_attn.v_proj.weight": "w_qkv:2", "self_attn.q_proj.bias": "b_qkv:0", "self_attn.k_proj.bias": "b_qkv:1",
+              "self_attn.v_proj.bias": "b_qkv:2", "self_attn.out_proj.weight": "w_dense", "self_attn.out_proj.bias": "b_dense",
+              "fc1.weight": "w_up", "fc1.bias": "b_up", "fc2.weight": "w_down", "fc2.bias": "b_down"}
+_BLOOM_GLOBAL = {"transformer.word_embeddings.weight": "wte", "transformer.word_embeddings_layernorm.weight": "emb_ln_g",
+                 "transformer.word_embeddings_layernorm.bias": "emb_ln_b", "transformer.ln_f.weight": "lnf_g",
+                 "transformer.ln_f.bias": "lnf_b", "lm_head.weight": "lm_head"}
+_BLOOM_LAYER = {"input_layernorm.weight": "ln1_g", "input_layernorm.bias": "ln1_b", "post_attention_layernorm.weight": "ln2_g",
+                "post_attention_layernorm.bias": "ln2_b", "self_attention.query_key_value.weight": "w_qkv",
+                "self_attention.query_key_value.bias": "b_qkv", "self_attention.dense.weight": "w_dense",
+                "self_attention.dense.bias": "b_dense", "mlp.dense_h_to_4h.weight": "w_up", "mlp.dense_h_to_4h.bias": "b_up",
+                "mlp.dense_4h_to_h.weight": "w_down", "mlp.dense_4h_to_h.bias": "b_down"}
+_LAYER_RE = re.compile(r"^(?:transformer\.h|gpt_neox\.layers|model\.layers|model\.decoder\.layers)\.(\d+)\.(.+)$")
 
 
 def flat_name(shape: DecoderShape, hf_name: str) -> Optional[str]:
     """Name of an HF state-dict entry in the flat layout, or None for entries the scorer does not use (rotary
     ``inv_freq`` buffers, causal-mask buffers)."""
     glob_map, layer_map = {ARCH_FALCON: (_FALCON_GLOBAL, _FALCON_LAYER), ARCH_GPT_NEOX: (_NEOX_GLOBAL, _NEOX_LAYER),
-                           ARCH_LLAMA: (_LLAMA_GLOBAL, _LLAMA_LAYER)}[shape.arch]
+                           ARCH_LLAMA: (_LLAMA_GLOBAL, _LLAMA_LAYER), ARCH_OPT: (_OPT_GLOBAL, _OPT_LAYER),
+                           ARCH_BLOOM: (_BLOOM_GLOBAL, _BLOOM_LAYER)}[shape.arch]
     if hf_name in glob_map:
         return glob_map[hf_name]
     m = _LAYER_RE.match(hf_name)
@@ -151,7 +192,7 @@ def flat_name(shape: DecoderShape, hf_name: str) -> Optional[str]:
 
 
 def expected_names(shape: DecoderShape):
-    names = [n for n in _weights.slot_names(shape) if n is not None and not n.startswith("rope_")]
+    names = [n for n in _weights.slot_names(shape) if n is not None and not n.startswith("rope_") and n != "alibi_slopes"]
     out = []
     for n in names:
         leaf = n.split(".")[-1]
@@ -161,6 +202,8 @@ def expected_names(shape: DecoderShape):
             continue
         if leaf in ("lnf_b", "ln1_b", "ln2_b") and shape.norm_type == NORM_RMS:
             continue
+        if (leaf == "wpe" and shape.pos_type != POS_LEARNED) or (leaf in ("emb_ln_g", "emb_ln_b") and not shape.emb_norm):
+            continue
         out.append(n)
     return out
 
@@ -169,12 +212,13 @@ def _check_shape(shape: DecoderShape, name: str, t: torch.Tensor):
     d, ff, V = shape.d_model, shape.d_ff, shape.vocab
     leaf = name.split(".")[-1]
     nq, nk = shape.n_head * shape.head_dim, shape.n_kv_head * shape.head_dim
-    part = {"w_qkv:0": (nq, d), "w_qkv:1": (nk, d), "w_qkv:2": (nk, d), "w_up:0": (ff, d), "w_up:1": (ff, d)}
+    part = {"w_qkv:0": (nq, d), "w_qkv:1": (nk, d), "w_qkv:2": (nk, d), "w_up:0": (ff, d), "w_up:1": (ff, d),
+            "b_qkv:0": (nq,), "b_qkv:1": (nk,), "b_qkv:2": (nk,)}
     if leaf in part:
         if tuple(t.shape) != part[leaf]:
             raise ValueError(f"checkpoint tensor {name} has shape {tuple(t.shape)}, the config implies {part[leaf]}")
         return
-    want = {"wte": (V, d), "lm_head": (V, d), "lnf_g": (d,), "lnf_b": (d,), "ln1_g": (d,), "ln1_b": (d,), "ln2_g": (d,),
+    want = {"wte": (V, d), "wpe": (shape.max_pos + shape.pos_offset, d), "emb_ln_g": (d,), "emb_ln_b": (d,), "lm_head": (V, d), "lnf_g": (d,), "lnf_b": (d,), "ln1_g": (d,), "ln1_b": (d,), "ln2_g": (d,),
             "ln2_b": (d,), "w_qkv": (shape.qkv_dim, d), "b_qkv": (shape.qkv_dim,), "w_dense": (d, shape.n_head * shape.head_dim),
             "b_dense": (d,), "w_up": (shape.up_dim, d), "b_up": (ff,), "w_down": (d, ff), "b_down": (d,)}[leaf]
     if tuple(t.shape) != want:
@@ -194,13 +238,15 @@ def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.
         W[n] = t.to(device=device, dtype=weight_dtype if _weights.is_matrix(n.split(":")[0]) else torch.float32).contiguous()
         base = n.split(":")[0]
         if base != n:                                  # a block of a fused matrix: fuse once every block is here
-            blocks = [f"{base}:{i}" for i in range(3 if base.endswith("w_qkv") else 2)]
+            blocks = [f"{base}:{i}" for i in range(3 if base.endswith("_qkv") else 2)]
             if all(b in W for b in blocks):
                 W[base] = torch.cat([W.pop(b) for b in blocks], dim=0).contiguous()
     if "lm_head" not in W:
         if not shape.tied_head:
             raise ValueError("checkpoint has no output embedding and the config does not tie it to the input embedding")
         W["lm_head"] = W["wte"]
+    if shape.pos_type == POS_ALIBI:                    # not stored in checkpoints: HF recomputes the slopes from n_head
+        W["alibi_slopes"] = _weights.alibi_slopes(shape.n_head).to(device)
     missing = [n for n in expected_names(shape) if n not in W]
     if missing:
         raise ValueError(f"checkpoint is missing {len(missing)} tensors, e.g. {missing[:4]}")

@@ -77,8 +77,9 @@ ln_kernel(LnArgs a) {
   if (a.tokens != nullptr) {
     const WT* e = reinterpret_cast<const WT*>(a.wte) + static_cast<size_t>(a.tokens[irow]) * d;
     float* xr = a.x + static_cast<size_t>(irow) * d;
+    const WT* pe = a.wpe ? reinterpret_cast<const WT*>(a.wpe) + static_cast<size_t>(a.pos[irow] + a.pos_offset) * d : nullptr;
     for (int i = threadIdx.x; i < d; i += blockDim.x) {
-      const float v = to_f32(e[i]);
+      const float v = pe ? to_f32(e[i]) + to_f32(pe[i]) : to_f32(e[i]);
       srow[i] = v; xr[i] = v; sum += v;
     }
   } else {
@@ -135,6 +136,8 @@ int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st) {
 template int launch_ln<float, float>(const LnArgs&, int, cudaStream_t);
 template int launch_ln<__nv_bfloat16, __nv_bfloat16>(const LnArgs&, int, cudaStream_t);
 template int launch_ln<__half, __half>(const LnArgs&, int, cudaStream_t);
+template int launch_ln<float, __nv_bfloat16>(const LnArgs&, int, cudaStream_t);   // embedding LayerNorm into the fp32 residual
+template int launch_ln<float, __half>(const LnArgs&, int, cudaStream_t);
 
 // =================================================================================================
 // SwiGLU gate (Llama family): act = silu(gate) * up on the [rows, 2*ff] output of the fused gate/up projection
@@ -172,6 +175,35 @@ int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t 
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
+template <typename AT>
+__global__ void __launch_bounds__(256)
+act_kernel(AT* __restrict__ x, int64_t n4, int kind) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    AT* p = x + 4 * i;
+    float o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float v = to_f32(p[k]);
+      o[k] = kind == 1 ? fmaxf(v, 0.f) : v * 0.5f * (1.0f + tanhf(0.79788456f * v * (1.0f + 0.044715f * v * v)));
+    }
+    store4(p, o[0], o[1], o[2], o[3]);
+  }
+}
+
+template <typename AT>
+int launch_act(void* x, int64_t n, int kind, cudaStream_t st) {
+  B2S_REQUIRE(n % 4 == 0 && (kind == 1 || kind == 2), "activation: n=%lld kind=%d", static_cast<long long>(n), kind);
+  const int64_t blocks = ceil_div(n / 4, 256);
+  const unsigned grid = static_cast<unsigned>(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
+  act_kernel<AT><<<grid, 256, 0, st>>>(reinterpret_cast<AT*>(x), n / 4, kind);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+template int launch_act<float>(void*, int64_t, int, cudaStream_t);
+template int launch_act<__nv_bfloat16>(void*, int64_t, int, cudaStream_t);
+template int launch_act<__half>(void*, int64_t, int, cudaStream_t);
+
 template int launch_swiglu<float>(const void*, void*, int64_t, int, cudaStream_t);
 template int launch_swiglu<__nv_bfloat16>(const void*, void*, int64_t, int, cudaStream_t);
 template int launch_swiglu<__half>(const void*, void*, int64_t, int, cudaStream_t);
@@ -310,6 +342,7 @@ attn_kernel(AttnArgs a) {
           }
         }
         s = d0 + d1;
+        if (a.alibi) s += a.alibi[h] * static_cast<float>(j);     // HF bloom: alibi = slope[head] * key position
       }
       const float mn = fmaxf(m, warp_max(s));
       const float p = (j < nkeys) ? __expf(s - mn) : 0.f;

@@ -27,6 +27,9 @@ struct LnArgs {
   int d;
   float eps;
   int rms;                  // RMSNorm: no mean subtraction, no bias (b1/b2 null)
+  const void* wpe;          // learned position table added to the gathered embedding (tokens != null), or null
+  const int32_t* pos;       // position of every row (with wpe)
+  int pos_offset;
 };
 
 struct RopeArgs {
@@ -47,6 +50,7 @@ struct AttnArgs {
   int q_base, q_hstride;
   int max_kv;
   int f16;             // 16-bit buffers hold fp16 instead of bf16 (tensor-core kernel)
+  const float* alibi;  // per-head ALiBi slopes (CUDA-core kernel only), or null
   int heads_per_cta;   // set by the launcher: ATT_HG for prefill, all heads of the KV head for single-token steps
   float scale;
 };
@@ -66,6 +70,8 @@ template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cuda
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
 // act[r, j] = silu(gu[r, j]) * gu[r, ff + j]   (HF llama LlamaMLP: act_fn(gate_proj(x)) * up_proj(x))
 template <typename AT> int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st);
+// x = relu(x) (kind 1) or tanh-GELU(x) (kind 2) in place (HF opt ReLU MLP; HF bloom bloom_gelu_forward)
+template <typename AT> int launch_act(void* x, int64_t n, int kind, cudaStream_t st);
 // tcgen05 prefill attention (b2s_attn_tc.cu): head_dim 64, <= 256 keys per sequence
 bool attn_tc_supported(int hd, int max_kv);
 bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride);

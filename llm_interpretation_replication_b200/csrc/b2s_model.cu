@@ -127,6 +127,16 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     ln.x = w.resid; ln.d = dm; ln.eps = d.norm_eps; ln.rms = d.norm_type == B2S_NORM_RMS;
     ln.tokens = (l == 0) ? tokens : nullptr;
     ln.wte = m->gw(B2S_W_WTE);
+    if (d.pos_type == B2S_POS_LEARNED) { ln.wpe = m->gw(B2S_W_WPE); ln.pos = w.meta.pos; ln.pos_offset = d.pos_offset; }
+    if (l == 0 && d.emb_norm) {
+      // BLOOM: the residual stream starts at LayerNorm(embedding); gather + normalise into the fp32 residual in place
+      // (the kernel writes the raw row before its barriers and the normalised row after them), then layer 0 reads it
+      LnArgs le = ln;
+      le.g1 = reinterpret_cast<const float*>(m->gw(B2S_W_EMB_LN_G)); le.b1 = reinterpret_cast<const float*>(m->gw(B2S_W_EMB_LN_B));
+      le.y1 = w.resid; le.rms = 0;
+      B2S_TRY((launch_ln<float, WT>(le, rows, st)));
+      ln.tokens = nullptr;
+    }
     ln.g1 = m->lwf(l, B2S_WL_LN1_G); ln.b1 = m->lwf(l, B2S_WL_LN1_B);
     ln.y1 = w.ln1;
     if (two_ln && d.parallel_residual) {   // both LayerNorms read the same residual: one pass, two affines
@@ -165,9 +175,10 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
     at.heads_per_cta = (max_qlen == 1) ? at.rep : ATT_HG;
     at.f16 = m->act_f16;
+    at.alibi = d.pos_type == B2S_POS_ALIBI ? reinterpret_cast<const float*>(m->gw(B2S_W_ALIBI)) : nullptr;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
     // tensor-core kernel when the shape allows it (head_dim 64, <= 256 keys), CUDA-core kernel otherwise
-    const bool tc_ok = m->bf16 && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
+    const bool tc_ok = m->bf16 && at.alibi == nullptr && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
                                                 : attn_tc_decode_supported(d.head_dim, max_kv, m->qkv_dim, m->q_base, m->q_hstride));
     if (tc_ok) {
       B2S_TRY(launch_attn_tc(at, n_seqs, rows, static_cast<int>(w.cache_slots), max_qlen, st));
@@ -190,6 +201,9 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     if (d.mlp_type == B2S_MLP_SWIGLU) {   // fused gate|up projection, then act = silu(gate) * up
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), nullptr, w.gu, rows, 2 * d.d_ff, dm, EPI_STORE_BF16, st));
       B2S_TRY(launch_swiglu<AT>(w.gu, w.act, rows, d.d_ff, st));
+    } else if (d.act_type != B2S_ACT_GELU) {   // ReLU / tanh-GELU: plain store epilogue, then the activation in place
+      B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_STORE_BF16, st));
+      B2S_TRY(launch_act<AT>(w.act, static_cast<int64_t>(rows) * d.d_ff, d.act_type, st));
     } else {
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st));
     }
@@ -255,7 +269,12 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   B2S_REQUIRE(d.n_head % d.n_kv_head == 0, "model_create: n_head %d not a multiple of n_kv_head %d", d.n_head, d.n_kv_head);
   B2S_REQUIRE(d.head_dim == 64 || d.head_dim == 80 || d.head_dim == 128, "model_create: head_dim %d unsupported (64, 80, 128)",
               d.head_dim);
-  B2S_REQUIRE(d.rotary_dim > 0 && d.rotary_dim <= d.head_dim && d.rotary_dim % 2 == 0, "model_create: bad rotary_dim %d",
+  B2S_REQUIRE(d.pos_type == B2S_POS_ROPE || d.pos_type == B2S_POS_LEARNED || d.pos_type == B2S_POS_ALIBI,
+              "model_create: unknown pos_type %d", d.pos_type);
+  B2S_REQUIRE(d.act_type == B2S_ACT_GELU || d.act_type == B2S_ACT_RELU || d.act_type == B2S_ACT_GELU_TANH,
+              "model_create: unknown act_type %d", d.act_type);
+  B2S_REQUIRE(d.pos_type == B2S_POS_ROPE ? (d.rotary_dim > 0 && d.rotary_dim <= d.head_dim && d.rotary_dim % 2 == 0) : d.rotary_dim == 0,
+              "model_create: bad rotary_dim %d",
               d.rotary_dim);
   B2S_REQUIRE(d.n_ln_per_layer == 1 || d.n_ln_per_layer == 2, "model_create: n_ln_per_layer must be 1 or 2");
   B2S_REQUIRE(d.norm_type == B2S_NORM_LAYERNORM || d.norm_type == B2S_NORM_RMS, "model_create: unknown norm_type %d", d.norm_type);
@@ -301,7 +320,12 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   const bool rms = d.norm_type == B2S_NORM_RMS;   // RMSNorm has gains only
   const int required[] = {B2S_W_WTE, B2S_W_LNF_G, B2S_W_LNF_B, B2S_W_LM_HEAD, B2S_W_ROPE_COS, B2S_W_ROPE_SIN};
   for (int s : required) {
-    if (m->w[s] == nullptr && !(rms && s == B2S_W_LNF_B)) { delete m; set_error("model_create: global weight slot %d is null", s); return B2S_EINVAL; }
+    const bool rope_slot = s == B2S_W_ROPE_COS || s == B2S_W_ROPE_SIN;
+    if (m->w[s] == nullptr && !(rms && s == B2S_W_LNF_B) && !(rope_slot && d.pos_type != B2S_POS_ROPE)) { delete m; set_error("model_create: global weight slot %d is null", s); return B2S_EINVAL; }
+  }
+  if ((d.pos_type == B2S_POS_LEARNED && m->w[B2S_W_WPE] == nullptr) || (d.pos_type == B2S_POS_ALIBI && m->w[B2S_W_ALIBI] == nullptr) ||
+      (d.emb_norm && (m->w[B2S_W_EMB_LN_G] == nullptr || m->w[B2S_W_EMB_LN_B] == nullptr))) {
+    delete m; set_error("model_create: position table / ALiBi slopes / embedding LayerNorm slot is null"); return B2S_EINVAL;
   }
   for (int l = 0; l < d.n_layer; ++l) {
     const int mats[] = {B2S_WL_LN1_G, B2S_WL_LN1_B, B2S_WL_W_QKV, B2S_WL_W_DENSE, B2S_WL_W_UP, B2S_WL_W_DOWN};

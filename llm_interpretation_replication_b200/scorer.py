@@ -87,7 +87,7 @@ class Scorer:
             W = {k: (v.to(torch.float16) if _weights.is_matrix(k) and v.dtype != torch.float16 else v) for k, v in W.items()}
             if weights_dev.get("lm_head") is weights_dev.get("wte"):
                 W["lm_head"] = W["wte"]
-        if "rope_cos" not in W:
+        if "rope_cos" not in W and shape.rotary_dim > 0:
             W["rope_cos"], W["rope_sin"] = _weights.rope_tables(shape, self.device)
         for k, v in W.items():
             assert v.is_cuda and v.is_contiguous(), k
@@ -102,7 +102,9 @@ class Scorer:
                            vocab=shape.vocab, rotary_dim=shape.rotary_dim, norm_eps=shape.norm_eps,
                            parallel_residual=int(shape.parallel_residual), n_ln_per_layer=shape.n_ln_per_layer,
                            has_bias=int(shape.has_bias), qkv_layout=shape.qkv_layout, max_pos=shape.max_pos,
-                           compute_mode=mode, norm_type=shape.norm_type, mlp_type=shape.mlp_type)
+                           compute_mode=mode, norm_type=shape.norm_type, mlp_type=shape.mlp_type,
+                           pos_type=shape.pos_type, pos_offset=shape.pos_offset, act_type=shape.act_type,
+                           emb_norm=int(shape.emb_norm))
         self._handle = C.c_void_p()
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2s_model_create(C.byref(d), self._ptrs, len(self._ptrs), self.device.index or 0,

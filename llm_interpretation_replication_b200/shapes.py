@@ -14,6 +14,16 @@ from dataclasses import dataclass, asdict, replace
 ARCH_FALCON = 0
 ARCH_GPT_NEOX = 1
 ARCH_LLAMA = 2            # Llama / Mistral family: RMSNorm, SwiGLU, grouped-query attention, no biases
+ARCH_OPT = 3              # OPT: learned positions (offset 2), ReLU MLP, pre-LayerNorm, biases, no rotary
+ARCH_BLOOM = 4            # BLOOM: ALiBi, LayerNorm on the embeddings, tanh-GELU MLP, per-head [q,k,v] fused projection
+
+# position encodings and MLP activations (must match include/b200score.h)
+POS_ROPE = 0
+POS_LEARNED = 1           # x = wte[token] + wpe[position + pos_offset]          (HF opt OPTLearnedPositionalEmbedding)
+POS_ALIBI = 2             # score(q, k) += slope[head] * key_position             (HF bloom build_alibi_tensor)
+ACT_GELU = 0              # exact (erf) GELU
+ACT_RELU = 1
+ACT_GELU_TANH = 2         # 0.5 x (1 + tanh(0.79788456 x (1 + 0.044715 x^2)))     (HF bloom bloom_gelu_forward)
 
 # normalisation and MLP kinds (must match include/b200score.h)
 NORM_LAYERNORM = 0
@@ -55,6 +65,10 @@ class DecoderShape:
     max_pos: int = 2048
     norm_type: int = NORM_LAYERNORM
     mlp_type: int = MLP_GELU
+    pos_type: int = POS_ROPE
+    pos_offset: int = 0          # rows of wpe skipped before position 0 (OPT: 2)
+    act_type: int = ACT_GELU
+    emb_norm: bool = False       # LayerNorm applied to the token embeddings (BLOOM word_embeddings_layernorm)
 
     @property
     def up_dim(self) -> int:
@@ -142,7 +156,39 @@ def llama2_7b() -> DecoderShape:
                         qkv_layout=QKV_FALCON_MQA, eos_id=2, max_pos=4096, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
 
 
+def opt_iml_1_3b() -> DecoderShape:
+    # facebook/opt-iml-1.3b (compare_instruct_models.py:151): HF:models/opt/configuration_opt.py, opt-1.3b sizes
+    return DecoderShape("opt-iml-1.3b", ARCH_OPT, 24, 2048, 32, 32, 64, 8192, 50272, 0, norm_eps=1e-5, parallel_residual=False,
+                        n_ln_per_layer=2, has_bias=True, tied_head=True, qkv_layout=QKV_FALCON_MQA, eos_id=2, max_pos=2048,
+                        pos_type=POS_LEARNED, pos_offset=2, act_type=ACT_RELU)
+
+
+def bloomz_7b1() -> DecoderShape:
+    # bigscience/bloomz-7b1 (compare_instruct_models.py:148): HF:models/bloom/configuration_bloom.py, bloom-7b1 sizes
+    return DecoderShape("bloomz-7b1", ARCH_BLOOM, 30, 4096, 32, 32, 128, 16384, 250880, 0, norm_eps=1e-5, parallel_residual=False,
+                        n_ln_per_layer=2, has_bias=True, tied_head=True, qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=2, max_pos=2048,
+                        pos_type=POS_ALIBI, act_type=ACT_GELU_TANH, emb_norm=True)
+
+
 # tiny variants (CPU-oracle sized) --------------------------------------------------------
+def tiny_opt(vocab=272, n_layer=2, n_head=3) -> DecoderShape:
+    hd = 64
+    d = n_head * hd
+    return DecoderShape("tiny-opt", ARCH_OPT, n_layer, d, n_head, n_head, hd, 4 * d, vocab, 0, norm_eps=1e-5,
+                        parallel_residual=False, n_ln_per_layer=2, has_bias=True, tied_head=True, qkv_layout=QKV_FALCON_MQA,
+                        eos_id=2, max_pos=512, pos_type=POS_LEARNED, pos_offset=2, act_type=ACT_RELU)
+
+
+def tiny_bloom(vocab=280, n_layer=2, n_head=6) -> DecoderShape:
+    # 6 heads: not a power of two, so the ALiBi slopes use both branches of HF's formula
+    hd = 64
+    d = n_head * hd
+    return DecoderShape("tiny-bloom", ARCH_BLOOM, n_layer, d, n_head, n_head, hd, 4 * d, vocab, 0, norm_eps=1e-5,
+                        parallel_residual=False, n_ln_per_layer=2, has_bias=True, tied_head=True,
+                        qkv_layout=QKV_NEOX_INTERLEAVED, eos_id=2, max_pos=2048, pos_type=POS_ALIBI, act_type=ACT_GELU_TANH,
+                        emb_norm=True)
+
+
 def tiny_llama(vocab=288, n_layer=2, n_head=4, n_kv_head=2) -> DecoderShape:
     # head_dim 64: the tensor-core attention and the fused QKV+RoPE epilogue with grouped-query heads
     hd = 64
@@ -197,6 +243,10 @@ REGISTRY = {
     "dolly-v2-7b": dolly_v2_7b,
     "mistral-7b": mistral_7b,
     "llama-2-7b": llama2_7b,
+    "opt-iml-1.3b": opt_iml_1_3b,
+    "bloomz-7b1": bloomz_7b1,
+    "tiny-opt": tiny_opt,
+    "tiny-bloom": tiny_bloom,
     "tiny-llama": tiny_llama,
     "tiny-mistral": tiny_mistral,
     "tiny-falcon": tiny_falcon,
@@ -215,6 +265,8 @@ HUB_TO_SHAPE = {
     "togethercomputer/RedPajama-INCITE-Instruct-3B-v1": redpajama_3b,
     "h2oai/h2ogpt-oasst1-512-12b": h2ogpt_12b,
     "EleutherAI/pythia-6.9b": dolly_v2_7b, "databricks/dolly-v2-7b": dolly_v2_7b,
+    "facebook/opt-iml-1.3b": opt_iml_1_3b, "facebook/opt-1.3b": opt_iml_1_3b,
+    "bigscience/bloomz-7b1": bloomz_7b1, "bigscience/bloom-7b1": bloomz_7b1,
     "mistralai/Mistral-7B-Instruct-v0.3": mistral_7b, "mistralai/Mistral-7B-v0.3": mistral_7b,
     "meta-llama/Llama-2-7b-chat-hf": llama2_7b, "meta-llama/Llama-2-7b-hf": llama2_7b,
 }

@@ -8,7 +8,8 @@ paths carry signal.  The same tensors are loaded into the HF model that serves a
 
 Slot order (``B2S_W_*`` in the header):
   global:    0 wte[V,d]  1 lnf_g[d]  2 lnf_b[d]  3 lm_head[V,d]  4 rope_cos[max_pos,rd/2]  5 rope_sin
-  per layer: base = 6 + 16*l
+             6 wpe[max_pos+pos_offset,d] (learned positions)  7 emb_ln_g[d]  8 emb_ln_b[d]  9 alibi_slopes[n_head]
+  per layer: base = 10 + 16*l
              +0 ln1_g +1 ln1_b +2 ln2_g +3 ln2_b +4 w_qkv[qkv,d] +5 b_qkv +6 w_dense[d,nh*hd] +7 b_dense
              +8 w_up[ff,d] ([2ff,d] = gate rows then up rows for SwiGLU) +9 b_up +10 w_down[d,ff] +11 b_down   (+12..15 reserved)
 RMSNorm models have no *_b vectors (null slots).
@@ -20,9 +21,10 @@ from typing import Dict, List, Optional
 
 import torch
 
-from .shapes import DecoderShape, ARCH_FALCON, ARCH_GPT_NEOX, ARCH_LLAMA, NORM_RMS
+from .shapes import (DecoderShape, ARCH_FALCON, ARCH_GPT_NEOX, ARCH_LLAMA, ARCH_OPT, ARCH_BLOOM, NORM_RMS, POS_LEARNED,
+                     POS_ALIBI)
 
-N_GLOBAL = 6
+N_GLOBAL = 10
 N_PER_LAYER = 16
 
 
@@ -37,7 +39,8 @@ def rope_tables(shape: DecoderShape, device="cpu"):
 
 
 def slot_names(shape: DecoderShape) -> List[Optional[str]]:
-    names: List[Optional[str]] = ["wte", "lnf_g", "lnf_b", "lm_head", "rope_cos", "rope_sin"]
+    names: List[Optional[str]] = ["wte", "lnf_g", "lnf_b", "lm_head", "rope_cos", "rope_sin", "wpe", "emb_ln_g", "emb_ln_b",
+                                  "alibi_slopes"]
     per = ["ln1_g", "ln1_b", "ln2_g", "ln2_b", "w_qkv", "b_qkv", "w_dense", "b_dense",
            "w_up", "b_up", "w_down", "b_down", None, None, None, None]
     for l in range(shape.n_layer):
@@ -48,7 +51,21 @@ def slot_names(shape: DecoderShape) -> List[Optional[str]]:
 
 def is_matrix(name: str) -> bool:
     leaf = name.split(".")[-1]
-    return leaf in ("wte", "lm_head", "w_qkv", "w_dense", "w_up", "w_down")
+    return leaf in ("wte", "wpe", "lm_head", "w_qkv", "w_dense", "w_up", "w_down")
+
+
+def alibi_slopes(n_head: int) -> torch.Tensor:
+    """Per-head ALiBi slopes exactly as HF:models/bloom/modeling_bloom.py build_alibi_tensor computes them (fp32):
+    powers of 2^(-8/n) for the closest power of two n <= n_head, then odd powers of the half-step base for the rest."""
+    import math
+    cp2 = 2 ** math.floor(math.log2(n_head))
+    base = torch.tensor(2 ** (-(2 ** -(math.log2(cp2) - 3))), dtype=torch.float32)
+    slopes = torch.pow(base, torch.arange(1, 1 + cp2, dtype=torch.int32))
+    if cp2 != n_head:
+        extra_base = torch.tensor(2 ** (-(2 ** -(math.log2(2 * cp2) - 3))), dtype=torch.float32)
+        n_rem = min(cp2, n_head - cp2)
+        slopes = torch.cat([slopes, torch.pow(extra_base, torch.arange(1, 1 + 2 * n_rem, 2, dtype=torch.int32))], dim=0)
+    return slopes.to(torch.float32).contiguous()
 
 
 def init_weights(shape: DecoderShape, seed: int = 0, device: str = "cpu",
@@ -78,6 +95,13 @@ def init_weights(shape: DecoderShape, seed: int = 0, device: str = "cpu",
     if not rms:
         W["lnf_b"] = vec(d, 0.0, 0.05)
     W["lm_head"] = W["wte"] if shape.tied_head else mat(V, d)
+    if shape.pos_type == POS_LEARNED:
+        W["wpe"] = mat(shape.max_pos + shape.pos_offset, d)
+    if shape.emb_norm:
+        W["emb_ln_g"] = vec(d, 1.0, 0.1)
+        W["emb_ln_b"] = vec(d, 0.0, 0.05)
+    if shape.pos_type == POS_ALIBI:
+        W["alibi_slopes"] = alibi_slopes(shape.n_head).to(device)
     for l in range(shape.n_layer):
         p = f"l{l}."
         W[p + "ln1_g"] = vec(d, 1.0, 0.1)
@@ -124,6 +148,13 @@ def init_weights_device(shape: DecoderShape, seed: int, device, weight_dtype=tor
     if not rms:
         W["lnf_b"] = vec(d, 0.0, 0.05)
     W["lm_head"] = W["wte"] if shape.tied_head else mat(V, d)
+    if shape.pos_type == POS_LEARNED:
+        W["wpe"] = mat(shape.max_pos + shape.pos_offset, d)
+    if shape.emb_norm:
+        W["emb_ln_g"] = vec(d, 1.0, 0.1)
+        W["emb_ln_b"] = vec(d, 0.0, 0.05)
+    if shape.pos_type == POS_ALIBI:
+        W["alibi_slopes"] = alibi_slopes(shape.n_head).to(device)
     for l in range(shape.n_layer):
         p = f"l{l}."
         W[p + "ln1_g"] = vec(d, 1.0, 0.1)
@@ -197,6 +228,20 @@ def hf_config(shape: DecoderShape):
                            max_position_embeddings=shape.max_pos, rms_norm_eps=shape.norm_eps, rope_theta=shape.rope_theta,
                            attention_bias=False, mlp_bias=False, tie_word_embeddings=shape.tied_head,
                            bos_token_id=1, eos_token_id=shape.eos_id, attention_dropout=0.0)
+    if shape.arch == ARCH_OPT:
+        from transformers import OPTConfig
+        return OPTConfig(vocab_size=shape.vocab, hidden_size=shape.d_model, num_hidden_layers=shape.n_layer,
+                         ffn_dim=shape.d_ff, num_attention_heads=shape.n_head, max_position_embeddings=shape.max_pos,
+                         do_layer_norm_before=True, word_embed_proj_dim=shape.d_model, activation_function="relu",
+                         dropout=0.0, attention_dropout=0.0, layerdrop=0.0, enable_bias=True,
+                         layer_norm_elementwise_affine=True, bos_token_id=shape.eos_id, eos_token_id=shape.eos_id,
+                         pad_token_id=1, tie_word_embeddings=True)
+    if shape.arch == ARCH_BLOOM:
+        from transformers import BloomConfig
+        return BloomConfig(vocab_size=shape.vocab, hidden_size=shape.d_model, n_layer=shape.n_layer, n_head=shape.n_head,
+                           layer_norm_epsilon=shape.norm_eps, apply_residual_connection_post_layernorm=False,
+                           hidden_dropout=0.0, attention_dropout=0.0, bos_token_id=1, eos_token_id=shape.eos_id,
+                           pad_token_id=3, tie_word_embeddings=True)
     raise ValueError(shape.arch)
 
 
@@ -232,6 +277,52 @@ def to_hf_state_dict(shape: DecoderShape, W: Dict[str, torch.Tensor]) -> Dict[st
             sd[h + "mlp.gate_proj.weight"] = W[p + "w_up"][:ff]
             sd[h + "mlp.up_proj.weight"] = W[p + "w_up"][ff:]
             sd[h + "mlp.down_proj.weight"] = W[p + "w_down"]
+    elif shape.arch == ARCH_OPT:
+        # HF:models/opt/modeling_opt.py: separate q/k/v projections with biases; fused by rows in the flat layout
+        nq = shape.n_head * shape.head_dim
+        b = "model.decoder."
+        sd[b + "embed_tokens.weight"] = W["wte"]
+        sd[b + "embed_positions.weight"] = W["wpe"]
+        sd[b + "final_layer_norm.weight"] = W["lnf_g"]
+        sd[b + "final_layer_norm.bias"] = W["lnf_b"]
+        sd["lm_head.weight"] = W["lm_head"]
+        for l in range(shape.n_layer):
+            p, h = f"l{l}.", f"{b}layers.{l}."
+            sd[h + "self_attn_layer_norm.weight"] = W[p + "ln1_g"]
+            sd[h + "self_attn_layer_norm.bias"] = W[p + "ln1_b"]
+            sd[h + "final_layer_norm.weight"] = W[p + "ln2_g"]
+            sd[h + "final_layer_norm.bias"] = W[p + "ln2_b"]
+            for i, n in enumerate(("q_proj", "k_proj", "v_proj")):
+                sd[h + f"self_attn.{n}.weight"] = W[p + "w_qkv"][i * nq:(i + 1) * nq]
+                sd[h + f"self_attn.{n}.bias"] = W[p + "b_qkv"][i * nq:(i + 1) * nq]
+            sd[h + "self_attn.out_proj.weight"] = W[p + "w_dense"]
+            sd[h + "self_attn.out_proj.bias"] = W[p + "b_dense"]
+            sd[h + "fc1.weight"] = W[p + "w_up"]
+            sd[h + "fc1.bias"] = W[p + "b_up"]
+            sd[h + "fc2.weight"] = W[p + "w_down"]
+            sd[h + "fc2.bias"] = W[p + "b_down"]
+    elif shape.arch == ARCH_BLOOM:
+        # HF:models/bloom/modeling_bloom.py: fused query_key_value with per-head [q, k, v] rows
+        sd["transformer.word_embeddings.weight"] = W["wte"]
+        sd["transformer.word_embeddings_layernorm.weight"] = W["emb_ln_g"]
+        sd["transformer.word_embeddings_layernorm.bias"] = W["emb_ln_b"]
+        sd["transformer.ln_f.weight"] = W["lnf_g"]
+        sd["transformer.ln_f.bias"] = W["lnf_b"]
+        sd["lm_head.weight"] = W["lm_head"]
+        for l in range(shape.n_layer):
+            p, h = f"l{l}.", f"transformer.h.{l}."
+            sd[h + "input_layernorm.weight"] = W[p + "ln1_g"]
+            sd[h + "input_layernorm.bias"] = W[p + "ln1_b"]
+            sd[h + "post_attention_layernorm.weight"] = W[p + "ln2_g"]
+            sd[h + "post_attention_layernorm.bias"] = W[p + "ln2_b"]
+            sd[h + "self_attention.query_key_value.weight"] = W[p + "w_qkv"]
+            sd[h + "self_attention.query_key_value.bias"] = W[p + "b_qkv"]
+            sd[h + "self_attention.dense.weight"] = W[p + "w_dense"]
+            sd[h + "self_attention.dense.bias"] = W[p + "b_dense"]
+            sd[h + "mlp.dense_h_to_4h.weight"] = W[p + "w_up"]
+            sd[h + "mlp.dense_h_to_4h.bias"] = W[p + "b_up"]
+            sd[h + "mlp.dense_4h_to_h.weight"] = W[p + "w_down"]
+            sd[h + "mlp.dense_4h_to_h.bias"] = W[p + "b_down"]
     else:
         sd["gpt_neox.embed_in.weight"] = W["wte"]
         sd["gpt_neox.final_layer_norm.weight"] = W["lnf_g"]
@@ -258,9 +349,11 @@ def build_hf_model(shape: DecoderShape, W: Dict[str, torch.Tensor]):
     """Instantiate the HF model on the meta device and bind ``W`` (fp32, CPU) to it; avoids the
     minutes-long HF random init for 7B shapes."""
     import torch.nn as nn
-    from transformers import FalconForCausalLM, GPTNeoXForCausalLM, LlamaForCausalLM
+    from transformers import (BloomForCausalLM, FalconForCausalLM, GPTNeoXForCausalLM, LlamaForCausalLM,
+                              OPTForCausalLM)
     cfg = hf_config(shape)
-    cls = {ARCH_FALCON: FalconForCausalLM, ARCH_GPT_NEOX: GPTNeoXForCausalLM, ARCH_LLAMA: LlamaForCausalLM}[shape.arch]
+    cls = {ARCH_FALCON: FalconForCausalLM, ARCH_GPT_NEOX: GPTNeoXForCausalLM, ARCH_LLAMA: LlamaForCausalLM,
+           ARCH_OPT: OPTForCausalLM, ARCH_BLOOM: BloomForCausalLM}[shape.arch]
     with torch.device("meta"):
         model = cls(cfg)
     sd = {k: v.to(torch.float32).contiguous() for k, v in to_hf_state_dict(shape, W).items()}

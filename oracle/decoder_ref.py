@@ -11,6 +11,10 @@ Follows, for the two families on the hot path:
   Llama    HF:models/llama/modeling_llama.py LlamaRMSNorm (x * rsqrt(mean(x^2) + eps) * w), LlamaMLP
            (down(silu(gate(x)) * up(x))), LlamaAttention (grouped-query heads, rotate_half RoPE on the whole head),
            LlamaDecoderLayer (sequential residual, two norms) -- also Mistral without a sliding window
+  OPT      HF:models/opt/modeling_opt.py OPTLearnedPositionalEmbedding (positions + 2), OPTDecoderLayer with
+           do_layer_norm_before (pre-LN, sequential residual), ReLU MLP, q/k/v/out projections with biases, no rotary
+  BLOOM    HF:models/bloom/modeling_bloom.py word_embeddings_layernorm, build_alibi_tensor (slope[h] * key position
+           added to the scaled scores), per-head [q,k,v] fused projection, bloom_gelu_forward (tanh GELU), BloomBlock
 It is validated against the HF modules themselves in tests/test_oracle_decoder.py, and is what the
 GPU parity tests call (it is faster than ``generate`` and can emulate bf16 operand rounding).
 """
@@ -22,7 +26,8 @@ from typing import Callable, Dict, List, Optional
 import torch
 import torch.nn.functional as F
 
-from llm_interpretation_replication_b200.shapes import DecoderShape, QKV_FALCON_MQA, NORM_RMS, MLP_SWIGLU
+from llm_interpretation_replication_b200.shapes import (DecoderShape, QKV_FALCON_MQA, NORM_RMS, MLP_SWIGLU, POS_ROPE, POS_LEARNED,
+                                                        POS_ALIBI, ACT_RELU, ACT_GELU_TANH)
 
 
 def _rope_cos_sin(shape: DecoderShape, L: int):
@@ -63,10 +68,19 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
     r = round_act if round_act is not None else (lambda t: t)
     d, nh, nkv, hd = shape.d_model, shape.n_head, shape.n_kv_head, shape.head_dim
     L = ids.shape[0]
-    cos, sin = _rope_cos_sin(shape, L)
-    cos, sin = cos.to(dtype), sin.to(dtype)
+    rope = shape.pos_type == POS_ROPE
+    if rope:
+        cos, sin = _rope_cos_sin(shape, L)
+        cos, sin = cos.to(dtype), sin.to(dtype)
     x = W["wte"].to(dtype)[ids]
+    if shape.pos_type == POS_LEARNED:
+        x = x + W["wpe"].to(dtype)[torch.arange(L) + shape.pos_offset]
+    if shape.emb_norm:
+        x = F.layer_norm(x, (d,), W["emb_ln_g"].to(dtype), W["emb_ln_b"].to(dtype), shape.norm_eps)
     causal = torch.tril(torch.ones(L, L, dtype=torch.bool))
+    alibi = None
+    if shape.pos_type == POS_ALIBI:      # [nh, 1, L]: slope * key position, the same for every query row
+        alibi = (W["alibi_slopes"].to(dtype)[:, None] * torch.arange(L, dtype=dtype)[None, :])[:, None, :]
 
     def norm(t, g, b):
         if shape.norm_type == NORM_RMS:
@@ -78,6 +92,11 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         if shape.mlp_type == MLP_SWIGLU:        # rows [0, ff) = gate_proj, [ff, 2ff) = up_proj
             up = r(up)                          # the 16-bit modes store gate/up before the elementwise kernel
             return F.silu(up[..., :shape.d_ff]) * up[..., shape.d_ff:]
+        if shape.act_type == ACT_RELU:
+            return F.relu(up)
+        if shape.act_type == ACT_GELU_TANH:     # the 16-bit modes store up before the elementwise kernel
+            up = r(up)
+            return up * 0.5 * (1.0 + torch.tanh(0.79788456 * up * (1 + 0.044715 * up * up)))
         return F.gelu(up)
 
     for l in range(shape.n_layer):
@@ -86,13 +105,16 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         ln1 = norm(x, p + "ln1_g", p + "ln1_b")
         qkv = F.linear(r(ln1), W[p + "w_qkv"].to(dtype), bias("b_qkv"))
         q, k, v = _split_qkv(shape, qkv)
-        q = r(_apply_rope(q, cos, sin, shape.rotary_dim))
-        k = r(_apply_rope(k, cos, sin, shape.rotary_dim))
+        if rope:
+            q, k = _apply_rope(q, cos, sin, shape.rotary_dim), _apply_rope(k, cos, sin, shape.rotary_dim)
+        q, k = r(q), r(k)
         v = r(v)
         rep = nh // k.shape[1]
         kk = k.repeat_interleave(rep, dim=1)
         vv = v.repeat_interleave(rep, dim=1)
         s = torch.einsum("qhd,khd->hqk", q, kk) / math.sqrt(hd)
+        if alibi is not None:
+            s = s + alibi
         s = s.masked_fill(~causal[None], float("-inf"))
         a = torch.softmax(s, dim=-1)
         o = torch.einsum("hqk,khd->qhd", a, vv).reshape(L, nh * hd)

@@ -79,6 +79,9 @@ SPECS = [
     # `make_golden.py --append 3`, which leaves the first three cases and the bootstrap goldens untouched
     ("tiny-llama", shapes.tiny_llama(), 104),
     ("tiny-mistral", shapes.tiny_mistral(), 105),
+    # OPT (opt-iml-1.3b) and BLOOM (bloomz-7b1) of the same sweep (:148,151): `make_golden.py --append 5`
+    ("tiny-opt", shapes.tiny_opt(), 106),
+    ("tiny-bloom", shapes.tiny_bloom(), 107),
 ]
 
 

@@ -15,7 +15,8 @@ def _save_hf(shape, W, path, safe=True):
     return model
 
 
-@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_neox_sequential", "tiny_llama", "tiny_mistral"])
+@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_neox_sequential", "tiny_llama", "tiny_mistral",
+                                   "tiny_opt", "tiny_bloom"])
 @pytest.mark.parametrize("safe", [True, False], ids=["safetensors", "bin"])
 def test_checkpoint_round_trip(tmp_path, maker, safe):
     """A checkpoint written by transformers itself comes back as the same shape and bit-identical tensors."""
@@ -25,7 +26,7 @@ def test_checkpoint_round_trip(tmp_path, maker, safe):
     shp2, W2 = checkpoint.load_checkpoint(str(tmp_path), device="cpu", weight_dtype=torch.float32)
     for f in ("arch", "n_layer", "d_model", "n_head", "n_kv_head", "head_dim", "d_ff", "vocab", "rotary_dim", "rope_theta",
               "norm_eps", "parallel_residual", "n_ln_per_layer", "has_bias", "tied_head", "qkv_layout", "eos_id", "max_pos",
-              "norm_type", "mlp_type"):
+              "norm_type", "mlp_type", "pos_type", "pos_offset", "act_type", "emb_norm"):
         assert getattr(shp2, f) == getattr(shp, f), f
     names = checkpoint.expected_names(shp)
     assert set(names) <= set(W2)
@@ -58,11 +59,20 @@ def test_config_mapping_matches_registry():
     llama2 = dict(model_type="llama", hidden_size=4096, num_hidden_layers=32, num_attention_heads=32, num_key_value_heads=32,
                   intermediate_size=11008, vocab_size=32000, rms_norm_eps=1e-5, max_position_embeddings=4096, hidden_act="silu",
                   tie_word_embeddings=False, eos_token_id=2, bos_token_id=1)
+    opt = dict(model_type="opt", hidden_size=2048, num_hidden_layers=24, ffn_dim=8192, num_attention_heads=32, vocab_size=50272,
+               max_position_embeddings=2048, do_layer_norm_before=True, word_embed_proj_dim=2048, activation_function="relu",
+               enable_bias=True, eos_token_id=2, tie_word_embeddings=True)
+    bloom = dict(model_type="bloom", hidden_size=4096, n_layer=30, n_head=32, vocab_size=250880, layer_norm_epsilon=1e-5,
+                 apply_residual_connection_post_layernorm=False, eos_token_id=2, seq_length=2048)
+    assert checkpoint.shape_from_hf_config(opt, "opt-iml-1.3b") == shapes.opt_iml_1_3b()
+    assert checkpoint.shape_from_hf_config(bloom, "bloomz-7b1") == shapes.bloomz_7b1()
     for cfg, ref in ((old_falcon, shapes.falcon_7b()), (new_falcon, shapes.falcon_7b()), (stablelm, shapes.stablelm_alpha_7b()),
                      (redpajama, shapes.redpajama_3b()), (mistral, shapes.mistral_7b()), (llama2, shapes.llama2_7b())):
         got = checkpoint.shape_from_hf_config(cfg, ref.name)
         assert got == ref, (got, ref)
-    for bad in (dict(model_type="bloom"), dict(model_type="mistral", hidden_size=64, num_attention_heads=2, num_hidden_layers=1,
+    for bad in (dict(model_type="t5"), dict(model_type="opt", hidden_size=1024, word_embed_proj_dim=512, num_hidden_layers=24,
+                                               ffn_dim=4096, num_attention_heads=16, vocab_size=50272, do_layer_norm_before=False),
+                dict(model_type="mistral", hidden_size=64, num_attention_heads=2, num_hidden_layers=1,
                                                   intermediate_size=128, vocab_size=32, sliding_window=1024),
                 dict(model_type="falcon", hidden_size=8192, num_attention_heads=128, num_hidden_layers=60,
                                                   vocab_size=65024, new_decoder_architecture=True),

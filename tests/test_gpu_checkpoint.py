@@ -12,7 +12,7 @@ PROMPTS = ['Question: Is "soup" a "beverage"? Answer either \'Yes\' or \'No\', w
            'Is the soup a beverage?']
 
 
-@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_llama"])
+@pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_llama", "tiny_opt", "tiny_bloom"])
 def test_local_checkpoint_end_to_end_vs_hf(tmp_path, monkeypatch, maker):
     from transformers import AutoModelForCausalLM, AutoTokenizer
     from llm_interpretation_replication_b200 import scorer as S, shapes, weights
@@ -63,7 +63,7 @@ def test_unsupported_checkpoint_becomes_nan_rows(tmp_path, monkeypatch):
     from llm_interpretation_replication_b200.entrypoints import run_base_vs_instruct_100q as ep
     d = tmp_path / "org" / "llama"
     d.mkdir(parents=True)
-    (d / "config.json").write_text(json.dumps({"model_type": "bloom", "hidden_size": 64}))
+    (d / "config.json").write_text(json.dumps({"model_type": "t5", "hidden_size": 64}))
     monkeypatch.setenv("B2S_CHECKPOINT_ROOT", str(tmp_path))
     rows = ep.run_model_on_prompts("org/llama", ["Is a tweet a publication?"], is_base_model=False)
     assert len(rows) == 1 and rows[0]["success"] is False and np.isnan(rows[0]["relative_prob"])

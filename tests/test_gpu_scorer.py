@@ -58,14 +58,14 @@ def _run_case(case, mode, tol):
     return worst
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
 def test_scorer_fp32_check_vs_reference_golden(case_idx):
     import gpu_util as U
     from llm_interpretation_replication_b200 import shapes
     _run_case(U.golden_cases()[case_idx], shapes.MODE_FP32_CHECK, TOL_FP32)
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
 def test_completion_50_tokens_vs_reference_golden(case_idx):
     """greedy decoding continues to the reference's max_new_tokens=50 for every prompt (up to EOS)
     while only the first 10 positions are scanned.  The decoded `completion` must equal the string the reference's
@@ -101,7 +101,7 @@ def test_completion_50_tokens_vs_reference_golden(case_idx):
     sc.close()
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
 @pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
 def test_scorer_bf16_vs_reference_golden(case_idx, mode_name):
     import gpu_util as U
@@ -210,4 +210,30 @@ def test_scorer_real_dims_mistral(mode_name):
         rel = (p[700] / (p[700] + p[900])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
         assert abs(rows[i][3] - torch.logsumexp(lo, -1).item()) <= 5e-3
+    sc.close()
+
+
+@pytest.mark.parametrize("maker", ["opt_iml_1_3b", "bloomz_7b1"])
+@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+def test_scorer_real_dims_opt_bloom(maker, mode_name):
+    """OPT-1.3B widths (learned positions, ReLU, head_dim 64 on the tensor-core attention) and BLOOM-7B1 widths (ALiBi,
+    embedding LayerNorm, tanh-GELU, head_dim 128; vocabulary cut to 32000 to keep the CPU oracle small) at 2 layers."""
+    import dataclasses
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights
+    from oracle import decoder_ref
+    shp = getattr(shapes, maker)().with_layers(2)
+    if shp.vocab > 60000:
+        shp = dataclasses.replace(shp, vocab=32000)
+    W = weights.init_weights(shp, seed=13)
+    sc = U.make_scorer(shp, W, getattr(shapes, mode_name), max_tokens=1024, max_seqs=8, max_lookahead=2)
+    g = np.random.RandomState(6)
+    ids = [g.randint(4, shp.vocab - 3, size=L).tolist() for L in (19, 111, 70)]
+    rows, gens = sc.score_ids(ids, np.array([[700, 900]]), topk=5, max_lookahead=2)
+    rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
+    for i, x in enumerate(ids):
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
+        p = torch.softmax(lo, -1)
+        rel = (p[700] / (p[700] + p[900])).item()
+        assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
     sc.close()
