@@ -49,22 +49,34 @@ def candidate_ids(tokenizer, variant: str, yes: str = " Yes", no: str = " No") -
 
 
 def plan_batches(lengths: Sequence[int], max_tokens: int, max_seqs: int) -> List[List[int]]:
-    """Length-bucketed packing: prompts sorted by length (longest first, stable), cut greedily into
-    batches of at most ``max_tokens`` packed tokens and ``max_seqs`` prompts."""
+    """Length-bucketed packing: prompts sorted by length (longest first, stable), cut greedily into batches of at most
+    ``max_tokens`` packed tokens and ``max_seqs`` prompts.  The cut points aim at EQUAL token counts over the smallest
+    number of batches that fits (a full batch followed by a small remainder would run its one-token steps with a
+    nearly empty GEMM wave); a prompt's result does not depend on the batch it lands in."""
     order = sorted(range(len(lengths)), key=lambda i: (-lengths[i], i))
-    batches, cur, cur_tok = [], [], 0
-    for i in order:
-        L = lengths[i]
-        if L > max_tokens:
-            raise ValueError(f"prompt {i} has {L} tokens, more than max_tokens={max_tokens}")
-        if cur and (cur_tok + L > max_tokens or len(cur) >= max_seqs):
+    total = sum(lengths)
+    for i in order[:1]:
+        if lengths[i] > max_tokens:
+            raise ValueError(f"prompt {i} has {lengths[i]} tokens, more than max_tokens={max_tokens}")
+    n_batches = max(1, -(-total // max_tokens), -(-len(order) // max_seqs)) if order else 0
+    while True:
+        target = -(-total // n_batches) if n_batches else 0
+        batches, cur, cur_tok, done_tok = [], [], 0, 0
+        for i in order:
+            L = lengths[i]
+            # close the batch when it is full, or when it has reached its share and later batches can still take the rest
+            at_share = cur_tok >= target and len(batches) < n_batches - 1
+            if cur and (cur_tok + L > max_tokens or len(cur) >= max_seqs or at_share):
+                batches.append(cur)
+                done_tok += cur_tok
+                cur, cur_tok = [], 0
+            cur.append(i)
+            cur_tok += L
+        if cur:
             batches.append(cur)
-            cur, cur_tok = [], 0
-        cur.append(i)
-        cur_tok += L
-    if cur:
-        batches.append(cur)
-    return batches
+        if len(batches) <= n_batches or n_batches >= len(order):
+            return batches
+        n_batches = len(batches)      # the limits forced more batches than planned: rebalance over that many
 
 
 class Scorer:
