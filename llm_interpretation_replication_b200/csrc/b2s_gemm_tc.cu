@@ -36,6 +36,8 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
+  int* wave_sync;        // experiment: global counters, one per synchronised wave (null = off)
+  int wave_sync_every;   // pair kernels: all producers meet every this many tiles
   int pair_stride;       // experiment: CTA pair p works on the tile sequence of pair (p * pair_stride) % num_pairs
   int serp;              // serpentine order: odd groups walk the column tiles backwards; K walked backwards by odd column tiles (1) or odd waves (2)
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
@@ -410,6 +412,26 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
 // ---------------------------------------------------------------------------------------------
 // Kernel
 // ---------------------------------------------------------------------------------------------
+// Wave meeting (b2s_set_option "gemm_wave_sync", default every 4 tiles).  CTAs that share an A or W panel only hit in
+// L2 while they walk K together; nothing keeps persistent CTAs together, and once they drift the panels are re-read
+// from DRAM (measured on the CTA-pair kernels: 63 -> 24 GB per launch and 1052 -> 1244 TFLOP/s sustained on the
+// down projection, profiles/r1_gemm_wave_sync.txt).  Every `every` tiles the producer threads of all CTAs meet at a
+// global counter.  Best effort: a CTA that waits longer than 4 ms (another grid is holding SMs) stops meeting, so the
+// kernel can never dead-lock on residency; results do not depend on the meeting at all.
+__device__ __forceinline__ void wave_meet(const GemmParams& p, int wave, int expect, bool& enabled) {
+  if (!enabled || p.wave_sync == nullptr || wave == 0 || wave % p.wave_sync_every != 0) return;
+  const int slot = wave / p.wave_sync_every;
+  atomicAdd(p.wave_sync + slot, 1);
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while (*reinterpret_cast<volatile int*>(p.wave_sync + slot) < expect) {
+    __nanosleep(64);
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 4000000ull) { enabled = false; return; }
+  }
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -449,9 +471,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
+      bool meet = true;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mb, nb;
         tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, p.serp, mb, nb);
+        {
+          const int wave = (tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x);
+          wave_meet(p, wave, min(static_cast<int>(gridDim.x), num_tiles - wave * static_cast<int>(gridDim.x)), meet);
+        }
         const bool rev = p.serp == 2 ? ((((tile - static_cast<int>(blockIdx.x)) / static_cast<int>(gridDim.x)) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
           const int kb = rev ? p.num_kb - 1 - kq : kq;   // the MMA side only counts k-blocks, so the order is free
@@ -634,9 +661,11 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
+      bool meet = true;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
         tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
+        wave_meet(p, (tile - pair) / num_pairs, 2 * min(num_pairs, num_tiles - ((tile - pair) / num_pairs) * num_pairs), meet);
         const bool rev = p.serp == 2 ? ((((tile - pair) / num_pairs) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
           const int kb = rev ? p.num_kb - 1 - kq : kq;
@@ -787,9 +816,11 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
+      bool meet = true;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
         tile_coords3(tile, tiles_m3, p.tiles_n, p.group_m, p.serp, mb, nb);
+        wave_meet(p, (tile - pair) / num_pairs, 2 * min(num_pairs, num_tiles - ((tile - pair) / num_pairs) * num_pairs), meet);
         const bool rev = p.serp == 2 ? ((((tile - pair) / num_pairs) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
           const int kb = rev ? p.num_kb - 1 - kq : kq;
@@ -932,6 +963,9 @@ int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = ru
 // starts on the panel bytes the previous one touched last) but a row's fp32 summation order then depends on which wave
 // its tile falls in, i.e. on the batch around it -- sharded and unsharded runs stop being bit-identical.  1 = direction by
 // column tile: batch-invariant, but CTAs that share an A row-block no longer walk K together: -1 %.
+int g_opt_policy = 1;        // b2s_set_option "gemm_policy" (see launch_epi)
+int g_opt_wave_sync = 4;     // b2s_set_option "gemm_wave_sync": all producers meet every N tiles (0 = never)
+static __device__ int g_wave_counters[8192];
 int g_opt_pair_stride = 1;   // b2s_set_option "gemm_pair_stride" (experiment; must be coprime to the number of CTA pairs)
 int g_opt_serp = 0;
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
@@ -955,6 +989,17 @@ static cudaEvent_t prof_event() {
   return g_prof.pool[g_prof.used++];
 }
 
+static int arm_wave_sync(GemmParams& q, int tiles, int pairs, cudaStream_t st) {
+  if (g_opt_wave_sync <= 0) return B2S_OK;
+  const int waves = static_cast<int>(ceil_div(tiles, pairs));
+  if (waves <= g_opt_wave_sync || waves / g_opt_wave_sync + 1 > 8192) return B2S_OK;   // no meeting would happen / table too small
+  int* ctr = nullptr;
+  B2S_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ctr), g_wave_counters));
+  B2S_CHECK_CUDA(cudaMemsetAsync(ctr, 0, sizeof(int) * (waves / g_opt_wave_sync + 1), st));
+  q.wave_sync = ctr; q.wave_sync_every = g_opt_wave_sync;
+  return B2S_OK;
+}
+
 template <int EPI>
 static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb2, const CUtensorMap& ta3,
                       const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
@@ -972,7 +1017,12 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   // long-K and GELU launches (down / up projections) on single-CTA tiles, the short-K store/residual launches
   // (QKV, dense, LM head, one-token steps) on CTA pairs.
   int cg = g_opt_cta_group;
-  if (cg == 0) cg = (p.M >= 4096 && (p.K >= 8192 || EPI == EPI_GELU_BF16)) ? 1 : 2;
+  if (cg == 0) {
+    if (g_opt_policy == 1)   // with the wave meeting the CTA-pair kernels keep their panels in L2: 512x256 pair tiles for long K
+      cg = (p.M >= 4096 && p.K >= 8192) ? 3 : 2;
+    else                     // round-1 policy before the wave meeting: single-CTA tiles for long-K and GELU launches
+      cg = (p.M >= 4096 && (p.K >= 8192 || EPI == EPI_GELU_BF16)) ? 1 : 2;
+  }
   const bool big = (cg == 3 && p.M >= 4096) || cg == 4;   // 4 = always (tests)
   if (big) {
     static bool attr3_set = false;
@@ -985,6 +1035,7 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
     if (tiles3 < pairs) pairs = tiles3;
     GemmParams q = p;
     if (pairs != g_num_sms / 2) q.pair_stride = 1;   // the permutation is only a bijection on the full grid
+    B2S_TRY(arm_wave_sync(q, tiles3, pairs, st));
     gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, tc, q);
   } else if (cg >= 2) {
     static bool attr2_set = false;
@@ -997,9 +1048,12 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
     if (tiles2 < pairs) pairs = tiles2;
     GemmParams q = p;
     if (pairs != g_num_sms / 2) q.pair_stride = 1;
+    B2S_TRY(arm_wave_sync(q, tiles2, pairs, st));
     gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, tc, q);
   } else {
-    gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, tc, p);
+    GemmParams q = p;
+    B2S_TRY(arm_wave_sync(q, tiles, grid, st));
+    gemm_tc_kernel<EPI><<<grid, NUM_THREADS, SMEM_BYTES, st>>>(ta, tb, tc, q);
   }
   if (g_prof.on) {
     cudaEventRecord(prof_event(), st);
@@ -1044,6 +1098,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     if (g_opt_small_w_group > 0 && 2.0 * N * K <= 48e6) gm = g_opt_small_w_group;
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
     p.serp = g_opt_serp;
+    p.wave_sync = nullptr; p.wave_sync_every = 0;
     p.pair_stride = 1;
     {
       const int np = g_num_sms / 2;
@@ -1115,6 +1170,16 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_l2_hint") {
     B2S_REQUIRE(value >= 0 && value <= 7, "set_option: gemm_l2_hint must be in [0, 7]");
     b2s::g_opt_hint = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_policy") {
+    B2S_REQUIRE(value == 0 || value == 1, "set_option: gemm_policy must be 0 or 1");
+    b2s::g_opt_policy = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_wave_sync") {
+    B2S_REQUIRE(value >= 0 && value <= 1024, "set_option: gemm_wave_sync must be in [0, 1024]");
+    b2s::g_opt_wave_sync = value;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_pair_stride") {

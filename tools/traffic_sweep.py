@@ -11,7 +11,10 @@ timed = "--time" in sys.argv
 secs = 1.0
 lib = _lib.load(); st = _lib.current_stream()
 shapes = {"up": (18176, 4544, 1), "down": (4544, 18176, 2), "dense": (4544, 4544, 2), "qkv": (4672, 4544, 0)}
-if "--pairs" in sys.argv:
+if "--wavesync" in sys.argv:
+    grid = [(cg, 0, 0, ws) for cg in (3, 2) for ws in (0, 1, 2, 4, 8)] + [(1, 0, 0, 0)]
+    shapes = {k: shapes[k] for k in ("down", "up")}
+elif "--pairs" in sys.argv:
     grid = [(cg, 0, 0, ps) for cg in (2, 3) for ps in (1, 3, 9, 21, 27, 35)] + [(1, 0, 0, 1)]
     shapes = {k: shapes[k] for k in ("down", "up")}
 elif "--cg3" in sys.argv:
@@ -29,7 +32,7 @@ for name, (N, K, epi) in shapes.items():
     alg = 2 * (M * K + N * K) + (8 if epi == 2 else 2) * M * N
     for cg, gm, serp, hint in grid:
         def f():
-            lib.b2s_set_option(b"gemm_cta_group", cg); lib.b2s_set_option(b"gemm_group_m", gm); lib.b2s_set_option(b"gemm_serpentine", serp); lib.b2s_set_option(b"gemm_l2_hint", 0 if "--pairs" in sys.argv else hint); lib.b2s_set_option(b"gemm_pair_stride", hint if "--pairs" in sys.argv else 1)
+            lib.b2s_set_option(b"gemm_cta_group", cg); lib.b2s_set_option(b"gemm_group_m", gm); lib.b2s_set_option(b"gemm_serpentine", serp); lib.b2s_set_option(b"gemm_l2_hint", 0 if ("--pairs" in sys.argv or "--wavesync" in sys.argv) else hint); lib.b2s_set_option(b"gemm_pair_stride", hint if "--pairs" in sys.argv else 1); lib.b2s_set_option(b"gemm_wave_sync", hint if "--wavesync" in sys.argv else 0)
             _lib.check(lib.b2s_gemm_f16(_lib.ptr(A), _lib.ptr(W), None, _lib.ptr(out), M, N, K, epi, st), "gemm")
         rec = {"shape": name, "cg": cg, "group_m": gm, "serp": serp, "hint": hint, "algorithmic_bytes": alg}
         if timed:
