@@ -333,7 +333,7 @@ def main():
                            "topk": TOPK, "batch_tokens": args.batch_tokens, "gemm_cta_group": max(args.gemm_cta_group, 0), "options": args.option, "batches_per_rank": len(batches), "parallelism": f"prompt-sharded x{world}, replicated weights",
                            "l2": "inputs larger than L2: 13.8 GB of 16-bit weights are re-read for every batch", "all_rel_prob_finite": finite},
                 "clocks": clk, "gpu_launches": launches,
-                "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel / gemm_tc2_kernel (tcgen05, cta_group::1 / ::2)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                "roofline": {"bound": "tensor", "kernel": "gemm_tc3_kernel / gemm_tc2_kernel (tcgen05 cta_group::2 on 512x256 / 256x256 pair tiles; gemm_tc_kernel when forced)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                              "frac": achieved / peak if peak else None, "traffic": traffic, "peak_source": peak_src,
                              "launches": int(g_n.value), "gemm_ms_per_step": g_ms.value / args.steps,
                              "gemm_share_of_step": (g_ms.value / ms) if ms else None,
