@@ -134,8 +134,21 @@ B2S_API int64_t b2s_launch_count(int32_t reset);
 B2S_API int b2s_profile_gemm(int32_t enable);
 B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* flops);
 
-/* Tuning knobs (no counterpart in the reference).  "gemm_cta_group": 1 = one CTA per 128x256 tile,
- * 2 = CTA pairs (tcgen05 cta_group::2) on 256x256 tiles. */
+/* Tuning / A-B knobs (no counterpart in the reference; process-wide; none of them changes a result bit except
+ * "gemm_serpentine", which changes the fp32 summation order).  Defaults in brackets.
+ *   "gemm_cta_group"     [0] 0 = per-launch policy; 1 = one CTA per 128x256 tile; 2 = CTA pairs (tcgen05
+ *                        cta_group::2) on 256x256 tiles; 3 = CTA pairs on 512x256 tiles when M >= 4096; 4 = always
+ *   "gemm_policy"        [1] policy used by gemm_cta_group 0: 1 = 512x256 pair tiles for K >= 8192 and M >= 4096, 256x256
+ *                        pairs otherwise; 0 = the earlier policy (single-CTA tiles for long-K and GELU launches)
+ *   "gemm_wave_sync"     [4] the producer threads of all CTAs meet at a global counter every N tiles so that CTAs sharing
+ *                        an A or W panel walk K together and hit in L2 (0 = never; bounded wait, cannot dead-lock)
+ *   "gemm_group_m"       [0] rasterisation group in 128-row blocks (0 = heuristic); "gemm_small_w_group" [8] group used
+ *                        when W itself is L2-sized
+ *   "gemm_serpentine"    [0] K walked backwards by odd column tiles (1) or odd waves (2)
+ *   "gemm_l2_hint"       [0] TMA L2 eviction hints 0..7; "gemm_tma_store" [1] epilogue through TMA bulk stores;
+ *                        "gemm_pair_stride" [1] experiment: permutation of the CTA-pair -> tile-sequence assignment
+ *   "attn_ts"            [1] prompt-pass / one-token attention with P kept in tensor memory (0 = first-generation kernels)
+ *   "attn_hold_s"        [0] first-generation attention only: keep S in registers between the two softmax passes */
 B2S_API int b2s_set_option(const char* name, int32_t value);
 
 /* ---- building blocks (exported so the parity tests can exercise each kernel through the ABI) ----
