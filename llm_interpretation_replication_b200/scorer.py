@@ -58,17 +58,20 @@ def plan_batches(lengths: Sequence[int], max_tokens: int, max_seqs: int) -> List
     for i in order[:1]:
         if lengths[i] > max_tokens:
             raise ValueError(f"prompt {i} has {lengths[i]} tokens, more than max_tokens={max_tokens}")
-    n_batches = max(1, -(-total // max_tokens), -(-len(order) // max_seqs)) if order else 0
+    if not order:
+        return []
+    by_tokens, by_count = -(-total // max_tokens), -(-len(order) // max_seqs)
+    n_batches = max(1, by_tokens, by_count)
     while True:
-        target = -(-total // n_batches) if n_batches else 0
-        batches, cur, cur_tok, done_tok = [], [], 0, 0
+        # share of a batch: tokens when the token limit decides the number of batches, prompts when the prompt limit does
+        tok_share = -(-total // n_batches) if by_tokens >= by_count else max_tokens
+        cnt_share = -(-len(order) // n_batches) if by_count > by_tokens else max_seqs
+        batches, cur, cur_tok = [], [], 0
         for i in order:
             L = lengths[i]
-            # close the batch when it is full, or when it has reached its share and later batches can still take the rest
-            at_share = cur_tok >= target and len(batches) < n_batches - 1
+            at_share = (cur_tok >= tok_share or len(cur) >= cnt_share) and len(batches) < n_batches - 1
             if cur and (cur_tok + L > max_tokens or len(cur) >= max_seqs or at_share):
                 batches.append(cur)
-                done_tok += cur_tok
                 cur, cur_tok = [], 0
             cur.append(i)
             cur_tok += L
@@ -76,7 +79,7 @@ def plan_batches(lengths: Sequence[int], max_tokens: int, max_seqs: int) -> List
             batches.append(cur)
         if len(batches) <= n_batches or n_batches >= len(order):
             return batches
-        n_batches = len(batches)      # the limits forced more batches than planned: rebalance over that many
+        n_batches = len(batches)      # packing loss forced more batches than planned: rebalance over that many
 
 
 class Scorer:

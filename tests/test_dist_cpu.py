@@ -2,6 +2,7 @@
 import os
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -28,6 +29,29 @@ def test_plan_batches_limits():
     for x in b:
         assert sum(lens[i] for i in x) <= 128 and len(x) <= 3
     assert plan_batches([], 10, 10) == []
+    with pytest.raises(ValueError):
+        plan_batches([5, 200], 128, 3)                       # a prompt longer than a batch
+
+
+def test_plan_batches_balances_token_counts():
+    """The smallest number of batches that fits, with near-equal token counts (no small remainder batch), every prompt
+    exactly once, limits respected; hypothesis-style sweep over random length sets."""
+    g = np.random.RandomState(0)
+    for trial in range(40):
+        n = int(g.randint(1, 4000))
+        lens = g.randint(1, 191, size=n).tolist()
+        max_tokens = int(g.choice([256, 4096, 65536, 262144]))
+        max_seqs = int(g.choice([8, 512, 4096]))
+        b = plan_batches(lens, max_tokens, max_seqs)
+        assert sorted(i for x in b for i in x) == list(range(n))
+        toks = [sum(lens[i] for i in x) for x in b]
+        assert all(t <= max_tokens for t in toks) and all(len(x) <= max_seqs for x in b)
+        need = max(-(-sum(lens) // max_tokens), -(-n // max_seqs))
+        if max_tokens < 4096:            # batches barely larger than a prompt: packing loss dominates, only validity is checked
+            continue
+        assert len(b) <= need + 1
+        if len(b) > 1 and 2 * -(-n // max_seqs) <= -(-sum(lens) // max_tokens):   # clearly token-bound: no small remainder batch
+            assert min(toks) >= 0.5 * max(toks), (trial, toks)
 
 
 def _worker(rank, ws, port, n_total):
