@@ -49,37 +49,40 @@ def candidate_ids(tokenizer, variant: str, yes: str = " Yes", no: str = " No") -
 
 
 def plan_batches(lengths: Sequence[int], max_tokens: int, max_seqs: int) -> List[List[int]]:
-    """Length-bucketed packing: prompts sorted by length (longest first, stable), cut greedily into batches of at most
-    ``max_tokens`` packed tokens and ``max_seqs`` prompts.  The cut points aim at EQUAL token counts over the smallest
-    number of batches that fits (a full batch followed by a small remainder would run its one-token steps with a
-    nearly empty GEMM wave); a prompt's result does not depend on the batch it lands in."""
+    """Length-bucketed packing: prompts sorted by length (longest first, stable) and cut into consecutive batches of at
+    most ``max_tokens`` packed tokens and ``max_seqs`` prompts.  The number of batches is the smallest the greedy cut
+    reaches; among those plans the one with the smallest token cap is taken, so the batches carry near-equal token
+    counts (a full batch followed by a small remainder would run its one-token steps with a nearly empty GEMM wave).
+    A prompt's result does not depend on the batch it lands in."""
     order = sorted(range(len(lengths)), key=lambda i: (-lengths[i], i))
-    total = sum(lengths)
-    for i in order[:1]:
-        if lengths[i] > max_tokens:
-            raise ValueError(f"prompt {i} has {lengths[i]} tokens, more than max_tokens={max_tokens}")
     if not order:
         return []
-    by_tokens, by_count = -(-total // max_tokens), -(-len(order) // max_seqs)
-    n_batches = max(1, by_tokens, by_count)
-    while True:
-        # share of a batch: tokens when the token limit decides the number of batches, prompts when the prompt limit does
-        tok_share = -(-total // n_batches) if by_tokens >= by_count else max_tokens
-        cnt_share = -(-len(order) // n_batches) if by_count > by_tokens else max_seqs
+    longest = lengths[order[0]]
+    if longest > max_tokens:
+        raise ValueError(f"prompt {order[0]} has {longest} tokens, more than max_tokens={max_tokens}")
+
+    def cut(cap: int) -> List[List[int]]:
         batches, cur, cur_tok = [], [], 0
         for i in order:
             L = lengths[i]
-            at_share = (cur_tok >= tok_share or len(cur) >= cnt_share) and len(batches) < n_batches - 1
-            if cur and (cur_tok + L > max_tokens or len(cur) >= max_seqs or at_share):
+            if cur and (cur_tok + L > cap or len(cur) >= max_seqs):
                 batches.append(cur)
                 cur, cur_tok = [], 0
             cur.append(i)
             cur_tok += L
-        if cur:
-            batches.append(cur)
-        if len(batches) <= n_batches or n_batches >= len(order):
-            return batches
-        n_batches = len(batches)      # packing loss forced more batches than planned: rebalance over that many
+        batches.append(cur)
+        return batches
+
+    best = cut(max_tokens)
+    lo, hi = max(longest, -(-sum(lengths) // len(best))), max_tokens     # smallest cap that still needs len(best) batches
+    while lo < hi:
+        mid = (lo + hi) // 2
+        b = cut(mid)
+        if len(b) <= len(best):
+            best, hi = b, mid
+        else:
+            lo = mid + 1
+    return best
 
 
 class Scorer:
