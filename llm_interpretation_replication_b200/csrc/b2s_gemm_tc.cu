@@ -1011,11 +1011,10 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   const int tiles = p.tiles_m * p.tiles_n;
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
   if (g_prof.on) cudaEventRecord(prof_event(), st);
-  // big tiles pay when there are enough 512-row blocks; short batches (one-token steps, LM head) keep 256-row tiles
-  // Tiling policy.  Under the 1 kW power cap the variants trade clock for tensor-pipe utilisation and land within
-  // ~10 % of each other (profiles/r1_gemm_sustained_sweep.jsonl); option 0 picks per launch what sustained best:
-  // long-K and GELU launches (down / up projections) on single-CTA tiles, the short-K store/residual launches
-  // (QKV, dense, LM head, one-token steps) on CTA pairs.
+  // Tiling policy (gemm_cta_group 0).  Under the 1 kW power cap the variants trade clock for tensor-pipe utilisation
+  // (profiles/r1_gemm_power.md).  Since the wave meeting keeps the CTA-pair kernels' panels in L2 they win everywhere:
+  // 512x256 pair tiles when K is long enough to amortise their exposed epilogue and there are enough 512-row blocks
+  // (down projection), 256x256 pair tiles otherwise (QKV, dense, up + GELU, LM head, one-token steps).
   int cg = g_opt_cta_group;
   if (cg == 0) {
     if (g_opt_policy == 1)   // with the wave meeting the CTA-pair kernels keep their panels in L2: 512x256 pair tiles for long K
