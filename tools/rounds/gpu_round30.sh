@@ -1,0 +1,11 @@
+#!/bin/bash
+mkdir -p gpurun_out
+cd "$(dirname "$0")/../.."
+rm -f gpurun_out/summary30.txt
+run() { name=$1; shift; timeout ${TMO:-900} "$@" > gpurun_out/$name.log 2>&1; echo "$name exit $?" | tee -a gpurun_out/summary30.txt; }
+run time30    python tools/traffic_sweep.py 131072 --time --cg3
+run plain30   python tools/traffic_sweep.py 131072 --cg3
+if grep -q "plain30 exit 0" gpurun_out/summary30.txt; then
+run ncu30     ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_bytes.sum,lts__t_sector_hit_rate.pct --clock-control none --csv --log-file gpurun_out/traffic30.csv -k regex:gemm_tc python tools/traffic_sweep.py 131072 --cg3
+fi
+grep '^{' gpurun_out/time30.log
