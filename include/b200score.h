@@ -28,7 +28,8 @@ extern "C" {
 #define B2S_API
 #endif
 
-enum { B2S_OK = 0, B2S_EINVAL = -1, B2S_ECUDA = -2, B2S_ENOMEM = -3, B2S_EUNSUPPORTED = -4 };
+enum { B2S_OK = 0, B2S_EINVAL = -1, B2S_ECUDA = -2, B2S_ENOMEM = -3, B2S_EUNSUPPORTED = -4,
+       B2S_ERANGE = -5 /* results were produced, but some rows are not finite (see b2s_score_host) */ };
 
 enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1, B2S_ARCH_LLAMA = 2, B2S_ARCH_OPT = 3, B2S_ARCH_BLOOM = 4 };
 /* position encoding: rotary; learned table added to the token embedding (HF opt, rows pos + pos_offset); ALiBi
@@ -91,9 +92,17 @@ B2S_API void   b2s_model_destroy(b2s_model* m);
 B2S_API size_t b2s_workspace_bytes(const b2s_model* m, int64_t max_tokens, int32_t max_seqs, int32_t max_lookahead);
 
 /* out rows: [p_a, p_b, rel, lse, logit_a, logit_b, pos_found, found]; gen_ids[N,max_lookahead]
- * holds the greedy tokens (-1 after EOS).  topk is 5 (100q script) or 2 (compare_* scripts).
- * tokens/cu_seqlens/cand_ids/out/gen_ids are DEVICE pointers; the call only enqueues work, except
- * for one 4-byte readback per look-ahead step that lets it stop once every prompt is resolved. */
+ * holds the greedy tokens (-1 after EOS, and at positions a prompt did not need).  topk is 5 (100q script) or 2
+ * (compare_* scripts).  tokens/cu_seqlens/cand_ids/out/gen_ids are DEVICE pointers.  Position 0 (the prompt pass) is
+ * only enqueued.  Every later look-ahead position costs one 4-byte read-back and a stream synchronisation: the number
+ * of prompts that still need a position sizes that step's launches -- a one-token step runs only the unresolved,
+ * still-alive prompts (in completion mode: every prompt that has not produced EOS), gathered into consecutive rows --
+ * and the call returns early once none is left.  A prompt's row does not depend on which other prompts share its
+ * batch or its step.
+ * Range check: a prompt whose logits are not finite at a position it is scored on (in the FP16 mode an activation
+ * beyond 65504 overflows to infinity) gets p_a = p_b = rel = lse = NaN and found = -1, and stops taking steps; it is
+ * never reported as a number.  b2s_score leaves it at that; the _host calls return B2S_ERANGE after copying all
+ * rows back. */
 B2S_API int b2s_score(b2s_model* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs,
               int32_t total_tokens, int32_t max_seqlen, const int32_t* cand_ids /*[N,2]*/,
               int32_t topk, int32_t max_lookahead, int32_t eos_id,
@@ -147,6 +156,8 @@ B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* f
  *   "gemm_serpentine"    [0] K walked backwards by odd column tiles (1) or odd waves (2)
  *   "gemm_l2_hint"       [0] TMA L2 eviction hints 0..7; "gemm_tma_store" [1] epilogue through TMA bulk stores;
  *                        "gemm_pair_stride" [1] experiment: permutation of the CTA-pair -> tile-sequence assignment
+ *   "lookahead_compact"  [1] one-token steps run only the prompts that still need a position (0 = every prompt of the
+ *                        batch runs every step, the round-1 behaviour; rows are bit-identical either way)
  *   "attn_ts"            [1] prompt-pass / one-token attention with P kept in tensor memory (0 = first-generation kernels)
  *   "attn_hold_s"        [0] first-generation attention only: keep S in registers between the two softmax passes */
 B2S_API int b2s_set_option(const char* name, int32_t value);

@@ -15,6 +15,13 @@ class B2SError(RuntimeError):
     pass
 
 
+class B2SRangeError(B2SError):
+    """B2S_ERANGE: the call completed, but some prompts produced non-finite logits (their rows are NaN with found = -1)."""
+
+
+E_RANGE = -5
+
+
 class ModelDesc(C.Structure):
     _fields_ = [
         ("abi_version", C.c_int32), ("arch", C.c_int32),
@@ -87,7 +94,7 @@ def load():
 def check(rc: int, what: str = ""):
     if rc != 0:
         msg = load().b2s_last_error().decode("utf-8", "replace")
-        raise B2SError(f"{what}: error {rc}: {msg}")
+        raise (B2SRangeError if rc == E_RANGE else B2SError)(f"{what}: error {rc}: {msg}")
 
 
 def ptr(t):

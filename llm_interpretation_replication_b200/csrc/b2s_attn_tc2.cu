@@ -435,11 +435,8 @@ attn_dec2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 
 template <bool F16, int KVBOX>
 static int launch_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_dec2_kernel<F16, KVBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, dec2_smem<KVBOX>()));
-    attr_set = true;
-  }
+  // per-device function attribute, and cheap: set on every launch rather than once per process
+  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_dec2_kernel<F16, KVBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, dec2_smem<KVBOX>()));
   CUtensorMap tq, tk, tv;
   const uint64_t rpt = static_cast<uint64_t>(a.qkv_dim / A2_HD);   // qkv viewed as [total_rows * qkv_dim/64, 64]
   B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows) * rpt, A2_HD, A2_HD * 2, A2_BM, A2_HD, a.f16));
@@ -472,12 +469,9 @@ int g_opt_attn_ts = 1;   // b2s_set_option("attn_ts"): 1 = this kernel for the p
 
 int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
   B2S_REQUIRE(attn_tc_supported(a.hd, a.max_kv), "attn_tc2: head_dim %d / %d keys not supported", a.hd, a.max_kv);
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
-    B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
-    attr_set = true;
-  }
+  // per-device function attribute, and cheap: set on every launch rather than once per process
+  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
+  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
   CUtensorMap tq, tk, tv;
   B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
                             static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, A2_HD, a.f16));

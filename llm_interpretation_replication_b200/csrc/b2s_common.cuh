@@ -6,6 +6,7 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <atomic>
 #include <string>
 
 #include "../../include/b200score.h"
@@ -15,7 +16,7 @@ namespace b2s {
 // ---- error plumbing --------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
-extern int64_t g_launch_count;
+extern std::atomic<int64_t> g_launch_count;   // kernels launched by this library, any thread (b2s_launch_count)
 
 #define B2S_CHECK_CUDA(expr)                                                                  \
   do {                                                                                        \
@@ -28,7 +29,7 @@ extern int64_t g_launch_count;
 
 #define B2S_CHECK_LAUNCH()                                                                    \
   do {                                                                                        \
-    b2s::g_launch_count++;                                                                    \
+    b2s::g_launch_count.fetch_add(1, std::memory_order_relaxed);                                                                   \
     cudaError_t _e = cudaGetLastError();                                                      \
     if (_e != cudaSuccess) {                                                                  \
       b2s::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \

@@ -21,20 +21,22 @@ __global__ void prep_prefill_kernel(const int32_t* __restrict__ cu, int n_seqs, 
   for (int t = s + threadIdx.x; t < e; t += blockDim.x) { m.pos[t] = t - s; m.slot[t] = kv0 + (t - s); }
 }
 
-// decode step `step` (>= 1): row i holds the token generated at position step-1 of prompt i
-__global__ void prep_decode_kernel(const int32_t* __restrict__ cu, int n_seqs, int lookahead, int step, BatchMeta m) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_seqs) return;
+// decode step `step` (>= 1): row r holds the token generated at position step-1 of prompt act[r] (act null: prompt r)
+__global__ void prep_decode_kernel(const int32_t* __restrict__ cu, int n_rows, int lookahead, int step,
+                                   const int32_t* __restrict__ act, BatchMeta m) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_rows) return;
+  const int i = act ? act[r] : r;
   const int L = cu[i + 1] - cu[i];
   const int kv0 = cu[i] + i * lookahead;
   const int p = L + step - 1;
-  m.q_start[i] = i; m.q_len[i] = 1; m.kv_start[i] = kv0; m.kv_len[i] = p + 1; m.last_row[i] = i;
-  m.pos[i] = p; m.slot[i] = kv0 + p;
+  m.q_start[r] = r; m.q_len[r] = 1; m.kv_start[r] = kv0; m.kv_len[r] = p + 1; m.last_row[r] = r;
+  m.pos[r] = p; m.slot[r] = kv0 + p;
 }
 
-int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const BatchMeta& m, cudaStream_t st) {
-  if (step == 0) prep_prefill_kernel<<<n_seqs, 128, 0, st>>>(cu, n_seqs, lookahead, m);
-  else prep_decode_kernel<<<static_cast<unsigned>(ceil_div(n_seqs, 128)), 128, 0, st>>>(cu, n_seqs, lookahead, step, m);
+int launch_prep(const int32_t* cu, int n_rows, int lookahead, int step, const int32_t* act, const BatchMeta& m, cudaStream_t st) {
+  if (step == 0) prep_prefill_kernel<<<n_rows, 128, 0, st>>>(cu, n_rows, lookahead, m);
+  else prep_decode_kernel<<<static_cast<unsigned>(ceil_div(n_rows, 128)), 128, 0, st>>>(cu, n_rows, lookahead, step, act, m);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
@@ -532,37 +534,79 @@ int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, 
 //     outputs.scores has no entry for later positions);
 //   - first alive position where either candidate logit is >= the k-th largest logit wins;
 //   - otherwise the position-0 probabilities stand.
-__global__ void scan_update_kernel(const float* __restrict__ stats, int n, int pos, int topk, int eos_id,
-                                   int scan_positions, int gen_tokens, ScanState s) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float* r = stats + static_cast<size_t>(i) * LMH_STATS;
-  const int arg = reinterpret_cast<const int*>(r)[15];
-  int alive = (pos == 0) ? 1 : s.alive[i];
-  int resolved = (pos == 0) ? 0 : s.resolved[i];
-  if (alive && !resolved && pos < scan_positions) {
-    const float lse = r[0], la = r[7], lb = r[8], kth = r[topk];   // r[1..5] = top1..top5
-    const float pa = expf(la - lse), pb = expf(lb - lse);
-    const bool hit = (la >= kth) || (lb >= kth);
-    if (pos == 0 || hit) {
-      float* o = s.out + static_cast<size_t>(i) * 8;
-      o[0] = pa; o[1] = pb; o[2] = pa / (pa + pb); o[3] = lse; o[4] = la; o[5] = lb;
-      o[6] = static_cast<float>(pos); o[7] = hit ? 1.f : 0.f;
+// The same pass compacts the look-ahead: the prompts that need another position (unresolved and alive; in completion
+// mode every prompt that has not produced EOS) are written in ascending order to act_out with their next token and
+// candidate pair, so the next one-token step runs exactly those rows.  One CTA walks the rows in chunks of its size
+// (a batch holds a few thousand prompts; the work per row is a dozen loads) and keeps the running count, which makes
+// the order stable without a second kernel.
+// A prompt whose logits are not finite at a position it is scored on (an fp16 activation overflowed somewhere in the
+// decoder) gets an all-NaN row with found = -1, is counted in n_active[1] and takes no further steps.
+constexpr int SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_update_kernel(const float* __restrict__ stats, int n_rows, int pos, int topk, int eos_id,
+                   int scan_positions, int gen_tokens, ScanState s) {
+  __shared__ int warp_tot[SCAN_THREADS / 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int base = 0, bad_total = 0;
+  for (int c0 = 0; c0 < n_rows; c0 += SCAN_THREADS) {
+    const int r = c0 + threadIdx.x;
+    int need = 0, i = 0, arg = 0, bad = 0;
+    if (r < n_rows) {
+      i = s.act_in ? s.act_in[r] : r;
+      const float* q = stats + static_cast<size_t>(r) * LMH_STATS;
+      arg = reinterpret_cast<const int*>(q)[15];
+      int alive = (pos == 0) ? 1 : s.alive[i];
+      int resolved = (pos == 0) ? 0 : s.resolved[i];
+      if (alive && !resolved && pos < scan_positions) {
+        const float lse = q[0], la = q[7], lb = q[8], kth = q[topk];   // q[1..5] = top1..top5
+        float* o = s.out + static_cast<size_t>(i) * 8;
+        if (!(isfinite(lse) && isfinite(la) && isfinite(lb))) {
+          const float nan = __int_as_float(0x7fc00000);
+          o[0] = nan; o[1] = nan; o[2] = nan; o[3] = nan; o[4] = nan; o[5] = nan; o[6] = static_cast<float>(pos); o[7] = -1.f;
+          resolved = 1; alive = 0; bad = 1;
+        } else {
+          const float pa = expf(la - lse), pb = expf(lb - lse);
+          const bool hit = (la >= kth) || (lb >= kth);
+          if (pos == 0 || hit) {
+            o[0] = pa; o[1] = pb; o[2] = pa / (pa + pb); o[3] = lse; o[4] = la; o[5] = lb;
+            o[6] = static_cast<float>(pos); o[7] = hit ? 1.f : 0.f;
+          }
+          if (hit) resolved = 1;
+        }
+      }
+      if (s.gen_ids) s.gen_ids[static_cast<size_t>(i) * gen_tokens + pos] = alive ? arg : -1;
+      s.next_tok[i] = arg;
+      if (alive && arg == eos_id) alive = 0;
+      s.alive[i] = alive; s.resolved[i] = resolved;
+      // another step is needed while a prompt is unresolved (scoring only), or, in completion mode (gen_tokens >
+      // scan_positions: the reference's max_new_tokens=50), while it has not produced EOS
+      need = (alive && (gen_tokens > scan_positions ? pos + 1 < gen_tokens : !resolved)) ? 1 : 0;
     }
-    if (hit) resolved = 1;
+    const unsigned ballot = __ballot_sync(0xffffffffu, need != 0);
+    const unsigned bad_ballot = __ballot_sync(0xffffffffu, bad != 0);
+    __syncthreads();                       // warp_tot of the previous chunk has been read by everyone
+    if (lane == 0) warp_tot[w] = __popc(ballot) | (__popc(bad_ballot) << 16);
+    __syncthreads();
+    int before = 0, total = 0;
+    for (int k = 0; k < SCAN_THREADS / 32; ++k) {
+      const int t = warp_tot[k];
+      if (k < w) before += t & 0xffff;
+      total += t & 0xffff;
+      bad_total += t >> 16;
+    }
+    if (need) {
+      const int o = base + before + __popc(ballot & ((1u << lane) - 1u));
+      s.act_out[o] = i; s.tok_out[o] = arg;
+      s.cand_out[2 * o] = s.cand[2 * i]; s.cand_out[2 * o + 1] = s.cand[2 * i + 1];
+    }
+    base += total;
   }
-  if (s.gen_ids) s.gen_ids[static_cast<size_t>(i) * gen_tokens + pos] = alive ? arg : -1;
-  s.next_tok[i] = arg;
-  if (alive && arg == eos_id) alive = 0;
-  s.alive[i] = alive; s.resolved[i] = resolved;
-  // another step is needed while a prompt is unresolved (scoring only), or, in completion mode (gen_tokens >
-  // scan_positions: the reference's max_new_tokens=50), while it has not produced EOS
-  if (alive && (gen_tokens > scan_positions ? pos + 1 < gen_tokens : !resolved)) atomicAdd(s.n_active, 1);
+  if (threadIdx.x == 0) { s.n_active[0] = base; if (bad_total) atomicAdd(s.n_active + 1, bad_total); }
 }
 
-int launch_scan_update(const float* stats, int n, int pos, int topk, int eos_id, int scan_positions, int gen_tokens,
+int launch_scan_update(const float* stats, int n_rows, int pos, int topk, int eos_id, int scan_positions, int gen_tokens,
                        const ScanState& s, cudaStream_t st) {
-  scan_update_kernel<<<static_cast<unsigned>(ceil_div(n, 128)), 128, 0, st>>>(stats, n, pos, topk, eos_id, scan_positions, gen_tokens, s);
+  scan_update_kernel<<<1, SCAN_THREADS, 0, st>>>(stats, n_rows, pos, topk, eos_id, scan_positions, gen_tokens, s);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }

@@ -60,11 +60,19 @@ struct ScanState {
   int32_t* resolved;   // [N]
   int32_t* next_tok;   // [N] greedy token = input of the next decode step
   int32_t* gen_ids;    // [N, lookahead] or null
-  int32_t* n_active;   // [1] prompts still needing another position
+  int32_t* n_active;   // [2]: prompts still needing another position; prompts whose logits were not finite (this call)
   float* out;          // [N, 8]
+  // Compaction of the look-ahead: row r of a one-token step is prompt act_in[r] (null: row == prompt).  The scan writes
+  // the prompts that need another position, in ascending order, with their next input token and candidate pair.
+  const int32_t* act_in;   // [rows of this step] or null
+  int32_t* act_out;        // [N]
+  int32_t* tok_out;        // [N]
+  int32_t* cand_out;       // [N, 2]
+  const int32_t* cand;     // [N, 2] candidate ids per prompt
 };
 
-int launch_prep(const int32_t* cu, int n_seqs, int lookahead, int step, const BatchMeta& m, cudaStream_t st);
+// step 0: prefill bookkeeping for n_rows = all prompts.  step >= 1: one row per prompt of `act` (null: every prompt).
+int launch_prep(const int32_t* cu, int n_rows, int lookahead, int step, const int32_t* act, const BatchMeta& m, cudaStream_t st);
 template <typename AT, typename WT> int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);

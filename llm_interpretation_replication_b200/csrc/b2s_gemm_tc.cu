@@ -13,7 +13,9 @@
 // MMAs of tile i+1.  Tiles are rasterised in groups of GROUP_M row-blocks so that the CTAs running at
 // the same time share A/W boxes in L2.
 #include "b2s_tc.cuh"
+#include <atomic>
 #include <mutex>
+#include <unordered_map>
 #include <vector>
 #include <stdarg.h>
 
@@ -923,9 +925,37 @@ static int get_encode_fn() {
   return B2S_OK;
 }
 
+// Encoded maps are pure functions of their arguments (no device state), and a scoring call asks for the same few
+// hundred of them over and over (32 layers x 4 weights, a handful of activation buffers, a few row counts), so they are
+// memoised: cuTensorMapEncodeTiled costs about as much as a kernel launch, and a one-token step is launch-bound.
+struct TmapKey {
+  const void* base; uint64_t rows, cols, pitch; uint32_t box_rows, box_cols; int esize, f16;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && rows == o.rows && cols == o.cols && pitch == o.pitch && box_rows == o.box_rows &&
+           box_cols == o.box_cols && esize == o.esize && f16 == o.f16;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = reinterpret_cast<uint64_t>(k.base) * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (k.cols * 1315423911ull + k.pitch + (h << 6) + (h >> 2));
+    h ^= (static_cast<uint64_t>(k.box_rows) << 32 | k.box_cols) + static_cast<uint64_t>(k.esize * 2 + k.f16) + (h << 6) + (h >> 2);
+    return static_cast<size_t>(h);
+  }
+};
+static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+static std::mutex g_tmap_mutex;
+
 int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
                  uint32_t box_rows, uint32_t box_cols, int esize, int f16) {
   B2S_TRY(get_encode_fn());
+  const TmapKey key{base, rows, cols, pitch_bytes, box_rows, box_cols, esize, f16};
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mutex);
+    auto it = g_tmap_cache.find(key);
+    if (it != g_tmap_cache.end()) { *map = it->second; return B2S_OK; }
+  }
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {pitch_bytes};
   cuuint32_t box[2] = {box_cols, box_rows};
@@ -940,6 +970,11 @@ int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t col
               static_cast<unsigned long long>(pitch_bytes), base);
     return B2S_ECUDA;
   }
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mutex);
+    if (g_tmap_cache.size() > 16384) g_tmap_cache.clear();   // callers that keep changing buffers must not grow it forever
+    g_tmap_cache.emplace(key, *map);
+  }
   return B2S_OK;
 }
 
@@ -953,9 +988,20 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uin
   return make_tmap_bf16_2d(map, base, rows, cols, cols * 2, box_rows, BK, f16);
 }
 
-static int g_num_sms = 0;
+// Per-device facts (function attributes and the SM count belong to a device, and one process may drive several).
+static constexpr int MAX_DEVICES = 64;
+static int g_num_sms_dev[MAX_DEVICES] = {0};
+static int current_device_sms(int* dev_out, int* sms_out) {
+  int dev = 0;
+  B2S_CHECK_CUDA(cudaGetDevice(&dev));
+  B2S_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "gemm: device ordinal %d outside [0, %d)", dev, MAX_DEVICES);
+  if (g_num_sms_dev[dev] == 0) B2S_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms_dev[dev], cudaDevAttrMultiProcessorCount, dev));
+  *dev_out = dev; *sms_out = g_num_sms_dev[dev];
+  return B2S_OK;
+}
 extern int g_opt_attn_hold_s;
 extern int g_opt_attn_ts;
+extern int g_opt_compact;
 int g_opt_tma_store = 1;   // 1: epilogue via shared memory + TMA bulk store / reduce-add; 0: per-thread global stores
 int g_opt_hint = 0;        // TMA L2 cache hints: 0 none, 1 A evict_first + W evict_last, 2 A evict_last + W evict_first, 3 both evict_last
 int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = rule off; b2s_set_option "gemm_small_w_group")
@@ -965,7 +1011,12 @@ int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = ru
 // column tile: batch-invariant, but CTAs that share an A row-block no longer walk K together: -1 %.
 int g_opt_policy = 1;        // b2s_set_option "gemm_policy" (see launch_epi)
 int g_opt_wave_sync = 4;     // b2s_set_option "gemm_wave_sync": all producers meet every N tiles (0 = never)
-static __device__ int g_wave_counters[8192];
+// Meeting counters: one table per device (a __device__ array exists once on every GPU that loads the library).  Each
+// launch takes its own slice at a rotating offset, so GEMMs that overlap on one device (several streams or host
+// threads) count in different slots; the table holds the slices of some hundreds of launches before it wraps.
+static constexpr int WAVE_TABLE = 65536;
+static __device__ int g_wave_counters[WAVE_TABLE];
+static std::atomic<unsigned> g_wave_cursor{0};
 int g_opt_pair_stride = 1;   // b2s_set_option "gemm_pair_stride" (experiment; must be coprime to the number of CTA pairs)
 int g_opt_serp = 0;
 int g_opt_group_m = 0;     // 0: heuristic below; otherwise forced (b2s_set_option "gemm_group_m")
@@ -992,24 +1043,31 @@ static cudaEvent_t prof_event() {
 static int arm_wave_sync(GemmParams& q, int tiles, int pairs, cudaStream_t st) {
   if (g_opt_wave_sync <= 0) return B2S_OK;
   const int waves = static_cast<int>(ceil_div(tiles, pairs));
-  if (waves <= g_opt_wave_sync || waves / g_opt_wave_sync + 1 > 8192) return B2S_OK;   // no meeting would happen / table too small
+  const int need = waves / g_opt_wave_sync + 1;
+  if (waves <= g_opt_wave_sync || need > WAVE_TABLE / 4) return B2S_OK;   // no meeting would happen / table too small
   int* ctr = nullptr;
-  B2S_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ctr), g_wave_counters));
-  B2S_CHECK_CUDA(cudaMemsetAsync(ctr, 0, sizeof(int) * (waves / g_opt_wave_sync + 1), st));
-  q.wave_sync = ctr; q.wave_sync_every = g_opt_wave_sync;
+  B2S_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ctr), g_wave_counters));   // address on the current device
+  unsigned at = g_wave_cursor.fetch_add(static_cast<unsigned>(need)) % WAVE_TABLE;
+  if (at + need > WAVE_TABLE) at = 0;                                      // slices never straddle the end of the table
+  B2S_CHECK_CUDA(cudaMemsetAsync(ctr + at, 0, sizeof(int) * need, st));
+  q.wave_sync = ctr + at; q.wave_sync_every = g_opt_wave_sync;
   return B2S_OK;
 }
 
 template <int EPI>
 static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tb2, const CUtensorMap& ta3,
                       const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  int dev = 0, num_sms = 0;
+  B2S_TRY(current_device_sms(&dev, &num_sms));
+  static bool attr_set[MAX_DEVICES] = {false};   // the dynamic shared memory opt-in is a per-device function attribute
+  if (!attr_set[dev]) {
     B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set = true;
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc3_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3_BYTES));
+    attr_set[dev] = true;
   }
   const int tiles = p.tiles_m * p.tiles_n;
-  const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+  const int grid = tiles < num_sms ? tiles : num_sms;
   if (g_prof.on) cudaEventRecord(prof_event(), st);
   // Tiling policy (gemm_cta_group 0).  Under the 1 kW power cap the variants trade clock for tensor-pipe utilisation
   // (profiles/r1_gemm_power.md).  Since the wave meeting keeps the CTA-pair kernels' panels in L2 they win everywhere:
@@ -1024,29 +1082,19 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
   }
   const bool big = (cg == 3 && p.M >= 4096) || cg == 4;   // 4 = always (tests)
   if (big) {
-    static bool attr3_set = false;
-    if (!attr3_set) {
-      B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc3_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM3_BYTES));
-      attr3_set = true;
-    }
     const int tiles3 = static_cast<int>(ceil_div(p.M, BM3)) * p.tiles_n;
-    int pairs = g_num_sms / 2;
+    int pairs = num_sms / 2;
     if (tiles3 < pairs) pairs = tiles3;
     GemmParams q = p;
-    if (pairs != g_num_sms / 2) q.pair_stride = 1;   // the permutation is only a bijection on the full grid
+    if (pairs != num_sms / 2) q.pair_stride = 1;   // the permutation is only a bijection on the full grid
     B2S_TRY(arm_wave_sync(q, tiles3, pairs, st));
     gemm_tc3_kernel<EPI><<<2 * pairs, NUM_THREADS3, SMEM3_BYTES, st>>>(ta3, tb2, tc, q);
   } else if (cg >= 2) {
-    static bool attr2_set = false;
-    if (!attr2_set) {
-      B2S_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2_BYTES));
-      attr2_set = true;
-    }
     const int tiles2 = static_cast<int>(ceil_div(p.M, BM2)) * p.tiles_n;
-    int pairs = g_num_sms / 2;
+    int pairs = num_sms / 2;
     if (tiles2 < pairs) pairs = tiles2;
     GemmParams q = p;
-    if (pairs != g_num_sms / 2) q.pair_stride = 1;
+    if (pairs != num_sms / 2) q.pair_stride = 1;
     B2S_TRY(arm_wave_sync(q, tiles2, pairs, st));
     gemm_tc2_kernel<EPI><<<2 * pairs, NUM_THREADS, SMEM2_BYTES, st>>>(ta, tb2, tc, q);
   } else {
@@ -1070,11 +1118,8 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   B2S_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0 &&
                   (reinterpret_cast<uintptr_t>(out) & 15) == 0,
               "gemm_bf16: operands must be 16-byte aligned");
-  if (g_num_sms == 0) {
-    int dev = 0;
-    B2S_CHECK_CUDA(cudaGetDevice(&dev));
-    B2S_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  int dev = 0, num_sms = 0;
+  B2S_TRY(current_device_sms(&dev, &num_sms));
   CUtensorMap ta, tb, tb2, ta3;
   B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM, act_f16));
   B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN, act_f16));
@@ -1100,7 +1145,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     p.wave_sync = nullptr; p.wave_sync_every = 0;
     p.pair_stride = 1;
     {
-      const int np = g_num_sms / 2;
+      const int np = num_sms / 2;
       int a = g_opt_pair_stride, b = np;
       while (b) { const int t = a % b; a = b; b = t; }
       if (g_opt_pair_stride > 1 && a == 1) p.pair_stride = g_opt_pair_stride;
@@ -1152,6 +1197,10 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_cta_group") {
     B2S_REQUIRE(value >= 0 && value <= 4, "set_option: gemm_cta_group must be 0..4");
     b2s::g_opt_cta_group = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "lookahead_compact") {
+    b2s::g_opt_compact = value ? 1 : 0;
     return B2S_OK;
   }
   if (std::string(name) == "attn_ts") {

@@ -11,7 +11,8 @@
 namespace b2s {
 
 thread_local std::string g_last_error;
-int64_t g_launch_count = 0;
+std::atomic<int64_t> g_launch_count{0};
+int g_opt_compact = 1;   // b2s_set_option "lookahead_compact": one-token steps run only the prompts that still need a position
 
 void set_error(const char* fmt, ...) {
   char buf[1024];
@@ -45,6 +46,7 @@ namespace {
 struct Workspace {
   BatchMeta meta;
   int32_t *tokens, *cu, *cand, *gen;
+  int32_t *alist[2], *tok_step, *cand_step;   // look-ahead compaction: active prompt lists (ping-pong), their tokens and candidates
   float* out;
   ScanState scan;
   float* resid;
@@ -84,6 +86,10 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.scan.resolved = reinterpret_cast<int32_t*>(take(4 * N));
   w.scan.next_tok = reinterpret_cast<int32_t*>(take(4 * N));
   w.scan.n_active = reinterpret_cast<int32_t*>(take(256));
+  w.alist[0] = reinterpret_cast<int32_t*>(take(4 * N));
+  w.alist[1] = reinterpret_cast<int32_t*>(take(4 * N));
+  w.tok_step = reinterpret_cast<int32_t*>(take(4 * N));
+  w.cand_step = reinterpret_cast<int32_t*>(take(8 * N));
   w.scan.gen_ids = nullptr;
   w.scan.out = nullptr;
   w.resid = reinterpret_cast<float*>(take(4 * rows * d.d_model));
@@ -253,9 +259,7 @@ const char* b2s_last_error(void) { return g_last_error.c_str(); }
 int b2s_abi_version(void) { return B2S_ABI_VERSION; }
 
 int64_t b2s_launch_count(int32_t reset) {
-  const int64_t v = g_launch_count;
-  if (reset) g_launch_count = 0;
-  return v;
+  return reset ? g_launch_count.exchange(0) : g_launch_count.load();
 }
 
 int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs, int32_t n_ptrs, int32_t device,
@@ -373,21 +377,29 @@ int b2s_score_complete(b2s_model* m, const int32_t* tokens, const int32_t* cu_se
   // numbers (0 * NaN would poison P.V), so the cache starts from zeros on every call.
   B2S_CHECK_CUDA(cudaMemsetAsync(w.kcache, 0, w.cache_layer_bytes * m->d.n_layer, st));
   B2S_CHECK_CUDA(cudaMemsetAsync(w.vcache, 0, w.cache_layer_bytes * m->d.n_layer, st));
-  B2S_TRY(launch_prep(cu_seqlens, n_seqs, gen_tokens, 0, w.meta, st));
+  B2S_TRY(launch_prep(cu_seqlens, n_seqs, gen_tokens, 0, nullptr, w.meta, st));
   B2S_TRY(forward(m, w, tokens, total_tokens, n_seqs, max_seqlen, max_seqlen, st));
   B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
-  B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
+  B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 8, st));
+  const bool compact = g_opt_compact != 0;
+  w.scan.cand = cand_ids; w.scan.tok_out = w.tok_step; w.scan.cand_out = w.cand_step;
+  w.scan.act_in = nullptr; w.scan.act_out = w.alist[0];
   B2S_TRY(launch_scan_update(w.stats, n_seqs, 0, topk, eos_id, scan_positions, gen_tokens, w.scan, st));
   for (int step = 1; step < gen_tokens; ++step) {
+    // The number of prompts that need another position sizes every launch of the step (grids, tensor maps), so it
+    // is read back: 4 bytes and one stream synchronisation per position, after which the step's ~200 launches are
+    // enqueued while the GPU is already working on the first of them.
     int32_t active = 0;
     B2S_CHECK_CUDA(cudaMemcpyAsync(&active, w.scan.n_active, 4, cudaMemcpyDeviceToHost, st));
     B2S_CHECK_CUDA(cudaStreamSynchronize(st));
     if (active == 0) break;
-    B2S_TRY(launch_prep(cu_seqlens, n_seqs, gen_tokens, step, w.meta, st));
-    B2S_TRY(forward(m, w, w.scan.next_tok, n_seqs, n_seqs, max_seqlen + step, 1, st));
-    B2S_TRY(lm_head(m, w, cand_ids, n_seqs, st));
-    B2S_CHECK_CUDA(cudaMemsetAsync(w.scan.n_active, 0, 4, st));
-    B2S_TRY(launch_scan_update(w.stats, n_seqs, step, topk, eos_id, scan_positions, gen_tokens, w.scan, st));
+    const int rows = compact ? active : n_seqs;
+    const int32_t* act = compact ? w.alist[(step - 1) & 1] : nullptr;
+    B2S_TRY(launch_prep(cu_seqlens, rows, gen_tokens, step, act, w.meta, st));
+    B2S_TRY(forward(m, w, compact ? w.tok_step : w.scan.next_tok, rows, rows, max_seqlen + step, 1, st));
+    B2S_TRY(lm_head(m, w, compact ? w.cand_step : cand_ids, rows, st));
+    w.scan.act_in = act; w.scan.act_out = w.alist[step & 1];
+    B2S_TRY(launch_scan_update(w.stats, rows, step, topk, eos_id, scan_positions, gen_tokens, w.scan, st));
   }
   return B2S_OK;
 }
@@ -435,7 +447,14 @@ int b2s_score_complete_host(b2s_model* m, const int32_t* tokens_h, const int32_t
   B2S_CHECK_CUDA(cudaMemcpyAsync(out_h, w.out, 32 * static_cast<size_t>(n_seqs), cudaMemcpyDeviceToHost, st));
   if (gen_h)
     B2S_CHECK_CUDA(cudaMemcpyAsync(gen_h, w.gen, 4 * static_cast<size_t>(n_seqs) * gen_tokens, cudaMemcpyDeviceToHost, st));
+  int32_t not_finite = 0;
+  B2S_CHECK_CUDA(cudaMemcpyAsync(&not_finite, w.scan.n_active + 1, 4, cudaMemcpyDeviceToHost, st));
   B2S_CHECK_CUDA(cudaStreamSynchronize(st));
+  if (not_finite > 0) {   // the rows are all there (NaN, found = -1 for the affected prompts); the caller decides what to do with them
+    set_error("score_host: %d of %d prompts produced non-finite logits%s", not_finite, n_seqs,
+              m->act_f16 ? " (an fp16 activation overflowed; rerun this model in a bf16 mode)" : "");
+    return B2S_ERANGE;
+  }
   return B2S_OK;
 }
 

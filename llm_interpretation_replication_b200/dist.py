@@ -45,7 +45,7 @@ def gather_rows(local_rows: torch.Tensor, local_index: Sequence[int], n_total: i
     return result
 
 
-def score_ids_sharded(scorer, id_lists, cand, topk, max_lookahead, eos_id, group=None, gen_tokens=None):
+def score_ids_sharded(scorer, id_lists, cand, topk, max_lookahead, eos_id, group=None, gen_tokens=None, nonfinite="nan"):
     """Each rank scores its shard of already-tokenised prompts on its own GPU; one all-gather returns every
     prompt's row (and greedy tokens) to every rank, in the callers' order."""
     import torch.distributed as dist
@@ -55,7 +55,7 @@ def score_ids_sharded(scorer, id_lists, cand, topk, max_lookahead, eos_id, group
     lens = [len(x) for x in id_lists]
     mine = shard_prompts(lens, world)[rank]
     rows, gens = scorer.score_ids([id_lists[i] for i in mine], cand[mine], topk=topk, max_lookahead=max_lookahead,
-                                  eos_id=eos_id, gen_tokens=gen_tokens)
+                                  eos_id=eos_id, gen_tokens=gen_tokens, nonfinite=nonfinite)
     dev = scorer.device
     local = torch.cat([torch.from_numpy(rows), torch.from_numpy(gens.astype(np.float32))], dim=1).to(dev)
     full = gather_rows(local, mine, len(id_lists), world, group=g).cpu().numpy()

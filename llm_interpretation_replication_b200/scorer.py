@@ -184,11 +184,15 @@ class Scorer:
                        "b2s_score")
 
     def score_ids(self, id_lists: Sequence[Sequence[int]], cand_pairs, topk: int = 5,
-                  max_lookahead: int = MAX_LOOK_AHEAD, eos_id: Optional[int] = None, gen_tokens: Optional[int] = None):
+                  max_lookahead: int = MAX_LOOK_AHEAD, eos_id: Optional[int] = None, gen_tokens: Optional[int] = None,
+                  nonfinite: str = "raise"):
         """Score already-tokenised prompts.  Returns (rows [N,8] float32, gen_ids [N,G] int32) in the callers' order.
         rows: p_a, p_b, rel, lse, logit_a, logit_b, pos_found, found.  G = ``max_lookahead``, or ``gen_tokens`` when
         given: the reference's max_new_tokens (50), generated for every prompt up to EOS while only the first
-        ``max_lookahead`` positions are scanned (run_base_vs_instruct_100q.py:338-363)."""
+        ``max_lookahead`` positions are scanned (run_base_vs_instruct_100q.py:338-363).
+        A prompt whose logits are not finite (an fp16 activation overflowed) never comes back as a number: with
+        ``nonfinite="raise"`` a :class:`B2SRangeError` is raised once all batches ran, with ``"nan"`` its row is kept as
+        NaN with found = -1 (the reference's NaN-row policy)."""
         N = len(id_lists)
         G = max_lookahead if gen_tokens is None else int(gen_tokens)
         if G < max_lookahead:
@@ -210,13 +214,19 @@ class Scorer:
             raise ValueError(f"max_lookahead / gen_tokens {G} > workspace limit {self.max_lookahead}")
         rows = np.zeros((N, 8), np.float32)
         gens = np.full((N, G), -1, np.int32)
+        range_error = None
         for batch in plan_batches(lens, self.max_tokens, self.max_seqs):
             t_tok, t_cu, t_cand, _ = self.pack([id_lists[i] for i in batch], cand[batch])
             out = torch.empty((len(batch), 8), dtype=torch.float32).pin_memory()
             gen = torch.empty((len(batch), G), dtype=torch.int32).pin_memory()
-            self.score_batch_host(t_tok, t_cu, t_cand, topk, max_lookahead, eos, out, gen, gen_tokens=G)
+            try:
+                self.score_batch_host(t_tok, t_cu, t_cand, topk, max_lookahead, eos, out, gen, gen_tokens=G)
+            except _lib.B2SRangeError as e:      # rows were copied back; the affected ones are NaN with found = -1
+                range_error = e
             rows[batch] = out.numpy()
             gens[batch] = gen.numpy()
+        if range_error is not None and nonfinite == "raise":
+            raise range_error
         return rows, gens
 
 
@@ -283,12 +293,15 @@ def score_prompts(scorer: Scorer, tokenizer, prompts: Sequence[str], variant: st
                                            eos_id=tokenizer.eos_token_id, group=shard_group, gen_tokens=gen_tokens)
         else:
             rows, gens = scorer.score_ids(ids, cand, topk=V["topk"], max_lookahead=max_lookahead,
-                                          eos_id=tokenizer.eos_token_id, gen_tokens=gen_tokens)
+                                          eos_id=tokenizer.eos_token_id, gen_tokens=gen_tokens, nonfinite="nan")
     except Exception as e:   # reference error policy: NaN rows, sweep continues
         if variant != "100q":
             raise
         return [_nan_dict(variant, p, e) for p in prompts]
-    return [_row_to_dict(rows[i], gens[i], variant, prompts[i], tokenizer) for i in range(len(prompts))]
+    # found = -1: the logits of this prompt were not finite (fp16 overflow) -- the reference's NaN row, never a number
+    return [_row_to_dict(rows[i], gens[i], variant, prompts[i], tokenizer) if rows[i][7] >= 0
+            else _nan_dict(variant, prompts[i], ArithmeticError("non-finite logits (activation overflow in the 16-bit mode)"))
+            for i in range(len(prompts))]
 
 
 def get_yes_no_logprobs(model: Scorer, tokenizer, prompt: str, device=None, variant: str = "100q") -> dict:
