@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define B2S_ABI_VERSION 3
+#define B2S_ABI_VERSION 4   /* 4: BF16_SPLIT mode, B2S_ERANGE, compacted look-ahead (gen_ids -1 at positions a prompt did not need) */
 
 #if defined(__GNUC__)
 #define B2S_API __attribute__((visibility("default")))
@@ -41,12 +41,19 @@ enum { B2S_MLP_GELU = 0, B2S_MLP_SWIGLU = 1 };      /* SwiGLU: down(silu(gate(x)
 enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQA, cat(q,k,v)_proj of the Llama family */,
        B2S_QKV_NEOX_INTERLEAVED = 1 /* per head [q, k, v] */ };
 /* compute modes (tensor-core modes: fp32 accumulation in TMEM, fp32 residual stream, LayerNorm and softmax):
- *   BF16_FAST   bf16 weight matrices; activations (every GEMM A operand, Q/K/V/P) rounded to bf16;
+ *   BF16_FAST   bf16 weight matrices; activations (every GEMM A operand, Q/K/V/P) rounded to bf16.  Fastest; at 32
+ *               layers its |delta relative_prob| sits at the bf16 noise floor (max ~3e-3: a share of the prompts misses
+ *               the 2e-3 gate);
  *   FP16        fp16 weight matrices (bf16 checkpoints convert exactly for |w| >= 2^-17) and activations rounded
  *               to fp16: 3 more mantissa bits at the same MMA rate (tcgen05 kind::f16 needs A and B alike, a
- *               mixed fp16 x bf16 MMA is an illegal instruction); the mode that holds the 2e-3 gate at 32 layers;
+ *               mixed fp16 x bf16 MMA is an illegal instruction); holds the 2e-3 gate at 32 layers.  fp16 overflows
+ *               beyond 65504: such prompts come back flagged (B2S_ERANGE, NaN rows), never as numbers;
+ *   BF16_SPLIT  bf16 weight matrices untouched; every GEMM A operand is kept as two bf16 halves hi = bf16(x),
+ *               lo = bf16(x - hi) (16 mantissa bits, bf16 range) and both halves meet the same weights in the same fp32
+ *               accumulator: holds the gate with bf16's range at twice the tensor work.  Q/K/V/P inside attention stay
+ *               bf16.  Needs d_model, d_ff and n_head*head_dim to be multiples of 64;
  *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5). */
-enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_FP32_CHECK = 3 };
+enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3 };
 
 /* weight_ptrs slots: 10 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
  * pointer must be 16-byte aligned (B2S_EINVAL otherwise) */
@@ -66,7 +73,7 @@ typedef struct {
   int32_t has_bias;
   int32_t qkv_layout;          /* B2S_QKV_* */
   int32_t max_pos;             /* rows of the rope cos/sin tables */
-  int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST expects bf16 matrices, FP16 fp16, FP32_CHECK fp32 */
+  int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST and BF16_SPLIT expect bf16 matrices, FP16 fp16, FP32_CHECK fp32 */
   int32_t norm_type;           /* B2S_NORM_*  (ABI 2) */
   int32_t mlp_type;            /* B2S_MLP_*   (ABI 2) */
   int32_t pos_type;            /* B2S_POS_*   (ABI 3) */

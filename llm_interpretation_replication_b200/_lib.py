@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200score.so")
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class B2SError(RuntimeError):

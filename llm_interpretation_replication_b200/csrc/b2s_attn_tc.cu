@@ -342,6 +342,7 @@ int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slot
     return launch_attn_dec2(a, n_seqs, total_rows, cache_slots, st);                                          // one-token steps: small CTAs
   B2S_REQUIRE(!decode || attn_tc_decode_supported(a.hd, a.max_kv, a.qkv_dim, a.q_base, a.q_hstride),
               "attn_tc: one-token mode needs contiguous 64-wide query heads");
+  B2S_REQUIRE(!a.split, "attn_tc: the first-generation kernel (attn_ts = 0) does not write split outputs");
   // per-device function attribute, and cheap: set on every launch rather than once per process
   B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
   B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));

@@ -31,7 +31,8 @@ static constexpr uint32_t A2_TMEM_COLS = 512;
 
 struct Attn2Params {
   BatchMeta meta;
-  uint16_t* out;          // [T, nh*64] 16-bit
+  uint16_t* out;          // [T, nh*64] 16-bit ([T, 2*nh*64] = hi | lo when split)
+  int split;              // BF16_SPLIT: also store the bf16 rounding remainders nh*64 elements after the values
   int nh, nkv, rep;
   int q_base, q_hstride;
   float scale_log2e;
@@ -108,7 +109,7 @@ __device__ __forceinline__ bool a2_test(uint32_t bar, uint32_t parity) {   // no
 template <bool F16>
 __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_live, int n_full, int n_p, int kvp, int limit, float sc,
                                         uint32_t bar_s, uint32_t bar_p, uint32_t bar_o, uint32_t bar_e, uint32_t ph, bool valid,
-                                        uint16_t* out_row) {
+                                        uint16_t* out_row, int lo_off = 0) {
   const uint32_t t_o = t_lane + o_off;
   a2_wait(bar_s, ph);
   tcgen05_fence_after();
@@ -179,6 +180,20 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
     for (int q = 0; q < 4; ++q)
       dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
                               pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
+    if constexpr (!F16) {
+      if (lo_off) {      // BF16_SPLIT: the dense projection reads [hi | lo]; lo = bf16(o - bf16(o))
+        uint4* dlo = reinterpret_cast<uint4*>(out_row + lo_off);
+        auto rem = [inv](float x) { const float y = x * inv; return y - __bfloat162float(__float2bfloat16_rn(y)); };
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          dlo[q] = make_uint4(pack_bf16x2(rem(o0[8 * q]), rem(o0[8 * q + 1])), pack_bf16x2(rem(o0[8 * q + 2]), rem(o0[8 * q + 3])),
+                              pack_bf16x2(rem(o0[8 * q + 4]), rem(o0[8 * q + 5])), pack_bf16x2(rem(o0[8 * q + 6]), rem(o0[8 * q + 7])));
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          dlo[4 + q] = make_uint4(pack_bf16x2(rem(o1[8 * q]), rem(o1[8 * q + 1])), pack_bf16x2(rem(o1[8 * q + 2]), rem(o1[8 * q + 3])),
+                                  pack_bf16x2(rem(o1[8 * q + 4]), rem(o1[8 * q + 5])), pack_bf16x2(rem(o1[8 * q + 6]), rem(o1[8 * q + 7])));
+      }
+    }
   }
 }
 
@@ -308,8 +323,10 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const float sc = p.scale_log2e;
     for (int i = l; i < n_items; i += nl) {
       const uint32_t ph = static_cast<uint32_t>(i / nl) & 1u;
-      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (static_cast<size_t>(p.nh) * A2_HD) + static_cast<size_t>(h_first + i) * A2_HD;
-      a2_item<F16>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst);
+      const size_t owidth = static_cast<size_t>(p.nh) * A2_HD;
+      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (owidth << p.split) + static_cast<size_t>(h_first + i) * A2_HD;
+      a2_item<F16>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst,
+                   p.split ? static_cast<int>(owidth) : 0);
     }
   }
 
@@ -331,6 +348,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 struct AttnDec2Params {
   BatchMeta meta;
   uint16_t* out;
+  int split;              // as in Attn2Params
   int nh, nkv, rep;
   int q_base;             // column of head 0 in the qkv row (multiple of 64)
   int qrows_per_token;    // qkv_dim / 64
@@ -418,10 +436,10 @@ attn_dec2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const int n_p = (kvp + 31) / 32;
     for (int i = 0; i < n_items; ++i) {
       const bool valid = row < min(A2_BM, p.rep - i * A2_BM);
-      uint16_t* dst = p.out + static_cast<size_t>(q0) * (static_cast<size_t>(p.nh) * A2_HD) +
-                      static_cast<size_t>(h_first + i * A2_BM + row) * A2_HD;
+      const size_t owidth = static_cast<size_t>(p.nh) * A2_HD;
+      uint16_t* dst = p.out + static_cast<size_t>(q0) * (owidth << p.split) + static_cast<size_t>(h_first + i * A2_BM + row) * A2_HD;
       a2_item<F16>(t_lane, O_OFF, n_live, n_full, n_p, kvp, limit, p.scale_log2e, bar_s, bar_p, bar_o, bar_e,
-                   static_cast<uint32_t>(i) & 1u, valid, dst);
+                   static_cast<uint32_t>(i) & 1u, valid, dst, p.split ? static_cast<int>(owidth) : 0);
     }
   }
 
@@ -446,6 +464,7 @@ static int launch_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_
   AttnDec2Params p;
   p.meta = a.meta;
   p.out = reinterpret_cast<uint16_t*>(a.out);
+  p.split = a.split ? 1 : 0;
   p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
   p.q_base = a.q_base;
   p.qrows_per_token = a.qkv_dim / A2_HD;
@@ -481,6 +500,7 @@ int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slo
   Attn2Params p;
   p.meta = a.meta;
   p.out = reinterpret_cast<uint16_t*>(a.out);
+  p.split = a.split ? 1 : 0;
   p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
   p.q_base = a.q_base; p.q_hstride = a.q_hstride;
   p.scale_log2e = a.scale * 1.4426950408889634f;

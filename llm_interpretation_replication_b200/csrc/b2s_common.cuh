@@ -75,8 +75,11 @@ struct RopeEpiArgs {
 };
 
 // act_f16: A, W and the 16-bit outputs are fp16 instead of bf16 (tcgen05 kind::f16 needs both operands alike)
+// a_split: A is [M, 2K] bf16 = [hi | lo] halves of the activations (BF16_SPLIT mode; both halves meet the same W, fp32
+// accumulate); out_split: a 16-bit store epilogue writes its result in that form, [M, 2N], for the GEMM that follows.
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K,
-                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0, const RopeEpiArgs* rope = nullptr);
+                   int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0, const RopeEpiArgs* rope = nullptr,
+                   int a_split = 0, int out_split = 0);
 int gemm_f32_launch(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
                     int epilogue, cudaStream_t st);
 

@@ -3,6 +3,7 @@
 // scan state machine.  All HBM-bound; templated on the activation type
 // (bf16 in BF16_FAST mode, float in FP32_CHECK mode).
 #include "b2s_decoder.cuh"
+#include <type_traits>
 
 namespace b2s {
 
@@ -56,6 +57,15 @@ __device__ __forceinline__ void store4(__nv_bfloat16* p, float a, float b, float
 __device__ __forceinline__ void store4(__half* p, float a, float b, float c, float d) {
   *reinterpret_cast<uint2*>(p) = make_uint2(pack_f16x2(a, b), pack_f16x2(c, d));
 }
+// store four values; with lo_off != 0 (BF16_SPLIT, bf16 only) also the rounding remainders lo_off elements further on
+__device__ __forceinline__ float bf16_rem(float x) { return x - __bfloat162float(__float2bfloat16_rn(x)); }
+template <typename T>
+__device__ __forceinline__ void store4s(T* p, float a, float b, float c, float d, int lo_off) {
+  store4(p, a, b, c, d);
+  if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+    if (lo_off) store4(p + lo_off, bf16_rem(a), bf16_rem(b), bf16_rem(c), bf16_rem(d));
+  }
+}
 __device__ __forceinline__ float block_sum(float v, float* red) {
   v = warp_sum(v);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -105,8 +115,9 @@ ln_kernel(LnArgs a) {
     sq += (c0 * c0 + c1 * c1) + (c2 * c2 + c3 * c3);
   }
   const float rstd = rsqrtf(block_sum(sq, red) / d + a.eps);
-  AT* y1 = reinterpret_cast<AT*>(a.y1) + static_cast<size_t>(orow) * d;
-  AT* y2 = a.y2 ? reinterpret_cast<AT*>(a.y2) + static_cast<size_t>(orow) * d : nullptr;
+  const size_t ypitch = static_cast<size_t>(d) * (a.split ? 2 : 1);
+  AT* y1 = reinterpret_cast<AT*>(a.y1) + static_cast<size_t>(orow) * ypitch;
+  AT* y2 = a.y2 ? reinterpret_cast<AT*>(a.y2) + static_cast<size_t>(orow) * ypitch : nullptr;
   const float4* g1 = reinterpret_cast<const float4*>(a.g1);
   const float4* b1 = reinterpret_cast<const float4*>(a.b1);
   const float4* g2 = reinterpret_cast<const float4*>(a.g2);
@@ -116,10 +127,10 @@ ln_kernel(LnArgs a) {
     const float4 v = s4[i];
     const float n0 = (v.x - mean) * rstd, n1 = (v.y - mean) * rstd, n2 = (v.z - mean) * rstd, n3 = (v.w - mean) * rstd;
     const float4 g = g1[i], b = b1 ? b1[i] : zero;
-    store4(y1 + 4 * i, n0 * g.x + b.x, n1 * g.y + b.y, n2 * g.z + b.z, n3 * g.w + b.w);
+    store4s(y1 + 4 * i, n0 * g.x + b.x, n1 * g.y + b.y, n2 * g.z + b.z, n3 * g.w + b.w, a.split ? d : 0);
     if (y2) {
       const float4 h = g2[i], c = b2 ? b2[i] : zero;
-      store4(y2 + 4 * i, n0 * h.x + c.x, n1 * h.y + c.y, n2 * h.z + c.z, n3 * h.w + c.w);
+      store4s(y2 + 4 * i, n0 * h.x + c.x, n1 * h.y + c.y, n2 * h.z + c.z, n3 * h.w + c.w, a.split ? d : 0);
     }
   }
 }
@@ -202,6 +213,42 @@ int launch_act(void* x, int64_t n, int kind, cudaStream_t st) {
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
+// BF16_SPLIT: fp32 pre-activations -> [hi | lo] bf16 activation (see b2s_decoder.cuh)
+__global__ void __launch_bounds__(256)
+act_split_kernel(const float* __restrict__ pre, __nv_bfloat16* __restrict__ act, int64_t rows, int ff, int kind) {
+  const int ff4 = ff >> 2;
+  const int64_t n = rows * ff4;
+  const int64_t in_pitch = kind == 0 ? 2 * static_cast<int64_t>(ff) : ff;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / ff4;
+    const int c = static_cast<int>(i - r * ff4) * 4;
+    const float4 g = *reinterpret_cast<const float4*>(pre + r * in_pitch + c);
+    const float x[4] = {g.x, g.y, g.z, g.w};
+    float o[4];
+    if (kind == 0) {
+      const float4 u4 = *reinterpret_cast<const float4*>(pre + r * in_pitch + ff + c);
+      const float u[4] = {u4.x, u4.y, u4.z, u4.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = x[k] / (1.f + expf(-x[k])) * u[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        o[k] = kind == 1 ? fmaxf(x[k], 0.f) : x[k] * 0.5f * (1.0f + tanhf(0.79788456f * x[k] * (1.0f + 0.044715f * x[k] * x[k])));
+    }
+    store4s(act + r * (2 * static_cast<int64_t>(ff)) + c, o[0], o[1], o[2], o[3], ff);
+  }
+}
+
+int launch_act_split(const float* pre, void* act, int64_t rows, int ff, int kind, cudaStream_t st) {
+  B2S_REQUIRE(ff % 4 == 0 && kind >= 0 && kind <= 2, "split activation: d_ff=%d kind=%d", ff, kind);
+  const int64_t blocks = ceil_div(rows * (ff >> 2), 256);
+  const unsigned grid = static_cast<unsigned>(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
+  act_split_kernel<<<grid, 256, 0, st>>>(pre, reinterpret_cast<__nv_bfloat16*>(act), rows, ff, kind);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
 template int launch_act<float>(void*, int64_t, int, cudaStream_t);
 template int launch_act<__nv_bfloat16>(void*, int64_t, int, cudaStream_t);
 template int launch_act<__half>(void*, int64_t, int, cudaStream_t);
@@ -370,11 +417,16 @@ attn_kernel(AttnArgs a) {
       __syncwarp();
     }
     const float inv = 1.f / l;
-    AT* op = out + row * (static_cast<size_t>(a.nh) * HD) + h * HD;
+    const size_t owidth = static_cast<size_t>(a.nh) * HD;
+    AT* op = out + row * (owidth * (a.split ? 2 : 1)) + h * HD;
 #pragma unroll
     for (int r = 0; r < DPL; ++r) {
       const int dd = lane + 32 * r;
-      if (dd < HD) op[dd] = from_f32<AT>(acc[r] * inv);
+      if (dd < HD) {
+        const float o = acc[r] * inv;
+        op[dd] = from_f32<AT>(o);
+        if (a.split) op[owidth + dd] = from_f32<AT>(o - to_f32(from_f32<AT>(o)));   // BF16_SPLIT: rounding remainder
+      }
     }
     __syncwarp();
   }

@@ -30,6 +30,7 @@ struct LnArgs {
   const void* wpe;          // learned position table added to the gathered embedding (tokens != null), or null
   const int32_t* pos;       // position of every row (with wpe)
   int pos_offset;
+  int split;                // BF16_SPLIT: output rows are [hi(d) | lo(d)] bf16, lo = bf16(y - bf16(y))
 };
 
 struct RopeArgs {
@@ -53,6 +54,7 @@ struct AttnArgs {
   const float* alibi;  // per-head ALiBi slopes (CUDA-core kernel only), or null
   int heads_per_cta;   // set by the launcher: ATT_HG for prefill, all heads of the KV head for single-token steps
   float scale;
+  int split;           // BF16_SPLIT: output rows are [hi(nh*hd) | lo(nh*hd)] bf16
 };
 
 struct ScanState {
@@ -80,6 +82,9 @@ template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream
 template <typename AT> int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st);
 // x = relu(x) (kind 1) or tanh-GELU(x) (kind 2) in place (HF opt ReLU MLP; HF bloom bloom_gelu_forward)
 template <typename AT> int launch_act(void* x, int64_t n, int kind, cudaStream_t st);
+// BF16_SPLIT: the MLP pre-activations arrive in fp32 (pre [rows, ff], or [rows, 2*ff] = gate | up for kind 0) and the
+// activation leaves as [rows, hi(ff) | lo(ff)] bf16.  kind 0 = SwiGLU, 1 = ReLU, 2 = tanh-GELU.
+int launch_act_split(const float* pre, void* act, int64_t rows, int ff, int kind, cudaStream_t st);
 // tcgen05 prefill attention (b2s_attn_tc.cu): head_dim 64, <= 256 keys per sequence
 bool attn_tc_supported(int hd, int max_kv);
 bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride);

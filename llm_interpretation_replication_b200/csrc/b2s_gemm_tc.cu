@@ -45,6 +45,9 @@ struct GemmParams {
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
+  int k_wrap;            // BF16_SPLIT: A is [M, 2K] = [hi | lo] and num_kb counts its k-blocks; the W box of k-block kb is
+                         // kb - k_wrap once kb >= k_wrap (0 = A and W walk K together)
+  int out_split;         // BF16_SPLIT, 16-bit store epilogues: the output is [M, 2N]; hi goes to column c, lo to out_split + c
   void* out;             // bf16 or f32 [M,N]
   const float* bias;     // [N] or null
   LmHeadArgs lmh;
@@ -403,6 +406,20 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) { tma_store_2d(tmC, stage, col0, row0); tma_store_commit(); }
+      if constexpr (EPI == EPI_STORE_BF16 || EPI == EPI_GELU_BF16) {
+        if (p.out_split) {   // BF16_SPLIT: the next GEMM reads this buffer as [hi | lo]; lo = bf16(x - bf16(x))
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            x1[j] -= __bfloat162float(__float2bfloat16_rn(x1[j]));
+            x2[j] -= __bfloat162float(__float2bfloat16_rn(x2[j]));
+          }
+          next_buffer(stage, my_line);
+          stage_store16<false>(my_line, sw, x1, x2);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) { tma_store_2d(tmC, stage, p.out_split + col0, row0); tma_store_commit(); }
+        }
+      }
     }
   }
   // all TMEM reads of this accumulator are done: hand it back to the MMA warp
@@ -488,8 +505,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           const uint32_t sb = sa + A_STAGE_BYTES;
           mbar_arrive_expect_tx(full_bar(stage), STAGE_BYTES);
+          const int kw = (p.k_wrap != 0 && kb >= p.k_wrap) ? kb - p.k_wrap : kb;   // lo half of A meets the same W block
           tma_load_2d_h(sa, &tmA, full_bar(stage), kb * BK, mb * BM, p.hint_a);
-          tma_load_2d_h(sb, &tmB, full_bar(stage), kb * BK, nb * BN, p.hint_b);
+          tma_load_2d_h(sb, &tmB, full_bar(stage), kw * BK, nb * BN, p.hint_b);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -676,8 +694,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t sb = sa + A_STAGE_BYTES;
           const uint32_t fb = full_bar(stage) & PEER_MASK;
           if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
+          const int kw = (p.k_wrap != 0 && kb >= p.k_wrap) ? kb - p.k_wrap : kb;
           tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM2 + static_cast<int>(rank) * BM, p.hint_a);
-          tma_load_2d_cg2(sb, &tmB, fb, kb * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
+          tma_load_2d_cg2(sb, &tmB, fb, kw * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
           if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
         }
       }
@@ -831,8 +850,9 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t sb = sa + A3_STAGE_BYTES;
           const uint32_t fb = full_bar(stage) & PEER_MASK;
           if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE3_BYTES);
+          const int kw = (p.k_wrap != 0 && kb >= p.k_wrap) ? kb - p.k_wrap : kb;
           tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM3 + static_cast<int>(rank) * 256, p.hint_a);
-          tma_load_2d_cg2(sb, &tmB, fb, kb * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
+          tma_load_2d_cg2(sb, &tmB, fb, kw * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
           if (++stage == STAGES3) { stage = 0; phase ^= 1u; }
         }
       }
@@ -1111,7 +1131,10 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
 }
 
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
-                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope) {
+                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope, int a_split, int out_split) {
+  B2S_REQUIRE(!a_split || (K % BK == 0 && !act_f16), "gemm_bf16: split activations need K %% 64 == 0 and bf16 operands (K=%d)", K);
+  B2S_REQUIRE(!out_split || (N % 64 == 0 && g_opt_tma_store && (epilogue == EPI_STORE_BF16 || epilogue == EPI_GELU_BF16)),
+              "gemm_bf16: a split 16-bit output needs N %% 64 == 0, the TMA-store epilogue and a 16-bit store epilogue (N=%d)", N);
   B2S_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
   B2S_REQUIRE(K % 8 == 0, "gemm_bf16: K=%d must be a multiple of 8 (16-byte TMA row pitch)", K);
   B2S_REQUIRE(epilogue == EPI_LMHEAD || N % 8 == 0, "gemm_bf16: N=%d must be a multiple of 8", N);
@@ -1121,15 +1144,18 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   int dev = 0, num_sms = 0;
   B2S_TRY(current_device_sms(&dev, &num_sms));
   CUtensorMap ta, tb, tb2, ta3;
-  B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), BM, act_f16));
+  const uint64_t KA = static_cast<uint64_t>(K) * (a_split ? 2 : 1);   // split activations: A is [M, hi(K) | lo(K)]
+  B2S_TRY(make_tmap_bf16(&ta, A, static_cast<uint64_t>(M), KA, BM, act_f16));
   B2S_TRY(make_tmap_bf16(&tb, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN, act_f16));
-  B2S_TRY(make_tmap_bf16(&ta3, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), 256, act_f16));   // big-tile kernel: 256-row A boxes
+  B2S_TRY(make_tmap_bf16(&ta3, A, static_cast<uint64_t>(M), KA, 256, act_f16));   // big-tile kernel: 256-row A boxes
   B2S_TRY(make_tmap_bf16(&tb2, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), BN / 2, act_f16));   // per-CTA half of a W box
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = static_cast<int>(ceil_div(M, BM));
   p.tiles_n = static_cast<int>(ceil_div(N, BN));
-  p.num_kb = static_cast<int>(ceil_div(K, BK));
+  p.num_kb = static_cast<int>(ceil_div(K, BK)) * (a_split ? 2 : 1);
+  p.k_wrap = a_split ? K / BK : 0;
+  p.out_split = out_split ? N : 0;
   // Rasterisation: the A panel of a group (group_m x 128 rows x K) is re-read by every wave of the group, so it
   // should stay L2-resident (<= ~40 MB); when K is so long that even 16 row-blocks exceed that, no cross-wave
   // reuse is possible and the near-square wave footprint (16 x 9 tiles) minimises the bytes each wave streams.
@@ -1166,8 +1192,8 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   CUtensorMap tc = ta;   // placeholder when the epilogue writes no [M,N] matrix
   if (p.tma_store) {
     const bool f32 = epilogue == EPI_RESID_F32 || epilogue == EPI_STORE_F32;
-    B2S_TRY(make_tmap_2d(&tc, out, static_cast<uint64_t>(M), static_cast<uint64_t>(N), static_cast<uint64_t>(N) * (f32 ? 4 : 2),
-                         32, f32 ? 32 : 64, f32 ? 4 : 2, act_f16));
+    const uint64_t NC = static_cast<uint64_t>(N) * (out_split ? 2 : 1);
+    B2S_TRY(make_tmap_2d(&tc, out, static_cast<uint64_t>(M), NC, NC * (f32 ? 4 : 2), 32, f32 ? 32 : 64, f32 ? 4 : 2, act_f16));
   }
   switch (epilogue) {
     case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, ta3, tc, p, st);

@@ -35,6 +35,7 @@ struct b2s_model {
   int q_base, q_hstride, k_base, v_base, kv_hstride;
   bool bf16;      // tensor-core mode (bf16 weights); false = fp32 check mode
   int act_f16;    // tensor-core mode with fp16 operands (weights handed over as fp16)
+  int split;      // BF16_SPLIT: every GEMM A operand is stored as [hi | lo] bf16 halves (row width doubled)
   size_t at_size;
   const void* gw(int slot) const { return w[slot]; }
   const void* lw(int layer, int slot) const { return w[B2S_W_NGLOBAL + layer * B2S_W_PER_LAYER + slot]; }
@@ -93,13 +94,17 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.scan.gen_ids = nullptr;
   w.scan.out = nullptr;
   w.resid = reinterpret_cast<float*>(take(4 * rows * d.d_model));
-  w.ln1 = take(at * rows * d.d_model);
-  w.ln2 = d.n_ln_per_layer == 2 ? take(at * rows * d.d_model) : nullptr;
+  const size_t am = m->split ? 2 : 1;   // [hi | lo] rows in BF16_SPLIT
+  w.ln1 = take(at * am * rows * d.d_model);
+  w.ln2 = d.n_ln_per_layer == 2 ? take(at * am * rows * d.d_model) : nullptr;
   w.qkv = take(at * rows * m->qkv_dim);
-  w.attn = take(at * rows * d.n_head * d.head_dim);
-  w.act = take(at * rows * d.d_ff);
-  w.gu = d.mlp_type == B2S_MLP_SWIGLU ? take(at * rows * 2 * d.d_ff) : nullptr;   // gate | up before the SwiGLU kernel
-  w.hfin = take(at * static_cast<size_t>(N) * d.d_model);
+  w.attn = take(at * am * rows * d.n_head * d.head_dim);
+  w.act = take(at * am * rows * d.d_ff);
+  // MLP pre-activations that a separate kernel turns into the activation: gate | up before SwiGLU; in BF16_SPLIT also
+  // the ReLU / tanh-GELU pre-activations, and then in fp32 so that nothing is rounded before the [hi | lo] split
+  const bool pre_buf = d.mlp_type == B2S_MLP_SWIGLU || (m->split && d.act_type != B2S_ACT_GELU);
+  w.gu = pre_buf ? take((m->split ? 4 : at) * rows * (d.mlp_type == B2S_MLP_SWIGLU ? 2 : 1) * d.d_ff) : nullptr;
+  w.hfin = take(at * am * static_cast<size_t>(N) * d.d_model);
   const size_t slots = static_cast<size_t>(T) + static_cast<size_t>(N) * LA;
   w.cache_slots = slots;
   w.cache_layer_bytes = align_up(at * slots * d.n_kv_head * d.head_dim, 256);
@@ -116,8 +121,8 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
 
 // C = A . W^T with the mode's GEMM.  `out` is AT except for EPI_RESID_F32 (always the fp32 residual).
 int linear(const b2s_model* m, const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epi,
-           cudaStream_t st) {
-  if (m->bf16) return gemm_tc_launch(A, W, bias, out, M, N, K, epi, nullptr, st, m->act_f16);
+           cudaStream_t st, int out_split = 0) {
+  if (m->bf16) return gemm_tc_launch(A, W, bias, out, M, N, K, epi, nullptr, st, m->act_f16, nullptr, m->split, out_split);
   return gemm_f32_launch(reinterpret_cast<const float*>(A), reinterpret_cast<const float*>(W), bias,
                          reinterpret_cast<float*>(out), M, N, K, epi, st);
 }
@@ -130,7 +135,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
   const bool two_ln = d.n_ln_per_layer == 2;
   for (int l = 0; l < d.n_layer; ++l) {
     LnArgs ln{};
-    ln.x = w.resid; ln.d = dm; ln.eps = d.norm_eps; ln.rms = d.norm_type == B2S_NORM_RMS;
+    ln.x = w.resid; ln.d = dm; ln.eps = d.norm_eps; ln.rms = d.norm_type == B2S_NORM_RMS; ln.split = m->split;
     ln.tokens = (l == 0) ? tokens : nullptr;
     ln.wte = m->gw(B2S_W_WTE);
     if (d.pos_type == B2S_POS_LEARNED) { ln.wpe = m->gw(B2S_W_WPE); ln.pos = w.meta.pos; ln.pos_offset = d.pos_offset; }
@@ -139,7 +144,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       // (the kernel writes the raw row before its barriers and the normalised row after them), then layer 0 reads it
       LnArgs le = ln;
       le.g1 = reinterpret_cast<const float*>(m->gw(B2S_W_EMB_LN_G)); le.b1 = reinterpret_cast<const float*>(m->gw(B2S_W_EMB_LN_B));
-      le.y1 = w.resid; le.rms = 0;
+      le.y1 = w.resid; le.rms = 0; le.split = 0;
       B2S_TRY((launch_ln<float, WT>(le, rows, st)));
       ln.tokens = nullptr;
     }
@@ -161,7 +166,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       re.sin = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_SIN));
       re.kcache = kc; re.vcache = vc; re.nh = d.n_head; re.nkv = d.n_kv_head;
       B2S_TRY(gemm_tc_launch(w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
-                             EPI_QKV_ROPE, nullptr, st, m->act_f16, &re));
+                             EPI_QKV_ROPE, nullptr, st, m->act_f16, &re, m->split, 0));
     } else {
       B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
                      EPI_STORE_BF16, st));
@@ -181,6 +186,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
     at.heads_per_cta = (max_qlen == 1) ? at.rep : ATT_HG;
     at.f16 = m->act_f16;
+    at.split = m->split;
     at.alibi = d.pos_type == B2S_POS_ALIBI ? reinterpret_cast<const float*>(m->gw(B2S_W_ALIBI)) : nullptr;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
     // tensor-core kernel when the shape allows it (head_dim 64, <= 256 keys), CUDA-core kernel otherwise
@@ -199,26 +205,32 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       mlp_in = w.ln2;
       if (!d.parallel_residual) {   // sequential residual: second LayerNorm reads x + attn
         LnArgs l2{};
-        l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps; l2.rms = d.norm_type == B2S_NORM_RMS;
+        l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps; l2.rms = d.norm_type == B2S_NORM_RMS; l2.split = m->split;
         l2.g1 = m->lwf(l, B2S_WL_LN2_G); l2.b1 = m->lwf(l, B2S_WL_LN2_B); l2.y1 = w.ln2;
         B2S_TRY((launch_ln<AT, WT>(l2, rows, st)));
       }
     }
-    if (d.mlp_type == B2S_MLP_SWIGLU) {   // fused gate|up projection, then act = silu(gate) * up
+    if (m->split && (d.mlp_type == B2S_MLP_SWIGLU || d.act_type != B2S_ACT_GELU)) {
+      // BF16_SPLIT: fp32 pre-activations, then one kernel forms the activation and its [hi | lo] halves
+      const bool glu = d.mlp_type == B2S_MLP_SWIGLU;
+      B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), glu ? nullptr : m->lwf(l, B2S_WL_B_UP), w.gu, rows, (glu ? 2 : 1) * d.d_ff, dm,
+                     EPI_STORE_F32, st));
+      B2S_TRY(launch_act_split(reinterpret_cast<const float*>(w.gu), w.act, rows, d.d_ff, glu ? 0 : d.act_type, st));
+    } else if (d.mlp_type == B2S_MLP_SWIGLU) {   // fused gate|up projection, then act = silu(gate) * up
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), nullptr, w.gu, rows, 2 * d.d_ff, dm, EPI_STORE_BF16, st));
       B2S_TRY(launch_swiglu<AT>(w.gu, w.act, rows, d.d_ff, st));
     } else if (d.act_type != B2S_ACT_GELU) {   // ReLU / tanh-GELU: plain store epilogue, then the activation in place
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_STORE_BF16, st));
       B2S_TRY(launch_act<AT>(w.act, static_cast<int64_t>(rows) * d.d_ff, d.act_type, st));
     } else {
-      B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st));
+      B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st, m->split));
     }
     B2S_TRY(linear(m, w.act, m->lw(l, B2S_WL_W_DOWN), m->lwf(l, B2S_WL_B_DOWN), w.resid, rows, dm, d.d_ff,
                    EPI_RESID_F32, st));
   }
   // final LayerNorm on the last row of every prompt only (HF generate sets logits_to_keep=1)
   LnArgs lf{};
-  lf.x = w.resid; lf.d = dm; lf.eps = d.norm_eps; lf.rows = w.meta.last_row; lf.rms = d.norm_type == B2S_NORM_RMS;
+  lf.x = w.resid; lf.d = dm; lf.eps = d.norm_eps; lf.rows = w.meta.last_row; lf.rms = d.norm_type == B2S_NORM_RMS; lf.split = m->split;
   lf.g1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_G)); lf.b1 = reinterpret_cast<const float*>(m->gw(B2S_W_LNF_B));
   lf.y1 = w.hfin;
   B2S_TRY((launch_ln<AT, WT>(lf, n_seqs, st)));
@@ -239,7 +251,7 @@ int lm_head(const b2s_model* m, const Workspace& w, const int32_t* cand, int n_s
   if (m->bf16) {
     LmHeadArgs a{cand, w.partials, w.cand_logits};
     B2S_TRY(gemm_tc_launch(w.hfin, m->gw(B2S_W_LM_HEAD), nullptr, nullptr, n_seqs, d.vocab, d.d_model, EPI_LMHEAD, &a, st,
-                           m->act_f16));
+                           m->act_f16, nullptr, m->split, 0));
   } else {
     B2S_TRY(gemm_f32_launch(reinterpret_cast<const float*>(w.hfin), reinterpret_cast<const float*>(m->gw(B2S_W_LM_HEAD)),
                             nullptr, w.logits, n_seqs, d.vocab, d.d_model, EPI_STORE_F32, st));
@@ -285,8 +297,11 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || d.mlp_type == B2S_MLP_SWIGLU, "model_create: unknown mlp_type %d", d.mlp_type);
   B2S_REQUIRE(d.mlp_type != B2S_MLP_SWIGLU || !d.has_bias, "model_create: SwiGLU with biases is not supported");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
-  B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_FP32_CHECK,
+  B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_BF16_SPLIT ||
+                  d.compute_mode == B2S_MODE_FP32_CHECK,
               "model_create: unknown compute mode %d", d.compute_mode);
+  B2S_REQUIRE(d.compute_mode != B2S_MODE_BF16_SPLIT || (d.d_model % 64 == 0 && d.d_ff % 64 == 0 && (d.n_head * d.head_dim) % 64 == 0),
+              "model_create: BF16_SPLIT needs d_model, d_ff and n_head*head_dim to be multiples of 64");
   B2S_REQUIRE(d.d_model % 8 == 0 && d.d_ff % 8 == 0, "model_create: d_model and d_ff must be multiples of 8");
   const int need = B2S_W_NGLOBAL + B2S_W_PER_LAYER * d.n_layer;
   B2S_REQUIRE(n_ptrs >= need, "model_create: %d weight pointers given, %d needed", n_ptrs, need);
@@ -307,6 +322,7 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   m->device = device;
   m->bf16 = d.compute_mode != B2S_MODE_FP32_CHECK;
   m->act_f16 = d.compute_mode == B2S_MODE_FP16 ? 1 : 0;
+  m->split = d.compute_mode == B2S_MODE_BF16_SPLIT ? 1 : 0;
   m->at_size = m->bf16 ? 2 : 4;
   m->qkv_dim = (d.n_head + 2 * d.n_kv_head) * d.head_dim;
   if (d.qkv_layout == B2S_QKV_FALCON_MQA) {

@@ -39,6 +39,7 @@ REF = "/root/reference"
 
 from llm_interpretation_replication_b200 import shapes, weights  # noqa: E402
 from llm_interpretation_replication_b200.tokenizer import HashTokenizer  # noqa: E402
+from oracle import hf_models  # noqa: E402
 
 FEW_SHOT = '''Question: Is "soup" a "beverage"? Answer either 'Yes' or 'No', without any other text.
 Answer: No.
@@ -90,7 +91,7 @@ def scorer_goldens(R, k2_fn, specs=SPECS):
     cases = []
     for name, shp, seed in specs:
         W = weights.init_weights(shp, seed=seed)
-        model = weights.build_hf_model(shp, W)
+        model = hf_models.build_hf_model(shp, W)
         tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
         prompts = []
         for q in R.ALL_PROMPTS[:10]:

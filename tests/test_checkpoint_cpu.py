@@ -7,10 +7,11 @@ import pytest
 import torch
 
 from llm_interpretation_replication_b200 import checkpoint, shapes, weights
+from oracle import hf_models
 
 
 def _save_hf(shape, W, path, safe=True):
-    model = weights.build_hf_model(shape, W)
+    model = hf_models.build_hf_model(shape, W)
     model.save_pretrained(path, safe_serialization=safe)
     return model
 
@@ -85,7 +86,7 @@ def test_config_mapping_matches_registry():
 def test_wrong_or_missing_tensors_are_rejected(tmp_path):
     shp = shapes.tiny_falcon()
     W = weights.init_weights(shp, seed=1)
-    sd = weights.to_hf_state_dict(shp, W)
+    sd = hf_models.to_hf_state_dict(shp, W)
     bad = dict(sd); bad["transformer.h.0.mlp.dense_h_to_4h.weight"] = torch.zeros(3, 3)
     with pytest.raises(ValueError, match="shape"):
         checkpoint.flat_from_hf(shp, bad)
@@ -96,7 +97,7 @@ def test_wrong_or_missing_tensors_are_rejected(tmp_path):
     extra = dict(sd); extra["transformer.h.0.self_attention.rotary_emb.inv_freq"] = torch.zeros(32)
     assert set(checkpoint.flat_from_hf(shp, extra)) == set(checkpoint.flat_from_hf(shp, sd))
     with pytest.raises(FileNotFoundError):
-        (tmp_path / "config.json").write_text(json.dumps(weights.hf_config(shp).to_dict()))
+        (tmp_path / "config.json").write_text(json.dumps(hf_models.hf_config(shp).to_dict()))
         checkpoint.load_checkpoint(str(tmp_path), device="cpu")
 
 

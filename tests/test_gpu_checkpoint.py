@@ -18,14 +18,14 @@ def test_local_checkpoint_end_to_end_vs_hf(tmp_path, monkeypatch, maker):
     from llm_interpretation_replication_b200 import scorer as S, shapes, weights
     from llm_interpretation_replication_b200.entrypoints import common
     from llm_interpretation_replication_b200.tokenizer import HashTokenizer
-    from oracle import scorer_oracle
+    from oracle import hf_models, scorer_oracle
     from test_checkpoint_cpu import _write_tokenizer
 
     shp = getattr(shapes, maker)(vocab=64)
     W = weights.init_weights(shp, seed=31)
     d = tmp_path / "someorg" / "some-model"
     d.mkdir(parents=True)
-    weights.build_hf_model(shp, W).save_pretrained(str(d))
+    hf_models.build_hf_model(shp, W).save_pretrained(str(d))
     _write_tokenizer(str(d))
     monkeypatch.setenv("B2S_CHECKPOINT_ROOT", str(tmp_path))
 

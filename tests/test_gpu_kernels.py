@@ -242,3 +242,55 @@ def test_attention_bf16(use_tc, nh, nkv, phase):
         got = out[qs:qs + ql].view(ql, nh, hd).float()
         err = (got - r).abs().max().item()
         assert err <= (3e-2 if use_tc else 1.5e-2), (use_tc, ql, err)     # bf16 output (+ bf16 P on the tensor-core path)
+
+
+@pytest.mark.parametrize("name,M,N,K,epi,f16", [("down", 16384, 4544, 18176, 2, True), ("up_gelu", 16384, 18176, 4544, 1, True),
+                                                ("down_bf16", 16384, 4544, 18176, 2, False)])
+def test_gemm_tc_default_policy_at_bench_sizes(name, M, N, K, epi, f16):
+    """The configuration bench.py actually runs, with the LIBRARY DEFAULTS (no gemm_cta_group override): Falcon-7B down
+    projection (M >= 4096 and K >= 8192 -> 512x256 CTA-pair tiles, 8 waves -> wave meeting armed) and up projection +
+    GELU (256x256 CTA-pair tiles, 60 waves, meeting armed), against fp32 torch on the same 16-bit operands."""
+    import gpu_util as U
+    dt = torch.float16 if f16 else torch.bfloat16
+    A, W = _rand((M, K), 1.0, 31, dt), _rand((N, K), 0.02, 32, dt)
+    fn = U.gemm_f16 if f16 else U.gemm_bf16
+    if epi == 2:
+        resid = _rand((M, N), 1.0, 33, torch.float32)
+        out = fn(A, W, None, 2, out=resid.clone())
+    else:
+        out = fn(A, W, None, epi).float()
+    torch.cuda.synchronize()
+    worst = 0.0
+    for r0 in range(0, M, 2048):                      # reference in row slabs: fp32 copies of A would not fit otherwise
+        ref = A[r0:r0 + 2048].float() @ W.float().T
+        if epi == 1:
+            ref = torch.nn.functional.gelu(ref)
+        if epi == 2:
+            ref = ref + resid[r0:r0 + 2048]
+        worst = max(worst, ((out[r0:r0 + 2048] - ref).abs() / (ref.abs() + 1.0)).max().item())
+    tol = 2e-3 if epi == 2 else (2.0 ** -10 if f16 else 2.0 ** -7)
+    assert worst <= tol, (name, worst)
+    # and bit-identical to the single-CTA tiling without the meeting (the summation order of a row does not depend on either)
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    try:
+        _lib.check(lib.b2s_set_option(b"gemm_cta_group", 1), "set_option")
+        _lib.check(lib.b2s_set_option(b"gemm_wave_sync", 0), "set_option")
+        out1 = fn(A, W, None, 2, out=resid.clone()) if epi == 2 else fn(A, W, None, epi).float()
+        torch.cuda.synchronize()
+    finally:
+        _lib.check(lib.b2s_set_option(b"gemm_cta_group", 0), "set_option")
+        _lib.check(lib.b2s_set_option(b"gemm_wave_sync", 4), "set_option")
+    assert torch.equal(out, out1), name
+
+
+def test_gemm_f32_large_matches_fp64():
+    """The register-tiled fp32 check GEMM at a Falcon-sized K against an fp64 reference (error of a K = 18176 fmaf chain)."""
+    import gpu_util as U
+    M, N, K = 300, 520, 18176
+    A, W = _rand((M, K), 1.0, 41, torch.float32), _rand((N, K), 0.02, 42, torch.float32)
+    out = U.gemm_f32(A, W, None, 4)
+    ref = (A.double() @ W.double().T)
+    torch.cuda.synchronize()
+    err = ((out.double() - ref).abs() / (ref.abs() + 1.0)).max().item()
+    assert err <= 2e-5, err

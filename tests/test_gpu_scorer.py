@@ -17,7 +17,21 @@ TOL_BF16_REAL_DIMS = 4e-3
 
 
 def _tol(mode_name):
-    return TOL_BF16 if mode_name == "MODE_FP16" else TOL_BF16_REAL_DIMS
+    return TOL_BF16_REAL_DIMS if mode_name == "MODE_BF16_FAST" else TOL_BF16
+
+
+def _rnd(mode_name):
+    """Operand rounding of each 16-bit mode for the emulating oracle (decoder_ref.forward_hidden round_act)."""
+    from oracle import decoder_ref
+    if mode_name == "MODE_BF16_FAST":
+        return decoder_ref.bf16_round
+    if mode_name == "MODE_FP16":
+        return lambda t: t.to(torch.float16).to(t.dtype)
+    # BF16_SPLIT: hi + lo bf16 halves (the attention operands, which stay plain bf16 on the GPU, are covered by the tolerance)
+    return lambda t: decoder_ref.bf16_round(t) + decoder_ref.bf16_round(t - decoder_ref.bf16_round(t))
+
+
+MODES_16 = ["MODE_BF16_FAST", "MODE_FP16", "MODE_BF16_SPLIT"]
 
 
 def _run_case(case, mode, tol):
@@ -29,6 +43,7 @@ def _run_case(case, mode, tol):
     W = weights.init_weights(shp, seed=case["seed"])
     sc = U.make_scorer(shp, W, mode, max_tokens=4096, max_seqs=64)
     worst = 0.0
+    n_rows = n_pos_mismatch = 0
     for variant, key, topk in (("100q", "ref_100q", 5), ("instruct", "ref_instruct", 2)):
         ids, cands = [], []
         for row in case["rows"]:
@@ -41,6 +56,9 @@ def _run_case(case, mode, tol):
             d = S._row_to_dict(rows[i], gens[i], variant, row["prompt"], U.tok_for(shp, row))
             # golden = the reference's own function; oracle = its restatement (tested equal on CPU)
             o = decoder_ref.score_ids(shp, W, ids[i], cands[i][0], cands[i][1], topk=topk, eos_id=shp.eos_id)
+            n_rows += 1
+            if mode != shapes.MODE_FP32_CHECK and o["pos_found"] != int(rows[i][6]):
+                n_pos_mismatch += 1      # a top-k membership flipped under 16-bit rounding: counted and bounded below
             if mode == shapes.MODE_FP32_CHECK or o["pos_found"] == int(rows[i][6]):
                 assert int(rows[i][6]) == o["pos_found"], (variant, i)
                 assert bool(rows[i][7]) == o["found"]
@@ -55,6 +73,14 @@ def _run_case(case, mode, tol):
             if variant == "instruct" and mode == shapes.MODE_FP32_CHECK:
                 assert d["position_found"] == g["position_found"] and d["yes_no_found"] == g["yes_no_found"]
     sc.close()
+    # position disagreements of the 16-bit modes: these tiny vocabularies (200-320 ids, top-5) flip far
+    # more often than a 65k one; bounded, and logged next to the other GPU evidence
+    import json, os
+    if os.path.isdir("gpurun_out"):
+        with open("gpurun_out/golden_position_mismatches.jsonl", "a") as f:
+            f.write(json.dumps({"case": case["shape"], "mode": int(mode), "rows": n_rows, "position_mismatches": n_pos_mismatch,
+                                "worst_abs_delta_rel_prob": worst}) + "\n")
+    assert n_pos_mismatch <= max(1, n_rows // 8), (case["shape"], n_pos_mismatch, n_rows)
     return worst
 
 
@@ -102,11 +128,17 @@ def test_completion_50_tokens_vs_reference_golden(case_idx):
 
 
 @pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
-@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+@pytest.mark.parametrize("mode_name", MODES_16)
 def test_scorer_bf16_vs_reference_golden(case_idx, mode_name):
     import gpu_util as U
-    from llm_interpretation_replication_b200 import shapes
-    _run_case(U.golden_cases()[case_idx], getattr(shapes, mode_name), TOL_BF16)
+    from llm_interpretation_replication_b200 import shapes, weights, _lib
+    case = U.golden_cases()[case_idx]
+    shp = shapes.REGISTRY[case["shape"]]()
+    if mode_name == "MODE_BF16_SPLIT" and (shp.d_model % 64 or shp.d_ff % 64 or (shp.n_head * shp.head_dim) % 64):
+        with pytest.raises(_lib.B2SError):      # the split mode says so instead of mis-addressing its [hi | lo] halves
+            U.make_scorer(shp, weights.init_weights(shp, seed=case["seed"]), shapes.MODE_BF16_SPLIT, max_tokens=256, max_seqs=4)
+        return
+    _run_case(case, getattr(shapes, mode_name), TOL_BF16)
 
 
 def test_scorer_edge_cases():
@@ -145,7 +177,7 @@ def test_scorer_edge_cases():
     sc.close()
 
 
-@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+@pytest.mark.parametrize("mode_name", MODES_16)
 def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle(mode_name):
     """Falcon-7B widths (d=4544, 71 heads MQA, ffn 18176, V=65024; ragged GEMM tails) at 2 layers."""
     import gpu_util as U
@@ -158,8 +190,7 @@ def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle(mode_name):
     ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (66, 111, 190, 128, 97)]
     rows, gens = sc.score_ids(ids, np.array([[1000, 2000]]), topk=5, max_lookahead=2)
     for i, x in enumerate(ids):
-        rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[1000] / (p[1000] + p[2000])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
@@ -168,7 +199,7 @@ def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle(mode_name):
 
 
 @pytest.mark.parametrize("maker,lens", [("stablelm_alpha_7b", (18, 84, 40)), ("redpajama_3b", (74, 28, 111))])
-@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+@pytest.mark.parametrize("mode_name", MODES_16)
 def test_scorer_real_dims_neox_bf16(maker, lens, mode_name):
     """GPT-NeoX shapes of BASELINE configs 1-2 at real widths (StableLM-alpha-7B: d 6144, 48 heads x 128, rotary 32,
     parallel residual; RedPajama-3B: d 2560, 32 heads x 80, sequential residual; biases, untied head) at 2 layers."""
@@ -181,16 +212,15 @@ def test_scorer_real_dims_neox_bf16(maker, lens, mode_name):
     g = np.random.RandomState(2)
     ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in lens]
     rows, gens = sc.score_ids(ids, np.array([[500, 600]]), topk=5, max_lookahead=2)
-    rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[500] / (p[500] + p[600])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
     sc.close()
 
 
-@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+@pytest.mark.parametrize("mode_name", MODES_16)
 def test_scorer_real_dims_mistral(mode_name):
     """Mistral-7B widths (d 4096, 32 query / 8 KV heads x 128, SwiGLU 14336, RMSNorm, rope_theta 1e6, vocab 32768) at
     2 layers against the oracle with the same 16-bit operand rounding."""
@@ -203,9 +233,8 @@ def test_scorer_real_dims_mistral(mode_name):
     g = np.random.RandomState(4)
     ids = [g.randint(3, shp.vocab - 3, size=L).tolist() for L in (23, 111, 64)]
     rows, gens = sc.score_ids(ids, np.array([[700, 900]]), topk=5, max_lookahead=2)
-    rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[700] / (p[700] + p[900])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
@@ -214,7 +243,7 @@ def test_scorer_real_dims_mistral(mode_name):
 
 
 @pytest.mark.parametrize("maker", ["opt_iml_1_3b", "bloomz_7b1"])
-@pytest.mark.parametrize("mode_name", ["MODE_BF16_FAST", "MODE_FP16"])
+@pytest.mark.parametrize("mode_name", MODES_16)
 def test_scorer_real_dims_opt_bloom(maker, mode_name):
     """OPT-1.3B widths (learned positions, ReLU, head_dim 64 on the tensor-core attention) and BLOOM-7B1 widths (ALiBi,
     embedding LayerNorm, tanh-GELU, head_dim 128; vocabulary cut to 32000 to keep the CPU oracle small) at 2 layers."""
@@ -230,10 +259,102 @@ def test_scorer_real_dims_opt_bloom(maker, mode_name):
     g = np.random.RandomState(6)
     ids = [g.randint(4, shp.vocab - 3, size=L).tolist() for L in (19, 111, 70)]
     rows, gens = sc.score_ids(ids, np.array([[700, 900]]), topk=5, max_lookahead=2)
-    rnd = decoder_ref.bf16_round if mode_name == "MODE_BF16_FAST" else (lambda t: t.to(torch.float16).to(t.dtype))
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=rnd)
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[700] / (p[700] + p[900])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
     sc.close()
+
+
+def test_lookahead_compaction_bit_identical():
+    """One-token steps run only the prompts that still need a position.  Prompts are made to resolve at positions 0..6
+    (candidate = the token greedy decoding emits there) or never; the rows must equal, bit for bit, those of the
+    round-1 behaviour (every prompt of the batch in every step), and the greedy tokens must agree wherever the compact
+    run produced them (a prompt stops generating once it is resolved)."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights, _lib
+    lib = _lib.load()
+    for shp, mode in ((shapes.tiny_falcon(), shapes.MODE_FP32_CHECK), (shapes.falcon_7b().with_layers(2), shapes.MODE_FP16)):
+        W = weights.init_weights(shp, seed=21)
+        sc = U.make_scorer(shp, W, mode, max_tokens=4096, max_seqs=64)
+        g = np.random.RandomState(8)
+        ids = [g.randint(32, shp.vocab - 32, size=int(L)).tolist() for L in g.randint(3, 120, size=24)]
+        cand = np.tile(np.array([[40, 41]], np.int32), (len(ids), 1))
+        _, gens0 = sc.score_ids(ids, cand, topk=5, eos_id=-1)       # no EOS, nothing resolves: ten greedy tokens per prompt
+        assert (gens0 >= 0).all()
+        eos = int(gens0[5][3])                                      # prompt 5 stops at position 3
+        for i in range(len(ids)):
+            if i % 4 != 3:
+                cand[i, i % 2] = gens0[i][i % 7]                    # resolves at (or before) position i % 7
+        out = {}
+        for compact in (0, 1):
+            _lib.check(lib.b2s_set_option(b"lookahead_compact", compact), "set_option")
+            try:
+                out[compact] = sc.score_ids(ids, cand, topk=5, eos_id=eos)
+            finally:
+                _lib.check(lib.b2s_set_option(b"lookahead_compact", 1), "set_option")
+        (r0, g0), (r1, g1) = out[0], out[1]
+        assert np.array_equal(r0, r1, equal_nan=True)
+        assert len(set(int(x) for x in r1[:, 6])) >= 4               # several different resolution positions
+        have = g1 >= 0
+        assert np.array_equal(g1[have], g0[have]) and have[:, 0].all()
+        for i in range(len(ids)):                                    # a resolved prompt takes no further steps
+            n = int(have[i].sum())
+            assert n >= int(r1[i][6]) + 1
+            if r1[i][7] > 0:
+                assert n == int(r1[i][6]) + 1, (i, n, r1[i])
+        # completion mode: every prompt continues to EOS / gen_tokens whatever its resolution
+        sc2 = U.make_scorer(shp, W, mode, max_tokens=4096, max_seqs=64, max_lookahead=16)
+        rc, gc_ = sc2.score_ids(ids, cand, topk=5, eos_id=eos, gen_tokens=16)
+        assert np.array_equal(rc, r1, equal_nan=True)
+        for i in range(len(ids)):
+            live = gc_[i][gc_[i] >= 0]
+            assert len(live) == 16 or live[-1] == eos
+        sc.close(); sc2.close()
+
+
+def test_fp16_range_overflow_is_flagged_never_silent():
+    """FP16 operands overflow beyond 65504.  Activations with large but representable outliers must still match the
+    oracle; activations beyond the range must come back flagged (NaN row, found = -1, B2SRangeError / NaN dict), never as
+    a finite wrong number; the bf16 mode has the range and must match the oracle on the same weights."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights, _lib
+    from llm_interpretation_replication_b200 import scorer as S
+    from oracle import decoder_ref
+    shp = shapes.tiny_falcon(n_layer=2)
+    g = np.random.RandomState(4)
+    ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (9, 40, 77)]
+    cand = np.array([[40, 41]])
+    for scale, overflows in ((2.0e3, False), (2.5e5, True)):     # the scaled weights themselves stay inside fp16
+        W = weights.init_weights(shp, seed=31)
+        # a few huge rows in the up projection: GELU outputs of ~|x| * scale * 0.02 * sqrt(d)
+        W["l0.w_up"][:7] = (W["l0.w_up"][:7] * scale).to(torch.bfloat16).float()
+        W["l0.w_down"][:, :7] = (W["l0.w_down"][:, :7] / scale).to(torch.bfloat16).float()
+        ref = [decoder_ref.score_ids(shp, W, x, 40, 41, topk=5) for x in ids]
+        assert float(W["l0.w_up"].abs().max()) < 65504.0
+        big = float(torch.nn.functional.linear(torch.randn(4, shp.d_model, generator=torch.Generator().manual_seed(1)), W["l0.w_up"][:7]).abs().max())
+        assert (big > 65504.0) == overflows, big
+        sc = U.make_scorer(shp, W, shapes.MODE_BF16_FAST, max_tokens=512, max_seqs=8)
+        rows, _ = sc.score_ids(ids, cand, topk=5)
+        sc.close()
+        for i, o in enumerate(ref):
+            if int(rows[i][6]) == o["pos_found"]:
+                assert abs(rows[i][2] - o["rel"]) <= 4e-3, (scale, i, rows[i][2], o["rel"])
+        sc = U.make_scorer(shp, W, shapes.MODE_FP16, max_tokens=512, max_seqs=8)
+        if not overflows:
+            rows, _ = sc.score_ids(ids, cand, topk=5)
+            assert np.isfinite(rows).all()
+            for i, o in enumerate(ref):
+                if int(rows[i][6]) == o["pos_found"]:
+                    assert abs(rows[i][2] - o["rel"]) <= TOL_BF16, (scale, i, rows[i][2], o["rel"])
+        else:
+            with pytest.raises(_lib.B2SRangeError):
+                sc.score_ids(ids, cand, topk=5)
+            rows, gens = sc.score_ids(ids, cand, topk=5, nonfinite="nan")
+            assert (rows[:, 7] == -1).all() and np.isnan(rows[:, :3]).all()
+            tok = U.tok_for(shp)
+            tok.overrides = {" Yes": 40, " No": 41}
+            dicts = S.score_prompts(sc, tok, ["abcdefgh" * 5, "xyz" * 9], variant="100q")
+            assert all((not d["success"]) and np.isnan(d["relative_prob"]) for d in dicts)     # the reference's NaN rows, not 0.5
+        sc.close()

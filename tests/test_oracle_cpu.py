@@ -10,7 +10,7 @@ import torch
 from conftest import GOLDEN
 from llm_interpretation_replication_b200 import shapes, weights
 from llm_interpretation_replication_b200.tokenizer import HashTokenizer
-from oracle import bootstrap_oracle, decoder_ref, scorer_oracle
+from oracle import bootstrap_oracle, decoder_ref, hf_models, scorer_oracle
 from oracle.mt19937 import MT19937, choice_table_numpy
 
 
@@ -36,7 +36,7 @@ def test_hf_oracle_matches_reference_function(scorer_golden, case_idx):
     case = scorer_golden["cases"][case_idx]
     shp = shapes.REGISTRY[case["shape"]]()
     W = weights.init_weights(shp, seed=case["seed"])
-    model = weights.build_hf_model(shp, W)
+    model = hf_models.build_hf_model(shp, W)
     for row in case["rows"][:6]:
         tok = _tok(shp, row)
         r = scorer_oracle.get_yes_no_logprobs(model, tok, row["prompt"], variant="100q")
