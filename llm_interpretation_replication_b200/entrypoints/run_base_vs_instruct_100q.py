@@ -5,7 +5,8 @@ Same constants, prompt formats, checkpoint JSON (`{'completed_models': [...], 'r
 result CSV columns (yes_prob, no_prob, relative_prob, completion, success, prompt, model, formatted_prompt,
 model_family, base_or_instruct; :376-382,473-475,547-549) and `analyze_results(df)` (:606-712).  The per-prompt
 `get_yes_no_logprobs` loop (:464-476) is one batched call into libb200score; the bootstrap loops (:655-658,
-:692-695) are the device kernels.  Models are random-init stand-ins of the named hub shapes (no weights offline).
+:692-695) are the device kernels.  Models are loaded from a local checkpoint directory when one is given (checkpoint.py), else random-init stand-ins of the
+named hub shapes (no hub access here).
 
     python -m llm_interpretation_replication_b200.entrypoints.run_base_vs_instruct_100q [--out DIR] [--layers N] [--questions K]
 """
@@ -25,11 +26,14 @@ OUTPUT_DIR = os.environ.get("B2S_OUTPUT_DIR", "llm_interpretation_out")
 CHECKPOINT_NAME = "base_vs_instruct_100q_checkpoint.json"
 RESULTS_NAME = "base_vs_instruct_100q_results.csv"
 
-# reference :88-115 (the three families of BASELINE configs 1-3; the others are "next" rows N4)
+# reference :88-103: all six active pairs (LLaMA-2 and Gemma are commented out there too)
 MODEL_PAIRS = [
     ("tiiuae/falcon-7b", "tiiuae/falcon-7b-instruct", "Falcon"),
     ("stabilityai/stablelm-base-alpha-7b", "stabilityai/stablelm-tuned-alpha-7b", "StableLM"),
     ("togethercomputer/RedPajama-INCITE-7B-Base", "togethercomputer/RedPajama-INCITE-7B-Instruct", "RedPajama"),
+    ("bigscience/bloom-7b1", "bigscience/bloomz-7b1", "BLOOM"),
+    ("EleutherAI/pythia-6.9b", "databricks/dolly-v2-7b", "Pythia-Dolly"),
+    ("mistralai/Mistral-7B-v0.1", "mistralai/Mistral-7B-Instruct-v0.2", "Mistral"),
 ]
 
 

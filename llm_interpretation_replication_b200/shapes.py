@@ -150,6 +150,17 @@ def mistral_7b() -> DecoderShape:
                         qkv_layout=QKV_FALCON_MQA, eos_id=2, max_pos=32768, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
 
 
+def mistral_7b_v01() -> DecoderShape:
+    # mistralai/Mistral-7B-v0.1 (run_base_vs_instruct_100q.py:102, compare_base_vs_instruct.py:155): vocab 32000, rope_theta 1e4.
+    # Its 4096-token sliding window never binds on this path (prompts + 50 generated tokens stay far below it).
+    return replace(mistral_7b(), name="mistral-7b-v0.1", vocab=32000, rope_theta=10000.0)
+
+
+def mistral_7b_v02() -> DecoderShape:
+    # mistralai/Mistral-7B-Instruct-v0.2: vocab 32000, rope_theta 1e6, no sliding window
+    return replace(mistral_7b(), name="mistral-7b-instruct-v0.2", vocab=32000)
+
+
 def llama2_7b() -> DecoderShape:
     # meta-llama/Llama-2-7b-chat-hf (commented out in the reference's list, compare_instruct_models.py:155)
     return DecoderShape("llama-2-7b", ARCH_LLAMA, 32, 4096, 32, 32, 128, 11008, 32000, 128, rope_theta=10000.0,
@@ -243,6 +254,8 @@ REGISTRY = {
     "h2ogpt-oasst1-512-12b": h2ogpt_12b,
     "dolly-v2-7b": dolly_v2_7b,
     "mistral-7b": mistral_7b,
+    "mistral-7b-v0.1": mistral_7b_v01,
+    "mistral-7b-instruct-v0.2": mistral_7b_v02,
     "llama-2-7b": llama2_7b,
     "opt-iml-1.3b": opt_iml_1_3b,
     "bloomz-7b1": bloomz_7b1,
@@ -269,5 +282,6 @@ HUB_TO_SHAPE = {
     "facebook/opt-iml-1.3b": opt_iml_1_3b, "facebook/opt-1.3b": opt_iml_1_3b,
     "bigscience/bloomz-7b1": bloomz_7b1, "bigscience/bloom-7b1": bloomz_7b1,
     "mistralai/Mistral-7B-Instruct-v0.3": mistral_7b, "mistralai/Mistral-7B-v0.3": mistral_7b,
+    "mistralai/Mistral-7B-v0.1": mistral_7b_v01, "mistralai/Mistral-7B-Instruct-v0.2": mistral_7b_v02,
     "meta-llama/Llama-2-7b-chat-hf": llama2_7b, "meta-llama/Llama-2-7b-hf": llama2_7b,
 }

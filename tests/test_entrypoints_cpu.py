@@ -64,3 +64,54 @@ def test_entry_point_5_host_pipeline_matches_reference():
     for (fam, e), gf in zip(errs.items(), g["shipped_families"]):
         assert np.array_equal(np.array(e["base"]), np.array(gf["base"])), fam
         assert np.array_equal(np.array(e["instruct"]), np.array(gf["instruct"])), fam
+
+
+def test_compare_base_vs_instruct_host_logic():
+    """Entry point 6: pair list, the reference's by-name prompt format (:462-463), the odds_ratio CSV schema (:90-111)."""
+    from llm_interpretation_replication_b200.entrypoints import compare_base_vs_instruct as E6
+    assert len(E6.model_pairs) == 9 and E6.model_pairs[0] == ("google/t5-v1_1-base", "google/flan-t5-base")
+    q = 'Is a "tent" a "building"?'
+    few = common.FEW_SHOT
+    base_form = f"{few}Question: {q} Answer either 'Yes' or 'No', without any other text.\nAnswer:"
+    bare_form = f"{few}{q} Answer either 'Yes' or 'No', without any other text."
+    assert E6.format_prompt("stabilityai/stablelm-base-alpha-7b", q) == base_form
+    assert E6.format_prompt("togethercomputer/RedPajama-INCITE-7B-Base", q) == base_form
+    assert E6.format_prompt("bigscience/bloom-7b1", q) == base_form
+    assert E6.format_prompt("tiiuae/falcon-7b", q) == bare_form              # no "base" in the name: the reference's quirk
+    assert E6.format_prompt("tiiuae/falcon-7b-instruct", q) == bare_form
+    out = {"tiiuae/falcon-7b": {q: {"completion": "x", "yes_prob": .2, "no_prob": .1, "odds_ratio": 2.0}},
+           "tiiuae/falcon-7b-instruct": {q: {"yes_prob": float("nan"), "no_prob": float("nan"), "odds_ratio": float("nan"),
+                                             "prompt": q, "completion": "N/A"}}}
+    df = E6.prepare_data_for_csv(out, [("tiiuae/falcon-7b", "tiiuae/falcon-7b-instruct")])
+    assert list(df.columns) == ["prompt", "model", "model_family", "base_or_instruct", "model_output", "yes_prob", "no_prob",
+                                "odds_ratio"]
+    assert df["base_or_instruct"].tolist() == ["base", "instruct"] and df["model_family"].tolist() == ["falcon", "falcon"]
+    # the shipped table of the reference has exactly this schema
+    ref = pd.read_csv(os.path.join(GOLDEN, "model_comparison_results.csv"))
+    assert list(ref.columns) == list(df.columns)
+    assert len(E1.MODEL_PAIRS) == 6 and [p[2] for p in E1.MODEL_PAIRS] == ["Falcon", "StableLM", "RedPajama", "BLOOM", "Pythia-Dolly", "Mistral"]
+    from llm_interpretation_replication_b200 import shapes
+    for pair in E1.MODEL_PAIRS:
+        assert pair[0] in shapes.HUB_TO_SHAPE and pair[1] in shapes.HUB_TO_SHAPE, pair
+
+
+def test_perturbation_requests_follow_the_reference_template():
+    """Entry point 7: 5 scenarios x 2000 rephrasings, prompt = f"{rephrasing} {response_format}" (perturb_prompts.py:215),
+    one candidate pair per scenario from target_tokens, the duplicate counts SURVEY.md 8d lists."""
+    from llm_interpretation_replication_b200.entrypoints import score_perturbations as E7
+    from llm_interpretation_replication_b200.tokenizer import HashTokenizer
+    from llm_interpretation_replication_b200 import scorer as S
+    sc = E7.load_perturbations()
+    assert len(sc) == 5 and all(len(s["rephrasings"]) == 2000 for s in sc)
+    assert [len(s["rephrasings"]) - len(set(s["rephrasings"])) for s in sc] == [60, 23, 28, 19, 48]
+    reqs = E7.build_requests(sc)
+    assert len(reqs) == 10000
+    p, cands, si, reph = reqs[2000]
+    assert si == 1 and p == f"{reph} {sc[1]['response_format']}" and cands == (" Ultimate", " First")
+    tok = HashTokenizer(65024, eos_token_id=11)
+    L = np.array([len(tok(q[0]).input_ids) for q in reqs])
+    assert L.min() >= 64 and L.max() <= 191 and abs(L.sum() - 1.11e6) < 2e4          # the length histogram the bench uses
+    for s in sc:
+        a, b = S.candidate_ids(tok, "100q", " " + s["target_tokens"][0], " " + s["target_tokens"][1])
+        assert a != b
+    assert len(E7.build_requests(sc, limit=3)) == 15

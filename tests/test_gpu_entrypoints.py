@@ -69,3 +69,45 @@ def test_entry_point_5_matches_survey_appendix_d1(tmp_path):
         got = (r.Base_MAE, r.Instruct_MAE, r.Difference, r.CI_Lower, r.CI_Upper, r.P_Value)
         assert np.allclose(got, want[r.Model_Family], atol=1e-6), r.Model_Family
         assert r.N_Questions == 49
+
+
+def test_entry_point_6_base_vs_instruct_odds_ratio_table(tmp_path):
+    """compare_base_vs_instruct.py: by-name prompt formats, "base_vs" scorer variant, NaN rows for the encoder-decoder pair."""
+    from llm_interpretation_replication_b200.entrypoints import compare_base_vs_instruct as E6
+    qs = ['Is a "tent" a "building"?', 'Is "water" a "food"?', 'Is a "drone" an "aircraft"?']
+    pairs = [E6.model_pairs[0], E6.model_pairs[4]]            # T5 pair (not built: NaN rows), Falcon pair
+    out = E6.run(qs, pairs=pairs, n_layer=1)
+    df = E6.prepare_data_for_csv(out, pairs)
+    assert list(df.columns) == ["prompt", "model", "model_family", "base_or_instruct", "model_output", "yes_prob", "no_prob",
+                                "odds_ratio"]
+    assert len(df) == 12
+    t5 = df[df.model_family == "t5"]
+    assert len(t5) == 3 and t5["odds_ratio"].isna().all() and (t5["model_output"] == "N/A").all()     # "flan" is its own family
+    ok = df[df.model_family == "falcon"]
+    assert len(ok) == 6 and np.isfinite(ok["yes_prob"]).all() and (ok["odds_ratio"] > 0).all()
+    assert np.allclose(ok["odds_ratio"], ok["yes_prob"] / ok["no_prob"], rtol=1e-6)
+    # entry point 3 consumes exactly this table
+    from llm_interpretation_replication_b200.entrypoints import analyze_results_base_versus_instruct as E3
+    d, pivot = E3.build_pivot(df)
+    assert pivot.shape == (3, 1)
+
+
+def test_entry_point_7_perturbations_duplicates_identical(tmp_path):
+    """All 10,000 prompts of data/perturbations.json through a 2-layer Falcon-7B-wide model: row schema, Relative_Prob as
+    analyze_perturbation_results.py derives it, and identical rows for the 60/23/28/19/48 duplicate rephrasings (they sit
+    in different batches next to different neighbours)."""
+    from llm_interpretation_replication_b200.entrypoints import score_perturbations as E7
+    df = E7.main(["--out", str(tmp_path), "--layers", "2"])
+    assert len(df) == 10000
+    for c in ("Model", "Original Main Part", "Response Format", "Confidence Format", "Rephrased Main Part", "Full Rephrased Prompt",
+              "Model Response", "Token_1_Prob", "Token_2_Prob", "Odds_Ratio", "Relative_Prob"):
+        assert c in df.columns, c
+    assert np.isfinite(df["Relative_Prob"]).all() and df["Relative_Prob"].between(0, 1).all()
+    assert np.allclose(df["Relative_Prob"], df["Token_1_Prob"] / (df["Token_1_Prob"] + df["Token_2_Prob"]))
+    dup = df[df.duplicated(subset=["Full Rephrased Prompt"], keep=False)]
+    n_dup_extra = int(df.duplicated(subset=["Full Rephrased Prompt"]).sum())
+    assert n_dup_extra == 60 + 23 + 28 + 19 + 48
+    for _, grp in dup.groupby("Full Rephrased Prompt"):
+        assert grp["Token_1_Prob"].nunique() == 1 and grp["Token_2_Prob"].nunique() == 1 and grp["Model Response"].nunique() == 1
+    assert df["Relative_Prob"].std() > 0.01
+    assert os.path.exists(os.path.join(tmp_path, E7.RESULTS_NAME))
