@@ -161,25 +161,31 @@ def analyze_results_bootstrap(family_diffs: Dict[str, np.ndarray], n_bootstrap=N
     return out, overall
 
 
-def prompt_bootstrap_and_signflip(pivot: np.ndarray, n_bootstrap=N_BOOTSTRAP, seed=RANDOM_SEED, device=None):
+def prompt_bootstrap_and_signflip(pivot: np.ndarray, n_bootstrap=N_BOOTSTRAP, seed=RANDOM_SEED, device=None,
+                                  observed_mae: Optional[float] = None, observed_mean: Optional[float] = None):
     """reference analyze_results_base_versus_instruct.py:300-365.  pivot [n_prompts, F]; rows are resampled,
-    statistics are taken over the flattened resample.  The sign-flip "permutation" MAE equals the observed MAE
-    for every draw (|x*s| == |x|), so its p-value is 1.0 by construction; the draws are still taken from the
-    stream (n_bootstrap * n*F words) to keep the stream position identical to the reference's."""
+    statistics are taken over the flattened resample.  ``observed_mae`` / ``observed_mean`` are what the script compares
+    against: pandas means over the UN-pivoted frame (``prompt_diff_df['Abs_Difference'].mean()``, :327-328), whose rows
+    and summation order differ from the pivot's; default = the pivot's own means.
+    The sign-flip "permutation" MAE is ``np.mean(np.abs(x * s))`` = ``np.mean(np.abs(x))`` bit for bit for every draw
+    (|x * s| == |x| exactly), so ``p_value_mae = mean(perm_maes >= observed_mae)`` (:350-357) is 1.0 or 0.0 according
+    to that one comparison; the draws are still taken from the stream (n_bootstrap * n*F words) to keep its position
+    identical to the reference's."""
     pivot = np.asarray(pivot, dtype=np.float64)
     n, F = pivot.shape
-    observed_mae = float(np.mean(np.abs(pivot.flatten())))
-    observed_mean = float(np.mean(pivot.flatten()))
+    perm_mae = float(np.mean(np.abs(pivot.flatten())))            # every entry of the script's perm_maes
+    observed_mae = perm_mae if observed_mae is None else float(observed_mae)
+    observed_mean = float(np.mean(pivot.flatten())) if observed_mean is None else float(observed_mean)
     rs = NumpyLegacyStream(seed, device)
     idx = rs.choice(n, n_bootstrap * n)
     boot = resample(np.ascontiguousarray(pivot.T), F, n_bootstrap, idx, device=rs.device)
     s_mae, _ = summary(boot, 2, 2.5, 97.5, observed_mae)
     s_mean, _ = summary(boot, 0, 2.5, 97.5, observed_mean)
     signs = rs.choice(2, n_bootstrap * n * F)          # choice([-1, 1]) consumes one masked word per draw
-    # perm_mae[b] = mean(|x * s|) = mean(|x|) exactly -> fraction >= observed is 1.0
     del signs
     p_mean = 2 * s_mean["frac_le0"] if observed_mean > 0 else 2 * s_mean["frac_ge0"]
-    return dict(mae=observed_mae, mae_ci_lower=s_mae["pct_lo"], mae_ci_upper=s_mae["pct_hi"], mae_p_value=1.0,
+    return dict(mae=observed_mae, mae_ci_lower=s_mae["pct_lo"], mae_ci_upper=s_mae["pct_hi"],
+                mae_p_value=1.0 if perm_mae >= observed_mae else 0.0,
                 mean_diff=observed_mean, mean_ci_lower=s_mean["pct_lo"], mean_ci_upper=s_mean["pct_hi"],
                 mean_p_value=p_mean, n_prompts=n, n_models=F)
 

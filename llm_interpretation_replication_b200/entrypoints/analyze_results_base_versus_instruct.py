@@ -58,9 +58,9 @@ def main(argv=None):
     args = ap.parse_args(argv)
     df = pd.read_csv(args.csv)
     d, pivot = build_pivot(df)
-    r = bootstrap.prompt_bootstrap_and_signflip(pivot.values)
-    observed_mae = d["Abs_Difference"].mean()
+    observed_mae = d["Abs_Difference"].mean()          # pandas means over the un-pivoted frame, as the script takes them (:327-328)
     observed_mean = d["Difference"].mean()
+    r = bootstrap.prompt_bootstrap_and_signflip(pivot.values, observed_mae=observed_mae, observed_mean=observed_mean)
     stats = {"Metric": ["MAE", "MAE_CI_Lower", "MAE_CI_Upper", "MAE_P_Value", "Mean_Diff", "Mean_Diff_CI_Lower",
                         "Mean_Diff_CI_Upper", "Mean_Diff_P_Value", "N_Prompts", "N_Models", "N_Bootstrap"],
              "Value": [observed_mae, r["mae_ci_lower"], r["mae_ci_upper"], r["mae_p_value"], observed_mean,
