@@ -32,83 +32,136 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   return y;
 }
 
-// One CTA walks the stream 624 words at a time.  The twist is done in the four dependency phases of the
-// in-place recurrence; acceptance flags are compacted with a block scan so that idx_out holds the accepted
-// draws in stream order, exactly as the sequential reference consumes them.
-__global__ void __launch_bounds__(640)
-mt_choice_kernel(uint32_t* __restrict__ state, uint32_t rng, uint32_t mask, long long count, int32_t* __restrict__ idx_out) {
-  __shared__ uint32_t mt[MT_N];
-  __shared__ int warp_tot[20];
-  __shared__ int s_pos, s_total, s_newpos;
+// ---- np.random.choice, device-wide ---------------------------------------------------------------------------
+// The word stream x[0..623] = state, x[j] = x[j-227] ^ mix(x[j-624], x[j-623]) is the same sequence whether it is
+// produced 624 words at a time in place (NumPy) or as a sliding recurrence.  Only the recurrence is serial, so it gets
+// a kernel of its own that does nothing else (mt_gen_kernel: one CTA, 454 words per barrier); tempering, masking,
+// rejection and the stream-order compaction of the accepted draws are data-parallel and run on the whole GPU
+// (count -> scan -> scatter over 4096-word chunks).  The raw words are kept in scratch memory because they ARE the
+// generator state: after the draw that consumes word e, NumPy's state array is the 624-word block containing e and its
+// position is (e mod 624) + 1.
+constexpr int MT_GEN_STEP = 454;      // words per barrier: j and j+227 by the same thread (x[j+227] needs x[j] from its own register)
+constexpr int MT_RING = 2048;         // circular window of the stream in shared memory (>= 624 + 2*454, power of two)
+constexpr int MT_CHUNK = 4096;        // words per CTA in the compaction kernels
+
+__global__ void __launch_bounds__(256)
+mt_gen_kernel(const uint32_t* __restrict__ state, uint32_t* __restrict__ raw, long long n_new /* multiple of MT_GEN_STEP */) {
+  __shared__ uint32_t x[MT_RING];
   const int t = threadIdx.x;
-  const int lane = t & 31, warp = t >> 5;
-  if (t < MT_N) mt[t] = state[t];
-  if (t == 0) s_pos = static_cast<int>(state[MT_N]);
+  for (int i = t; i < MT_N; i += blockDim.x) { const uint32_t v = state[i]; x[i] = v; raw[i] = v; }
   __syncthreads();
-  long long produced = 0;
-  while (produced < count) {
-    int pos = s_pos;
-    if (pos >= MT_N) {
-      uint32_t y = 0;
-      if (t < MT_N - 1) y = (mt[t] & 0x80000000u) | (mt[t + 1] & 0x7fffffffu);
-      __syncthreads();
-      if (t < MT_N - MT_M) mt[t] = mt[t + MT_M] ^ mt_mix(y);                       // kk in [0,227)
-      __syncthreads();
-      if (t >= MT_N - MT_M && t < 2 * (MT_N - MT_M)) mt[t] = mt[t - (MT_N - MT_M)] ^ mt_mix(y);   // [227,454)
-      __syncthreads();
-      if (t >= 2 * (MT_N - MT_M) && t < MT_N - 1) mt[t] = mt[t - (MT_N - MT_M)] ^ mt_mix(y);     // [454,623)
-      __syncthreads();
-      if (t == MT_N - 1) {
-        const uint32_t yy = (mt[MT_N - 1] & 0x80000000u) | (mt[0] & 0x7fffffffu);
-        mt[MT_N - 1] = mt[MT_M - 1] ^ mt_mix(yy);
-      }
-      pos = 0;
-      __syncthreads();
+  for (long long base = MT_N; base < MT_N + n_new; base += MT_GEN_STEP) {
+    if (t < MT_N - MT_M) {   // 227 lanes
+      const long long j = base + t;
+      const uint32_t a = x[(j - 624) & (MT_RING - 1)], b = x[(j - 623) & (MT_RING - 1)], c = x[(j - 227) & (MT_RING - 1)];
+      const uint32_t v0 = c ^ mt_mix((a & 0x80000000u) | (b & 0x7fffffffu));
+      const uint32_t a2 = x[(j - 397) & (MT_RING - 1)], b2 = x[(j - 396) & (MT_RING - 1)];       // both older than `base`
+      const uint32_t v1 = v0 ^ mt_mix((a2 & 0x80000000u) | (b2 & 0x7fffffffu));
+      x[j & (MT_RING - 1)] = v0; x[(j + 227) & (MT_RING - 1)] = v1;
+      raw[j] = v0; raw[j + 227] = v1;
     }
-    const int w = pos + t;
-    uint32_t v = 0;
-    int acc = 0;
-    if (w < MT_N) {
-      v = mt_temper(mt[w]) & mask;
-      acc = (v <= rng) ? 1 : 0;
-    }
-    // block exclusive scan of acc
-    int incl = acc;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += n;
-    }
-    if (lane == 31) warp_tot[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-      int x = (lane < 20) ? warp_tot[lane] : 0;
-      int xi = x;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int n = __shfl_up_sync(0xffffffffu, xi, o);
-        if (lane >= o) xi += n;
-      }
-      if (lane < 20) warp_tot[lane] = xi - x;   // exclusive warp offsets
-      if (lane == 19) s_total = xi;
-    }
-    __syncthreads();
-    const int excl = warp_tot[warp] + incl - acc;
-    const int total = s_total;
-    const long long need = count - produced;
-    if (acc && excl < need) idx_out[produced + excl] = static_cast<int32_t>(v);
-    if (total < need) {
-      if (t == 0) s_newpos = MT_N;          // whole block consumed, more draws needed
-    } else if (acc && excl == need - 1) {
-      s_newpos = w + 1;                     // the word after the last one consumed
-    }
-    __syncthreads();
-    produced += (total < need) ? total : need;
-    if (t == 0) s_pos = s_newpos;
     __syncthreads();
   }
-  if (t < MT_N) state[t] = mt[t];
-  if (t == 0) state[MT_N] = static_cast<uint32_t>(s_pos);
+}
+
+// accepted draws of one chunk: word w is consumed iff w >= pos0 (the unconsumed tail of the current state block comes
+// first) and its masked value is <= rng
+__device__ __forceinline__ int mt_accept(const uint32_t* raw, long long w, long long n_words, long long pos0, uint32_t mask,
+                                         uint32_t rng, uint32_t& v) {
+  if (w >= n_words || w < pos0) return 0;
+  v = mt_temper(raw[w]) & mask;
+  return v <= rng ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256)
+mt_count_kernel(const uint32_t* __restrict__ raw, const uint32_t* __restrict__ state, long long n_words, uint32_t mask, uint32_t rng,
+                int* __restrict__ counts) {
+  __shared__ int red[8];
+  const long long pos0 = state[MT_N];
+  const long long w0 = static_cast<long long>(blockIdx.x) * MT_CHUNK + threadIdx.x * 16;
+  int c = 0;
+  uint32_t v;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) c += mt_accept(raw, w0 + k, n_words, pos0, mask, rng, v);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) { int tsum = 0; for (int i = 0; i < 8; ++i) tsum += red[i]; counts[blockIdx.x] = tsum; }
+}
+
+// exclusive scan of the chunk counts (one CTA; 64-bit running offsets)
+__global__ void __launch_bounds__(1024)
+mt_scan_kernel(const int* __restrict__ counts, long long n_chunks, long long* __restrict__ offsets) {
+  __shared__ long long wsum[32];
+  __shared__ long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (long long c0 = 0; c0 < n_chunks; c0 += 1024) {
+    const long long c = c0 + threadIdx.x;
+    const long long v = c < n_chunks ? counts[c] : 0;
+    long long incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const long long n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    long long before = carry;
+    for (int k = 0; k < warp; ++k) before += wsum[k];
+    if (c < n_chunks) offsets[c] = before + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) offsets[n_chunks] = carry;     // total accepted in the generated words
+}
+
+__global__ void __launch_bounds__(256)
+mt_scatter_kernel(const uint32_t* __restrict__ raw, const uint32_t* __restrict__ state, long long n_words, uint32_t mask, uint32_t rng,
+                  const long long* __restrict__ offsets, long long count, int32_t* __restrict__ idx_out,
+                  uint32_t* __restrict__ new_state) {
+  __shared__ int wtot[8];
+  __shared__ long long s_last;      // stream position of the last consumed word, if it lies in this chunk
+  const long long pos0 = state[MT_N];
+  const long long chunk_off = offsets[blockIdx.x];
+  if (chunk_off >= count) return;                       // everything needed was produced by earlier chunks (uniform per CTA)
+  if (threadIdx.x == 0) s_last = -1;
+  const long long w0 = static_cast<long long>(blockIdx.x) * MT_CHUNK + threadIdx.x * 16;
+  uint32_t v[16];
+  int acc[16], c = 0;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) { acc[k] = mt_accept(raw, w0 + k, n_words, pos0, mask, rng, v[k]); c += acc[k]; }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
+  if (lane == 31) wtot[warp] = incl;
+  __syncthreads();
+  long long off = chunk_off + incl - c;
+  for (int k = 0; k < warp; ++k) off += wtot[k];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    if (acc[k]) {
+      if (off < count) idx_out[off] = static_cast<int32_t>(v[k]);
+      if (off == count - 1) s_last = w0 + k;
+      ++off;
+    }
+  }
+  __syncthreads();
+  const long long e = s_last;
+  if (e >= 0) {          // this CTA saw the last draw: NumPy's state is now the block that contains word e.  It goes to a
+    const long long blk = e / MT_N;   // staging copy: other CTAs are still reading the position out of `state`
+    for (int i = threadIdx.x; i < MT_N; i += blockDim.x) new_state[i] = raw[blk * MT_N + i];
+    if (threadIdx.x == 0) new_state[MT_N] = static_cast<uint32_t>(e - blk * MT_N + 1);
+  }
+}
+
+__global__ void mt_commit_kernel(const uint32_t* __restrict__ new_state, uint32_t* __restrict__ state) {
+  if (new_state[MT_N] == 0xFFFFFFFFu) {   // the generated words did not contain `count` accepted draws (a 40-sigma event)
+    if (threadIdx.x == 0) printf("b2s mt19937_choice: word budget exhausted before the requested draws were produced\n");
+    __trap();
+  }
+  for (int i = threadIdx.x; i <= MT_N; i += blockDim.x) state[i] = new_state[i];
 }
 
 // ---- Philox4x32-10 (counter-based stream for the non-NumPy mode) ----------------------------------
@@ -319,9 +372,43 @@ int b2s_mt19937_choice(uint32_t* state, int32_t n, int64_t count, int32_t* idx_o
   const uint32_t rng = static_cast<uint32_t>(n - 1);
   uint32_t mask = rng;
   mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
-  mt_choice_kernel<<<1, 640, 0, st>>>(state, rng, mask, static_cast<long long>(count), idx_out);
-  B2S_CHECK_LAUNCH();
-  return B2S_OK;
+  // Word budget of a segment of `c` draws: c / p expected (p = n / (mask + 1) >= 1/2), plus 40 standard deviations of the
+  // negative-binomial spread, rounded up to whole generator steps.  mt_commit_kernel traps if that were ever not enough.
+  const double pacc = static_cast<double>(n) / (static_cast<double>(mask) + 1.0);
+  auto words_for = [&](long long c) {
+    const double w = c / pacc + 40.0 * sqrt(static_cast<double>(c) * (1.0 - pacc)) / pacc + 1024.0;
+    return static_cast<long long>(ceil_div(static_cast<int64_t>(w) + 1, MT_GEN_STEP)) * MT_GEN_STEP;
+  };
+  const long long SEG = 1LL << 26;                                   // draws per segment (bounds the scratch to ~0.6 GB)
+  const long long seg_max = count < SEG ? count : SEG;
+  const long long words_max = MT_N + words_for(seg_max);
+  const long long chunks_max = ceil_div(words_max, MT_CHUNK);
+  const size_t raw_bytes = align_up(4 * static_cast<size_t>(words_max), 256);
+  const size_t cnt_bytes = align_up(4 * static_cast<size_t>(chunks_max), 256);
+  const size_t off_bytes = align_up(8 * static_cast<size_t>(chunks_max + 1), 256);
+  uint8_t* scratch = nullptr;
+  B2S_CHECK_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&scratch), raw_bytes + cnt_bytes + off_bytes + 4096, st));
+  uint32_t* raw = reinterpret_cast<uint32_t*>(scratch);
+  int* counts = reinterpret_cast<int*>(scratch + raw_bytes);
+  long long* offsets = reinterpret_cast<long long*>(scratch + raw_bytes + cnt_bytes);
+  uint32_t* new_state = reinterpret_cast<uint32_t*>(scratch + raw_bytes + cnt_bytes + off_bytes);
+  int rc = B2S_OK;
+  for (long long done = 0; done < count && rc == B2S_OK; done += SEG) {
+    const long long c = count - done < SEG ? count - done : SEG;
+    const long long n_new = words_for(c), n_words = MT_N + n_new;
+    const unsigned n_chunks = static_cast<unsigned>(ceil_div(n_words, MT_CHUNK));
+    cudaMemsetAsync(new_state + MT_N, 0xFF, 4, st);
+    mt_gen_kernel<<<1, 256, 0, st>>>(state, raw, n_new);
+    mt_count_kernel<<<n_chunks, 256, 0, st>>>(raw, state, n_words, mask, rng, counts);
+    mt_scan_kernel<<<1, 1024, 0, st>>>(counts, n_chunks, offsets);
+    mt_scatter_kernel<<<n_chunks, 256, 0, st>>>(raw, state, n_words, mask, rng, offsets, c, idx_out + done, new_state);
+    mt_commit_kernel<<<1, 640, 0, st>>>(new_state, state);
+    g_launch_count.fetch_add(4, std::memory_order_relaxed);
+    if (cudaGetLastError() != cudaSuccess) { set_error("mt19937_choice: kernel launch failed"); rc = B2S_ECUDA; }
+    g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  }
+  cudaFreeAsync(scratch, st);
+  return rc;
 }
 
 int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t n, int64_t B, const int32_t* idx,
