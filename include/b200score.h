@@ -50,8 +50,10 @@ enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQ
  *               beyond 65504: such prompts come back flagged (B2S_ERANGE, NaN rows), never as numbers;
  *   BF16_SPLIT  bf16 weight matrices untouched; every GEMM A operand is kept as two bf16 halves hi = bf16(x),
  *               lo = bf16(x - hi) (16 mantissa bits, bf16 range) and both halves meet the same weights in the same fp32
- *               accumulator: holds the gate with bf16's range at twice the tensor work.  Q/K/V/P inside attention stay
- *               bf16.  Needs d_model, d_ff and n_head*head_dim to be multiples of 64;
+ *               accumulator: holds the gate with bf16's range in every linear layer at twice the tensor work.  Attention has
+ *               no split form: q/k/v, the KV cache and P are fp16 there (an overflow surfaces as B2S_ERANGE like in the
+ *               FP16 mode; q/k/v are LayerNorm-fed projections, not where decoder outliers live).  Needs d_model, d_ff
+ *               and n_head*head_dim to be multiples of 64;
  *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5). */
 enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3 };
 

@@ -172,27 +172,34 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
   if (valid) {
     const float inv = 1.f / lsum;
     uint4* dst = reinterpret_cast<uint4*>(out_row);
+    if (lo_off) {
+      // BF16_SPLIT: the dense projection reads this row as [hi | lo] bf16 halves, whatever format Q/K/V/P had
+      uint4* dlo = reinterpret_cast<uint4*>(out_row + lo_off);
+      auto hi = [inv](float x) { return x * inv; };
+      auto rem = [inv](float x) { const float y = x * inv; return y - __bfloat162float(__float2bfloat16_rn(y)); };
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
-      dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
-                          pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-      dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
-                              pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
-    if constexpr (!F16) {
-      if (lo_off) {      // BF16_SPLIT: the dense projection reads [hi | lo]; lo = bf16(o - bf16(o))
-        uint4* dlo = reinterpret_cast<uint4*>(out_row + lo_off);
-        auto rem = [inv](float x) { const float y = x * inv; return y - __bfloat162float(__float2bfloat16_rn(y)); };
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          dlo[q] = make_uint4(pack_bf16x2(rem(o0[8 * q]), rem(o0[8 * q + 1])), pack_bf16x2(rem(o0[8 * q + 2]), rem(o0[8 * q + 3])),
-                              pack_bf16x2(rem(o0[8 * q + 4]), rem(o0[8 * q + 5])), pack_bf16x2(rem(o0[8 * q + 6]), rem(o0[8 * q + 7])));
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          dlo[4 + q] = make_uint4(pack_bf16x2(rem(o1[8 * q]), rem(o1[8 * q + 1])), pack_bf16x2(rem(o1[8 * q + 2]), rem(o1[8 * q + 3])),
-                                  pack_bf16x2(rem(o1[8 * q + 4]), rem(o1[8 * q + 5])), pack_bf16x2(rem(o1[8 * q + 6]), rem(o1[8 * q + 7])));
+      for (int q = 0; q < 4; ++q) {
+        dst[q] = make_uint4(pack_bf16x2(hi(o0[8 * q]), hi(o0[8 * q + 1])), pack_bf16x2(hi(o0[8 * q + 2]), hi(o0[8 * q + 3])),
+                            pack_bf16x2(hi(o0[8 * q + 4]), hi(o0[8 * q + 5])), pack_bf16x2(hi(o0[8 * q + 6]), hi(o0[8 * q + 7])));
+        dlo[q] = make_uint4(pack_bf16x2(rem(o0[8 * q]), rem(o0[8 * q + 1])), pack_bf16x2(rem(o0[8 * q + 2]), rem(o0[8 * q + 3])),
+                            pack_bf16x2(rem(o0[8 * q + 4]), rem(o0[8 * q + 5])), pack_bf16x2(rem(o0[8 * q + 6]), rem(o0[8 * q + 7])));
       }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        dst[4 + q] = make_uint4(pack_bf16x2(hi(o1[8 * q]), hi(o1[8 * q + 1])), pack_bf16x2(hi(o1[8 * q + 2]), hi(o1[8 * q + 3])),
+                                pack_bf16x2(hi(o1[8 * q + 4]), hi(o1[8 * q + 5])), pack_bf16x2(hi(o1[8 * q + 6]), hi(o1[8 * q + 7])));
+        dlo[4 + q] = make_uint4(pack_bf16x2(rem(o1[8 * q]), rem(o1[8 * q + 1])), pack_bf16x2(rem(o1[8 * q + 2]), rem(o1[8 * q + 3])),
+                                pack_bf16x2(rem(o1[8 * q + 4]), rem(o1[8 * q + 5])), pack_bf16x2(rem(o1[8 * q + 6]), rem(o1[8 * q + 7])));
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
+                            pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
+                                pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
     }
   }
 }

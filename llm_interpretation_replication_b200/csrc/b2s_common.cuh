@@ -79,7 +79,7 @@ struct RopeEpiArgs {
 // accumulate); out_split: a 16-bit store epilogue writes its result in that form, [M, 2N], for the GEMM that follows.
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K,
                    int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0, const RopeEpiArgs* rope = nullptr,
-                   int a_split = 0, int out_split = 0);
+                   int a_split = 0, int out_split = 0, int out_f16 = -1 /* 16-bit outputs as fp16; -1 = as the operands */);
 int gemm_f32_launch(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
                     int epilogue, cudaStream_t st);
 

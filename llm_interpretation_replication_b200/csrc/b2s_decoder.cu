@@ -418,14 +418,21 @@ attn_kernel(AttnArgs a) {
     }
     const float inv = 1.f / l;
     const size_t owidth = static_cast<size_t>(a.nh) * HD;
-    AT* op = out + row * (owidth * (a.split ? 2 : 1)) + h * HD;
+    AT* op = out + row * owidth + h * HD;
+    // BF16_SPLIT: the dense projection reads the row as [hi | lo] bf16 halves, whatever format Q/K/V are stored in
+    __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + row * (2 * owidth) + h * HD;
 #pragma unroll
     for (int r = 0; r < DPL; ++r) {
       const int dd = lane + 32 * r;
       if (dd < HD) {
         const float o = acc[r] * inv;
-        op[dd] = from_f32<AT>(o);
-        if (a.split) op[owidth + dd] = from_f32<AT>(o - to_f32(from_f32<AT>(o)));   // BF16_SPLIT: rounding remainder
+        if (a.split) {
+          const __nv_bfloat16 hi = __float2bfloat16_rn(o);
+          ob[dd] = hi;
+          ob[owidth + dd] = __float2bfloat16_rn(o - __bfloat162float(hi));
+        } else {
+          op[dd] = from_f32<AT>(o);
+        }
       }
     }
     __syncwarp();

@@ -45,6 +45,7 @@ struct GemmParams {
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
+  int out_f16;           // the 16-bit outputs are fp16 (normally = act_f16; BF16_SPLIT writes fp16 q/k/v from bf16 operands)
   int k_wrap;            // BF16_SPLIT: A is [M, 2K] = [hi | lo] and num_kb counts its k-blocks; the W box of k-block kb is
                          // kb - k_wrap once kb >= k_wrap (0 = A and W walk K together)
   int out_split;         // BF16_SPLIT, 16-bit store epilogues: the output is [M, 2N]; hi goes to column c, lo to out_split + c
@@ -111,10 +112,10 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
     for (int j = 0; j < 32; j += 8) {
       if (col0 + j < N) {   // N % 8 == 0 is required by the launcher
         uint4 w;
-        w.x = pack_act16x2(v[j], v[j + 1], p.act_f16);
-        w.y = pack_act16x2(v[j + 2], v[j + 3], p.act_f16);
-        w.z = pack_act16x2(v[j + 4], v[j + 5], p.act_f16);
-        w.w = pack_act16x2(v[j + 6], v[j + 7], p.act_f16);
+        w.x = pack_act16x2(v[j], v[j + 1], p.out_f16);
+        w.y = pack_act16x2(v[j + 2], v[j + 3], p.out_f16);
+        w.z = pack_act16x2(v[j + 4], v[j + 5], p.out_f16);
+        w.w = pack_act16x2(v[j + 6], v[j + 7], p.out_f16);
         *reinterpret_cast<uint4*>(o + j) = w;
       }
     }
@@ -235,12 +236,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int row, int 
       uint4* d4 = reinterpret_cast<uint4*>(dst);
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        d4[q] = make_uint4(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.act_f16), pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.act_f16),
-                           pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.act_f16), pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.act_f16));
+        d4[q] = make_uint4(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.out_f16), pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.out_f16),
+                           pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.out_f16), pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.out_f16));
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        d4[4 + q] = make_uint4(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.act_f16), pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.act_f16),
-                               pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.act_f16), pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.act_f16));
+        d4[4 + q] = make_uint4(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.out_f16), pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.out_f16),
+                               pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.out_f16), pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.out_f16));
     }
   } else if constexpr (EPI == EPI_RESID_F32) {
     // read-modify-write of the fp32 residual: the loads of chunk c+1 are in flight while chunk c is processed
@@ -392,17 +393,17 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
             uint4* d4 = reinterpret_cast<uint4*>(dst);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              d4[q] = make_uint4(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.act_f16), pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.act_f16),
-                                 pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.act_f16), pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.act_f16));
-              d4[4 + q] = make_uint4(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.act_f16), pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.act_f16),
-                                     pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.act_f16), pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.act_f16));
+              d4[q] = make_uint4(pack_act16x2(x1[8 * q], x1[8 * q + 1], p.out_f16), pack_act16x2(x1[8 * q + 2], x1[8 * q + 3], p.out_f16),
+                                 pack_act16x2(x1[8 * q + 4], x1[8 * q + 5], p.out_f16), pack_act16x2(x1[8 * q + 6], x1[8 * q + 7], p.out_f16));
+              d4[4 + q] = make_uint4(pack_act16x2(x2[8 * q], x2[8 * q + 1], p.out_f16), pack_act16x2(x2[8 * q + 2], x2[8 * q + 3], p.out_f16),
+                                     pack_act16x2(x2[8 * q + 4], x2[8 * q + 5], p.out_f16), pack_act16x2(x2[8 * q + 6], x2[8 * q + 7], p.out_f16));
             }
           }
         }
       }
       if (to_cache) continue;
       next_buffer(stage, my_line);
-      if (p.act_f16) stage_store16<true>(my_line, sw, x1, x2); else stage_store16<false>(my_line, sw, x1, x2);
+      if (p.out_f16) stage_store16<true>(my_line, sw, x1, x2); else stage_store16<false>(my_line, sw, x1, x2);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) { tma_store_2d(tmC, stage, col0, row0); tma_store_commit(); }
@@ -1131,7 +1132,8 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
 }
 
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
-                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope, int a_split, int out_split) {
+                   const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope, int a_split, int out_split,
+                   int out_f16) {
   B2S_REQUIRE(!a_split || (K % BK == 0 && !act_f16), "gemm_bf16: split activations need K %% 64 == 0 and bf16 operands (K=%d)", K);
   B2S_REQUIRE(!out_split || (N % 64 == 0 && g_opt_tma_store && (epilogue == EPI_STORE_BF16 || epilogue == EPI_GELU_BF16)),
               "gemm_bf16: a split 16-bit output needs N %% 64 == 0, the TMA-store epilogue and a 16-bit store epilogue (N=%d)", N);
@@ -1179,6 +1181,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   }
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
+  p.out_f16 = out_f16 < 0 ? p.act_f16 : (out_f16 ? 1 : 0);
   {
     // 0 none | 1 A first, W last | 2 A last, W first | 3 both last | 4 both normal | 5 W last | 6 A first | 7 A normal, W last
     static const unsigned long long HA[8] = {0ull, HINT_EVICT_FIRST, HINT_EVICT_LAST, HINT_EVICT_LAST, HINT_EVICT_NORMAL, 0ull, HINT_EVICT_FIRST, HINT_EVICT_NORMAL};
@@ -1193,7 +1196,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   if (p.tma_store) {
     const bool f32 = epilogue == EPI_RESID_F32 || epilogue == EPI_STORE_F32;
     const uint64_t NC = static_cast<uint64_t>(N) * (out_split ? 2 : 1);
-    B2S_TRY(make_tmap_2d(&tc, out, static_cast<uint64_t>(M), NC, NC * (f32 ? 4 : 2), 32, f32 ? 32 : 64, f32 ? 4 : 2, act_f16));
+    B2S_TRY(make_tmap_2d(&tc, out, static_cast<uint64_t>(M), NC, NC * (f32 ? 4 : 2), 32, f32 ? 32 : 64, f32 ? 4 : 2, p.out_f16));
   }
   switch (epilogue) {
     case EPI_STORE_BF16: return launch_epi<EPI_STORE_BF16>(ta, tb, tb2, ta3, tc, p, st);

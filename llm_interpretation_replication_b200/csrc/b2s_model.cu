@@ -6,6 +6,7 @@
 // the look-ahead scan (:348-363) is unresolved.
 #include "b2s_decoder.cuh"
 #include <stdarg.h>
+#include <type_traits>
 #include <vector>
 
 namespace b2s {
@@ -127,9 +128,13 @@ int linear(const b2s_model* m, const void* A, const void* W, const float* bias, 
                          reinterpret_cast<float*>(out), M, N, K, epi, st);
 }
 
-template <typename AT, typename WT>
+// AT: type of the GEMM A operands (LayerNorm / activation outputs); WT: weight matrices; QT: q/k/v, the KV cache and P
+// inside attention.  QT == AT except in BF16_SPLIT, where the linear layers see bf16 [hi | lo] halves and attention, which
+// has no split form, works on fp16 (3 more mantissa bits than bf16; an overflow there surfaces as B2S_ERANGE).
+template <typename AT, typename WT, typename QT = AT>
 int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
               int max_qlen, cudaStream_t st) {
+  const int q_f16 = std::is_same<QT, __half>::value ? 1 : 0;
   const b2s_model_desc& d = m->d;
   const int dm = d.d_model;
   const bool two_ln = d.n_ln_per_layer == 2;
@@ -166,10 +171,13 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       re.sin = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_SIN));
       re.kcache = kc; re.vcache = vc; re.nh = d.n_head; re.nkv = d.n_kv_head;
       B2S_TRY(gemm_tc_launch(w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
-                             EPI_QKV_ROPE, nullptr, st, m->act_f16, &re, m->split, 0));
+                             EPI_QKV_ROPE, nullptr, st, m->act_f16, &re, m->split, 0, q_f16));
     } else {
-      B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
-                     EPI_STORE_BF16, st));
+      if (m->bf16)
+        B2S_TRY(gemm_tc_launch(w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm, EPI_STORE_BF16,
+                               nullptr, st, m->act_f16, nullptr, m->split, 0, q_f16));
+      else
+        B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm, EPI_STORE_BF16, st));
       RopeArgs ro{};
       ro.qkv = w.qkv; ro.kcache = kc; ro.vcache = vc; ro.pos = w.meta.pos; ro.slot = w.meta.slot;
       ro.cos = reinterpret_cast<const float*>(m->gw(B2S_W_ROPE_COS));
@@ -177,7 +185,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       ro.qkv_dim = m->qkv_dim; ro.nh = d.n_head; ro.nkv = d.n_kv_head; ro.hd = d.head_dim; ro.rd = d.rotary_dim;
       ro.q_base = m->q_base; ro.q_hstride = m->q_hstride; ro.k_base = m->k_base; ro.v_base = m->v_base;
       ro.kv_hstride = m->kv_hstride;
-      B2S_TRY(launch_rope_cache<AT>(ro, rows, st));
+      B2S_TRY(launch_rope_cache<QT>(ro, rows, st));
     }
 
     AttnArgs at{};
@@ -185,7 +193,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.qkv_dim = m->qkv_dim; at.nh = d.n_head; at.nkv = d.n_kv_head; at.hd = d.head_dim; at.rep = d.n_head / d.n_kv_head;
     at.q_base = m->q_base; at.q_hstride = m->q_hstride; at.max_kv = max_kv;
     at.heads_per_cta = (max_qlen == 1) ? at.rep : ATT_HG;
-    at.f16 = m->act_f16;
+    at.f16 = q_f16;
     at.split = m->split;
     at.alibi = d.pos_type == B2S_POS_ALIBI ? reinterpret_cast<const float*>(m->gw(B2S_W_ALIBI)) : nullptr;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
@@ -195,7 +203,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     if (tc_ok) {
       B2S_TRY(launch_attn_tc(at, n_seqs, rows, static_cast<int>(w.cache_slots), max_qlen, st));
     } else {
-      B2S_TRY(launch_attn<AT>(at, n_seqs, st));
+      B2S_TRY(launch_attn<QT>(at, n_seqs, st));
     }
 
     B2S_TRY(linear(m, w.attn, m->lw(l, B2S_WL_W_DENSE), m->lwf(l, B2S_WL_B_DENSE), w.resid, rows, dm,
@@ -239,6 +247,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
 
 int forward(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
             int max_qlen, cudaStream_t st) {
+  if (m->bf16 && m->split) return forward_t<__nv_bfloat16, __nv_bfloat16, __half>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
   if (m->bf16 && m->act_f16) return forward_t<__half, __half>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
   if (m->bf16) return forward_t<__nv_bfloat16, __nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
   return forward_t<float, float>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);

@@ -15,7 +15,7 @@ Follows, for the two families on the hot path:
            do_layer_norm_before (pre-LN, sequential residual), ReLU MLP, q/k/v/out projections with biases, no rotary
   BLOOM    HF:models/bloom/modeling_bloom.py word_embeddings_layernorm, build_alibi_tensor (slope[h] * key position
            added to the scaled scores), per-head [q,k,v] fused projection, bloom_gelu_forward (tanh GELU), BloomBlock
-It is validated against the HF modules themselves in tests/test_oracle_decoder.py, and is what the
+It is validated against the HF modules themselves in tests/test_oracle_cpu.py (test_torch_decoder_restatement_matches_reference), and is what the
 GPU parity tests call (it is faster than ``generate`` and can emulate bf16 operand rounding).
 """
 from __future__ import annotations
@@ -62,10 +62,12 @@ def _split_qkv(shape: DecoderShape, qkv):
 
 
 def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.Tensor,
-                   round_act: Optional[Callable] = None, dtype=torch.float32) -> torch.Tensor:
+                   round_act: Optional[Callable] = None, dtype=torch.float32, round_attn: Optional[Callable] = None) -> torch.Tensor:
     """ids [L] -> hidden after the final LayerNorm, [L, d].  ``round_act`` (e.g. bf16 round trip) is
-    applied to every GEMM input and to q/k/v, emulating bf16 MMA operands with fp32 accumulate."""
+    applied to every GEMM input and to q/k/v, emulating bf16 MMA operands with fp32 accumulate; ``round_attn``
+    overrides it for q/k/v (the BF16_SPLIT mode keeps those in fp16 while the GEMM inputs are hi + lo bf16 halves)."""
     r = round_act if round_act is not None else (lambda t: t)
+    ra = round_attn if round_attn is not None else r
     d, nh, nkv, hd = shape.d_model, shape.n_head, shape.n_kv_head, shape.head_dim
     L = ids.shape[0]
     rope = shape.pos_type == POS_ROPE
@@ -107,8 +109,8 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         q, k, v = _split_qkv(shape, qkv)
         if rope:
             q, k = _apply_rope(q, cos, sin, shape.rotary_dim), _apply_rope(k, cos, sin, shape.rotary_dim)
-        q, k = r(q), r(k)
-        v = r(v)
+        q, k = ra(q), ra(k)
+        v = ra(v)
         rep = nh // k.shape[1]
         kk = k.repeat_interleave(rep, dim=1)
         vv = v.repeat_interleave(rep, dim=1)
@@ -133,9 +135,9 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
     return norm(x, "lnf_g", "lnf_b")
 
 
-def last_logits(shape, W, ids, round_act=None, dtype=torch.float32) -> torch.Tensor:
+def last_logits(shape, W, ids, round_act=None, dtype=torch.float32, round_attn=None) -> torch.Tensor:
     r = round_act if round_act is not None else (lambda t: t)
-    h = forward_hidden(shape, W, ids, round_act, dtype)[-1]
+    h = forward_hidden(shape, W, ids, round_act, dtype, round_attn)[-1]
     return F.linear(r(h), W["lm_head"].to(dtype)).float()
 
 

@@ -21,14 +21,15 @@ def _tol(mode_name):
 
 
 def _rnd(mode_name):
-    """Operand rounding of each 16-bit mode for the emulating oracle (decoder_ref.forward_hidden round_act)."""
+    """Operand rounding of each 16-bit mode for the emulating oracle: kwargs of decoder_ref.last_logits."""
     from oracle import decoder_ref
+    f16 = lambda t: t.to(torch.float16).to(t.dtype)
     if mode_name == "MODE_BF16_FAST":
-        return decoder_ref.bf16_round
+        return dict(round_act=decoder_ref.bf16_round)
     if mode_name == "MODE_FP16":
-        return lambda t: t.to(torch.float16).to(t.dtype)
-    # BF16_SPLIT: hi + lo bf16 halves (the attention operands, which stay plain bf16 on the GPU, are covered by the tolerance)
-    return lambda t: decoder_ref.bf16_round(t) + decoder_ref.bf16_round(t - decoder_ref.bf16_round(t))
+        return dict(round_act=f16)
+    # BF16_SPLIT: GEMM inputs as hi + lo bf16 halves, q/k/v in fp16
+    return dict(round_act=lambda t: decoder_ref.bf16_round(t) + decoder_ref.bf16_round(t - decoder_ref.bf16_round(t)), round_attn=f16)
 
 
 MODES_16 = ["MODE_BF16_FAST", "MODE_FP16", "MODE_BF16_SPLIT"]
@@ -192,7 +193,7 @@ def test_scorer_real_dims_bf16_vs_bf16_emulating_oracle(mode_name):
     ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (66, 111, 190, 128, 97)]
     rows, gens = sc.score_ids(ids, np.array([[1000, 2000]]), topk=5, max_lookahead=2)
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), **_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[1000] / (p[1000] + p[2000])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
@@ -215,7 +216,7 @@ def test_scorer_real_dims_neox_bf16(maker, lens, mode_name):
     ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in lens]
     rows, gens = sc.score_ids(ids, np.array([[500, 600]]), topk=5, max_lookahead=2)
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), **_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[500] / (p[500] + p[600])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
@@ -236,7 +237,7 @@ def test_scorer_real_dims_mistral(mode_name):
     ids = [g.randint(3, shp.vocab - 3, size=L).tolist() for L in (23, 111, 64)]
     rows, gens = sc.score_ids(ids, np.array([[700, 900]]), topk=5, max_lookahead=2)
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), **_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[700] / (p[700] + p[900])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
@@ -262,7 +263,7 @@ def test_scorer_real_dims_opt_bloom(maker, mode_name):
     ids = [g.randint(4, shp.vocab - 3, size=L).tolist() for L in (19, 111, 70)]
     rows, gens = sc.score_ids(ids, np.array([[700, 900]]), topk=5, max_lookahead=2)
     for i, x in enumerate(ids):
-        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), round_act=_rnd(mode_name))
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), **_rnd(mode_name))
         p = torch.softmax(lo, -1)
         rel = (p[700] / (p[700] + p[900])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
