@@ -238,6 +238,63 @@ boot_resample_kernel(const double* __restrict__ vals, int F, int split, int n, l
   }
 }
 
+// Index-table fast path (n <= 256, n % 4 == 0; the BASELINE sizes).  The table is the only HBM stream (B * n * 4 bytes)
+// and must be read at HBM speed, which the thread-per-row kernel above cannot do: a warp there touches 32 different rows
+// per load.  Here a CTA stages the rows of 256 resamples with fully coalesced 16-byte loads, packs each index into one
+// byte and stores the rows in shared memory with a stride of an odd number of words, so that afterwards thread t walks
+// row t four indices per conflict-free 32-bit load.  The fp64 value gather is the other co-limiter (B * n * F shared
+// loads): the [F, n] table is replicated 16 times, element e of copy c at word pair e * 16 + c, and thread t uses copy
+// t mod 16 -- every lane of a half-warp then owns its bank pair and the gather never conflicts.  The sums run in index
+// order exactly as in the kernel above (same bits).
+constexpr int BT_ROWS = 256;
+__global__ void __launch_bounds__(BT_ROWS)
+boot_resample_tile_kernel(const double* __restrict__ vals, int F, int split, int n, long long B, const int32_t* __restrict__ idx,
+                          double* __restrict__ boot, int stride_words) {
+  extern __shared__ double sv[];                                   // [F * n][16] replicated values
+  uint32_t* sidx = reinterpret_cast<uint32_t*>(sv + static_cast<size_t>(F) * n * 16);   // [BT_ROWS][stride_words] packed indices
+  for (int i = threadIdx.x; i < F * n * 16; i += BT_ROWS) sv[i] = vals[i >> 4];
+  const int n4 = n >> 2;
+  const long long tiles = (B + BT_ROWS - 1) / BT_ROWS;
+  const int copy = threadIdx.x & 15;
+  for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    __syncthreads();                                               // the previous tile's rows have been consumed (and sv is filled)
+    const long long b0 = tile * BT_ROWS;
+    const int R = static_cast<int>(B - b0 < BT_ROWS ? B - b0 : BT_ROWS);
+    const int4* g = reinterpret_cast<const int4*>(idx + b0 * n);
+    const int nq = R * n4;
+#pragma unroll 5
+    for (int q = threadIdx.x; q < nq; q += BT_ROWS) {
+      int4 v;
+      asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(g + q));
+      const int r = q / n4, c4 = q - r * n4;
+      sidx[r * stride_words + c4] = static_cast<uint32_t>(v.x) | (static_cast<uint32_t>(v.y) << 8) | (static_cast<uint32_t>(v.z) << 16) |
+                                    (static_cast<uint32_t>(v.w) << 24);
+    }
+    __syncthreads();
+    if (threadIdx.x < R) {
+      const uint32_t* row = sidx + threadIdx.x * stride_words;
+      double lo = 0.0, hi = 0.0, ab = 0.0;
+      for (int j4 = 0; j4 < n4; ++j4) {
+        const uint32_t w = row[j4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int id = (w >> (8 * u)) & 255;
+          for (int f = 0; f < F; ++f) {
+            const double x = sv[(f * n + id) * 16 + copy];
+            if (f < split) lo += x; else hi += x;
+            ab += fabs(x);
+          }
+        }
+      }
+      const long long b = b0 + threadIdx.x;
+      const double nlo = static_cast<double>(split) * n, nhi = static_cast<double>(F - split) * n;
+      boot[b * 3 + 0] = split > 0 ? lo / nlo : nan("");
+      boot[b * 3 + 1] = F > split ? hi / nhi : nan("");
+      boot[b * 3 + 2] = ab / (static_cast<double>(F) * n);
+    }
+  }
+}
+
 // ---- summary: select statistic, sort, percentiles, tail fractions -----------------------------------
 __device__ __forceinline__ double boot_stat(const double* boot, long long b, int stat) {
   if (stat == 0) return boot[b * 3];
@@ -419,6 +476,23 @@ int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t
   const size_t smem = static_cast<size_t>(F) * n * sizeof(double);
   B2S_REQUIRE(smem <= 200 * 1024, "bootstrap_resample: F*n=%d values exceed the shared-memory table (25600)", F * n);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  {
+    int dev = 0, sms = 0;
+    B2S_CHECK_CUDA(cudaGetDevice(&dev));
+    B2S_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int sw = (n + 3) / 4;
+    if (sw % 2 == 0) ++sw;                                              // odd word stride: conflict-free row walks
+    const size_t tile_smem = static_cast<size_t>(F) * n * 16 * sizeof(double) + static_cast<size_t>(BT_ROWS) * sw * 4;
+    if (idx != nullptr && n % 4 == 0 && n <= 256 && (reinterpret_cast<uintptr_t>(idx) & 15) == 0 && tile_smem <= 110 * 1024) {
+      B2S_CHECK_CUDA(cudaFuncSetAttribute(boot_resample_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tile_smem)));
+      const long long tiles = ceil_div(B, BT_ROWS);
+      const int per_sm = static_cast<int>((220 * 1024) / (tile_smem + 1024));
+      const long long cap = static_cast<long long>(sms) * (per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm));
+      boot_resample_tile_kernel<<<static_cast<unsigned>(tiles < cap ? tiles : cap), BT_ROWS, tile_smem, st>>>(vals, F, split, n, B, idx, boot, sw);
+      B2S_CHECK_LAUNCH();
+      return B2S_OK;
+    }
+  }
   if (smem > 48 * 1024)
     B2S_CHECK_CUDA(cudaFuncSetAttribute(boot_resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   int dev = 0, sms = 0;

@@ -147,3 +147,34 @@ def test_entry_point_4_schema(tmp_path):
         assert o[k]["ci_lower"] <= o[k]["mean"] + 0.05 and o[k]["ci_upper"] >= o[k]["mean"] - 0.05
     assert len(res["per_model_results"]) >= 10          # models whose rel_probs are all finite
     assert os.path.exists(os.path.join(tmp_path, "bootstrap_confidence_intervals.json"))
+
+
+@pytest.mark.parametrize("n,F,split,B", [(100, 2, 1, 10_000), (100, 6, 3, 1000), (48, 1, 1, 777), (256, 2, 1, 300), (4, 3, 0, 513),
+                                         (49, 2, 1, 1000), (300, 2, 1, 500)])
+def test_resample_kernels_match_numpy(n, F, split, B):
+    """Index-table resampling against numpy on the same table: the staged, coalesced kernel (n % 4 == 0, n <= 256) and the
+    general one (n = 49, 300), ragged last tile included."""
+    from llm_interpretation_replication_b200 import bootstrap as Bm
+    rs = np.random.RandomState(n + F)
+    vals = rs.normal(0.1, 0.4, size=(F, n))
+    idx = rs.randint(0, n, size=(B, n)).astype(np.int32)
+    boot = Bm.resample(vals, split, B, torch.from_numpy(idx.reshape(-1)).cuda()).cpu().numpy()
+    g = vals[:, idx]                                         # [F, B, n]
+    if split > 0:
+        assert np.allclose(boot[:, 0], g[:split].mean(axis=(0, 2)), rtol=0, atol=1e-13)
+    else:
+        assert np.isnan(boot[:, 0]).all()
+    if F > split:
+        assert np.allclose(boot[:, 1], g[split:].mean(axis=(0, 2)), rtol=0, atol=1e-13)
+    assert np.allclose(boot[:, 2], np.abs(g).mean(axis=(0, 2)), rtol=0, atol=1e-13)
+
+
+def test_mt19937_choice_large_and_state_after():
+    """Several million draws in one call (many generator steps, many compaction chunks), then the stream must continue
+    exactly where numpy's does -- the state handed back is the 624-word block of the last consumed word."""
+    from llm_interpretation_replication_b200.bootstrap import NumpyLegacyStream
+    rs = NumpyLegacyStream(123)
+    np.random.seed(123)
+    for n, count in ((100, 3_000_000), (7, 1), (100, 623), (65, 100_001), (2, 624 * 3)):
+        got = rs.choice(n, count).cpu().numpy()
+        assert np.array_equal(got, np.random.choice(n, size=count, replace=True)), (n, count)
