@@ -79,7 +79,8 @@ struct RopeEpiArgs {
 // accumulate); out_split: a 16-bit store epilogue writes its result in that form, [M, 2N], for the GEMM that follows.
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K,
                    int epilogue, const LmHeadArgs* lmh, cudaStream_t st, int act_f16 = 0, const RopeEpiArgs* rope = nullptr,
-                   int a_split = 0, int out_split = 0, int out_f16 = -1 /* 16-bit outputs as fp16; -1 = as the operands */);
+                   int a_split = 0, int out_split = 0, int out_f16 = -1 /* 16-bit outputs as fp16; -1 = as the operands */,
+                   int act_kind = 0 /* EPI_GELU_BF16: B2S_ACT_* applied in the epilogue */);
 int gemm_f32_launch(const float* A, const float* W, const float* bias, float* out, int M, int N, int K,
                     int epilogue, cudaStream_t st);
 
@@ -102,6 +103,13 @@ __device__ __forceinline__ float gelu_fast(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-ax * ax * 1.4426950408889634f));
   const float h = 0.5f * q * e;
   return x * (x >= 0.f ? 1.0f - h : h);
+}
+// MLP activation of the fused "activation + 16-bit store" epilogue: erf-GELU (HF falcon / gpt_neox), ReLU (HF opt), tanh-GELU
+// (HF bloom bloom_gelu_forward)
+__device__ __forceinline__ float mlp_act(float x, int kind) {
+  if (kind == B2S_ACT_RELU) return fmaxf(x, 0.f);
+  if (kind == B2S_ACT_GELU_TANH) return x * 0.5f * (1.0f + tanhf(0.79788456f * x * (1.0f + 0.044715f * x * x)));
+  return gelu_fast(x);
 }
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);

@@ -45,6 +45,7 @@ struct GemmParams {
   unsigned long long hint_a, hint_b;   // L2 cache-policy words for the TMA loads (0 = none)
   int tma_store;         // epilogue through shared memory + TMA bulk stores / reduce-adds
   int act_f16;           // both operands and the 16-bit outputs are fp16 instead of bf16 (idesc a/b_format F16)
+  int act_kind;          // EPI_GELU_BF16: B2S_ACT_GELU (erf), B2S_ACT_RELU or B2S_ACT_GELU_TANH applied to acc + bias before the store
   int out_f16;           // the 16-bit outputs are fp16 (normally = act_f16; BF16_SPLIT writes fp16 q/k/v from bf16 operands)
   int k_wrap;            // BF16_SPLIT: A is [M, 2K] = [hi | lo] and num_kb counts its k-blocks; the W box of k-block kb is
                          // kb - k_wrap once kb >= k_wrap (0 = A and W walk K together)
@@ -105,7 +106,7 @@ __device__ __forceinline__ void epi_chunk(const GemmParams& p, int row, int col0
   if constexpr (EPI == EPI_STORE_BF16 || EPI == EPI_GELU_BF16) {
     if constexpr (EPI == EPI_GELU_BF16) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = gelu_fast(v[j]);
+      for (int j = 0; j < 32; ++j) v[j] = mlp_act(v[j], p.act_kind);
     }
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(row) * N + col0;
 #pragma unroll
@@ -365,8 +366,13 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
         }
       }
       if constexpr (EPI == EPI_GELU_BF16) {
+        if (p.act_kind == B2S_ACT_GELU) {      // the bench family: no per-element branch
 #pragma unroll
-        for (int j = 0; j < 32; ++j) { x1[j] = gelu_fast(x1[j]); x2[j] = gelu_fast(x2[j]); }
+          for (int j = 0; j < 32; ++j) { x1[j] = gelu_fast(x1[j]); x2[j] = gelu_fast(x2[j]); }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { x1[j] = mlp_act(x1[j], p.act_kind); x2[j] = mlp_act(x2[j], p.act_kind); }
+        }
       }
       bool to_cache = false;
       if constexpr (EPI == EPI_QKV_ROPE) {
@@ -1133,7 +1139,7 @@ static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const CUtens
 
 int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, int M, int N, int K, int epilogue,
                    const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope, int a_split, int out_split,
-                   int out_f16) {
+                   int out_f16, int act_kind) {
   B2S_REQUIRE(!a_split || (K % BK == 0 && !act_f16), "gemm_bf16: split activations need K %% 64 == 0 and bf16 operands (K=%d)", K);
   B2S_REQUIRE(!out_split || (N % 64 == 0 && g_opt_tma_store && (epilogue == EPI_STORE_BF16 || epilogue == EPI_GELU_BF16)),
               "gemm_bf16: a split 16-bit output needs N %% 64 == 0, the TMA-store epilogue and a 16-bit store epilogue (N=%d)", N);
@@ -1182,6 +1188,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   p.out = out; p.bias = bias;
   p.act_f16 = act_f16 ? 1 : 0;
   p.out_f16 = out_f16 < 0 ? p.act_f16 : (out_f16 ? 1 : 0);
+  p.act_kind = act_kind;
   {
     // 0 none | 1 A first, W last | 2 A last, W first | 3 both last | 4 both normal | 5 W last | 6 A first | 7 A normal, W last
     static const unsigned long long HA[8] = {0ull, HINT_EVICT_FIRST, HINT_EVICT_LAST, HINT_EVICT_LAST, HINT_EVICT_NORMAL, 0ull, HINT_EVICT_FIRST, HINT_EVICT_NORMAL};

@@ -103,7 +103,7 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.act = take(at * am * rows * d.d_ff);
   // MLP pre-activations that a separate kernel turns into the activation: gate | up before SwiGLU; in BF16_SPLIT also
   // the ReLU / tanh-GELU pre-activations, and then in fp32 so that nothing is rounded before the [hi | lo] split
-  const bool pre_buf = d.mlp_type == B2S_MLP_SWIGLU || (m->split && d.act_type != B2S_ACT_GELU);
+  const bool pre_buf = d.mlp_type == B2S_MLP_SWIGLU;
   w.gu = pre_buf ? take((m->split ? 4 : at) * rows * (d.mlp_type == B2S_MLP_SWIGLU ? 2 : 1) * d.d_ff) : nullptr;
   w.hfin = take(at * am * static_cast<size_t>(N) * d.d_model);
   const size_t slots = static_cast<size_t>(T) + static_cast<size_t>(N) * LA;
@@ -218,7 +218,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
         B2S_TRY((launch_ln<AT, WT>(l2, rows, st)));
       }
     }
-    if (m->split && (d.mlp_type == B2S_MLP_SWIGLU || d.act_type != B2S_ACT_GELU)) {
+    if (m->split && d.mlp_type == B2S_MLP_SWIGLU) {
       // BF16_SPLIT: fp32 pre-activations, then one kernel forms the activation and its [hi | lo] halves
       const bool glu = d.mlp_type == B2S_MLP_SWIGLU;
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), glu ? nullptr : m->lwf(l, B2S_WL_B_UP), w.gu, rows, (glu ? 2 : 1) * d.d_ff, dm,
@@ -227,9 +227,12 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     } else if (d.mlp_type == B2S_MLP_SWIGLU) {   // fused gate|up projection, then act = silu(gate) * up
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), nullptr, w.gu, rows, 2 * d.d_ff, dm, EPI_STORE_BF16, st));
       B2S_TRY(launch_swiglu<AT>(w.gu, w.act, rows, d.d_ff, st));
-    } else if (d.act_type != B2S_ACT_GELU) {   // ReLU / tanh-GELU: plain store epilogue, then the activation in place
+    } else if (d.act_type != B2S_ACT_GELU && !m->bf16) {   // fp32 check mode: plain store, then ReLU / tanh-GELU in place
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_STORE_BF16, st));
       B2S_TRY(launch_act<AT>(w.act, static_cast<int64_t>(rows) * d.d_ff, d.act_type, st));
+    } else if (m->bf16) {                                  // GELU / ReLU / tanh-GELU fused into the up-projection's epilogue
+      B2S_TRY(gemm_tc_launch(mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, nullptr, st,
+                             m->act_f16, nullptr, m->split, m->split, -1, d.act_type));
     } else {
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st, m->split));
     }

@@ -96,8 +96,7 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
             return F.silu(up[..., :shape.d_ff]) * up[..., shape.d_ff:]
         if shape.act_type == ACT_RELU:
             return F.relu(up)
-        if shape.act_type == ACT_GELU_TANH:     # the 16-bit modes store up before the elementwise kernel
-            up = r(up)
+        if shape.act_type == ACT_GELU_TANH:     # applied to the fp32 accumulators in the up-projection's epilogue
             return up * 0.5 * (1.0 + torch.tanh(0.79788456 * up * (1 + 0.044715 * up * up)))
         return F.gelu(up)
 

@@ -40,7 +40,7 @@ def main():
     e0.record(); idx = st.choice(100, 1_000_000); e1.record(); torch.cuda.synchronize()
     out["mt19937_choice_1M_draws_ms"] = e0.elapsed_time(e1)
     vals = np.stack([base, inst])
-    n, Bn = 100, 10_000_000
+    n, Bn = 100, (1_000_000 if "--small" in sys.argv else 10_000_000)    # --small: short enough for an ncu --set full replay
     idx = torch.randint(0, n, (Bn * n,), dtype=torch.int32, device="cuda")     # index table of the scaled size (4 GB)
     boot = B.resample(vals, 1, Bn, idx)
     torch.cuda.synchronize()
