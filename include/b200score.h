@@ -229,8 +229,9 @@ B2S_API int b2s_lm_head_bf16_static(const void* hidden, const void* W, const int
  * analyze_base_vs_instruct_mae_100q.py:296,312,357,382; analyze_results_base_versus_instruct.py:304,
  * 312,349.  state = 624 words + position (625 uint32, device).
  * b2s_mt19937_choice takes its temporary (the raw word stream of the call, about 4 * count * (mask + 1) / n bytes,
- * at most ~0.6 GB per 2^26-draw segment) from the device's default memory pool with cudaMallocAsync / cudaFreeAsync on
- * the caller's stream: stream-ordered, no device-wide synchronisation, nothing is kept after the call. */
+ * at most ~0.6 GB per 2^26-draw segment) from a memory pool the library creates per device on first use
+ * (cudaMallocFromPoolAsync / cudaFreeAsync on the caller's stream: stream-ordered, no device-wide synchronisation; the
+ * pool keeps up to 1 GiB between calls and never touches the application's default pool). */
 B2S_API int b2s_mt19937_seed(uint32_t seed, uint32_t* state /*dev [625]*/, void* stream);
 B2S_API int b2s_mt19937_choice(uint32_t* state /*dev [625], in/out*/, int32_t n, int64_t count,
                        int32_t* idx_out /*dev [count]*/, void* stream);

@@ -7,6 +7,7 @@
 // NumPy legacy stream: np.random.seed(s) = Knuth init of 624 words;
 // np.random.choice(n, size) = per draw, words masked to the smallest 2^b-1 >= n-1 and rejected while > n-1.
 #include "b2s_common.cuh"
+#include <mutex>
 
 namespace b2s {
 
@@ -397,6 +398,30 @@ boot_summary_kernel(const double* __restrict__ sorted, long long B, double q_lo,
   }
 }
 
+// Scratch for b2s_mt19937_choice comes from a memory pool the library owns (one per device, created on first use):
+// stream-ordered allocation without touching the application's default pool, and with a release threshold so that
+// the bootstrap entry points, which call it back to back, reuse the same block instead of going to the driver each time.
+static cudaMemPool_t g_boot_pool[64] = {nullptr};
+static std::mutex g_boot_pool_mutex;
+static int boot_pool(cudaMemPool_t* out) {
+  int dev = 0;
+  B2S_CHECK_CUDA(cudaGetDevice(&dev));
+  B2S_REQUIRE(dev >= 0 && dev < 64, "mt19937_choice: device ordinal %d outside [0, 64)", dev);
+  std::lock_guard<std::mutex> g(g_boot_pool_mutex);
+  if (g_boot_pool[dev] == nullptr) {
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = dev;
+    B2S_CHECK_CUDA(cudaMemPoolCreate(&g_boot_pool[dev], &props));
+    unsigned long long keep = 1ull << 30;     // blocks up to 1 GiB stay in the pool between calls
+    B2S_CHECK_CUDA(cudaMemPoolSetAttribute(g_boot_pool[dev], cudaMemPoolAttrReleaseThreshold, &keep));
+  }
+  *out = g_boot_pool[dev];
+  return B2S_OK;
+}
+
 static long long next_pow2(long long v) {
   long long p = SORT_CHUNK;
   while (p < v) p <<= 1;
@@ -444,7 +469,9 @@ int b2s_mt19937_choice(uint32_t* state, int32_t n, int64_t count, int32_t* idx_o
   const size_t cnt_bytes = align_up(4 * static_cast<size_t>(chunks_max), 256);
   const size_t off_bytes = align_up(8 * static_cast<size_t>(chunks_max + 1), 256);
   uint8_t* scratch = nullptr;
-  B2S_CHECK_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&scratch), raw_bytes + cnt_bytes + off_bytes + 4096, st));
+  cudaMemPool_t pool;
+  B2S_TRY(boot_pool(&pool));
+  B2S_CHECK_CUDA(cudaMallocFromPoolAsync(reinterpret_cast<void**>(&scratch), raw_bytes + cnt_bytes + off_bytes + 4096, pool, st));
   uint32_t* raw = reinterpret_cast<uint32_t*>(scratch);
   int* counts = reinterpret_cast<int*>(scratch + raw_bytes);
   long long* offsets = reinterpret_cast<long long*>(scratch + raw_bytes + cnt_bytes);

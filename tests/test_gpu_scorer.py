@@ -365,3 +365,22 @@ def test_fp16_range_overflow_is_flagged_never_silent():
             dicts = S.score_prompts(sc, tok, ["abcdefgh" * 5, "xyz" * 9], variant="100q")
             assert all((not d["success"]) and np.isnan(d["relative_prob"]) for d in dicts)     # the reference's NaN rows, not 0.5
         sc.close()
+
+
+def test_two_devices_in_one_process():
+    """Function attributes (the dynamic shared memory opt-in) and the SM count belong to a device: a model created on
+    device 1 first and then on device 0 must run on both from one process.  Skipped with fewer than two GPUs."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    from llm_interpretation_replication_b200 import shapes, weights
+    from llm_interpretation_replication_b200.scorer import Scorer
+    shp = shapes.falcon_7b().with_layers(1)
+    W = weights.init_weights(shp, seed=5)
+    g = np.random.RandomState(3)
+    ids = [g.randint(32, shp.vocab - 32, size=L).tolist() for L in (70, 111, 9)]
+    rows = {}
+    for dev in ("cuda:1", "cuda:0"):
+        sc = Scorer(shp, weights.to_device(W, dev, torch.bfloat16), mode=shapes.MODE_FP16, device=dev, max_tokens=1024, max_seqs=8)
+        rows[dev], _ = sc.score_ids(ids, np.array([[1000, 2000]]), topk=5)
+        sc.close()
+    assert np.isfinite(rows["cuda:0"]).all() and np.array_equal(rows["cuda:0"], rows["cuda:1"])
