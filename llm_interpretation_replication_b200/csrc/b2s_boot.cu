@@ -33,6 +33,85 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   return y;
 }
 
+// Small draws (a few thousand, e.g. one np.random.choice(n, n) at a time): one CTA walks the stream 624 words at a time.  The twist is done in the four dependency phases of the
+// in-place recurrence; acceptance flags are compacted with a block scan so that idx_out holds the accepted
+// draws in stream order, exactly as the sequential reference consumes them.
+__global__ void __launch_bounds__(640)
+mt_choice_kernel(uint32_t* __restrict__ state, uint32_t rng, uint32_t mask, long long count, int32_t* __restrict__ idx_out) {
+  __shared__ uint32_t mt[MT_N];
+  __shared__ int warp_tot[20];
+  __shared__ int s_pos, s_total, s_newpos;
+  const int t = threadIdx.x;
+  const int lane = t & 31, warp = t >> 5;
+  if (t < MT_N) mt[t] = state[t];
+  if (t == 0) s_pos = static_cast<int>(state[MT_N]);
+  __syncthreads();
+  long long produced = 0;
+  while (produced < count) {
+    int pos = s_pos;
+    if (pos >= MT_N) {
+      uint32_t y = 0;
+      if (t < MT_N - 1) y = (mt[t] & 0x80000000u) | (mt[t + 1] & 0x7fffffffu);
+      __syncthreads();
+      if (t < MT_N - MT_M) mt[t] = mt[t + MT_M] ^ mt_mix(y);                       // kk in [0,227)
+      __syncthreads();
+      if (t >= MT_N - MT_M && t < 2 * (MT_N - MT_M)) mt[t] = mt[t - (MT_N - MT_M)] ^ mt_mix(y);   // [227,454)
+      __syncthreads();
+      if (t >= 2 * (MT_N - MT_M) && t < MT_N - 1) mt[t] = mt[t - (MT_N - MT_M)] ^ mt_mix(y);     // [454,623)
+      __syncthreads();
+      if (t == MT_N - 1) {
+        const uint32_t yy = (mt[MT_N - 1] & 0x80000000u) | (mt[0] & 0x7fffffffu);
+        mt[MT_N - 1] = mt[MT_M - 1] ^ mt_mix(yy);
+      }
+      pos = 0;
+      __syncthreads();
+    }
+    const int w = pos + t;
+    uint32_t v = 0;
+    int acc = 0;
+    if (w < MT_N) {
+      v = mt_temper(mt[w]) & mask;
+      acc = (v <= rng) ? 1 : 0;
+    }
+    // block exclusive scan of acc
+    int incl = acc;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += n;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int x = (lane < 20) ? warp_tot[lane] : 0;
+      int xi = x;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, xi, o);
+        if (lane >= o) xi += n;
+      }
+      if (lane < 20) warp_tot[lane] = xi - x;   // exclusive warp offsets
+      if (lane == 19) s_total = xi;
+    }
+    __syncthreads();
+    const int excl = warp_tot[warp] + incl - acc;
+    const int total = s_total;
+    const long long need = count - produced;
+    if (acc && excl < need) idx_out[produced + excl] = static_cast<int32_t>(v);
+    if (total < need) {
+      if (t == 0) s_newpos = MT_N;          // whole block consumed, more draws needed
+    } else if (acc && excl == need - 1) {
+      s_newpos = w + 1;                     // the word after the last one consumed
+    }
+    __syncthreads();
+    produced += (total < need) ? total : need;
+    if (t == 0) s_pos = s_newpos;
+    __syncthreads();
+  }
+  if (t < MT_N) state[t] = mt[t];
+  if (t == 0) state[MT_N] = static_cast<uint32_t>(s_pos);
+}
+
 // ---- np.random.choice, device-wide ---------------------------------------------------------------------------
 // The word stream x[0..623] = state, x[j] = x[j-227] ^ mix(x[j-624], x[j-623]) is the same sequence whether it is
 // produced 624 words at a time in place (NumPy) or as a sliding recurrence.  Only the recurrence is serial, so it gets
@@ -51,16 +130,20 @@ mt_gen_kernel(const uint32_t* __restrict__ state, uint32_t* __restrict__ raw, lo
   const int t = threadIdx.x;
   for (int i = t; i < MT_N; i += blockDim.x) { const uint32_t v = state[i]; x[i] = v; raw[i] = v; }
   __syncthreads();
-  for (long long base = MT_N; base < MT_N + n_new; base += MT_GEN_STEP) {
+  constexpr uint32_t RM = MT_RING - 1;
+  uint32_t* out = raw + MT_N + t;                                   // word j of this thread; j + 227 is out[227]
+  uint32_t r = static_cast<uint32_t>(MT_N + t);                    // j mod ring size (32-bit arithmetic in the serial loop)
+  const long long steps = n_new / MT_GEN_STEP;
+  for (long long sidx = 0; sidx < steps; ++sidx) {
     if (t < MT_N - MT_M) {   // 227 lanes
-      const long long j = base + t;
-      const uint32_t a = x[(j - 624) & (MT_RING - 1)], b = x[(j - 623) & (MT_RING - 1)], c = x[(j - 227) & (MT_RING - 1)];
+      const uint32_t a = x[(r - 624u) & RM], b = x[(r - 623u) & RM], c = x[(r - 227u) & RM];
+      const uint32_t a2 = x[(r - 397u) & RM], b2 = x[(r - 396u) & RM];           // both older than this step
       const uint32_t v0 = c ^ mt_mix((a & 0x80000000u) | (b & 0x7fffffffu));
-      const uint32_t a2 = x[(j - 397) & (MT_RING - 1)], b2 = x[(j - 396) & (MT_RING - 1)];       // both older than `base`
       const uint32_t v1 = v0 ^ mt_mix((a2 & 0x80000000u) | (b2 & 0x7fffffffu));
-      x[j & (MT_RING - 1)] = v0; x[(j + 227) & (MT_RING - 1)] = v1;
-      raw[j] = v0; raw[j + 227] = v1;
+      x[r & RM] = v0; x[(r + 227u) & RM] = v1;
+      out[0] = v0; out[227] = v1;
     }
+    r += MT_GEN_STEP; out += MT_GEN_STEP;
     __syncthreads();
   }
 }
@@ -248,15 +331,18 @@ boot_resample_kernel(const double* __restrict__ vals, int F, int split, int n, l
 // t mod 16 -- every lane of a half-warp then owns its bank pair and the gather never conflicts.  The sums run in index
 // order exactly as in the kernel above (same bits).
 constexpr int BT_ROWS = 256;
+template <int FT>    // FT = number of value rows when it is 1..4 or 6 (loops unroll, loads of four indices are in flight together); 0 = any F
 __global__ void __launch_bounds__(BT_ROWS)
-boot_resample_tile_kernel(const double* __restrict__ vals, int F, int split, int n, long long B, const int32_t* __restrict__ idx,
+boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, int n, long long B, const int32_t* __restrict__ idx,
                           double* __restrict__ boot, int stride_words) {
+  const int F = FT > 0 ? FT : F_rt;
   extern __shared__ double sv[];                                   // [F * n][16] replicated values
   uint32_t* sidx = reinterpret_cast<uint32_t*>(sv + static_cast<size_t>(F) * n * 16);   // [BT_ROWS][stride_words] packed indices
   for (int i = threadIdx.x; i < F * n * 16; i += BT_ROWS) sv[i] = vals[i >> 4];
   const int n4 = n >> 2;
   const long long tiles = (B + BT_ROWS - 1) / BT_ROWS;
-  const int copy = threadIdx.x & 15;
+  const double* tab = sv + (threadIdx.x & 15);                     // this thread's copy of the table
+  const int fstride = n * 16;                                      // doubles between value rows
   for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
     __syncthreads();                                               // the previous tile's rows have been consumed (and sv is filled)
     const long long b0 = tile * BT_ROWS;
@@ -274,16 +360,34 @@ boot_resample_tile_kernel(const double* __restrict__ vals, int F, int split, int
     __syncthreads();
     if (threadIdx.x < R) {
       const uint32_t* row = sidx + threadIdx.x * stride_words;
-      double lo = 0.0, hi = 0.0, ab = 0.0;
+      double lo = 0.0, hi = 0.0, ab0 = 0.0, ab1 = 0.0;
       for (int j4 = 0; j4 < n4; ++j4) {
         const uint32_t w = row[j4];
+        if constexpr (FT > 0) {
+          double x[4][FT];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int id = (w >> (8 * u)) & 255;
-          for (int f = 0; f < F; ++f) {
-            const double x = sv[(f * n + id) * 16 + copy];
-            if (f < split) lo += x; else hi += x;
-            ab += fabs(x);
+          for (int u = 0; u < 4; ++u) {
+            const double* p = tab + ((w >> (8 * u)) & 255u) * 16;
+#pragma unroll
+            for (int f = 0; f < FT; ++f) x[u][f] = p[f * fstride];
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+#pragma unroll
+            for (int f = 0; f < FT; ++f) {           // lo / hi in index order, value row by value row: same bits as the general kernel
+              if (f < split) lo += x[u][f]; else hi += x[u][f];
+              if (u & 1) ab1 += fabs(x[u][f]); else ab0 += fabs(x[u][f]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const double* p = tab + ((w >> (8 * u)) & 255u) * 16;
+            for (int f = 0; f < F; ++f) {
+              const double x = p[f * fstride];
+              if (f < split) lo += x; else hi += x;
+              ab0 += fabs(x);
+            }
           }
         }
       }
@@ -291,7 +395,7 @@ boot_resample_tile_kernel(const double* __restrict__ vals, int F, int split, int
       const double nlo = static_cast<double>(split) * n, nhi = static_cast<double>(F - split) * n;
       boot[b * 3 + 0] = split > 0 ? lo / nlo : nan("");
       boot[b * 3 + 1] = F > split ? hi / nhi : nan("");
-      boot[b * 3 + 2] = ab / (static_cast<double>(F) * n);
+      boot[b * 3 + 2] = (ab0 + ab1) / (static_cast<double>(F) * n);
     }
   }
 }
@@ -454,6 +558,11 @@ int b2s_mt19937_choice(uint32_t* state, int32_t n, int64_t count, int32_t* idx_o
   const uint32_t rng = static_cast<uint32_t>(n - 1);
   uint32_t mask = rng;
   mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+  if (count <= 16384) {   // one launch; the device-wide path below has a fixed cost of six launches and an allocation
+    mt_choice_kernel<<<1, 640, 0, st>>>(state, rng, mask, static_cast<long long>(count), idx_out);
+    B2S_CHECK_LAUNCH();
+    return B2S_OK;
+  }
   // Word budget of a segment of `c` draws: c / p expected (p = n / (mask + 1) >= 1/2), plus 40 standard deviations of the
   // negative-binomial spread, rounded up to whole generator steps.  mt_commit_kernel traps if that were ever not enough.
   const double pacc = static_cast<double>(n) / (static_cast<double>(mask) + 1.0);
@@ -511,11 +620,25 @@ int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t
     if (sw % 2 == 0) ++sw;                                              // odd word stride: conflict-free row walks
     const size_t tile_smem = static_cast<size_t>(F) * n * 16 * sizeof(double) + static_cast<size_t>(BT_ROWS) * sw * 4;
     if (idx != nullptr && n % 4 == 0 && n <= 256 && (reinterpret_cast<uintptr_t>(idx) & 15) == 0 && tile_smem <= 110 * 1024) {
-      B2S_CHECK_CUDA(cudaFuncSetAttribute(boot_resample_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tile_smem)));
       const long long tiles = ceil_div(B, BT_ROWS);
       const int per_sm = static_cast<int>((220 * 1024) / (tile_smem + 1024));
       const long long cap = static_cast<long long>(sms) * (per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm));
-      boot_resample_tile_kernel<<<static_cast<unsigned>(tiles < cap ? tiles : cap), BT_ROWS, tile_smem, st>>>(vals, F, split, n, B, idx, boot, sw);
+      const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
+#define B2S_BOOT_TILE(FT)                                                                                                     \
+  do {                                                                                                                        \
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(boot_resample_tile_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
+                                        static_cast<int>(tile_smem)));                                                        \
+    boot_resample_tile_kernel<FT><<<grid, BT_ROWS, tile_smem, st>>>(vals, F, split, n, B, idx, boot, sw);                     \
+  } while (0)
+      switch (F) {
+        case 1: B2S_BOOT_TILE(1); break;
+        case 2: B2S_BOOT_TILE(2); break;
+        case 3: B2S_BOOT_TILE(3); break;
+        case 4: B2S_BOOT_TILE(4); break;
+        case 6: B2S_BOOT_TILE(6); break;
+        default: B2S_BOOT_TILE(0); break;
+      }
+#undef B2S_BOOT_TILE
       B2S_CHECK_LAUNCH();
       return B2S_OK;
     }

@@ -37,6 +37,8 @@ static constexpr uint32_t TMEM_COLS = 512;
 struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, num_kb;
+  int prefetch;          // the producer asks the TMA unit to pull the boxes of the k-block this many steps ahead into L2 (0 = off)
+  int band_n;            // CTA-pair 256x256 kernel: > 0 = column bands of this many tiles, all row blocks walked inside a band
   int group_m;           // row-blocks (of 128 rows) per rasterisation group
   int* wave_sync;        // experiment: global counters, one per synchronised wave (null = off)
   int wave_sync_every;   // pair kernels: all producers meet every this many tiles
@@ -63,6 +65,13 @@ __device__ __forceinline__ void tma_load_2d_h(uint32_t smem_dst, const CUtensorM
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
       ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(hint)
       : "memory");
+}
+
+// L2 prefetch of one operand box (no shared-memory destination, no barrier): turns the DRAM miss of a later TMA load into an
+// L2 hit.  The operand ring holds ~2 us of MMA work; a load that misses L2 under full DRAM load can take longer than that.
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int32_t c0, int32_t c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1) : "memory");
 }
 
 __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m, int serp, int& mb, int& nb) {
@@ -631,6 +640,18 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// Column-band order: the W rows of one band (band_n x 256 rows of W, sized to stay L2-resident) are met by every row block
+// before the next band starts, so W is read from DRAM once and A once per band.  For launches whose whole W is L2-sized
+// but does not survive next to the A and residual streams (QKV, dense: 42 MB), the row-group order re-read W every wave.
+__device__ __forceinline__ void tile_coords2_band(int tile, int tiles_m, int tiles_n, int band_n, int& mb, int& nb) {
+  const int per_band = band_n * tiles_m;
+  const int band = tile / per_band;
+  const int first_n = band * band_n;
+  const int bn = min(band_n, tiles_n - first_n);
+  const int within = tile - band * per_band;
+  nb = first_n + within % bn;
+  mb = within / bn;
+}
 __device__ __forceinline__ void tile_coords2(int tile, int tiles_m, int tiles_n, int group_m, int serp, int& mb, int& nb) {
   const int GM = max(1, group_m / 2);    // groups of group_m x 128 rows = GM x 256 rows
   const int per_group = GM * tiles_n;
@@ -691,7 +712,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       bool meet = true;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int mb, nb;
-        tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
+        if (p.band_n > 0) tile_coords2_band(tile, tiles_m2, p.tiles_n, p.band_n, mb, nb);
+        else tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
         wave_meet(p, (tile - pair) / num_pairs, 2 * min(num_pairs, num_tiles - ((tile - pair) / num_pairs) * num_pairs), meet);
         const bool rev = p.serp == 2 ? ((((tile - pair) / num_pairs) & 1) != 0) : (p.serp == 1 && (nb & 1));
         for (int kq = 0; kq < p.num_kb; ++kq) {
@@ -702,6 +724,24 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t fb = full_bar(stage) & PEER_MASK;
           if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
           const int kw = (p.k_wrap != 0 && kb >= p.k_wrap) ? kb - p.k_wrap : kb;
+          if (p.prefetch > 0 && !rev) {     // boxes of k-block kq + prefetch: this tile's, or the first ones of this pair's next tile
+            int kp = kq + p.prefetch, pmb = mb, pnb = nb;
+            bool ok = true;
+            if (kp >= p.num_kb) {
+              kp -= p.num_kb;
+              const int nt = tile + num_pairs;
+              ok = nt < num_tiles && kp < p.num_kb;
+              if (ok) {
+                if (p.band_n > 0) tile_coords2_band(nt, tiles_m2, p.tiles_n, p.band_n, pmb, pnb);
+                else tile_coords2(nt, tiles_m2, p.tiles_n, p.group_m, p.serp, pmb, pnb);
+              }
+            }
+            if (ok) {
+              const int kpw = (p.k_wrap != 0 && kp >= p.k_wrap) ? kp - p.k_wrap : kp;
+              tma_prefetch_2d(&tmA, kp * BK, pmb * BM2 + static_cast<int>(rank) * BM);
+              if (kp < p.k_wrap || p.k_wrap == 0) tma_prefetch_2d(&tmB, kpw * BK, pnb * BN + static_cast<int>(rank) * (BN / 2));
+            }
+          }
           tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM2 + static_cast<int>(rank) * BM, p.hint_a);
           tma_load_2d_cg2(sb, &tmB, fb, kw * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
           if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
@@ -743,7 +783,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int it = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
       int mb, nb;
-      tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
+      if (p.band_n > 0) tile_coords2_band(tile, tiles_m2, p.tiles_n, p.band_n, mb, nb);
+      else tile_coords2(tile, tiles_m2, p.tiles_n, p.group_m, p.serp, mb, nb);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
       const int row = mb * BM2 + static_cast<int>(rank) * BM + quad * 32 + lane;
@@ -858,6 +899,21 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t fb = full_bar(stage) & PEER_MASK;
           if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE3_BYTES);
           const int kw = (p.k_wrap != 0 && kb >= p.k_wrap) ? kb - p.k_wrap : kb;
+          if (p.prefetch > 0 && !rev) {
+            int kp = kq + p.prefetch, pmb = mb, pnb = nb;
+            bool ok = true;
+            if (kp >= p.num_kb) {
+              kp -= p.num_kb;
+              const int nt = tile + num_pairs;
+              ok = nt < num_tiles && kp < p.num_kb;
+              if (ok) tile_coords3(nt, tiles_m3, p.tiles_n, p.group_m, p.serp, pmb, pnb);
+            }
+            if (ok) {
+              const int kpw = (p.k_wrap != 0 && kp >= p.k_wrap) ? kp - p.k_wrap : kp;
+              tma_prefetch_2d(&tmA, kp * BK, pmb * BM3 + static_cast<int>(rank) * 256);
+              if (kp < p.k_wrap || p.k_wrap == 0) tma_prefetch_2d(&tmB, kpw * BK, pnb * BN + static_cast<int>(rank) * (BN / 2));
+            }
+          }
           tma_load_2d_cg2(sa, &tmA, fb, kb * BK, mb * BM3 + static_cast<int>(rank) * 256, p.hint_a);
           tma_load_2d_cg2(sb, &tmB, fb, kw * BK, nb * BN + static_cast<int>(rank) * (BN / 2), p.hint_b);
           if (++stage == STAGES3) { stage = 0; phase ^= 1u; }
@@ -1036,6 +1092,8 @@ int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = ru
 // starts on the panel bytes the previous one touched last) but a row's fp32 summation order then depends on which wave
 // its tile falls in, i.e. on the batch around it -- sharded and unsharded runs stop being bit-identical.  1 = direction by
 // column tile: batch-invariant, but CTAs that share an A row-block no longer walk K together: -1 %.
+int g_opt_prefetch = 0;      // b2s_set_option "gemm_prefetch": L2 prefetch distance of the CTA-pair producers in k-blocks (0 = off)
+int g_opt_band_n = 0;        // b2s_set_option "gemm_band_n": 0 = row-group order; -1 = column bands when W is L2-sized; k > 0 = bands of k tiles
 int g_opt_policy = 1;        // b2s_set_option "gemm_policy" (see launch_epi)
 int g_opt_wave_sync = 4;     // b2s_set_option "gemm_wave_sync": all producers meet every N tiles (0 = never)
 // Meeting counters: one table per device (a __device__ array exists once on every GPU that loads the library).  Each
@@ -1175,6 +1233,13 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     // is then 9 MB and W is the only thing re-read (measured: profiles/r1_gemm_l2_hints.txt, DRAM 5.4 -> 4.1 GB on qkv)
     if (g_opt_small_w_group > 0 && 2.0 * N * K <= 48e6) gm = g_opt_small_w_group;
     p.group_m = g_opt_group_m > 0 ? g_opt_group_m : gm;
+    p.prefetch = g_opt_prefetch;
+    p.band_n = 0;
+    if (g_opt_band_n > 0) p.band_n = g_opt_band_n;
+    else if (g_opt_band_n < 0 && 2.0 * N * K <= 48e6 && 2.0 * N * K > 24e6 && p.serp == 0) {
+      const int bands = static_cast<int>(ceil_div(static_cast<int64_t>(2.0 * N * K), 22000000));   // W bands of <= 22 MB
+      p.band_n = static_cast<int>(ceil_div(p.tiles_n, bands));
+    }
     p.serp = g_opt_serp;
     p.wave_sync = nullptr; p.wave_sync_every = 0;
     p.pair_stride = 1;
@@ -1254,6 +1319,16 @@ int b2s_set_option(const char* name, int32_t value) {
   if (std::string(name) == "gemm_l2_hint") {
     B2S_REQUIRE(value >= 0 && value <= 7, "set_option: gemm_l2_hint must be in [0, 7]");
     b2s::g_opt_hint = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_prefetch") {
+    B2S_REQUIRE(value >= 0 && value <= 64, "set_option: gemm_prefetch must be in [0, 64]");
+    b2s::g_opt_prefetch = value;
+    return B2S_OK;
+  }
+  if (std::string(name) == "gemm_band_n") {
+    B2S_REQUIRE(value >= -1 && value <= 1024, "set_option: gemm_band_n must be in [-1, 1024]");
+    b2s::g_opt_band_n = value;
     return B2S_OK;
   }
   if (std::string(name) == "gemm_policy") {
