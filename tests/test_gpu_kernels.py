@@ -294,3 +294,28 @@ def test_gemm_f32_large_matches_fp64():
     torch.cuda.synchronize()
     err = ((out.double() - ref).abs() / (ref.abs() + 1.0)).max().item()
     assert err <= 5e-5, err      # measured 2.4e-5: what one fp32 fmaf chain of 18176 terms costs
+
+
+@pytest.mark.parametrize("opt,val", [("gemm_band_n", 3), ("gemm_band_n", -1), ("gemm_prefetch", 8), ("gemm_prefetch", 3)])
+@pytest.mark.parametrize("M,N,K,epi", [(9000, 4544, 4544, 2), (5000, 2304, 832, 1)])
+def test_gemm_tc_rasterisation_and_prefetch_knobs_keep_the_bits(opt, val, M, N, K, epi):
+    """Column-band tile order and the producers' L2 prefetch change when a tile is computed and what is in L2, never a
+    result: the output must equal the default configuration's bit for bit (several bands, several waves, ragged edges)."""
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    A, W = _rand((M, K), 1.0, 51, torch.float16), _rand((N, K), 0.03, 52, torch.float16)
+    resid = _rand((M, N), 1.0, 53, torch.float32)
+    run = lambda: U.gemm_f16(A, W, None, 2, out=resid.clone()) if epi == 2 else U.gemm_f16(A, W, None, epi)
+    base = run()
+    torch.cuda.synchronize()
+    try:
+        _lib.check(lib.b2s_set_option(opt.encode(), val), "set_option")
+        got = run()
+        torch.cuda.synchronize()
+    finally:
+        _lib.check(lib.b2s_set_option(opt.encode(), 0), "set_option")
+    assert torch.equal(base, got), (opt, val)
+    ref = A.float() @ W.float().T
+    ref = ref + resid if epi == 2 else torch.nn.functional.gelu(ref)
+    assert ((got.float() - ref).abs() / (ref.abs() + 1.0)).max().item() <= 2e-3
