@@ -244,6 +244,21 @@ B2S_API int b2s_mt19937_choice(uint32_t* state /*dev [625], in/out*/, int32_t n,
 B2S_API int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t n, int64_t B,
                            const int32_t* idx, uint64_t philox_seed, double* boot /*dev [B,3]*/, void* stream);
 
+/* The index table of the Philox mode, for consumers that need the indices themselves (b2s_corr_bootstrap): idx_out [B, n],
+ * idx[b, j] = the index b2s_bootstrap_resample(idx = NULL, philox_seed = seed) uses for draw j of resample b.  Stands in for
+ * the reference loops that resample from an UNSEEDED generator (survey_analysis/analyze_llm_agreement_simple_bootstrap.py:
+ * 176-178; survey_analysis_consolidated.py:228,323,386,499,635), where no particular stream can be reproduced. */
+B2S_API int b2s_philox_indices(uint64_t seed, int32_t n, int64_t B, int32_t* idx_out /*dev [B,n]*/, void* stream);
+
+/* Question-resampled agreement of one model with the human averages: the body of the loop of survey_analysis/
+ * analyze_llm_agreement_simple_bootstrap.py:169-180 with calculate_bootstrap_metrics (:89-148).  human / model [n] fp64 (model
+ * NaN = no answer for that question), idx [B, n] sampled question numbers (b2s_philox_indices: the script is unseeded).  A
+ * resample uses every question that was drawn at least once AND has a model value (the script's `prompt in sampled_questions`).
+ * out [B, 4] = MAE, MSE, MAPE in percent (finite terms only), Pearson r (NaN without spread); a row is all NaN when fewer than
+ * min_matched (the script: 10) questions matched. */
+B2S_API int b2s_agreement_bootstrap(const double* human, const double* model, int32_t n, const int32_t* idx, int64_t B,
+                            int32_t min_matched, double* out /*dev [B,4]*/, void* stream);
+
 /* Percentile CI + tail fractions of one statistic of boot (np.percentile linear interpolation):
  * stat 0 = boot[:,0], 1 = boot[:,1]-boot[:,0], 2 = boot[:,2].
  * summary[8] = {pct(q_lo), pct(q_hi), frac(x<=0), frac(x>=0), mean(x), frac(x>=observed), min, max}.
@@ -264,6 +279,14 @@ B2S_API int b2s_bootstrap_summary(const double* boot, int64_t B, int32_t stat, d
 B2S_API int b2s_corr_bootstrap(const double* X, int32_t P, int32_t M, const int32_t* idx, int32_t B,
                        const int32_t* pairs, int32_t n_pairs, int32_t method, double* corr, double* stats /*or NULL*/,
                        void* stream);
+
+/* Same, with the respondent filter of the reference's cross-prompt bootstraps (survey_analysis_consolidated.py:520-523, 748-751):
+ * with min_valid > 0 (pearson only) a column takes part in a resample only if at least min_valid of its resampled rows are not
+ * NaN; the pairs of a dropped column are NaN for that resample.  n_pairs may exceed 2048 here: stats then holds mean, NaN
+ * (no median), std and count. */
+B2S_API int b2s_corr_bootstrap_ex(const double* X, int32_t P, int32_t M, const int32_t* idx, int32_t B,
+                          const int32_t* pairs, int32_t n_pairs, int32_t method, int32_t min_valid, double* corr,
+                          double* stats /*or NULL*/, void* stream);
 
 /* Simulated-individual correlation bootstrap: the body of the 10,000-iteration loop of
  * survey_analysis/bootstrap_confidence_intervals.py:54-99,126-148.  Seed s = seed0 + i runs

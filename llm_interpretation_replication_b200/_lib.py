@@ -64,6 +64,9 @@ SIGNATURES = {
     "b2s_bootstrap_resample": (C.c_int, [_vp, _i32, _i32, _i32, _i64, _vp, _u64, _vp, _vp]),
     "b2s_ci_simulate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _u32, _i32, _vp, _vp, _vp, _vp]),
     "b2s_corr_bootstrap": (C.c_int, [_vp, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _vp, _vp, _vp]),
+    "b2s_corr_bootstrap_ex": (C.c_int, [_vp, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "b2s_philox_indices": (C.c_int, [_u64, _i32, _i64, _vp, _vp]),
+    "b2s_agreement_bootstrap": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _i32, _vp, _vp]),
     "b2s_bootstrap_scratch_bytes": (_sz, [_i64]),
     "b2s_bootstrap_summary": (C.c_int, [_vp, _i64, _i32, _dbl, _dbl, _dbl, _vp, _vp, _vp, _sz, _vp]),
 }

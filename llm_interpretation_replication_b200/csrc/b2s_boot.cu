@@ -400,6 +400,69 @@ boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, 
   }
 }
 
+// The index table the Philox mode of the resample kernels draws, written out: idx[b, j] = floor(n * u / 2^32) with u the
+// (j mod 4)-th word of Philox4x32-10(counter = (b, j / 4), key = seed).  For consumers that need the indices themselves
+// (the correlation bootstraps) of the reference loops that draw from an unseeded generator.
+__global__ void __launch_bounds__(256)
+philox_indices_kernel(unsigned long long seed, int n, long long B, int32_t* __restrict__ idx) {
+  const int n4 = (n + 3) / 4;
+  const long long total = B * n4;
+  const uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long b = i / n4;
+    const int q = static_cast<int>(i - b * n4);
+    uint32_t c[4] = {static_cast<uint32_t>(b), static_cast<uint32_t>(static_cast<unsigned long long>(b) >> 32), static_cast<uint32_t>(q), 0u};
+    philox4x32_10(c, k0, k1);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (4 * q + u < n) idx[b * n + 4 * q + u] = static_cast<int32_t>(__umulhi(c[u], static_cast<uint32_t>(n)));
+  }
+}
+
+// Question-resampled model/human agreement metrics (survey_analysis/analyze_llm_agreement_simple_bootstrap.py:89-148): a
+// resample is the SET of distinct sampled questions (the script matches model rows with `prompt in sampled_questions`), a
+// question is used when the model has a value for it; MAE, MSE, MAPE over the finite |h - m| / |h| terms (in percent) and
+// scipy's pearsonr of (human, model) when both have spread, else NaN.  Fewer than min_matched rows: all NaN (the script
+// returns None).  One thread per resample; n <= 1024 questions.
+__global__ void __launch_bounds__(128)
+agreement_boot_kernel(const double* __restrict__ human, const double* __restrict__ model, int n, const int32_t* __restrict__ idx,
+                      long long B, int min_matched, double* __restrict__ out) {
+  const long long b = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  uint32_t mask[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) mask[i] = 0u;
+  const int32_t* row = idx + b * n;
+  for (int j = 0; j < n; ++j) { const int q = row[j]; mask[q >> 5] |= 1u << (q & 31); }
+  int cnt = 0, n_ape = 0;
+  double sh = 0.0, sm = 0.0, sae = 0.0, sse = 0.0, sape = 0.0;
+  for (int q = 0; q < n; ++q) {
+    const double m = model[q];
+    if (((mask[q >> 5] >> (q & 31)) & 1u) && m == m) {
+      const double h = human[q], d = h - m;
+      sh += h; sm += m; sae += fabs(d); sse += d * d; ++cnt;
+      const double ape = fabs(d / h);
+      if (isfinite(ape)) { sape += ape; ++n_ape; }
+    }
+  }
+  double* o = out + b * 4;
+  if (cnt < min_matched) { o[0] = o[1] = o[2] = o[3] = nan(""); return; }
+  const double mh = sh / cnt, mm = sm / cnt;
+  double vxx = 0.0, vyy = 0.0, vxy = 0.0;
+  for (int q = 0; q < n; ++q) {
+    const double m = model[q];
+    if (((mask[q >> 5] >> (q & 31)) & 1u) && m == m) {
+      const double dx = human[q] - mh, dy = m - mm;
+      vxx += dx * dx; vyy += dy * dy; vxy += dx * dy;
+    }
+  }
+  o[0] = sae / cnt;
+  o[1] = sse / cnt;
+  o[2] = n_ape > 0 ? sape / n_ape * 100.0 : nan("");
+  o[3] = (cnt > 1 && vxx > 0.0 && vyy > 0.0) ? vxy / sqrt(vxx * vyy) : nan("");
+}
+
 // ---- summary: select statistic, sort, percentiles, tail fractions -----------------------------------
 __device__ __forceinline__ double boot_stat(const double* boot, long long b, int stat) {
   if (stat == 0) return boot[b * 3];
@@ -602,6 +665,27 @@ int b2s_mt19937_choice(uint32_t* state, int32_t n, int64_t count, int32_t* idx_o
   }
   cudaFreeAsync(scratch, st);
   return rc;
+}
+
+int b2s_philox_indices(uint64_t seed, int32_t n, int64_t B, int32_t* idx_out, void* stream) {
+  B2S_REQUIRE(idx_out, "philox_indices: null argument");
+  B2S_REQUIRE(n >= 1 && B >= 1, "philox_indices: bad sizes n=%d B=%lld", n, static_cast<long long>(B));
+  const long long total = static_cast<long long>(B) * ((n + 3) / 4);
+  const long long blocks = ceil_div(total, 256);
+  philox_indices_kernel<<<static_cast<unsigned>(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      seed, n, B, idx_out);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+int b2s_agreement_bootstrap(const double* human, const double* model, int32_t n, const int32_t* idx, int64_t B,
+                            int32_t min_matched, double* out, void* stream) {
+  B2S_REQUIRE(human && model && idx && out, "agreement_bootstrap: null argument");
+  B2S_REQUIRE(n >= 1 && n <= 1024 && B >= 1, "agreement_bootstrap: n=%d outside [1, 1024] or B=%lld < 1", n, static_cast<long long>(B));
+  agreement_boot_kernel<<<static_cast<unsigned>(ceil_div(B, 128)), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      human, model, n, idx, B, min_matched, out);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
 }
 
 int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t n, int64_t B, const int32_t* idx,

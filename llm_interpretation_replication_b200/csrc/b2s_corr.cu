@@ -21,9 +21,12 @@ namespace b2s {
 constexpr int CORR_MAX_P = 2048;      // Spearman: rows per resample that fit the shared-memory sort
 constexpr int CORR_MAX_PAIRS = 2048;  // stats kernel: pairs per resample (the reference samples at most 1000)
 
+// min_valid > 0: a column takes part in a resample only if at least min_valid of its resampled rows are not NaN (the
+// reference's cross-prompt bootstrap drops respondents who answered fewer than 5 of the sampled questions,
+// survey_analysis/survey_analysis_consolidated.py:520-523); its pairs are NaN for that resample.
 __global__ void __launch_bounds__(128)
 corr_pearson_kernel(const double* __restrict__ X, int P, int M, const int32_t* __restrict__ idx, int B,
-                    const int32_t* __restrict__ pairs, int n_pairs, double* __restrict__ corr) {
+                    const int32_t* __restrict__ pairs, int n_pairs, int min_valid, double* __restrict__ corr) {
   const int b = blockIdx.y;
   const int pr = blockIdx.x * blockDim.x + threadIdx.x;
   if (pr >= n_pairs) return;
@@ -32,15 +35,17 @@ corr_pearson_kernel(const double* __restrict__ X, int P, int M, const int32_t* _
   // Values are shifted by the first complete row so that a constant column gives EXACTLY zero variance (pandas'
   // Welford pass does: dx = vx - meanx is 0 at every step), whatever its value; NaN then, as in pandas.
   double x0 = 0.0, y0 = 0.0, sx = 0.0, sy = 0.0;
-  int n = 0;
+  int n = 0, nx = 0, ny = 0;
   for (int r = 0; r < P; ++r) {
     const size_t row = static_cast<size_t>(ib[r]) * M;
     const double x = X[row + ci], y = X[row + cj];
+    nx += (x == x); ny += (y == y);
     if (x == x && y == y) {
       if (n == 0) { x0 = x; y0 = y; }
       sx += x - x0; sy += y - y0; ++n;
     }
   }
+  if (nx < min_valid || ny < min_valid) n = 0;
   double out = CUDART_NAN;
   if (n >= 1) {
     const double mx = sx / n, my = sy / n;
@@ -206,37 +211,76 @@ corr_stats_kernel(const double* __restrict__ corr, int n_pairs, int n2, double* 
   }
 }
 
+// more pairs than the shared-memory sort holds: mean, population std and count only (median = NaN); two passes, sums in
+// a fixed order per thread and a fixed tree across threads -> deterministic
+__global__ void __launch_bounds__(256)
+corr_stats_big_kernel(const double* __restrict__ corr, int n_pairs, double* __restrict__ stats) {
+  __shared__ double s_red[8];
+  __shared__ double s_cnt[8];
+  const int b = blockIdx.x;
+  const double* c = corr + static_cast<size_t>(b) * n_pairs;
+  auto block_sum = [&](double v, double* red) {
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+#pragma unroll
+    for (int q = 16; q > 0; q >>= 1) v += __shfl_xor_sync(0xffffffffu, v, q);
+    __syncthreads();
+    if (l == 0) red[w] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int q = 0; q < 8; ++q) t += red[q];
+    return t;
+  };
+  double sum = 0.0, cnt = 0.0;
+  for (int t = threadIdx.x; t < n_pairs; t += blockDim.x) { const double v = c[t]; if (v == v) { sum += v; cnt += 1.0; } }
+  const double n = block_sum(cnt, s_cnt);
+  const double tot = block_sum(sum, s_red);
+  double* o = stats + static_cast<size_t>(b) * 4;
+  if (n == 0.0) { if (threadIdx.x == 0) { o[0] = o[1] = o[2] = CUDART_NAN; o[3] = 0.0; } return; }
+  const double mean = tot / n;
+  double q = 0.0;
+  for (int t = threadIdx.x; t < n_pairs; t += blockDim.x) { const double v = c[t]; if (v == v) q += (v - mean) * (v - mean); }
+  const double var = block_sum(q, s_red) / n;
+  if (threadIdx.x == 0) { o[0] = mean; o[1] = CUDART_NAN; o[2] = sqrt(var); o[3] = n; }
+}
+
 }  // namespace b2s
+
+extern "C" int b2s_corr_bootstrap_ex(const double* X, int32_t P, int32_t M, const int32_t* idx, int32_t B, const int32_t* pairs,
+                                     int32_t n_pairs, int32_t method, int32_t min_valid, double* corr, double* stats, void* stream);
 
 extern "C" int b2s_corr_bootstrap(const double* X, int32_t P, int32_t M, const int32_t* idx, int32_t B, const int32_t* pairs,
                                   int32_t n_pairs, int32_t method, double* corr, double* stats, void* stream) {
+  return b2s_corr_bootstrap_ex(X, P, M, idx, B, pairs, n_pairs, method, 0, corr, stats, stream);
+}
+
+extern "C" int b2s_corr_bootstrap_ex(const double* X, int32_t P, int32_t M, const int32_t* idx, int32_t B, const int32_t* pairs,
+                                     int32_t n_pairs, int32_t method, int32_t min_valid, double* corr, double* stats, void* stream) {
   using namespace b2s;
   B2S_REQUIRE(X && idx && pairs && corr, "corr_bootstrap: null argument");
   B2S_REQUIRE(P > 0 && M > 1 && B > 0 && n_pairs > 0, "corr_bootstrap: empty problem (P=%d M=%d B=%d pairs=%d)", P, M, B, n_pairs);
   B2S_REQUIRE(B <= 65535, "corr_bootstrap: at most 65535 resamples per call");
   B2S_REQUIRE(method == 0 || method == 1, "corr_bootstrap: method must be 0 (pearson) or 1 (spearman)");
+  B2S_REQUIRE(min_valid >= 0 && (min_valid == 0 || method == 0), "corr_bootstrap: min_valid is supported for pearson only");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (method == 0) {
     dim3 grid(static_cast<unsigned>(ceil_div(n_pairs, 128)), static_cast<unsigned>(B));
-    corr_pearson_kernel<<<grid, 128, 0, st>>>(X, P, M, idx, B, pairs, n_pairs, corr);
+    corr_pearson_kernel<<<grid, 128, 0, st>>>(X, P, M, idx, B, pairs, n_pairs, min_valid, corr);
     B2S_CHECK_LAUNCH();
   } else {
     B2S_REQUIRE(P <= CORR_MAX_P, "corr_bootstrap: spearman supports at most %d rows per resample (got %d)", CORR_MAX_P, P);
     int n2 = 1;
     while (n2 < P) n2 <<= 1;
     const size_t smem = static_cast<size_t>(n2) * (5 * sizeof(double) + sizeof(int));
-    static size_t attr_smem = 0;
-    if (smem > 48 * 1024 && smem > attr_smem) {
+    if (smem > 48 * 1024)   // per-device attribute: set whenever it is needed
       B2S_CHECK_CUDA(cudaFuncSetAttribute(corr_spearman_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      attr_smem = smem;
-    }
     dim3 grid(static_cast<unsigned>(n_pairs), static_cast<unsigned>(B));
     corr_spearman_kernel<<<grid, 256, smem, st>>>(X, P, M, idx, B, pairs, n_pairs, n2, corr);
     B2S_CHECK_LAUNCH();
   }
-  if (stats) {
-    B2S_REQUIRE(n_pairs <= CORR_MAX_PAIRS, "corr_bootstrap: per-resample statistics support at most %d pairs (got %d)",
-                CORR_MAX_PAIRS, n_pairs);
+  if (stats && n_pairs > CORR_MAX_PAIRS) {     // mean / std / count without the median (no shared-memory sort of that size)
+    corr_stats_big_kernel<<<static_cast<unsigned>(B), 256, 0, st>>>(corr, n_pairs, stats);
+    B2S_CHECK_LAUNCH();
+  } else if (stats) {
     int n2 = 1;
     while (n2 < n_pairs) n2 <<= 1;
     const size_t smem = static_cast<size_t>(n2) * (sizeof(double) + sizeof(int));

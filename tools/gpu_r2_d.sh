@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 cd "$(dirname "$0")/.."
 rm -f gpurun_out/summary_d.txt gpurun_out/d_ab.jsonl
 run() { name=$1; shift; timeout ${TMO:-900} "$@" > gpurun_out/$name.log 2>&1; echo "$name exit $?" | tee -a gpurun_out/summary_d.txt; }
-run d_tests python -m pytest tests/test_gpu_bootstrap.py tests/test_gpu_kernels.py tests/test_gpu_corr.py -q --maxfail=10 -rf
+run d_tests python -m pytest tests/test_gpu_bootstrap.py tests/test_gpu_kernels.py tests/test_gpu_corr.py tests/test_gpu_agreement.py tests/test_gpu_entrypoints.py -q --maxfail=10 -rf
 run d_boot python tools/boot_bench.py
 B="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-other-modes"
 for cfg in "" "--option gemm_prefetch=8" "--option gemm_band_n=-1" "--option gemm_prefetch=8 --option gemm_band_n=-1" "--option gemm_prefetch=16" "--option gemm_prefetch=4" "" "--option gemm_prefetch=8"; do
