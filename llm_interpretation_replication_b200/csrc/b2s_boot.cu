@@ -332,7 +332,7 @@ boot_resample_kernel(const double* __restrict__ vals, int F, int split, int n, l
 // order exactly as in the kernel above (same bits).
 constexpr int BT_ROWS = 256;
 template <int FT>    // FT = number of value rows when it is 1..4 or 6 (loops unroll, loads of four indices are in flight together); 0 = any F
-__global__ void __launch_bounds__(BT_ROWS)
+__global__ void __launch_bounds__(BT_ROWS, 2)
 boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, int n, long long B, const int32_t* __restrict__ idx,
                           double* __restrict__ boot, int stride_words) {
   const int F = FT > 0 ? FT : F_rt;
@@ -349,13 +349,26 @@ boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, 
     const int R = static_cast<int>(B - b0 < BT_ROWS ? B - b0 : BT_ROWS);
     const int4* g = reinterpret_cast<const int4*>(idx + b0 * n);
     const int nq = R * n4;
-#pragma unroll 5
-    for (int q = threadIdx.x; q < nq; q += BT_ROWS) {
-      int4 v;
-      asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(g + q));
-      const int r = q / n4, c4 = q - r * n4;
-      sidx[r * stride_words + c4] = static_cast<uint32_t>(v.x) | (static_cast<uint32_t>(v.y) << 8) | (static_cast<uint32_t>(v.z) << 16) |
-                                    (static_cast<uint32_t>(v.w) << 24);
+    // The table streams at HBM speed only with enough bytes in flight (~45 KB per SM): 13 independent 16-byte loads per
+    // thread are issued before the first one is consumed (53 KB per CTA), in two rounds for n = 100.
+    for (int q0 = threadIdx.x; q0 < nq; q0 += 13 * BT_ROWS) {
+      int4 v[13];
+#pragma unroll
+      for (int u = 0; u < 13; ++u) {
+        const int q = q0 + u * BT_ROWS;
+        if (q < nq)
+          asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(g + q));
+      }
+#pragma unroll
+      for (int u = 0; u < 13; ++u) {
+        const int q = q0 + u * BT_ROWS;
+        if (q < nq) {
+          const int r = q / n4, c4 = q - r * n4;
+          sidx[r * stride_words + c4] = static_cast<uint32_t>(v[u].x) | (static_cast<uint32_t>(v[u].y) << 8) |
+                                        (static_cast<uint32_t>(v[u].z) << 16) | (static_cast<uint32_t>(v[u].w) << 24);
+        }
+      }
     }
     __syncthreads();
     if (threadIdx.x < R) {
@@ -706,12 +719,13 @@ int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t
     if (idx != nullptr && n % 4 == 0 && n <= 256 && (reinterpret_cast<uintptr_t>(idx) & 15) == 0 && tile_smem <= 110 * 1024) {
       const long long tiles = ceil_div(B, BT_ROWS);
       const int per_sm = static_cast<int>((220 * 1024) / (tile_smem + 1024));
-      const long long cap = static_cast<long long>(sms) * (per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm));
+      const long long cap = static_cast<long long>(sms) * (per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm));   // registers allow two CTAs per SM
       const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
 #define B2S_BOOT_TILE(FT)                                                                                                     \
   do {                                                                                                                        \
     B2S_CHECK_CUDA(cudaFuncSetAttribute(boot_resample_tile_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
                                         static_cast<int>(tile_smem)));                                                        \
+    B2S_CHECK_CUDA(cudaFuncSetAttribute(boot_resample_tile_kernel<FT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100)); \
     boot_resample_tile_kernel<FT><<<grid, BT_ROWS, tile_smem, st>>>(vals, F, split, n, B, idx, boot, sw);                     \
   } while (0)
       switch (F) {
