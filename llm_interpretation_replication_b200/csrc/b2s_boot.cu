@@ -328,11 +328,13 @@ boot_resample_kernel(const double* __restrict__ vals, int F, int split, int n, l
 // byte and stores the rows in shared memory with a stride of an odd number of words, so that afterwards thread t walks
 // row t four indices per conflict-free 32-bit load.  The fp64 value gather is the other co-limiter (B * n * F shared
 // loads): the [F, n] table is replicated 16 times, element e of copy c at word pair e * 16 + c, and thread t uses copy
-// t mod 16 -- every lane of a half-warp then owns its bank pair and the gather never conflicts.  The sums run in index
-// order exactly as in the kernel above (same bits).
+// t mod 16 -- every lane of a half-warp then owns its bank pair and the gather never conflicts.  Each value row has its own
+// running fp64 sum in index order; rows are combined at the end (differs from the general kernel's interleaved order in
+// the last bits when several rows share a side).
 constexpr int BT_ROWS = 256;
+constexpr int BT_INFLIGHT = 7;     // 16-byte index loads a thread has in flight while staging (64 registers: four CTAs per SM)
 template <int FT>    // FT = number of value rows when it is 1..4 or 6 (loops unroll, loads of four indices are in flight together); 0 = any F
-__global__ void __launch_bounds__(BT_ROWS, 2)
+__global__ void __launch_bounds__(BT_ROWS, 4)
 boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, int n, long long B, const int32_t* __restrict__ idx,
                           double* __restrict__ boot, int stride_words) {
   const int F = FT > 0 ? FT : F_rt;
@@ -342,6 +344,8 @@ boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, 
   const int n4 = n >> 2;
   const long long tiles = (B + BT_ROWS - 1) / BT_ROWS;
   const double* tab = sv + (threadIdx.x & 15);                     // this thread's copy of the table
+  const int r_first = static_cast<int>(threadIdx.x) / n4, c_first = static_cast<int>(threadIdx.x) - r_first * n4;   // int4 number tid of a tile
+  const int dr = BT_ROWS / n4, dc = BT_ROWS - dr * n4;             // ... and what 256 int4 further on adds to (row, word)
   const int fstride = n * 16;                                      // doubles between value rows
   for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
     __syncthreads();                                               // the previous tile's rows have been consumed (and sv is filled)
@@ -349,50 +353,65 @@ boot_resample_tile_kernel(const double* __restrict__ vals, int F_rt, int split, 
     const int R = static_cast<int>(B - b0 < BT_ROWS ? B - b0 : BT_ROWS);
     const int4* g = reinterpret_cast<const int4*>(idx + b0 * n);
     const int nq = R * n4;
-    // The table streams at HBM speed only with enough bytes in flight (~45 KB per SM): 13 independent 16-byte loads per
-    // thread are issued before the first one is consumed (53 KB per CTA), in two rounds for n = 100.
-    for (int q0 = threadIdx.x; q0 < nq; q0 += 13 * BT_ROWS) {
-      int4 v[13];
+    // The table streams at HBM speed only with enough bytes in flight: BT_INFLIGHT independent 16-byte loads per thread are
+    // issued before the first one is consumed (28 KB per CTA, four CTAs per SM).  (row, word) of a staged int4 advance
+    // incrementally -- an integer division per 16 bytes would cost more instructions than everything else in the tile.
+    int r = r_first, c4 = c_first;
+    for (int q0 = threadIdx.x; q0 < nq; q0 += BT_INFLIGHT * BT_ROWS) {
+      int4 v[BT_INFLIGHT];
 #pragma unroll
-      for (int u = 0; u < 13; ++u) {
+      for (int u = 0; u < BT_INFLIGHT; ++u) {
         const int q = q0 + u * BT_ROWS;
         if (q < nq)
           asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
                        : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(g + q));
       }
 #pragma unroll
-      for (int u = 0; u < 13; ++u) {
+      for (int u = 0; u < BT_INFLIGHT; ++u) {
         const int q = q0 + u * BT_ROWS;
-        if (q < nq) {
-          const int r = q / n4, c4 = q - r * n4;
+        if (q < nq)
           sidx[r * stride_words + c4] = static_cast<uint32_t>(v[u].x) | (static_cast<uint32_t>(v[u].y) << 8) |
                                         (static_cast<uint32_t>(v[u].z) << 16) | (static_cast<uint32_t>(v[u].w) << 24);
-        }
+        r += dr; c4 += dc;
+        if (c4 >= n4) { c4 -= n4; ++r; }
       }
     }
     __syncthreads();
     if (threadIdx.x < R) {
       const uint32_t* row = sidx + threadIdx.x * stride_words;
       double lo = 0.0, hi = 0.0, ab0 = 0.0, ab1 = 0.0;
-      for (int j4 = 0; j4 < n4; ++j4) {
-        const uint32_t w = row[j4];
-        if constexpr (FT > 0) {
+      if constexpr (FT > 0) {
+        // one running sum per value row (no select on `split` inside the loop), four indices' loads in flight together
+        double sum[FT];
+#pragma unroll
+        for (int f = 0; f < FT; ++f) sum[f] = 0.0;
+        const uint32_t tab_addr = static_cast<uint32_t>(__cvta_generic_to_shared(tab));
+        const uint32_t fbytes = static_cast<uint32_t>(fstride) * 8u;
+        for (int j4 = 0; j4 < n4; ++j4) {
+          const uint32_t w = row[j4];
           double x[4][FT];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            const double* p = tab + ((w >> (8 * u)) & 255u) * 16;
+            // byte u of w is the index; its table row starts 128 bytes * index after this thread's copy
+            const uint32_t a = tab_addr + ((u == 0 ? (w << 7) : (u == 1 ? (w >> 1) : (u == 2 ? (w >> 9) : (w >> 17)))) & (255u << 7));
 #pragma unroll
-            for (int f = 0; f < FT; ++f) x[u][f] = p[f * fstride];
+            for (int f = 0; f < FT; ++f)
+              asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x[u][f]) : "r"(a + static_cast<uint32_t>(f) * fbytes));
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
 #pragma unroll
-            for (int f = 0; f < FT; ++f) {           // lo / hi in index order, value row by value row: same bits as the general kernel
-              if (f < split) lo += x[u][f]; else hi += x[u][f];
+            for (int f = 0; f < FT; ++f) {
+              sum[f] += x[u][f];
               if (u & 1) ab1 += fabs(x[u][f]); else ab0 += fabs(x[u][f]);
             }
           }
-        } else {
+        }
+#pragma unroll
+        for (int f = 0; f < FT; ++f) { if (f < split) lo += sum[f]; else hi += sum[f]; }
+      } else {
+        for (int j4 = 0; j4 < n4; ++j4) {
+          const uint32_t w = row[j4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const double* p = tab + ((w >> (8 * u)) & 255u) * 16;
@@ -719,7 +738,7 @@ int b2s_bootstrap_resample(const double* vals, int32_t F, int32_t split, int32_t
     if (idx != nullptr && n % 4 == 0 && n <= 256 && (reinterpret_cast<uintptr_t>(idx) & 15) == 0 && tile_smem <= 110 * 1024) {
       const long long tiles = ceil_div(B, BT_ROWS);
       const int per_sm = static_cast<int>((220 * 1024) / (tile_smem + 1024));
-      const long long cap = static_cast<long long>(sms) * (per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm));   // registers allow two CTAs per SM
+      const long long cap = static_cast<long long>(sms) * (per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm));   // registers allow four CTAs per SM
       const unsigned grid = static_cast<unsigned>(tiles < cap ? tiles : cap);
 #define B2S_BOOT_TILE(FT)                                                                                                     \
   do {                                                                                                                        \
