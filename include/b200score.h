@@ -37,7 +37,9 @@ enum { B2S_ARCH_FALCON = 0, B2S_ARCH_GPT_NEOX = 1, B2S_ARCH_LLAMA = 2, B2S_ARCH_
 enum { B2S_POS_ROPE = 0, B2S_POS_LEARNED = 1, B2S_POS_ALIBI = 2 };
 enum { B2S_ACT_GELU = 0, B2S_ACT_RELU = 1, B2S_ACT_GELU_TANH = 2 };   /* MLP activation when mlp_type == B2S_MLP_GELU */
 enum { B2S_NORM_LAYERNORM = 0, B2S_NORM_RMS = 1 };   /* RMSNorm: x * rsqrt(mean(x^2) + eps) * g, *_B slots null (HF llama LlamaRMSNorm) */
-enum { B2S_MLP_GELU = 0, B2S_MLP_SWIGLU = 1 };      /* SwiGLU: down(silu(gate(x)) * up(x)); W_UP slot = [2*d_ff, d_model], gate rows first */
+enum { B2S_MLP_GELU = 0, B2S_MLP_SWIGLU = 1 /* SwiGLU: down(silu(gate(x)) * up(x)); W_UP slot = [2*d_ff, d_model], gate rows first */,
+       B2S_MLP_SWIGLU_FUSED = 2 /* same MLP, W_UP rows interleaved (row 2i = gate_proj row i, row 2i+1 = up_proj row i): the
+                                   tensor-core modes form silu(gate)*up in the projection's epilogue, no elementwise pass */ };
 enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQA, cat(q,k,v)_proj of the Llama family */,
        B2S_QKV_NEOX_INTERLEAVED = 1 /* per head [q, k, v] */ };
 /* compute modes (tensor-core modes: fp32 accumulation in TMEM, fp32 residual stream, LayerNorm and softmax):
@@ -174,7 +176,8 @@ B2S_API int b2s_set_option(const char* name, int32_t value);
 /* ---- building blocks (exported so the parity tests can exercise each kernel through the ABI) ----
  * C[M,N] = A[M,K] . W[N,K]^T (+bias[N]) with the epilogues the decoder layers need; replaces the
  * FalconLinear / nn.Linear calls (HF falcon:60-65, gpt_neox:41-42,200-201).
- *  epilogue: 0 store bf16, 1 GELU(erf) then store bf16, 2 out_f32 += acc (residual), 4 store fp32 */
+ *  epilogue: 0 store bf16, 1 GELU(erf) then store bf16, 2 out_f32 += acc (residual), 4 store fp32,
+ *  6 SwiGLU: W rows alternate (gate_i, up_i), out is bf16 [M, N/2] = silu(acc[:, 2i]) * acc[:, 2i+1] (no bias) */
 B2S_API int b2s_gemm_bf16(const void* A /*bf16 [M,K]*/, const void* W /*bf16 [N,K]*/, const float* bias,
                   void* out, int32_t M, int32_t N, int32_t K, int32_t epilogue, void* stream);
 /* same as b2s_gemm_bf16 with fp16 operands (and fp16 16-bit outputs) */

@@ -49,7 +49,8 @@ static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
 
 // ---- epilogue codes (b200score.h) ---------------------------------------------------------------
-enum { EPI_STORE_BF16 = 0, EPI_GELU_BF16 = 1, EPI_RESID_F32 = 2, EPI_LMHEAD = 3, EPI_STORE_F32 = 4, EPI_QKV_ROPE = 5 };
+enum { EPI_STORE_BF16 = 0, EPI_GELU_BF16 = 1, EPI_RESID_F32 = 2, EPI_LMHEAD = 3, EPI_STORE_F32 = 4, EPI_QKV_ROPE = 5,
+       EPI_SWIGLU = 6 /* W rows interleaved (gate_i, up_i): out[M, N/2] = silu(acc[2i]) * acc[2i+1], 16-bit */ };
 
 // LM-head partial record per (row, vocab tile): 8 floats
 //   [0] max  [1] sum exp(x-max)  [2..6] top-5 (desc)  [7] argmax column (int bits)

@@ -348,6 +348,48 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
         tma_store_commit();
       }
     }
+  } else if constexpr (EPI == EPI_SWIGLU) {
+    // Llama-family MLP (HF llama LlamaMLP: down(silu(gate(x)) * up(x))): the rows of W alternate gate_i, up_i, so a thread
+    // holds both halves of every output element; 128 accumulator columns make one 64-column, 16-bit bulk store.
+    auto glu32 = [](const float (&a)[32], const float (&b)[32], float (&o)[32]) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        o[j] = __fdividef(a[2 * j], 1.f + __expf(-a[2 * j])) * a[2 * j + 1];
+        o[16 + j] = __fdividef(b[2 * j], 1.f + __expf(-b[2 * j])) * b[2 * j + 1];
+      }
+    };
+#pragma unroll 1
+    for (int g = 0; g < BN / 128; ++g) {
+      const int col0 = nb * BN + g * 128;          // accumulator column; the output column is col0 / 2
+      if (col0 >= p.N) break;
+      float o1[32], o2[32];
+      {
+        float a[32], b[32];
+        tmem_ld32(taddr + static_cast<uint32_t>(g * 128), a);
+        tmem_ld32(taddr + static_cast<uint32_t>(g * 128 + 32), b);
+        glu32(a, b, o1);
+        tmem_ld32(taddr + static_cast<uint32_t>(g * 128 + 64), a);
+        tmem_ld32(taddr + static_cast<uint32_t>(g * 128 + 96), b);
+        glu32(a, b, o2);
+      }
+      next_buffer(stage, my_line);
+      if (p.out_f16) stage_store16<true>(my_line, sw, o1, o2); else stage_store16<false>(my_line, sw, o1, o2);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) { tma_store_2d(tmC, stage, col0 / 2, row0); tma_store_commit(); }
+      if (p.out_split) {   // BF16_SPLIT: [hi | lo] halves for the down projection
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          o1[j] -= __bfloat162float(__float2bfloat16_rn(o1[j]));
+          o2[j] -= __bfloat162float(__float2bfloat16_rn(o2[j]));
+        }
+        next_buffer(stage, my_line);
+        stage_store16<false>(my_line, sw, o1, o2);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) { tma_store_2d(tmC, stage, p.out_split + col0 / 2, row0); tma_store_commit(); }
+      }
+    }
   } else {
     // 16-bit outputs: 64 columns (two TMEM chunks) per bulk store
     int slot = 0;
@@ -1199,8 +1241,10 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
                    const LmHeadArgs* lmh, cudaStream_t st, int act_f16, const RopeEpiArgs* rope, int a_split, int out_split,
                    int out_f16, int act_kind) {
   B2S_REQUIRE(!a_split || (K % BK == 0 && !act_f16), "gemm_bf16: split activations need K %% 64 == 0 and bf16 operands (K=%d)", K);
-  B2S_REQUIRE(!out_split || (N % 64 == 0 && g_opt_tma_store && (epilogue == EPI_STORE_BF16 || epilogue == EPI_GELU_BF16)),
-              "gemm_bf16: a split 16-bit output needs N %% 64 == 0, the TMA-store epilogue and a 16-bit store epilogue (N=%d)", N);
+  B2S_REQUIRE(!out_split || (N % (epilogue == EPI_SWIGLU ? 128 : 64) == 0 && g_opt_tma_store &&
+                             (epilogue == EPI_STORE_BF16 || epilogue == EPI_GELU_BF16 || epilogue == EPI_SWIGLU)),
+              "gemm_bf16: a split 16-bit output needs whole 64-column store groups, the TMA-store epilogue and a 16-bit store epilogue (N=%d)", N);
+  B2S_REQUIRE(epilogue != EPI_SWIGLU || (g_opt_tma_store && N % 16 == 0), "gemm_bf16: the SwiGLU epilogue needs the TMA-store epilogue and N %% 16 == 0");
   B2S_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
   B2S_REQUIRE(K % 8 == 0, "gemm_bf16: K=%d must be a multiple of 8 (16-byte TMA row pitch)", K);
   B2S_REQUIRE(epilogue == EPI_LMHEAD || N % 8 == 0, "gemm_bf16: N=%d must be a multiple of 8", N);
@@ -1221,7 +1265,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   p.tiles_n = static_cast<int>(ceil_div(N, BN));
   p.num_kb = static_cast<int>(ceil_div(K, BK)) * (a_split ? 2 : 1);
   p.k_wrap = a_split ? K / BK : 0;
-  p.out_split = out_split ? N : 0;
+  p.out_split = out_split ? (epilogue == EPI_SWIGLU ? N / 2 : N) : 0;
   // Rasterisation: the A panel of a group (group_m x 128 rows x K) is re-read by every wave of the group, so it
   // should stay L2-resident (<= ~40 MB); when K is so long that even 16 row-blocks exceed that, no cross-wave
   // reuse is possible and the near-square wave footprint (16 x 9 tiles) minimises the bytes each wave streams.
@@ -1267,7 +1311,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   CUtensorMap tc = ta;   // placeholder when the epilogue writes no [M,N] matrix
   if (p.tma_store) {
     const bool f32 = epilogue == EPI_RESID_F32 || epilogue == EPI_STORE_F32;
-    const uint64_t NC = static_cast<uint64_t>(N) * (out_split ? 2 : 1);
+    const uint64_t NC = static_cast<uint64_t>(epilogue == EPI_SWIGLU ? N / 2 : N) * (out_split ? 2 : 1);
     B2S_TRY(make_tmap_2d(&tc, out, static_cast<uint64_t>(M), NC, NC * (f32 ? 4 : 2), 32, f32 ? 32 : 64, f32 ? 4 : 2, p.out_f16));
   }
   switch (epilogue) {
@@ -1275,6 +1319,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
     case EPI_GELU_BF16: return launch_epi<EPI_GELU_BF16>(ta, tb, tb2, ta3, tc, p, st);
     case EPI_RESID_F32: return launch_epi<EPI_RESID_F32>(ta, tb, tb2, ta3, tc, p, st);
     case EPI_STORE_F32: return launch_epi<EPI_STORE_F32>(ta, tb, tb2, ta3, tc, p, st);
+    case EPI_SWIGLU: return launch_epi<EPI_SWIGLU>(ta, tb, tb2, ta3, tc, p, st);
     case EPI_QKV_ROPE:
       B2S_REQUIRE(rope && rope->pos && rope->slot && rope->cos && rope->sin && rope->kcache && rope->vcache,
                   "gemm_bf16: the QKV+RoPE epilogue needs its buffers");

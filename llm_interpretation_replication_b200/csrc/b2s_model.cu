@@ -218,7 +218,10 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
         B2S_TRY((launch_ln<AT, WT>(l2, rows, st)));
       }
     }
-    if (m->split && d.mlp_type == B2S_MLP_SWIGLU) {
+    if (d.mlp_type == B2S_MLP_SWIGLU_FUSED) {   // gate / up rows interleaved: silu(gate) * up formed in the projection's epilogue
+      B2S_TRY(gemm_tc_launch(mlp_in, m->lw(l, B2S_WL_W_UP), nullptr, w.act, rows, 2 * d.d_ff, dm, EPI_SWIGLU, nullptr, st, m->act_f16,
+                             nullptr, m->split, m->split));
+    } else if (m->split && d.mlp_type == B2S_MLP_SWIGLU) {
       // BF16_SPLIT: fp32 pre-activations, then one kernel forms the activation and its [hi | lo] halves
       const bool glu = d.mlp_type == B2S_MLP_SWIGLU;
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), glu ? nullptr : m->lwf(l, B2S_WL_B_UP), w.gu, rows, (glu ? 2 : 1) * d.d_ff, dm,
@@ -306,8 +309,11 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
               d.rotary_dim);
   B2S_REQUIRE(d.n_ln_per_layer == 1 || d.n_ln_per_layer == 2, "model_create: n_ln_per_layer must be 1 or 2");
   B2S_REQUIRE(d.norm_type == B2S_NORM_LAYERNORM || d.norm_type == B2S_NORM_RMS, "model_create: unknown norm_type %d", d.norm_type);
-  B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || d.mlp_type == B2S_MLP_SWIGLU, "model_create: unknown mlp_type %d", d.mlp_type);
-  B2S_REQUIRE(d.mlp_type != B2S_MLP_SWIGLU || !d.has_bias, "model_create: SwiGLU with biases is not supported");
+  B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || d.mlp_type == B2S_MLP_SWIGLU || d.mlp_type == B2S_MLP_SWIGLU_FUSED,
+              "model_create: unknown mlp_type %d", d.mlp_type);
+  B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || !d.has_bias, "model_create: SwiGLU with biases is not supported");
+  B2S_REQUIRE(d.mlp_type != B2S_MLP_SWIGLU_FUSED || d.compute_mode != B2S_MODE_FP32_CHECK,
+              "model_create: interleaved gate/up rows (B2S_MLP_SWIGLU_FUSED) are for the tensor-core modes");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
   B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_BF16_SPLIT ||
                   d.compute_mode == B2S_MODE_FP32_CHECK,

@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .shapes import DecoderShape, MODE_BF16_FAST, MODE_FP16, MODE_FP32_CHECK
+from .shapes import DecoderShape, MODE_BF16_FAST, MODE_FP16, MODE_FP32_CHECK, MLP_SWIGLU, MLP_SWIGLU_FUSED
 from . import weights as _weights
 
 MAX_LOOK_AHEAD = 10   # reference run_base_vs_instruct_100q.py:285
@@ -105,6 +105,14 @@ class Scorer:
             W = {k: (v.to(torch.float16) if _weights.is_matrix(k) and v.dtype != torch.float16 else v) for k, v in W.items()}
             if weights_dev.get("lm_head") is weights_dev.get("wte"):
                 W["lm_head"] = W["wte"]
+        mlp_type = shape.mlp_type
+        if mlp_type == MLP_SWIGLU and mode != MODE_FP32_CHECK:
+            # tensor-core modes: gate / up rows interleaved so that the projection's epilogue holds both halves of an output
+            mlp_type = MLP_SWIGLU_FUSED
+            ff = shape.d_ff
+            for l in range(shape.n_layer):
+                w = W[f"l{l}.w_up"]
+                W[f"l{l}.w_up"] = torch.stack((w[:ff], w[ff:]), dim=1).reshape(2 * ff, w.shape[1]).contiguous()
         if "rope_cos" not in W and shape.rotary_dim > 0:
             W["rope_cos"], W["rope_sin"] = _weights.rope_tables(shape, self.device)
         for k, v in W.items():
@@ -120,7 +128,7 @@ class Scorer:
                            vocab=shape.vocab, rotary_dim=shape.rotary_dim, norm_eps=shape.norm_eps,
                            parallel_residual=int(shape.parallel_residual), n_ln_per_layer=shape.n_ln_per_layer,
                            has_bias=int(shape.has_bias), qkv_layout=shape.qkv_layout, max_pos=shape.max_pos,
-                           compute_mode=mode, norm_type=shape.norm_type, mlp_type=shape.mlp_type,
+                           compute_mode=mode, norm_type=shape.norm_type, mlp_type=mlp_type,
                            pos_type=shape.pos_type, pos_offset=shape.pos_offset, act_type=shape.act_type,
                            emb_norm=int(shape.emb_norm))
         self._handle = C.c_void_p()

@@ -30,6 +30,8 @@ NORM_LAYERNORM = 0
 NORM_RMS = 1              # x * rsqrt(mean(x^2) + eps) * g, no bias   (HF llama LlamaRMSNorm)
 MLP_GELU = 0              # down(gelu(up(x)))
 MLP_SWIGLU = 1            # down(silu(gate(x)) * up(x)); the W_UP slot holds [gate rows; up rows]  (HF llama LlamaMLP)
+MLP_SWIGLU_FUSED = 2      # the same MLP with the W_UP rows interleaved (gate_0, up_0, gate_1, ...): what Scorer hands to the library in
+                          # the tensor-core modes, so that silu(gate) * up is formed in the GEMM epilogue
 
 # qkv column layouts (must match include/b200score.h)
 QKV_FALCON_MQA = 0       # [q_0 .. q_{nh-1}, k_0 .. k_{nkv-1}, v_0 .. v_{nkv-1}] each head_dim wide (HF falcon _split_heads with

@@ -91,8 +91,7 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
 
     def mlp_act(t, p, bias):
         up = F.linear(r(t), W[p + "w_up"].to(dtype), bias("b_up"))
-        if shape.mlp_type == MLP_SWIGLU:        # rows [0, ff) = gate_proj, [ff, 2ff) = up_proj
-            up = r(up)                          # the 16-bit modes store gate/up before the elementwise kernel
+        if shape.mlp_type == MLP_SWIGLU:        # rows [0, ff) = gate_proj, [ff, 2ff) = up_proj; formed on the fp32 accumulators
             return F.silu(up[..., :shape.d_ff]) * up[..., shape.d_ff:]
         if shape.act_type == ACT_RELU:
             return F.relu(up)

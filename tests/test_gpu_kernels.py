@@ -319,3 +319,20 @@ def test_gemm_tc_rasterisation_and_prefetch_knobs_keep_the_bits(opt, val, M, N, 
     ref = A.float() @ W.float().T
     ref = ref + resid if epi == 2 else torch.nn.functional.gelu(ref)
     assert ((got.float() - ref).abs() / (ref.abs() + 1.0)).max().item() <= 2e-3
+
+
+@pytest.mark.parametrize("M,ff,K", [(300, 704, 256), (1000, 14336, 512), (77, 1152, 520)])
+@pytest.mark.parametrize("f16", [False, True])
+def test_gemm_tc_swiglu_epilogue(M, ff, K, f16, cta_group):
+    """SwiGLU formed in the epilogue: W rows alternate gate_i, up_i; out[M, ff] = silu(gate) * up (HF llama LlamaMLP)."""
+    import gpu_util as U
+    dt = torch.float16 if f16 else torch.bfloat16
+    A = _rand((M, K), 1.0, 61, dt)
+    Wg, Wu = _rand((ff, K), 0.05, 62, dt), _rand((ff, K), 0.05, 63, dt)
+    W = torch.stack((Wg, Wu), dim=1).reshape(2 * ff, K).contiguous()
+    out = torch.empty((M, ff), dtype=dt, device="cuda")
+    (U.gemm_f16 if f16 else U.gemm_bf16)(A, W, None, 6, out=out)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.silu(A.float() @ Wg.float().T) * (A.float() @ Wu.float().T)
+    err = ((out.float() - ref).abs() / (ref.abs() + 1.0)).max().item()
+    assert err <= (2.0 ** -10 if f16 else 2.0 ** -7), err
