@@ -20,6 +20,9 @@
 
 namespace b2s {
 
+extern int g_opt_attn_ts;
+static inline bool g_opt_attn_ts_on() { return g_opt_attn_ts != 0; }
+
 static constexpr int AT_HD = 64;
 static constexpr int AT_BM = 128;          // tile rows
 static constexpr int AT_MAXKV = 256;       // keys per prompt supported by this kernel
@@ -324,10 +327,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 int g_opt_attn_hold_s = 0;   // b2s_set_option("attn_hold_s")
 
 // The caller decides which kernel to use from attn_tc_supported(); there is no silent fallback here.
-bool attn_tc_supported(int hd, int max_kv) { return hd == AT_HD && max_kv <= AT_MAXKV; }
+// prompt pass: head_dim 64 or 128 (second-generation kernel; the first-generation one below knows 64 only), <= 256 keys
+bool attn_tc_supported(int hd, int max_kv) { return (hd == AT_HD || (hd == 128 && g_opt_attn_ts_on())) && max_kv <= AT_MAXKV; }
 // one-token steps additionally need contiguous 64-wide query heads (the qkv row is read as a [heads, 64] matrix)
 bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride) {
-  return attn_tc_supported(hd, max_kv) && q_hstride == AT_HD && qkv_dim % AT_HD == 0 && q_base % AT_HD == 0;
+  return hd == AT_HD && max_kv <= AT_MAXKV && q_hstride == AT_HD && qkv_dim % AT_HD == 0 && q_base % AT_HD == 0;
 }
 
 extern int g_opt_attn_ts;

@@ -26,6 +26,14 @@ static constexpr int A2_Q_BYTES = A2_BM * A2_HD * 2;         // 16 KB per Q tile
 static constexpr int A2_NQ = 6;                              // Q ring depth
 static constexpr int A2_LANES = 4;
 static constexpr int A2_SMEM = 2 * A2_KV_BYTES + A2_NQ * A2_Q_BYTES + 1024 + 256;
+// head_dim 128 (StableLM-alpha, RedPajama-7B, Mistral, BLOOM ...): K, V and Q are staged as two 64-column sub-tiles each (a
+// 128B-swizzled K-major tile is 64 elements wide), S accumulates over both, O = P.V is two N = 64 products side by side.
+// K + V take 128 KB, so the Q ring is 3 deep; an item needs 256 tensor-memory columns (P over S[0,128), O in [128,256)):
+// two items in flight whatever the key count.
+template <int HD> constexpr int a2_nq() { return HD == 64 ? A2_NQ : 3; }
+template <int HD> constexpr int a2_q_bytes() { return A2_BM * HD * 2; }
+template <int HD> constexpr int a2_kv_bytes() { return A2_MAXKV * HD * 2; }
+template <int HD> constexpr int a2_smem() { return 2 * a2_kv_bytes<HD>() + a2_nq<HD>() * a2_q_bytes<HD>() + 1024 + 256; }
 static constexpr int A2_THREADS = A2_LANES * 128 + 32;       // 16 softmax warps + the issuer warp
 static constexpr uint32_t A2_TMEM_COLS = 512;
 
@@ -36,6 +44,7 @@ struct Attn2Params {
   int nh, nkv, rep;
   int q_base, q_hstride;
   float scale_log2e;
+  const float* alibi;     // per-head slopes (ALIBI kernels), or null
 };
 
 __device__ __forceinline__ uint32_t a2_idesc(int m, int n, int b_mn, bool f16) {
@@ -106,19 +115,61 @@ __device__ __forceinline__ bool a2_test(uint32_t bar, uint32_t parity) {   // no
 
 // One item for one thread (== tile row): wait for S, two passes over this row's S in tensor memory (max, then
 // exp / pack / store P over S), hand P to the issuer, wait for O, normalise and write 64 outputs.
+// a row of 64 outputs (two 32-column chunks of O) normalised and stored in the run's 16-bit format, or, with lo_off != 0, as
+// bf16 [hi | lo] halves (BF16_SPLIT: the dense projection reads this row that way whatever format Q/K/V/P had)
 template <bool F16>
+__device__ __forceinline__ void a2_store64(const float (&o0)[32], const float (&o1)[32], float inv, uint16_t* out_row, int lo_off) {
+  uint4* dst = reinterpret_cast<uint4*>(out_row);
+  if (lo_off) {
+    uint4* dlo = reinterpret_cast<uint4*>(out_row + lo_off);
+    auto hi = [inv](float x) { return x * inv; };
+    auto rem = [inv](float x) { const float y = x * inv; return y - __bfloat162float(__float2bfloat16_rn(y)); };
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      dst[q] = make_uint4(pack_bf16x2(hi(o0[8 * q]), hi(o0[8 * q + 1])), pack_bf16x2(hi(o0[8 * q + 2]), hi(o0[8 * q + 3])),
+                          pack_bf16x2(hi(o0[8 * q + 4]), hi(o0[8 * q + 5])), pack_bf16x2(hi(o0[8 * q + 6]), hi(o0[8 * q + 7])));
+      dlo[q] = make_uint4(pack_bf16x2(rem(o0[8 * q]), rem(o0[8 * q + 1])), pack_bf16x2(rem(o0[8 * q + 2]), rem(o0[8 * q + 3])),
+                          pack_bf16x2(rem(o0[8 * q + 4]), rem(o0[8 * q + 5])), pack_bf16x2(rem(o0[8 * q + 6]), rem(o0[8 * q + 7])));
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      dst[4 + q] = make_uint4(pack_bf16x2(hi(o1[8 * q]), hi(o1[8 * q + 1])), pack_bf16x2(hi(o1[8 * q + 2]), hi(o1[8 * q + 3])),
+                              pack_bf16x2(hi(o1[8 * q + 4]), hi(o1[8 * q + 5])), pack_bf16x2(hi(o1[8 * q + 6]), hi(o1[8 * q + 7])));
+      dlo[4 + q] = make_uint4(pack_bf16x2(rem(o1[8 * q]), rem(o1[8 * q + 1])), pack_bf16x2(rem(o1[8 * q + 2]), rem(o1[8 * q + 3])),
+                              pack_bf16x2(rem(o1[8 * q + 4]), rem(o1[8 * q + 5])), pack_bf16x2(rem(o1[8 * q + 6]), rem(o1[8 * q + 7])));
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
+                          pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
+                              pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
+  }
+}
+
+// One item for one thread (== tile row): wait for S, two passes over this row's S in tensor memory (max, then
+// exp / pack / store P over S), hand P to the issuer, wait for O, normalise and write HD outputs.
+// ALIBI: the score of key j is s_j * scale + slope * j (HF bloom build_alibi_tensor); `ab` = slope * log2(e).
+template <bool F16, int HD = 64, bool ALIBI = false>
 __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_live, int n_full, int n_p, int kvp, int limit, float sc,
                                         uint32_t bar_s, uint32_t bar_p, uint32_t bar_o, uint32_t bar_e, uint32_t ph, bool valid,
-                                        uint16_t* out_row, int lo_off = 0) {
+                                        uint16_t* out_row, int lo_off = 0, float ab = 0.f) {
   const uint32_t t_o = t_lane + o_off;
   a2_wait(bar_s, ph);
   tcgen05_fence_after();
-  // pass 1: row maximum over the visible keys
+  // pass 1: row maximum over the visible keys (ALIBI: of the biased, scaled scores)
   float m = -INFINITY;
   for (int c = 0; c < n_live; ++c) {
     float v[32];
     tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
-    if (c < n_full) {
+    if constexpr (ALIBI) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c * 32 + j <= limit) m = fmaxf(m, fmaf(v[j], sc, ab * static_cast<float>(c * 32 + j)));
+    } else if (c < n_full) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) m = fmaxf(m, v[j]);
     } else {
@@ -127,7 +178,7 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
         if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
     }
   }
-  const float ms = m * sc;
+  const float ms = ALIBI ? m : m * sc;
   // pass 2: p = 2^(s*scale*log2e - max), rounded to 16 bits, two per column over the first half of S
   float lsum = 0.f;
   for (int c = 0; c < n_p; ++c) {
@@ -135,7 +186,16 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
     if (c < n_live) {
       float v[32];
       tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
-      if (c < n_full) {
+      if constexpr (ALIBI) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float b0 = ab * static_cast<float>(c * 32 + j) - ms, b1 = ab * static_cast<float>(c * 32 + j + 1) - ms;
+          const float p0 = (c * 32 + j <= limit) ? a2_ex2(fmaf(v[j], sc, b0)) : 0.f;
+          const float p1 = (c * 32 + j + 1 <= limit) ? a2_ex2(fmaf(v[j + 1], sc, b1)) : 0.f;
+          lsum += p0 + p1;
+          pk[j >> 1] = pack16x2<F16>(p0, p1);
+        }
+      } else if (c < n_full) {
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
           const float p0 = a2_ex2(fmaf(v[j], sc, -ms)), p1 = a2_ex2(fmaf(v[j + 1], sc, -ms));
@@ -161,50 +221,24 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
   a2_tmem_st_wait();
   tcgen05_fence_before();
   mbar_arrive(bar_p);
-  // epilogue of this item: O / rowsum
+  // epilogue of this item: O / rowsum, 64 output columns at a time
   a2_wait(bar_o, ph);
   tcgen05_fence_after();
-  float o0[32], o1[32];
-  tmem_ld32(t_o, o0);
-  tmem_ld32(t_o + 32, o1);
-  tcgen05_fence_before();
-  mbar_arrive(bar_e);                   // the lane's columns may be overwritten by the next S
-  if (valid) {
-    const float inv = 1.f / lsum;
-    uint4* dst = reinterpret_cast<uint4*>(out_row);
-    if (lo_off) {
-      // BF16_SPLIT: the dense projection reads this row as [hi | lo] bf16 halves, whatever format Q/K/V/P had
-      uint4* dlo = reinterpret_cast<uint4*>(out_row + lo_off);
-      auto hi = [inv](float x) { return x * inv; };
-      auto rem = [inv](float x) { const float y = x * inv; return y - __bfloat162float(__float2bfloat16_rn(y)); };
+  const float inv = 1.f / lsum;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        dst[q] = make_uint4(pack_bf16x2(hi(o0[8 * q]), hi(o0[8 * q + 1])), pack_bf16x2(hi(o0[8 * q + 2]), hi(o0[8 * q + 3])),
-                            pack_bf16x2(hi(o0[8 * q + 4]), hi(o0[8 * q + 5])), pack_bf16x2(hi(o0[8 * q + 6]), hi(o0[8 * q + 7])));
-        dlo[q] = make_uint4(pack_bf16x2(rem(o0[8 * q]), rem(o0[8 * q + 1])), pack_bf16x2(rem(o0[8 * q + 2]), rem(o0[8 * q + 3])),
-                            pack_bf16x2(rem(o0[8 * q + 4]), rem(o0[8 * q + 5])), pack_bf16x2(rem(o0[8 * q + 6]), rem(o0[8 * q + 7])));
-      }
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        dst[4 + q] = make_uint4(pack_bf16x2(hi(o1[8 * q]), hi(o1[8 * q + 1])), pack_bf16x2(hi(o1[8 * q + 2]), hi(o1[8 * q + 3])),
-                                pack_bf16x2(hi(o1[8 * q + 4]), hi(o1[8 * q + 5])), pack_bf16x2(hi(o1[8 * q + 6]), hi(o1[8 * q + 7])));
-        dlo[4 + q] = make_uint4(pack_bf16x2(rem(o1[8 * q]), rem(o1[8 * q + 1])), pack_bf16x2(rem(o1[8 * q + 2]), rem(o1[8 * q + 3])),
-                                pack_bf16x2(rem(o1[8 * q + 4]), rem(o1[8 * q + 5])), pack_bf16x2(rem(o1[8 * q + 6]), rem(o1[8 * q + 7])));
-      }
-    } else {
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        dst[q] = make_uint4(pack16x2<F16>(o0[8 * q] * inv, o0[8 * q + 1] * inv), pack16x2<F16>(o0[8 * q + 2] * inv, o0[8 * q + 3] * inv),
-                            pack16x2<F16>(o0[8 * q + 4] * inv, o0[8 * q + 5] * inv), pack16x2<F16>(o0[8 * q + 6] * inv, o0[8 * q + 7] * inv));
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        dst[4 + q] = make_uint4(pack16x2<F16>(o1[8 * q] * inv, o1[8 * q + 1] * inv), pack16x2<F16>(o1[8 * q + 2] * inv, o1[8 * q + 3] * inv),
-                                pack16x2<F16>(o1[8 * q + 4] * inv, o1[8 * q + 5] * inv), pack16x2<F16>(o1[8 * q + 6] * inv, o1[8 * q + 7] * inv));
+  for (int h = 0; h < HD / 64; ++h) {
+    float o0[32], o1[32];
+    tmem_ld32(t_o + static_cast<uint32_t>(64 * h), o0);
+    tmem_ld32(t_o + static_cast<uint32_t>(64 * h + 32), o1);
+    if (h == HD / 64 - 1) {
+      tcgen05_fence_before();
+      mbar_arrive(bar_e);                 // the lane's columns may be overwritten by the next S
     }
+    if (valid) a2_store64<F16>(o0, o1, inv, out_row + 64 * h, lo_off);
   }
 }
 
-template <bool F16>
+template <bool F16, int HD, bool ALIBI>
 __global__ void __launch_bounds__(A2_THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const Attn2Params p) {
@@ -219,14 +253,15 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int base_lim = kl - ql + mt * A2_BM;           // last key visible to row 0 of the tile (causal)
   const int kv_tile = min(kl, base_lim + rows_here);   // keys visible to the last data row
   const int kvp = (kv_tile + 15) & ~15;                // MMA granularity (N % 16, K % 16)
-  const int nl = kvp <= 128 ? 4 : 2;                   // items in flight
+  constexpr int NQ = a2_nq<HD>(), Q_BYTES = a2_q_bytes<HD>(), KV_BYTES = a2_kv_bytes<HD>(), NSUB = HD / 64;
+  const int nl = (HD == 64 && kvp <= 128) ? 4 : 2;     // items in flight
   const uint32_t lane_cols = 512u / static_cast<uint32_t>(nl);
   const uint32_t o_off = nl == 4 ? 64u : 128u;         // O overlays S columns that P does not cover
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sK = base, sV = base + A2_KV_BYTES, sQ = base + 2 * A2_KV_BYTES;
-  const uint32_t bars = sQ + A2_NQ * A2_Q_BYTES;
+  const uint32_t sK = base, sV = base + KV_BYTES, sQ = base + 2 * KV_BYTES;
+  const uint32_t bars = sQ + NQ * Q_BYTES;
   // barriers (8 B each): kv, q[6], s[4], p[4], o[4], e[4]; then the TMEM slot
   const uint32_t bar_kv = bars;
   auto bar_q = [&](int b) { return bars + 8u * (1 + b); };
@@ -239,7 +274,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == A2_LANES * 128) {
     mbar_init(bar_kv, 1);
-    for (int b = 0; b < A2_NQ; ++b) mbar_init(bar_q(b), 1);
+    for (int b = 0; b < NQ; ++b) mbar_init(bar_q(b), 1);
     for (int l = 0; l < A2_LANES; ++l) {
       mbar_init(bar_s(l), 1); mbar_init(bar_p(l), 128); mbar_init(bar_o(l), 1); mbar_init(bar_e(l), 128);
     }
@@ -261,19 +296,22 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (lane == 0) {
       // ---------------- TMA + MMA issuer ----------------
       auto load_q = [&](int i) {
-        const uint32_t bq = bar_q(i % A2_NQ);
-        mbar_arrive_expect_tx(bq, A2_Q_BYTES);
-        tma_load_2d(sQ + (i % A2_NQ) * A2_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i) * p.q_hstride, q0);
+        const uint32_t bq = bar_q(i % NQ);
+        mbar_arrive_expect_tx(bq, Q_BYTES);
+#pragma unroll
+        for (int sb = 0; sb < NSUB; ++sb)
+          tma_load_2d(sQ + (i % NQ) * Q_BYTES + sb * A2_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i) * p.q_hstride + 64 * sb, q0);
       };
-      mbar_arrive_expect_tx(bar_kv, 2 * A2_KV_BYTES);
-      tma_load_2d(sK, &tmK, bar_kv, g * A2_HD, kv0);
-      tma_load_2d(sV, &tmV, bar_kv, g * A2_HD, kv0);
-      for (int i = 0; i < A2_NQ && i < n_items; ++i) load_q(i);
+      mbar_arrive_expect_tx(bar_kv, 2 * KV_BYTES);
+#pragma unroll
+      for (int sb = 0; sb < NSUB; ++sb) {
+        tma_load_2d(sK + sb * A2_KV_BYTES, &tmK, bar_kv, g * HD + 64 * sb, kv0);
+        tma_load_2d(sV + sb * A2_KV_BYTES, &tmV, bar_kv, g * HD + 64 * sb, kv0);
+      }
+      for (int i = 0; i < NQ && i < n_items; ++i) load_q(i);
       a2_wait(bar_kv, 0);
       const uint32_t idesc_s = a2_idesc(A2_BM, kvp, 0, F16);
-      const uint32_t idesc_o = a2_idesc(A2_BM, A2_HD, 1, F16);
-      const uint64_t kdesc = make_kmajor_sw128_desc(sK);
-      const uint64_t vdesc = a2_vdesc(sV);
+      const uint32_t idesc_o = a2_idesc(A2_BM, 64, 1, F16);      // one 64-column slice of O per product
       int is = 0, ipv = 0;
       uint32_t idle = 0;
       while (ipv < n_items) {
@@ -281,15 +319,19 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (is < n_items) {
           // S(is): its lane is free once the previous item of the lane has had its O read
           const int l = is & (nl - 1);
-          const int qb = is % A2_NQ;
+          const int qb = is % NQ;
           const bool free_lane = is < nl || a2_test(bar_e(l), static_cast<uint32_t>((is / nl) - 1) & 1u);
-          if (free_lane && a2_test(bar_q(qb), static_cast<uint32_t>(is / A2_NQ) & 1u)) {
+          if (free_lane && a2_test(bar_q(qb), static_cast<uint32_t>(is / NQ) & 1u)) {
             tcgen05_fence_after();
-            const uint64_t qdesc = make_kmajor_sw128_desc(sQ + qb * A2_Q_BYTES);
             const uint32_t t_s = tmem_base + static_cast<uint32_t>(l) * lane_cols;
 #pragma unroll
-            for (int k = 0; k < A2_HD / 16; ++k)
-              tcgen05_mma_bf16(t_s, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
+            for (int sb = 0; sb < NSUB; ++sb) {      // S accumulates over the 64-wide slices of the head dimension
+              const uint64_t qdesc = make_kmajor_sw128_desc(sQ + qb * Q_BYTES + sb * A2_Q_BYTES);
+              const uint64_t kdesc = make_kmajor_sw128_desc(sK + sb * A2_KV_BYTES);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tcgen05_mma_bf16(t_s, qdesc + 2u * k, kdesc + 2u * k, idesc_s, (sb | k) != 0 ? 1u : 0u);
+            }
             tcgen05_commit(bar_s(l));
             ++is; did = true;
           }
@@ -300,10 +342,14 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tcgen05_fence_after();
             const uint32_t t_p = tmem_base + static_cast<uint32_t>(l) * lane_cols;
             const uint32_t t_o = t_p + o_off;
-            for (int ks = 0; ks < kvp / 16; ++ks)   // 16 keys = 8 columns of packed P, 16 rows (2048 B) of V
-              a2_mma_ts(t_o, t_p + 8u * ks, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o, ks != 0 ? 1u : 0u);
+#pragma unroll
+            for (int sb = 0; sb < NSUB; ++sb) {
+              const uint64_t vdesc = a2_vdesc(sV + sb * A2_KV_BYTES);
+              for (int ks = 0; ks < kvp / 16; ++ks)   // 16 keys = 8 columns of packed P, 16 rows (2048 B) of V
+                a2_mma_ts(t_o + 64u * sb, t_p + 8u * ks, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o, ks != 0 ? 1u : 0u);
+            }
             tcgen05_commit(bar_o(l));
-            if (ipv + A2_NQ < n_items) load_q(ipv + A2_NQ);   // S(ipv) is complete, so its Q buffer is free
+            if (ipv + NQ < n_items) load_q(ipv + NQ);   // S(ipv) is complete, so its Q buffer is free
             ++ipv; did = true;
           }
         }
@@ -330,10 +376,12 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const float sc = p.scale_log2e;
     for (int i = l; i < n_items; i += nl) {
       const uint32_t ph = static_cast<uint32_t>(i / nl) & 1u;
-      const size_t owidth = static_cast<size_t>(p.nh) * A2_HD;
-      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (owidth << p.split) + static_cast<size_t>(h_first + i) * A2_HD;
-      a2_item<F16>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst,
-                   p.split ? static_cast<int>(owidth) : 0);
+      const size_t owidth = static_cast<size_t>(p.nh) * HD;
+      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (owidth << p.split) + static_cast<size_t>(h_first + i) * HD;
+      float ab = 0.f;
+      if constexpr (ALIBI) ab = p.alibi[h_first + i] * 1.4426950408889634f;
+      a2_item<F16, HD, ALIBI>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst,
+                              p.split ? static_cast<int>(owidth) : 0, ab);
     }
   }
 
@@ -493,17 +541,16 @@ int launch_attn_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_sl
 
 int g_opt_attn_ts = 1;   // b2s_set_option("attn_ts"): 1 = this kernel for the prompt pass, 0 = attn_tc_kernel
 
-int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
-  B2S_REQUIRE(attn_tc_supported(a.hd, a.max_kv), "attn_tc2: head_dim %d / %d keys not supported", a.hd, a.max_kv);
+template <bool F16, int HD, bool ALIBI>
+static int launch_tc2_t(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
   // per-device function attribute, and cheap: set on every launch rather than once per process
-  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
-  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM));
-  CUtensorMap tq, tk, tv;
+  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<F16, HD, ALIBI>, cudaFuncAttributeMaxDynamicSharedMemorySize, a2_smem<HD>()));
+  CUtensorMap tq, tk, tv;      // boxes are 64 columns wide whatever the head dimension (one swizzle atom)
   B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
-                            static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, A2_HD, a.f16));
-  const uint64_t kvw = static_cast<uint64_t>(a.nkv) * A2_HD;
-  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, A2_HD, a.f16));
-  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, A2_HD, a.f16));
+                            static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, 64, a.f16));
+  const uint64_t kvw = static_cast<uint64_t>(a.nkv) * HD;
+  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, 64, a.f16));
+  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, 64, a.f16));
   Attn2Params p;
   p.meta = a.meta;
   p.out = reinterpret_cast<uint16_t*>(a.out);
@@ -511,11 +558,24 @@ int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slo
   p.nh = a.nh; p.nkv = a.nkv; p.rep = a.rep;
   p.q_base = a.q_base; p.q_hstride = a.q_hstride;
   p.scale_log2e = a.scale * 1.4426950408889634f;
+  p.alibi = a.alibi;
   dim3 grid(n_seqs, static_cast<unsigned>(ceil_div(max_qlen, A2_BM)), a.nkv);
-  if (a.f16) attn_tc2_kernel<true><<<grid, A2_THREADS, A2_SMEM, st>>>(tq, tk, tv, p);
-  else attn_tc2_kernel<false><<<grid, A2_THREADS, A2_SMEM, st>>>(tq, tk, tv, p);
+  attn_tc2_kernel<F16, HD, ALIBI><<<grid, A2_THREADS, a2_smem<HD>(), st>>>(tq, tk, tv, p);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
+}
+
+int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
+  B2S_REQUIRE(attn_tc_supported(a.hd, a.max_kv), "attn_tc2: head_dim %d / %d keys not supported", a.hd, a.max_kv);
+  B2S_REQUIRE(a.q_base % 8 == 0 && a.q_hstride % 8 == 0, "attn_tc2: query heads must start at 16-byte boundaries");
+#define B2S_TC2(F, H, AL) return launch_tc2_t<F, H, AL>(a, n_seqs, total_rows, cache_slots, max_qlen, st)
+  if (a.hd == 64) {
+    if (a.alibi) { if (a.f16) B2S_TC2(true, 64, true); else B2S_TC2(false, 64, true); }
+    if (a.f16) B2S_TC2(true, 64, false); else B2S_TC2(false, 64, false);
+  }
+  if (a.alibi) { if (a.f16) B2S_TC2(true, 128, true); else B2S_TC2(false, 128, true); }
+  if (a.f16) B2S_TC2(true, 128, false); else B2S_TC2(false, 128, false);
+#undef B2S_TC2
 }
 
 }  // namespace b2s

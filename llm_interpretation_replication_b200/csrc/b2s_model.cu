@@ -198,7 +198,8 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.alibi = d.pos_type == B2S_POS_ALIBI ? reinterpret_cast<const float*>(m->gw(B2S_W_ALIBI)) : nullptr;
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
     // tensor-core kernel when the shape allows it (head_dim 64, <= 256 keys), CUDA-core kernel otherwise
-    const bool tc_ok = m->bf16 && at.alibi == nullptr && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
+    // (ALiBi: prompt pass only -- the one-token tensor-core kernel has no bias term)
+    const bool tc_ok = m->bf16 && (at.alibi == nullptr || max_qlen > 1) && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
                                                 : attn_tc_decode_supported(d.head_dim, max_kv, m->qkv_dim, m->q_base, m->q_hstride));
     if (tc_ok) {
       B2S_TRY(launch_attn_tc(at, n_seqs, rows, static_cast<int>(w.cache_slots), max_qlen, st));

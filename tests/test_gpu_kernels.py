@@ -244,6 +244,41 @@ def test_attention_bf16(use_tc, nh, nkv, phase):
         assert err <= (3e-2 if use_tc else 1.5e-2), (use_tc, ql, err)     # bf16 output (+ bf16 P on the tensor-core path)
 
 
+@pytest.mark.parametrize("nh,nkv,interleaved", [(4, 2, False), (3, 3, True), (8, 1, False), (6, 6, False)])
+def test_attention_tc_head_dim_128(nh, nkv, interleaved):
+    """Prompt pass on the tensor cores at head_dim 128 (StableLM-alpha / RedPajama-7B / Mistral / BLOOM shapes): K, V and Q
+    staged as two 64-wide sub-tiles, grouped-query and per-head [q, k, v] interleaved query layouts, ragged lengths up to
+    256 keys with cached keys in front of some prompts."""
+    from llm_interpretation_replication_b200 import _lib
+    lib = _lib.load()
+    hd = 128
+    qlens = [1, 2, 17, 64, 127, 128, 129, 190, 256, 33, 100, 192, 193]
+    extra = [0, 0, 3, 0, 0, 0, 0, 10, 0, 64, 28, 0, 0]
+    q_start, kv_start, t, c = [], [], 0, 0
+    for ql, ex in zip(qlens, extra):
+        q_start.append(t); kv_start.append(c); t += ql; c += ql + ex + 10
+    T, slots = t, c + 300
+    if interleaved:                      # HF gpt_neox: per head [q, k, v]
+        qkv_dim, q_base, q_hstride = 3 * nh * hd, 0, 3 * hd
+    else:
+        qkv_dim, q_base, q_hstride = (nh + 2 * nkv) * hd, 0, hd
+    qkv = _rand((T, qkv_dim), 1.0, 71)
+    kc, vc = _rand((slots, nkv * hd), 1.0, 72), _rand((slots, nkv * hd), 1.0, 73)
+    out = torch.zeros((T, nh * hd), dtype=torch.bfloat16, device="cuda")
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device="cuda")
+    kvl = [a + b for a, b in zip(qlens, extra)]
+    a_qs, a_ql, a_ks, a_kl = i32(q_start), i32(qlens), i32(kv_start), i32(kvl)
+    _lib.check(lib.b2s_attention_bf16(_lib.ptr(qkv), _lib.ptr(kc), _lib.ptr(vc), _lib.ptr(out), _lib.ptr(a_qs), _lib.ptr(a_ql),
+                                      _lib.ptr(a_ks), _lib.ptr(a_kl), len(qlens), T, slots, max(qlens), max(kvl), nh, nkv, hd,
+                                      qkv_dim, q_base, q_hstride, 1, _lib.current_stream()), "attention")
+    torch.cuda.synchronize()
+    q = qkv.view(T, -1, hd)[:, 0::3][:, :nh] if interleaved else qkv[:, :nh * hd].view(T, nh, hd)
+    ref = _attn_ref(q, kc.view(slots, nkv, hd), vc.view(slots, nkv, hd), list(zip(q_start, qlens, kv_start, kvl)), extra)
+    for (qs, ql), r in zip(zip(q_start, qlens), ref):
+        err = (out[qs:qs + ql].view(ql, nh, hd).float() - r).abs().max().item()
+        assert err <= 3e-2, (ql, err)
+
+
 @pytest.mark.parametrize("name,M,N,K,epi,f16", [("down", 16384, 4544, 18176, 2, True), ("up_gelu", 16384, 18176, 4544, 1, True),
                                                 ("down_bf16", 16384, 4544, 18176, 2, False)])
 def test_gemm_tc_default_policy_at_bench_sizes(name, M, N, K, epi, f16):
