@@ -164,6 +164,9 @@ B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* f
  *                        an A or W panel walk K together and hit in L2 (0 = never; bounded wait, cannot dead-lock)
  *   "gemm_group_m"       [0] rasterisation group in 128-row blocks (0 = heuristic); "gemm_small_w_group" [8] group used
  *                        when W itself is L2-sized
+ *   "gemm_band_n"        [-1] CTA-pair 256x256 kernel: tiles walked in column bands (all row blocks inside a band) so that a band of
+ *                        W stays L2-resident; -1 = only for launches whose W is L2-sized (QKV, dense), k > 0 = bands of k tiles, 0 = off
+ *   "gemm_prefetch"      [0] producers issue TMA L2 prefetches this many k-blocks ahead (measured: -11 % end to end; kept for A/B)
  *   "gemm_serpentine"    [0] K walked backwards by odd column tiles (1) or odd waves (2)
  *   "gemm_l2_hint"       [0] TMA L2 eviction hints 0..7; "gemm_tma_store" [1] epilogue through TMA bulk stores;
  *                        "gemm_pair_stride" [1] experiment: permutation of the CTA-pair -> tile-sequence assignment

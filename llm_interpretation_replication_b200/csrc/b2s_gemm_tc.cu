@@ -1135,7 +1135,7 @@ int g_opt_small_w_group = 8;   // rasterisation group when W is L2-sized (0 = ru
 // its tile falls in, i.e. on the batch around it -- sharded and unsharded runs stop being bit-identical.  1 = direction by
 // column tile: batch-invariant, but CTAs that share an A row-block no longer walk K together: -1 %.
 int g_opt_prefetch = 0;      // b2s_set_option "gemm_prefetch": L2 prefetch distance of the CTA-pair producers in k-blocks (0 = off)
-int g_opt_band_n = 0;        // b2s_set_option "gemm_band_n": 0 = row-group order; -1 = column bands when W is L2-sized; k > 0 = bands of k tiles
+int g_opt_band_n = -1;       // b2s_set_option "gemm_band_n": 0 = row-group order; -1 (default) = column bands when W is L2-sized; k > 0 = bands of k tiles
 int g_opt_policy = 1;        // b2s_set_option "gemm_policy" (see launch_epi)
 int g_opt_wave_sync = 4;     // b2s_set_option "gemm_wave_sync": all producers meet every N tiles (0 = never)
 // Meeting counters: one table per device (a __device__ array exists once on every GPU that loads the library).  Each
@@ -1272,7 +1272,7 @@ int gemm_tc_launch(const void* A, const void* W, const float* bias, void* out, i
   {
     const double mb_bytes = 2.0 * BM * K;
     int gm = 64;
-    while (gm > 16 && gm * mb_bytes > 40e6) gm >>= 1;
+    while (gm > 8 && gm * mb_bytes > 40e6) gm >>= 1;      // K = 18176 (down projection): 8 row-blocks = 37 MB (measured: -0.9 % time, -9 % DRAM vs 16; profiles/r2_gemm_probe.json)
     // a W that can stay L2-resident by itself (qkv, dense: 42 MB) is better served by one-wave groups: the A panel
     // is then 9 MB and W is the only thing re-read (measured: profiles/r1_gemm_l2_hints.txt, DRAM 5.4 -> 4.1 GB on qkv)
     if (g_opt_small_w_group > 0 && 2.0 * N * K <= 48e6) gm = g_opt_small_w_group;

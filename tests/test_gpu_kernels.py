@@ -331,7 +331,7 @@ def test_gemm_f32_large_matches_fp64():
     assert err <= 5e-5, err      # measured 2.4e-5: what one fp32 fmaf chain of 18176 terms costs
 
 
-@pytest.mark.parametrize("opt,val", [("gemm_band_n", 3), ("gemm_band_n", -1), ("gemm_prefetch", 8), ("gemm_prefetch", 3)])
+@pytest.mark.parametrize("opt,val", [("gemm_band_n", 3), ("gemm_band_n", 0), ("gemm_prefetch", 8), ("gemm_prefetch", 3)])
 @pytest.mark.parametrize("M,N,K,epi", [(9000, 4544, 4544, 2), (5000, 2304, 832, 1)])
 def test_gemm_tc_rasterisation_and_prefetch_knobs_keep_the_bits(opt, val, M, N, K, epi):
     """Column-band tile order and the producers' L2 prefetch change when a tile is computed and what is in L2, never a
@@ -349,7 +349,7 @@ def test_gemm_tc_rasterisation_and_prefetch_knobs_keep_the_bits(opt, val, M, N, 
         got = run()
         torch.cuda.synchronize()
     finally:
-        _lib.check(lib.b2s_set_option(opt.encode(), 0), "set_option")
+        _lib.check(lib.b2s_set_option(opt.encode(), -1 if opt == "gemm_band_n" else 0), "set_option")     # library defaults
     assert torch.equal(base, got), (opt, val)
     ref = A.float() @ W.float().T
     ref = ref + resid if epi == 2 else torch.nn.functional.gelu(ref)

@@ -13,12 +13,12 @@ from llm_interpretation_replication_b200 import _lib
 M = int(sys.argv[1]) if len(sys.argv) > 1 else 131072
 lib = _lib.load()
 st = _lib.current_stream()
-DEFAULTS = {"gemm_cta_group": 0, "gemm_wave_sync": 4, "gemm_band_n": 0, "gemm_prefetch": 0, "gemm_group_m": 0, "gemm_tma_store": 1}
+DEFAULTS = {"gemm_cta_group": 0, "gemm_wave_sync": 4, "gemm_band_n": -1, "gemm_prefetch": 0, "gemm_group_m": 0, "gemm_tma_store": 1}
 shapes = {"up": (18176, 4544), "dense": (4544, 4544), "qkv": (4672, 4544), "down": (4544, 18176)}
 # (label, epilogue or None = the layer's own, knob overrides)
 configs = [("default", None, {}), ("no_meeting", None, {"gemm_wave_sync": 0}), ("meeting_every_8", None, {"gemm_wave_sync": 8}),
            ("plain_store_epilogue", 0, {}), ("fp32_store_epilogue", 4, {}), ("pairs_512x256", None, {"gemm_cta_group": 3}),
-           ("single_cta", None, {"gemm_cta_group": 1}), ("column_bands", None, {"gemm_band_n": -1}),
+           ("single_cta", None, {"gemm_cta_group": 1}), ("row_groups_only", None, {"gemm_band_n": 0}),
            ("group_m_8", None, {"gemm_group_m": 8}), ("group_m_64", None, {"gemm_group_m": 64})]
 own_epi = {"up": 1, "dense": 2, "qkv": 0, "down": 2}
 for name, (N, K) in shapes.items():
