@@ -145,6 +145,64 @@ B2S_API int b2s_score_complete_host(b2s_model* m, const int32_t* tokens_h, const
                    float* out_h, int32_t* gen_ids_h /*or NULL*/,
                    void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- encoder-decoder scorer (T5 family) -----------------------------------------------------------
+ * Replaces the `is_encoder_decoder` branch of the same reference functions (compare_instruct_models.py:178-226,
+ * run_base_vs_instruct_100q.py:290-325, compare_base_vs_instruct.py:192-237: tk-instruct-3b-def, T0_3B, t5-v1_1-base,
+ * flan-t5-base): AutoModelForSeq2SeqLM.generate(input_ids, max_new_tokens, output_scores) = one encoder pass over the
+ * prompt (HF t5 T5Stack, bidirectional self-attention with the bucketed relative position bias of the first layer
+ * shared by all layers, no 1/sqrt(d) scaling, T5LayerNorm = RMSNorm, no biases), then greedy decoder steps from
+ * decoder_start_id (self-attention over the generated prefix with the decoder's relative bias, cross-attention over
+ * the encoder output without bias, ReLU or gated tanh-GELU feed-forward), the LM head on every step, and the same
+ * top-k look-ahead scan and position-0 fallback as the decoder-only branch.
+ *
+ * weight_ptrs: B2S_T5_NGLOBAL global slots, then n_enc_layer x B2S_T5_ENC_PER_LAYER, then n_dec_layer x
+ * B2S_T5_DEC_PER_LAYER.  Matrices [out, in] row-major in the mode's weight type, vectors and bias tables fp32.
+ *   ENC_BIAS / DEC_BIAS: fp32 [n_head, 2*max_pos - 1]; entry [h][(key position - query position) + max_pos - 1] =
+ *   relative_attention_bias.weight[bucket(key - query)][h] with HF's T5Attention._relative_position_bucket
+ *   (bidirectional for the encoder, not for the decoder).  The host expands the bucket table once per model, the way
+ *   it builds the rotary tables of the decoder-only families (llm_interpretation_replication_b200/t5.py bias_table).
+ *   W_QKV = rows of q, then k, then v ([3*n_head*head_dim, d_model]); W_CKV = cross-attention k rows then v rows.
+ *   W_UP: ff_type 0 = wi [d_ff, d_model] with ReLU; 1 = gated, wi_0 (tanh-GELU gate) rows then wi_1 rows
+ *   [2*d_ff, d_model]; 2 = gated with the rows interleaved (2i = wi_0 row i, 2i+1 = wi_1 row i; tensor-core modes:
+ *   the gate is formed in the projection's epilogue).
+ * A model with tied embeddings (original t5-*: logits = lm_head(hidden * d_model^-0.5)) is given with DEC_LNF_G
+ * pre-multiplied by d_model^-0.5; the v1.1 / Flan / LM-adapted checkpoints of the reference's lists are untied. */
+enum { B2S_T5_WTE = 0, B2S_T5_ENC_LNF_G = 1, B2S_T5_DEC_LNF_G = 2, B2S_T5_LM_HEAD = 3, B2S_T5_ENC_BIAS = 4, B2S_T5_DEC_BIAS = 5,
+       B2S_T5_NGLOBAL = 8, B2S_T5_ENC_PER_LAYER = 8, B2S_T5_DEC_PER_LAYER = 12 };
+enum { B2S_T5E_LN1_G = 0, B2S_T5E_W_QKV, B2S_T5E_W_O, B2S_T5E_LN2_G, B2S_T5E_W_UP, B2S_T5E_W_DOWN };
+enum { B2S_T5D_LN1_G = 0, B2S_T5D_W_QKV, B2S_T5D_W_O, B2S_T5D_LN2_G, B2S_T5D_W_CQ, B2S_T5D_W_CKV, B2S_T5D_W_CO, B2S_T5D_LN3_G,
+       B2S_T5D_W_UP, B2S_T5D_W_DOWN };
+enum { B2S_T5_FF_RELU = 0, B2S_T5_FF_GATED_GELU = 1, B2S_T5_FF_GATED_GELU_FUSED = 2 };
+
+typedef struct {
+  int32_t abi_version;       /* B2S_ABI_VERSION */
+  int32_t n_enc_layer, n_dec_layer, d_model, n_head, head_dim /* d_kv: 64 */, d_ff, vocab;
+  float   norm_eps;
+  int32_t ff_type;           /* B2S_T5_FF_* */
+  int32_t max_pos;           /* longest prompt / generated prefix the bias tables cover */
+  int32_t compute_mode;      /* B2S_MODE_* (same meaning as for the decoder-only handle) */
+  int32_t decoder_start_id;  /* config.decoder_start_token_id (T5: the pad id, 0) */
+} b2s_encdec_desc;
+
+typedef struct b2s_encdec b2s_encdec;
+
+B2S_API int    b2s_encdec_create(const b2s_encdec_desc* desc, const void* const* weight_ptrs, int32_t n_ptrs, int32_t device,
+                         b2s_encdec** out);
+B2S_API void   b2s_encdec_destroy(b2s_encdec* m);
+/* The cross-attention keys / values of every decoder layer stay resident for the whole call:
+ * max_tokens * n_dec_layer * 2 * n_head * head_dim elements dominate this figure (size the batch with it). */
+B2S_API size_t b2s_encdec_workspace_bytes(const b2s_encdec* m, int64_t max_tokens, int32_t max_seqs, int32_t max_gen_tokens);
+/* Same arguments, rows, compaction, range check and return codes as b2s_score_complete / b2s_score_complete_host.
+ * tokens are the ENCODER input ids (the T5 tokenizer's trailing </s> included); gen_ids the decoder's greedy tokens
+ * (the start id is not part of them). */
+B2S_API int b2s_encdec_score(b2s_encdec* m, const int32_t* tokens, const int32_t* cu_seqlens, int32_t n_seqs, int32_t total_tokens,
+                     int32_t max_seqlen, const int32_t* cand_ids /*[N,2]*/, int32_t topk, int32_t scan_positions,
+                     int32_t gen_tokens, int32_t eos_id, float* out /*[N,8]*/, int32_t* gen_ids /*[N,gen_tokens] or NULL*/,
+                     void* workspace, size_t workspace_bytes, void* stream);
+B2S_API int b2s_encdec_score_host(b2s_encdec* m, const int32_t* tokens_h, const int32_t* cu_seqlens_h, int32_t n_seqs,
+                          const int32_t* cand_ids_h, int32_t topk, int32_t scan_positions, int32_t gen_tokens, int32_t eos_id,
+                          float* out_h, int32_t* gen_ids_h /*or NULL*/, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Number of kernels this library launched since the last call with reset != 0 (bench "gpu_launches"). */
 B2S_API int64_t b2s_launch_count(int32_t reset);
 

@@ -35,6 +35,15 @@ class ModelDesc(C.Structure):
     ]
 
 
+class EncDecDesc(C.Structure):
+    _fields_ = [
+        ("abi_version", C.c_int32), ("n_enc_layer", C.c_int32), ("n_dec_layer", C.c_int32), ("d_model", C.c_int32),
+        ("n_head", C.c_int32), ("head_dim", C.c_int32), ("d_ff", C.c_int32), ("vocab", C.c_int32),
+        ("norm_eps", C.c_float), ("ff_type", C.c_int32), ("max_pos", C.c_int32), ("compute_mode", C.c_int32),
+        ("decoder_start_id", C.c_int32),
+    ]
+
+
 # every symbol include/b200score.h declares: name -> (restype, argtypes)
 _vp, _i32, _i64, _u32, _u64, _sz, _dbl = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_uint64, C.c_size_t, C.c_double
 SIGNATURES = {
@@ -47,6 +56,11 @@ SIGNATURES = {
     "b2s_score_host": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "b2s_score_complete": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "b2s_score_complete_host": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "b2s_encdec_create": (C.c_int, [C.POINTER(EncDecDesc), C.POINTER(_vp), _i32, _i32, C.POINTER(_vp)]),
+    "b2s_encdec_destroy": (None, [_vp]),
+    "b2s_encdec_workspace_bytes": (_sz, [_vp, _i64, _i32, _i32]),
+    "b2s_encdec_score": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "b2s_encdec_score_host": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "b2s_launch_count": (_i64, [_i32]),
     "b2s_set_option": (C.c_int, [C.c_char_p, _i32]),
     "b2s_profile_gemm": (C.c_int, [_i32]),

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200score.so")
-SOURCES = ["b2s_gemm_tc.cu", "b2s_gemm_f32.cu", "b2s_decoder.cu", "b2s_attn_tc.cu", "b2s_attn_tc2.cu", "b2s_boot.cu", "b2s_ci.cu", "b2s_corr.cu", "b2s_noalloc.cu", "b2s_model.cu"]
+SOURCES = ["b2s_gemm_tc.cu", "b2s_gemm_f32.cu", "b2s_decoder.cu", "b2s_attn_tc.cu", "b2s_attn_tc2.cu", "b2s_boot.cu", "b2s_ci.cu", "b2s_corr.cu", "b2s_noalloc.cu", "b2s_model.cu", "b2s_encdec.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

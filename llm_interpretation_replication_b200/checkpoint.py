@@ -12,6 +12,8 @@ sharded with ``model.safetensors.index.json``) or ``pytorch_model*.bin``.
 * ``flat_from_hf``          inverse of ``weights.to_hf_state_dict``.  The fused QKV matrices keep HF's own row order
   (Falcon ``[q heads..., k, v]`` HF falcon:285-288; NeoX per-head ``[q, k, v]`` HF gpt_neox:212-215): the kernels
   index them through ``qkv_layout``, nothing is permuted at load time.
+* ``t5_shape_from_hf_config`` / ``t5_flat_from_hf``  the same for the encoder-decoder checkpoints of the reference's lists
+  (T5 v1.1, Flan-T5, T0, Tk-Instruct) -> ``t5.EncDecShape`` and the layout of ``t5.slot_names``.
 * ``load_checkpoint``       streams tensor by tensor to the device in the compute dtype (a 7B model never holds a
   second host copy) and returns ``(shape, weights)`` ready for ``Scorer``.
 * ``load_tokenizer``        ``AutoTokenizer.from_pretrained(dir, local_files_only=True)`` passed through unchanged, so
@@ -253,6 +255,97 @@ def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.
     return W
 
 
+# ---- encoder-decoder (T5 family) ------------------------------------------------------------------------------------
+def t5_shape_from_hf_config(cfg: dict, name: str = "checkpoint"):
+    """HF:models/t5/configuration_t5.py -> ``t5.EncDecShape`` (google/t5-v1_1-base, google/flan-t5-base, bigscience/T0_3B,
+    allenai/tk-instruct-3b-def: compare_base_vs_instruct.py:137-138, compare_instruct_models.py:147,150)."""
+    from .t5 import EncDecShape
+    ffp = cfg.get("feed_forward_proj", "relu")
+    if ffp not in ("relu", "gated-gelu"):
+        raise KeyError(f"{name}: T5 feed_forward_proj {ffp!r} is not supported (relu, gated-gelu)")
+    if int(cfg.get("d_kv", 64)) != 64:
+        raise KeyError(f"{name}: T5 d_kv {cfg.get('d_kv')} is not supported (64)")
+    # Original T5 ties the head to the embedding and scales the decoder output by d_model^-0.5; v1.1 does neither.  Hub
+    # configs say so through `tie_word_embeddings`; configs re-saved by transformers >= 5 through `scale_decoder_outputs`
+    # (HF:models/t5/configuration_t5.py:77-83).  Whether a separate lm_head exists is read off the checkpoint itself.
+    scaled = bool(cfg["scale_decoder_outputs"]) if "scale_decoder_outputs" in cfg else cfg.get("tie_word_embeddings", True) is not False
+    n_enc = int(cfg["num_layers"])
+    n_dec = cfg.get("num_decoder_layers")
+    eos = cfg.get("eos_token_id", 1)
+    eos = eos[0] if isinstance(eos, (list, tuple)) else eos
+    return EncDecShape(name, n_enc, int(n_dec if n_dec is not None else n_enc), int(cfg["d_model"]), int(cfg["num_heads"]),
+                       int(cfg["d_ff"]), int(cfg["vocab_size"]), head_dim=64, norm_eps=float(cfg.get("layer_norm_epsilon", 1e-6)),
+                       gated=ffp == "gated-gelu", rel_buckets=int(cfg.get("relative_attention_num_buckets", 32)),
+                       rel_max_distance=int(cfg.get("relative_attention_max_distance", 128)),
+                       tied_head=scaled, eos_id=int(eos), pad_id=int(cfg.get("pad_token_id", 0)),
+                       decoder_start_id=int(cfg.get("decoder_start_token_id", 0)), max_pos=int(cfg.get("n_positions", 512)))
+
+
+_T5_GLOBAL = {"shared.weight": "wte", "encoder.final_layer_norm.weight": "enc_lnf_g", "decoder.final_layer_norm.weight": "dec_lnf_g",
+              "lm_head.weight": "lm_head",
+              "encoder.block.0.layer.0.SelfAttention.relative_attention_bias.weight": "enc_rel_bias",
+              "decoder.block.0.layer.0.SelfAttention.relative_attention_bias.weight": "dec_rel_bias"}
+_T5_ATT = {"q.weight": "w_qkv:0", "k.weight": "w_qkv:1", "v.weight": "w_qkv:2", "o.weight": "w_o"}
+_T5_CROSS = {"q.weight": "w_cq", "k.weight": "w_ckv:0", "v.weight": "w_ckv:1", "o.weight": "w_co"}
+_T5_FF = {"wi.weight": "w_up", "wi_0.weight": "w_up:0", "wi_1.weight": "w_up:1", "wo.weight": "w_down"}
+_T5_RE = re.compile(r"^(encoder|decoder)\.block\.(\d+)\.layer\.(\d)\.(layer_norm\.weight|SelfAttention\.(.+)|EncDecAttention\.(.+)|DenseReluDense\.(.+))$")
+
+
+def t5_flat_name(hf_name: str) -> Optional[str]:
+    if hf_name in _T5_GLOBAL:
+        return _T5_GLOBAL[hf_name]
+    m = _T5_RE.match(hf_name)
+    if not m:
+        return None      # encoder/decoder.embed_tokens.weight (copies of shared.weight) and anything else unused
+    stack, l, sub = m.group(1), int(m.group(2)), int(m.group(3))
+    p = f"{'e' if stack == 'encoder' else 'd'}{l}."
+    ff_sub = 1 if stack == "encoder" else 2
+    if m.group(4) == "layer_norm.weight":
+        return p + ("ln1_g" if sub == 0 else "ln2_g" if (sub == 1) else "ln3_g")
+    if m.group(5) is not None and sub == 0:
+        return p + _T5_ATT[m.group(5)] if m.group(5) in _T5_ATT else None
+    if m.group(6) is not None and stack == "decoder" and sub == 1:
+        return p + _T5_CROSS[m.group(6)] if m.group(6) in _T5_CROSS else None
+    if m.group(7) is not None and sub == ff_sub:
+        return p + _T5_FF[m.group(7)] if m.group(7) in _T5_FF else None
+    return None
+
+
+def t5_flat_from_hf(shape, tensors, device="cpu", weight_dtype=torch.float32) -> Dict[str, torch.Tensor]:
+    """HF T5 state dict (or an iterator of (name, tensor)) -> the flat layout of ``t5.slot_names`` (q/k/v, cross k/v and
+    wi_0/wi_1 fused by rows as they arrive).  The relative-bias tables stay in checkpoint form ([buckets, heads]);
+    ``EncDecScorer`` expands them."""
+    from . import t5 as _t5
+    items = tensors.items() if hasattr(tensors, "items") else tensors
+    d, ff, V, inner = shape.d_model, shape.d_ff, shape.vocab, shape.inner
+    want = {"wte": (V, d), "lm_head": (V, d), "enc_lnf_g": (d,), "dec_lnf_g": (d,), "enc_rel_bias": (shape.rel_buckets, shape.n_head),
+            "dec_rel_bias": (shape.rel_buckets, shape.n_head), "ln1_g": (d,), "ln2_g": (d,), "ln3_g": (d,), "w_o": (d, inner),
+            "w_co": (d, inner), "w_cq": (inner, d), "w_down": (d, ff), "w_up": (ff, d)}
+    W: Dict[str, torch.Tensor] = {}
+    for hf_name, t in items:
+        n = t5_flat_name(hf_name)
+        if n is None:
+            continue
+        leaf = n.split(".")[-1]
+        base_leaf = leaf.split(":")[0]
+        shp_want = want[base_leaf] if ":" not in leaf else ((ff, d) if base_leaf == "w_up" else (inner, d))
+        if tuple(t.shape) != shp_want:
+            raise ValueError(f"checkpoint tensor {hf_name} has shape {tuple(t.shape)}, the config implies {shp_want}")
+        W[n] = t.to(device=device, dtype=weight_dtype if _t5.is_matrix(n.split(":")[0]) else torch.float32).contiguous()
+        base = n.split(":")[0]
+        if base != n:
+            blocks = [f"{base}:{i}" for i in range(3 if base.endswith("w_qkv") else 2)]
+            if all(b in W for b in blocks):
+                W[base] = torch.cat([W.pop(b) for b in blocks], dim=0).contiguous()
+    if "lm_head" not in W:      # tied checkpoints store the shared embedding only
+        W["lm_head"] = W["wte"]
+    expected = [n for n in _t5.slot_names(shape) if n is not None and n not in ("enc_bias", "dec_bias")] + ["enc_rel_bias", "dec_rel_bias"]
+    missing = [n for n in expected if n not in W]
+    if missing:
+        raise ValueError(f"checkpoint is missing {len(missing)} tensors, e.g. {missing[:4]}")
+    return W
+
+
 def iter_checkpoint_tensors(path: str) -> Iterator[Tuple[str, torch.Tensor]]:
     st = sorted(glob.glob(os.path.join(path, "*.safetensors")))
     if st:
@@ -288,9 +381,22 @@ def resolve_local(model_name: str) -> Optional[str]:
 
 def load_checkpoint(path: str, device="cuda:0", weight_dtype=torch.float16, n_layer: int = 0):
     """(shape, weights on ``device``) from a local HF checkpoint directory.  ``n_layer`` > 0 keeps only the first
-    layers (smoke runs)."""
+    layers (smoke runs).  A T5 checkpoint comes back as (``t5.EncDecShape``, weights in the layout of ``t5.slot_names``)."""
     with open(os.path.join(path, "config.json")) as f:
         cfg = json.load(f)
+    if cfg.get("model_type") in ("t5", "mt5"):
+        from dataclasses import replace
+        shape = t5_shape_from_hf_config(cfg, name=os.path.basename(os.path.normpath(path)))
+        if n_layer:
+            shape = replace(shape, n_enc_layer=min(n_layer, shape.n_enc_layer), n_dec_layer=min(n_layer, shape.n_dec_layer))
+
+        def wanted_t5():
+            for k, v in iter_checkpoint_tensors(path):
+                m = _T5_RE.match(k)
+                if m and int(m.group(2)) >= (shape.n_enc_layer if m.group(1) == "encoder" else shape.n_dec_layer):
+                    continue
+                yield k, v
+        return shape, t5_flat_from_hf(shape, wanted_t5(), device=device, weight_dtype=weight_dtype)
     shape = shape_from_hf_config(cfg, name=os.path.basename(os.path.normpath(path)))
     if n_layer:
         shape = shape.with_layers(min(n_layer, shape.n_layer))

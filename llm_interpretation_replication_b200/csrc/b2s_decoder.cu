@@ -159,7 +159,7 @@ template int launch_ln<float, __half>(const LnArgs&, int, cudaStream_t);
 // =================================================================================================
 template <typename AT>
 __global__ void __launch_bounds__(256)
-swiglu_kernel(const AT* __restrict__ gu, AT* __restrict__ act, int64_t rows, int ff) {
+swiglu_kernel(const AT* __restrict__ gu, AT* __restrict__ act, int64_t rows, int ff, int gate_kind) {
   const int ff4 = ff >> 2;
   const int64_t n = rows * ff4;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
@@ -172,19 +172,21 @@ swiglu_kernel(const AT* __restrict__ gu, AT* __restrict__ act, int64_t rows, int
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float x = to_f32(g[k]);
-      o[k] = x / (1.f + expf(-x)) * to_f32(u[k]);
+      const float gate = gate_kind == B2S_ACT_GELU_TANH ? x * 0.5f * (1.0f + tanhf(0.79788456f * x * (1.0f + 0.044715f * x * x)))
+                                                        : x / (1.f + expf(-x));
+      o[k] = gate * to_f32(u[k]);
     }
     store4(act + r * ff + c, o[0], o[1], o[2], o[3]);
   }
 }
 
 template <typename AT>
-int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st) {
+int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st, int gate_kind) {
   B2S_REQUIRE(ff % 4 == 0, "swiglu: d_ff=%d must be a multiple of 4", ff);
   const int64_t n = rows * (ff >> 2);
   const int64_t blocks = ceil_div(n, 256);
   const unsigned grid = static_cast<unsigned>(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
-  swiglu_kernel<AT><<<grid, 256, 0, st>>>(reinterpret_cast<const AT*>(gu), reinterpret_cast<AT*>(act), rows, ff);
+  swiglu_kernel<AT><<<grid, 256, 0, st>>>(reinterpret_cast<const AT*>(gu), reinterpret_cast<AT*>(act), rows, ff, gate_kind);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
@@ -218,7 +220,8 @@ __global__ void __launch_bounds__(256)
 act_split_kernel(const float* __restrict__ pre, __nv_bfloat16* __restrict__ act, int64_t rows, int ff, int kind) {
   const int ff4 = ff >> 2;
   const int64_t n = rows * ff4;
-  const int64_t in_pitch = kind == 0 ? 2 * static_cast<int64_t>(ff) : ff;
+  const bool glu = kind == 0 || kind == 3;
+  const int64_t in_pitch = glu ? 2 * static_cast<int64_t>(ff) : ff;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     const int64_t r = i / ff4;
@@ -226,11 +229,12 @@ act_split_kernel(const float* __restrict__ pre, __nv_bfloat16* __restrict__ act,
     const float4 g = *reinterpret_cast<const float4*>(pre + r * in_pitch + c);
     const float x[4] = {g.x, g.y, g.z, g.w};
     float o[4];
-    if (kind == 0) {
+    if (glu) {
       const float4 u4 = *reinterpret_cast<const float4*>(pre + r * in_pitch + ff + c);
       const float u[4] = {u4.x, u4.y, u4.z, u4.w};
 #pragma unroll
-      for (int k = 0; k < 4; ++k) o[k] = x[k] / (1.f + expf(-x[k])) * u[k];
+      for (int k = 0; k < 4; ++k)
+        o[k] = (kind == 0 ? x[k] / (1.f + expf(-x[k])) : x[k] * 0.5f * (1.0f + tanhf(0.79788456f * x[k] * (1.0f + 0.044715f * x[k] * x[k])))) * u[k];
     } else {
 #pragma unroll
       for (int k = 0; k < 4; ++k)
@@ -241,7 +245,7 @@ act_split_kernel(const float* __restrict__ pre, __nv_bfloat16* __restrict__ act,
 }
 
 int launch_act_split(const float* pre, void* act, int64_t rows, int ff, int kind, cudaStream_t st) {
-  B2S_REQUIRE(ff % 4 == 0 && kind >= 0 && kind <= 2, "split activation: d_ff=%d kind=%d", ff, kind);
+  B2S_REQUIRE(ff % 4 == 0 && kind >= 0 && kind <= 3, "split activation: d_ff=%d kind=%d", ff, kind);
   const int64_t blocks = ceil_div(rows * (ff >> 2), 256);
   const unsigned grid = static_cast<unsigned>(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
   act_split_kernel<<<grid, 256, 0, st>>>(pre, reinterpret_cast<__nv_bfloat16*>(act), rows, ff, kind);
@@ -253,9 +257,9 @@ template int launch_act<float>(void*, int64_t, int, cudaStream_t);
 template int launch_act<__nv_bfloat16>(void*, int64_t, int, cudaStream_t);
 template int launch_act<__half>(void*, int64_t, int, cudaStream_t);
 
-template int launch_swiglu<float>(const void*, void*, int64_t, int, cudaStream_t);
-template int launch_swiglu<__nv_bfloat16>(const void*, void*, int64_t, int, cudaStream_t);
-template int launch_swiglu<__half>(const void*, void*, int64_t, int, cudaStream_t);
+template int launch_swiglu<float>(const void*, void*, int64_t, int, cudaStream_t, int);
+template int launch_swiglu<__nv_bfloat16>(const void*, void*, int64_t, int, cudaStream_t, int);
+template int launch_swiglu<__half>(const void*, void*, int64_t, int, cudaStream_t, int);
 
 // =================================================================================================
 // RoPE (rotate_half form on the first rotary_dim dims) + KV-cache append.
@@ -339,9 +343,9 @@ attn_kernel(AttnArgs a) {
   float* sV = sK + kv_rows * HDP;
   float* sQ = sV + kv_rows * HDP;                           // [warps][HD]
   float* sP = sQ + (ATT_THREADS / 32) * HD;                 // [warps][32]
-  const AT* kc = reinterpret_cast<const AT*>(a.kcache) + (static_cast<size_t>(kv0) * a.nkv + g) * HD;
-  const AT* vc = reinterpret_cast<const AT*>(a.vcache) + (static_cast<size_t>(kv0) * a.nkv + g) * HD;
-  const size_t kv_stride = static_cast<size_t>(a.nkv) * HD;
+  const size_t kv_stride = a.kv_stride ? static_cast<size_t>(a.kv_stride) : static_cast<size_t>(a.nkv) * HD;
+  const AT* kc = reinterpret_cast<const AT*>(a.kcache) + static_cast<size_t>(kv0) * kv_stride + g * HD;
+  const AT* vc = reinterpret_cast<const AT*>(a.vcache) + static_cast<size_t>(kv0) * kv_stride + g * HD;
   if (!KV_GLOBAL) {
     for (int idx = threadIdx.x; idx < kl * HD; idx += blockDim.x) {
       const int j = idx / HD, dd = idx - j * HD;
@@ -362,7 +366,9 @@ attn_kernel(AttnArgs a) {
     const AT* qp = qkv + row * a.qkv_dim + a.q_base + h * a.q_hstride;
     for (int dd = lane; dd < HD; dd += 32) q[dd] = to_f32(qp[dd]) * a.scale;
     __syncwarp();
-    const int nkeys = kl - ql + qi + 1;     // causal: query qi sees keys [0, nkeys)
+    const int qpos = kl - ql + qi;                       // position of this query among the keys
+    const int nkeys = a.noncausal ? kl : qpos + 1;       // causal: query qi sees keys [0, qpos]
+    const float* rb = a.relbias ? a.relbias + static_cast<size_t>(h) * (2 * a.rel_R + 1) + (a.rel_R - qpos) : nullptr;
     float m = -INFINITY, l = 0.f;
     float acc[DPL];
 #pragma unroll
@@ -392,6 +398,7 @@ attn_kernel(AttnArgs a) {
         }
         s = d0 + d1;
         if (a.alibi) s += a.alibi[h] * static_cast<float>(j);     // HF bloom: alibi = slope[head] * key position
+        if (rb) s += rb[j];                                        // HF t5: position_bias[head][query, key]
       }
       const float mn = fmaxf(m, warp_max(s));
       const float p = (j < nkeys) ? __expf(s - mn) : 0.f;

@@ -55,6 +55,12 @@ struct AttnArgs {
   int heads_per_cta;   // set by the launcher: ATT_HG for prefill, all heads of the KV head for single-token steps
   float scale;
   int split;           // BF16_SPLIT: output rows are [hi(nh*hd) | lo(nh*hd)] bf16
+  // encoder-decoder (T5) forms, CUDA-core kernel only:
+  const float* relbias;  // [nh, 2*rel_R + 1] additive bias by (key position - query position), or null
+  int rel_R;
+  int noncausal;         // every query row sees all kv_len keys (encoder self-attention, cross-attention)
+  int kv_stride;         // elements between consecutive keys in kcache / vcache (0 = nkv*hd): K/V read in place from a
+                         // fused projection output instead of a cache
 };
 
 struct ScanState {
@@ -79,11 +85,12 @@ template <typename AT, typename WT> int launch_ln(const LnArgs& a, int n_rows, c
 template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
 // act[r, j] = silu(gu[r, j]) * gu[r, ff + j]   (HF llama LlamaMLP: act_fn(gate_proj(x)) * up_proj(x))
-template <typename AT> int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st);
+// gate_kind B2S_ACT_GELU_TANH: tanh-GELU gate instead of SiLU (HF t5 T5DenseGatedActDense: act(wi_0(x)) * wi_1(x))
+template <typename AT> int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st, int gate_kind = 0);
 // x = relu(x) (kind 1) or tanh-GELU(x) (kind 2) in place (HF opt ReLU MLP; HF bloom bloom_gelu_forward)
 template <typename AT> int launch_act(void* x, int64_t n, int kind, cudaStream_t st);
 // BF16_SPLIT: the MLP pre-activations arrive in fp32 (pre [rows, ff], or [rows, 2*ff] = gate | up for kind 0) and the
-// activation leaves as [rows, hi(ff) | lo(ff)] bf16.  kind 0 = SwiGLU, 1 = ReLU, 2 = tanh-GELU.
+// activation leaves as [rows, hi(ff) | lo(ff)] bf16.  kind 0 = SwiGLU, 1 = ReLU, 2 = tanh-GELU, 3 = tanh-GELU gate * up.
 int launch_act_split(const float* pre, void* act, int64_t rows, int ff, int kind, cudaStream_t st);
 // tcgen05 prefill attention (b2s_attn_tc.cu): head_dim 64, <= 256 keys per sequence
 bool attn_tc_supported(int hd, int max_kv);

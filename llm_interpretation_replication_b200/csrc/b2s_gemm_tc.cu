@@ -351,11 +351,21 @@ __device__ __forceinline__ void epilogue_tile_tma(const GemmParams& p, const CUt
   } else if constexpr (EPI == EPI_SWIGLU) {
     // Llama-family MLP (HF llama LlamaMLP: down(silu(gate(x)) * up(x))): the rows of W alternate gate_i, up_i, so a thread
     // holds both halves of every output element; 128 accumulator columns make one 64-column, 16-bit bulk store.
-    auto glu32 = [](const float (&a)[32], const float (&b)[32], float (&o)[32]) {
+    // act_kind B2S_ACT_GELU_TANH: the gate is tanh-GELU (HF t5 T5DenseGatedActDense, "gelu_new") instead of SiLU
+    const bool gelu_gate = p.act_kind == B2S_ACT_GELU_TANH;
+    auto glu32 = [gelu_gate](const float (&a)[32], const float (&b)[32], float (&o)[32]) {
+      if (gelu_gate) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        o[j] = __fdividef(a[2 * j], 1.f + __expf(-a[2 * j])) * a[2 * j + 1];
-        o[16 + j] = __fdividef(b[2 * j], 1.f + __expf(-b[2 * j])) * b[2 * j + 1];
+        for (int j = 0; j < 16; ++j) {
+          o[j] = mlp_act(a[2 * j], B2S_ACT_GELU_TANH) * a[2 * j + 1];
+          o[16 + j] = mlp_act(b[2 * j], B2S_ACT_GELU_TANH) * b[2 * j + 1];
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          o[j] = __fdividef(a[2 * j], 1.f + __expf(-a[2 * j])) * a[2 * j + 1];
+          o[16 + j] = __fdividef(b[2 * j], 1.f + __expf(-b[2 * j])) * b[2 * j + 1];
+        }
       }
     };
 #pragma unroll 1

@@ -8,7 +8,7 @@ import sys
 
 import torch
 
-from .. import shapes, weights
+from .. import shapes, t5, weights
 from ..scorer import Scorer
 from ..tokenizer import HashTokenizer
 
@@ -60,25 +60,42 @@ def model_seed(model_name: str) -> int:
     return zlib.crc32(model_name.encode()) & 0x7FFFFFFF
 
 
-def load_model(model_name: str, device=None, mode=shapes.MODE_FP16, n_layer: int = 0, max_tokens: int = 65536,
+def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_tokens: int = 65536,
                max_seqs: int = 1024):
     """AutoTokenizer/AutoModelForCausalLM.from_pretrained of the reference (:416-450).  A checkpoint that is on disk
     (``model_name`` is a directory, or ``$B2S_CHECKPOINT_ROOT/<model_name>`` exists; see ``checkpoint.py``) is loaded
     with its own tokenizer.  Otherwise (no hub access here) the stand-in is the shape of the named hub model with
     random-init weights seeded by the name and the offline tokenizer.  Raises KeyError for architectures outside the
-    supported families, which the callers turn into NaN rows as the reference does for models that fail to load."""
+    supported families, which the callers turn into NaN rows as the reference does for models that fail to load.
+    ``mode`` None = FP16 for the decoder-only families, BF16_SPLIT for the T5 family (whose feed-forward activations are
+    the known case of values beyond fp16's range; see ``t5.EncDecScorer``)."""
     from .. import checkpoint
     from ..scorer import MAX_LOOK_AHEAD
     device = torch.device(device if device is not None else "cuda:0")
-    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
     local = checkpoint.resolve_local(model_name)
+    if mode is None:
+        is_t5 = model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY
+        if local is not None:
+            with open(os.path.join(local, "config.json")) as f:
+                is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
+        mode = shapes.MODE_BF16_SPLIT if is_t5 else shapes.MODE_FP16
+    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
     if local is not None:
         shp, W = checkpoint.load_checkpoint(local, device=device, weight_dtype=dt, n_layer=n_layer)
         try:
             tok = checkpoint.load_tokenizer(local)
         except Exception as e:   # weights without tokenizer files: offline tokenizer, said out loud
             log_print(f"  no usable tokenizer under {local} ({type(e).__name__}); using the offline HashTokenizer")
-            tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
+            tok = (HashTokenizer(shp.vocab, eos_token_id=shp.eos_id, append_eos=True, pad_token_id=shp.pad_id)
+                   if getattr(shp, "is_encoder_decoder", False) else HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default())
+    elif model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY:
+        # encoder-decoder stand-in: the named T5 shape, random-init, offline tokenizer in its T5 form (</s> appended, pad 0)
+        from dataclasses import replace
+        shp = (t5.HUB_TO_SHAPE.get(model_name) or t5.REGISTRY[model_name])()
+        if n_layer:
+            shp = replace(shp, n_enc_layer=min(n_layer, shp.n_enc_layer), n_dec_layer=min(n_layer, shp.n_dec_layer))
+        W = t5.init_weights(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
+        tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id, append_eos=True, pad_token_id=shp.pad_id)
     else:
         if model_name in shapes.HUB_TO_SHAPE:
             shp = shapes.HUB_TO_SHAPE[model_name]()
@@ -90,6 +107,11 @@ def load_model(model_name: str, device=None, mode=shapes.MODE_FP16, n_layer: int
             shp = shp.with_layers(n_layer)
         W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
         tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
+    if getattr(shp, "is_encoder_decoder", False):
+        # the cross-attention K/V of every decoder layer stay resident per call: a smaller token budget than a decoder-only model
+        scorer = t5.EncDecScorer(shp, W, mode=mode, device=device, max_tokens=min(max_tokens, 32768), max_seqs=min(max_seqs, 512),
+                                 max_lookahead=max(MAX_LOOK_AHEAD, COMPLETION_TOKENS))
+        return scorer, tok
     scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs,
                     max_lookahead=max(MAX_LOOK_AHEAD, COMPLETION_TOKENS))
     return scorer, tok

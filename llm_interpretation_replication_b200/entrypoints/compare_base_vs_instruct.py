@@ -10,8 +10,9 @@ variant (top-2, candidate ids WITH special tokens, ``max_length = len + 50``, ``
 NaN rows for a model that cannot be run or a prompt that fails (:472-492); ``prepare_data_for_csv`` (:90-111) with the
 columns prompt, model, model_family, base_or_instruct, model_output, yes_prob, no_prob, odds_ratio and
 ``model_family = name.split('/')[1].split('-')[0].lower()``.  The per-prompt loop (:456-480) is one batched call into
-libb200score per model.  Encoder-decoder models (the T5 pair) and architectures that need custom modelling code (Qwen-1)
-produce the reference's NaN rows.  The reference's cache purge (:62-88) is deliberately not reproduced.
+libb200score per model.  The T5 pair runs through ``t5.EncDecScorer`` (the script's encoder-decoder branch :192-237: bare-word
+candidate ids, ``max_length=50`` = 49 generated tokens); architectures that need custom modelling code (Qwen-1) produce the
+reference's NaN rows.  The reference's cache purge (:62-88) is deliberately not reproduced.
 
     python -m llm_interpretation_replication_b200.entrypoints.compare_base_vs_instruct [--out DIR] [--layers N] [--questions K]
 """
@@ -72,8 +73,9 @@ def run(prompts, pairs=None, n_layer=0, device=None, shard_group=None):
             formatted = [format_prompt(model_name, p) for p in prompts]
             try:
                 scorer, tok = load_model(model_name, device=device, n_layer=n_layer)
-                rows = S.score_prompts(scorer, tok, formatted, variant="base_vs", shard_group=shard_group,
-                                       gen_tokens=COMPLETION_TOKENS)
+                # reference :199 generates with max_length=50 in the encoder-decoder branch: the start token counts, 49 new ones
+                n_gen = COMPLETION_TOKENS - 1 if getattr(scorer, "is_encoder_decoder", False) else COMPLETION_TOKENS
+                rows = S.score_prompts(scorer, tok, formatted, variant="base_vs", shard_group=shard_group, gen_tokens=n_gen)
                 for p, r in zip(prompts, rows):
                     outputs[model_name][p] = r
             except Exception as e:      # reference :482-492: the error is stored for every prompt of the model

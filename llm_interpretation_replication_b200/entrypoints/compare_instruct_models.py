@@ -5,8 +5,9 @@ the reference except for the prompt list and the CSV name).
 Keeps the model list (:145-166), the bare / Baichuan prompt formats (:488-492), the k=2 scorer variant with
 candidate ids resolved WITH special tokens (:229-233), the NaN rows for models that cannot be run (:502-522), and
 `prepare_data_for_csv` (:103-121) with columns prompt, model, model_family, model_output, yes_prob, no_prob,
-relative_prob.  Eight of the ten models run (Falcon, GPT-NeoX, Mistral, OPT and BLOOM families); the encoder-decoder models
-(tk-instruct, T0: the T5 branch at :178-226) and the two that need custom modelling code (Baichuan2, Qwen-1) get the reference's
+relative_prob.  Eight of the ten models run: the Falcon, GPT-NeoX, Mistral, OPT and BLOOM families through the decoder-only
+scorer, the encoder-decoder models (tk-instruct, T0: the T5 branch at :178-226) through ``t5.EncDecScorer`` with the bare-word
+candidate ids of that branch (:197-198); the two that need custom modelling code (Baichuan2, Qwen-1) get the reference's
 NaN rows ("next" row N4).  The reference's cache purge (:81-101) is deliberately not reproduced.
 
     python -m llm_interpretation_replication_b200.entrypoints.compare_instruct_models [--survey 1|2] [--out DIR]

@@ -269,17 +269,26 @@ def _nan_dict(variant: str, prompt: str, err: Exception) -> dict:
     return d
 
 
-def tokenize_prompts(tokenizer, prompts, variant, cand_strings=None):
-    """Token ids per prompt and the [N,2] candidate-id table, resolved as the chosen entry point does."""
+def candidate_ids_encdec(tokenizer, yes: str = "Yes", no: str = "No") -> Tuple[int, int]:
+    """Candidate ids as the `is_encoder_decoder` branch of every reference script resolves them: first id of the bare
+    word, special tokens included (compare_instruct_models.py:197-198, run_base_vs_instruct_100q.py:305-306,
+    compare_base_vs_instruct.py:211-212; the T5 tokenizers append </s>, so [0] is the word piece)."""
+    return int(tokenizer(yes).input_ids[0]), int(tokenizer(no).input_ids[0])
+
+
+def tokenize_prompts(tokenizer, prompts, variant, cand_strings=None, encdec: bool = False):
+    """Token ids per prompt and the [N,2] candidate-id table, resolved as the chosen entry point does (``encdec``: as its
+    encoder-decoder branch does)."""
     ids = [list(tokenizer(p).input_ids) for p in prompts]
+    resolve = (lambda *a: candidate_ids_encdec(tokenizer, *a)) if encdec else (lambda *a: candidate_ids(tokenizer, variant, *a))
     if cand_strings is None:
-        cand = np.array([candidate_ids(tokenizer, variant)] * len(prompts), dtype=np.int32).reshape(-1, 2)
+        cand = np.array([resolve()] * len(prompts), dtype=np.int32).reshape(-1, 2)
     else:
         cache = {}
         cand = np.zeros((len(prompts), 2), np.int32)
         for i, (a, b) in enumerate(cand_strings):
             if (a, b) not in cache:
-                cache[(a, b)] = candidate_ids(tokenizer, variant, a, b)
+                cache[(a, b)] = resolve(a, b)
             cand[i] = cache[(a, b)]
     return ids, cand
 
@@ -294,7 +303,7 @@ def score_prompts(scorer: Scorer, tokenizer, prompts: Sequence[str], variant: st
     scores its shard of the prompts and all ranks receive all rows (BASELINE config 4: sharded by prompt)."""
     V = VARIANTS[variant]
     try:
-        ids, cand = tokenize_prompts(tokenizer, prompts, variant, cand_strings)
+        ids, cand = tokenize_prompts(tokenizer, prompts, variant, cand_strings, encdec=getattr(scorer, "is_encoder_decoder", False))
         if shard_group is not None:
             from .dist import score_ids_sharded
             rows, gens = score_ids_sharded(scorer, ids, cand, topk=V["topk"], max_lookahead=max_lookahead,

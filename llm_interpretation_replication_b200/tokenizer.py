@@ -29,13 +29,15 @@ class HashTokenizer:
     CHUNK = 4
 
     def __init__(self, vocab: int, eos_token_id: int = 11, bos_token_id: int | None = None,
-                 prepend_bos: bool = False, overrides: dict | None = None):
+                 prepend_bos: bool = False, overrides: dict | None = None, append_eos: bool = False,
+                 pad_token_id: int | None = None):
         assert vocab > 64 + 8
         self.vocab_size = vocab
         self.eos_token_id = eos_token_id
         self.eos_token = "<|endoftext|>"
-        self.pad_token_id = None
-        self.pad_token = None
+        self.pad_token_id = pad_token_id
+        self.pad_token = None if pad_token_id is None else "<pad>"
+        self.append_eos = append_eos     # emulates the T5 tokenizers, which close every encoded string with </s>
         self.bos_token_id = bos_token_id
         self.prepend_bos = prepend_bos   # emulates BOS-prepending tokenizers
         self.overrides = dict(overrides or {})   # whole-string -> single id (tests pin candidate ids)
@@ -54,6 +56,8 @@ class HashTokenizer:
         ids = self._ids(text)
         if add_special_tokens and self.prepend_bos and self.bos_token_id is not None:
             ids = [self.bos_token_id] + ids
+        if add_special_tokens and self.append_eos:
+            ids = ids + [self.eos_token_id]
         return ids
 
     def __call__(self, text, return_tensors=None, add_special_tokens: bool = True, padding=False):
@@ -67,7 +71,7 @@ class HashTokenizer:
         toks = []
         for t in ids:
             t = int(t)
-            if skip_special_tokens and t == self.eos_token_id:
+            if skip_special_tokens and (t == self.eos_token_id or (self.pad_token_id is not None and t == self.pad_token_id)):
                 continue
             toks.append(f"<{t}>")
         return "".join(toks)

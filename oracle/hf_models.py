@@ -191,3 +191,74 @@ def build_hf_model(shape: DecoderShape, W: Dict[str, torch.Tensor]):
     assert not still_meta, f"meta tensors left: {still_meta[:4]}"
     model.eval()
     return model
+
+
+# ---- encoder-decoder (T5 family) ------------------------------------------------------------------
+def t5_config(shape):
+    """HF T5Config equivalent to an ``EncDecShape`` (llm_interpretation_replication_b200.t5)."""
+    from transformers import T5Config
+    return T5Config(vocab_size=shape.vocab, d_model=shape.d_model, d_kv=shape.head_dim, d_ff=shape.d_ff,
+                    num_layers=shape.n_enc_layer, num_decoder_layers=shape.n_dec_layer, num_heads=shape.n_head,
+                    relative_attention_num_buckets=shape.rel_buckets, relative_attention_max_distance=shape.rel_max_distance,
+                    dropout_rate=0.0, layer_norm_epsilon=shape.norm_eps,
+                    feed_forward_proj="gated-gelu" if shape.gated else "relu", is_encoder_decoder=True, use_cache=True,
+                    pad_token_id=shape.pad_id, eos_token_id=shape.eos_id, decoder_start_token_id=shape.decoder_start_id,
+                    tie_word_embeddings=shape.tied_head)
+
+
+def t5_state_dict(shape, W: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """Flat T5 layout -> HF names (HF:models/t5/modeling_t5.py: separate q/k/v/o per attention, wi or wi_0/wi_1 + wo, the
+    relative bias on block 0 of each stack)."""
+    inner, ff = shape.inner, shape.d_ff
+    sd = {"shared.weight": W["wte"], "encoder.embed_tokens.weight": W["wte"], "decoder.embed_tokens.weight": W["wte"],
+          "encoder.final_layer_norm.weight": W["enc_lnf_g"], "decoder.final_layer_norm.weight": W["dec_lnf_g"],
+          "lm_head.weight": W["lm_head"],
+          "encoder.block.0.layer.0.SelfAttention.relative_attention_bias.weight": W["enc_rel_bias"],
+          "decoder.block.0.layer.0.SelfAttention.relative_attention_bias.weight": W["dec_rel_bias"]}
+
+    def ffn(h, p):
+        if shape.gated:
+            sd[h + "DenseReluDense.wi_0.weight"] = W[p + "w_up"][:ff]
+            sd[h + "DenseReluDense.wi_1.weight"] = W[p + "w_up"][ff:]
+        else:
+            sd[h + "DenseReluDense.wi.weight"] = W[p + "w_up"]
+        sd[h + "DenseReluDense.wo.weight"] = W[p + "w_down"]
+
+    for l in range(shape.n_enc_layer):
+        p, h = f"e{l}.", f"encoder.block.{l}.layer."
+        sd[h + "0.layer_norm.weight"] = W[p + "ln1_g"]
+        for i, n in enumerate("qkv"):
+            sd[h + f"0.SelfAttention.{n}.weight"] = W[p + "w_qkv"][i * inner:(i + 1) * inner]
+        sd[h + "0.SelfAttention.o.weight"] = W[p + "w_o"]
+        sd[h + "1.layer_norm.weight"] = W[p + "ln2_g"]
+        ffn(h + "1.", p)
+    for l in range(shape.n_dec_layer):
+        p, h = f"d{l}.", f"decoder.block.{l}.layer."
+        sd[h + "0.layer_norm.weight"] = W[p + "ln1_g"]
+        for i, n in enumerate("qkv"):
+            sd[h + f"0.SelfAttention.{n}.weight"] = W[p + "w_qkv"][i * inner:(i + 1) * inner]
+        sd[h + "0.SelfAttention.o.weight"] = W[p + "w_o"]
+        sd[h + "1.layer_norm.weight"] = W[p + "ln2_g"]
+        sd[h + "1.EncDecAttention.q.weight"] = W[p + "w_cq"]
+        sd[h + "1.EncDecAttention.k.weight"] = W[p + "w_ckv"][:inner]
+        sd[h + "1.EncDecAttention.v.weight"] = W[p + "w_ckv"][inner:]
+        sd[h + "1.EncDecAttention.o.weight"] = W[p + "w_co"]
+        sd[h + "2.layer_norm.weight"] = W[p + "ln3_g"]
+        ffn(h + "2.", p)
+    return sd
+
+
+def build_hf_t5(shape, W: Dict[str, torch.Tensor]):
+    """``T5ForConditionalGeneration`` (what ``AutoModelForSeq2SeqLM.from_pretrained`` returns for the reference's
+    encoder-decoder models, compare_instruct_models.py:470-476) holding ``W`` (fp32, CPU)."""
+    from transformers import T5ForConditionalGeneration
+    with torch.device("meta"):
+        model = T5ForConditionalGeneration(t5_config(shape))
+    sd = {k: v.to(torch.float32).contiguous() for k, v in t5_state_dict(shape, W).items()}
+    missing, unexpected = model.load_state_dict(sd, strict=False, assign=True)
+    assert not missing, f"missing keys {missing}"
+    assert not unexpected, f"unexpected keys {unexpected}"
+    still_meta = [n for n, p in list(model.named_parameters()) + list(model.named_buffers()) if p.is_meta]
+    assert not still_meta, f"meta tensors left: {still_meta[:4]}"
+    model.eval()
+    return model

@@ -27,13 +27,18 @@ def test_entry_point_1_run_and_resume(tmp_path):
 
 
 def test_entry_point_2_nan_rows_for_unsupported_models(tmp_path):
+    """Qwen-1 (custom modelling code) keeps the reference's NaN rows; the encoder-decoder models of the list (T0_3B,
+    tk-instruct: reference :178-226) and the decoder-only ones produce numbers."""
     from llm_interpretation_replication_b200.entrypoints import compare_instruct_models as E2
-    out = E2.run(['Is a "tent" a "dwelling"?', 'Is "water" a "food"?'],
-                 model_names=["bigscience/T0_3B", "tiiuae/falcon-7b-instruct"], n_layer=1)
-    df = E2.prepare_data_for_csv(out, ["bigscience/T0_3B", "tiiuae/falcon-7b-instruct"])
-    assert df[df.model == "bigscience/T0_3B"]["relative_prob"].isna().all()
-    ok = df[df.model == "tiiuae/falcon-7b-instruct"]
-    assert ok["relative_prob"].between(0, 1).all() and len(ok) == 2
+    names = ["Qwen/Qwen-7B-Chat", "bigscience/T0_3B", "tiiuae/falcon-7b-instruct"]
+    out = E2.run(['Is a "tent" a "dwelling"?', 'Is "water" a "food"?'], model_names=names, n_layer=1)
+    df = E2.prepare_data_for_csv(out, names)
+    assert df[df.model == "Qwen/Qwen-7B-Chat"]["relative_prob"].isna().all()
+    for name in names[1:]:
+        ok = df[df.model == name]
+        assert len(ok) == 2 and ok["yes_prob"].between(0, 1).all() and ok["no_prob"].between(0, 1).all(), name
+        assert (ok["model_output"] != "N/A").all()
+    assert df[df.model == "bigscience/T0_3B"]["model_family"].iloc[0] == "t0_3b"
 
 
 def test_entry_point_3_matches_reference_output(tmp_path):
@@ -72,20 +77,24 @@ def test_entry_point_5_matches_survey_appendix_d1(tmp_path):
 
 
 def test_entry_point_6_base_vs_instruct_odds_ratio_table(tmp_path):
-    """compare_base_vs_instruct.py: by-name prompt formats, "base_vs" scorer variant, NaN rows for the encoder-decoder pair."""
+    """compare_base_vs_instruct.py: by-name prompt formats, "base_vs" scorer variant, the T5 pair through the encoder-decoder
+    scorer (NaN rows for models that cannot be run: entry point 2's test)."""
     from llm_interpretation_replication_b200.entrypoints import compare_base_vs_instruct as E6
     qs = ['Is a "tent" a "building"?', 'Is "water" a "food"?', 'Is a "drone" an "aircraft"?']
-    pairs = [E6.model_pairs[0], E6.model_pairs[4]]            # T5 pair (not built: NaN rows), Falcon pair
+    pairs = [E6.model_pairs[0], E6.model_pairs[4]]            # T5 pair, Falcon pair
     out = E6.run(qs, pairs=pairs, n_layer=1)
     df = E6.prepare_data_for_csv(out, pairs)
     assert list(df.columns) == ["prompt", "model", "model_family", "base_or_instruct", "model_output", "yes_prob", "no_prob",
                                 "odds_ratio"]
     assert len(df) == 12
-    t5 = df[df.model_family == "t5"]
-    assert len(t5) == 3 and t5["odds_ratio"].isna().all() and (t5["model_output"] == "N/A").all()     # "flan" is its own family
-    ok = df[df.model_family == "falcon"]
-    assert len(ok) == 6 and np.isfinite(ok["yes_prob"]).all() and (ok["odds_ratio"] > 0).all()
-    assert np.allclose(ok["odds_ratio"], ok["yes_prob"] / ok["no_prob"], rtol=1e-6)
+    for fam, n in (("t5", 3), ("flan", 3), ("falcon", 6)):                       # "flan" is its own family under the reference's rule
+        ok = df[df.model_family == fam]
+        assert len(ok) == n and np.isfinite(ok["yes_prob"]).all() and (ok["odds_ratio"] > 0).all(), fam
+        assert np.allclose(ok["odds_ratio"], ok["yes_prob"] / ok["no_prob"], rtol=1e-6)
+        assert (ok["model_output"] != "N/A").all()
+    # the encoder-decoder branch generates max_length=50 = 49 new tokens (reference :199)
+    n_tok = df[df.model_family == "t5"]["model_output"].map(lambda c: c.count("<"))
+    assert n_tok.max() <= 49
     # entry point 3 consumes exactly this table
     from llm_interpretation_replication_b200.entrypoints import analyze_results_base_versus_instruct as E3
     d, pivot = E3.build_pivot(df)
