@@ -153,10 +153,13 @@ __device__ __forceinline__ void a2_store64(const float (&o0)[32], const float (&
 // One item for one thread (== tile row): wait for S, two passes over this row's S in tensor memory (max, then
 // exp / pack / store P over S), hand P to the issuer, wait for O, normalise and write HD outputs.
 // ALIBI: the score of key j is s_j * scale + slope * j (HF bloom build_alibi_tensor); `ab` = slope * log2(e).
-template <bool F16, int HD = 64, bool ALIBI = false>
+// TABLE: the score of key j is s_j * scale + tb[j] (HF t5 position_bias: `tb` points at this row's slice of the per-head bias
+// table laid out by key - query distance).
+template <bool F16, int HD = 64, bool ALIBI = false, bool TABLE = false>
 __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_live, int n_full, int n_p, int kvp, int limit, float sc,
                                         uint32_t bar_s, uint32_t bar_p, uint32_t bar_o, uint32_t bar_e, uint32_t ph, bool valid,
-                                        uint16_t* out_row, int lo_off = 0, float ab = 0.f) {
+                                        uint16_t* out_row, int lo_off = 0, float ab = 0.f, const float* tb = nullptr) {
+  constexpr float L2E = 1.4426950408889634f;
   const uint32_t t_o = t_lane + o_off;
   a2_wait(bar_s, ph);
   tcgen05_fence_after();
@@ -165,7 +168,11 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
   for (int c = 0; c < n_live; ++c) {
     float v[32];
     tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
-    if constexpr (ALIBI) {
+    if constexpr (TABLE) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c * 32 + j <= limit) m = fmaxf(m, fmaf(v[j], sc, __ldg(tb + c * 32 + j) * L2E));
+    } else if constexpr (ALIBI) {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
         if (c * 32 + j <= limit) m = fmaxf(m, fmaf(v[j], sc, ab * static_cast<float>(c * 32 + j)));
@@ -178,7 +185,7 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
         if (c * 32 + j <= limit) m = fmaxf(m, v[j]);
     }
   }
-  const float ms = ALIBI ? m : m * sc;
+  const float ms = (ALIBI || TABLE) ? m : m * sc;
   // pass 2: p = 2^(s*scale*log2e - max), rounded to 16 bits, two per column over the first half of S
   float lsum = 0.f;
   for (int c = 0; c < n_p; ++c) {
@@ -186,7 +193,16 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
     if (c < n_live) {
       float v[32];
       tmem_ld32(t_lane + static_cast<uint32_t>(c * 32), v);
-      if constexpr (ALIBI) {
+      if constexpr (TABLE) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const bool in0 = c * 32 + j <= limit, in1 = c * 32 + j + 1 <= limit;
+          const float p0 = in0 ? a2_ex2(fmaf(v[j], sc, fmaf(__ldg(tb + c * 32 + j), L2E, -ms))) : 0.f;
+          const float p1 = in1 ? a2_ex2(fmaf(v[j + 1], sc, fmaf(__ldg(tb + c * 32 + j + 1), L2E, -ms))) : 0.f;
+          lsum += p0 + p1;
+          pk[j >> 1] = pack16x2<F16>(p0, p1);
+        }
+      } else if constexpr (ALIBI) {
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
           const float b0 = ab * static_cast<float>(c * 32 + j) - ms, b1 = ab * static_cast<float>(c * 32 + j + 1) - ms;
@@ -391,6 +407,189 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(A2_TMEM_COLS) : "memory");
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Multi-head bidirectional attention with a relative-position bias table: the T5 encoder (HF t5:153-345; every head has
+// its own K and V, every query row sees every key, score = q.k + bias[head][key - query], no 1/sqrt(d)).  One CTA per
+// (prompt, 128-query tile) walks the heads; an item (= head) brings its own Q, K and V tiles, straight from the fused
+// q|k|v projection output (no cache copy), into a ring of NS stages; stage s and tensor-memory lane s belong together.
+// KVBOX 128: four 48 KB stages / four items in flight; KVBOX 256: two 80 KB stages / two items.  Per item the tensor core
+// does 128 x keys x 64 twice and the 128 softmax threads of the lane do two passes over their row: the kernel is bound by
+// the K/V bytes it streams (every q|k|v row is read once per query tile of its prompt).
+// ---------------------------------------------------------------------------------------------
+extern int g_opt_attn_ts;
+struct AttnEncParams {
+  BatchMeta meta;
+  uint16_t* out;          // [T, nh*64] 16-bit ([T, 2*nh*64] = hi | lo when split)
+  int split;
+  int nh, inner;          // inner = nh*64: K at column inner, V at column 2*inner of the projection output
+  float scale_log2e;
+  const float* table;     // [nh, 2*R + 1]
+  int R;
+};
+template <int KVBOX> constexpr int enc_stage_bytes() { return A2_Q_BYTES + 2 * KVBOX * A2_HD * 2; }
+template <int KVBOX> constexpr int enc_stages() { return KVBOX == 128 ? 4 : 2; }
+template <int KVBOX> constexpr int enc_smem() { return enc_stages<KVBOX>() * enc_stage_bytes<KVBOX>() + 1024 + 256; }
+
+template <bool F16, int KVBOX>
+__global__ void __launch_bounds__(A2_THREADS, 1)
+attn_enc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnEncParams p) {
+  constexpr int NS = enc_stages<KVBOX>();
+  constexpr uint32_t STAGE = enc_stage_bytes<KVBOX>(), KV_BYTES = KVBOX * A2_HD * 2;
+  const int seq = blockIdx.x, mt = blockIdx.y;
+  const int kl = p.meta.q_len[seq];
+  if (mt * A2_BM >= kl) return;
+  const int row0 = p.meta.q_start[seq];
+  const int q0 = row0 + mt * A2_BM;
+  const int rows_here = min(A2_BM, kl - mt * A2_BM);
+  const int kvp = (kl + 15) & ~15;
+  const int n_items = p.nh;
+  constexpr uint32_t lane_cols = 512u / NS;
+  constexpr uint32_t o_off = NS == 4 ? 64u : 128u;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  auto sQ = [&](int s) { return base + static_cast<uint32_t>(s) * STAGE; };
+  auto sK = [&](int s) { return sQ(s) + A2_Q_BYTES; };
+  auto sV = [&](int s) { return sK(s) + KV_BYTES; };
+  const uint32_t bars = base + NS * STAGE;
+  auto bar_f = [&](int l) { return bars + 8u * l; };            // Q, K, V of the stage landed      (TMA -> issuer)
+  auto bar_s = [&](int l) { return bars + 8u * (4 + l); };
+  auto bar_p = [&](int l) { return bars + 8u * (8 + l); };
+  auto bar_o = [&](int l) { return bars + 8u * (12 + l); };
+  auto bar_e = [&](int l) { return bars + 8u * (16 + l); };
+  const uint32_t tmem_slot = bars + 8u * 20;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == A2_LANES * 128) {
+    for (int l = 0; l < NS; ++l) {
+      mbar_init(bar_f(l), 1); mbar_init(bar_s(l), 1); mbar_init(bar_p(l), 128); mbar_init(bar_o(l), 1); mbar_init(bar_e(l), 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(A2_TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+  if (warp == A2_LANES * 4) {
+    if (lane == 0) {
+      const uint32_t idesc_s = a2_idesc(A2_BM, kvp, 0, F16);
+      const uint32_t idesc_o = a2_idesc(A2_BM, A2_HD, 1, F16);
+      int il = 0, is = 0, ipv = 0;
+      uint32_t idle = 0;
+      while (ipv < n_items) {
+        bool did = false;
+        if (il < n_items) {
+          // the stage is free once P.V of the item that used it last has completed (S before it, in issue order)
+          const int l = il % NS;
+          if (il < NS || a2_test(bar_o(l), static_cast<uint32_t>((il / NS) - 1) & 1u)) {
+            mbar_arrive_expect_tx(bar_f(l), STAGE);
+            tma_load_2d(sQ(l), &tmQ, bar_f(l), il * A2_HD, q0);
+            tma_load_2d(sK(l), &tmKV, bar_f(l), p.inner + il * A2_HD, row0);
+            tma_load_2d(sV(l), &tmKV, bar_f(l), 2 * p.inner + il * A2_HD, row0);
+            ++il; did = true;
+          }
+        }
+        if (is < il) {
+          const int l = is % NS;
+          const bool free_lane = is < NS || a2_test(bar_e(l), static_cast<uint32_t>((is / NS) - 1) & 1u);
+          if (free_lane && a2_test(bar_f(l), static_cast<uint32_t>(is / NS) & 1u)) {
+            tcgen05_fence_after();
+            const uint32_t t_s = tmem_base + static_cast<uint32_t>(l) * lane_cols;
+            const uint64_t qdesc = make_kmajor_sw128_desc(sQ(l));
+            const uint64_t kdesc = make_kmajor_sw128_desc(sK(l));
+#pragma unroll
+            for (int k = 0; k < A2_HD / 16; ++k) tcgen05_mma_bf16(t_s, qdesc + 2u * k, kdesc + 2u * k, idesc_s, k != 0 ? 1u : 0u);
+            tcgen05_commit(bar_s(l));
+            ++is; did = true;
+          }
+        }
+        if (ipv < is) {
+          const int l = ipv % NS;
+          if (a2_test(bar_p(l), static_cast<uint32_t>(ipv / NS) & 1u)) {
+            tcgen05_fence_after();
+            const uint32_t t_p = tmem_base + static_cast<uint32_t>(l) * lane_cols;
+            const uint64_t vdesc = a2_vdesc(sV(l));
+            for (int ks = 0; ks < kvp / 16; ++ks)
+              a2_mma_ts(t_p + o_off, t_p + 8u * ks, vdesc + static_cast<uint64_t>(ks) * (2048 >> 4), idesc_o, ks != 0 ? 1u : 0u);
+            tcgen05_commit(bar_o(l));
+            ++ipv; did = true;
+          }
+        }
+        if (did) idle = 0;
+        else if (++idle > (1u << 28)) {
+          printf("b2s attn_enc: issuer stalled (block %d,%d load %d S %d PV %d of %d)\n", blockIdx.x, blockIdx.y, il, is, ipv, n_items);
+          __trap();
+        }
+      }
+    }
+  } else if (warp < 4 * NS) {
+    const int l = warp >> 2, quad = warp & 3;
+    const int row = quad * 32 + lane;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(l) * lane_cols;
+    const bool valid = row < rows_here;
+    const int limit = kl - 1;                  // every query row sees every key
+    const int n_live = limit / 32 + 1;
+    const int n_p = (kvp + 31) / 32;
+    const size_t owidth = static_cast<size_t>(p.inner);
+    const size_t tw = 2 * static_cast<size_t>(p.R) + 1;
+    const int qpos = mt * A2_BM + row;         // (rows past the prompt's end compute on, unused: R >= 255 keeps them in the table)
+    for (int i = l; i < n_items; i += NS) {
+      const uint32_t ph = static_cast<uint32_t>(i / NS) & 1u;
+      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (owidth << p.split) + static_cast<size_t>(i) * A2_HD;
+      const float* tb = p.table + static_cast<size_t>(i) * tw + (p.R - qpos);
+      a2_item<F16, 64, false, true>(t_lane, o_off, n_live, 0, n_p, kvp, limit, p.scale_log2e, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph,
+                                    valid, dst, p.split ? static_cast<int>(owidth) : 0, 0.f, tb);
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(A2_TMEM_COLS) : "memory");
+  }
+}
+
+template <bool F16, int KVBOX>
+static int launch_enc_t(const AttnArgs& a, int n_seqs, int total_rows, int max_qlen, cudaStream_t st) {
+  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_enc_kernel<F16, KVBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, enc_smem<KVBOX>()));
+  CUtensorMap tq, tkv;      // the same buffer twice: 128-row boxes for Q, KVBOX-row boxes for K and V
+  B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
+                            static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, 64, a.f16));
+  B2S_TRY(make_tmap_bf16_2d(&tkv, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
+                            static_cast<uint64_t>(a.qkv_dim) * 2, KVBOX, 64, a.f16));
+  AttnEncParams p;
+  p.meta = a.meta;
+  p.out = reinterpret_cast<uint16_t*>(a.out);
+  p.split = a.split ? 1 : 0;
+  p.nh = a.nh; p.inner = a.nh * A2_HD;
+  p.scale_log2e = a.scale * 1.4426950408889634f;
+  p.table = a.relbias; p.R = a.rel_R;
+  dim3 grid(n_seqs, static_cast<unsigned>(ceil_div(max_qlen, A2_BM)));
+  attn_enc_kernel<F16, KVBOX><<<grid, A2_THREADS, enc_smem<KVBOX>(), st>>>(tq, tkv, p);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+// q|k|v of every head side by side in one [rows, 3*nh*64] 16-bit buffer (a.qkv; a.kcache / a.vcache are not used)
+bool attn_enc_supported(const AttnArgs& a) {
+  return g_opt_attn_ts != 0 && a.hd == A2_HD && a.nkv == a.nh && a.noncausal && a.relbias != nullptr && a.rel_R >= A2_MAXKV - 1 &&
+         a.max_kv <= A2_MAXKV && a.qkv_dim == 3 * a.nh * A2_HD && a.q_base == 0 && a.q_hstride == A2_HD && a.alibi == nullptr;
+}
+
+int launch_attn_enc(const AttnArgs& a, int n_seqs, int total_rows, int max_qlen, cudaStream_t st) {
+  B2S_REQUIRE(attn_enc_supported(a), "attn_enc: shape not supported (head_dim 64, <= 256 keys, fused q|k|v rows, bias table of >= 511 entries)");
+  if (a.max_kv <= 128) return a.f16 ? launch_enc_t<true, 128>(a, n_seqs, total_rows, max_qlen, st)
+                                    : launch_enc_t<false, 128>(a, n_seqs, total_rows, max_qlen, st);
+  return a.f16 ? launch_enc_t<true, 256>(a, n_seqs, total_rows, max_qlen, st) : launch_enc_t<false, 256>(a, n_seqs, total_rows, max_qlen, st);
 }
 
 // ---------------------------------------------------------------------------------------------

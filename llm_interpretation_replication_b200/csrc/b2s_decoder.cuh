@@ -96,6 +96,10 @@ int launch_act_split(const float* pre, void* act, int64_t rows, int ff, int kind
 bool attn_tc_supported(int hd, int max_kv);
 bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride);
 int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st);
+// tcgen05 multi-head bidirectional attention with a relative-bias table (T5 encoder; b2s_attn_tc2.cu): q|k|v read in place
+// from a.qkv = [rows, 3*nh*64], <= 256 keys per prompt
+bool attn_enc_supported(const AttnArgs& a);
+int launch_attn_enc(const AttnArgs& a, int n_seqs, int total_rows, int max_qlen, cudaStream_t st);
 int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const int32_t* cand, float* partials,
                                        float* cand_logits, cudaStream_t st);
 int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, int tiles_n, float* stats,

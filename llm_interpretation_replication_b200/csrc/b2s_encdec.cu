@@ -10,8 +10,10 @@
 // T5Attention (:153-345: no 1/sqrt(d) scaling, position_bias added to the scores, fp32 softmax), T5Block (:411-498),
 // T5Stack (:617-790) and T5ForConditionalGeneration.forward (:1040-1137).  Every linear layer is the tensor-core GEMM
 // of b2s_gemm_tc.cu (fp32 check mode: b2s_gemm_f32.cu) with the residual add, the ReLU or the gated tanh-GELU in its
-// epilogue; attention is the CUDA-core varlen kernel of b2s_decoder.cu with the bias-table, non-causal and
-// strided-K/V forms added for this family.
+// epilogue.  Attention: the encoder runs attn_enc_kernel (b2s_attn_tc2.cu: tcgen05, P in tensor memory, one item per head
+// with its own Q/K/V tiles); the decoder's self-attention over the few generated positions runs the CUDA-core varlen
+// kernel of b2s_decoder.cu (bias-table form), its cross-attention the streaming kernel below; the fp32 check mode and
+// prompts beyond 256 tokens run the CUDA-core kernel everywhere (non-causal, strided-K/V forms).
 #include "b2s_decoder.cuh"
 #include <type_traits>
 #include <vector>
@@ -114,6 +116,140 @@ __global__ void encdec_prep_kernel(const int32_t* __restrict__ cu, int n_rows, i
   ckv_start[r] = cu[i]; ckv_len[r] = cu[i + 1] - cu[i];
 }
 
+// -------------------------------------------------------------------------------------------------
+// Cross-attention of a one-token decoder step (HF t5:153-345 with key_value_states = encoder output: no mask, no position
+// bias, no scaling).  HBM-bound: every step re-reads the K and V rows of each prompt (2 * L * inner elements per row and
+// layer).  One warp per (decoder row, head); four heads of a row per CTA, so that a CTA reads 512 contiguous bytes of
+// every key row.
+//   pass 1  scores: 8 lanes share a key (16 bytes = 8 dims each, 3 shuffles to reduce), 4 keys per warp instruction,
+//           4 instructions in flight; scores parked in shared memory
+//   pass 2  softmax statistics over the parked scores (lanes split keys)
+//   pass 3  P.V: a lane owns two output dims, one coalesced 128-byte row of V per key, 8 keys in flight
+// The generic varlen kernel spent 470 us per layer and step here (one CTA per (row, head) staging K and V into shared
+// memory as fp32 and then using one of its eight warps): 0.45 TB/s.
+// -------------------------------------------------------------------------------------------------
+struct CrossArgs {
+  const void* q;          // [rows, inner] QT
+  const void* kv;         // [T, 2*inner] QT: K at column 0, V at column inner
+  void* out;              // [rows, inner] QT-sized 16-bit / fp32, or [rows, 2*inner] bf16 hi | lo (split)
+  const int32_t *kv_start, *kv_len;
+  int nh, inner, max_kv, split;
+};
+
+__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void load8(const __half* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+}
+__device__ __forceinline__ float2 load2(const float* p) { return *reinterpret_cast<const float2*>(p); }
+__device__ __forceinline__ float2 load2(const __half* p) { return __half22float2(*reinterpret_cast<const __half2*>(p)); }
+__device__ __forceinline__ float2 load2(const __nv_bfloat16* p) { return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p)); }
+
+template <typename QT>
+__global__ void __launch_bounds__(128)
+cross_attn_kernel(CrossArgs a) {
+  extern __shared__ float cs_scores[];                  // [4 warps][max_kv]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = blockIdx.x * 4 + warp, r = blockIdx.y;
+  if (h >= a.nh) return;                                // warp-uniform; no block-wide barrier below
+  float* sc = cs_scores + warp * a.max_kv;
+  const int L = a.kv_len[r];
+  const size_t pitch = 2 * static_cast<size_t>(a.inner);
+  const QT* kbase = reinterpret_cast<const QT*>(a.kv) + static_cast<size_t>(a.kv_start[r]) * pitch + h * 64;
+  const QT* vbase = kbase + a.inner;
+  const int sub = lane & 7, grp = lane >> 3;
+  float q[8];
+  load8(reinterpret_cast<const QT*>(a.q) + static_cast<size_t>(r) * a.inner + h * 64 + 8 * sub, q);
+  // pass 1
+  for (int j0 = 0; j0 < L; j0 += 16) {
+    float k[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + 4 * u + grp;
+      if (j < L) load8(kbase + static_cast<size_t>(j) * pitch + 8 * sub, k[u]);
+      else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) k[u][i] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float d = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d = fmaf(q[i], k[u][i], d);
+      d += __shfl_xor_sync(0xffffffffu, d, 1);
+      d += __shfl_xor_sync(0xffffffffu, d, 2);
+      d += __shfl_xor_sync(0xffffffffu, d, 4);
+      const int j = j0 + 4 * u + grp;
+      if (sub == 0 && j < L) sc[j] = d;
+    }
+  }
+  __syncwarp();
+  // pass 2
+  float m = -INFINITY;
+  for (int j = lane; j < L; j += 32) m = fmaxf(m, sc[j]);
+  m = warp_max(m);
+  float l = 0.f;
+  for (int j = lane; j < L; j += 32) {
+    const float p = __expf(sc[j] - m);
+    sc[j] = p;
+    l += p;
+  }
+  l = warp_sum(l);
+  __syncwarp();
+  // pass 3
+  float o0 = 0.f, o1 = 0.f;
+  const QT* vp = vbase + 2 * lane;
+  int j = 0;
+  for (; j + 8 <= L; j += 8) {
+    float2 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = load2(vp + static_cast<size_t>(j + u) * pitch);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const float p = sc[j + u]; o0 = fmaf(p, v[u].x, o0); o1 = fmaf(p, v[u].y, o1); }
+  }
+  for (; j < L; ++j) {
+    const float2 v = load2(vp + static_cast<size_t>(j) * pitch);
+    const float p = sc[j];
+    o0 = fmaf(p, v.x, o0); o1 = fmaf(p, v.y, o1);
+  }
+  const float inv = 1.f / l;
+  o0 *= inv; o1 *= inv;
+  const size_t col = static_cast<size_t>(h) * 64 + 2 * lane;
+  if (a.split) {
+    __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + static_cast<size_t>(r) * pitch + col;
+    const __nv_bfloat162 hi = __floats2bfloat162_rn(o0, o1);
+    *reinterpret_cast<__nv_bfloat162*>(ob) = hi;
+    *reinterpret_cast<__nv_bfloat162*>(ob + a.inner) = __floats2bfloat162_rn(o0 - __low2float(hi), o1 - __high2float(hi));
+  } else {
+    QT* op = reinterpret_cast<QT*>(a.out) + static_cast<size_t>(r) * a.inner + col;
+    if constexpr (std::is_same<QT, float>::value) *reinterpret_cast<float2*>(op) = make_float2(o0, o1);
+    else if constexpr (std::is_same<QT, __half>::value) *reinterpret_cast<__half2*>(op) = __floats2half2_rn(o0, o1);
+    else *reinterpret_cast<__nv_bfloat162*>(op) = __floats2bfloat162_rn(o0, o1);
+  }
+}
+
+template <typename QT>
+int launch_cross_attn(const CrossArgs& a, int rows, cudaStream_t st) {
+  const size_t smem = 4 * static_cast<size_t>(a.max_kv) * sizeof(float);
+  B2S_REQUIRE(smem <= 48 * 1024, "cross attention: %d keys exceed the score buffer", a.max_kv);
+  dim3 grid(static_cast<unsigned>(ceil_div(a.nh, 4)), static_cast<unsigned>(rows));
+  cross_attn_kernel<QT><<<grid, 128, smem, st>>>(a);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
 // AT: GEMM A operands (norm / activation outputs); WT: weight matrices; QT: q/k/v, the caches and the cross K/V
 // (QT == AT except in BF16_SPLIT, where attention works on fp16: see forward_t in b2s_model.cu).
 template <typename AT, typename WT, typename QT>
@@ -190,7 +326,11 @@ struct Run {
       a.kv_stride = 3 * inner;
       a.noncausal = 1;
       a.relbias = m->gwf(B2S_T5_ENC_BIAS);
-      B2S_TRY(launch_attn<QT>(a, n_seqs, st));
+      if (m->bf16 && attn_enc_supported(a)) {      // tensor-core kernel for <= 256-token prompts, CUDA-core kernel beyond
+        B2S_TRY(launch_attn_enc(a, n_seqs, T, max_len, st));
+      } else {
+        B2S_TRY(launch_attn<QT>(a, n_seqs, st));
+      }
       B2S_TRY(lin(w.attn, m->ew(l, B2S_T5E_W_O), w.resid, T, dm, inner, EPI_RESID_F32));
       B2S_TRY(norm(m->ew(l, B2S_T5E_LN2_G), w.ln, T));
       B2S_TRY(ffn(m->ew(l, B2S_T5E_W_UP), m->ew(l, B2S_T5E_W_DOWN), T));
@@ -227,11 +367,10 @@ struct Run {
       // cross-attention over the prompt's encoder output (no position bias: HF t5:310-317)
       B2S_TRY(norm(m->dw(l, B2S_T5D_LN2_G), w.ln, rows));
       B2S_TRY(lin(w.ln, m->dw(l, B2S_T5D_W_CQ), w.cq, rows, inner, dm, EPI_STORE_BF16, 0, q_f16));
-      AttnArgs c = attn_args(max_len);
-      c.qkv = w.cq; c.qkv_dim = inner; c.kcache = ckv; c.vcache = ckv + inner; c.kv_stride = 2 * inner;
-      c.meta.kv_start = w.ckv_start; c.meta.kv_len = w.ckv_len;
-      c.noncausal = 1;
-      B2S_TRY(launch_attn<QT>(c, rows, st));
+      CrossArgs c{};
+      c.q = w.cq; c.kv = ckv; c.out = w.attn; c.kv_start = w.ckv_start; c.kv_len = w.ckv_len;
+      c.nh = d.n_head; c.inner = inner; c.max_kv = max_len; c.split = m->split;
+      B2S_TRY(launch_cross_attn<QT>(c, rows, st));
       B2S_TRY(lin(w.attn, m->dw(l, B2S_T5D_W_CO), w.resid, rows, dm, inner, EPI_RESID_F32));
       B2S_TRY(norm(m->dw(l, B2S_T5D_LN3_G), w.ln, rows));
       B2S_TRY(ffn(m->dw(l, B2S_T5D_W_UP), m->dw(l, B2S_T5D_W_DOWN), rows));

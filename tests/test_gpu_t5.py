@@ -261,3 +261,37 @@ def test_t5_original_tied_scaled_head_vs_oracle():
         assert int(rows[i][6]) == o["pos_found"] == 0
         assert abs(float(rows[i][2]) - o["rel"]) <= TOL_FP32 and abs(float(rows[i][3]) - o["lse"]) < 1e-4
     sc.close()
+
+
+@pytest.mark.parametrize("mode_name", ["MODE_FP16", "MODE_BF16_SPLIT"])
+def test_t5_tensor_core_encoder_attention_vs_cuda_core(mode_name):
+    """attn_enc_kernel (tcgen05, one item per head, bias table) against the CUDA-core varlen kernel (`attn_ts` = 0) on the same
+    model: 1..3 query tiles per prompt (lengths to 256 = the kernel's limit), both K/V box sizes (batches of <= 128 and of
+    longer prompts), a length that is not a multiple of 16, and a 257-token prompt that must take the CUDA-core kernel."""
+    from dataclasses import replace
+    from llm_interpretation_replication_b200 import shapes, t5, _lib
+    mode = getattr(shapes, mode_name)
+    shp = replace(t5.tiny_t5(n_head=5, n_layer=2), max_pos=320)
+    W = t5.init_weights(shp, seed=55)
+    g = torch.Generator().manual_seed(6)
+    lib = _lib.load()
+    for lens in ([128, 127, 96, 17, 1, 64], [256, 129, 255, 200, 33, 128], [257, 40]):
+        ids = [torch.randint(2, shp.vocab, (L,), generator=g).tolist()[:-1] + [shp.eos_id] for L in lens]
+        cands = np.array([[5 + i, 50 + i] for i in range(len(ids))])
+        sc = _scorer(shp, W, mode, max_tokens=2048, max_seqs=16)
+        rows, gens = sc.score_ids(ids, cands, topk=5, eos_id=shp.eos_id)
+        try:
+            lib.b2s_set_option(b"attn_ts", 0)
+            rows0, gens0 = sc.score_ids(ids, cands, topk=5, eos_id=shp.eos_id)
+        finally:
+            lib.b2s_set_option(b"attn_ts", 1)
+        sc.close()
+        assert np.isfinite(rows[:, :6]).all()
+        # logits of the two candidates and the log-sum-exp at position 0 of the same prompts: the two attention kernels round
+        # P differently (16-bit P in tensor memory vs fp32 P), nothing else differs
+        same = rows[:, 6] == rows0[:, 6]
+        assert same.all()
+        assert np.abs(rows[:, 3:6] - rows0[:, 3:6]).max() < 2e-2, np.abs(rows[:, 3:6] - rows0[:, 3:6]).max()
+        assert np.abs(rows[:, 2] - rows0[:, 2]).max() < TOL_16
+        if max(lens) > 256:
+            assert np.array_equal(rows, rows0)      # both runs took the CUDA-core kernel
