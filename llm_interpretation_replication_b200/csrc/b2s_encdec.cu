@@ -117,23 +117,32 @@ __global__ void encdec_prep_kernel(const int32_t* __restrict__ cu, int n_rows, i
 }
 
 // -------------------------------------------------------------------------------------------------
-// Cross-attention of a one-token decoder step (HF t5:153-345 with key_value_states = encoder output: no mask, no position
-// bias, no scaling).  HBM-bound: every step re-reads the K and V rows of each prompt (2 * L * inner elements per row and
-// layer).  One warp per (decoder row, head); four heads of a row per CTA, so that a CTA reads 512 contiguous bytes of
-// every key row.
+// Attention of a one-token decoder step, both kinds (HF t5:153-345): one warp per (decoder row, head), four heads of a
+// row per CTA, so that a CTA reads 512 contiguous bytes of every key row.
+//   cross (SELF = false)  keys / values = the prompt's rows of this layer's projected encoder output; no mask, no bias, no
+//                         scaling.  HBM-bound: every step re-reads 2 * L * inner elements per row and layer.
+//   self  (SELF = true)   the warp first appends this position's k and v (read from the fused q|k|v row) to the cache,
+//                         then attends over the step + 1 cached positions with the decoder's relative bias
+//                         (bias[head][key - query], query = last position).
 //   pass 1  scores: 8 lanes share a key (16 bytes = 8 dims each, 3 shuffles to reduce), 4 keys per warp instruction,
 //           4 instructions in flight; scores parked in shared memory
 //   pass 2  softmax statistics over the parked scores (lanes split keys)
 //   pass 3  P.V: a lane owns two output dims, one coalesced 128-byte row of V per key, 8 keys in flight
-// The generic varlen kernel spent 470 us per layer and step here (one CTA per (row, head) staging K and V into shared
-// memory as fp32 and then using one of its eight warps): 0.45 TB/s.
+// The generic varlen kernel spent 470 us (cross) and 35 us (self, after a separate 12 us append kernel) per layer and step
+// here: one CTA per (row, head) staging K and V into shared memory as fp32 and then using one of its eight warps.
 // -------------------------------------------------------------------------------------------------
-struct CrossArgs {
-  const void* q;          // [rows, inner] QT
-  const void* kv;         // [T, 2*inner] QT: K at column 0, V at column inner
+struct StepAttnArgs {
+  const void* q;          // [rows, q_pitch] QT: query of head h at column h*64 (self: the fused q|k|v row)
+  const void *k, *v;      // key / value rows, kv_pitch elements apart; head h at column h*64
   void* out;              // [rows, inner] QT-sized 16-bit / fp32, or [rows, 2*inner] bf16 hi | lo (split)
   const int32_t *kv_start, *kv_len;
+  int q_pitch, kv_pitch;
   int nh, inner, max_kv, split;
+  // self-attention only
+  const int32_t* slot;    // cache slot this row's k / v go to
+  void *k_cache, *v_cache;   // == k, v (written)
+  const float* relbias;   // [nh, 2*R + 1]
+  int R;
 };
 
 __device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
@@ -156,21 +165,30 @@ __device__ __forceinline__ float2 load2(const float* p) { return *reinterpret_ca
 __device__ __forceinline__ float2 load2(const __half* p) { return __half22float2(*reinterpret_cast<const __half2*>(p)); }
 __device__ __forceinline__ float2 load2(const __nv_bfloat16* p) { return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p)); }
 
-template <typename QT>
+template <typename QT, bool SELF>
 __global__ void __launch_bounds__(128)
-cross_attn_kernel(CrossArgs a) {
+step_attn_kernel(StepAttnArgs a) {
   extern __shared__ float cs_scores[];                  // [4 warps][max_kv]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = blockIdx.x * 4 + warp, r = blockIdx.y;
   if (h >= a.nh) return;                                // warp-uniform; no block-wide barrier below
   float* sc = cs_scores + warp * a.max_kv;
   const int L = a.kv_len[r];
-  const size_t pitch = 2 * static_cast<size_t>(a.inner);
-  const QT* kbase = reinterpret_cast<const QT*>(a.kv) + static_cast<size_t>(a.kv_start[r]) * pitch + h * 64;
-  const QT* vbase = kbase + a.inner;
+  const size_t pitch = static_cast<size_t>(a.kv_pitch);
+  const QT* qrow = reinterpret_cast<const QT*>(a.q) + static_cast<size_t>(r) * a.q_pitch;
+  if constexpr (SELF) {     // append this position's k, v (columns inner + h*64 and 2*inner + h*64 of the fused row)
+    const size_t dst = static_cast<size_t>(a.slot[r]) * pitch + h * 64 + 2 * lane;
+    using V2 = typename std::conditional<std::is_same<QT, float>::value, float2, uint32_t>::type;
+    *reinterpret_cast<V2*>(reinterpret_cast<QT*>(a.k_cache) + dst) = *reinterpret_cast<const V2*>(qrow + a.inner + h * 64 + 2 * lane);
+    *reinterpret_cast<V2*>(reinterpret_cast<QT*>(a.v_cache) + dst) = *reinterpret_cast<const V2*>(qrow + 2 * a.inner + h * 64 + 2 * lane);
+    __syncwarp();           // the warp reads these rows back below
+  }
+  const QT* kbase = reinterpret_cast<const QT*>(a.k) + static_cast<size_t>(a.kv_start[r]) * pitch + h * 64;
+  const QT* vbase = reinterpret_cast<const QT*>(a.v) + static_cast<size_t>(a.kv_start[r]) * pitch + h * 64;
+  const float* tb = SELF ? a.relbias + static_cast<size_t>(h) * (2 * a.R + 1) + (a.R - (L - 1)) : nullptr;
   const int sub = lane & 7, grp = lane >> 3;
   float q[8];
-  load8(reinterpret_cast<const QT*>(a.q) + static_cast<size_t>(r) * a.inner + h * 64 + 8 * sub, q);
+  load8(qrow + h * 64 + 8 * sub, q);
   // pass 1
   for (int j0 = 0; j0 < L; j0 += 16) {
     float k[4][8];
@@ -192,7 +210,7 @@ cross_attn_kernel(CrossArgs a) {
       d += __shfl_xor_sync(0xffffffffu, d, 2);
       d += __shfl_xor_sync(0xffffffffu, d, 4);
       const int j = j0 + 4 * u + grp;
-      if (sub == 0 && j < L) sc[j] = d;
+      if (sub == 0 && j < L) sc[j] = SELF ? d + tb[j] : d;
     }
   }
   __syncwarp();
@@ -228,7 +246,7 @@ cross_attn_kernel(CrossArgs a) {
   o0 *= inv; o1 *= inv;
   const size_t col = static_cast<size_t>(h) * 64 + 2 * lane;
   if (a.split) {
-    __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + static_cast<size_t>(r) * pitch + col;
+    __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + static_cast<size_t>(r) * (2 * static_cast<size_t>(a.inner)) + col;
     const __nv_bfloat162 hi = __floats2bfloat162_rn(o0, o1);
     *reinterpret_cast<__nv_bfloat162*>(ob) = hi;
     *reinterpret_cast<__nv_bfloat162*>(ob + a.inner) = __floats2bfloat162_rn(o0 - __low2float(hi), o1 - __high2float(hi));
@@ -240,12 +258,12 @@ cross_attn_kernel(CrossArgs a) {
   }
 }
 
-template <typename QT>
-int launch_cross_attn(const CrossArgs& a, int rows, cudaStream_t st) {
+template <typename QT, bool SELF>
+int launch_step_attn(const StepAttnArgs& a, int rows, cudaStream_t st) {
   const size_t smem = 4 * static_cast<size_t>(a.max_kv) * sizeof(float);
-  B2S_REQUIRE(smem <= 48 * 1024, "cross attention: %d keys exceed the score buffer", a.max_kv);
+  B2S_REQUIRE(smem <= 48 * 1024, "step attention: %d keys exceed the score buffer", a.max_kv);
   dim3 grid(static_cast<unsigned>(ceil_div(a.nh, 4)), static_cast<unsigned>(rows));
-  cross_attn_kernel<QT><<<grid, 128, smem, st>>>(a);
+  step_attn_kernel<QT, SELF><<<grid, 128, smem, st>>>(a);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
@@ -354,23 +372,20 @@ struct Run {
       // self-attention over the generated prefix
       B2S_TRY(norm(m->dw(l, B2S_T5D_LN1_G), w.ln, rows, l == 0 ? tokens : nullptr));
       B2S_TRY(lin(w.ln, m->dw(l, B2S_T5D_W_QKV), w.qkv, rows, 3 * inner, dm, EPI_STORE_BF16, 0, q_f16));
-      RopeArgs ro{};                       // rotary_dim 0: plain append of this position's k / v to the cache
-      ro.qkv = w.qkv; ro.kcache = kc; ro.vcache = vc; ro.pos = w.meta.pos; ro.slot = w.meta.slot;
-      ro.qkv_dim = 3 * inner; ro.nh = d.n_head; ro.nkv = d.n_head; ro.hd = d.head_dim; ro.rd = 0;
-      ro.q_base = 0; ro.q_hstride = d.head_dim; ro.k_base = inner; ro.v_base = 2 * inner; ro.kv_hstride = d.head_dim;
-      B2S_TRY(launch_rope_cache<QT>(ro, rows, st));
-      AttnArgs a = attn_args(step + 1);
-      a.qkv = w.qkv; a.qkv_dim = 3 * inner; a.kcache = kc; a.vcache = vc;
-      a.relbias = m->gwf(B2S_T5_DEC_BIAS);
-      B2S_TRY(launch_attn<QT>(a, rows, st));
+      StepAttnArgs sa{};                   // appends this position's k / v to the cache, then attends over the prefix
+      sa.q = w.qkv; sa.q_pitch = 3 * inner; sa.k = kc; sa.v = vc; sa.kv_pitch = inner; sa.out = w.attn;
+      sa.kv_start = w.meta.kv_start; sa.kv_len = w.meta.kv_len; sa.nh = d.n_head; sa.inner = inner; sa.max_kv = step + 1;
+      sa.split = m->split; sa.slot = w.meta.slot; sa.k_cache = kc; sa.v_cache = vc;
+      sa.relbias = m->gwf(B2S_T5_DEC_BIAS); sa.R = d.max_pos - 1;
+      B2S_TRY((launch_step_attn<QT, true>(sa, rows, st)));
       B2S_TRY(lin(w.attn, m->dw(l, B2S_T5D_W_O), w.resid, rows, dm, inner, EPI_RESID_F32));
       // cross-attention over the prompt's encoder output (no position bias: HF t5:310-317)
       B2S_TRY(norm(m->dw(l, B2S_T5D_LN2_G), w.ln, rows));
       B2S_TRY(lin(w.ln, m->dw(l, B2S_T5D_W_CQ), w.cq, rows, inner, dm, EPI_STORE_BF16, 0, q_f16));
-      CrossArgs c{};
-      c.q = w.cq; c.kv = ckv; c.out = w.attn; c.kv_start = w.ckv_start; c.kv_len = w.ckv_len;
-      c.nh = d.n_head; c.inner = inner; c.max_kv = max_len; c.split = m->split;
-      B2S_TRY(launch_cross_attn<QT>(c, rows, st));
+      StepAttnArgs c{};
+      c.q = w.cq; c.q_pitch = inner; c.k = ckv; c.v = ckv + inner; c.kv_pitch = 2 * inner; c.out = w.attn;
+      c.kv_start = w.ckv_start; c.kv_len = w.ckv_len; c.nh = d.n_head; c.inner = inner; c.max_kv = max_len; c.split = m->split;
+      B2S_TRY((launch_step_attn<QT, false>(c, rows, st)));
       B2S_TRY(lin(w.attn, m->dw(l, B2S_T5D_W_CO), w.resid, rows, dm, inner, EPI_RESID_F32));
       B2S_TRY(norm(m->dw(l, B2S_T5D_LN3_G), w.ln, rows));
       B2S_TRY(ffn(m->dw(l, B2S_T5D_W_UP), m->dw(l, B2S_T5D_W_DOWN), rows));

@@ -108,8 +108,8 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
         W = weights.init_weights_device(shp, seed=model_seed(model_name), device=device, weight_dtype=dt)
         tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
     if getattr(shp, "is_encoder_decoder", False):
-        # the cross-attention K/V of every decoder layer stay resident per call: a smaller token budget than a decoder-only model
-        scorer = t5.EncDecScorer(shp, W, mode=mode, device=device, max_tokens=min(max_tokens, 32768), max_seqs=min(max_seqs, 512),
+        # the cross-attention K/V of every decoder layer stay resident per call: the token budget is capped (t5.EncDecScorer)
+        scorer = t5.EncDecScorer(shp, W, mode=mode, device=device, max_tokens=min(max_tokens, 131072), max_seqs=min(max_seqs, 2048),
                                  max_lookahead=max(MAX_LOOK_AHEAD, COMPLETION_TOKENS))
         return scorer, tok
     scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs,

@@ -207,12 +207,16 @@ class EncDecScorer(Scorer):
     Default mode: BF16_SPLIT.  The T5 v1.1 family is the textbook case of activations that leave fp16's range in the
     feed-forward layers (HF keeps ``wo`` in fp32 for that reason, HF t5:527 ``_keep_in_fp32_modules``), so the mode that
     keeps bf16's range and still holds the 2e-3 gate is the one to start from; MODE_FP16 runs at twice the rate and flags an
-    overflow as B2S_ERANGE."""
+    overflow as B2S_ERANGE.
+
+    Batch size: the one-token decoder steps are launch- and latency-bound below ~1000 rows, so the default batch is 131072
+    prompt tokens (about 1200 prompts; 37 GB of workspace at T0_3B size, dominated by the resident cross-attention K/V:
+    tools/t5_bench.py measured 1704 / 2284 / 2341 prompts/s at 32768 / 131072 / 262144 tokens)."""
 
     is_encoder_decoder = True
 
     def __init__(self, shape: EncDecShape, weights_dev: Dict[str, torch.Tensor], mode: int = MODE_BF16_SPLIT,
-                 device: Optional[torch.device] = None, max_tokens: int = 32768, max_seqs: int = 512,
+                 device: Optional[torch.device] = None, max_tokens: int = 131072, max_seqs: int = 2048,
                  max_lookahead: int = MAX_LOOK_AHEAD):
         if not torch.cuda.is_available():
             raise _lib.B2SError("no CUDA device: the B200 scorer has no CPU fallback")

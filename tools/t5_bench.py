@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--prompts", type=int, default=2000)
     ap.add_argument("--modes", nargs="*", default=["bf16_split", "fp16", "bf16"])
     ap.add_argument("--max-tokens", type=int, default=32768)
+    ap.add_argument("--max-seqs", type=int, default=1024)
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--steps", type=int, default=2)
     args = ap.parse_args()
@@ -40,7 +41,7 @@ def main():
         mode = modes[name]
         dt = torch.float16 if mode == shapes.MODE_FP16 else torch.bfloat16
         W = t5.init_weights(shp, seed=1, device="cuda:0", weight_dtype=dt)
-        sc = t5.EncDecScorer(shp, W, mode=mode, device="cuda:0", max_tokens=args.max_tokens, max_seqs=512)
+        sc = t5.EncDecScorer(shp, W, mode=mode, device="cuda:0", max_tokens=args.max_tokens, max_seqs=args.max_seqs)
         del W
         rows, gens = sc.score_ids(ids[:256], cand[:256], topk=2, eos_id=shp.eos_id, nonfinite="nan")     # warm-up
         torch.cuda.synchronize()
@@ -61,7 +62,7 @@ def main():
                           "gemm_ms_per_pass": ms.value / args.steps, "gemm_share": ms.value / args.steps / 1e3 / dt_s,
                           "gemm_tflops": fl.value / (ms.value / 1e3) / 1e12 if ms.value > 0 else None,
                           "launches_per_pass": int(launches), "mean_decoder_positions": float(steps_taken.mean()),
-                          "finite": bool(np.isfinite(rows[:, 2]).all()), "workspace_gb": sc.workspace_bytes / 2**30}), flush=True)
+                          "finite": bool(np.isfinite(rows[:, 2]).all()), "workspace_gb": sc.workspace_bytes / 2**30, "max_tokens": args.max_tokens}), flush=True)
         sc.close()
         del sc
         torch.cuda.empty_cache()
