@@ -74,7 +74,7 @@ typedef struct {
   float   norm_eps;
   int32_t parallel_residual;   /* HF gpt_neox use_parallel_residual / falcon parallel_attn */
   int32_t n_ln_per_layer;      /* 1 (falcon-7b) or 2 */
-  int32_t has_bias;
+  int32_t has_bias;            /* 0 none; 1 every linear layer (B_QKV, B_DENSE, B_UP, B_DOWN); 2 the q|k|v projection only (Qwen) */
   int32_t qkv_layout;          /* B2S_QKV_* */
   int32_t max_pos;             /* rows of the rope cos/sin tables */
   int32_t compute_mode;        /* B2S_MODE_*: BF16_FAST and BF16_SPLIT expect bf16 matrices, FP16 fp16, FP32_CHECK fp32 */

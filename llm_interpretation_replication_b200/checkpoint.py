@@ -5,7 +5,8 @@ Replaces ``AutoTokenizer.from_pretrained`` / ``AutoModelForCausalLM.from_pretrai
 already on disk (there is no hub access here): a directory with ``config.json`` plus ``*.safetensors`` (single file or
 sharded with ``model.safetensors.index.json``) or ``pytorch_model*.bin``.
 
-* ``shape_from_hf_config``  Falcon (``model_type`` "falcon" or the original "RefinedWebModel" key names; multi-query,
+* ``shape_from_hf_config``  (also the Llama family, OPT, BLOOM, Qwen2, and -- key names from their published custom code, which
+  this image cannot instantiate -- the first-generation Qwen and Baichuan2-7B)  Falcon (``model_type`` "falcon" or the original "RefinedWebModel" key names; multi-query,
   parallel attention, rotary: HF:models/falcon/configuration_falcon.py:53-76) and GPT-NeoX (StableLM-alpha, RedPajama,
   Pythia/Dolly, h2oGPT: HF:models/gpt_neox/configuration_gpt_neox.py) configs to a ``DecoderShape``; anything else
   raises ``KeyError``, which the entry points turn into the reference's NaN rows for a model that fails to load.
@@ -114,6 +115,49 @@ def shape_from_hf_config(cfg: dict, name: str = "checkpoint") -> DecoderShape:
                             parallel_residual=False, n_ln_per_layer=2, has_bias=False,
                             tied_head=bool(cfg.get("tie_word_embeddings", False)), qkv_layout=QKV_FALCON_MQA, eos_id=int(eos),
                             max_pos=min(max_pos, 32768), norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+    if mt == "qwen2":
+        # HF:models/qwen2/configuration_qwen2.py: the Llama block with q/k/v biases (the in-library successor of the reference's Qwen-1)
+        if cfg.get("hidden_act", "silu") != "silu":
+            raise KeyError(f"{name}: hidden_act {cfg.get('hidden_act')!r} is not supported (SiLU-gated MLP only)")
+        if cfg.get("use_sliding_window", False):
+            raise KeyError(f"{name}: Qwen2 with a sliding window is not supported")
+        d, n_head = int(cfg["hidden_size"]), int(cfg["num_attention_heads"])
+        theta, pct = _rope(cfg, ("rope_theta",), 1.0)
+        eos = cfg.get("eos_token_id", 151643)
+        eos = eos[0] if isinstance(eos, (list, tuple)) else eos
+        return DecoderShape(name, ARCH_LLAMA, int(cfg["num_hidden_layers"]), d, n_head, int(cfg.get("num_key_value_heads") or n_head),
+                            int(cfg.get("head_dim") or d // n_head), int(cfg["intermediate_size"]), int(cfg["vocab_size"]),
+                            int(cfg.get("head_dim") or d // n_head), rope_theta=theta, norm_eps=float(cfg.get("rms_norm_eps", 1e-6)),
+                            parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=bool(cfg.get("tie_word_embeddings", False)),
+                            qkv_layout=QKV_FALCON_MQA, eos_id=int(eos), max_pos=min(int(cfg.get("max_position_embeddings", 32768)), 32768),
+                            norm_type=NORM_RMS, mlp_type=MLP_SWIGLU, qkv_bias=True)
+    if mt == "qwen":
+        # Qwen/Qwen-7B(-Chat) (compare_instruct_models.py:159): custom code on the hub (QWenLMHeadModel), so the key names come from
+        # its published config.json / modeling_qwen.py, not from a class this image can instantiate -- parity of the MATH is
+        # pinned through Qwen2 (same block), the key mapping is unpinned.  intermediate_size counts w1 and w2 together.
+        if not cfg.get("no_bias", True):
+            raise KeyError(f"{name}: Qwen with biases beyond c_attn is not supported")
+        if float(cfg.get("rotary_pct", 1.0)) != 1.0:
+            raise KeyError(f"{name}: partial rotary in Qwen is not supported")
+        d, n_head = int(cfg["hidden_size"]), int(cfg["num_attention_heads"])
+        hd = int(cfg.get("kv_channels") or d // n_head)
+        return DecoderShape(name, ARCH_LLAMA, int(cfg["num_hidden_layers"]), d, n_head, n_head, hd, int(cfg["intermediate_size"]) // 2,
+                            int(cfg["vocab_size"]), hd, rope_theta=float(cfg.get("rotary_emb_base", 10000.0)),
+                            norm_eps=float(cfg.get("layer_norm_epsilon", 1e-6)), parallel_residual=False, n_ln_per_layer=2, has_bias=False,
+                            tied_head=bool(cfg.get("tie_word_embeddings", False)), qkv_layout=QKV_FALCON_MQA,
+                            eos_id=int(cfg.get("eos_token_id", 151643)), max_pos=min(int(cfg.get("seq_length", 8192)), 32768),
+                            norm_type=NORM_RMS, mlp_type=MLP_SWIGLU, qkv_bias=True)
+    if mt == "baichuan":
+        # baichuan-inc/Baichuan2-7B-Chat (compare_instruct_models.py:147): custom code on the hub (BaichuanForCausalLM); Llama block
+        # with q|k|v packed in W_pack.  The 13B models use ALiBi instead of rotary positions and are refused.
+        if int(cfg["num_hidden_layers"]) >= 40 or int(cfg["hidden_size"]) > 4096:
+            raise KeyError(f"{name}: Baichuan 13B (ALiBi) is not supported")
+        d, n_head = int(cfg["hidden_size"]), int(cfg["num_attention_heads"])
+        return DecoderShape(name, ARCH_LLAMA, int(cfg["num_hidden_layers"]), d, n_head, n_head, d // n_head, int(cfg["intermediate_size"]),
+                            int(cfg["vocab_size"]), d // n_head, rope_theta=10000.0, norm_eps=float(cfg.get("rms_norm_eps", 1e-6)),
+                            parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False, qkv_layout=QKV_FALCON_MQA,
+                            eos_id=int(cfg.get("eos_token_id", 2)), max_pos=int(cfg.get("model_max_length", cfg.get("max_position_embeddings", 4096))),
+                            norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
     if mt == "opt":
         # HF:models/opt/configuration_opt.py (facebook/opt-iml-1.3b of the instruct sweep, compare_instruct_models.py:151)
         d = int(cfg["hidden_size"])
@@ -154,12 +198,20 @@ _NEOX_LAYER = {"input_layernorm.weight": "ln1_g", "input_layernorm.bias": "ln1_b
                "attention.dense.weight": "w_dense", "attention.dense.bias": "b_dense",
                "mlp.dense_h_to_4h.weight": "w_up", "mlp.dense_h_to_4h.bias": "b_up",
                "mlp.dense_4h_to_h.weight": "w_down", "mlp.dense_4h_to_h.bias": "b_down"}
-_LLAMA_GLOBAL = {"model.embed_tokens.weight": "wte", "model.norm.weight": "lnf_g", "lm_head.weight": "lm_head"}
+_LLAMA_GLOBAL = {"model.embed_tokens.weight": "wte", "model.norm.weight": "lnf_g", "lm_head.weight": "lm_head",
+                 "transformer.wte.weight": "wte", "transformer.ln_f.weight": "lnf_g"}            # (Qwen-1 names)
 # q/k/v and gate/up arrive as separate tensors and are fused by rows (":0" = first block of the fused matrix, ...)
 _LLAMA_LAYER = {"input_layernorm.weight": "ln1_g", "post_attention_layernorm.weight": "ln2_g",
                 "self_attn.q_proj.weight": "w_qkv:0", "self_attn.k_proj.weight": "w_qkv:1", "self_attn.v_proj.weight": "w_qkv:2",
                 "self_attn.o_proj.weight": "w_dense", "mlp.gate_proj.weight": "w_up:0", "mlp.up_proj.weight": "w_up:1",
-                "mlp.down_proj.weight": "w_down"}
+                "mlp.down_proj.weight": "w_down",
+                # Qwen2: biases on q, k, v
+                "self_attn.q_proj.bias": "b_qkv:0", "self_attn.k_proj.bias": "b_qkv:1", "self_attn.v_proj.bias": "b_qkv:2",
+                # Baichuan2: q|k|v packed by rows (modeling_baichuan.py: W_pack(x).unflatten(-1, (3, hidden)))
+                "self_attn.W_pack.weight": "w_qkv",
+                # Qwen-1 (modeling_qwen.py): c_attn = q|k|v with bias; MLP = c_proj(w1(x) * silu(w2(x))): w2 is the gate
+                "ln_1.weight": "ln1_g", "ln_2.weight": "ln2_g", "attn.c_attn.weight": "w_qkv", "attn.c_attn.bias": "b_qkv",
+                "attn.c_proj.weight": "w_dense", "mlp.w2.weight": "w_up:0", "mlp.w1.weight": "w_up:1", "mlp.c_proj.weight": "w_down"}
 _OPT_GLOBAL = {"model.decoder.embed_tokens.weight": "wte", "model.decoder.embed_positions.weight": "wpe",
                "model.decoder.final_layer_norm.weight": "lnf_g", "model.decoder.final_layer_norm.bias": "lnf_b",
                "lm_head.weight": "lm_head"}
@@ -200,7 +252,7 @@ def expected_names(shape: DecoderShape):
         leaf = n.split(".")[-1]
         if leaf in ("ln2_g", "ln2_b") and shape.n_ln_per_layer != 2:
             continue
-        if leaf.startswith("b_") and not shape.has_bias:
+        if leaf.startswith("b_") and not shape.has_bias and not (leaf == "b_qkv" and shape.qkv_bias):
             continue
         if leaf in ("lnf_b", "ln1_b", "ln2_b") and shape.norm_type == NORM_RMS:
             continue
@@ -227,9 +279,10 @@ def _check_shape(shape: DecoderShape, name: str, t: torch.Tensor):
         raise ValueError(f"checkpoint tensor {name} has shape {tuple(t.shape)}, the config implies {want}")
 
 
-def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.float32) -> Dict[str, torch.Tensor]:
+def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.float32, norm_head: bool = False) -> Dict[str, torch.Tensor]:
     """``tensors``: a state dict or an iterator of (hf_name, tensor).  Matrices are converted to ``weight_dtype``,
-    vectors to fp32, each moved to ``device`` as it arrives."""
+    vectors to fp32, each moved to ``device`` as it arrives.  ``norm_head``: the rows of lm_head are L2-normalised once
+    (Baichuan2's NormHead does so on every inference call, modeling_baichuan.py NormHead.forward)."""
     items = tensors.items() if hasattr(tensors, "items") else tensors
     W: Dict[str, torch.Tensor] = {}
     for hf_name, t in items:
@@ -247,6 +300,8 @@ def flat_from_hf(shape: DecoderShape, tensors, device="cpu", weight_dtype=torch.
         if not shape.tied_head:
             raise ValueError("checkpoint has no output embedding and the config does not tie it to the input embedding")
         W["lm_head"] = W["wte"]
+    if norm_head:
+        W["lm_head"] = torch.nn.functional.normalize(W["lm_head"].float(), dim=-1).to(W["lm_head"].dtype).contiguous()
     if shape.pos_type == POS_ALIBI:                    # not stored in checkpoints: HF recomputes the slopes from n_head
         W["alibi_slopes"] = _weights.alibi_slopes(shape.n_head).to(device)
     missing = [n for n in expected_names(shape) if n not in W]
@@ -407,7 +462,8 @@ def load_checkpoint(path: str, device="cuda:0", weight_dtype=torch.float16, n_la
             if m and int(m.group(1)) >= shape.n_layer:
                 continue
             yield k, v
-    return shape, flat_from_hf(shape, wanted(), device=device, weight_dtype=weight_dtype)
+    norm_head = cfg.get("model_type") == "baichuan" and int(cfg.get("vocab_size", 0)) > 100000     # Baichuan2 (Baichuan-1: plain head)
+    return shape, flat_from_hf(shape, wanted(), device=device, weight_dtype=weight_dtype, norm_head=norm_head)
 
 
 def load_tokenizer(path: str):

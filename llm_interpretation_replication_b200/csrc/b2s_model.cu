@@ -312,7 +312,8 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   B2S_REQUIRE(d.norm_type == B2S_NORM_LAYERNORM || d.norm_type == B2S_NORM_RMS, "model_create: unknown norm_type %d", d.norm_type);
   B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || d.mlp_type == B2S_MLP_SWIGLU || d.mlp_type == B2S_MLP_SWIGLU_FUSED,
               "model_create: unknown mlp_type %d", d.mlp_type);
-  B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || !d.has_bias, "model_create: SwiGLU with biases is not supported");
+  B2S_REQUIRE(d.has_bias >= 0 && d.has_bias <= 2, "model_create: has_bias %d outside [0,2]", d.has_bias);
+  B2S_REQUIRE(d.mlp_type == B2S_MLP_GELU || d.has_bias != 1, "model_create: SwiGLU with MLP biases is not supported (q|k|v bias only: has_bias = 2)");
   B2S_REQUIRE(d.mlp_type != B2S_MLP_SWIGLU_FUSED || d.compute_mode != B2S_MODE_FP32_CHECK,
               "model_create: interleaved gate/up rows (B2S_MLP_SWIGLU_FUSED) are for the tensor-core modes");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");

@@ -127,7 +127,7 @@ class Scorer:
                            n_head=shape.n_head, n_kv_head=shape.n_kv_head, head_dim=shape.head_dim, d_ff=shape.d_ff,
                            vocab=shape.vocab, rotary_dim=shape.rotary_dim, norm_eps=shape.norm_eps,
                            parallel_residual=int(shape.parallel_residual), n_ln_per_layer=shape.n_ln_per_layer,
-                           has_bias=int(shape.has_bias), qkv_layout=shape.qkv_layout, max_pos=shape.max_pos,
+                           has_bias=(1 if shape.has_bias else 2 if shape.qkv_bias else 0), qkv_layout=shape.qkv_layout, max_pos=shape.max_pos,
                            compute_mode=mode, norm_type=shape.norm_type, mlp_type=mlp_type,
                            pos_type=shape.pos_type, pos_offset=shape.pos_offset, act_type=shape.act_type,
                            emb_norm=int(shape.emb_norm))

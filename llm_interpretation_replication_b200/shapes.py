@@ -72,6 +72,7 @@ class DecoderShape:
     pos_offset: int = 0          # rows of wpe skipped before position 0 (OPT: 2)
     act_type: int = ACT_GELU
     emb_norm: bool = False       # LayerNorm applied to the token embeddings (BLOOM word_embeddings_layernorm)
+    qkv_bias: bool = False       # a bias on the fused q|k|v projection only (Qwen: c_attn / q,k,v_proj biases; has_bias stays False)
 
     @property
     def up_dim(self) -> int:
@@ -163,6 +164,27 @@ def mistral_7b_v02() -> DecoderShape:
     return replace(mistral_7b(), name="mistral-7b-instruct-v0.2", vocab=32000)
 
 
+def qwen_7b() -> DecoderShape:
+    # Qwen/Qwen-7B and Qwen/Qwen-7B-Chat (compare_instruct_models.py:159, compare_base_vs_instruct.py:159): the first-generation
+    # Qwen, shipped as custom modelling code (QWenLMHeadModel, trust_remote_code).  Its published forward is the Llama block
+    # with a bias on the fused c_attn projection: RMSNorm 1e-6, rotate_half RoPE over the whole 128-wide head (base 10000; the
+    # dynamic-NTK and log-n scalings only act beyond seq_length, far above this path's prompts), c_proj(w1(x) * silu(w2(x)))
+    # with w1 / w2 of intermediate_size / 2 = 11008 rows, untied lm_head, vocab 151936.
+    return DecoderShape("qwen-7b", ARCH_LLAMA, 32, 4096, 32, 32, 128, 11008, 151936, 128, rope_theta=10000.0,
+                        norm_eps=1e-6, parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=151643, max_pos=8192, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU,
+                        qkv_bias=True)
+
+
+def baichuan2_7b() -> DecoderShape:
+    # baichuan-inc/Baichuan2-7B-Chat (compare_instruct_models.py:147): custom modelling code (BaichuanForCausalLM); the published
+    # forward is the Llama block with the q, k, v projections packed in W_pack and an lm_head whose rows are L2-normalised at
+    # inference (NormHead) -- done once at load time here.  vocab 125696, RMSNorm 1e-6.
+    return DecoderShape("baichuan2-7b", ARCH_LLAMA, 32, 4096, 32, 32, 128, 11008, 125696, 128, rope_theta=10000.0,
+                        norm_eps=1e-6, parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=2, max_pos=4096, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
+
+
 def llama2_7b() -> DecoderShape:
     # meta-llama/Llama-2-7b-chat-hf (commented out in the reference's list, compare_instruct_models.py:155)
     return DecoderShape("llama-2-7b", ARCH_LLAMA, 32, 4096, 32, 32, 128, 11008, 32000, 128, rope_theta=10000.0,
@@ -212,6 +234,15 @@ def tiny_llama(vocab=288, n_layer=2, n_head=4, n_kv_head=2) -> DecoderShape:
                         qkv_layout=QKV_FALCON_MQA, eos_id=2, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU)
 
 
+def tiny_qwen(vocab=304, n_layer=2, n_head=3) -> DecoderShape:
+    # Llama block with a q|k|v bias (Qwen): head_dim 64, multi-head
+    hd = 64
+    d = n_head * hd
+    return DecoderShape("tiny-qwen", ARCH_LLAMA, n_layer, d, n_head, n_head, hd, 2 * d + 64, vocab, hd, rope_theta=10000.0,
+                        norm_eps=1e-6, parallel_residual=False, n_ln_per_layer=2, has_bias=False, tied_head=False,
+                        qkv_layout=QKV_FALCON_MQA, eos_id=2, norm_type=NORM_RMS, mlp_type=MLP_SWIGLU, qkv_bias=True)
+
+
 def tiny_mistral(vocab=264, n_layer=2, n_head=4, n_kv_head=1) -> DecoderShape:
     # Mistral-like: head_dim 128 (CUDA-core attention, separate RoPE kernel), rope_theta 1e6
     hd = 128
@@ -259,6 +290,9 @@ REGISTRY = {
     "mistral-7b-v0.1": mistral_7b_v01,
     "mistral-7b-instruct-v0.2": mistral_7b_v02,
     "llama-2-7b": llama2_7b,
+    "qwen-7b": qwen_7b,
+    "baichuan2-7b": baichuan2_7b,
+    "tiny-qwen": tiny_qwen,
     "opt-iml-1.3b": opt_iml_1_3b,
     "bloomz-7b1": bloomz_7b1,
     "tiny-opt": tiny_opt,
@@ -286,4 +320,5 @@ HUB_TO_SHAPE = {
     "mistralai/Mistral-7B-Instruct-v0.3": mistral_7b, "mistralai/Mistral-7B-v0.3": mistral_7b,
     "mistralai/Mistral-7B-v0.1": mistral_7b_v01, "mistralai/Mistral-7B-Instruct-v0.2": mistral_7b_v02,
     "meta-llama/Llama-2-7b-chat-hf": llama2_7b, "meta-llama/Llama-2-7b-hf": llama2_7b,
+    "Qwen/Qwen-7B": qwen_7b, "Qwen/Qwen-7B-Chat": qwen_7b, "baichuan-inc/Baichuan2-7B-Chat": baichuan2_7b,
 }

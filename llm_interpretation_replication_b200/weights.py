@@ -114,6 +114,8 @@ def init_weights(shape: DecoderShape, seed: int = 0, device: str = "cpu",
         W[p + "w_dense"] = mat(d, shape.n_head * shape.head_dim)
         W[p + "w_up"] = mat(shape.up_dim, d)
         W[p + "w_down"] = mat(d, ff)
+        if shape.qkv_bias and not shape.has_bias:
+            W[p + "b_qkv"] = 0.0 + 0.2 * torch.empty(shape.qkv_dim, dtype=torch.float32, device=device).normal_(0.0, 1.0, generator=g)
         if shape.has_bias:
             W[p + "b_qkv"] = vec(shape.qkv_dim, 0.0, 0.02)
             W[p + "b_dense"] = vec(d, 0.0, 0.02)
@@ -167,6 +169,8 @@ def init_weights_device(shape: DecoderShape, seed: int, device, weight_dtype=tor
         W[p + "w_dense"] = mat(d, shape.n_head * shape.head_dim)
         W[p + "w_up"] = mat(shape.up_dim, d)
         W[p + "w_down"] = mat(d, ff)
+        if shape.qkv_bias and not shape.has_bias:
+            W[p + "b_qkv"] = 0.0 + 0.2 * torch.empty(shape.qkv_dim, dtype=torch.float32, device=device).normal_(0.0, 1.0, generator=g)
         if shape.has_bias:
             W[p + "b_qkv"] = vec(shape.qkv_dim, 0.0, 0.02)
             W[p + "b_dense"] = vec(d, 0.0, 0.02)

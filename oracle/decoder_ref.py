@@ -8,6 +8,8 @@ Follows, for the two families on the hot path:
   GPT-NeoX HF:models/gpt_neox/modeling_gpt_neox.py:38-49 (MLP), :126-159 (partial rotary),
            :203-244 (attention, per-head [q,k,v] interleave), :258-289 (layer, parallel/sequential),
            :331-381 (model), :463-464 (embed_out)
+  Qwen     the Llama block with a bias on q|k|v (HF:models/qwen2/modeling_qwen2.py Qwen2Attention q/k/v_proj bias=True; the
+           first-generation Qwen's c_attn bias)
   Llama    HF:models/llama/modeling_llama.py LlamaRMSNorm (x * rsqrt(mean(x^2) + eps) * w), LlamaMLP
            (down(silu(gate(x)) * up(x))), LlamaAttention (grouped-query heads, rotate_half RoPE on the whole head),
            LlamaDecoderLayer (sequential residual, two norms) -- also Mistral without a sliding window
@@ -101,7 +103,8 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
 
     for l in range(shape.n_layer):
         p = f"l{l}."
-        bias = (lambda n: W[p + n].to(dtype)) if shape.has_bias else (lambda n: None)
+        bias = (lambda n: W[p + n].to(dtype)) if shape.has_bias else \
+               (lambda n: W[p + n].to(dtype) if (n == "b_qkv" and shape.qkv_bias) else None)
         ln1 = norm(x, p + "ln1_g", p + "ln1_b")
         qkv = F.linear(r(ln1), W[p + "w_qkv"].to(dtype), bias("b_qkv"))
         q, k, v = _split_qkv(shape, qkv)

@@ -36,6 +36,15 @@ def hf_config(shape: DecoderShape):
                              bos_token_id=shape.eos_id, eos_token_id=shape.eos_id,
                              max_position_embeddings=shape.max_pos, tie_word_embeddings=False,
                              attention_bias=True, hidden_dropout=0.0, attention_dropout=0.0)
+    if shape.arch == ARCH_LLAMA and shape.qkv_bias:
+        # The Llama block with q/k/v biases is HF's Qwen2 (HF:models/qwen2/modeling_qwen2.py: q_proj/k_proj/v_proj bias=True,
+        # o_proj and the MLP without).  The first-generation Qwen of the reference's lists is custom code with the same math.
+        from transformers import Qwen2Config
+        return Qwen2Config(vocab_size=shape.vocab, hidden_size=shape.d_model, intermediate_size=shape.d_ff,
+                           num_hidden_layers=shape.n_layer, num_attention_heads=shape.n_head,
+                           num_key_value_heads=shape.n_kv_head, hidden_act="silu", max_position_embeddings=shape.max_pos,
+                           rms_norm_eps=shape.norm_eps, rope_theta=shape.rope_theta, use_sliding_window=False,
+                           tie_word_embeddings=shape.tied_head, bos_token_id=1, eos_token_id=shape.eos_id, attention_dropout=0.0)
     if shape.arch == ARCH_LLAMA:
         from transformers import LlamaConfig
         return LlamaConfig(vocab_size=shape.vocab, hidden_size=shape.d_model, intermediate_size=shape.d_ff,
@@ -89,6 +98,10 @@ def to_hf_state_dict(shape: DecoderShape, W: Dict[str, torch.Tensor]) -> Dict[st
             sd[h + "self_attn.q_proj.weight"] = W[p + "w_qkv"][:nq]
             sd[h + "self_attn.k_proj.weight"] = W[p + "w_qkv"][nq:nq + nk]
             sd[h + "self_attn.v_proj.weight"] = W[p + "w_qkv"][nq + nk:]
+            if shape.qkv_bias:
+                sd[h + "self_attn.q_proj.bias"] = W[p + "b_qkv"][:nq]
+                sd[h + "self_attn.k_proj.bias"] = W[p + "b_qkv"][nq:nq + nk]
+                sd[h + "self_attn.v_proj.bias"] = W[p + "b_qkv"][nq + nk:]
             sd[h + "self_attn.o_proj.weight"] = W[p + "w_dense"]
             sd[h + "mlp.gate_proj.weight"] = W[p + "w_up"][:ff]
             sd[h + "mlp.up_proj.weight"] = W[p + "w_up"][ff:]
@@ -166,10 +179,12 @@ def build_hf_model(shape: DecoderShape, W: Dict[str, torch.Tensor]):
     minutes-long HF random init for 7B shapes."""
     import torch.nn as nn
     from transformers import (BloomForCausalLM, FalconForCausalLM, GPTNeoXForCausalLM, LlamaForCausalLM,
-                              OPTForCausalLM)
+                              OPTForCausalLM, Qwen2ForCausalLM)
     cfg = hf_config(shape)
     cls = {ARCH_FALCON: FalconForCausalLM, ARCH_GPT_NEOX: GPTNeoXForCausalLM, ARCH_LLAMA: LlamaForCausalLM,
            ARCH_OPT: OPTForCausalLM, ARCH_BLOOM: BloomForCausalLM}[shape.arch]
+    if shape.arch == ARCH_LLAMA and shape.qkv_bias:
+        cls = Qwen2ForCausalLM
     with torch.device("meta"):
         model = cls(cfg)
     sd = {k: v.to(torch.float32).contiguous() for k, v in to_hf_state_dict(shape, W).items()}

@@ -295,3 +295,59 @@ def test_t5_tensor_core_encoder_attention_vs_cuda_core(mode_name):
         assert np.abs(rows[:, 2] - rows0[:, 2]).max() < TOL_16
         if max(lens) > 256:
             assert np.array_equal(rows, rows0)      # both runs took the CUDA-core kernel
+
+
+@pytest.mark.parametrize("shape_name,n_prompts", [("t5-v1_1-base", 6), ("t5-xl-lm-adapt", 4)])
+def test_t5_full_depth_vs_oracle(shape_name, n_prompts):
+    """The reference's encoder-decoder models at their real size: google/t5-v1_1-base = flan-t5-base (12 + 12 layers,
+    compare_base_vs_instruct.py:137-138) and t5-xl-lm-adapt = T0_3B = tk-instruct-3b-def (24 + 24 layers, d_model 2048,
+    compare_instruct_models.py:147,150), random-init bf16-representable weights, perturbation-length prompts, top-2 /
+    10-position look-ahead, against the fp32 oracle on the host cores.  Gates: <= 1e-5 in the fp32 check mode, <= 2e-3 in FP16
+    and BF16_SPLIT, identical look-ahead position (a 16-bit disagreement is counted: at most one prompt)."""
+    import gc
+    from llm_interpretation_replication_b200 import shapes, t5
+    from oracle import t5_ref
+    shp = t5.REGISTRY[shape_name]()
+    Wd = t5.init_weights(shp, seed=91, device=DEV, weight_dtype=torch.bfloat16)
+    torch.set_num_threads(os.cpu_count() or 1)
+    Wc = {k: v.detach().to("cpu", torch.float32) for k, v in Wd.items()}
+    rs = np.random.RandomState(17)
+    lens = [int(x) for x in rs.randint(66, 191, size=n_prompts)]
+    lens[0] = 190
+    ids = [rs.randint(32, shp.vocab - 32, size=L - 1).tolist() + [shp.eos_id] for L in lens]
+    cands, want = [], []
+    for x in ids:
+        rows, gen = t5_ref.greedy_scores(shp, Wc, x, 10, shp.eos_id)
+        top = torch.topk(rows[0], 3).indices.tolist()
+        c = [top[0], top[2]] if len(cands) % 2 == 0 else [gen[min(3, len(gen) - 1)], top[1]]   # hits at position 0 and later
+        if c[0] == c[1]:
+            c[1] = top[2]
+        cands.append(c)
+        pa, pb, pos, found = t5_ref.scan_positions(rows, c[0], c[1], 2)
+        want.append(dict(rel=pa / (pa + pb), pos=pos, found=found, gen=gen))
+    cands = np.array(cands)
+    stats = {}
+    for label, mode, tol in (("fp32_check", shapes.MODE_FP32_CHECK, TOL_FP32), ("fp16", shapes.MODE_FP16, TOL_16),
+                             ("bf16_split", shapes.MODE_BF16_SPLIT, TOL_16)):
+        Wm = Wd if mode != shapes.MODE_FP32_CHECK else {k: (v.float() if t5.is_matrix(k) else v) for k, v in Wd.items()}
+        sc = t5.EncDecScorer(shp, Wm, mode=mode, device=DEV, max_tokens=2048, max_seqs=16)
+        rows, gens = sc.score_ids(ids, cands, topk=2, eos_id=shp.eos_id)
+        sc.close()
+        del sc, Wm
+        gc.collect(); torch.cuda.empty_cache()
+        worst, flips = 0.0, 0
+        for i, w in enumerate(want):
+            if int(rows[i][6]) != w["pos"]:
+                flips += 1
+                continue
+            worst = max(worst, abs(float(rows[i][2]) - w["rel"]))
+            if mode == shapes.MODE_FP32_CHECK:
+                got = [int(t) for t in gens[i] if t >= 0]
+                assert got == w["gen"][:len(got)] and bool(rows[i][7]) == w["found"]
+        stats[label] = dict(worst=worst, flips=flips)
+        if os.path.isdir("gpurun_out"):
+            with open("gpurun_out/t5_golden_parity.jsonl", "a") as f:
+                f.write(json.dumps({"case": f"{shape_name} full depth ({shp.n_enc_layer}+{shp.n_dec_layer} layers), {n_prompts} prompts",
+                                    "mode": int(mode), "worst_abs_delta_rel_prob_vs_fp32_oracle": worst, "position_mismatches": flips}) + "\n")
+        assert flips <= (0 if mode == shapes.MODE_FP32_CHECK else 1), (label, flips)
+        assert worst <= tol, (label, worst)
