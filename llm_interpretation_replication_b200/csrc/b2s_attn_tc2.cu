@@ -25,7 +25,6 @@ static constexpr int A2_KV_BYTES = A2_MAXKV * A2_HD * 2;     // 32 KB per K or V
 static constexpr int A2_Q_BYTES = A2_BM * A2_HD * 2;         // 16 KB per Q tile
 static constexpr int A2_NQ = 6;                              // Q ring depth
 static constexpr int A2_LANES = 4;
-static constexpr int A2_SMEM = 2 * A2_KV_BYTES + A2_NQ * A2_Q_BYTES + 1024 + 256;
 // head_dim 128 (StableLM-alpha, RedPajama-7B, Mistral, BLOOM ...): K, V and Q are staged as two 64-column sub-tiles each (a
 // 128B-swizzled K-major tile is 64 elements wide), S accumulates over both, O = P.V is two N = 64 products side by side.
 // K + V take 128 KB, so the Q ring is 3 deep; an item needs 256 tensor-memory columns (P over S[0,128), O in [128,256)):

@@ -25,7 +25,6 @@ static constexpr int BM = 128, BN = 256, BK = 64, UMMA_K = 16;
 static constexpr unsigned long long HINT_EVICT_FIRST = 0x12F0000000000000ull, HINT_EVICT_LAST = 0x14F0000000000000ull,
                                     HINT_EVICT_NORMAL = 0x1000000000000000ull;
 static constexpr int STAGES = 4;
-static constexpr int GROUP_M = 16;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
 static constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KB
 static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;

@@ -11,8 +11,8 @@ NaN rows for a model that cannot be run or a prompt that fails (:472-492); ``pre
 columns prompt, model, model_family, base_or_instruct, model_output, yes_prob, no_prob, odds_ratio and
 ``model_family = name.split('/')[1].split('-')[0].lower()``.  The per-prompt loop (:456-480) is one batched call into
 libb200score per model.  The T5 pair runs through ``t5.EncDecScorer`` (the script's encoder-decoder branch :192-237: bare-word
-candidate ids, ``max_length=50`` = 49 generated tokens); architectures that need custom modelling code (Qwen-1) produce the
-reference's NaN rows.  The reference's cache purge (:62-88) is deliberately not reproduced.
+candidate ids, ``max_length=50`` = 49 generated tokens), the Qwen pair through the Llama path with a q|k|v bias; a model
+outside the supported families produces the reference's NaN rows.  The reference's cache purge (:62-88) is deliberately not reproduced.
 
     python -m llm_interpretation_replication_b200.entrypoints.compare_base_vs_instruct [--out DIR] [--layers N] [--questions K]
 """

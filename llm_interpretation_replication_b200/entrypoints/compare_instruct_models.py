@@ -5,10 +5,12 @@ the reference except for the prompt list and the CSV name).
 Keeps the model list (:145-166), the bare / Baichuan prompt formats (:488-492), the k=2 scorer variant with
 candidate ids resolved WITH special tokens (:229-233), the NaN rows for models that cannot be run (:502-522), and
 `prepare_data_for_csv` (:103-121) with columns prompt, model, model_family, model_output, yes_prob, no_prob,
-relative_prob.  Eight of the ten models run: the Falcon, GPT-NeoX, Mistral, OPT and BLOOM families through the decoder-only
+relative_prob.  All ten models run: the Falcon, GPT-NeoX, Mistral, OPT and BLOOM families through the decoder-only
 scorer, the encoder-decoder models (tk-instruct, T0: the T5 branch at :178-226) through ``t5.EncDecScorer`` with the bare-word
-candidate ids of that branch (:197-198); the two that need custom modelling code (Baichuan2, Qwen-1) get the reference's
-NaN rows ("next" row N4).  The reference's cache purge (:81-101) is deliberately not reproduced.
+candidate ids of that branch (:197-198), and the two whose hub repositories ship custom modelling code (Baichuan2-7B: Llama block
+with packed W_pack and a row-normalised head; Qwen-7B: Llama block with a q|k|v bias) through the Llama path -- their math is
+pinned against HF's Qwen2 / Llama classes, their checkpoint key maps follow the published code and are not pinnable offline
+(``checkpoint.py``).  A model outside these families gets the reference's NaN rows.  The reference's cache purge (:81-101) is deliberately not reproduced.
 
     python -m llm_interpretation_replication_b200.entrypoints.compare_instruct_models [--survey 1|2] [--out DIR]
 """

@@ -83,6 +83,8 @@ SPECS = [
     # OPT (opt-iml-1.3b) and BLOOM (bloomz-7b1) of the same sweep (:148,151): `make_golden.py --append 5`
     ("tiny-opt", shapes.tiny_opt(), 106),
     ("tiny-bloom", shapes.tiny_bloom(), 107),
+    # the Llama block with a q|k|v bias (Qwen of the sweep, :159; HF class Qwen2ForCausalLM): `make_golden.py --append 7`
+    ("tiny-qwen", shapes.tiny_qwen(), 108),
 ]
 
 

@@ -17,7 +17,7 @@ def _save_hf(shape, W, path, safe=True):
 
 
 @pytest.mark.parametrize("maker", ["tiny_falcon", "tiny_neox_parallel", "tiny_neox_sequential", "tiny_llama", "tiny_mistral",
-                                   "tiny_opt", "tiny_bloom"])
+                                   "tiny_opt", "tiny_bloom", "tiny_qwen"])
 @pytest.mark.parametrize("safe", [True, False], ids=["safetensors", "bin"])
 def test_checkpoint_round_trip(tmp_path, maker, safe):
     """A checkpoint written by transformers itself comes back as the same shape and bit-identical tensors."""
@@ -27,7 +27,7 @@ def test_checkpoint_round_trip(tmp_path, maker, safe):
     shp2, W2 = checkpoint.load_checkpoint(str(tmp_path), device="cpu", weight_dtype=torch.float32)
     for f in ("arch", "n_layer", "d_model", "n_head", "n_kv_head", "head_dim", "d_ff", "vocab", "rotary_dim", "rope_theta",
               "norm_eps", "parallel_residual", "n_ln_per_layer", "has_bias", "tied_head", "qkv_layout", "eos_id", "max_pos",
-              "norm_type", "mlp_type", "pos_type", "pos_offset", "act_type", "emb_norm"):
+              "norm_type", "mlp_type", "pos_type", "pos_offset", "act_type", "emb_norm", "qkv_bias"):
         assert getattr(shp2, f) == getattr(shp, f), f
     names = checkpoint.expected_names(shp)
     assert set(names) <= set(W2)
@@ -137,3 +137,63 @@ def test_resolve_local(tmp_path, monkeypatch):
     assert checkpoint.resolve_local("tiiuae/falcon-7b") == str(d)
     assert checkpoint.resolve_local(str(d)) == str(d)
     assert checkpoint.resolve_local("tiiuae/falcon-40b") is None
+
+
+
+def test_qwen1_and_baichuan2_key_maps(tmp_path):
+    """Qwen-7B (QWenLMHeadModel) and Baichuan2-7B (BaichuanForCausalLM) ship as custom code this image cannot instantiate, so
+    only the MAPPING is tested here: a state dict laid out under their published key names and config keys loads into the same
+    flat weights as the Llama / Qwen2 layout of the same tensors (whose math is pinned against HF), with Qwen's w2 as the gate,
+    Baichuan's packed W_pack, and Baichuan2's lm_head rows L2-normalised once at load."""
+    import json
+    from safetensors.torch import save_file
+    # Qwen-1
+    shp = shapes.tiny_qwen()
+    W = weights.init_weights(shp, seed=21)
+    ff = shp.d_ff
+    sd = {"transformer.wte.weight": W["wte"], "transformer.ln_f.weight": W["lnf_g"], "lm_head.weight": W["lm_head"]}
+    for l in range(shp.n_layer):
+        p, h = f"l{l}.", f"transformer.h.{l}."
+        sd[h + "ln_1.weight"] = W[p + "ln1_g"]; sd[h + "ln_2.weight"] = W[p + "ln2_g"]
+        sd[h + "attn.c_attn.weight"] = W[p + "w_qkv"]; sd[h + "attn.c_attn.bias"] = W[p + "b_qkv"]
+        sd[h + "attn.c_proj.weight"] = W[p + "w_dense"]
+        sd[h + "mlp.w2.weight"] = W[p + "w_up"][:ff]          # gate: c_proj(w1(x) * silu(w2(x)))
+        sd[h + "mlp.w1.weight"] = W[p + "w_up"][ff:]
+        sd[h + "mlp.c_proj.weight"] = W[p + "w_down"]
+    d = tmp_path / "qwen"
+    d.mkdir()
+    save_file({k: v.contiguous().clone() for k, v in sd.items()}, str(d / "model.safetensors"))
+    json.dump(dict(model_type="qwen", architectures=["QWenLMHeadModel"], hidden_size=shp.d_model, num_hidden_layers=shp.n_layer,
+                   num_attention_heads=shp.n_head, kv_channels=shp.head_dim, intermediate_size=2 * ff, vocab_size=shp.vocab,
+                   layer_norm_epsilon=1e-6, rotary_emb_base=10000, rotary_pct=1.0, seq_length=2048, no_bias=True,
+                   use_dynamic_ntk=True, use_logn_attn=True, tie_word_embeddings=False, eos_token_id=2), open(d / "config.json", "w"))
+    shp2, W2 = checkpoint.load_checkpoint(str(d), device="cpu", weight_dtype=torch.float32)
+    assert (shp2.d_ff, shp2.qkv_bias, shp2.norm_type, shp2.mlp_type, shp2.n_kv_head, shp2.head_dim) == (ff, True, shp.norm_type, shp.mlp_type, shp.n_head, 64)
+    assert set(W2) == set(W) and all(torch.equal(W[k], W2[k]) for k in W)
+    # Baichuan2
+    shp = shapes.tiny_llama(n_kv_head=4)
+    W = weights.init_weights(shp, seed=22)
+    ff, V = shp.d_ff, 100352
+    big = torch.randn(V, shp.d_model, generator=torch.Generator().manual_seed(1)) * 3.0
+    sd = {"model.embed_tokens.weight": big, "model.norm.weight": W["lnf_g"], "lm_head.weight": big * 0.5 + 0.1}
+    for l in range(shp.n_layer):
+        p, h = f"l{l}.", f"model.layers.{l}."
+        sd[h + "input_layernorm.weight"] = W[p + "ln1_g"]; sd[h + "post_attention_layernorm.weight"] = W[p + "ln2_g"]
+        sd[h + "self_attn.W_pack.weight"] = W[p + "w_qkv"]; sd[h + "self_attn.o_proj.weight"] = W[p + "w_dense"]
+        sd[h + "mlp.gate_proj.weight"] = W[p + "w_up"][:ff]; sd[h + "mlp.up_proj.weight"] = W[p + "w_up"][ff:]
+        sd[h + "mlp.down_proj.weight"] = W[p + "w_down"]
+    d = tmp_path / "baichuan"
+    d.mkdir()
+    save_file({k: v.contiguous().clone() for k, v in sd.items()}, str(d / "model.safetensors"))
+    json.dump(dict(model_type="baichuan", architectures=["BaichuanForCausalLM"], hidden_size=shp.d_model, intermediate_size=ff,
+                   num_attention_heads=shp.n_head, num_hidden_layers=shp.n_layer, rms_norm_eps=1e-6, vocab_size=V,
+                   model_max_length=4096, tie_word_embeddings=False, bos_token_id=1, eos_token_id=2, pad_token_id=0),
+              open(d / "config.json", "w"))
+    shp2, W2 = checkpoint.load_checkpoint(str(d), device="cpu", weight_dtype=torch.float32)
+    assert shp2.vocab == V and not shp2.qkv_bias and shp2.n_kv_head == shp.n_head and shp2.max_pos == 4096
+    assert torch.equal(W2["l1.w_qkv"], W["l1.w_qkv"]) and torch.equal(W2["l0.w_up"], W["l0.w_up"])
+    assert torch.allclose(W2["lm_head"].norm(dim=-1), torch.ones(V), atol=1e-5)                     # NormHead
+    assert torch.allclose(W2["lm_head"], torch.nn.functional.normalize(sd["lm_head.weight"], dim=-1))
+    with pytest.raises(KeyError):
+        checkpoint.shape_from_hf_config(dict(model_type="baichuan", hidden_size=5120, num_hidden_layers=40, num_attention_heads=40,
+                                             intermediate_size=13696, vocab_size=125696), "13b")

@@ -27,13 +27,15 @@ def test_entry_point_1_run_and_resume(tmp_path):
 
 
 def test_entry_point_2_nan_rows_for_unsupported_models(tmp_path):
-    """Qwen-1 (custom modelling code) keeps the reference's NaN rows; the encoder-decoder models of the list (T0_3B,
-    tk-instruct: reference :178-226) and the decoder-only ones produce numbers."""
+    """A model outside the supported families keeps the reference's NaN rows (:502-522); the encoder-decoder models of the list
+    (T0_3B, tk-instruct: reference :178-226), the Qwen-1 / Baichuan2 stand-ins (Llama block, q|k|v bias / packed W_pack; the
+    Baichuan prompt format :491-492) and the other decoder-only families produce numbers."""
     from llm_interpretation_replication_b200.entrypoints import compare_instruct_models as E2
-    names = ["Qwen/Qwen-7B-Chat", "bigscience/T0_3B", "tiiuae/falcon-7b-instruct"]
+    names = ["Salesforce/xgen-7b-8k-inst", "bigscience/T0_3B", "Qwen/Qwen-7B-Chat", "baichuan-inc/Baichuan2-7B-Chat", "tiiuae/falcon-7b-instruct"]
+    assert set(names[1:]) <= set(E2.models)
     out = E2.run(['Is a "tent" a "dwelling"?', 'Is "water" a "food"?'], model_names=names, n_layer=1)
     df = E2.prepare_data_for_csv(out, names)
-    assert df[df.model == "Qwen/Qwen-7B-Chat"]["relative_prob"].isna().all()
+    assert df[df.model == names[0]]["relative_prob"].isna().all()
     for name in names[1:]:
         ok = df[df.model == name]
         assert len(ok) == 2 and ok["yes_prob"].between(0, 1).all() and ok["no_prob"].between(0, 1).all(), name

@@ -88,14 +88,14 @@ def _run_case(case, mode, tol):
     return worst
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_scorer_fp32_check_vs_reference_golden(case_idx):
     import gpu_util as U
     from llm_interpretation_replication_b200 import shapes
     _run_case(U.golden_cases()[case_idx], shapes.MODE_FP32_CHECK, TOL_FP32)
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_completion_50_tokens_vs_reference_golden(case_idx):
     """greedy decoding continues to the reference's max_new_tokens=50 for every prompt (up to EOS)
     while only the first 10 positions are scanned.  The decoded `completion` must equal the string the reference's
@@ -131,7 +131,7 @@ def test_completion_50_tokens_vs_reference_golden(case_idx):
     sc.close()
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("mode_name", MODES_16)
 def test_scorer_bf16_vs_reference_golden(case_idx, mode_name):
     import gpu_util as U
@@ -243,6 +243,29 @@ def test_scorer_real_dims_mistral(mode_name):
         rel = (p[700] / (p[700] + p[900])).item()
         assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
         assert abs(rows[i][3] - torch.logsumexp(lo, -1).item()) <= 5e-3
+    sc.close()
+
+
+@pytest.mark.parametrize("mode_name", MODES_16)
+def test_scorer_real_dims_qwen(mode_name):
+    """Qwen-7B widths (d 4096, 32 heads x 128, SwiGLU 11008, RMSNorm 1e-6, a bias on q|k|v; vocabulary cut to 32000 to keep
+    the CPU oracle small) at 2 layers against the oracle with the same 16-bit operand rounding."""
+    import dataclasses
+    import gpu_util as U
+    from llm_interpretation_replication_b200 import shapes, weights
+    from oracle import decoder_ref
+    shp = dataclasses.replace(shapes.qwen_7b().with_layers(2), vocab=32000, eos_id=2)
+    W = weights.init_weights(shp, seed=19)
+    assert "l1.b_qkv" in W and "l1.b_dense" not in W
+    sc = U.make_scorer(shp, W, getattr(shapes, mode_name), max_tokens=1024, max_seqs=8, max_lookahead=2)
+    g = np.random.RandomState(6)
+    ids = [g.randint(3, shp.vocab - 3, size=L).tolist() for L in (31, 120, 77)]
+    rows, gens = sc.score_ids(ids, np.array([[700, 900]]), topk=5, max_lookahead=2)
+    for i, x in enumerate(ids):
+        lo = decoder_ref.last_logits(shp, W, torch.tensor(x), **_rnd(mode_name))
+        p = torch.softmax(lo, -1)
+        rel = (p[700] / (p[700] + p[900])).item()
+        assert abs(rows[i][2] - rel) <= _tol(mode_name), (i, rows[i][2], rel)
     sc.close()
 
 

@@ -31,7 +31,7 @@ def _tok(shp, row):
     return tok
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_hf_oracle_matches_reference_function(scorer_golden, case_idx):
     case = scorer_golden["cases"][case_idx]
     shp = shapes.REGISTRY[case["shape"]]()
@@ -50,7 +50,7 @@ def test_hf_oracle_matches_reference_function(scorer_golden, case_idx):
         assert abs(r2["relative_prob"] - g2["relative_prob"]) <= 1e-9
 
 
-@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("case_idx", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_torch_decoder_restatement_matches_reference(scorer_golden, case_idx):
     """All 32 golden rows per family through the plain-torch restatement (k=2 and k=5 rules)."""
     case = scorer_golden["cases"][case_idx]
