@@ -242,7 +242,7 @@ def main():
                     help="packed prompt tokens per C-ABI call; 262144 = 2350 prompts per batch, which fills the waves of the one-token GEMMs (profiles/r1_bench_batch_tokens.jsonl)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--mode", default="fp16", choices=["bf16", "fp16", "bf16_split"],
+    ap.add_argument("--mode", default="fp16", choices=["bf16", "fp16", "bf16_split", "int8_emu"],
                     help="operand format of the tensor-core path: fp16 (weights converted from bf16; default), bf16 (fast, "
                          "misses the 2e-3 gate on some prompts) or bf16_split (bf16 weights, hi+lo bf16 activations)")
     ap.add_argument("--no-other-modes", action="store_true", help="skip the short BF16_FAST / BF16_SPLIT / 50-token legs (N = 1)")
@@ -286,7 +286,8 @@ def main():
 
     W = weights.init_weights_device(shp, seed=0, device=dev, weight_dtype=torch.bfloat16)
     max_seqs = max(2048, args.batch_tokens // 64)   # prompts per batch are bounded by tokens, not by this
-    MODES = {"fp16": shapes.MODE_FP16, "bf16": shapes.MODE_BF16_FAST, "bf16_split": shapes.MODE_BF16_SPLIT}
+    MODES = {"fp16": shapes.MODE_FP16, "bf16": shapes.MODE_BF16_FAST, "bf16_split": shapes.MODE_BF16_SPLIT,
+             "int8_emu": shapes.MODE_INT8_EMU}
     mode = MODES[args.mode]
     sc = Scorer(shp, W, mode=mode, device=dev, max_tokens=args.batch_tokens, max_seqs=max_seqs,
                 max_lookahead=LOOKAHEAD)
@@ -430,7 +431,8 @@ def main():
             cfg["workload"] += f" -- VARIANT: {args.resolve_rate:.0%} of the prompts resolve at position 0 (not the headline workload)"
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-                "dtype": {"fp16": "fp16", "bf16": "bf16", "bf16_split": "bf16 (hi+lo activations)"}[args.mode], "data": "synthetic",
+                "dtype": {"fp16": "fp16", "bf16": "bf16", "bf16_split": "bf16 (hi+lo activations)",
+                          "int8_emu": "fp16 holding int8-grid values (LLM.int8 emulation)"}[args.mode], "data": "synthetic",
                 "config": cfg,
                 "clocks": clk, "gpu_launches": launches,
                 "roofline": {"bound": "tensor", "kernel": "gemm_tc3_kernel / gemm_tc2_kernel (tcgen05 cta_group::2 on 512x256 / 256x256 pair tiles; gemm_tc_kernel when forced)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",

@@ -56,8 +56,18 @@ enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQ
  *               no split form: q/k/v, the KV cache and P are fp16 there (an overflow surfaces as B2S_ERANGE like in the
  *               FP16 mode; q/k/v are LayerNorm-fed projections, not where decoder outliers live).  Needs d_model, d_ff
  *               and n_head*head_dim to be multiples of 64;
- *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5). */
-enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3 };
+ *   FP32_CHECK  fp32 weights and activations on CUDA cores (parity gate 1e-5);
+ *   INT8_EMU    the reference's own GPU configuration, bitsandbytes LLM.int8 (run_base_vs_instruct_100q.py:84,433-437
+ *               USE_8BIT / BitsAndBytesConfig(load_in_8bit)), emulated on the FP16 kernels: the host hands over every
+ *               layer matrix already on its row-wise int8 grid (fp16(rint(W * 127 / s_row) * s_row / 127); embeddings and
+ *               lm_head untouched, as bitsandbytes leaves them), and the library puts the input rows of every linear layer
+ *               on theirs first -- per prompt, columns holding an |x| >= 6.0 stay fp16 (the mixed-precision decomposition),
+ *               every other element becomes rint(x * 127 / s) * s / 127 with s the row's largest |x| below the threshold.
+ *               fp16 x fp16 -> fp32 then multiplies the same numbers as int8 x int8 -> int32 followed by the dequantisation,
+ *               up to the fp16 rounding of the dequantised operands (2^-11, 16 times finer than the int8 step).  Decoder-only
+ *               handles only.  bitsandbytes is not in this image: the mode is pinned against a restatement of its published
+ *               MatMul8bitLt (oracle/int8_ref.py), not against the library itself. */
+enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3, B2S_MODE_INT8_EMU = 4 };
 
 /* weight_ptrs slots: 10 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
  * pointer must be 16-byte aligned (B2S_EINVAL otherwise) */
@@ -203,6 +213,14 @@ B2S_API int b2s_encdec_score_host(b2s_encdec* m, const int32_t* tokens_h, const 
                           const int32_t* cand_ids_h, int32_t topk, int32_t scan_positions, int32_t gen_tokens, int32_t eos_id,
                           float* out_h, int32_t* gen_ids_h /*or NULL*/, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Building block of B2S_MODE_INT8_EMU: puts the fp16 rows x[rows, K] (device, in place) on bitsandbytes' LLM.int8 grid the way
+ * MatMul8bitLt.forward treats the input of one Linear8bitLt call per prompt (prompt i = rows [q_start[i], q_start[i] + q_len[i]),
+ * packed in row order): columns where any row of the prompt has |x| >= threshold stay fp16, every other element becomes
+ * rint(x * 127 / s) * s / 127 with s = the row's largest |x| below the threshold.  mask_scratch: n_seqs * K bytes on the device.
+ * threshold <= 0: no outlier columns. */
+B2S_API int b2s_int8_fakequant_f16(void* x, int32_t rows, int32_t K, const int32_t* q_start, const int32_t* q_len, int32_t n_seqs,
+                           void* mask_scratch, float threshold, void* stream);
+
 /* Number of kernels this library launched since the last call with reset != 0 (bench "gpu_launches"). */
 B2S_API int64_t b2s_launch_count(int32_t reset);
 
@@ -228,6 +246,7 @@ B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* f
  *   "gemm_serpentine"    [0] K walked backwards by odd column tiles (1) or odd waves (2)
  *   "gemm_l2_hint"       [0] TMA L2 eviction hints 0..7; "gemm_tma_store" [1] epilogue through TMA bulk stores;
  *                        "gemm_pair_stride" [1] experiment: permutation of the CTA-pair -> tile-sequence assignment
+ *   "int8_threshold_milli" [6000] INT8_EMU: bitsandbytes' llm_int8_threshold in thousandths (0 = no outlier decomposition)
  *   "lookahead_compact"  [1] one-token steps run only the prompts that still need a position (0 = every prompt of the
  *                        batch runs every step, the round-1 behaviour; rows are bit-identical either way)
  *   "attn_ts"            [1] prompt-pass / one-token attention with P kept in tensor memory (0 = first-generation kernels)

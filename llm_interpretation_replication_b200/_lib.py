@@ -61,6 +61,7 @@ SIGNATURES = {
     "b2s_encdec_workspace_bytes": (_sz, [_vp, _i64, _i32, _i32]),
     "b2s_encdec_score": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
     "b2s_encdec_score_host": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _sz, _vp]),
+    "b2s_int8_fakequant_f16": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _vp, C.c_float, _vp]),
     "b2s_launch_count": (_i64, [_i32]),
     "b2s_set_option": (C.c_int, [C.c_char_p, _i32]),
     "b2s_profile_gemm": (C.c_int, [_i32]),

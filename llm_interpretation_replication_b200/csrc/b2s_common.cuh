@@ -17,6 +17,7 @@ namespace b2s {
 void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
 extern std::atomic<int64_t> g_launch_count;   // kernels launched by this library, any thread (b2s_launch_count)
+extern float g_opt_int8_threshold;            // b2s_set_option "int8_threshold_milli" (b2s_model.cu)
 extern int g_opt_compact;                     // b2s_set_option "lookahead_compact" (b2s_model.cu)
 
 #define B2S_CHECK_CUDA(expr)                                                                  \

@@ -262,6 +262,76 @@ template int launch_swiglu<__nv_bfloat16>(const void*, void*, int64_t, int, cuda
 template int launch_swiglu<__half>(const void*, void*, int64_t, int, cudaStream_t, int);
 
 // =================================================================================================
+// LLM.int8 emulation: per-prompt outlier columns, per-row absmax int8 round trip (see b2s_decoder.cuh).
+//   bitsandbytes MatMul8bitLt.forward: double_quant(A, threshold) -> row statistics without the outlier elements, int8 rows with
+//   the outlier columns zeroed, the outlier columns multiplied in fp16 against the dequantised weight columns, the int32
+//   product dequantised with SCA[m] * SCB[n] / 127^2.  Here the integer grid is applied to the fp16 operand itself and the
+//   tensor core multiplies fp16 x fp16 into fp32: the same numbers up to the fp16 rounding of the dequantised operands
+//   (2^-11 relative, 16 times finer than the int8 step).
+// HBM-bound elementwise work: x is read twice and written once.
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+int8_colmask_kernel(const __half* __restrict__ x, int K, BatchMeta meta, uint8_t* __restrict__ mask, float thr) {
+  const int seq = blockIdx.y;
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) * 2;        // two columns per thread (half2 loads)
+  if (k >= K) return;
+  const int r0 = meta.q_start[seq], n = meta.q_len[seq];
+  bool o0 = false, o1 = false;
+  for (int r = 0; r < n; ++r) {
+    const float2 v = __half22float2(*reinterpret_cast<const __half2*>(x + static_cast<size_t>(r0 + r) * K + k));
+    o0 |= fabsf(v.x) >= thr;
+    o1 |= fabsf(v.y) >= thr;
+  }
+  mask[static_cast<size_t>(seq) * K + k] = o0;
+  mask[static_cast<size_t>(seq) * K + k + 1] = o1;
+}
+
+// row -> prompt: prompts are packed back to back in row order, so a binary search over q_start finds the owner
+__global__ void __launch_bounds__(256)
+int8_fakequant_kernel(__half* __restrict__ x, int K, int n_seqs, BatchMeta meta, const uint8_t* __restrict__ mask, float thr) {
+  __shared__ float red[8];
+  const int row = blockIdx.x;
+  int lo = 0, hi = n_seqs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (meta.q_start[mid] <= row) lo = mid; else hi = mid - 1;
+  }
+  const uint8_t* mk = mask + static_cast<size_t>(lo) * K;
+  __half* xr = x + static_cast<size_t>(row) * K;
+  float amax = 0.f;
+  for (int k = threadIdx.x * 2; k < K; k += blockDim.x * 2) {
+    const float2 v = __half22float2(*reinterpret_cast<const __half2*>(xr + k));
+    const float a0 = fabsf(v.x), a1 = fabsf(v.y);
+    if (a0 < thr) amax = fmaxf(amax, a0);
+    if (a1 < thr) amax = fmaxf(amax, a1);
+  }
+  amax = warp_max(amax);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) red[w] = amax;
+  __syncthreads();
+  amax = warp_max(l < (blockDim.x >> 5) ? red[l] : 0.f);
+  if (amax == 0.f) return;                                          // an all-zero (or all-outlier) row quantises to itself
+  const float q = 127.0f / amax, dq = amax / 127.0f;
+  for (int k = threadIdx.x * 2; k < K; k += blockDim.x * 2) {
+    float2 v = __half22float2(*reinterpret_cast<const __half2*>(xr + k));
+    if (!mk[k]) v.x = rintf(v.x * q) * dq;
+    if (!mk[k + 1]) v.y = rintf(v.y * q) * dq;
+    *reinterpret_cast<__half2*>(xr + k) = __floats2half2_rn(v.x, v.y);
+  }
+}
+
+int launch_int8_fakequant(void* x, int rows, int K, int n_seqs, const BatchMeta& meta, uint8_t* mask, float threshold, cudaStream_t st) {
+  B2S_REQUIRE(K % 2 == 0 && rows > 0 && n_seqs > 0, "int8 emulation: K=%d rows=%d prompts=%d", K, rows, n_seqs);
+  if (!(threshold > 0.f)) threshold = INFINITY;      // bitsandbytes: threshold 0 = no mixed-precision decomposition
+  dim3 g1(static_cast<unsigned>(ceil_div(K / 2, 256)), static_cast<unsigned>(n_seqs));
+  int8_colmask_kernel<<<g1, 256, 0, st>>>(reinterpret_cast<const __half*>(x), K, meta, mask, threshold);
+  B2S_CHECK_LAUNCH();
+  int8_fakequant_kernel<<<rows, 256, 0, st>>>(reinterpret_cast<__half*>(x), K, n_seqs, meta, mask, threshold);
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+
+// =================================================================================================
 // RoPE (rotate_half form on the first rotary_dim dims) + KV-cache append.
 //   HF falcon:69-99,154-165 / gpt_neox:126-159: q' = q*cos + rotate_half(q)*sin with cos/sin of shape
 //   [pos, rd] = cat(freqs, freqs); here cos/sin tables hold the first rd/2 columns.

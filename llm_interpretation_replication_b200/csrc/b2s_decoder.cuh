@@ -100,6 +100,12 @@ int launch_attn_tc(const AttnArgs& a, int n_seqs, int total_rows, int cache_slot
 // from a.qkv = [rows, 3*nh*64], <= 256 keys per prompt
 bool attn_enc_supported(const AttnArgs& a);
 int launch_attn_enc(const AttnArgs& a, int n_seqs, int total_rows, int max_qlen, cudaStream_t st);
+// LLM.int8 emulation (B2S_MODE_INT8_EMU): the fp16 rows x[rows, K] that feed a linear layer are replaced in place by what
+// bitsandbytes' MatMul8bitLt makes of them.  A column is an outlier column of a prompt when any of the prompt's rows holds
+// |x| >= threshold there (prompt = rows [q_start, q_start + q_len) of `meta`; one row per prompt in one-token steps): those
+// columns stay fp16.  Every other element becomes rint(x * 127 / s) * s / 127 with s = the row's largest |x| below the threshold.
+// `mask` is scratch of n_seqs * K bytes.
+int launch_int8_fakequant(void* x, int rows, int K, int n_seqs, const BatchMeta& meta, uint8_t* mask, float threshold, cudaStream_t st);
 int launch_lmhead_partials_from_logits(const float* logits, int M, int V, const int32_t* cand, float* partials,
                                        float* cand_logits, cudaStream_t st);
 int launch_lmhead_merge(const float* partials, const float* cand_logits, int M, int tiles_n, float* stats,

@@ -6,6 +6,7 @@
 // the look-ahead scan (:348-363) is unresolved.
 #include "b2s_decoder.cuh"
 #include <stdarg.h>
+#include <algorithm>
 #include <type_traits>
 #include <vector>
 
@@ -14,6 +15,7 @@ namespace b2s {
 thread_local std::string g_last_error;
 std::atomic<int64_t> g_launch_count{0};
 int g_opt_compact = 1;   // b2s_set_option "lookahead_compact": one-token steps run only the prompts that still need a position
+float g_opt_int8_threshold = 6.0f;   // b2s_set_option "int8_threshold_milli": bitsandbytes' llm_int8_threshold (default 6.0)
 
 void set_error(const char* fmt, ...) {
   char buf[1024];
@@ -37,6 +39,7 @@ struct b2s_model {
   bool bf16;      // tensor-core mode (bf16 weights); false = fp32 check mode
   int act_f16;    // tensor-core mode with fp16 operands (weights handed over as fp16)
   int split;      // BF16_SPLIT: every GEMM A operand is stored as [hi | lo] bf16 halves (row width doubled)
+  int int8;       // INT8_EMU: FP16 kernels, every linear layer's input put on bitsandbytes' int8 grid first (launch_int8_fakequant)
   size_t at_size;
   const void* gw(int slot) const { return w[slot]; }
   const void* lw(int layer, int slot) const { return w[B2S_W_NGLOBAL + layer * B2S_W_PER_LAYER + slot]; }
@@ -57,6 +60,7 @@ struct Workspace {
   size_t cache_layer_bytes;
   size_t cache_slots;
   float *partials, *cand_logits, *stats, *logits;
+  uint8_t* qmask;   // INT8_EMU: outlier-column flags, [N, widest linear input]
   size_t total;
 };
 
@@ -116,6 +120,8 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.cand_logits = reinterpret_cast<float*>(take(8 * N));
   w.stats = reinterpret_cast<float*>(take(4 * static_cast<size_t>(N) * LMH_STATS));
   w.logits = m->bf16 ? nullptr : reinterpret_cast<float*>(take(4 * static_cast<size_t>(N) * d.vocab));
+  const size_t widest = static_cast<size_t>(std::max(std::max(d.d_model, d.d_ff), d.n_head * d.head_dim));
+  w.qmask = m->int8 ? take(static_cast<size_t>(N) * widest) : nullptr;
   w.total = off;
   return w;
 }
@@ -159,6 +165,12 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       ln.g2 = m->lwf(l, B2S_WL_LN2_G); ln.b2 = m->lwf(l, B2S_WL_LN2_B); ln.y2 = w.ln2;
     }
     B2S_TRY((launch_ln<AT, WT>(ln, rows, st)));
+    // INT8_EMU: what bitsandbytes' Linear8bitLt does to the input of every linear layer (one prompt = one of its calls)
+    auto q8 = [&](void* x, int K) -> int {
+      return m->int8 ? launch_int8_fakequant(x, rows, K, n_seqs, w.meta, w.qmask, g_opt_int8_threshold, st) : B2S_OK;
+    };
+    B2S_TRY(q8(w.ln1, dm));
+    if (ln.y2) B2S_TRY(q8(w.ln2, dm));
 
     uint8_t* kc = reinterpret_cast<uint8_t*>(w.kcache) + w.cache_layer_bytes * l;
     uint8_t* vc = reinterpret_cast<uint8_t*>(w.vcache) + w.cache_layer_bytes * l;
@@ -207,6 +219,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
       B2S_TRY(launch_attn<QT>(at, n_seqs, st));
     }
 
+    B2S_TRY(q8(w.attn, d.n_head * d.head_dim));
     B2S_TRY(linear(m, w.attn, m->lw(l, B2S_WL_W_DENSE), m->lwf(l, B2S_WL_B_DENSE), w.resid, rows, dm,
                    d.n_head * d.head_dim, EPI_RESID_F32, st));
     const void* mlp_in = w.ln1;
@@ -217,6 +230,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
         l2.x = w.resid; l2.d = dm; l2.eps = d.norm_eps; l2.rms = d.norm_type == B2S_NORM_RMS; l2.split = m->split;
         l2.g1 = m->lwf(l, B2S_WL_LN2_G); l2.b1 = m->lwf(l, B2S_WL_LN2_B); l2.y1 = w.ln2;
         B2S_TRY((launch_ln<AT, WT>(l2, rows, st)));
+        B2S_TRY(q8(w.ln2, dm));
       }
     }
     if (d.mlp_type == B2S_MLP_SWIGLU_FUSED) {   // gate / up rows interleaved: silu(gate) * up formed in the projection's epilogue
@@ -240,6 +254,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     } else {
       B2S_TRY(linear(m, mlp_in, m->lw(l, B2S_WL_W_UP), m->lwf(l, B2S_WL_B_UP), w.act, rows, d.d_ff, dm, EPI_GELU_BF16, st, m->split));
     }
+    B2S_TRY(q8(w.act, d.d_ff));
     B2S_TRY(linear(m, w.act, m->lw(l, B2S_WL_W_DOWN), m->lwf(l, B2S_WL_B_DOWN), w.resid, rows, dm, d.d_ff,
                    EPI_RESID_F32, st));
   }
@@ -318,7 +333,7 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
               "model_create: interleaved gate/up rows (B2S_MLP_SWIGLU_FUSED) are for the tensor-core modes");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
   B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_BF16_SPLIT ||
-                  d.compute_mode == B2S_MODE_FP32_CHECK,
+                  d.compute_mode == B2S_MODE_FP32_CHECK || d.compute_mode == B2S_MODE_INT8_EMU,
               "model_create: unknown compute mode %d", d.compute_mode);
   B2S_REQUIRE(d.compute_mode != B2S_MODE_BF16_SPLIT || (d.d_model % 64 == 0 && d.d_ff % 64 == 0 && (d.n_head * d.head_dim) % 64 == 0),
               "model_create: BF16_SPLIT needs d_model, d_ff and n_head*head_dim to be multiples of 64");
@@ -341,7 +356,8 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   m->w.assign(weight_ptrs, weight_ptrs + need);
   m->device = device;
   m->bf16 = d.compute_mode != B2S_MODE_FP32_CHECK;
-  m->act_f16 = d.compute_mode == B2S_MODE_FP16 ? 1 : 0;
+  m->int8 = d.compute_mode == B2S_MODE_INT8_EMU ? 1 : 0;
+  m->act_f16 = (d.compute_mode == B2S_MODE_FP16 || m->int8) ? 1 : 0;
   m->split = d.compute_mode == B2S_MODE_BF16_SPLIT ? 1 : 0;
   m->at_size = m->bf16 ? 2 : 4;
   m->qkv_dim = (d.n_head + 2 * d.n_kv_head) * d.head_dim;
@@ -538,6 +554,15 @@ int b2s_attention_bf16(const void* qkv, const void* kcache, const void* vcache, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (use_tensor_cores) return launch_attn_tc(a, n_seqs, total_rows, cache_slots, max_qlen, st);
   return launch_attn<__nv_bfloat16>(a, n_seqs, st);
+}
+
+int b2s_int8_fakequant_f16(void* x, int32_t rows, int32_t K, const int32_t* q_start, const int32_t* q_len, int32_t n_seqs,
+                           void* mask_scratch, float threshold, void* stream) {
+  B2S_REQUIRE(x && q_start && q_len && mask_scratch, "int8_fakequant: null argument");
+  BatchMeta meta{};
+  meta.q_start = const_cast<int32_t*>(q_start); meta.q_len = const_cast<int32_t*>(q_len);
+  return launch_int8_fakequant(x, rows, K, n_seqs, meta, reinterpret_cast<uint8_t*>(mask_scratch), threshold,
+                               reinterpret_cast<cudaStream_t>(stream));
 }
 
 size_t b2s_lm_head_scratch_bytes(int32_t M, int32_t V) {

@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .shapes import DecoderShape, MODE_BF16_FAST, MODE_FP16, MODE_FP32_CHECK, MLP_SWIGLU, MLP_SWIGLU_FUSED
+from .shapes import DecoderShape, MODE_BF16_FAST, MODE_FP16, MODE_FP32_CHECK, MODE_INT8_EMU, MLP_SWIGLU, MLP_SWIGLU_FUSED
 from . import weights as _weights
 
 MAX_LOOK_AHEAD = 10   # reference run_base_vs_instruct_100q.py:285
@@ -46,6 +46,14 @@ def candidate_ids(tokenizer, variant: str, yes: str = " Yes", no: str = " No") -
     y_id = y[0] if len(y) > 0 else tokenizer.encode(yes.strip())[0]
     n_id = n[0] if len(n) > 0 else tokenizer.encode(no.strip())[0]
     return int(y_id), int(n_id)
+
+
+def int8_rowwise_dequant(w: torch.Tensor) -> torch.Tensor:
+    """fp16(rint(W * 127 / s) * s / 127) with s = max |W[row]|: the weight a bitsandbytes ``Linear8bitLt`` effectively multiplies
+    by (``CB`` int8 rows, ``SCB`` row scales; ``F.double_quant`` / ``int8_vectorwise_quant`` with round-to-nearest-even)."""
+    wf = w.float()
+    s = wf.abs().amax(dim=1, keepdim=True).clamp_min(1e-30)
+    return (torch.round(wf * (torch.full_like(s, 127.0) / s)) * (s / 127.0)).to(torch.float16)
 
 
 def plan_batches(lengths: Sequence[int], max_tokens: int, max_seqs: int) -> List[List[int]]:
@@ -99,9 +107,13 @@ class Scorer:
         self.mode = mode
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.max_tokens, self.max_seqs, self.max_lookahead = int(max_tokens), int(max_seqs), int(max_lookahead)
-        want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
+        want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16, MODE_INT8_EMU: torch.float16}.get(mode, torch.bfloat16)
         W = dict(weights_dev)
-        if mode == MODE_FP16:   # bf16 (or fp32) checkpoints are handed to the library as fp16 copies
+        if mode == MODE_INT8_EMU:
+            # bitsandbytes Linear8bitLt: every nn.Linear of the decoder layers is stored as int8 rows with one fp32 scale per output
+            # row (lm_head is skipped, embeddings are not Linear); the library multiplies their dequantised form
+            W = {k: (int8_rowwise_dequant(v) if k.split(".")[-1] in ("w_qkv", "w_dense", "w_up", "w_down") else v) for k, v in W.items()}
+        if mode in (MODE_FP16, MODE_INT8_EMU):   # bf16 (or fp32) checkpoints are handed to the library as fp16 copies
             W = {k: (v.to(torch.float16) if _weights.is_matrix(k) and v.dtype != torch.float16 else v) for k, v in W.items()}
             if weights_dev.get("lm_head") is weights_dev.get("wte"):
                 W["lm_head"] = W["wte"]

@@ -64,11 +64,15 @@ def _split_qkv(shape: DecoderShape, qkv):
 
 
 def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.Tensor,
-                   round_act: Optional[Callable] = None, dtype=torch.float32, round_attn: Optional[Callable] = None) -> torch.Tensor:
+                   round_act: Optional[Callable] = None, dtype=torch.float32, round_attn: Optional[Callable] = None,
+                   linear_fn: Optional[Callable] = None) -> torch.Tensor:
     """ids [L] -> hidden after the final LayerNorm, [L, d].  ``round_act`` (e.g. bf16 round trip) is
     applied to every GEMM input and to q/k/v, emulating bf16 MMA operands with fp32 accumulate; ``round_attn``
-    overrides it for q/k/v (the BF16_SPLIT mode keeps those in fp16 while the GEMM inputs are hi + lo bf16 halves)."""
+    overrides it for q/k/v (the BF16_SPLIT mode keeps those in fp16 while the GEMM inputs are hi + lo bf16 halves).
+    ``linear_fn(x, weight, bias)`` replaces the four linear layers of every block (oracle/int8_ref.py: bitsandbytes'
+    Linear8bitLt restated); the LM head is not one of them."""
     r = round_act if round_act is not None else (lambda t: t)
+    lin = linear_fn if linear_fn is not None else (lambda t, w, b: F.linear(r(t), w, b))
     ra = round_attn if round_attn is not None else r
     d, nh, nkv, hd = shape.d_model, shape.n_head, shape.n_kv_head, shape.head_dim
     L = ids.shape[0]
@@ -92,7 +96,7 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         return F.layer_norm(t, (d,), W[g].to(dtype), W[b].to(dtype), shape.norm_eps)
 
     def mlp_act(t, p, bias):
-        up = F.linear(r(t), W[p + "w_up"].to(dtype), bias("b_up"))
+        up = lin(t, W[p + "w_up"].to(dtype), bias("b_up"))
         if shape.mlp_type == MLP_SWIGLU:        # rows [0, ff) = gate_proj, [ff, 2ff) = up_proj; formed on the fp32 accumulators
             return F.silu(up[..., :shape.d_ff]) * up[..., shape.d_ff:]
         if shape.act_type == ACT_RELU:
@@ -106,7 +110,7 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         bias = (lambda n: W[p + n].to(dtype)) if shape.has_bias else \
                (lambda n: W[p + n].to(dtype) if (n == "b_qkv" and shape.qkv_bias) else None)
         ln1 = norm(x, p + "ln1_g", p + "ln1_b")
-        qkv = F.linear(r(ln1), W[p + "w_qkv"].to(dtype), bias("b_qkv"))
+        qkv = lin(ln1, W[p + "w_qkv"].to(dtype), bias("b_qkv"))
         q, k, v = _split_qkv(shape, qkv)
         if rope:
             q, k = _apply_rope(q, cos, sin, shape.rotary_dim), _apply_rope(k, cos, sin, shape.rotary_dim)
@@ -121,24 +125,24 @@ def forward_hidden(shape: DecoderShape, W: Dict[str, torch.Tensor], ids: torch.T
         s = s.masked_fill(~causal[None], float("-inf"))
         a = torch.softmax(s, dim=-1)
         o = torch.einsum("hqk,khd->qhd", a, vv).reshape(L, nh * hd)
-        attn = F.linear(r(o), W[p + "w_dense"].to(dtype), bias("b_dense"))
+        attn = lin(o, W[p + "w_dense"].to(dtype), bias("b_dense"))
         if shape.parallel_residual:
             ln2 = ln1 if shape.n_ln_per_layer == 1 else norm(x, p + "ln2_g", p + "ln2_b")
             h = mlp_act(ln2, p, bias)
-            mlp = F.linear(r(h), W[p + "w_down"].to(dtype), bias("b_down"))
+            mlp = lin(h, W[p + "w_down"].to(dtype), bias("b_down"))
             x = mlp + attn + x
         else:
             x1 = attn + x
             ln2 = norm(x1, p + "ln2_g", p + "ln2_b")
             h = mlp_act(ln2, p, bias)
-            mlp = F.linear(r(h), W[p + "w_down"].to(dtype), bias("b_down"))
+            mlp = lin(h, W[p + "w_down"].to(dtype), bias("b_down"))
             x = mlp + x1
     return norm(x, "lnf_g", "lnf_b")
 
 
-def last_logits(shape, W, ids, round_act=None, dtype=torch.float32, round_attn=None) -> torch.Tensor:
+def last_logits(shape, W, ids, round_act=None, dtype=torch.float32, round_attn=None, linear_fn=None) -> torch.Tensor:
     r = round_act if round_act is not None else (lambda t: t)
-    h = forward_hidden(shape, W, ids, round_act, dtype, round_attn)[-1]
+    h = forward_hidden(shape, W, ids, round_act, dtype, round_attn, linear_fn)[-1]
     return F.linear(r(h), W["lm_head"].to(dtype)).float()
 
 
@@ -160,14 +164,14 @@ def scan_positions(score_rows: List[torch.Tensor], id_a: int, id_b: int, topk: i
 
 
 def greedy_scores(shape, W, ids: List[int], n_positions: int, eos_id: int, round_act=None,
-                  dtype=torch.float32):
+                  dtype=torch.float32, round_attn=None, linear_fn=None):
     """Greedy decode restated without a KV cache: scores[t] = logits after prompt + t generated
     tokens (HF:generation/utils.py:2743-2805; SURVEY.md Appendix A, last row).  Stops after the
     position whose argmax is EOS, as ``generate`` does."""
     seq = list(ids)
     rows, gen = [], []
     for _ in range(n_positions):
-        row = last_logits(shape, W, torch.tensor(seq, dtype=torch.long), round_act, dtype)
+        row = last_logits(shape, W, torch.tensor(seq, dtype=torch.long), round_act, dtype, round_attn, linear_fn)
         rows.append(row)
         nxt = int(torch.argmax(row))
         gen.append(nxt)
@@ -178,9 +182,9 @@ def greedy_scores(shape, W, ids: List[int], n_positions: int, eos_id: int, round
 
 
 def score_ids(shape, W, ids: List[int], id_a: int, id_b: int, topk: int = 5, max_lookahead: int = 10,
-              eos_id: Optional[int] = None, round_act=None, dtype=torch.float32):
+              eos_id: Optional[int] = None, round_act=None, dtype=torch.float32, round_attn=None, linear_fn=None):
     eos = shape.eos_id if eos_id is None else eos_id
-    rows, gen = greedy_scores(shape, W, ids, max_lookahead, eos, round_act, dtype)
+    rows, gen = greedy_scores(shape, W, ids, max_lookahead, eos, round_act, dtype, round_attn, linear_fn)
     pa, pb, pos, found = scan_positions(rows, id_a, id_b, topk)
     row = rows[pos]
     lse = torch.logsumexp(row, dim=-1).item()
