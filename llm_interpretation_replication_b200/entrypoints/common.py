@@ -73,13 +73,21 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
     from ..scorer import MAX_LOOK_AHEAD
     device = torch.device(device if device is not None else "cuda:0")
     local = checkpoint.resolve_local(model_name)
+    if mode is None and os.environ.get("B2S_USE_8BIT", "0") not in ("", "0"):
+        # the reference's USE_8BIT = True (run_base_vs_instruct_100q.py:84, compare_instruct_models.py:412): LLM.int8 for the
+        # decoder-only models (emulated: shapes.MODE_INT8_EMU); the encoder-decoder scorer has no such mode and keeps its default
+        is_t5 = model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY
+        if local is not None:
+            with open(os.path.join(local, "config.json")) as f:
+                is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
+        mode = shapes.MODE_BF16_SPLIT if is_t5 else shapes.MODE_INT8_EMU
     if mode is None:
         is_t5 = model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY
         if local is not None:
             with open(os.path.join(local, "config.json")) as f:
                 is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
         mode = shapes.MODE_BF16_SPLIT if is_t5 else shapes.MODE_FP16
-    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
+    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16}.get(mode, torch.bfloat16)
     if local is not None:
         shp, W = checkpoint.load_checkpoint(local, device=device, weight_dtype=dt, n_layer=n_layer)
         try:
