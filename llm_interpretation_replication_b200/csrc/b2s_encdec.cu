@@ -124,10 +124,10 @@ __global__ void encdec_prep_kernel(const int32_t* __restrict__ cu, int n_rows, i
 //   self  (SELF = true)   the warp first appends this position's k and v (read from the fused q|k|v row) to the cache,
 //                         then attends over the step + 1 cached positions with the decoder's relative bias
 //                         (bias[head][key - query], query = last position).
-//   pass 1  scores: 8 lanes share a key (16 bytes = 8 dims each, 3 shuffles to reduce), 4 keys per warp instruction,
-//           4 instructions in flight; scores parked in shared memory
-//   pass 2  softmax statistics over the parked scores (lanes split keys)
-//   pass 3  P.V: a lane owns two output dims, one coalesced 128-byte row of V per key, 8 keys in flight
+// 8 lanes share a key (16 bytes = 8 dims each of its K row and of its V row), the four 8-lane groups of the warp walk the
+// keys in four interleaved streams with an online softmax each (running maximum, sum, 8 output dims per lane; no shared
+// memory, no barrier) and are merged with shuffles at the end.  (A three-pass version -- scores parked in shared memory,
+// statistics, then P.V -- ran at the same speed: the kernel is bound by CTA turnover and HBM latency, not by instructions.)
 // The generic varlen kernel spent 470 us (cross) and 35 us (self, after a separate 12 us append kernel) per layer and step
 // here: one CTA per (row, head) staging K and V into shared memory as fp32 and then using one of its eight warps.
 // -------------------------------------------------------------------------------------------------
@@ -161,18 +161,13 @@ __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
 }
-__device__ __forceinline__ float2 load2(const float* p) { return *reinterpret_cast<const float2*>(p); }
-__device__ __forceinline__ float2 load2(const __half* p) { return __half22float2(*reinterpret_cast<const __half2*>(p)); }
-__device__ __forceinline__ float2 load2(const __nv_bfloat16* p) { return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p)); }
 
 template <typename QT, bool SELF>
 __global__ void __launch_bounds__(128)
 step_attn_kernel(StepAttnArgs a) {
-  extern __shared__ float cs_scores[];                  // [4 warps][max_kv]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = blockIdx.x * 4 + warp, r = blockIdx.y;
   if (h >= a.nh) return;                                // warp-uniform; no block-wide barrier below
-  float* sc = cs_scores + warp * a.max_kv;
   const int L = a.kv_len[r];
   const size_t pitch = static_cast<size_t>(a.kv_pitch);
   const QT* qrow = reinterpret_cast<const QT*>(a.q) + static_cast<size_t>(r) * a.q_pitch;
@@ -189,81 +184,94 @@ step_attn_kernel(StepAttnArgs a) {
   const int sub = lane & 7, grp = lane >> 3;
   float q[8];
   load8(qrow + h * 64 + 8 * sub, q);
-  // pass 1
-  for (int j0 = 0; j0 < L; j0 += 16) {
-    float k[4][8];
+  // One pass, online softmax, four independent streams: the 8 lanes of group g own keys g, g + 4, g + 8, ... -- 16-byte
+  // slices of the K row and of the V row of two keys in flight per lane (K and V of 8 keys per warp instruction pair),
+  // running maximum / sum / 8 output dims per lane; the four groups are merged with shuffles at the end.
+  float m = -INFINITY, l = 0.f;
+  float o[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+  for (int i = 0; i < 8; ++i) o[i] = 0.f;
+  for (int j0 = 0; j0 < L; j0 += 8) {
+    float k[2][8], v[2][8], d[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
       const int j = j0 + 4 * u + grp;
-      if (j < L) load8(kbase + static_cast<size_t>(j) * pitch + 8 * sub, k[u]);
-      else {
+      if (j < L) {
+        load8(kbase + static_cast<size_t>(j) * pitch + 8 * sub, k[u]);
+        load8(vbase + static_cast<size_t>(j) * pitch + 8 * sub, v[u]);
+      } else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) k[u][i] = 0.f;
+        for (int i = 0; i < 8; ++i) { k[u][i] = 0.f; v[u][i] = 0.f; }
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      float d = 0.f;
+    for (int u = 0; u < 2; ++u) {
+      float t = 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) d = fmaf(q[i], k[u][i], d);
-      d += __shfl_xor_sync(0xffffffffu, d, 1);
-      d += __shfl_xor_sync(0xffffffffu, d, 2);
-      d += __shfl_xor_sync(0xffffffffu, d, 4);
+      for (int i = 0; i < 8; ++i) t = fmaf(q[i], k[u][i], t);
+      t += __shfl_xor_sync(0xffffffffu, t, 1);
+      t += __shfl_xor_sync(0xffffffffu, t, 2);
+      t += __shfl_xor_sync(0xffffffffu, t, 4);
       const int j = j0 + 4 * u + grp;
-      if (sub == 0 && j < L) sc[j] = SELF ? d + tb[j] : d;
+      if constexpr (SELF) { if (j < L) t += tb[j]; }
+      d[u] = j < L ? t : -INFINITY;
+    }
+    const float mn = fmaxf(m, fmaxf(d[0], d[1]));
+    if (mn > -INFINITY) {                               // (a group with no key yet keeps its empty state)
+      const float corr = __expf(m - mn), p0 = __expf(d[0] - mn), p1 = __expf(d[1] - mn);
+      l = fmaf(l, corr, p0 + p1);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = fmaf(o[i], corr, fmaf(p0, v[0][i], p1 * v[1][i]));
+      m = mn;
     }
   }
-  __syncwarp();
-  // pass 2
-  float m = -INFINITY;
-  for (int j = lane; j < L; j += 32) m = fmaxf(m, sc[j]);
-  m = warp_max(m);
-  float l = 0.f;
-  for (int j = lane; j < L; j += 32) {
-    const float p = __expf(sc[j] - m);
-    sc[j] = p;
-    l += p;
-  }
-  l = warp_sum(l);
-  __syncwarp();
-  // pass 3
-  float o0 = 0.f, o1 = 0.f;
-  const QT* vp = vbase + 2 * lane;
-  int j = 0;
-  for (; j + 8 <= L; j += 8) {
-    float2 v[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = load2(vp + static_cast<size_t>(j + u) * pitch);
-#pragma unroll
-    for (int u = 0; u < 8; ++u) { const float p = sc[j + u]; o0 = fmaf(p, v[u].x, o0); o1 = fmaf(p, v[u].y, o1); }
-  }
-  for (; j < L; ++j) {
-    const float2 v = load2(vp + static_cast<size_t>(j) * pitch);
-    const float p = sc[j];
-    o0 = fmaf(p, v.x, o0); o1 = fmaf(p, v.y, o1);
-  }
+  // merge the four groups
+  float mall = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+  mall = fmaxf(mall, __shfl_xor_sync(0xffffffffu, mall, 16));
+  const float w = m > -INFINITY ? __expf(m - mall) : 0.f;
+  l *= w;
+  l += __shfl_xor_sync(0xffffffffu, l, 8);
+  l += __shfl_xor_sync(0xffffffffu, l, 16);
   const float inv = 1.f / l;
-  o0 *= inv; o1 *= inv;
-  const size_t col = static_cast<size_t>(h) * 64 + 2 * lane;
-  if (a.split) {
-    __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + static_cast<size_t>(r) * (2 * static_cast<size_t>(a.inner)) + col;
-    const __nv_bfloat162 hi = __floats2bfloat162_rn(o0, o1);
-    *reinterpret_cast<__nv_bfloat162*>(ob) = hi;
-    *reinterpret_cast<__nv_bfloat162*>(ob + a.inner) = __floats2bfloat162_rn(o0 - __low2float(hi), o1 - __high2float(hi));
-  } else {
-    QT* op = reinterpret_cast<QT*>(a.out) + static_cast<size_t>(r) * a.inner + col;
-    if constexpr (std::is_same<QT, float>::value) *reinterpret_cast<float2*>(op) = make_float2(o0, o1);
-    else if constexpr (std::is_same<QT, __half>::value) *reinterpret_cast<__half2*>(op) = __floats2half2_rn(o0, o1);
-    else *reinterpret_cast<__nv_bfloat162*>(op) = __floats2bfloat162_rn(o0, o1);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    o[i] *= w;
+    o[i] += __shfl_xor_sync(0xffffffffu, o[i], 8);
+    o[i] += __shfl_xor_sync(0xffffffffu, o[i], 16);
+    o[i] *= inv;
+  }
+  if (grp == 0) {
+    const size_t col = static_cast<size_t>(h) * 64 + 8 * sub;
+    if (a.split) {
+      __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + static_cast<size_t>(r) * (2 * static_cast<size_t>(a.inner)) + col;
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 hv = __floats2bfloat162_rn(o[2 * i], o[2 * i + 1]);
+        const __nv_bfloat162 lv = __floats2bfloat162_rn(o[2 * i] - __low2float(hv), o[2 * i + 1] - __high2float(hv));
+        hi[i] = *reinterpret_cast<const uint32_t*>(&hv);
+        lo[i] = *reinterpret_cast<const uint32_t*>(&lv);
+      }
+      *reinterpret_cast<uint4*>(ob) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<uint4*>(ob + a.inner) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    } else {
+      QT* op = reinterpret_cast<QT*>(a.out) + static_cast<size_t>(r) * a.inner + col;
+      if constexpr (std::is_same<QT, float>::value) {
+        *reinterpret_cast<float4*>(op) = make_float4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<float4*>(op + 4) = make_float4(o[4], o[5], o[6], o[7]);
+      } else if constexpr (std::is_same<QT, __half>::value) {
+        *reinterpret_cast<uint4*>(op) = make_uint4(pack_f16x2(o[0], o[1]), pack_f16x2(o[2], o[3]), pack_f16x2(o[4], o[5]), pack_f16x2(o[6], o[7]));
+      } else {
+        *reinterpret_cast<uint4*>(op) = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+      }
+    }
   }
 }
 
 template <typename QT, bool SELF>
 int launch_step_attn(const StepAttnArgs& a, int rows, cudaStream_t st) {
-  const size_t smem = 4 * static_cast<size_t>(a.max_kv) * sizeof(float);
-  B2S_REQUIRE(smem <= 48 * 1024, "step attention: %d keys exceed the score buffer", a.max_kv);
   dim3 grid(static_cast<unsigned>(ceil_div(a.nh, 4)), static_cast<unsigned>(rows));
-  step_attn_kernel<QT, SELF><<<grid, 128, smem, st>>>(a);
+  step_attn_kernel<QT, SELF><<<grid, 128, 0, st>>>(a);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
