@@ -246,6 +246,8 @@ B2S_API int b2s_profile_gemm_read(double* total_ms, int64_t* launches, double* f
  *   "gemm_serpentine"    [0] K walked backwards by odd column tiles (1) or odd waves (2)
  *   "gemm_l2_hint"       [0] TMA L2 eviction hints 0..7; "gemm_tma_store" [1] epilogue through TMA bulk stores;
  *                        "gemm_pair_stride" [1] experiment: permutation of the CTA-pair -> tile-sequence assignment
+ *   "attn_step"          [1] one-token attention of head_dim 80 / 128, ALiBi models and the fp32 mode on the streaming kernel
+ *                        (0 = the varlen kernel that also runs their prompt pass)
  *   "int8_threshold_milli" [6000] INT8_EMU: bitsandbytes' llm_int8_threshold in thousandths (0 = no outlier decomposition)
  *   "lookahead_compact"  [1] one-token steps run only the prompts that still need a position (0 = every prompt of the
  *                        batch runs every step, the round-1 behaviour; rows are bit-identical either way)

@@ -17,6 +17,7 @@ namespace b2s {
 void set_error(const char* fmt, ...);
 extern thread_local std::string g_last_error;
 extern std::atomic<int64_t> g_launch_count;   // kernels launched by this library, any thread (b2s_launch_count)
+extern int g_opt_attn_step;                   // b2s_set_option "attn_step" (b2s_model.cu)
 extern float g_opt_int8_threshold;            // b2s_set_option "int8_threshold_milli" (b2s_model.cu)
 extern int g_opt_compact;                     // b2s_set_option "lookahead_compact" (b2s_model.cu)
 
@@ -144,6 +145,24 @@ template <typename T> __device__ __forceinline__ T from_f32(float v);
 template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+// eight consecutive elements (16 bytes of a 16-bit type, 32 bytes of fp32) as floats
+__device__ __forceinline__ void load8(const float* p, float (&v)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void load8(const __half* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 f = __half22float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+}
 
 // insert v into a descending top-5 list
 __device__ __forceinline__ void top5_insert(float (&t)[5], float v) {

@@ -553,6 +553,136 @@ template int launch_attn<__nv_bfloat16>(const AttnArgs&, int, cudaStream_t);
 template int launch_attn<__half>(const AttnArgs&, int, cudaStream_t);
 
 // =================================================================================================
+// One-token attention, streaming form (q_len == 1 for every sequence): HF falcon:349-362 / gpt_neox:224-238 / llama / bloom with
+// one query row.  HBM-bound: each step re-reads the K and V rows of every sequence.  One warp per (sequence, head), four heads
+// per CTA (with grouped-query heads they share a KV head and its rows come from L1 after the first warp).  LPK lanes share a
+// key (16-byte slices of its K row and of its V row: 8 lanes for head_dim 64, 16 for 80 / 128), the 32 / LPK lane groups walk
+// the keys in interleaved streams with an online softmax each and are merged with shuffles at the end; no shared memory, no
+// barrier.  The varlen kernel above, which stages the whole K and V of a sequence in shared memory as fp32 before one warp per
+// head uses them, took 10x longer on these steps (profiles/r2_t5_launches_before.summary.txt: 472 us vs 47 us per layer).
+// =================================================================================================
+template <typename AT, int HD>
+__global__ void __launch_bounds__(128)
+attn_step_kernel(AttnArgs a) {
+  constexpr int LPK = HD == 64 ? 8 : 16;       // lanes per key
+  constexpr int NG = 32 / LPK;                 // key streams per warp
+  constexpr int NSUB = HD / 8;                 // lanes of a group that hold data (10 of 16 for head_dim 80)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = blockIdx.x * 4 + warp, seq = blockIdx.y;
+  if (h >= a.nh) return;
+  const int sub = lane % LPK, grp = lane / LPK;
+  const bool live = sub < NSUB;
+  const int L = a.meta.kv_len[seq];
+  const size_t row = static_cast<size_t>(a.meta.q_start[seq]);
+  const size_t pitch = a.kv_stride ? static_cast<size_t>(a.kv_stride) : static_cast<size_t>(a.nkv) * HD;
+  const size_t kv_off = static_cast<size_t>(a.meta.kv_start[seq]) * pitch + static_cast<size_t>(h / a.rep) * HD + 8 * (live ? sub : 0);
+  const AT* kbase = reinterpret_cast<const AT*>(a.kcache) + kv_off;
+  const AT* vbase = reinterpret_cast<const AT*>(a.vcache) + kv_off;
+  float q[8];
+  load8(reinterpret_cast<const AT*>(a.qkv) + row * a.qkv_dim + a.q_base + h * a.q_hstride + 8 * (live ? sub : 0), q);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) q[i] = live ? q[i] * a.scale : 0.f;
+  const float slope = a.alibi ? a.alibi[h] : 0.f;
+  float m = -INFINITY, l = 0.f;
+  float o[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] = 0.f;
+  for (int j0 = 0; j0 < L; j0 += 2 * NG) {
+    float k[2][8], v[2][8], d[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int j = j0 + NG * u + grp;
+      if (j < L) {
+        load8(kbase + static_cast<size_t>(j) * pitch, k[u]);
+        load8(vbase + static_cast<size_t>(j) * pitch, v[u]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { k[u][i] = 0.f; v[u][i] = 0.f; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t = fmaf(q[i], k[u][i], t);      // (q is zero on the idle lanes of a head_dim-80 group)
+#pragma unroll
+      for (int s = 1; s < LPK; s <<= 1) t += __shfl_xor_sync(0xffffffffu, t, s);
+      const int j = j0 + NG * u + grp;
+      t += slope * static_cast<float>(j);                           // HF bloom: alibi = slope[head] * key position
+      d[u] = j < L ? t : -INFINITY;
+    }
+    const float mn = fmaxf(m, fmaxf(d[0], d[1]));
+    if (mn > -INFINITY) {
+      const float corr = __expf(m - mn), p0 = __expf(d[0] - mn), p1 = __expf(d[1] - mn);
+      l = fmaf(l, corr, p0 + p1);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = fmaf(o[i], corr, fmaf(p0, v[0][i], p1 * v[1][i]));
+      m = mn;
+    }
+  }
+  float mall = m;
+#pragma unroll
+  for (int s = LPK; s < 32; s <<= 1) mall = fmaxf(mall, __shfl_xor_sync(0xffffffffu, mall, s));
+  const float w = m > -INFINITY ? __expf(m - mall) : 0.f;
+  l *= w;
+#pragma unroll
+  for (int s = LPK; s < 32; s <<= 1) l += __shfl_xor_sync(0xffffffffu, l, s);
+  const float inv = 1.f / l;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    o[i] *= w;
+#pragma unroll
+    for (int s = LPK; s < 32; s <<= 1) o[i] += __shfl_xor_sync(0xffffffffu, o[i], s);
+    o[i] *= inv;
+  }
+  if (grp == 0 && live) {
+    const size_t owidth = static_cast<size_t>(a.nh) * HD;
+    const size_t col = static_cast<size_t>(h) * HD + 8 * sub;
+    if (a.split) {
+      __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(a.out) + row * (2 * owidth) + col;
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 hv = __floats2bfloat162_rn(o[2 * i], o[2 * i + 1]);
+        const __nv_bfloat162 lv = __floats2bfloat162_rn(o[2 * i] - __low2float(hv), o[2 * i + 1] - __high2float(hv));
+        hi[i] = *reinterpret_cast<const uint32_t*>(&hv);
+        lo[i] = *reinterpret_cast<const uint32_t*>(&lv);
+      }
+      *reinterpret_cast<uint4*>(ob) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<uint4*>(ob + owidth) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    } else {
+      AT* op = reinterpret_cast<AT*>(a.out) + row * owidth + col;
+      if constexpr (std::is_same<AT, float>::value) {
+        *reinterpret_cast<float4*>(op) = make_float4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<float4*>(op + 4) = make_float4(o[4], o[5], o[6], o[7]);
+      } else if constexpr (std::is_same<AT, __half>::value) {
+        *reinterpret_cast<uint4*>(op) = make_uint4(pack_f16x2(o[0], o[1]), pack_f16x2(o[2], o[3]), pack_f16x2(o[4], o[5]), pack_f16x2(o[6], o[7]));
+      } else {
+        *reinterpret_cast<uint4*>(op) = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+      }
+    }
+  }
+}
+
+template <typename AT>
+int launch_attn_step(const AttnArgs& a, int n_seqs, cudaStream_t st) {
+  B2S_REQUIRE(a.relbias == nullptr && !a.noncausal, "attn_step: the relative-bias / non-causal forms belong to the varlen kernel");
+  B2S_REQUIRE(a.q_base % 8 == 0 && a.q_hstride % 8 == 0 && a.qkv_dim % 8 == 0, "attn_step: query heads must start at 16-byte boundaries");
+  dim3 grid(static_cast<unsigned>(ceil_div(a.nh, 4)), static_cast<unsigned>(n_seqs));
+  switch (a.hd) {
+    case 64: attn_step_kernel<AT, 64><<<grid, 128, 0, st>>>(a); break;
+    case 80: attn_step_kernel<AT, 80><<<grid, 128, 0, st>>>(a); break;
+    case 128: attn_step_kernel<AT, 128><<<grid, 128, 0, st>>>(a); break;
+    default: set_error("attn_step: unsupported head_dim %d (64, 80, 128)", a.hd); return B2S_EUNSUPPORTED;
+  }
+  B2S_CHECK_LAUNCH();
+  return B2S_OK;
+}
+template int launch_attn_step<float>(const AttnArgs&, int, cudaStream_t);
+template int launch_attn_step<__nv_bfloat16>(const AttnArgs&, int, cudaStream_t);
+template int launch_attn_step<__half>(const AttnArgs&, int, cudaStream_t);
+
+// =================================================================================================
 // LM head: reduce full fp32 logits to per-tile partials (FP32_CHECK mode; the bf16 path produces the
 // same partial records inside the GEMM epilogue), merge partials per row, then advance the look-ahead
 // scan state.

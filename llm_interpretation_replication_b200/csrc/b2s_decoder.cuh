@@ -84,6 +84,9 @@ int launch_prep(const int32_t* cu, int n_rows, int lookahead, int step, const in
 template <typename AT, typename WT> int launch_ln(const LnArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st);
 template <typename AT> int launch_attn(const AttnArgs& a, int n_seqs, cudaStream_t st);
+// One-token steps (every sequence has q_len 1) for the shapes the tensor-core one-token kernel does not take (head_dim 80 /
+// 128, ALiBi, the fp32 mode): HBM-bound streaming kernel, one warp per (sequence, head).
+template <typename AT> int launch_attn_step(const AttnArgs& a, int n_seqs, cudaStream_t st);
 // act[r, j] = silu(gu[r, j]) * gu[r, ff + j]   (HF llama LlamaMLP: act_fn(gate_proj(x)) * up_proj(x))
 // gate_kind B2S_ACT_GELU_TANH: tanh-GELU gate instead of SiLU (HF t5 T5DenseGatedActDense: act(wi_0(x)) * wi_1(x))
 template <typename AT> int launch_swiglu(const void* gu, void* act, int64_t rows, int ff, cudaStream_t st, int gate_kind = 0);

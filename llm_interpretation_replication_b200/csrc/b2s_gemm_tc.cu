@@ -1358,6 +1358,10 @@ int b2s_set_option(const char* name, int32_t value) {
     b2s::g_opt_compact = value ? 1 : 0;
     return B2S_OK;
   }
+  if (std::string(name) == "attn_step") {
+    b2s::g_opt_attn_step = value ? 1 : 0;
+    return B2S_OK;
+  }
   if (std::string(name) == "int8_threshold_milli") {
     B2S_REQUIRE(value >= 0, "set_option: int8_threshold_milli must be >= 0");
     b2s::g_opt_int8_threshold = value / 1000.0f;

@@ -15,6 +15,7 @@ namespace b2s {
 thread_local std::string g_last_error;
 std::atomic<int64_t> g_launch_count{0};
 int g_opt_compact = 1;   // b2s_set_option "lookahead_compact": one-token steps run only the prompts that still need a position
+int g_opt_attn_step = 1;   // b2s_set_option "attn_step": streaming one-token attention (0 = the varlen kernel, for A/B and parity checks)
 float g_opt_int8_threshold = 6.0f;   // b2s_set_option "int8_threshold_milli": bitsandbytes' llm_int8_threshold (default 6.0)
 
 void set_error(const char* fmt, ...) {
@@ -211,10 +212,15 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     at.scale = 1.0f / sqrtf(static_cast<float>(d.head_dim));
     // tensor-core kernel when the shape allows it (head_dim 64, <= 256 keys), CUDA-core kernel otherwise
     // (ALiBi: prompt pass only -- the one-token tensor-core kernel has no bias term)
+    // (the one-token tensor-core kernel makes a tile out of the query heads that share a KV head: worth it for multi-query
+    // models -- 71 rows for Falcon -- not for 1..4 heads per KV head, which stream better)
     const bool tc_ok = m->bf16 && (at.alibi == nullptr || max_qlen > 1) && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
-                                                : attn_tc_decode_supported(d.head_dim, max_kv, m->qkv_dim, m->q_base, m->q_hstride));
+                                                : (attn_tc_decode_supported(d.head_dim, max_kv, m->qkv_dim, m->q_base, m->q_hstride) &&
+                                                   (at.rep >= 8 || !g_opt_attn_step)));
     if (tc_ok) {
       B2S_TRY(launch_attn_tc(at, n_seqs, rows, static_cast<int>(w.cache_slots), max_qlen, st));
+    } else if (max_qlen == 1 && g_opt_attn_step) {    // one-token steps of head_dim 80 / 128, ALiBi models, the fp32 mode
+      B2S_TRY(launch_attn_step<QT>(at, n_seqs, st));
     } else {
       B2S_TRY(launch_attn<QT>(at, n_seqs, st));
     }
