@@ -328,7 +328,7 @@ int g_opt_attn_hold_s = 0;   // b2s_set_option("attn_hold_s")
 
 // The caller decides which kernel to use from attn_tc_supported(); there is no silent fallback here.
 // prompt pass: head_dim 64 or 128 (second-generation kernel; the first-generation one below knows 64 only), <= 256 keys
-bool attn_tc_supported(int hd, int max_kv) { return (hd == AT_HD || (hd == 128 && g_opt_attn_ts_on())) && max_kv <= AT_MAXKV; }
+bool attn_tc_supported(int hd, int max_kv) { return (hd == AT_HD || ((hd == 128 || hd == 80) && g_opt_attn_ts_on())) && max_kv <= AT_MAXKV; }
 // one-token steps additionally need contiguous 64-wide query heads (the qkv row is read as a [heads, 64] matrix)
 bool attn_tc_decode_supported(int hd, int max_kv, int qkv_dim, int q_base, int q_hstride) {
   return hd == AT_HD && max_kv <= AT_MAXKV && q_hstride == AT_HD && qkv_dim % AT_HD == 0 && q_base % AT_HD == 0;

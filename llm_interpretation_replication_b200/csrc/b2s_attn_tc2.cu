@@ -149,12 +149,36 @@ __device__ __forceinline__ void a2_store64(const float (&o0)[32], const float (&
   }
 }
 
+// the first 16 of a chunk's 32 columns (columns 64..79 of an 80-wide head)
+template <bool F16>
+__device__ __forceinline__ void a2_store16(const float (&o)[32], float inv, uint16_t* out_row, int lo_off) {
+  uint4* dst = reinterpret_cast<uint4*>(out_row);
+  if (lo_off) {
+    uint4* dlo = reinterpret_cast<uint4*>(out_row + lo_off);
+    auto rem = [inv](float x) { const float y = x * inv; return y - __bfloat162float(__float2bfloat16_rn(y)); };
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      dst[q] = make_uint4(pack_bf16x2(o[8 * q] * inv, o[8 * q + 1] * inv), pack_bf16x2(o[8 * q + 2] * inv, o[8 * q + 3] * inv),
+                          pack_bf16x2(o[8 * q + 4] * inv, o[8 * q + 5] * inv), pack_bf16x2(o[8 * q + 6] * inv, o[8 * q + 7] * inv));
+      dlo[q] = make_uint4(pack_bf16x2(rem(o[8 * q]), rem(o[8 * q + 1])), pack_bf16x2(rem(o[8 * q + 2]), rem(o[8 * q + 3])),
+                          pack_bf16x2(rem(o[8 * q + 4]), rem(o[8 * q + 5])), pack_bf16x2(rem(o[8 * q + 6]), rem(o[8 * q + 7])));
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      dst[q] = make_uint4(pack16x2<F16>(o[8 * q] * inv, o[8 * q + 1] * inv), pack16x2<F16>(o[8 * q + 2] * inv, o[8 * q + 3] * inv),
+                          pack16x2<F16>(o[8 * q + 4] * inv, o[8 * q + 5] * inv), pack16x2<F16>(o[8 * q + 6] * inv, o[8 * q + 7] * inv));
+  }
+}
+
 // One item for one thread (== tile row): wait for S, two passes over this row's S in tensor memory (max, then
 // exp / pack / store P over S), hand P to the issuer, wait for O, normalise and write HD outputs.
 // ALIBI: the score of key j is s_j * scale + slope * j (HF bloom build_alibi_tensor); `ab` = slope * log2(e).
 // TABLE: the score of key j is s_j * scale + tb[j] (HF t5 position_bias: `tb` points at this row's slice of the per-head bias
 // table laid out by key - query distance).
-template <bool F16, int HD = 64, bool ALIBI = false, bool TABLE = false>
+// HDR: the model's head dimension when it is staged in a wider layout (80 columns in the two 64-wide sub-tiles of HD = 128: the
+// upper 48 columns of Q, K and V are TMA zero fill and only 16 columns of the second O slice are stored).
+template <bool F16, int HD = 64, bool ALIBI = false, bool TABLE = false, int HDR = HD>
 __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_live, int n_full, int n_p, int kvp, int limit, float sc,
                                         uint32_t bar_s, uint32_t bar_p, uint32_t bar_o, uint32_t bar_e, uint32_t ph, bool valid,
                                         uint16_t* out_row, int lo_off = 0, float ab = 0.f, const float* tb = nullptr) {
@@ -249,11 +273,15 @@ __device__ __forceinline__ void a2_item(uint32_t t_lane, uint32_t o_off, int n_l
       tcgen05_fence_before();
       mbar_arrive(bar_e);                 // the lane's columns may be overwritten by the next S
     }
-    if (valid) a2_store64<F16>(o0, o1, inv, out_row + 64 * h, lo_off);
+    if (HDR == 80 && h == 1) {
+      if (valid) a2_store16<F16>(o0, inv, out_row + 64, lo_off);
+    } else if (valid) {
+      a2_store64<F16>(o0, o1, inv, out_row + 64 * h, lo_off);
+    }
   }
 }
 
-template <bool F16, int HD, bool ALIBI>
+template <bool F16, int HD, bool ALIBI, int HDR = HD>
 __global__ void __launch_bounds__(A2_THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const Attn2Params p) {
@@ -314,14 +342,23 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const uint32_t bq = bar_q(i % NQ);
         mbar_arrive_expect_tx(bq, Q_BYTES);
 #pragma unroll
-        for (int sb = 0; sb < NSUB; ++sb)
-          tma_load_2d(sQ + (i % NQ) * Q_BYTES + sb * A2_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i) * p.q_hstride + 64 * sb, q0);
+        for (int sb = 0; sb < NSUB; ++sb) {
+          if constexpr (HDR == 80)      // 3D map [rows][segments of 80][80]: the box's columns past 80 arrive as zeros
+            tma_load_3d(sQ + (i % NQ) * Q_BYTES + sb * A2_Q_BYTES, &tmQ, bq, 64 * sb, (p.q_base + (h_first + i) * p.q_hstride) / 80, q0);
+          else
+            tma_load_2d(sQ + (i % NQ) * Q_BYTES + sb * A2_Q_BYTES, &tmQ, bq, p.q_base + (h_first + i) * p.q_hstride + 64 * sb, q0);
+        }
       };
       mbar_arrive_expect_tx(bar_kv, 2 * KV_BYTES);
 #pragma unroll
       for (int sb = 0; sb < NSUB; ++sb) {
-        tma_load_2d(sK + sb * A2_KV_BYTES, &tmK, bar_kv, g * HD + 64 * sb, kv0);
-        tma_load_2d(sV + sb * A2_KV_BYTES, &tmV, bar_kv, g * HD + 64 * sb, kv0);
+        if constexpr (HDR == 80) {
+          tma_load_3d(sK + sb * A2_KV_BYTES, &tmK, bar_kv, 64 * sb, g, kv0);
+          tma_load_3d(sV + sb * A2_KV_BYTES, &tmV, bar_kv, 64 * sb, g, kv0);
+        } else {
+          tma_load_2d(sK + sb * A2_KV_BYTES, &tmK, bar_kv, g * HD + 64 * sb, kv0);
+          tma_load_2d(sV + sb * A2_KV_BYTES, &tmV, bar_kv, g * HD + 64 * sb, kv0);
+        }
       }
       for (int i = 0; i < NQ && i < n_items; ++i) load_q(i);
       a2_wait(bar_kv, 0);
@@ -391,11 +428,11 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const float sc = p.scale_log2e;
     for (int i = l; i < n_items; i += nl) {
       const uint32_t ph = static_cast<uint32_t>(i / nl) & 1u;
-      const size_t owidth = static_cast<size_t>(p.nh) * HD;
-      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (owidth << p.split) + static_cast<size_t>(h_first + i) * HD;
+      const size_t owidth = static_cast<size_t>(p.nh) * HDR;
+      uint16_t* dst = p.out + static_cast<size_t>(q0 + row) * (owidth << p.split) + static_cast<size_t>(h_first + i) * HDR;
       float ab = 0.f;
       if constexpr (ALIBI) ab = p.alibi[h_first + i] * 1.4426950408889634f;
-      a2_item<F16, HD, ALIBI>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst,
+      a2_item<F16, HD, ALIBI, false, HDR>(t_lane, o_off, n_live, n_full, n_p, kvp, limit, sc, bar_s(l), bar_p(l), bar_o(l), bar_e(l), ph, valid, dst,
                               p.split ? static_cast<int>(owidth) : 0, ab);
     }
   }
@@ -739,16 +776,24 @@ int launch_attn_dec2(const AttnArgs& a, int n_seqs, int total_rows, int cache_sl
 
 int g_opt_attn_ts = 1;   // b2s_set_option("attn_ts"): 1 = this kernel for the prompt pass, 0 = attn_tc_kernel
 
-template <bool F16, int HD, bool ALIBI>
+template <bool F16, int HD, bool ALIBI, int HDR = HD>
 static int launch_tc2_t(const AttnArgs& a, int n_seqs, int total_rows, int cache_slots, int max_qlen, cudaStream_t st) {
   // per-device function attribute, and cheap: set on every launch rather than once per process
-  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<F16, HD, ALIBI>, cudaFuncAttributeMaxDynamicSharedMemorySize, a2_smem<HD>()));
+  B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<F16, HD, ALIBI, HDR>, cudaFuncAttributeMaxDynamicSharedMemorySize, a2_smem<HD>()));
   CUtensorMap tq, tk, tv;      // boxes are 64 columns wide whatever the head dimension (one swizzle atom)
-  B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
-                            static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, 64, a.f16));
-  const uint64_t kvw = static_cast<uint64_t>(a.nkv) * HD;
-  B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, 64, a.f16));
-  B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, 64, a.f16));
+  const uint64_t kvw = static_cast<uint64_t>(a.nkv) * HDR;
+  if constexpr (HDR == 80) {
+    B2S_REQUIRE(a.qkv_dim % 80 == 0 && a.q_base % 80 == 0 && a.q_hstride % 80 == 0, "attn_tc2: 80-wide heads must start at multiples of 80");
+    B2S_TRY(make_tmap_16bit_3d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim / 80), 80,
+                               static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, 64, a.f16));
+    B2S_TRY(make_tmap_16bit_3d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), static_cast<uint64_t>(a.nkv), 80, kvw * 2, A2_MAXKV, 64, a.f16));
+    B2S_TRY(make_tmap_16bit_3d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), static_cast<uint64_t>(a.nkv), 80, kvw * 2, A2_MAXKV, 64, a.f16));
+  } else {
+    B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
+                              static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, 64, a.f16));
+    B2S_TRY(make_tmap_bf16_2d(&tk, a.kcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, 64, a.f16));
+    B2S_TRY(make_tmap_bf16_2d(&tv, a.vcache, static_cast<uint64_t>(cache_slots), kvw, kvw * 2, A2_MAXKV, 64, a.f16));
+  }
   Attn2Params p;
   p.meta = a.meta;
   p.out = reinterpret_cast<uint16_t*>(a.out);
@@ -758,7 +803,7 @@ static int launch_tc2_t(const AttnArgs& a, int n_seqs, int total_rows, int cache
   p.scale_log2e = a.scale * 1.4426950408889634f;
   p.alibi = a.alibi;
   dim3 grid(n_seqs, static_cast<unsigned>(ceil_div(max_qlen, A2_BM)), a.nkv);
-  attn_tc2_kernel<F16, HD, ALIBI><<<grid, A2_THREADS, a2_smem<HD>(), st>>>(tq, tk, tv, p);
+  attn_tc2_kernel<F16, HD, ALIBI, HDR><<<grid, A2_THREADS, a2_smem<HD>(), st>>>(tq, tk, tv, p);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
@@ -770,6 +815,11 @@ int launch_attn_tc2(const AttnArgs& a, int n_seqs, int total_rows, int cache_slo
   if (a.hd == 64) {
     if (a.alibi) { if (a.f16) B2S_TC2(true, 64, true); else B2S_TC2(false, 64, true); }
     if (a.f16) B2S_TC2(true, 64, false); else B2S_TC2(false, 64, false);
+  }
+  if (a.hd == 80) {      // staged as 128 with TMA zero fill (no ALiBi model has this head size)
+    B2S_REQUIRE(a.alibi == nullptr, "attn_tc2: head_dim 80 with ALiBi is not built");
+    if (a.f16) return launch_tc2_t<true, 128, false, 80>(a, n_seqs, total_rows, cache_slots, max_qlen, st);
+    return launch_tc2_t<false, 128, false, 80>(a, n_seqs, total_rows, cache_slots, max_qlen, st);
   }
   if (a.alibi) { if (a.f16) B2S_TC2(true, 128, true); else B2S_TC2(false, 128, true); }
   if (a.f16) B2S_TC2(true, 128, false); else B2S_TC2(false, 128, false);

@@ -1112,6 +1112,25 @@ int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t col
   return B2S_OK;
 }
 
+int make_tmap_16bit_3d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t segs, uint64_t seg_cols, uint64_t pitch_bytes,
+                       uint32_t box_rows, uint32_t box_cols, int f16) {
+  B2S_TRY(get_encode_fn());
+  cuuint64_t dims[3] = {seg_cols, segs, rows};
+  cuuint64_t strides[2] = {seg_cols * 2, pitch_bytes};
+  cuuint32_t box[3] = {box_cols, 1, box_rows};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims,
+                        strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (3D) failed with CUresult %d (rows=%llu segs=%llu seg_cols=%llu pitch=%llu base=%p)", static_cast<int>(r),
+              static_cast<unsigned long long>(rows), static_cast<unsigned long long>(segs), static_cast<unsigned long long>(seg_cols),
+              static_cast<unsigned long long>(pitch_bytes), base);
+    return B2S_ECUDA;
+  }
+  return B2S_OK;
+}
+
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
                       uint32_t box_rows, uint32_t box_cols, int f16) {
   return make_tmap_2d(map, base, rows, cols, pitch_bytes, box_rows, box_cols, 2, f16);

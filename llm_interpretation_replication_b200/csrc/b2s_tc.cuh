@@ -68,6 +68,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap
       ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar,
+                                            int32_t c0, int32_t c1, int32_t c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
@@ -136,6 +143,12 @@ __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.p
 // out-of-bounds elements read as zero.
 int make_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,
                       uint32_t box_rows, uint32_t box_cols, int f16 = 0);
+
+// 3D 16-bit tensor [rows][segs][seg_cols] (segments seg_cols elements apart, rows pitch_bytes apart); box = [box_rows][1][box_cols];
+// 128B swizzle.  A box that reaches past seg_cols is zero-filled there: this is how a head of 80 columns is staged as two
+// 64-wide sub-tiles (the second one = columns 64..79 and 48 zeros).  Not memoised (one encode per call).
+int make_tmap_16bit_3d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t segs, uint64_t seg_cols, uint64_t pitch_bytes,
+                       uint32_t box_rows, uint32_t box_cols, int f16);
 
 // general form: esize 2 (bf16, or fp16 when f16) or 4 (fp32)
 int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t pitch_bytes,

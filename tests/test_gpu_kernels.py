@@ -244,14 +244,15 @@ def test_attention_bf16(use_tc, nh, nkv, phase):
         assert err <= (3e-2 if use_tc else 1.5e-2), (use_tc, ql, err)     # bf16 output (+ bf16 P on the tensor-core path)
 
 
-@pytest.mark.parametrize("nh,nkv,interleaved", [(4, 2, False), (3, 3, True), (8, 1, False), (6, 6, False)])
-def test_attention_tc_head_dim_128(nh, nkv, interleaved):
+@pytest.mark.parametrize("nh,nkv,interleaved,hd", [(4, 2, False, 128), (3, 3, True, 128), (8, 1, False, 128), (6, 6, False, 128),
+                                                   (5, 5, True, 80), (4, 4, False, 80), (6, 2, False, 80)])
+def test_attention_tc_head_dim_128(nh, nkv, interleaved, hd):
     """Prompt pass on the tensor cores at head_dim 128 (StableLM-alpha / RedPajama-7B / Mistral / BLOOM shapes): K, V and Q
     staged as two 64-wide sub-tiles, grouped-query and per-head [q, k, v] interleaved query layouts, ragged lengths up to
-    256 keys with cached keys in front of some prompts."""
+    256 keys with cached keys in front of some prompts.  head_dim 80 (RedPajama-3B) rides the same kernel: a 3D tensor map
+    zero-fills columns 80..127 of every Q, K and V box and only 16 columns of the second output slice are stored."""
     from llm_interpretation_replication_b200 import _lib
     lib = _lib.load()
-    hd = 128
     qlens = [1, 2, 17, 64, 127, 128, 129, 190, 256, 33, 100, 192, 193]
     extra = [0, 0, 3, 0, 0, 0, 0, 10, 0, 64, 28, 0, 0]
     q_start, kv_start, t, c = [], [], 0, 0
