@@ -373,8 +373,62 @@ rope_cache_kernel(RopeArgs a) {
   }
 }
 
+// The same, eight elements (16 bytes of a 16-bit type) at a time: a work item is one 8-wide slice of a rotated pair
+// (x[i..i+8), x[i+half..i+half+8)) of a query or key head, of a key head's unrotated tail, or of a value head.  The scalar
+// kernel above (2-byte accesses, a division per element) ran at a quarter of the HBM rate: 6 % of a Llama-2-7B pass
+// (profiles/r2_llama_launches.summary.txt).  Needs rotary_dim / 2, head_dim and every head offset to be multiples of 8.
+template <typename AT>
+__global__ void __launch_bounds__(256)
+rope_cache_vec_kernel(RopeArgs a) {
+  const int t = blockIdx.x;
+  const int pos = a.pos[t];
+  const size_t slot = static_cast<size_t>(a.slot[t]);
+  AT* row = reinterpret_cast<AT*>(a.qkv) + static_cast<size_t>(t) * a.qkv_dim;
+  const int hd = a.hd, half = a.rd / 2;
+  const int hv = half / 8, tv = (hd - a.rd) / 8, dv = hd / 8;      // 8-wide slices per head: rotated pairs, tail, whole head
+  const float* cs = a.cos + static_cast<size_t>(pos) * half;
+  const float* sn = a.sin + static_cast<size_t>(pos) * half;
+  AT* kc = reinterpret_cast<AT*>(a.kcache) + slot * (a.nkv * hd);
+  AT* vc = reinterpret_cast<AT*>(a.vcache) + slot * (a.nkv * hd);
+  const int nq = a.nh * hv, nk = a.nkv * hv, nkt = a.nkv * tv, nv = a.nkv * dv;
+  for (int w = threadIdx.x; w < nq + nk + nkt + nv; w += blockDim.x) {
+    if (w < nq + nk) {                       // a rotated pair of a query head (in place) or of a key head (into the cache)
+      const bool is_q = w < nq;
+      const int u = is_q ? w : w - nq;
+      const int h = u / hv, i = (u - h * hv) * 8;
+      const AT* src = row + (is_q ? a.q_base + h * a.q_hstride : a.k_base + h * a.kv_hstride);
+      AT* dst = is_q ? row + a.q_base + h * a.q_hstride : kc + h * hd;
+      float x1[8], x2[8], c[8], s[8], o1[8], o2[8];
+      load8(src + i, x1); load8(src + i + half, x2);
+      load8(cs + i, c); load8(sn + i, s);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { o1[e] = x1[e] * c[e] - x2[e] * s[e]; o2[e] = x2[e] * c[e] + x1[e] * s[e]; }
+      store8(dst + i, o1); store8(dst + i + half, o2);
+    } else if (w < nq + nk + nkt) {          // unrotated tail of a key head (partial rotary)
+      const int u = w - nq - nk;
+      const int h = u / tv, i = a.rd + (u - h * tv) * 8;
+      float x[8];
+      load8(row + a.k_base + h * a.kv_hstride + i, x);
+      store8(kc + h * hd + i, x);
+    } else {                                 // value head
+      const int u = w - nq - nk - nkt;
+      const int h = u / dv, i = (u - h * dv) * 8;
+      float x[8];
+      load8(row + a.v_base + h * a.kv_hstride + i, x);
+      store8(vc + h * hd + i, x);
+    }
+  }
+}
+
 template <typename AT>
 int launch_rope_cache(const RopeArgs& a, int n_rows, cudaStream_t st) {
+  const bool vec = a.rd > 0 && (a.rd / 2) % 8 == 0 && a.hd % 8 == 0 && a.rd % 8 == 0 && a.qkv_dim % 8 == 0 && a.q_base % 8 == 0 &&
+                   a.q_hstride % 8 == 0 && a.k_base % 8 == 0 && a.v_base % 8 == 0 && a.kv_hstride % 8 == 0;
+  if (vec) {
+    rope_cache_vec_kernel<AT><<<n_rows, 256, 0, st>>>(a);
+    B2S_CHECK_LAUNCH();
+    return B2S_OK;
+  }
   rope_cache_kernel<AT><<<n_rows, 256, 0, st>>>(a);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
@@ -587,10 +641,11 @@ attn_step_kernel(AttnArgs a) {
   float o[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) o[i] = 0.f;
-  for (int j0 = 0; j0 < L; j0 += 2 * NG) {
-    float k[2][8], v[2][8], d[2];
+  constexpr int U = 2;      // keys in flight per lane group (4 for the wide heads: 109 registers, fewer warps, 188 -> 283 us per Llama-7B launch)
+  for (int j0 = 0; j0 < L; j0 += U * NG) {
+    float k[U][8], v[U][8], d[U];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) {
       const int j = j0 + NG * u + grp;
       if (j < L) {
         load8(kbase + static_cast<size_t>(j) * pitch, k[u]);
@@ -600,8 +655,9 @@ attn_step_kernel(AttnArgs a) {
         for (int i = 0; i < 8; ++i) { k[u][i] = 0.f; v[u][i] = 0.f; }
       }
     }
+    float dmax = -INFINITY;
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) {
       float t = 0.f;
 #pragma unroll
       for (int i = 0; i < 8; ++i) t = fmaf(q[i], k[u][i], t);      // (q is zero on the idle lanes of a head_dim-80 group)
@@ -610,13 +666,22 @@ attn_step_kernel(AttnArgs a) {
       const int j = j0 + NG * u + grp;
       t += slope * static_cast<float>(j);                           // HF bloom: alibi = slope[head] * key position
       d[u] = j < L ? t : -INFINITY;
+      dmax = fmaxf(dmax, d[u]);
     }
-    const float mn = fmaxf(m, fmaxf(d[0], d[1]));
+    const float mn = fmaxf(m, dmax);
     if (mn > -INFINITY) {
-      const float corr = __expf(m - mn), p0 = __expf(d[0] - mn), p1 = __expf(d[1] - mn);
-      l = fmaf(l, corr, p0 + p1);
+      const float corr = __expf(m - mn);
+      float psum = 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) o[i] = fmaf(o[i], corr, fmaf(p0, v[0][i], p1 * v[1][i]));
+      for (int i = 0; i < 8; ++i) o[i] *= corr;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float pu = __expf(d[u] - mn);
+        psum += pu;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = fmaf(pu, v[u][i], o[i]);
+      }
+      l = fmaf(l, corr, psum);
       m = mn;
     }
   }
