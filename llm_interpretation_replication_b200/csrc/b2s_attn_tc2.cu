@@ -473,8 +473,8 @@ __global__ void __launch_bounds__(A2_THREADS, 1)
 attn_enc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnEncParams p) {
   constexpr int NS = enc_stages<KVBOX>();
   constexpr uint32_t STAGE = enc_stage_bytes<KVBOX>(), KV_BYTES = KVBOX * A2_HD * 2;
-  const int seq = blockIdx.x, mt = blockIdx.y;
-  const int kl = p.meta.q_len[seq];
+  const int mt = blockIdx.x, seq = blockIdx.y;      // query tiles of a prompt are neighbours in launch order: the second one
+  const int kl = p.meta.q_len[seq];                 // finds the prompt's K and V in L2
   if (mt * A2_BM >= kl) return;
   const int row0 = p.meta.q_start[seq];
   const int q0 = row0 + mt * A2_BM;
@@ -526,10 +526,17 @@ attn_enc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           // the stage is free once P.V of the item that used it last has completed (S before it, in issue order)
           const int l = il % NS;
           if (il < NS || a2_test(bar_o(l), static_cast<uint32_t>((il / NS) - 1) & 1u)) {
-            mbar_arrive_expect_tx(bar_f(l), STAGE);
-            tma_load_2d(sQ(l), &tmQ, bar_f(l), il * A2_HD, q0);
-            tma_load_2d(sK(l), &tmKV, bar_f(l), p.inner + il * A2_HD, row0);
-            tma_load_2d(sV(l), &tmKV, bar_f(l), 2 * p.inner + il * A2_HD, row0);
+            // 64-row boxes (8 KB, one after the other: the layout of a single tall box), only as many as hold rows of this
+            // prompt: a 170-token prompt moves 192 key rows and, for its second query tile, 64 query rows instead of 256 / 128.
+            // Rows of a stage that are not loaded keep older finite data: keys past kvp are not multiplied, P is zero
+            // for keys past kl, and query rows past rows_here are never stored.
+            const uint32_t nqb = static_cast<uint32_t>((rows_here + 63) >> 6), nkb = static_cast<uint32_t>((kl + 63) >> 6);
+            mbar_arrive_expect_tx(bar_f(l), (nqb + 2 * nkb) * 8192u);
+            for (uint32_t b = 0; b < nqb; ++b) tma_load_2d(sQ(l) + b * 8192u, &tmQ, bar_f(l), il * A2_HD, q0 + 64 * b);
+            for (uint32_t b = 0; b < nkb; ++b) {
+              tma_load_2d(sK(l) + b * 8192u, &tmKV, bar_f(l), p.inner + il * A2_HD, row0 + 64 * b);
+              tma_load_2d(sV(l) + b * 8192u, &tmKV, bar_f(l), 2 * p.inner + il * A2_HD, row0 + 64 * b);
+            }
             ++il; did = true;
           }
         }
@@ -597,11 +604,10 @@ attn_enc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 template <bool F16, int KVBOX>
 static int launch_enc_t(const AttnArgs& a, int n_seqs, int total_rows, int max_qlen, cudaStream_t st) {
   B2S_CHECK_CUDA(cudaFuncSetAttribute(attn_enc_kernel<F16, KVBOX>, cudaFuncAttributeMaxDynamicSharedMemorySize, enc_smem<KVBOX>()));
-  CUtensorMap tq, tkv;      // the same buffer twice: 128-row boxes for Q, KVBOX-row boxes for K and V
+  CUtensorMap tq, tkv;      // one map over the projection output, 64 x 64 boxes, used for Q, K and V
   B2S_TRY(make_tmap_bf16_2d(&tq, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
-                            static_cast<uint64_t>(a.qkv_dim) * 2, A2_BM, 64, a.f16));
-  B2S_TRY(make_tmap_bf16_2d(&tkv, a.qkv, static_cast<uint64_t>(total_rows), static_cast<uint64_t>(a.qkv_dim),
-                            static_cast<uint64_t>(a.qkv_dim) * 2, KVBOX, 64, a.f16));
+                            static_cast<uint64_t>(a.qkv_dim) * 2, 64, 64, a.f16));
+  tkv = tq;
   AttnEncParams p;
   p.meta = a.meta;
   p.out = reinterpret_cast<uint16_t*>(a.out);
@@ -609,7 +615,7 @@ static int launch_enc_t(const AttnArgs& a, int n_seqs, int total_rows, int max_q
   p.nh = a.nh; p.inner = a.nh * A2_HD;
   p.scale_log2e = a.scale * 1.4426950408889634f;
   p.table = a.relbias; p.R = a.rel_R;
-  dim3 grid(n_seqs, static_cast<unsigned>(ceil_div(max_qlen, A2_BM)));
+  dim3 grid(static_cast<unsigned>(ceil_div(max_qlen, A2_BM)), n_seqs);
   attn_enc_kernel<F16, KVBOX><<<grid, A2_THREADS, enc_smem<KVBOX>(), st>>>(tq, tkv, p);
   B2S_CHECK_LAUNCH();
   return B2S_OK;

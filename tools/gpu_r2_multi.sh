@@ -9,7 +9,7 @@ run() { name=$1; shift; timeout ${TMO:-900} "$@" > gpurun_out/$name.log 2>&1; ec
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 run m_twodev      python -m pytest tests/test_gpu_scorer.py -q -k "two_devices" -rs
 run m_bench       $TR --master-port 29551 bench.py --gpus $N --steps 2 --warmup 1
-MODELS="tiiuae/falcon-7b-instruct togethercomputer/RedPajama-INCITE-7B-Instruct"
+MODELS="tiiuae/falcon-7b-instruct togethercomputer/RedPajama-INCITE-7B-Instruct bigscience/T0_3B Qwen/Qwen-7B-Chat"
 run m_c4_sharded  $TR --master-port 29553 -m llm_interpretation_replication_b200.entrypoints.compare_instruct_models --layers 2 --questions 24 --models $MODELS --out gpurun_out/c4_n$N
 run m_c4_single   python -m llm_interpretation_replication_b200.entrypoints.compare_instruct_models --layers 2 --questions 24 --models $MODELS --out gpurun_out/c4_n1
 run m_p_sharded   $TR --master-port 29554 -m llm_interpretation_replication_b200.entrypoints.score_perturbations --layers 2 --limit 300 --out gpurun_out/pert_n$N
