@@ -60,13 +60,15 @@ def model_seed(model_name: str) -> int:
     return zlib.crc32(model_name.encode()) & 0x7FFFFFFF
 
 
-def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_tokens: int = 65536,
+def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_tokens=None,
                max_seqs: int = 1024):
     """AutoTokenizer/AutoModelForCausalLM.from_pretrained of the reference (:416-450).  A checkpoint that is on disk
     (``model_name`` is a directory, or ``$B2S_CHECKPOINT_ROOT/<model_name>`` exists; see ``checkpoint.py``) is loaded
     with its own tokenizer.  Otherwise (no hub access here) the stand-in is the shape of the named hub model with
     random-init weights seeded by the name and the offline tokenizer.  Raises KeyError for architectures outside the
     supported families, which the callers turn into NaN rows as the reference does for models that fail to load.
+    ``max_tokens`` None = the batch is sized from the device memory that is free once the weights are resident
+    (``scorer.fit_batch``: a multi-head 7B model needs 0.5 MB of KV cache per prompt token, Falcon 8 KB).
     ``mode`` None = FP16 for the decoder-only families, BF16_SPLIT for the T5 family (whose feed-forward activations are
     the known case of values beyond fp16's range; see ``t5.EncDecScorer``)."""
     from .. import checkpoint
@@ -117,7 +119,7 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
         tok = HashTokenizer(shp.vocab, eos_token_id=shp.eos_id).apply_pad_default()
     if getattr(shp, "is_encoder_decoder", False):
         # the cross-attention K/V of every decoder layer stay resident per call: the token budget is capped (t5.EncDecScorer)
-        scorer = t5.EncDecScorer(shp, W, mode=mode, device=device, max_tokens=min(max_tokens, 131072), max_seqs=min(max_seqs, 2048),
+        scorer = t5.EncDecScorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs,
                                  max_lookahead=max(MAX_LOOK_AHEAD, COMPLETION_TOKENS))
         return scorer, tok
     scorer = Scorer(shp, W, mode=mode, device=device, max_tokens=max_tokens, max_seqs=max_seqs,

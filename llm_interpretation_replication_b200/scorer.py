@@ -93,12 +93,31 @@ def plan_batches(lengths: Sequence[int], max_tokens: int, max_seqs: int) -> List
     return best
 
 
+def fit_batch(workspace_bytes_fn, free_bytes: int, max_lookahead: int, fraction: float = 0.6, cap_tokens: int = 262144):
+    """Largest (max_tokens, max_seqs) whose workspace fits into ``fraction`` of the free device memory: the KV cache of a
+    multi-head 7B model is 0.5 MB per prompt token (32 layers x 2 x 4096 x 2 B), the cross-attention K/V of a T5-XL 0.2 MB, a
+    multi-query Falcon's 8 KB -- one fixed token budget cannot suit all of them.  ``workspace_bytes_fn(tokens, seqs, lookahead)``
+    is the library's own size query (b2s_workspace_bytes / b2s_encdec_workspace_bytes)."""
+    budget = int(free_bytes * fraction)
+    lo, hi = 2048, cap_tokens
+    seqs = lambda t: max(64, t // 48)
+    if workspace_bytes_fn(lo, seqs(lo), max_lookahead) > budget:
+        raise _lib.B2SError(f"not enough free device memory for a 2048-token batch ({free_bytes >> 20} MiB free)")
+    while lo < hi:
+        mid = (lo + hi + 1) // 2
+        if workspace_bytes_fn(mid, seqs(mid), max_lookahead) <= budget:
+            lo = mid
+        else:
+            hi = mid - 1
+    return lo, seqs(lo)
+
+
 class Scorer:
     """One decoder resident on one GPU (the reference keeps one model resident at a time too,
-    run_base_vs_instruct_100q.py:498-505)."""
+    run_base_vs_instruct_100q.py:498-505).  ``max_tokens=None`` sizes the batch from the free device memory (:func:`fit_batch`)."""
 
     def __init__(self, shape: DecoderShape, weights_dev: Dict[str, torch.Tensor], mode: int = MODE_BF16_FAST,
-                 device: Optional[torch.device] = None, max_tokens: int = 65536, max_seqs: int = 1024,
+                 device: Optional[torch.device] = None, max_tokens: Optional[int] = 65536, max_seqs: int = 1024,
                  max_lookahead: int = MAX_LOOK_AHEAD):
         if not torch.cuda.is_available():
             raise _lib.B2SError("no CUDA device: the B200 scorer has no CPU fallback")
@@ -106,7 +125,7 @@ class Scorer:
         self.shape = shape
         self.mode = mode
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
-        self.max_tokens, self.max_seqs, self.max_lookahead = int(max_tokens), int(max_seqs), int(max_lookahead)
+        self.max_tokens, self.max_seqs, self.max_lookahead = max_tokens, int(max_seqs), int(max_lookahead)
         want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16, MODE_INT8_EMU: torch.float16}.get(mode, torch.bfloat16)
         W = dict(weights_dev)
         if mode == MODE_INT8_EMU:
@@ -147,6 +166,12 @@ class Scorer:
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2s_model_create(C.byref(d), self._ptrs, len(self._ptrs), self.device.index or 0,
                                                  C.byref(self._handle)), "b2s_model_create")
+        if self.max_tokens is None:      # batch sized from what is free on the device once the weights are resident
+            torch.cuda.empty_cache()     # (cached blocks of a model that was just unloaded count as used otherwise)
+            free, _ = torch.cuda.mem_get_info(self.device)
+            self.max_tokens, self.max_seqs = fit_batch(lambda t, s, g: self.lib.b2s_workspace_bytes(self._handle, t, s, g), free,
+                                                       self.max_lookahead)
+        self.max_tokens = int(self.max_tokens)
         nbytes = self.lib.b2s_workspace_bytes(self._handle, self.max_tokens, self.max_seqs, self.max_lookahead)
         if nbytes == 0:
             raise _lib.B2SError("b2s_workspace_bytes returned 0")
@@ -157,6 +182,11 @@ class Scorer:
         if getattr(self, "_handle", None) is not None and self._handle:
             self.lib.b2s_model_destroy(self._handle)
             self._handle = None
+        # drop the device memory this object keeps alive, so that it can be returned to the driver even while a caller
+        # still holds the (closed) scorer
+        self.workspace = None
+        self.W = None
+        self._ptrs = None
 
     def __del__(self):
         try:

@@ -24,7 +24,7 @@ import torch
 
 from . import _lib
 from .shapes import MODE_BF16_FAST, MODE_BF16_SPLIT, MODE_FP16, MODE_FP32_CHECK
-from .scorer import Scorer, MAX_LOOK_AHEAD
+from .scorer import Scorer, MAX_LOOK_AHEAD, fit_batch
 
 FF_RELU, FF_GATED_GELU, FF_GATED_GELU_FUSED = 0, 1, 2   # must match B2S_T5_FF_* in include/b200score.h
 N_GLOBAL, N_PER_ENC, N_PER_DEC = 8, 8, 12
@@ -216,7 +216,7 @@ class EncDecScorer(Scorer):
     is_encoder_decoder = True
 
     def __init__(self, shape: EncDecShape, weights_dev: Dict[str, torch.Tensor], mode: int = MODE_BF16_SPLIT,
-                 device: Optional[torch.device] = None, max_tokens: int = 131072, max_seqs: int = 2048,
+                 device: Optional[torch.device] = None, max_tokens: Optional[int] = 131072, max_seqs: int = 2048,
                  max_lookahead: int = MAX_LOOK_AHEAD):
         if not torch.cuda.is_available():
             raise _lib.B2SError("no CUDA device: the B200 scorer has no CPU fallback")
@@ -224,7 +224,7 @@ class EncDecScorer(Scorer):
         self.shape = shape
         self.mode = mode
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
-        self.max_tokens, self.max_seqs, self.max_lookahead = int(max_tokens), int(max_seqs), int(max_lookahead)
+        self.max_tokens, self.max_seqs, self.max_lookahead = max_tokens, int(max_seqs), int(max_lookahead)
         want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
         W = dict(weights_dev)
         if mode == MODE_FP16:
@@ -256,6 +256,12 @@ class EncDecScorer(Scorer):
         with torch.cuda.device(self.device):
             _lib.check(self.lib.b2s_encdec_create(C.byref(d), self._ptrs, len(self._ptrs), self.device.index or 0,
                                                   C.byref(self._handle)), "b2s_encdec_create")
+        if self.max_tokens is None:
+            torch.cuda.empty_cache()
+            free, _ = torch.cuda.mem_get_info(self.device)
+            self.max_tokens, self.max_seqs = fit_batch(lambda t, s, g: self.lib.b2s_encdec_workspace_bytes(self._handle, t, s, g), free,
+                                                       self.max_lookahead, cap_tokens=131072)
+        self.max_tokens = int(self.max_tokens)
         nbytes = self.lib.b2s_encdec_workspace_bytes(self._handle, self.max_tokens, self.max_seqs, self.max_lookahead)
         if nbytes == 0:
             raise _lib.B2SError("b2s_encdec_workspace_bytes returned 0")
@@ -266,6 +272,9 @@ class EncDecScorer(Scorer):
         if getattr(self, "_handle", None) is not None and self._handle:
             self.lib.b2s_encdec_destroy(self._handle)
             self._handle = None
+        self.workspace = None
+        self.W = None
+        self._ptrs = None
 
     def score_batch_host(self, t_tok, t_cu, t_cand, topk, max_lookahead, eos_id, out, gen, gen_tokens=None):
         n = t_cu.numel() - 1

@@ -70,3 +70,18 @@ def _worker(rank, ws, port, n_total):
 
 def test_gather_rows_gloo_world2():
     mp.spawn(_worker, args=(2, 29611, 101), nprocs=2, join=True)
+
+
+def test_fit_batch_picks_the_largest_batch_that_fits():
+    """Host logic of the automatic batch sizing: binary search over the library's workspace-size query."""
+    from llm_interpretation_replication_b200.scorer import fit_batch
+    from llm_interpretation_replication_b200 import _lib
+    per_token, per_seq, fixed = 500_000, 40_000, 1 << 20           # a multi-head 7B model: 0.5 MB of KV cache per token
+    size = lambda t, s, g: fixed + per_token * t + per_seq * s * g
+    tokens, seqs = fit_batch(size, free_bytes=100 << 30, max_lookahead=10)
+    assert size(tokens, seqs, 10) <= 0.6 * (100 << 30) < size(tokens + 1, max(64, (tokens + 1) // 48), 10)
+    assert 100_000 < tokens < 140_000 and seqs == tokens // 48
+    tokens, seqs = fit_batch(lambda t, s, g: 8192 * t, free_bytes=150 << 30, max_lookahead=10)       # multi-query: the cap binds
+    assert tokens == 262144
+    with pytest.raises(_lib.B2SError):
+        fit_batch(size, free_bytes=1 << 30, max_lookahead=10)
