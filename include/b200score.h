@@ -273,7 +273,9 @@ B2S_API int b2s_gemm_f32(const float* A, const float* W, const float* bias, floa
  * head h at columns q_base + h*q_hstride; kcache/vcache bf16 [cache_slots, n_kv_head*head_dim]; sequence i has
  * q_len[i] query rows starting at q_start[i] and kv_len[i] keys starting at slot kv_start[i]; query j sees keys
  * [0, kv_len - q_len + j].  out bf16 [total_rows, n_head*head_dim].  use_tensor_cores != 0 selects the tcgen05
- * kernel (head_dim 64, <= 256 keys; cache slots past a sequence must hold finite values), 0 the CUDA-core one. */
+ * kernels (<= 256 keys; cache slots past a sequence must hold finite values; prompt pass: head_dim 64, 80 or 128;
+ * max_qlen == 1: head_dim 64 with contiguous 64-wide query heads), 0 the CUDA-core varlen kernel.  (Inside b2s_score the
+ * one-token steps of the other shapes run a third, streaming kernel: "attn_step" in b2s_set_option.) */
 B2S_API int b2s_attention_bf16(const void* qkv, const void* kcache, const void* vcache, void* out,
                        const int32_t* q_start, const int32_t* q_len, const int32_t* kv_start, const int32_t* kv_len,
                        int32_t n_seqs, int32_t total_rows, int32_t cache_slots, int32_t max_qlen, int32_t max_kv,
