@@ -611,8 +611,8 @@ template int launch_attn<__half>(const AttnArgs&, int, cudaStream_t);
 // one query row.  HBM-bound: each step re-reads the K and V rows of every sequence.  One warp per (sequence, head), four heads
 // per CTA (with grouped-query heads they share a KV head and its rows come from L1 after the first warp).  LPK lanes share a
 // key (16-byte slices of its K row and of its V row: 8 lanes for head_dim 64, 16 for 80 / 128), the 32 / LPK lane groups walk
-// the keys in interleaved streams with an online softmax each and are merged with shuffles at the end; no shared memory, no
-// barrier.  The varlen kernel above, which stages the whole K and V of a sequence in shared memory as fp32 before one warp per
+// the keys in interleaved streams with an online softmax each and are merged with shuffles at the end; the slices reach the
+// lanes through a cp.async ring in shared memory (three iterations in flight per warp), no barrier.  The varlen kernel above, which stages the whole K and V of a sequence in shared memory as fp32 before one warp per
 // head uses them, took 10x longer on these steps (profiles/r2_t5_launches_before.summary.txt: 472 us vs 47 us per layer).
 // =================================================================================================
 template <typename AT, int HD>
@@ -641,15 +641,49 @@ attn_step_kernel(AttnArgs a) {
   float o[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) o[i] = 0.f;
-  constexpr int U = 2;      // keys in flight per lane group (4 for the wide heads: 109 registers, fewer warps, 188 -> 283 us per Llama-7B launch)
-  for (int j0 = 0; j0 < L; j0 += U * NG) {
+  // K / V slices travel through a per-warp ring in shared memory (cp.async, 16 bytes per lane and key for K and for V): STG
+  // iterations of U keys per lane group are in flight while one is consumed -- 6 KB per warp instead of the 2 KB that fit in
+  // registers.  A lane copies exactly the slices it consumes itself, so the only synchronisation is its own wait_group.
+  constexpr int U = 2, STG = 3;
+  constexpr int VB = 8 * sizeof(AT);                       // bytes of one 8-element slice
+  extern __shared__ __align__(16) uint8_t ring_raw[];
+  uint8_t* ring = ring_raw + static_cast<size_t>(warp) * (STG * U * 2 * 32 * VB);
+  const uint32_t ring_s = static_cast<uint32_t>(__cvta_generic_to_shared(ring)) + static_cast<uint32_t>(lane) * VB;
+  const int n_iter = (L + U * NG - 1) / (U * NG);
+  auto issue = [&](int it) {
+    if (it < n_iter) {
+      const uint32_t dst = ring_s + static_cast<uint32_t>(it % STG) * (U * 2 * 32 * VB);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = it * (U * NG) + NG * u + grp;
+        if (j < L) {
+          const AT* kp = kbase + static_cast<size_t>(j) * pitch;
+          const AT* vp = vbase + static_cast<size_t>(j) * pitch;
+#pragma unroll
+          for (int c = 0; c < VB / 16; ++c) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (2 * u) * 32 * VB + 16 * c),
+                         "l"(reinterpret_cast<const uint8_t*>(kp) + 16 * c) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (2 * u + 1) * 32 * VB + 16 * c),
+                         "l"(reinterpret_cast<const uint8_t*>(vp) + 16 * c) : "memory");
+          }
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");     // (an empty group keeps the count uniform)
+  };
+#pragma unroll
+  for (int s0 = 0; s0 < STG; ++s0) issue(s0);
+  for (int it = 0; it < n_iter; ++it) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(STG - 1) : "memory");
+    const AT* slot = reinterpret_cast<const AT*>(ring + static_cast<size_t>(it % STG) * (U * 2 * 32 * VB) + static_cast<size_t>(lane) * VB);
+    const int j0 = it * (U * NG);
     float k[U][8], v[U][8], d[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int j = j0 + NG * u + grp;
       if (j < L) {
-        load8(kbase + static_cast<size_t>(j) * pitch, k[u]);
-        load8(vbase + static_cast<size_t>(j) * pitch, v[u]);
+        load8(slot + (2 * u) * 32 * 8, k[u]);
+        load8(slot + (2 * u + 1) * 32 * 8, v[u]);
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) { k[u][i] = 0.f; v[u][i] = 0.f; }
@@ -684,7 +718,9 @@ attn_step_kernel(AttnArgs a) {
       l = fmaf(l, corr, psum);
       m = mn;
     }
+    issue(it + STG);       // refill the slot just consumed (its values are in registers: the loads above have returned)
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   float mall = m;
 #pragma unroll
   for (int s = LPK; s < 32; s <<= 1) mall = fmaxf(mall, __shfl_xor_sync(0xffffffffu, mall, s));
@@ -734,10 +770,11 @@ int launch_attn_step(const AttnArgs& a, int n_seqs, cudaStream_t st) {
   B2S_REQUIRE(a.relbias == nullptr && !a.noncausal, "attn_step: the relative-bias / non-causal forms belong to the varlen kernel");
   B2S_REQUIRE(a.q_base % 8 == 0 && a.q_hstride % 8 == 0 && a.qkv_dim % 8 == 0, "attn_step: query heads must start at 16-byte boundaries");
   dim3 grid(static_cast<unsigned>(ceil_div(a.nh, 4)), static_cast<unsigned>(n_seqs));
+  const size_t smem = 4 * 3 * 2 * 2 * 32 * 8 * sizeof(AT);      // 4 warps x STG x U x (K, V) x 32 lanes x one 8-element slice
   switch (a.hd) {
-    case 64: attn_step_kernel<AT, 64><<<grid, 128, 0, st>>>(a); break;
-    case 80: attn_step_kernel<AT, 80><<<grid, 128, 0, st>>>(a); break;
-    case 128: attn_step_kernel<AT, 128><<<grid, 128, 0, st>>>(a); break;
+    case 64: attn_step_kernel<AT, 64><<<grid, 128, smem, st>>>(a); break;
+    case 80: attn_step_kernel<AT, 80><<<grid, 128, smem, st>>>(a); break;
+    case 128: attn_step_kernel<AT, 128><<<grid, 128, smem, st>>>(a); break;
     default: set_error("attn_step: unsupported head_dim %d (64, 80, 128)", a.hd); return B2S_EUNSUPPORTED;
   }
   B2S_CHECK_LAUNCH();

@@ -174,14 +174,46 @@ step_attn_kernel(StepAttnArgs a) {
   float o[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) o[i] = 0.f;
-  for (int j0 = 0; j0 < L; j0 += 8) {
+  // K / V slices reach the lanes through a per-warp cp.async ring in shared memory (as in attn_step_kernel, b2s_decoder.cu):
+  // three iterations of two keys per lane group in flight while one is consumed; a lane copies exactly what it consumes.
+  constexpr int U = 2, STG = 3, NG = 4;
+  constexpr int VB = 8 * sizeof(QT);
+  extern __shared__ __align__(16) uint8_t ring_raw[];
+  uint8_t* ring = ring_raw + static_cast<size_t>(warp) * (STG * U * 2 * 32 * VB);
+  const uint32_t ring_s = static_cast<uint32_t>(__cvta_generic_to_shared(ring)) + static_cast<uint32_t>(lane) * VB;
+  const int n_iter = (L + U * NG - 1) / (U * NG);
+  auto issue = [&](int it) {
+    if (it < n_iter) {
+      const uint32_t dst = ring_s + static_cast<uint32_t>(it % STG) * (U * 2 * 32 * VB);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int j = it * (U * NG) + NG * u + grp;
+        if (j < L) {
+          const uint8_t* kp = reinterpret_cast<const uint8_t*>(kbase + static_cast<size_t>(j) * pitch + 8 * sub);
+          const uint8_t* vp = reinterpret_cast<const uint8_t*>(vbase + static_cast<size_t>(j) * pitch + 8 * sub);
+#pragma unroll
+          for (int c = 0; c < VB / 16; ++c) {
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (2 * u) * 32 * VB + 16 * c), "l"(kp + 16 * c) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (2 * u + 1) * 32 * VB + 16 * c), "l"(vp + 16 * c) : "memory");
+          }
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+#pragma unroll
+  for (int s0 = 0; s0 < STG; ++s0) issue(s0);
+  for (int it = 0; it < n_iter; ++it) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(STG - 1) : "memory");
+    const QT* slot = reinterpret_cast<const QT*>(ring + static_cast<size_t>(it % STG) * (U * 2 * 32 * VB) + static_cast<size_t>(lane) * VB);
+    const int j0 = it * (U * NG);
     float k[2][8], v[2][8], d[2];
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
       const int j = j0 + 4 * u + grp;
       if (j < L) {
-        load8(kbase + static_cast<size_t>(j) * pitch + 8 * sub, k[u]);
-        load8(vbase + static_cast<size_t>(j) * pitch + 8 * sub, v[u]);
+        load8(slot + (2 * u) * 32 * 8, k[u]);
+        load8(slot + (2 * u + 1) * 32 * 8, v[u]);
       } else {
 #pragma unroll
         for (int i = 0; i < 8; ++i) { k[u][i] = 0.f; v[u][i] = 0.f; }
@@ -207,7 +239,9 @@ step_attn_kernel(StepAttnArgs a) {
       for (int i = 0; i < 8; ++i) o[i] = fmaf(o[i], corr, fmaf(p0, v[0][i], p1 * v[1][i]));
       m = mn;
     }
+    issue(it + STG);       // refill the slot just consumed
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   // merge the four groups
   float mall = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
   mall = fmaxf(mall, __shfl_xor_sync(0xffffffffu, mall, 16));
@@ -254,7 +288,8 @@ step_attn_kernel(StepAttnArgs a) {
 template <typename QT, bool SELF>
 int launch_step_attn(const StepAttnArgs& a, int rows, cudaStream_t st) {
   dim3 grid(static_cast<unsigned>(ceil_div(a.nh, 4)), static_cast<unsigned>(rows));
-  step_attn_kernel<QT, SELF><<<grid, 128, 0, st>>>(a);
+  const size_t smem = 4 * 3 * 2 * 2 * 32 * 8 * sizeof(QT);      // 4 warps x STG x U x (K, V) x 32 lanes x one 8-element slice
+  step_attn_kernel<QT, SELF><<<grid, 128, smem, st>>>(a);
   B2S_CHECK_LAUNCH();
   return B2S_OK;
 }
