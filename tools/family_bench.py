@@ -25,10 +25,9 @@ for maker in args.models:
     shp = getattr(shapes, maker)()
     ids, cand, L = bench.synthetic_prompts(shp, args.prompts, seed=2)
     W = weights.init_weights_device(shp, seed=1, device="cuda:0", weight_dtype=torch.float16)
-    # batch size: the KV cache of a multi-head 7B model is 0.5 MB per token (32 layers x 2 x 4096 x 2 B): keep it near 40 GB
-    kv_bytes_per_token = shp.n_layer * 2 * shp.n_kv_head * shp.head_dim * 2
-    max_tokens = int(min(262144, max(32768, 40e9 // kv_bytes_per_token)))
-    sc = Scorer(shp, W, mode=shapes.MODE_FP16, device="cuda:0", max_tokens=max_tokens, max_seqs=2048)
+    # batch sized by the scorer from the free device memory (scorer.fit_batch): the KV cache of a multi-head 7B model is 0.5 MB per token
+    sc = Scorer(shp, W, mode=shapes.MODE_FP16, device="cuda:0", max_tokens=None)
+    max_tokens = sc.max_tokens
     del W
     sc.score_ids(ids[:300], cand[:300], topk=5, nonfinite="nan")
     torch.cuda.synchronize()
