@@ -122,3 +122,16 @@ def test_entry_point_7_perturbations_duplicates_identical(tmp_path):
         assert grp["Token_1_Prob"].nunique() == 1 and grp["Token_2_Prob"].nunique() == 1 and grp["Model Response"].nunique() == 1
     assert df["Relative_Prob"].std() > 0.01
     assert os.path.exists(os.path.join(tmp_path, E7.RESULTS_NAME))
+
+
+def test_entry_point_1_with_the_reference_8bit_switch(tmp_path, monkeypatch):
+    """B2S_USE_8BIT=1 = the reference's USE_8BIT (run_base_vs_instruct_100q.py:84): the decoder-only models run in the LLM.int8
+    emulation mode; the rows keep their schema and stay close to, but not equal to, the FP16 run's."""
+    from llm_interpretation_replication_b200.entrypoints import run_base_vs_instruct_100q as E1
+    args = ["--layers", "2", "--questions", "8", "--pairs", "1"]
+    df16 = E1.main(args + ["--out", str(tmp_path / "fp16")])
+    monkeypatch.setenv("B2S_USE_8BIT", "1")
+    df8 = E1.main(args + ["--out", str(tmp_path / "int8")])
+    assert list(df8.columns) == list(df16.columns) and len(df8) == len(df16) == 16 and df8["success"].all()
+    d = (df8["relative_prob"] - df16["relative_prob"]).abs()
+    assert 0 < d.max() < 0.2, d.max()
