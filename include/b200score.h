@@ -66,8 +66,15 @@ enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQ
  *               fp16 x fp16 -> fp32 then multiplies the same numbers as int8 x int8 -> int32 followed by the dequantisation,
  *               up to the fp16 rounding of the dequantised operands (2^-11, 16 times finer than the int8 step).  Decoder-only
  *               handles only.  bitsandbytes is not in this image: the mode is pinned against a restatement of its published
- *               MatMul8bitLt (oracle/int8_ref.py), not against the library itself. */
-enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3, B2S_MODE_INT8_EMU = 4 };
+ *               MatMul8bitLt (oracle/int8_ref.py), not against the library itself;
+ *   FP16_FFN_SPLIT (encoder-decoder handles only) FP16 everywhere except the one place where the T5 family is known to leave
+ *               fp16's range, the activation that feeds the feed-forward's second projection (HF keeps that layer, `wo`, in fp32
+ *               for fp16 inference: t5 `_keep_in_fp32_modules`): the first projection's epilogue forms act(wi_0 x) * wi_1 x on the
+ *               fp32 accumulators and stores it as bf16 hi + lo halves, and the W_DOWN matrices are handed over in bf16 and
+ *               meet both halves (as in BF16_SPLIT).  The residual stream, which receives that projection's output, is fp32
+ *               in every mode.  Costs the doubled K of one GEMM in four instead of all of them. */
+enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3, B2S_MODE_INT8_EMU = 4,
+       B2S_MODE_FP16_FFN_SPLIT = 5 };
 
 /* weight_ptrs slots: 10 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
  * pointer must be 16-byte aligned (B2S_EINVAL otherwise) */

@@ -27,6 +27,7 @@ struct b2s_encdec {
   int inner;      // n_head * head_dim
   bool bf16;      // tensor-core mode
   int act_f16, split;
+  int ffn_split;  // FP16_FFN_SPLIT: fp16 everywhere, the feed-forward activation as bf16 hi | lo halves against bf16 W_DOWN
   size_t at_size;
   const void* gw(int slot) const { return w[slot]; }
   const float* gwf(int slot) const { return reinterpret_cast<const float*>(w[slot]); }
@@ -79,7 +80,7 @@ EdWorkspace carve(const b2s_encdec* m, int64_t T, int32_t N, int32_t G, uint8_t*
   w.ln = take(at * am * rows * d.d_model);
   w.qkv = take(at * rows * 3 * inner);
   w.attn = take(at * am * rows * inner);
-  w.act = take(at * am * rows * d.d_ff);
+  w.act = take(at * (m->ffn_split ? 2 : am) * rows * d.d_ff);
   w.gu = d.ff_type == B2S_T5_FF_GATED_GELU ? take((m->split ? 4 : at) * rows * 2 * d.d_ff) : nullptr;
   w.cq = take(at * static_cast<size_t>(N) * inner);
   w.hfin = take(at * am * static_cast<size_t>(N) * d.d_model);
@@ -324,6 +325,15 @@ struct Run {
   int ffn(const void* w_up, const void* w_down, int rows) const {
     const b2s_encdec_desc& d = m->d;
     const int dm = d.d_model, ff = d.d_ff;
+    if (m->ffn_split) {
+      // fp16 operands in, act(...) formed on the fp32 accumulators and stored as bf16 [hi | lo]; then the bf16 second
+      // projection over both halves (fp32 accumulate, reduce-add into the fp32 residual)
+      if (d.ff_type == B2S_T5_FF_GATED_GELU_FUSED)
+        B2S_TRY(gemm_tc_launch(w.ln, w_up, nullptr, w.act, rows, 2 * ff, dm, EPI_SWIGLU, nullptr, st, 1, nullptr, 0, 1, 0, B2S_ACT_GELU_TANH));
+      else
+        B2S_TRY(gemm_tc_launch(w.ln, w_up, nullptr, w.act, rows, ff, dm, EPI_GELU_BF16, nullptr, st, 1, nullptr, 0, 1, 0, B2S_ACT_RELU));
+      return gemm_tc_launch(w.act, w_down, nullptr, w.resid, rows, dm, ff, EPI_RESID_F32, nullptr, st, 0, nullptr, 1, 0);
+    }
     if (d.ff_type == B2S_T5_FF_GATED_GELU_FUSED) {
       B2S_TRY(lin(w.ln, w_up, w.act, rows, 2 * ff, dm, EPI_SWIGLU, m->split, -1, B2S_ACT_GELU_TANH));
     } else if (d.ff_type == B2S_T5_FF_GATED_GELU) {
@@ -486,10 +496,12 @@ int b2s_encdec_create(const b2s_encdec_desc* desc, const void* const* weight_ptr
   B2S_REQUIRE(d.ff_type != B2S_T5_FF_GATED_GELU_FUSED || d.compute_mode != B2S_MODE_FP32_CHECK,
               "encdec_create: interleaved wi_0 / wi_1 rows (B2S_T5_FF_GATED_GELU_FUSED) are for the tensor-core modes");
   B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_BF16_SPLIT ||
-                  d.compute_mode == B2S_MODE_FP32_CHECK,
+                  d.compute_mode == B2S_MODE_FP32_CHECK || d.compute_mode == B2S_MODE_FP16_FFN_SPLIT,
               "encdec_create: unknown compute mode %d", d.compute_mode);
-  B2S_REQUIRE(d.compute_mode != B2S_MODE_BF16_SPLIT || (d.d_model % 64 == 0 && d.d_ff % 64 == 0),
-              "encdec_create: BF16_SPLIT needs d_model and d_ff to be multiples of 64");
+  B2S_REQUIRE((d.compute_mode != B2S_MODE_BF16_SPLIT && d.compute_mode != B2S_MODE_FP16_FFN_SPLIT) || (d.d_model % 64 == 0 && d.d_ff % 64 == 0),
+              "encdec_create: the split modes need d_model and d_ff to be multiples of 64");
+  B2S_REQUIRE(d.compute_mode != B2S_MODE_FP16_FFN_SPLIT || d.ff_type != B2S_T5_FF_GATED_GELU,
+              "encdec_create: FP16_FFN_SPLIT forms the gate in the projection's epilogue: hand W_UP over interleaved (B2S_T5_FF_GATED_GELU_FUSED)");
   B2S_REQUIRE(d.d_model % 8 == 0 && d.d_ff % 8 == 0, "encdec_create: d_model and d_ff must be multiples of 8");
   B2S_REQUIRE(d.decoder_start_id >= 0 && d.decoder_start_id < d.vocab, "encdec_create: decoder_start_id %d outside the vocabulary",
               d.decoder_start_id);
@@ -512,7 +524,8 @@ int b2s_encdec_create(const b2s_encdec_desc* desc, const void* const* weight_ptr
   m->device = device;
   m->inner = d.n_head * d.head_dim;
   m->bf16 = d.compute_mode != B2S_MODE_FP32_CHECK;
-  m->act_f16 = d.compute_mode == B2S_MODE_FP16 ? 1 : 0;
+  m->ffn_split = d.compute_mode == B2S_MODE_FP16_FFN_SPLIT ? 1 : 0;
+  m->act_f16 = (d.compute_mode == B2S_MODE_FP16 || m->ffn_split) ? 1 : 0;
   m->split = d.compute_mode == B2S_MODE_BF16_SPLIT ? 1 : 0;
   m->at_size = m->bf16 ? 2 : 4;
   auto fail = [&](const char* what, int l, int s) {

@@ -69,7 +69,7 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
     supported families, which the callers turn into NaN rows as the reference does for models that fail to load.
     ``max_tokens`` None = the batch is sized from the device memory that is free once the weights are resident
     (``scorer.fit_batch``: a multi-head 7B model needs 0.5 MB of KV cache per prompt token, Falcon 8 KB).
-    ``mode`` None = FP16 for the decoder-only families, BF16_SPLIT for the T5 family (whose feed-forward activations are
+    ``mode`` None = FP16 for the decoder-only families, FP16_FFN_SPLIT for the T5 family (whose feed-forward activations are
     the known case of values beyond fp16's range; see ``t5.EncDecScorer``)."""
     from .. import checkpoint
     from ..scorer import MAX_LOOK_AHEAD
@@ -82,14 +82,14 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
         if local is not None:
             with open(os.path.join(local, "config.json")) as f:
                 is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
-        mode = shapes.MODE_BF16_SPLIT if is_t5 else shapes.MODE_INT8_EMU
+        mode = shapes.MODE_FP16_FFN_SPLIT if is_t5 else shapes.MODE_INT8_EMU
     if mode is None:
         is_t5 = model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY
         if local is not None:
             with open(os.path.join(local, "config.json")) as f:
                 is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
-        mode = shapes.MODE_BF16_SPLIT if is_t5 else shapes.MODE_FP16
-    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16}.get(mode, torch.bfloat16)
+        mode = shapes.MODE_FP16_FFN_SPLIT if is_t5 else shapes.MODE_FP16
+    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16}.get(mode, torch.bfloat16)   # (FP16_FFN_SPLIT: bf16 in, the scorer converts all but wo)
     if local is not None:
         shp, W = checkpoint.load_checkpoint(local, device=device, weight_dtype=dt, n_layer=n_layer)
         try:

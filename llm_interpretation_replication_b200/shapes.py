@@ -43,6 +43,7 @@ MODE_BF16_FAST = 0    # bf16 MMA operands, fp32 accumulate in TMEM, fp32 residua
 MODE_FP16 = 1         # fp16 weights + activations on the tensor cores (holds the 2e-3 gate at full depth)
 MODE_BF16_SPLIT = 2   # bf16 weights; GEMM activations as hi + lo bf16 halves (holds the gate with bf16 range, 2x tensor work)
 MODE_FP32_CHECK = 3   # fp32 weights + activations on CUDA cores; parity gate 1e-5
+MODE_FP16_FFN_SPLIT = 5   # T5 handles only: fp16 everywhere, the feed-forward activation as bf16 hi + lo halves against bf16 wo
 MODE_INT8_EMU = 4     # bitsandbytes LLM.int8 (the reference's USE_8BIT configuration) emulated on the FP16 kernels
 
 

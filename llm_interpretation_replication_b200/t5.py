@@ -23,7 +23,7 @@ from typing import Dict, List, Optional
 import torch
 
 from . import _lib
-from .shapes import MODE_BF16_FAST, MODE_BF16_SPLIT, MODE_FP16, MODE_FP32_CHECK
+from .shapes import MODE_BF16_FAST, MODE_BF16_SPLIT, MODE_FP16, MODE_FP16_FFN_SPLIT, MODE_FP32_CHECK
 from .scorer import Scorer, MAX_LOOK_AHEAD, fit_batch
 
 FF_RELU, FF_GATED_GELU, FF_GATED_GELU_FUSED = 0, 1, 2   # must match B2S_T5_FF_* in include/b200score.h
@@ -204,10 +204,12 @@ class EncDecScorer(Scorer):
     it ``score_prompts``, ``dist.score_ids_sharded``) runs the encoder-decoder entry points instead.  ``weights_dev`` is
     the flat dict of :func:`init_weights` / ``checkpoint.load_t5`` on the device (matrices in the mode's weight type).
 
-    Default mode: BF16_SPLIT.  The T5 v1.1 family is the textbook case of activations that leave fp16's range in the
-    feed-forward layers (HF keeps ``wo`` in fp32 for that reason, HF t5:527 ``_keep_in_fp32_modules``), so the mode that
-    keeps bf16's range and still holds the 2e-3 gate is the one to start from; MODE_FP16 runs at twice the rate and flags an
-    overflow as B2S_ERANGE.
+    Default mode: FP16_FFN_SPLIT.  The T5 v1.1 family is the textbook case of activations that leave fp16's range, and the place
+    is known: the product act(wi_0 x) * wi_1 x that feeds ``wo`` (HF keeps ``wo`` in fp32 for fp16 inference for that reason,
+    HF t5:527 ``_keep_in_fp32_modules``).  The default therefore runs fp16 everywhere except there: that activation is stored as
+    bf16 hi + lo halves (formed on the fp32 accumulators) and ``wo`` stays bf16; its output lands in the fp32 residual stream
+    like every projection's.  One GEMM in four pays the doubled K.  BF16_SPLIT (every GEMM split, bf16 weights untouched) and
+    plain FP16 (an overflow is flagged as B2S_ERANGE) remain available.
 
     Batch size: the one-token decoder steps are launch- and latency-bound below ~1000 rows, so the default batch is 131072
     prompt tokens (about 1200 prompts; 37 GB of workspace at T0_3B size, dominated by the resident cross-attention K/V:
@@ -215,7 +217,7 @@ class EncDecScorer(Scorer):
 
     is_encoder_decoder = True
 
-    def __init__(self, shape: EncDecShape, weights_dev: Dict[str, torch.Tensor], mode: int = MODE_BF16_SPLIT,
+    def __init__(self, shape: EncDecShape, weights_dev: Dict[str, torch.Tensor], mode: int = MODE_FP16_FFN_SPLIT,
                  device: Optional[torch.device] = None, max_tokens: Optional[int] = 131072, max_seqs: int = 2048,
                  max_lookahead: int = MAX_LOOK_AHEAD):
         if not torch.cuda.is_available():
@@ -225,10 +227,12 @@ class EncDecScorer(Scorer):
         self.mode = mode
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.max_tokens, self.max_seqs, self.max_lookahead = max_tokens, int(max_seqs), int(max_lookahead)
-        want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16}.get(mode, torch.bfloat16)
+        want = {MODE_FP32_CHECK: torch.float32, MODE_FP16: torch.float16, MODE_FP16_FFN_SPLIT: torch.float16}.get(mode, torch.bfloat16)
         W = dict(weights_dev)
-        if mode == MODE_FP16:
-            W = {k: (v.to(torch.float16) if is_matrix(k) and v.dtype != torch.float16 else v) for k, v in W.items()}
+        if mode in (MODE_FP16, MODE_FP16_FFN_SPLIT):
+            # FP16_FFN_SPLIT: the second feed-forward projection stays bf16 (it meets the bf16 hi + lo halves of the activation)
+            keep = (lambda k: k.endswith(".w_down")) if mode == MODE_FP16_FFN_SPLIT else (lambda k: False)
+            W = {k: (v.to(torch.bfloat16 if keep(k) else torch.float16) if is_matrix(k) else v) for k, v in W.items()}
             if weights_dev.get("lm_head") is weights_dev.get("wte"):
                 W["lm_head"] = W["wte"]
         ff_type = FF_GATED_GELU if shape.gated else FF_RELU
@@ -245,7 +249,8 @@ class EncDecScorer(Scorer):
         W["dec_bias"] = bias_table(W.pop("dec_rel_bias"), False, shape).to(self.device)
         for k, v in W.items():
             assert v.is_cuda and v.is_contiguous(), k
-            assert v.dtype == (want if is_matrix(k) else torch.float32), f"{k} is {v.dtype}"
+            exp = torch.bfloat16 if (mode == MODE_FP16_FFN_SPLIT and k.endswith(".w_down")) else want
+            assert v.dtype == (exp if is_matrix(k) else torch.float32), f"{k} is {v.dtype}"
         self.W = W
         self._ptrs = pointer_table(shape, W)
         d = _lib.EncDecDesc(abi_version=_lib.ABI_VERSION, n_enc_layer=shape.n_enc_layer, n_dec_layer=shape.n_dec_layer,

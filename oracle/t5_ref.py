@@ -11,7 +11,7 @@ Follows HF:models/t5/modeling_t5.py:
     d_model^-0.5 before the head only when the embeddings are tied)
 and the reference's procedure around it (analysis/compare_instruct_models.py:178-226): generate from
 decoder_start_token_id, one score row per generated position, stop after EOS, top-k scan of the first 10 rows.
-Validated against the HF module itself in tests/test_oracle_cpu.py; the GPU parity tests call it because it can emulate
+Validated against the HF module itself in tests/test_t5_cpu.py; the GPU parity tests call it because it can emulate
 the operand rounding of the 16-bit modes.
 """
 from __future__ import annotations
@@ -54,17 +54,19 @@ def _attend(shape, q, k, v, bias, mask=None):
     return torch.einsum("hqk,khd->qhd", a, vh).reshape(-1, nh * hd)
 
 
-def _ff(shape, W, p, x, r):
+def _ff(shape, W, p, x, r, rf=None):
+    """``rf``: rounding of the activation that feeds the second projection when it differs from ``r`` (FP16_FFN_SPLIT)."""
+    rf = rf if rf is not None else r
     up = F.linear(r(x), W[p + "w_up"])
     if shape.gated:     # rows [0, ff) = wi_0 (gate), [ff, 2ff) = wi_1; formed on the fp32 accumulators
         h = _gelu_new(up[..., :shape.d_ff]) * up[..., shape.d_ff:]
     else:
         h = F.relu(up)
-    return F.linear(r(h), W[p + "w_down"])
+    return F.linear(rf(h), W[p + "w_down"])
 
 
 def encode(shape: EncDecShape, W: Dict[str, torch.Tensor], ids: torch.Tensor, round_act: Optional[Callable] = None,
-           round_attn: Optional[Callable] = None) -> torch.Tensor:
+           round_attn: Optional[Callable] = None, round_ffn: Optional[Callable] = None) -> torch.Tensor:
     """ids [L] -> encoder output after the final norm, [L, d].  ``round_act`` is applied to every GEMM input,
     ``round_attn`` (default: the same) to q/k/v, as in decoder_ref.forward_hidden."""
     r = round_act if round_act is not None else (lambda t: t)
@@ -77,11 +79,11 @@ def encode(shape: EncDecShape, W: Dict[str, torch.Tensor], ids: torch.Tensor, ro
         qkv = ra(F.linear(r(_norm(x, W[p + "ln1_g"], shape.norm_eps)), W[p + "w_qkv"]))
         o = _attend(shape, qkv[:, :inner], qkv[:, inner:2 * inner], qkv[:, 2 * inner:], bias)
         x = x + F.linear(r(o), W[p + "w_o"])
-        x = x + _ff(shape, W, p, _norm(x, W[p + "ln2_g"], shape.norm_eps), r)
+        x = x + _ff(shape, W, p, _norm(x, W[p + "ln2_g"], shape.norm_eps), r, round_ffn)
     return _norm(x, W["enc_lnf_g"], shape.norm_eps)
 
 
-def decode_logits(shape: EncDecShape, W, enc_out: torch.Tensor, dec_ids: torch.Tensor, round_act=None, round_attn=None):
+def decode_logits(shape: EncDecShape, W, enc_out: torch.Tensor, dec_ids: torch.Tensor, round_act=None, round_attn=None, round_ffn=None):
     """Logits of the last decoder position given the encoder output and the decoder input ids (start id + generated
     tokens), recomputed without a cache."""
     r = round_act if round_act is not None else (lambda t: t)
@@ -100,21 +102,21 @@ def decode_logits(shape: EncDecShape, W, enc_out: torch.Tensor, dec_ids: torch.T
         ckv = ra(F.linear(enc_r, W[p + "w_ckv"]))
         o = _attend(shape, cq, ckv[:, :inner], ckv[:, inner:], None)
         x = x + F.linear(r(o), W[p + "w_co"])
-        x = x + _ff(shape, W, p, _norm(x, W[p + "ln3_g"], shape.norm_eps), r)
+        x = x + _ff(shape, W, p, _norm(x, W[p + "ln3_g"], shape.norm_eps), r, round_ffn)
     h = _norm(x[-1], W["dec_lnf_g"], shape.norm_eps)
     if shape.tied_head:
         h = h * (shape.d_model ** -0.5)
     return F.linear(r(h), W["lm_head"].float()).float()
 
 
-def greedy_scores(shape, W, ids: List[int], n_positions: int, eos_id: int, round_act=None, round_attn=None):
+def greedy_scores(shape, W, ids: List[int], n_positions: int, eos_id: int, round_act=None, round_attn=None, round_ffn=None):
     """scores[t] = logits after the start id + t generated tokens (HF generate, greedy); stops after the position whose
     argmax is EOS, as ``generate`` does."""
-    enc = encode(shape, W, torch.tensor(ids, dtype=torch.long), round_act, round_attn)
+    enc = encode(shape, W, torch.tensor(ids, dtype=torch.long), round_act, round_attn, round_ffn)
     dec = [shape.decoder_start_id]
     rows, gen = [], []
     for _ in range(n_positions):
-        row = decode_logits(shape, W, enc, torch.tensor(dec, dtype=torch.long), round_act, round_attn)
+        row = decode_logits(shape, W, enc, torch.tensor(dec, dtype=torch.long), round_act, round_attn, round_ffn)
         rows.append(row)
         nxt = int(torch.argmax(row))
         gen.append(nxt)
@@ -125,9 +127,9 @@ def greedy_scores(shape, W, ids: List[int], n_positions: int, eos_id: int, round
 
 
 def score_ids(shape, W, ids: List[int], id_a: int, id_b: int, topk: int = 2, max_lookahead: int = 10,
-              eos_id: Optional[int] = None, round_act=None, round_attn=None):
+              eos_id: Optional[int] = None, round_act=None, round_attn=None, round_ffn=None):
     eos = shape.eos_id if eos_id is None else eos_id
-    rows, gen = greedy_scores(shape, W, ids, max_lookahead, eos, round_act, round_attn)
+    rows, gen = greedy_scores(shape, W, ids, max_lookahead, eos, round_act, round_attn, round_ffn)
     pa, pb, pos, found = scan_positions(rows, id_a, id_b, topk)
     row = rows[pos]
     return dict(p_a=pa, p_b=pb, rel=(pa / (pa + pb) if pa + pb > 0 else float("nan")), lse=torch.logsumexp(row, dim=-1).item(),

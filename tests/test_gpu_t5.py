@@ -19,7 +19,7 @@ TOL_FP32, TOL_16 = 1e-5, 2e-3
 # BF16_FAST (bf16 activations) is held to a regression bound only, as on the decoder-only path (tests/test_gpu_scorer.py):
 # two correct bf16 implementations differ by a few 1e-3 (2.97e-3 seen on a tiny-t5 golden row, 2.3e-3 at t5-v1_1-base widths)
 TOL_BF16_FAST = 1e-2
-MODES_16 = ["MODE_BF16_FAST", "MODE_FP16", "MODE_BF16_SPLIT"]
+MODES_16 = ["MODE_BF16_FAST", "MODE_FP16", "MODE_BF16_SPLIT", "MODE_FP16_FFN_SPLIT"]
 
 
 def _cases():
@@ -47,7 +47,10 @@ def _rnd(mode_name):
         return dict(round_act=bf16_round)
     if mode_name == "MODE_FP16":
         return dict(round_act=f16)
-    return dict(round_act=lambda t: bf16_round(t) + bf16_round(t - bf16_round(t)), round_attn=f16)
+    split = lambda t: bf16_round(t) + bf16_round(t - bf16_round(t))
+    if mode_name == "MODE_FP16_FFN_SPLIT":      # fp16 everywhere, the feed-forward activation as bf16 hi + lo
+        return dict(round_act=f16, round_ffn=split)
+    return dict(round_act=split, round_attn=f16)
 
 
 def _ids_and_cands(shp, rows):
@@ -328,7 +331,7 @@ def test_t5_full_depth_vs_oracle(shape_name, n_prompts):
     cands = np.array(cands)
     stats = {}
     for label, mode, tol in (("fp32_check", shapes.MODE_FP32_CHECK, TOL_FP32), ("fp16", shapes.MODE_FP16, TOL_16),
-                             ("bf16_split", shapes.MODE_BF16_SPLIT, TOL_16)):
+                             ("bf16_split", shapes.MODE_BF16_SPLIT, TOL_16), ("fp16_ffn_split", shapes.MODE_FP16_FFN_SPLIT, TOL_16)):
         Wm = Wd if mode != shapes.MODE_FP32_CHECK else {k: (v.float() if t5.is_matrix(k) else v) for k, v in Wd.items()}
         sc = t5.EncDecScorer(shp, Wm, mode=mode, device=DEV, max_tokens=2048, max_seqs=16)
         rows, gens = sc.score_ids(ids, cands, topk=2, eos_id=shp.eos_id)
@@ -351,3 +354,37 @@ def test_t5_full_depth_vs_oracle(shape_name, n_prompts):
                                     "mode": int(mode), "worst_abs_delta_rel_prob_vs_fp32_oracle": worst, "position_mismatches": flips}) + "\n")
         assert flips <= (0 if mode == shapes.MODE_FP32_CHECK else 1), (label, flips)
         assert worst <= tol, (label, worst)
+
+
+def test_t5_default_mode_survives_feed_forward_activations_beyond_fp16():
+    """The reason for FP16_FFN_SPLIT: scale wi_1 up (and wo down by the same factor, so that the fp32 model is unchanged) until
+    act(wi_0 x) * wi_1 x exceeds 65504.  Plain FP16 must flag every prompt (B2S_ERANGE), never return a number; the default
+    mode keeps that activation as bf16 hi + lo halves and must still match the oracle."""
+    from llm_interpretation_replication_b200 import shapes, t5, _lib
+    from oracle import t5_ref
+    shp = t5.tiny_t5()
+    W = t5.init_weights(shp, seed=41)
+    ff, scale = shp.d_ff, 2.0 ** 17
+    for k in [k for k in W if k.endswith(".w_up")]:
+        W[k] = W[k].clone()
+        W[k][ff:] = (W[k][ff:] * scale).to(torch.bfloat16).float()               # wi_1 rows; still inside fp16 as weights
+        W[k.replace("w_up", "w_down")] = (W[k.replace("w_up", "w_down")] / scale).to(torch.bfloat16).float()
+    assert max(float(W[k].abs().max()) for k in W if k.endswith(".w_up")) < 65504.0
+    g = torch.Generator().manual_seed(2)
+    ids = [torch.randint(2, shp.vocab, (L,), generator=g).tolist() + [shp.eos_id] for L in (30, 70, 11)]
+    cands = []
+    for x in ids:
+        rows, gen = t5_ref.greedy_scores(shp, W, x, 1, shp.eos_id)
+        cands.append(torch.topk(rows[0], 2).indices.tolist())
+    cands = np.array(cands)
+    sc = _scorer(shp, W, shapes.MODE_FP16, max_tokens=1024, max_seqs=8)
+    with pytest.raises(_lib.B2SRangeError):
+        sc.score_ids(ids, cands, topk=2, eos_id=shp.eos_id)
+    sc.close()
+    sc = _scorer(shp, W, shapes.MODE_FP16_FFN_SPLIT, max_tokens=1024, max_seqs=8)
+    rows, gens = sc.score_ids(ids, cands, topk=2, eos_id=shp.eos_id)
+    sc.close()
+    assert np.isfinite(rows[:, :6]).all()
+    for i, x in enumerate(ids):
+        o = t5_ref.score_ids(shp, W, x, int(cands[i][0]), int(cands[i][1]), topk=2)
+        assert int(rows[i][6]) == o["pos_found"] and abs(float(rows[i][2]) - o["rel"]) <= 4e-3, (i, rows[i], o)

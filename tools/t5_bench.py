@@ -36,10 +36,11 @@ def main():
     ids = [np.concatenate([rs.randint(32, shp.vocab - 32, size=int(l) - 1), [shp.eos_id]]).astype(np.int32) for l in L]
     cand = np.tile(np.array([[1001, 1002]], np.int32), (len(ids), 1))
     lib = _lib.load()
-    modes = {"bf16_split": shapes.MODE_BF16_SPLIT, "fp16": shapes.MODE_FP16, "bf16": shapes.MODE_BF16_FAST}
+    modes = {"bf16_split": shapes.MODE_BF16_SPLIT, "fp16": shapes.MODE_FP16, "bf16": shapes.MODE_BF16_FAST,
+             "fp16_ffn_split": shapes.MODE_FP16_FFN_SPLIT}
     for name in args.modes:
         mode = modes[name]
-        dt = torch.float16 if mode == shapes.MODE_FP16 else torch.bfloat16
+        dt = torch.bfloat16      # (the scorer converts to what the mode needs; FP16_FFN_SPLIT keeps wo in bf16)
         W = t5.init_weights(shp, seed=1, device="cuda:0", weight_dtype=dt)
         sc = t5.EncDecScorer(shp, W, mode=mode, device="cuda:0", max_tokens=args.max_tokens, max_seqs=args.max_seqs)
         del W
