@@ -89,7 +89,9 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
             with open(os.path.join(local, "config.json")) as f:
                 is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
         mode = shapes.MODE_FP16_FFN_SPLIT if is_t5 else shapes.MODE_FP16
-    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16}.get(mode, torch.bfloat16)   # (FP16_FFN_SPLIT: bf16 in, the scorer converts all but wo)
+    # (FP16_FFN_SPLIT wants fp16 matrices except wo in bf16: the checkpoint is read in fp32 and the scorer converts each matrix once)
+    dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16,
+          shapes.MODE_FP16_FFN_SPLIT: torch.float32}.get(mode, torch.bfloat16)
     if local is not None:
         shp, W = checkpoint.load_checkpoint(local, device=device, weight_dtype=dt, n_layer=n_layer)
         try:
