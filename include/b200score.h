@@ -72,9 +72,14 @@ enum { B2S_QKV_FALCON_MQA = 0 /* [q heads..., k heads..., v heads...]: Falcon MQ
  *               for fp16 inference: t5 `_keep_in_fp32_modules`): the first projection's epilogue forms act(wi_0 x) * wi_1 x on the
  *               fp32 accumulators and stores it as bf16 hi + lo halves, and the W_DOWN matrices are handed over in bf16 and
  *               meet both halves (as in BF16_SPLIT).  The residual stream, which receives that projection's output, is fp32
- *               in every mode.  Costs the doubled K of one GEMM in four instead of all of them. */
+ *               in every mode.  Costs the doubled K of one GEMM in four instead of all of them;
+ *   BF16_SPLIT_ATTN32 (decoder-only handles) BF16_SPLIT with q/k/v, the KV cache and all of attention in fp32 on the CUDA-core
+ *               kernels: nothing between two fp32 points is rounded below 16 mantissa bits.  For models whose scores are more
+ *               sensitive to operand rounding than the BASELINE configs -- the Llama family at 32 layers leaves the 2e-3 gate on
+ *               a fifth of the prompts in every 16-bit-attention mode, in the torch emulation of the roundings as on the GPU
+ *                -- at the price of the slow attention path. */
 enum { B2S_MODE_BF16_FAST = 0, B2S_MODE_FP16 = 1, B2S_MODE_BF16_SPLIT = 2, B2S_MODE_FP32_CHECK = 3, B2S_MODE_INT8_EMU = 4,
-       B2S_MODE_FP16_FFN_SPLIT = 5 };
+       B2S_MODE_FP16_FFN_SPLIT = 5, B2S_MODE_BF16_SPLIT_ATTN32 = 6 };
 
 /* weight_ptrs slots: 10 global + 16 per layer (see llm_interpretation_replication_b200/weights.py); every non-null
  * pointer must be 16-byte aligned (B2S_EINVAL otherwise) */

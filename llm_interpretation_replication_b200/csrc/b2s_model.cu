@@ -40,6 +40,7 @@ struct b2s_model {
   bool bf16;      // tensor-core mode (bf16 weights); false = fp32 check mode
   int act_f16;    // tensor-core mode with fp16 operands (weights handed over as fp16)
   int split;      // BF16_SPLIT: every GEMM A operand is stored as [hi | lo] bf16 halves (row width doubled)
+  int attn32;     // BF16_SPLIT_ATTN32: as BF16_SPLIT, with q/k/v, the KV cache and the whole of attention in fp32 (CUDA-core kernels)
   int int8;       // INT8_EMU: FP16 kernels, every linear layer's input put on bitsandbytes' int8 grid first (launch_int8_fakequant)
   size_t at_size;
   const void* gw(int slot) const { return w[slot]; }
@@ -103,7 +104,8 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   const size_t am = m->split ? 2 : 1;   // [hi | lo] rows in BF16_SPLIT
   w.ln1 = take(at * am * rows * d.d_model);
   w.ln2 = d.n_ln_per_layer == 2 ? take(at * am * rows * d.d_model) : nullptr;
-  w.qkv = take(at * rows * m->qkv_dim);
+  const size_t qt = m->attn32 ? 4 : at;     // q/k/v and the KV cache: 16-bit, or fp32 in BF16_SPLIT_ATTN32
+  w.qkv = take(qt * rows * m->qkv_dim);
   w.attn = take(at * am * rows * d.n_head * d.head_dim);
   w.act = take(at * am * rows * d.d_ff);
   // MLP pre-activations that a separate kernel turns into the activation: gate | up before SwiGLU; in BF16_SPLIT also
@@ -113,7 +115,7 @@ Workspace carve(const b2s_model* m, int64_t T, int32_t N, int32_t LA, uint8_t* b
   w.hfin = take(at * am * static_cast<size_t>(N) * d.d_model);
   const size_t slots = static_cast<size_t>(T) + static_cast<size_t>(N) * LA;
   w.cache_slots = slots;
-  w.cache_layer_bytes = align_up(at * slots * d.n_kv_head * d.head_dim, 256);
+  w.cache_layer_bytes = align_up(qt * slots * d.n_kv_head * d.head_dim, 256);
   w.kcache = take(w.cache_layer_bytes * d.n_layer);
   w.vcache = take(w.cache_layer_bytes * d.n_layer);
   const size_t tiles_n = static_cast<size_t>(ceil_div(d.vocab, LMH_TILE_N));
@@ -176,7 +178,8 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     uint8_t* kc = reinterpret_cast<uint8_t*>(w.kcache) + w.cache_layer_bytes * l;
     uint8_t* vc = reinterpret_cast<uint8_t*>(w.vcache) + w.cache_layer_bytes * l;
     // Falcon layout with 64-wide fully rotated heads: RoPE and the cache append ride in the QKV GEMM epilogue
-    const bool fused_rope = m->bf16 && d.qkv_layout == B2S_QKV_FALCON_MQA && d.head_dim == 64 && d.rotary_dim == 64;
+    constexpr bool q32 = std::is_same<QT, float>::value && !std::is_same<AT, float>::value;   // BF16_SPLIT_ATTN32
+    const bool fused_rope = m->bf16 && !q32 && d.qkv_layout == B2S_QKV_FALCON_MQA && d.head_dim == 64 && d.rotary_dim == 64;
     if (fused_rope) {
       RopeEpiArgs re{};
       re.pos = w.meta.pos; re.slot = w.meta.slot;
@@ -187,8 +190,8 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
                              EPI_QKV_ROPE, nullptr, st, m->act_f16, &re, m->split, 0, q_f16));
     } else {
       if (m->bf16)
-        B2S_TRY(gemm_tc_launch(w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm, EPI_STORE_BF16,
-                               nullptr, st, m->act_f16, nullptr, m->split, 0, q_f16));
+        B2S_TRY(gemm_tc_launch(w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm,
+                               q32 ? EPI_STORE_F32 : EPI_STORE_BF16, nullptr, st, m->act_f16, nullptr, m->split, 0, q_f16));
       else
         B2S_TRY(linear(m, w.ln1, m->lw(l, B2S_WL_W_QKV), m->lwf(l, B2S_WL_B_QKV), w.qkv, rows, m->qkv_dim, dm, EPI_STORE_BF16, st));
       RopeArgs ro{};
@@ -214,7 +217,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
     // (ALiBi: prompt pass only -- the one-token tensor-core kernel has no bias term)
     // (the one-token tensor-core kernel makes a tile out of the query heads that share a KV head: worth it for multi-query
     // models -- 71 rows for Falcon -- not for 1..4 heads per KV head, which stream better)
-    const bool tc_ok = m->bf16 && (at.alibi == nullptr || max_qlen > 1) && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
+    const bool tc_ok = m->bf16 && !q32 && (at.alibi == nullptr || max_qlen > 1) && (max_qlen > 1 ? attn_tc_supported(d.head_dim, max_kv)
                                                 : (attn_tc_decode_supported(d.head_dim, max_kv, m->qkv_dim, m->q_base, m->q_hstride) &&
                                                    (at.rep >= 8 || !g_opt_attn_step)));
     if (tc_ok) {
@@ -275,6 +278,7 @@ int forward_t(const b2s_model* m, const Workspace& w, const int32_t* tokens, int
 
 int forward(const b2s_model* m, const Workspace& w, const int32_t* tokens, int rows, int n_seqs, int max_kv,
             int max_qlen, cudaStream_t st) {
+  if (m->bf16 && m->split && m->attn32) return forward_t<__nv_bfloat16, __nv_bfloat16, float>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
   if (m->bf16 && m->split) return forward_t<__nv_bfloat16, __nv_bfloat16, __half>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
   if (m->bf16 && m->act_f16) return forward_t<__half, __half>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
   if (m->bf16) return forward_t<__nv_bfloat16, __nv_bfloat16>(m, w, tokens, rows, n_seqs, max_kv, max_qlen, st);
@@ -339,9 +343,9 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
               "model_create: interleaved gate/up rows (B2S_MLP_SWIGLU_FUSED) are for the tensor-core modes");
   B2S_REQUIRE(d.n_ln_per_layer == 2 || d.parallel_residual, "model_create: a single LayerNorm implies parallel residual");
   B2S_REQUIRE(d.compute_mode == B2S_MODE_BF16_FAST || d.compute_mode == B2S_MODE_FP16 || d.compute_mode == B2S_MODE_BF16_SPLIT ||
-                  d.compute_mode == B2S_MODE_FP32_CHECK || d.compute_mode == B2S_MODE_INT8_EMU,
+                  d.compute_mode == B2S_MODE_FP32_CHECK || d.compute_mode == B2S_MODE_INT8_EMU || d.compute_mode == B2S_MODE_BF16_SPLIT_ATTN32,
               "model_create: unknown compute mode %d", d.compute_mode);
-  B2S_REQUIRE(d.compute_mode != B2S_MODE_BF16_SPLIT || (d.d_model % 64 == 0 && d.d_ff % 64 == 0 && (d.n_head * d.head_dim) % 64 == 0),
+  B2S_REQUIRE((d.compute_mode != B2S_MODE_BF16_SPLIT && d.compute_mode != B2S_MODE_BF16_SPLIT_ATTN32) || (d.d_model % 64 == 0 && d.d_ff % 64 == 0 && (d.n_head * d.head_dim) % 64 == 0),
               "model_create: BF16_SPLIT needs d_model, d_ff and n_head*head_dim to be multiples of 64");
   B2S_REQUIRE(d.d_model % 8 == 0 && d.d_ff % 8 == 0, "model_create: d_model and d_ff must be multiples of 8");
   const int need = B2S_W_NGLOBAL + B2S_W_PER_LAYER * d.n_layer;
@@ -364,7 +368,8 @@ int b2s_model_create(const b2s_model_desc* desc, const void* const* weight_ptrs,
   m->bf16 = d.compute_mode != B2S_MODE_FP32_CHECK;
   m->int8 = d.compute_mode == B2S_MODE_INT8_EMU ? 1 : 0;
   m->act_f16 = (d.compute_mode == B2S_MODE_FP16 || m->int8) ? 1 : 0;
-  m->split = d.compute_mode == B2S_MODE_BF16_SPLIT ? 1 : 0;
+  m->attn32 = d.compute_mode == B2S_MODE_BF16_SPLIT_ATTN32 ? 1 : 0;
+  m->split = (d.compute_mode == B2S_MODE_BF16_SPLIT || m->attn32) ? 1 : 0;
   m->at_size = m->bf16 ? 2 : 4;
   m->qkv_dim = (d.n_head + 2 * d.n_kv_head) * d.head_dim;
   if (d.qkv_layout == B2S_QKV_FALCON_MQA) {

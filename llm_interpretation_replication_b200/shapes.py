@@ -44,6 +44,7 @@ MODE_FP16 = 1         # fp16 weights + activations on the tensor cores (holds th
 MODE_BF16_SPLIT = 2   # bf16 weights; GEMM activations as hi + lo bf16 halves (holds the gate with bf16 range, 2x tensor work)
 MODE_FP32_CHECK = 3   # fp32 weights + activations on CUDA cores; parity gate 1e-5
 MODE_FP16_FFN_SPLIT = 5   # T5 handles only: fp16 everywhere, the feed-forward activation as bf16 hi + lo halves against bf16 wo
+MODE_BF16_SPLIT_ATTN32 = 6   # decoder-only handles: BF16_SPLIT with q/k/v, the KV cache and attention in fp32 (CUDA-core kernels)
 MODE_INT8_EMU = 4     # bitsandbytes LLM.int8 (the reference's USE_8BIT configuration) emulated on the FP16 kernels
 
 

@@ -29,11 +29,14 @@ def _rnd(mode_name):
         return dict(round_act=decoder_ref.bf16_round)
     if mode_name == "MODE_FP16":
         return dict(round_act=f16)
+    split = lambda t: decoder_ref.bf16_round(t) + decoder_ref.bf16_round(t - decoder_ref.bf16_round(t))
+    if mode_name == "MODE_BF16_SPLIT_ATTN32":      # GEMM inputs as hi + lo bf16 halves, q/k/v and attention in fp32
+        return dict(round_act=split, round_attn=lambda t: t)
     # BF16_SPLIT: GEMM inputs as hi + lo bf16 halves, q/k/v in fp16
-    return dict(round_act=lambda t: decoder_ref.bf16_round(t) + decoder_ref.bf16_round(t - decoder_ref.bf16_round(t)), round_attn=f16)
+    return dict(round_act=split, round_attn=f16)
 
 
-MODES_16 = ["MODE_BF16_FAST", "MODE_FP16", "MODE_BF16_SPLIT"]
+MODES_16 = ["MODE_BF16_FAST", "MODE_FP16", "MODE_BF16_SPLIT", "MODE_BF16_SPLIT_ATTN32"]
 
 
 def _run_case(case, mode, tol):
@@ -138,9 +141,9 @@ def test_scorer_bf16_vs_reference_golden(case_idx, mode_name):
     from llm_interpretation_replication_b200 import shapes, weights, _lib
     case = U.golden_cases()[case_idx]
     shp = shapes.REGISTRY[case["shape"]]()
-    if mode_name == "MODE_BF16_SPLIT" and (shp.d_model % 64 or shp.d_ff % 64 or (shp.n_head * shp.head_dim) % 64):
-        with pytest.raises(_lib.B2SError):      # the split mode says so instead of mis-addressing its [hi | lo] halves
-            U.make_scorer(shp, weights.init_weights(shp, seed=case["seed"]), shapes.MODE_BF16_SPLIT, max_tokens=256, max_seqs=4)
+    if mode_name.startswith("MODE_BF16_SPLIT") and (shp.d_model % 64 or shp.d_ff % 64 or (shp.n_head * shp.head_dim) % 64):
+        with pytest.raises(_lib.B2SError):      # the split modes say so instead of mis-addressing their [hi | lo] halves
+            U.make_scorer(shp, weights.init_weights(shp, seed=case["seed"]), getattr(shapes, mode_name), max_tokens=256, max_seqs=4)
         return
     _run_case(case, getattr(shapes, mode_name), TOL_BF16)
 

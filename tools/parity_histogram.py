@@ -6,7 +6,9 @@ modes on a large sample of the bench prompt set: Falcon-7B, 32 layers, top-5 / 1
 bf16-representable weights in every mode.  Reports, per mode, the |delta relative_prob| histogram, the pass rate at the
 2e-3 gate, and how often the look-ahead position or the found flag disagrees (those prompts are counted, not compared).
 
-  python tools/parity_histogram.py [n_prompts=2000] [n_layer=32] [modes=fp16,bf16,bf16_split] > gpurun_out/parity_histogram.json
+  python tools/parity_histogram.py [n_prompts=2000] [n_layer=32] [modes=fp16,bf16,bf16_split] [shape=falcon_7b] > gpurun_out/parity_histogram.json
+(shape: any maker of shapes.py, e.g. llama2_7b -- multi-head, head_dim 128: the tensor-core prompt pass at 128, the streaming
+one-token attention and the vectorised RoPE kernel; n_layer 0 = the shape's own depth)
 """
 import json
 import sys
@@ -27,11 +29,17 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
     n_layer = int(sys.argv[2]) if len(sys.argv) > 2 else 32
     which = sys.argv[3].split(",") if len(sys.argv) > 3 else ["fp16", "bf16", "bf16_split"]
-    modes = {"fp16": shapes.MODE_FP16, "bf16": shapes.MODE_BF16_FAST, "bf16_split": shapes.MODE_BF16_SPLIT}
-    shp = shapes.falcon_7b()
-    if n_layer != 32:
+    modes = {"fp16": shapes.MODE_FP16, "bf16": shapes.MODE_BF16_FAST, "bf16_split": shapes.MODE_BF16_SPLIT,
+             "bf16_split_attn32": shapes.MODE_BF16_SPLIT_ATTN32}
+    shp = getattr(shapes, sys.argv[4])() if len(sys.argv) > 4 else shapes.falcon_7b()
+    if n_layer and n_layer != shp.n_layer:
         shp = shp.with_layers(n_layer)
     dev = torch.device("cuda:0")
+    import os
+    from llm_interpretation_replication_b200 import _lib
+    for kv in filter(None, os.environ.get("B2S_OPTIONS", "").split(",")):      # e.g. B2S_OPTIONS=attn_ts=0 : A/B of one kernel choice
+        k, v = kv.split("=")
+        _lib.check(_lib.load().b2s_set_option(k.encode(), int(v)), "set_option")
     W = weights.init_weights_device(shp, seed=0, device=dev, weight_dtype=torch.bfloat16, randomize_affine=True)
     ids, cand, L = bench.synthetic_prompts(shp, 10000)
     pick = np.linspace(0, 9999, n).astype(int)
@@ -52,7 +60,7 @@ def main():
         return rows, gens, dt
 
     W32 = {k: (v.float() if weights.is_matrix(k) else v) for k, v in W.items() if k != "lm_head"}
-    W32["lm_head"] = W32["wte"]
+    W32["lm_head"] = W32["wte"] if shp.tied_head else W["lm_head"].float()
     # pass 1 (fp32): the greedy tokens; a tenth of the prompts then gets candidate a = the token emitted at position
     # 1 + (i mod 8), so that the look-ahead rule is exercised at later positions too, as in the goldens
     _, g32, _ = run(shapes.MODE_FP32_CHECK, W32, my_cand, 32768)
