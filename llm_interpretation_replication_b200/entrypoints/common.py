@@ -69,26 +69,33 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
     supported families, which the callers turn into NaN rows as the reference does for models that fail to load.
     ``max_tokens`` None = the batch is sized from the device memory that is free once the weights are resident
     (``scorer.fit_batch``: a multi-head 7B model needs 0.5 MB of KV cache per prompt token, Falcon 8 KB).
-    ``mode`` None = FP16 for the decoder-only families, FP16_FFN_SPLIT for the T5 family (whose feed-forward activations are
+    ``mode`` None = the fastest mode that holds the 2e-3 gate for the family at full depth: FP16 (Falcon, GPT-NeoX, OPT, BLOOM),
+    BF16_SPLIT_ATTN32 (the Llama block: Llama-2, Mistral, Qwen, Baichuan2), FP16_FFN_SPLIT (T5, whose feed-forward activations are
     the known case of values beyond fp16's range; see ``t5.EncDecScorer``)."""
     from .. import checkpoint
     from ..scorer import MAX_LOOK_AHEAD
     device = torch.device(device if device is not None else "cuda:0")
     local = checkpoint.resolve_local(model_name)
-    if mode is None and os.environ.get("B2S_USE_8BIT", "0") not in ("", "0"):
-        # the reference's USE_8BIT = True (run_base_vs_instruct_100q.py:84, compare_instruct_models.py:412): LLM.int8 for the
-        # decoder-only models (emulated: shapes.MODE_INT8_EMU); the encoder-decoder scorer has no such mode and keeps its default
-        is_t5 = model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY
-        if local is not None:
-            with open(os.path.join(local, "config.json")) as f:
-                is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
-        mode = shapes.MODE_FP16_FFN_SPLIT if is_t5 else shapes.MODE_INT8_EMU
     if mode is None:
-        is_t5 = model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY
+        # The default is the fastest mode that holds the 2e-3 gate for the model's family at full depth (DESIGN.md 5,
+        # profiles/r2_parity_by_family_full_depth.jsonl): FP16 for Falcon / GPT-NeoX / OPT / BLOOM; the Llama block (Llama-2,
+        # Mistral, Qwen, Baichuan2) is several times more sensitive to the rounding of q/k/v and gets fp32 attention under
+        # hi + lo bf16 GEMM inputs; T5 gets fp16 with the split feed-forward activation.
         if local is not None:
             with open(os.path.join(local, "config.json")) as f:
-                is_t5 = json.load(f).get("model_type") in ("t5", "mt5")
-        mode = shapes.MODE_FP16_FFN_SPLIT if is_t5 else shapes.MODE_FP16
+                mt = json.load(f).get("model_type", "")
+            family = "t5" if mt in ("t5", "mt5") else "llama" if mt in ("llama", "mistral", "qwen", "qwen2", "baichuan") else "other"
+        elif model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY:
+            family = "t5"
+        else:
+            mk = shapes.HUB_TO_SHAPE.get(model_name) or shapes.REGISTRY.get(model_name)
+            family = "llama" if (mk is not None and mk().arch == shapes.ARCH_LLAMA) else "other"
+        if os.environ.get("B2S_USE_8BIT", "0") not in ("", "0") and family != "t5":
+            # the reference's USE_8BIT = True (run_base_vs_instruct_100q.py:84, compare_instruct_models.py:412): LLM.int8 for the
+            # decoder-only models (emulated: shapes.MODE_INT8_EMU); the encoder-decoder scorer has no such mode and keeps its default
+            mode = shapes.MODE_INT8_EMU
+        else:
+            mode = {"t5": shapes.MODE_FP16_FFN_SPLIT, "llama": shapes.MODE_BF16_SPLIT_ATTN32}.get(family, shapes.MODE_FP16)
     # (FP16_FFN_SPLIT wants fp16 matrices except wo in bf16: the checkpoint is read in fp32 and the scorer converts each matrix once)
     dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16,
           shapes.MODE_FP16_FFN_SPLIT: torch.float32}.get(mode, torch.bfloat16)
