@@ -60,6 +60,27 @@ def model_seed(model_name: str) -> int:
     return zlib.crc32(model_name.encode()) & 0x7FFFFFFF
 
 
+def default_mode(model_name: str, local=None) -> int:
+    """The fastest compute mode that holds the 2e-3 gate for the model's family at full depth (DESIGN.md 5,
+    profiles/r2_parity_by_family_full_depth.jsonl): FP16 for Falcon / GPT-NeoX / OPT / BLOOM; the Llama block (Llama-2,
+    Mistral, Qwen, Baichuan2) is an order of magnitude more sensitive to the rounding of q/k/v and gets fp32 attention under
+    hi + lo bf16 GEMM inputs; T5 gets fp16 with the split feed-forward activation.  ``B2S_USE_8BIT=1`` = the reference's
+    USE_8BIT = True (run_base_vs_instruct_100q.py:84, compare_instruct_models.py:412): LLM.int8 for the decoder-only models
+    (emulated: shapes.MODE_INT8_EMU); the encoder-decoder scorer has no such mode and keeps its default."""
+    if local is not None:
+        with open(os.path.join(local, "config.json")) as f:
+            mt = json.load(f).get("model_type", "")
+        family = "t5" if mt in ("t5", "mt5") else "llama" if mt in ("llama", "mistral", "qwen", "qwen2", "baichuan") else "other"
+    elif model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY:
+        family = "t5"
+    else:
+        mk = shapes.HUB_TO_SHAPE.get(model_name) or shapes.REGISTRY.get(model_name)
+        family = "llama" if (mk is not None and mk().arch == shapes.ARCH_LLAMA) else "other"
+    if os.environ.get("B2S_USE_8BIT", "0") not in ("", "0") and family != "t5":
+        return shapes.MODE_INT8_EMU
+    return {"t5": shapes.MODE_FP16_FFN_SPLIT, "llama": shapes.MODE_BF16_SPLIT_ATTN32}.get(family, shapes.MODE_FP16)
+
+
 def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_tokens=None,
                max_seqs: int = 1024):
     """AutoTokenizer/AutoModelForCausalLM.from_pretrained of the reference (:416-450).  A checkpoint that is on disk
@@ -77,25 +98,7 @@ def load_model(model_name: str, device=None, mode=None, n_layer: int = 0, max_to
     device = torch.device(device if device is not None else "cuda:0")
     local = checkpoint.resolve_local(model_name)
     if mode is None:
-        # The default is the fastest mode that holds the 2e-3 gate for the model's family at full depth (DESIGN.md 5,
-        # profiles/r2_parity_by_family_full_depth.jsonl): FP16 for Falcon / GPT-NeoX / OPT / BLOOM; the Llama block (Llama-2,
-        # Mistral, Qwen, Baichuan2) is several times more sensitive to the rounding of q/k/v and gets fp32 attention under
-        # hi + lo bf16 GEMM inputs; T5 gets fp16 with the split feed-forward activation.
-        if local is not None:
-            with open(os.path.join(local, "config.json")) as f:
-                mt = json.load(f).get("model_type", "")
-            family = "t5" if mt in ("t5", "mt5") else "llama" if mt in ("llama", "mistral", "qwen", "qwen2", "baichuan") else "other"
-        elif model_name in t5.HUB_TO_SHAPE or model_name in t5.REGISTRY:
-            family = "t5"
-        else:
-            mk = shapes.HUB_TO_SHAPE.get(model_name) or shapes.REGISTRY.get(model_name)
-            family = "llama" if (mk is not None and mk().arch == shapes.ARCH_LLAMA) else "other"
-        if os.environ.get("B2S_USE_8BIT", "0") not in ("", "0") and family != "t5":
-            # the reference's USE_8BIT = True (run_base_vs_instruct_100q.py:84, compare_instruct_models.py:412): LLM.int8 for the
-            # decoder-only models (emulated: shapes.MODE_INT8_EMU); the encoder-decoder scorer has no such mode and keeps its default
-            mode = shapes.MODE_INT8_EMU
-        else:
-            mode = {"t5": shapes.MODE_FP16_FFN_SPLIT, "llama": shapes.MODE_BF16_SPLIT_ATTN32}.get(family, shapes.MODE_FP16)
+        mode = default_mode(model_name, local)
     # (FP16_FFN_SPLIT wants fp16 matrices except wo in bf16: the checkpoint is read in fp32 and the scorer converts each matrix once)
     dt = {shapes.MODE_FP32_CHECK: torch.float32, shapes.MODE_FP16: torch.float16, shapes.MODE_INT8_EMU: torch.float16,
           shapes.MODE_FP16_FFN_SPLIT: torch.float32}.get(mode, torch.bfloat16)

@@ -115,3 +115,25 @@ def test_perturbation_requests_follow_the_reference_template():
         a, b = S.candidate_ids(tok, "100q", " " + s["target_tokens"][0], " " + s["target_tokens"][1])
         assert a != b
     assert len(E7.build_requests(sc, limit=3)) == 15
+
+
+def test_default_mode_per_family(tmp_path, monkeypatch):
+    """load_model's default: the fastest mode that holds the parity gate for the family (and the reference's 8-bit switch)."""
+    import json
+    from llm_interpretation_replication_b200 import shapes
+    from llm_interpretation_replication_b200.entrypoints.common import default_mode
+    monkeypatch.delenv("B2S_USE_8BIT", raising=False)
+    assert default_mode("tiiuae/falcon-7b-instruct") == shapes.MODE_FP16
+    assert default_mode("togethercomputer/RedPajama-INCITE-7B-Instruct") == shapes.MODE_FP16
+    assert default_mode("bigscience/bloomz-7b1") == shapes.MODE_FP16 and default_mode("facebook/opt-iml-1.3b") == shapes.MODE_FP16
+    for name in ("mistralai/Mistral-7B-Instruct-v0.3", "meta-llama/Llama-2-7b-hf", "Qwen/Qwen-7B-Chat", "baichuan-inc/Baichuan2-7B-Chat"):
+        assert default_mode(name) == shapes.MODE_BF16_SPLIT_ATTN32, name
+    assert default_mode("bigscience/T0_3B") == shapes.MODE_FP16_FFN_SPLIT and default_mode("google/flan-t5-base") == shapes.MODE_FP16_FFN_SPLIT
+    for mt, want in (("mistral", shapes.MODE_BF16_SPLIT_ATTN32), ("t5", shapes.MODE_FP16_FFN_SPLIT), ("gpt_neox", shapes.MODE_FP16)):
+        d = tmp_path / mt
+        d.mkdir()
+        json.dump({"model_type": mt}, open(d / "config.json", "w"))
+        assert default_mode("whatever", str(d)) == want
+    monkeypatch.setenv("B2S_USE_8BIT", "1")
+    assert default_mode("tiiuae/falcon-7b") == shapes.MODE_INT8_EMU and default_mode("meta-llama/Llama-2-7b-hf") == shapes.MODE_INT8_EMU
+    assert default_mode("bigscience/T0_3B") == shapes.MODE_FP16_FFN_SPLIT
